@@ -1,0 +1,223 @@
+"""Generate ``tests/golden/*.npz`` by running the UNMODIFIED reference in the build container.
+
+TEST INFRASTRUCTURE ONLY. Usage (build container only; ``/root/reference`` does not exist on the
+GPU box, which is why the outputs are committed):
+
+    PYTHONPATH=oracle/stubs:/root/reference python oracle/make_golden.py
+
+The stubs under ``oracle/stubs`` stand in for ``pytorch_lightning`` / ``torchmetrics`` / ``fire``
+(absent from this image); they contribute no arithmetic. Everything numerical below is computed by
+``collie`` (v1.3.1) + torch (2.11.0 here; the reference pins 1.13.1).
+"""
+import os
+import sys
+from functools import partial
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+OUT = os.path.join(os.path.dirname(HERE), 'tests', 'golden')
+
+import collie  # noqa: E402  (the reference)
+from collie.interactions import ExplicitInteractions, Interactions  # noqa: E402
+from collie.metrics import auc, evaluate_in_batches, mapk, mrr  # noqa: E402
+from collie.model import MatrixFactorizationModel  # noqa: E402
+
+assert collie.__file__.startswith('/root/reference'), collie.__file__
+
+
+def synthetic_pairs(rng, n_users, n_items, n):
+    flat = rng.choice(n_users * n_items, size=n, replace=False)
+    return (flat // n_items).astype(np.int64), (flat % n_items).astype(np.int64)
+
+
+def randomize(model, rng, scale=0.5):
+    with torch.no_grad():
+        for p in model.parameters():
+            p.copy_(torch.from_numpy(rng.normal(0, scale, size=tuple(p.shape)).astype(np.float32)))
+
+
+def state(model):
+    return {
+        'U': model.user_embeddings.weight.detach().numpy().copy(),
+        'I': model.item_embeddings.weight.detach().numpy().copy(),
+        'bu': model.user_biases.weight.detach().numpy().copy(),
+        'bi': model.item_biases.weight.detach().numpy().copy(),
+    }
+
+
+def implicit_case(loss, n_neg, optimizer, sparse, seed, with_metadata=False, dim=16,
+                  n_users=37, n_items=53, n_inter=400, batch=64, steps=3):
+    rng = np.random.default_rng(seed)
+    torch.manual_seed(seed)
+    users, items = synthetic_pairs(rng, n_users, n_items, n_inter)
+    train = Interactions(users=users, items=items, ratings=np.ones(n_inter),
+                         num_negative_samples=n_neg, num_users=n_users, num_items=n_items,
+                         allow_missing_ids=True, remove_duplicate_user_item_pairs=False,
+                         check_num_negative_samples_is_valid=False)
+    kwargs = {}
+    meta = {}
+    if with_metadata:
+        meta = {'a': rng.integers(0, 3, size=n_items), 'b': rng.integers(0, 4, size=n_items)}
+        kwargs = dict(metadata_for_loss={k: torch.from_numpy(v) for k, v in meta.items()},
+                      metadata_for_loss_weights={'a': 0.2, 'b': 0.3})
+    model = MatrixFactorizationModel(train=train, embedding_dim=dim, sparse=sparse, lr=1e-2,
+                                     bias_lr=5e-2, optimizer=optimizer, bias_optimizer='sgd',
+                                     loss=loss, lr_scheduler_func=None, **kwargs)
+    randomize(model, rng)
+    out = {'n_users': n_users, 'n_items': n_items, 'dim': dim, 'n_neg': n_neg,
+           'loss_name': model.loss_function.__name__, 'lr': 1e-2, 'bias_lr': 5e-2}
+    for k, v in meta.items():
+        out['meta_' + k] = v
+    for k, v in state(model).items():
+        out['init_' + k] = v
+
+    optimizers = model.configure_optimizers()
+    if isinstance(optimizers, tuple):
+        optimizers = optimizers[0]
+    if not isinstance(optimizers, (list, tuple)):
+        optimizers = [optimizers]
+    model.train()
+    for s in range(steps):
+        bu_ = rng.integers(0, n_users, size=batch)
+        bp_ = rng.integers(0, n_items, size=batch)
+        bn_ = rng.integers(0, n_items, size=(batch, n_neg))
+        batch_t = ((torch.from_numpy(bu_.astype(np.int32)), torch.from_numpy(bp_.astype(np.int32))),
+                   torch.from_numpy(bn_))
+        for opt in optimizers:
+            opt.zero_grad()
+        loss_t = model.calculate_loss(batch_t)
+        if s == 0:
+            with torch.no_grad():
+                out['step0_pos_scores'] = model(batch_t[0][0].long(), batch_t[0][1].long()).numpy()
+        loss_t.backward()
+        if s == 0:
+            for name, p in (('U', model.user_embeddings.weight), ('I', model.item_embeddings.weight),
+                            ('bu', model.user_biases.weight), ('bi', model.item_biases.weight)):
+                g = p.grad
+                out['step0_grad_' + name] = (g.to_dense() if g.is_sparse else g).numpy().copy()
+        for i, opt in enumerate(optimizers):
+            model.optimizer_step(epoch=0, batch_idx=s, optimizer=opt, optimizer_idx=i)
+        out[f'step{s}_users'] = bu_
+        out[f'step{s}_pos'] = bp_
+        out[f'step{s}_negs'] = bn_
+        out[f'step{s}_loss'] = np.float64(loss_t.item())
+    for k, v in state(model).items():
+        out['final_' + k] = v
+    out['steps'] = steps
+    return out
+
+
+def explicit_case(loss, optimizer, sparse, seed, y_range=None, dim=16, n_users=29, n_items=41,
+                  n_inter=300, batch=48, steps=3):
+    rng = np.random.default_rng(seed)
+    users, items = synthetic_pairs(rng, n_users, n_items, n_inter)
+    ratings = rng.integers(1, 6, size=n_inter).astype(np.float64)
+    train = ExplicitInteractions(users=users, items=items, ratings=ratings, num_users=n_users,
+                                 num_items=n_items, allow_missing_ids=True,
+                                 remove_duplicate_user_item_pairs=False)
+    model = MatrixFactorizationModel(train=train, embedding_dim=dim, sparse=sparse, lr=1e-2,
+                                     bias_lr=5e-2, optimizer=optimizer, bias_optimizer='sgd',
+                                     loss=loss, y_range=y_range, lr_scheduler_func=None)
+    randomize(model, rng)
+    out = {'n_users': n_users, 'n_items': n_items, 'dim': dim, 'lr': 1e-2, 'bias_lr': 5e-2,
+           'y_range': np.array(y_range if y_range is not None else [np.nan, np.nan])}
+    for k, v in state(model).items():
+        out['init_' + k] = v
+    optimizers = model.configure_optimizers()
+    if not isinstance(optimizers, (list, tuple)):
+        optimizers = [optimizers]
+    for s in range(steps):
+        bu_ = rng.integers(0, n_users, size=batch)
+        bi_ = rng.integers(0, n_items, size=batch)
+        br_ = rng.integers(1, 6, size=batch).astype(np.float32)
+        batch_t = (torch.from_numpy(bu_.astype(np.int32)), torch.from_numpy(bi_.astype(np.int32)),
+                   torch.from_numpy(br_))
+        for opt in optimizers:
+            opt.zero_grad()
+        loss_t = model.calculate_loss(batch_t)
+        loss_t.backward()
+        if s == 0:
+            for name, p in (('U', model.user_embeddings.weight), ('I', model.item_embeddings.weight),
+                            ('bu', model.user_biases.weight), ('bi', model.item_biases.weight)):
+                g = p.grad
+                out['step0_grad_' + name] = (g.to_dense() if g.is_sparse else g).numpy().copy()
+        for i, opt in enumerate(optimizers):
+            model.optimizer_step(epoch=0, batch_idx=s, optimizer=opt, optimizer_idx=i)
+        out[f'step{s}_users'], out[f'step{s}_items'], out[f'step{s}_ratings'] = bu_, bi_, br_
+        out[f'step{s}_loss'] = np.float64(loss_t.item())
+    for k, v in state(model).items():
+        out['final_' + k] = v
+    out['steps'] = steps
+    return out
+
+
+def metrics_case(seed, n_users=37, n_items=101, dim=12, n_test=260, exact_grid=False):
+    rng = np.random.default_rng(seed)
+    users, items = synthetic_pairs(rng, n_users, n_items, n_test)
+    keep = users != 5                  # one user without test interactions
+    users, items = users[keep], items[keep]
+    test = Interactions(users=users, items=items, ratings=np.ones(len(users)), num_users=n_users,
+                        num_items=n_items, allow_missing_ids=True,
+                        remove_duplicate_user_item_pairs=False,
+                        check_num_negative_samples_is_valid=False)
+    model = MatrixFactorizationModel(train=test, embedding_dim=dim, lr_scheduler_func=None)
+    if exact_grid:
+        # exactly representable weights (multiples of 2^-2 in [-1, 1]): any summation order and any
+        # bf16-split tensor-core product gives the same fp32 scores, with many genuine ties
+        with torch.no_grad():
+            for p in model.parameters():
+                p.copy_(torch.from_numpy(
+                    (rng.integers(-4, 5, size=tuple(p.shape)) / 4.0).astype(np.float32)))
+    else:
+        randomize(model, rng, scale=0.7)
+    model.eval()
+    out = {'n_users': n_users, 'n_items': n_items, 'dim': dim, 'test_users': users,
+           'test_items': items}
+    for k, v in state(model).items():
+        out[k] = v
+    for k_ in (1, 4, 10):
+        for bs in (20, 7):
+            res = evaluate_in_batches([mapk, mrr, auc], test, model, k=k_, batch_size=bs,
+                                      verbose=False)
+            out[f'k{k_}_bs{bs}'] = np.array(res, dtype=np.float64)
+    with torch.no_grad():
+        uu = torch.arange(n_users).repeat_interleave(n_items)
+        ii = torch.arange(n_items).repeat(n_users)
+        out['scores'] = model(uu, ii).view(n_users, n_items).numpy()
+    return out
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    cases = {
+        'implicit_bpr_n1_sparse_adam': implicit_case('bpr', 1, 'sparse_adam', True, 11),
+        'implicit_hinge_n1_adam': implicit_case('hinge', 1, 'adam', False, 12),
+        'implicit_adaptive_bpr_n5_sparse_adam': implicit_case('bpr', 5, 'sparse_adam', True, 13),
+        'implicit_adaptive_hinge_n10_adam': implicit_case('adaptive', 10, 'adam', False, 14),
+        'implicit_warp_n7_sparse_adam': implicit_case('warp', 7, 'sparse_adam', True, 15),
+        'implicit_warp_n4_sgd': implicit_case('warp', 4, 'sgd', False, 16),
+        'implicit_adaptive_hinge_meta_n5': implicit_case('adaptive_hinge', 5, 'sparse_adam', True,
+                                                         17, with_metadata=True),
+        'implicit_warp_meta_n6': implicit_case('warp', 6, 'adam', False, 18, with_metadata=True),
+        'implicit_adaptive_bpr_d10_n5': implicit_case('bpr', 5, 'adam', False, 19, dim=10),
+        'implicit_adaptive_bpr_d30_n3': implicit_case('bpr', 3, 'sparse_adam', True, 20, dim=30),
+        'implicit_adaptive_bpr_d128_n5': implicit_case('bpr', 5, 'sparse_adam', True, 21, dim=128),
+        'implicit_hinge_adagrad': implicit_case('hinge', 1, 'adagrad', False, 22),
+        'explicit_mse_adam': explicit_case('mse', 'adam', False, 31),
+        'explicit_mse_sparse_adam_d64': explicit_case('mse', 'sparse_adam', True, 32, dim=64),
+        'explicit_mae_sgd': explicit_case('mae', 'sgd', False, 33),
+        'explicit_mse_yrange': explicit_case('mse', 'adam', False, 34, y_range=(1.0, 5.0)),
+        'metrics_random': metrics_case(41),
+        'metrics_exact_grid': metrics_case(42, exact_grid=True),
+        'metrics_d128': metrics_case(43, n_users=64, n_items=333, dim=128, n_test=700),
+    }
+    for name, arrays in cases.items():
+        np.savez_compressed(os.path.join(OUT, name + '.npz'), **arrays)
+        print(name, 'ok')
+    print('torch', torch.__version__, 'collie', collie.__version__, file=sys.stderr)
+
+
+if __name__ == '__main__':
+    main()
