@@ -1,0 +1,25 @@
+# Builds the C-ABI library (sm_100a only) and nothing else.
+NVCC      ?= nvcc
+ARCH      := -gencode arch=compute_100a,code=sm_100a
+NVCCFLAGS := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -fvisibility=hidden \
+             --expt-relaxed-constexpr -Iinclude
+SRC_DIR   := collie_b200/csrc
+OBJ_DIR   := build/obj
+LIB       := collie_b200/lib/libcollie_b200.so
+SRCS      := $(wildcard $(SRC_DIR)/*.cu)
+OBJS      := $(patsubst $(SRC_DIR)/%.cu,$(OBJ_DIR)/%.o,$(SRCS))
+
+all: $(LIB)
+
+$(OBJ_DIR)/%.o: $(SRC_DIR)/%.cu $(SRC_DIR)/common.cuh include/collie_b200.h
+	@mkdir -p $(OBJ_DIR)
+	$(NVCC) $(NVCCFLAGS) -c $< -o $@
+
+$(LIB): $(OBJS)
+	@mkdir -p $(dir $(LIB))
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lcuda
+
+clean:
+	rm -rf build $(LIB)
+
+.PHONY: all clean

@@ -1,0 +1,24 @@
+"""collie_b200: the matrix-factorization training + evaluation hot path of ShopRunner/collie,
+rebuilt for NVIDIA B200 (sm_100a) behind Collie's own API for that path.
+
+    from collie_b200 import (Interactions, MatrixFactorizationModel, CollieTrainer,
+                             evaluate_in_batches, mapk, mrr, auc)
+
+All arithmetic runs in ``lib/libcollie_b200.so`` (``include/collie_b200.h``); there is no CPU or
+PyTorch fallback -- a missing library or a non-CUDA tensor raises.
+"""
+from . import _abi
+from .interactions import (ApproximateNegativeSamplingInteractionsDataLoader,
+                           ExplicitInteractions, Interactions, InteractionsDataLoader)
+from .metrics import auc, evaluate_in_batches, get_preds, mapk, mrr
+from .model import (MatrixFactorizationModel, RowOptimizer, ScaledEmbedding, ZeroEmbedding)
+from .trainer import CollieMinimalTrainer, CollieTrainer
+
+__version__ = '0.1.0'
+
+__all__ = [
+    'ApproximateNegativeSamplingInteractionsDataLoader', 'CollieMinimalTrainer', 'CollieTrainer',
+    'ExplicitInteractions', 'Interactions', 'InteractionsDataLoader', 'MatrixFactorizationModel',
+    'RowOptimizer', 'ScaledEmbedding', 'ZeroEmbedding', 'auc', 'evaluate_in_batches', 'get_preds',
+    'mapk', 'mrr',
+]

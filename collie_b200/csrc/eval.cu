@@ -1,0 +1,332 @@
+// Evaluation, exact-fp32 path: tiled SIMT scoring of a user tile against the item table, then one
+// CTA per user ranks its score row (top-k in canonical order, MAP@k, best-target rank for MRR,
+// Mann-Whitney pair count for AUC).
+//
+// Reference: collie/metrics.py  get_preds :77-107, mapk :144-198, mrr :201-240, auc :243-282,
+// one iteration of the evaluate_in_batches loop :379-384.
+// Canonical order everywhere: score descending, item id ascending (torch.topk's tie order is
+// unpinned in the reference).
+#include "common.cuh"
+
+namespace cmf {
+
+int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s);  // eval_tc.cu (tcgen05 path)
+
+// ------------------------------------------------------------------ scores: 64x64 tile, K step 16
+constexpr int TM = 64, TN = 64, TK = 16;
+
+__global__ void __launch_bounds__(256)
+k_score_tile(const float* __restrict__ U, const float* __restrict__ I, const float* __restrict__ bu,
+             const float* __restrict__ bi, int D, const int32_t* __restrict__ user_ids, int64_t n_users,
+             int64_t item_offset, int64_t n_items, float* __restrict__ out, int64_t ld_out) {
+  __shared__ float As[TK][TM + 4];
+  __shared__ float Bs[TK][TN + 4];
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;  // 16 x 16 threads, 4x4 outputs each
+  const int64_t row0 = (int64_t)blockIdx.y * TM, col0 = (int64_t)blockIdx.x * TN;
+  float acc[4][4] = {};
+  // loader mapping: 256 threads fetch 64 rows x 16 k-values; thread -> (row = t / 4, 4 k's)
+  const int lr = threadIdx.x >> 2, lk = (threadIdx.x & 3) * 4;
+  const int64_t arow = row0 + lr, brow = col0 + lr;
+  const float* aptr = (arow < n_users) ? U + (int64_t)user_ids[arow] * D : nullptr;
+  const float* bptr = (brow < n_items) ? I + (item_offset + brow) * D : nullptr;
+  for (int k0 = 0; k0 < D; k0 += TK) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int d = k0 + lk + j;
+      As[lk + j][lr] = (aptr && d < D) ? aptr[d] : 0.f;
+      Bs[lk + j][lr] = (bptr && d < D) ? bptr[d] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < TK; ++k) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { a[i] = As[k][ty * 4 + i]; b[i] = Bs[k][tx * 4 + i]; }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int64_t r = row0 + ty * 4 + i;
+    if (r >= n_users) continue;
+    const float ub = bu[user_ids[r]];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t c = col0 + tx * 4 + j;
+      if (c < n_items) out[r * ld_out + c] = acc[i][j] + ub + bi[item_offset + c];
+    }
+  }
+}
+
+// ------------------------------------------------------------------ ranking: one CTA per user row
+struct Key {
+  float s;
+  int id;
+};
+// canonical order: a before b  <=>  a.s > b.s or (a.s == b.s and a.id < b.id)
+__device__ __forceinline__ bool before(const Key& a, const Key& b) {
+  return a.s > b.s || (a.s == b.s && a.id < b.id);
+}
+
+__device__ __forceinline__ Key block_best(Key v, Key* s_red) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    Key w;
+    w.s = __shfl_xor_sync(0xffffffffu, v.s, o);
+    w.id = __shfl_xor_sync(0xffffffffu, v.id, o);
+    if (w.id >= 0 && (v.id < 0 || before(w, v))) v = w;
+  }
+  if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  Key r = s_red[0];
+  for (int w = 1; w < (int)(blockDim.x >> 5); ++w) {
+    const Key c = s_red[w];
+    if (c.id >= 0 && (r.id < 0 || before(c, r))) r = c;
+  }
+  __syncthreads();
+  return r;
+}
+
+template <typename T>
+__device__ __forceinline__ T block_sum(T v, T* s_red) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  T r = 0;
+  for (int w = 0; w < (int)(blockDim.x >> 5); ++w) r += s_red[w];
+  __syncthreads();
+  return r;
+}
+
+constexpr int kSigSmem = 2048;
+
+struct RankDev {
+  const float* S;  // [n, ld]
+  int64_t ld, n_items, item_offset;
+  int k;
+  const int64_t* tgt_indptr;
+  const int32_t* tgt_items;
+  int want_mrr, want_auc;
+  const float* ext_best_score;
+  const int32_t* ext_best_id;
+  int32_t* topk_ids;
+  float* topk_scores;
+  double* ap;
+  int32_t* n_before_best;
+  float* best_score;
+  int32_t* best_id;
+  double* auc_pairs;
+  float* sig_scratch;  // [total targets of the tile], same offsets as tgt_items (minus indptr[0])
+};
+
+__global__ void __launch_bounds__(256)
+k_rank_rows(const RankDev p) {
+  __shared__ Key s_key[8];
+  __shared__ long long s_ll[8];
+  __shared__ double s_dbl[8];
+  __shared__ float s_sig[kSigSmem];
+  __shared__ float s_raw[kSigSmem];
+  const int r = blockIdx.x;
+  const float* row = p.S + (int64_t)r * p.ld;
+  const int64_t t0 = p.tgt_indptr ? p.tgt_indptr[r] : 0, t1 = p.tgt_indptr ? p.tgt_indptr[r + 1] : 0;
+  const int n_tgt = (int)(t1 - t0);
+  const int32_t* tgt = p.tgt_items + t0;
+  const int lo_id = (int)p.item_offset, hi_id = (int)(p.item_offset + p.n_items);
+
+  // ---- top-k: k selection passes, each finds the best key strictly after the previous one
+  if (p.topk_ids || p.topk_scores || p.ap) {
+    int hits = 0;
+    double ap_acc = 0.0;
+    Key prev;
+    prev.s = INFINITY;
+    prev.id = -1;
+    for (int j = 0; j < p.k; ++j) {
+      Key best;
+      best.s = -INFINITY;
+      best.id = -1;
+      for (int64_t c = threadIdx.x; c < p.n_items; c += blockDim.x) {
+        Key cur;
+        cur.s = row[c];
+        cur.id = (int)(p.item_offset + c);
+        const bool after_prev = (prev.id < 0) || before(prev, cur);
+        if (after_prev && (best.id < 0 || before(cur, best))) best = cur;
+      }
+      best = block_best(best, s_key);
+      if (threadIdx.x == 0) {
+        if (p.topk_ids) p.topk_ids[(int64_t)r * p.k + j] = best.id;
+        if (p.topk_scores) p.topk_scores[(int64_t)r * p.k + j] = best.id >= 0 ? best.s : -INFINITY;
+        if (best.id >= 0 && csr_contains(tgt, 0, n_tgt, best.id)) {
+          ++hits;
+          ap_acc += (double)hits / (double)(j + 1);
+        }
+      }
+      prev = best;
+      if (best.id < 0) {  // fewer than k items in this shard: pad
+        if (threadIdx.x == 0)
+          for (int jj = j + 1; jj < p.k; ++jj) {
+            if (p.topk_ids) p.topk_ids[(int64_t)r * p.k + jj] = -1;
+            if (p.topk_scores) p.topk_scores[(int64_t)r * p.k + jj] = -INFINITY;
+          }
+        break;
+      }
+    }
+    if (threadIdx.x == 0 && p.ap) {
+      // AP@k = sum_j acc_j * cumsum_j / j / min(k, nnz_u); 0 when the user has no targets
+      const int denom = p.k < n_tgt ? p.k : n_tgt;
+      p.ap[r] = denom > 0 ? ap_acc / (double)denom : 0.0;
+    }
+  }
+
+  // ---- MRR ingredient: the best-ranked target and how many items precede it
+  if (p.want_mrr) {
+    Key best;
+    best.s = -INFINITY;
+    best.id = -1;
+    for (int t = threadIdx.x; t < n_tgt; t += blockDim.x) {
+      const int id = tgt[t];
+      if (id < lo_id || id >= hi_id) continue;
+      Key cur;
+      cur.s = row[id - lo_id];
+      cur.id = id;
+      if (best.id < 0 || before(cur, best)) best = cur;
+    }
+    best = block_best(best, s_key);
+    if (threadIdx.x == 0) {
+      if (p.best_score) p.best_score[r] = best.id >= 0 ? best.s : -INFINITY;
+      if (p.best_id) p.best_id[r] = best.id;
+    }
+    if (p.ext_best_id) {
+      best.id = p.ext_best_id[r];
+      best.s = p.ext_best_score[r];
+    }
+    long long cnt = 0;
+    if (best.id >= 0) {
+      for (int64_t c = threadIdx.x; c < p.n_items; c += blockDim.x) {
+        Key cur;
+        cur.s = row[c];
+        cur.id = (int)(p.item_offset + c);
+        cnt += before(cur, best) ? 1 : 0;
+      }
+    }
+    cnt = block_sum<long long>(cnt, s_ll);
+    if (threadIdx.x == 0 && p.n_before_best) p.n_before_best[r] = best.id >= 0 ? (int)cnt : -1;
+  }
+
+  // ---- AUC ingredient: sum over targets of (#non-targets with lower sigmoid + ties / 2)
+  if (p.want_auc) {
+    double total = 0.0;
+    if (n_tgt > 0) {
+      const bool in_smem = n_tgt <= kSigSmem;
+      float* sig = in_smem ? s_sig : p.sig_scratch + 2 * (t0 - p.tgt_indptr[0]);
+      float* raw = in_smem ? s_raw : sig + n_tgt;
+      for (int t = threadIdx.x; t < n_tgt; t += blockDim.x) raw[t] = sigmoidf_(row[tgt[t] - lo_id]);
+      __syncthreads();
+      // rank-sort the targets' sigmoids (ascending) by counting
+      for (int t = threadIdx.x; t < n_tgt; t += blockDim.x) {
+        const float v = raw[t];
+        int rank = 0;
+        for (int q = 0; q < n_tgt; ++q) {
+          const float w = raw[q];
+          rank += (w < v || (w == v && q < t)) ? 1 : 0;
+        }
+        sig[rank] = v;
+      }
+      __syncthreads();
+      // every item adds (#targets above it) + (#targets equal to it) / 2
+      for (int64_t c = threadIdx.x; c < p.n_items; c += blockDim.x) {
+        const float v = sigmoidf_(row[c]);
+        int lo = 0, hi = n_tgt;  // lower_bound
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (sig[mid] < v) lo = mid + 1; else hi = mid; }
+        const int lb = lo;
+        hi = n_tgt;              // upper_bound
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (sig[mid] <= v) lo = mid + 1; else hi = mid; }
+        total += (double)(n_tgt - lo) + 0.5 * (double)(lo - lb);
+      }
+    }
+    total = block_sum<double>(total, s_dbl);
+    // target-target pairs (self pairs included) contribute exactly n_tgt^2 / 2
+    if (threadIdx.x == 0 && p.auc_pairs)
+      p.auc_pairs[r] = n_tgt > 0 ? total - 0.5 * (double)n_tgt * (double)n_tgt : 0.0;
+  }
+}
+
+static size_t eval_ws_scores(int64_t n, int64_t items) { return align_up(sizeof(float) * n * items, 256); }
+
+}  // namespace cmf
+
+using namespace cmf;
+
+extern "C" size_t cmf_eval_workspace_bytes(int64_t n_users_tile, int64_t num_items_shard, int32_t D,
+                                           int32_t k, int32_t precision) {
+  (void)D; (void)k; (void)precision;
+  if (n_users_tile < 1 || num_items_shard < 1) return 0;
+  // score tile + sigmoid scratch for users with more than kSigSmem targets (bounded by the shard)
+  return eval_ws_scores(n_users_tile, num_items_shard) +
+         align_up(2 * sizeof(float) * n_users_tile * num_items_shard, 256);
+}
+
+extern "C" int cmf_score_tile(const float* U, const float* I, const float* bu, const float* bi,
+                              int32_t D, const int32_t* user_ids, int64_t n_users_tile,
+                              int64_t num_items, float* out, void* stream) {
+  CMF_REQUIRE(U && I && bu && bi && out, "cmf_score_tile: null pointer");
+  CMF_REQUIRE(D >= 1, "cmf_score_tile: bad embedding_dim");
+  if (n_users_tile == 0 || num_items == 0) return CMF_OK;
+  CMF_REQUIRE(user_ids, "cmf_score_tile: null user ids");
+  dim3 grid((unsigned)((num_items + TN - 1) / TN), (unsigned)((n_users_tile + TM - 1) / TM));
+  k_score_tile<<<grid, 256, 0, (cudaStream_t)stream>>>(U, I, bu, bi, D, user_ids, n_users_tile, 0,
+                                                       num_items, out, num_items);
+  CMF_LAUNCH_CHECK();
+  return CMF_OK;
+}
+
+extern "C" int cmf_eval_tile(const cmf_eval_t* a, void* stream) {
+  CMF_REQUIRE(a, "cmf_eval_tile: null args");
+  CMF_REQUIRE(a->scores_in || (a->U && a->I && a->bu && a->bi),
+              "cmf_eval_tile: null parameter table");
+  CMF_REQUIRE(a->scores_in || a->D >= 1, "cmf_eval_tile: bad embedding_dim");
+  CMF_REQUIRE(a->n_users_tile >= 0 && a->num_items_shard >= 1 && a->item_offset >= 0,
+              "cmf_eval_tile: bad tile shape");
+  CMF_REQUIRE(a->k >= 1, "cmf_eval_tile: k must be >= 1");
+  if (a->n_users_tile == 0) return CMF_OK;
+  CMF_REQUIRE(a->scores_in || a->user_ids, "cmf_eval_tile: null user ids");
+  CMF_REQUIRE(a->tgt_indptr && a->tgt_items, "cmf_eval_tile: target CSR required");
+  CMF_REQUIRE(!a->want_auc || a->item_offset == 0,
+              "cmf_eval_tile: AUC needs the whole item table in one shard (item_offset must be 0)");
+  CMF_REQUIRE((a->ext_best_id == nullptr) == (a->ext_best_score == nullptr),
+              "cmf_eval_tile: ext_best_score and ext_best_id go together");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (a->precision == 1 && !a->scores_in) return eval_tile_tc(a, s);
+  CMF_REQUIRE(a->precision == 0 || a->scores_in, "cmf_eval_tile: unknown precision %d",
+              a->precision);
+  const size_t need = cmf_eval_workspace_bytes(a->n_users_tile, a->num_items_shard, a->D, a->k, 0);
+  if (!a->workspace || a->workspace_bytes < need)
+    return fail(CMF_ERR_WORKSPACE, "cmf_eval_tile: workspace of %zu bytes needed, %zu given", need,
+                a->workspace ? a->workspace_bytes : (size_t)0);
+  const float* S = a->scores_in;
+  float* sig = (float*)((char*)a->workspace + eval_ws_scores(a->n_users_tile, a->num_items_shard));
+  if (!S) {
+    float* Sw = (float*)a->workspace;
+    dim3 grid((unsigned)((a->num_items_shard + TN - 1) / TN),
+              (unsigned)((a->n_users_tile + TM - 1) / TM));
+    k_score_tile<<<grid, 256, 0, s>>>(a->U, a->I, a->bu, a->bi, a->D, a->user_ids, a->n_users_tile,
+                                      a->item_offset, a->num_items_shard, Sw, a->num_items_shard);
+    CMF_LAUNCH_CHECK();
+    S = Sw;
+  }
+  RankDev p{};
+  p.S = S; p.ld = a->num_items_shard; p.n_items = a->num_items_shard; p.item_offset = a->item_offset;
+  p.k = a->k; p.tgt_indptr = a->tgt_indptr; p.tgt_items = a->tgt_items;
+  p.want_mrr = a->want_mrr; p.want_auc = a->want_auc;
+  p.ext_best_score = a->ext_best_score; p.ext_best_id = a->ext_best_id;
+  p.topk_ids = a->topk_ids; p.topk_scores = a->topk_scores; p.ap = a->ap;
+  p.n_before_best = a->n_before_best; p.best_score = a->best_score; p.best_id = a->best_id;
+  p.auc_pairs = a->auc_pairs; p.sig_scratch = sig;
+  k_rank_rows<<<(unsigned)a->n_users_tile, 256, 0, s>>>(p);
+  CMF_LAUNCH_CHECK();
+  return CMF_OK;
+}

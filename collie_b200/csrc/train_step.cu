@@ -1,0 +1,777 @@
+// Fused MF training step: on-device negative sampling + gather + scores + loss + backward +
+// in-place row optimizer for whole user segments, vector-RED item gradients, and one row-update
+// kernel for everything that could not be finished in place.
+//
+// Reference call sites replaced (one iteration of collie/model/base/trainer.py:458-470):
+//   Interactions._negative_sample        collie/interactions/datasets.py:390-445
+//   BasePipeline.calculate_loss          collie/model/base/base_pipeline.py:582-654
+//   MatrixFactorizationModel.forward x2  collie/model/matrix_factorization.py:120-159
+//   losses                               collie/loss/{bpr,hinge,warp,metadata_utils}.py
+//   loss.backward() + optimizer.step()   torch autograd / torch.optim.{SparseAdam,Adam,SGD,Adagrad}
+//
+// Work decomposition: the batch is ordered by user (radix sort of <=B 32-bit keys);
+// the ordered batch is cut into chunks of L consecutive interactions; one G-lane group walks one
+// chunk. A user whose interactions all lie inside one chunk is finished in place (its row, Adam
+// moments and bias are read once and written once, no atomics, no gradient scratch). Users that
+// straddle a chunk boundary, and all item rows, accumulate into dense fp32 gradient tables with
+// vector RED operations and are finished by k_update_rows, which walks the de-duplicated lists of
+// touched rows. Every chunk has the same amount of work, so the grid is balanced whatever the skew.
+#include <cub/device/device_radix_sort.cuh>
+
+#include <cmath>
+#include <cstdlib>
+
+#include "common.cuh"
+
+namespace cmf {
+
+constexpr int kMaxNeg = 64;          // negatives per interaction supported by the fused step
+constexpr int kMaxPartials = 8192;   // upper bound on the fused kernel's grid size
+constexpr int kThreads = 256;
+
+struct WsHeader {
+  int item_count;
+  int user_count;
+  unsigned blocks_done;
+  int pad[61];
+};
+static_assert(sizeof(WsHeader) == 256, "header is one 256-byte line group");
+
+struct WsLayout {
+  // persistent (zero between steps; the kernels restore the invariant)
+  size_t item_flag, user_flag, GI, gbi, GU, gbu, persistent_end;
+  // per step
+  size_t hdr, partials, item_list, user_list, keys_out, vals_in, vals_out, iota, cub_temp;
+  size_t cub_temp_bytes, total;
+};
+
+static size_t cub_sort_bytes(int64_t B) {
+  size_t bytes = 0;
+  cub::DeviceRadixSort::SortPairs((void*)nullptr, bytes, (const uint32_t*)nullptr,
+                                  (uint32_t*)nullptr, (const uint32_t*)nullptr, (uint32_t*)nullptr,
+                                  (int)B, 0, 32, (cudaStream_t)0);
+  return bytes;
+}
+
+static WsLayout ws_layout(int64_t B, int64_t num_users, int64_t num_items, int D) {
+  WsLayout w;
+  size_t o = 0;
+  auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes, 256); return at; };
+  w.item_flag = take(sizeof(int) * num_items);
+  w.user_flag = take(sizeof(int) * num_users);
+  w.GI = take(sizeof(float) * num_items * D);
+  w.gbi = take(sizeof(float) * num_items);
+  w.GU = take(sizeof(float) * num_users * D);
+  w.gbu = take(sizeof(float) * num_users);
+  w.persistent_end = o;
+  w.hdr = take(sizeof(WsHeader));
+  w.partials = take(sizeof(double) * kMaxPartials);
+  w.item_list = take(sizeof(int) * num_items);
+  w.user_list = take(sizeof(int) * num_users);
+  w.keys_out = take(sizeof(uint32_t) * B);
+  w.vals_out = take(sizeof(uint32_t) * B);
+  w.iota = take(sizeof(uint32_t) * B);
+  w.cub_temp_bytes = cub_sort_bytes(B);
+  w.cub_temp = take(w.cub_temp_bytes);
+  w.total = o;
+  return w;
+}
+
+// ------------------------------------------------------------------------------- optimizer rules
+struct OptDev {
+  int rule;
+  int dense;        // every row of the table moves each step
+  float lr, wd, eps;
+  float b2;         // Adam: beta2
+  float omb1, omb2; // 1 - beta
+  float step_size;  // SparseAdam: lr*sqrt(1-b2^t)/(1-b1^t); Adam: lr/(1-b1^t)
+  float bc2_sqrt;   // Adam: sqrt(1-b2^t)
+};
+
+static OptDev make_opt(const cmf_opt_t& o) {
+  OptDev d{};
+  d.rule = o.rule;
+  d.lr = (float)o.lr;
+  d.wd = (float)o.weight_decay;
+  d.eps = (float)(o.rule == CMF_OPT_ADAGRAD ? 1e-10 : o.eps);
+  d.b2 = (float)o.beta2;
+  d.omb1 = (float)(1.0 - o.beta1);
+  d.omb2 = (float)(1.0 - o.beta2);
+  const double t = (double)(o.step < 1 ? 1 : o.step);
+  const double bc1 = 1.0 - std::pow(o.beta1, t), bc2 = 1.0 - std::pow(o.beta2, t);
+  if (o.rule == CMF_OPT_SPARSE_ADAM) d.step_size = (float)(o.lr * std::sqrt(bc2) / bc1);
+  if (o.rule == CMF_OPT_ADAM) { d.step_size = (float)(o.lr / bc1); d.bc2_sqrt = (float)std::sqrt(bc2); }
+  d.dense = (o.rule == CMF_OPT_ADAM) || (o.weight_decay != 0.0);
+  return d;
+}
+
+// One parameter element. m/v are the rule's state (Adagrad keeps its sum in m).
+__device__ __forceinline__ void apply_rule(const OptDev& o, float& p, float& m, float& v, float g) {
+  switch (o.rule) {
+    case CMF_OPT_SPARSE_ADAM: {  // torch/optim/sparse_adam.py (functional sparse_adam)
+      const float mn = m + (g - m) * o.omb1;
+      const float vn = v + (g * g - v) * o.omb2;
+      m = mn;
+      v = vn;
+      p = p - o.step_size * (mn / (sqrtf(vn) + o.eps));
+      break;
+    }
+    case CMF_OPT_ADAM: {  // torch/optim/adam.py _single_tensor_adam
+      if (o.wd != 0.f) g = g + o.wd * p;
+      m = m + o.omb1 * (g - m);
+      v = v * o.b2 + (o.omb2 * g) * g;
+      const float denom = sqrtf(v) / o.bc2_sqrt + o.eps;
+      p = p - o.step_size * (m / denom);
+      break;
+    }
+    case CMF_OPT_ADAGRAD: {  // torch/optim/adagrad.py _single_tensor_adagrad
+      if (o.wd != 0.f) g = g + o.wd * p;
+      m = m + g * g;
+      p = p - o.lr * (g / (sqrtf(m) + o.eps));
+      break;
+    }
+    default: {  // SGD
+      if (o.wd != 0.f) g = g + o.wd * p;
+      p = p - o.lr * g;
+      break;
+    }
+  }
+}
+
+__device__ __forceinline__ bool rule_has_m(int rule) { return rule != CMF_OPT_SGD; }
+__device__ __forceinline__ bool rule_has_v(int rule) {
+  return rule == CMF_OPT_SPARSE_ADAM || rule == CMF_OPT_ADAM;
+}
+
+template <int V, int G, int R>
+__device__ __forceinline__ void update_row(const OptDev& o, float* __restrict__ P,
+                                           float* __restrict__ M, float* __restrict__ Vv, int D, int l,
+                                           int64_t row, const Row<V, G, R>& g) {
+  Row<V, G, R> p, m, v;
+  p.load(P + row * D, D, l);
+  if (rule_has_m(o.rule)) m.load(M + row * D, D, l); else m.zero();
+  if (rule_has_v(o.rule)) v.load(Vv + row * D, D, l); else v.zero();
+#pragma unroll
+  for (int i = 0; i < R * V; ++i) apply_rule(o, p.f[i], m.f[i], v.f[i], g.f[i]);
+  p.store(P + row * D, D, l);
+  if (rule_has_m(o.rule)) m.store(M + row * D, D, l);
+  if (rule_has_v(o.rule)) v.store(Vv + row * D, D, l);
+}
+
+__device__ __forceinline__ void update_scalar(const OptDev& o, float* P, float* M, float* Vv,
+                                              int64_t row, float g) {
+  float p = P[row];
+  float m = rule_has_m(o.rule) ? M[row] : 0.f;
+  float v = rule_has_v(o.rule) ? Vv[row] : 0.f;
+  apply_rule(o, p, m, v, g);
+  P[row] = p;
+  if (rule_has_m(o.rule)) M[row] = m;
+  if (rule_has_v(o.rule)) Vv[row] = v;
+}
+
+// ------------------------------------------------------------------------------- fused step
+struct StepDev {
+  float *U, *I, *bu, *bi, *U_m, *U_v, *bu_m, *bu_v;
+  int D;
+  uint32_t num_items;
+  const int32_t* su;    // users in sorted order
+  const uint32_t* perm; // sorted position -> batch position (NULL: identity)
+  const int32_t* items;
+  const float* ratings;
+  const int64_t* negs_in;
+  const int64_t* gidx;
+  int64_t gidx_base;
+  int64_t B;
+  int N, L;
+  int64_t num_chunks;
+  uint64_t seed;
+  uint32_t epoch;
+  const int64_t* indptr;
+  const int32_t* csr_items;
+  int max_tries;
+  int loss, has_range;
+  float y_lo, y_hi;
+  int n_meta;
+  const int32_t* meta[CMF_MAX_METADATA];
+  float meta_w[CMF_MAX_METADATA];
+  OptDev emb, bias;
+  int train, user_inplace, use_lists;
+  float inv_B;
+  float *GU, *gbu, *GI, *gbi;
+  int *user_flag, *item_flag, *user_list, *item_list;
+  WsHeader* hdr;
+  double* partials;
+  float* loss_out;
+  int64_t* negs_out;
+  int32_t* sel_out;
+  float* pos_out;
+  float* neg_out;
+};
+
+__device__ __forceinline__ void mark_row(int* flag, int* list, int* count, int id, int use_list) {
+  if (*(volatile int*)(flag + id) == 0) {
+    if (atomicExch(flag + id, 1) == 0 && use_list) list[atomicAdd(count, 1)] = id;
+  }
+}
+
+__device__ __forceinline__ float ideal_of(const StepDev& p, int pos, int neg) {
+  // 1 - sum_k w_k [meta_k[pos] == meta_k[neg]]   (collie/loss/metadata_utils.py:60-71)
+  float frac = 0.f;
+  for (int k = 0; k < p.n_meta; ++k)
+    frac += (p.meta[k][pos] == p.meta[k][neg]) ? p.meta_w[k] : 0.f;
+  return 1.0f - frac;
+}
+
+template <int V, int G, int R>
+__global__ void __launch_bounds__(kThreads)
+k_fused_step(const StepDev p) {
+  constexpr int NC = (R * V <= 4) ? 4 : (R * V <= 8 ? 2 : 1);
+  constexpr int kGroups = kThreads / G;
+  __shared__ int s_negs[kGroups][kMaxNeg];
+  __shared__ float s_warp_loss[kThreads / 32];
+
+  const int lane_w = threadIdx.x & 31;
+  const int l = threadIdx.x & (G - 1);
+  const int gib = threadIdx.x / G;  // group in block
+  const unsigned mask = group_mask<G>(lane_w);
+  const int64_t group = (int64_t)blockIdx.x * kGroups + gib;
+  const int64_t n_groups = (int64_t)gridDim.x * kGroups;
+  const int D = p.D, N = p.N;
+  const bool implicit = p.loss <= CMF_LOSS_WARP;
+  int* negs = s_negs[gib];
+
+  float loss_acc = 0.f;
+
+  for (int64_t c = group; c < p.num_chunks; c += n_groups) {
+    const int64_t e0 = c * p.L;
+    const int64_t e1 = (e0 + p.L < p.B) ? e0 + p.L : p.B;
+    int cur_user = -1;
+    bool left_whole = false;
+    Row<V, G, R> urow, gu;
+    float ubias = 0.f, gbu_acc = 0.f;
+
+    for (int64_t e = e0; e <= e1; ++e) {
+      const int u = (e < e1) ? p.su[e] : -2;
+      if (u != cur_user) {
+        // ---- finish the previous user's segment
+        if (cur_user >= 0 && p.train) {
+          // e < e1: the next entry (inside this chunk) belongs to another user; e == e1: look
+          // across the chunk boundary
+          const bool right_whole = (e < e1) || (e1 == p.B) || (p.su[e1] != cur_user);
+          if (left_whole && right_whole && p.user_inplace) {
+            update_row<V, G, R>(p.emb, p.U, p.U_m, p.U_v, D, l, cur_user, gu);
+            if (l == 0) update_scalar(p.bias, p.bu, p.bu_m, p.bu_v, cur_user, gbu_acc);
+          } else {
+            gu.red_add(p.GU + (int64_t)cur_user * D, D, l);
+            if (l == 0) {
+              atomicAdd(p.gbu + cur_user, gbu_acc);
+              mark_row(p.user_flag, p.user_list, &p.hdr->user_count, cur_user, p.use_lists);
+            }
+          }
+        }
+        if (e == e1) break;
+        cur_user = u;
+        left_whole = (e == 0) || (p.su[e - 1] != u);
+        urow.load(p.U + (int64_t)u * D, D, l);
+        ubias = p.bu[u];
+        gu.zero();
+        gbu_acc = 0.f;
+      }
+
+      const int64_t b = p.perm ? (int64_t)p.perm[e] : e;
+      const int pos = p.items[b];
+      Row<V, G, R> irow;
+      irow.load(p.I + (int64_t)pos * D, D, l);
+
+      if (!implicit) {
+        // ---------------- explicit: mse / mae (base_pipeline.py:635-650)
+        const float s = group_sum<G>(urow.dot(irow), mask) + ubias + p.bi[pos];
+        float sg = 0.f, pred = s;
+        if (p.has_range) { sg = sigmoidf_(s); pred = sg * (p.y_hi - p.y_lo) + p.y_lo; }
+        const float diff = pred - p.ratings[b];
+        float dp;
+        if (p.loss == CMF_LOSS_MSE) { loss_acc += diff * diff; dp = 2.f * diff * p.inv_B; }
+        else { loss_acc += fabsf(diff); dp = (diff > 0.f ? 1.f : (diff < 0.f ? -1.f : 0.f)) * p.inv_B; }
+        const float ds = p.has_range ? dp * (sg * (1.f - sg) * (p.y_hi - p.y_lo)) : dp;
+        if (p.pos_out && l == 0) p.pos_out[b] = pred;
+        if (p.train) {
+          gu.axpy(ds, irow);
+          gbu_acc += ds;
+          Row<V, G, R> t;
+          t.zero();
+          t.axpy(ds, urow);
+          t.red_add(p.GI + (int64_t)pos * D, D, l);
+          if (l == 0) {
+            atomicAdd(p.gbi + pos, ds);
+            mark_row(p.item_flag, p.item_list, &p.hdr->item_count, pos, p.use_lists);
+          }
+        }
+        continue;
+      }
+
+      // ---------------- implicit
+      const float sp = group_sum<G>(urow.dot(irow), mask) + ubias + p.bi[pos];
+      if (p.pos_out && l == 0) p.pos_out[b] = sp;
+
+      // negatives of this interaction -> shared memory
+      __syncwarp(mask);
+      if (p.negs_in) {
+        for (int n = l; n < N; n += G) negs[n] = (int)p.negs_in[b * N + n];
+      } else {
+        const int64_t gi = p.gidx ? p.gidx[b] : p.gidx_base + b;
+        if (p.indptr == nullptr) {
+          for (int n = l; n < N; n += G) negs[n] = draw_item(p.seed, p.epoch, gi, n, p.num_items);
+        } else if (l == 0) {
+          // exact sampling: the reference's rejection loop (datasets.py:399-426) over our stream
+          const int64_t lo = p.indptr[cur_user], hi = p.indptr[cur_user + 1];
+          uint32_t d = 0;
+          int taken = 0, checked = 0;
+          while (taken < N) {
+            int cand = draw_item(p.seed, p.epoch, gi, d++, p.num_items);
+            for (;;) {
+              bool clash = csr_contains(p.csr_items, lo, hi, cand);
+              for (int j = 0; j < taken && !clash; ++j) clash = (negs[j] == cand);
+              if (!clash) break;
+              if (checked >= p.max_tries) {
+                const int left = N - taken - 1;
+                for (int j = 0; j < left; ++j)
+                  negs[taken++] = draw_item(p.seed, p.epoch, gi, d++, p.num_items);
+                break;
+              }
+              cand = draw_item(p.seed, p.epoch, gi, d++, p.num_items);
+              ++checked;
+            }
+            negs[taken++] = cand;
+          }
+        }
+      }
+      __syncwarp(mask);
+      if (p.negs_out) for (int n = l; n < N; n += G) p.negs_out[b * N + n] = negs[n];
+
+      // scan the negatives; keep the row of the selected one for the backward
+      Row<V, G, R> sel_row;
+      sel_row.zero();
+      int sel = (p.loss == CMF_LOSS_WARP) ? N : 0;
+      int sel_id = -1;
+      float sel_s = -INFINITY, sel_h = 0.f;
+      const bool adaptive = p.loss == CMF_LOSS_ADAPTIVE_BPR || p.loss == CMF_LOSS_ADAPTIVE_HINGE;
+      for (int n0 = 0; n0 < N; n0 += NC) {
+        Row<V, G, R> rows[NC];
+        int ids[NC];
+#pragma unroll
+        for (int j = 0; j < NC; ++j) {
+          ids[j] = (n0 + j < N) ? negs[n0 + j] : -1;
+          if (ids[j] >= 0) rows[j].load(p.I + (int64_t)ids[j] * D, D, l);
+        }
+#pragma unroll
+        for (int j = 0; j < NC; ++j) {
+          if (ids[j] < 0) continue;
+          const int n = n0 + j;
+          const float s = group_sum<G>(urow.dot(rows[j]), mask) + ubias + p.bi[ids[j]];
+          if (p.neg_out && l == 0) p.neg_out[b * N + n] = s;
+          if (p.loss == CMF_LOSS_WARP) {
+            // h = ideal - pos + neg, first strict violation wins (warp.py:95-105,136-154)
+            const float h = (ideal_of(p, pos, ids[j]) - sp) + s;
+            if (sel == N && h > 0.f) { sel = n; sel_id = ids[j]; sel_h = h; sel_row = rows[j]; }
+          } else if (adaptive) {
+            // torch.max over the N axis: first index of the maximum (bpr.py:153, hinge.py:157)
+            if (n == 0 || s > sel_s) { sel = n; sel_id = ids[j]; sel_s = s; sel_row = rows[j]; }
+          } else {
+            if (n == 0) { sel = 0; sel_id = ids[j]; sel_s = s; sel_row = rows[j]; }
+          }
+        }
+      }
+      if (p.sel_out && l == 0) p.sel_out[b] = sel;
+
+      // per-interaction loss value and d loss / d pos score (d / d selected neg = -g)
+      float g = 0.f;
+      if (p.loss == CMF_LOSS_WARP) {
+        if (sel < N) {
+          const float w = logf((float)p.num_items / (float)(sel + 1));
+          const float Lw = w * sel_h;
+          loss_acc += Lw + Lw * Lw;
+          g = -((1.f + 2.f * Lw) * w) * p.inv_B;
+        }
+      } else {
+        const float ideal = ideal_of(p, pos, sel_id);
+        const float x = sp - sel_s;
+        if (p.loss == CMF_LOSS_BPR || p.loss == CMF_LOSS_ADAPTIVE_BPR) {
+          const float sg = sigmoidf_(x);
+          const float lv = ideal - sg;
+          loss_acc += lv + lv * lv;
+          g = -((1.f + 2.f * lv) * (sg * (1.f - sg))) * p.inv_B;
+        } else {
+          const float raw = ideal - x;
+          const float lv = raw > 0.f ? raw : 0.f;
+          loss_acc += lv + lv * lv;
+          g = (raw >= 0.f) ? -(1.f + 2.f * lv) * p.inv_B : 0.f;
+        }
+      }
+
+      if (p.train) {
+        if (g != 0.f) {
+          gu.axpy(g, irow);
+          gu.axpy(-g, sel_row);
+          gbu_acc += g;
+          gbu_acc += -g;
+          Row<V, G, R> t;
+          t.zero();
+          t.axpy(g, urow);
+          t.red_add(p.GI + (int64_t)pos * D, D, l);
+#pragma unroll
+          for (int i = 0; i < R * V; ++i) t.f[i] = -t.f[i];
+          t.red_add(p.GI + (int64_t)sel_id * D, D, l);
+          if (l == 0) {
+            atomicAdd(p.gbi + pos, g);
+            atomicAdd(p.gbi + sel_id, -g);
+          }
+        }
+        // every gathered row is "touched" (SparseAdam moves rows whose gradient is exactly zero)
+        for (int n = l; n <= N; n += G)
+          mark_row(p.item_flag, p.item_list, &p.hdr->item_count, n == N ? pos : negs[n],
+                   p.use_lists);
+      }
+    }
+  }
+
+  // ---- loss: lane 0 of every group holds its share; deterministic two-level reduction
+  float v = (l == 0) ? loss_acc : 0.f;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if (lane_w == 0) s_warp_loss[threadIdx.x >> 5] = v;
+  __syncthreads();
+  __shared__ bool s_last;
+  if (threadIdx.x == 0) {
+    double tot = 0.0;
+    for (int w = 0; w < kThreads / 32; ++w) tot += (double)s_warp_loss[w];
+    p.partials[blockIdx.x] = tot;
+    __threadfence();
+    const unsigned ticket = atomicAdd(&p.hdr->blocks_done, 1u);
+    s_last = (ticket == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (s_last && threadIdx.x == 0) {
+    __threadfence();
+    double tot = 0.0;
+    for (unsigned i = 0; i < gridDim.x; ++i) tot += ((volatile double*)p.partials)[i];
+    p.loss_out[0] = (float)(tot / (double)p.B);
+  }
+}
+
+// ------------------------------------------------------------------------------- row update
+struct UpdDev {
+  // table 0 = items, table 1 = users
+  float *P[2], *M[2], *Vv[2], *G[2];
+  float *bP[2], *bM[2], *bV[2], *bG[2];
+  int* flag[2];
+  const int* list[2];
+  int64_t rows[2];
+  int D;
+  int dense;  // walk every row instead of the touched lists
+  OptDev emb, bias;
+  WsHeader* hdr;
+};
+
+template <int V, int G, int R>
+__global__ void __launch_bounds__(kThreads)
+k_update_rows(const UpdDev p) {
+  constexpr int kGroups = kThreads / G;
+  const int l = threadIdx.x & (G - 1);
+  const int64_t group = (int64_t)blockIdx.x * kGroups + threadIdx.x / G;
+  const int64_t n_groups = (int64_t)gridDim.x * kGroups;
+  const int64_t n0 = p.dense ? p.rows[0] : (int64_t)p.hdr->item_count;
+  const int64_t n1 = p.dense ? p.rows[1] : (int64_t)p.hdr->user_count;
+  for (int64_t w = group; w < n0 + n1; w += n_groups) {
+    const int t = w < n0 ? 0 : 1;
+    const int64_t k = t == 0 ? w : w - n0;
+    const int64_t row = p.dense ? k : (int64_t)p.list[t][k];
+    const bool touched = p.flag[t][row] != 0;
+    if (p.emb.dense || touched) {
+      Row<V, G, R> g;
+      float* grow = p.G[t] + row * p.D;
+      g.load(grow, p.D, l);
+      if (touched) {
+        Row<V, G, R> z;
+        z.zero();
+        z.store(grow, p.D, l);
+      }
+      update_row<V, G, R>(p.emb, p.P[t], p.M[t], p.Vv[t], p.D, l, row, g);
+    }
+    if (l == 0) {
+      if (p.bias.dense || touched) {
+        const float gb = p.bG[t][row];
+        if (touched) p.bG[t][row] = 0.f;
+        update_scalar(p.bias, p.bP[t], p.bM[t], p.bV[t], row, gb);
+      }
+      if (touched) p.flag[t][row] = 0;
+    }
+  }
+}
+
+__global__ void k_iota(uint32_t* out, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (uint32_t)i;
+}
+
+// standalone optimizer over a dense gradient table (autograd-compatible path)
+template <int V, int G, int R>
+__global__ void __launch_bounds__(kThreads)
+k_optimizer_rows(float* P, float* M, float* Vv, float* Gr, int64_t num_rows, int D,
+                 const int32_t* rows, int64_t n_rows, const OptDev o, int zero_grad) {
+  constexpr int kGroups = kThreads / G;
+  const int l = threadIdx.x & (G - 1);
+  const int64_t group = (int64_t)blockIdx.x * kGroups + threadIdx.x / G;
+  const int64_t n_groups = (int64_t)gridDim.x * kGroups;
+  const int64_t total = rows ? n_rows : num_rows;
+  for (int64_t w = group; w < total; w += n_groups) {
+    const int64_t row = rows ? (int64_t)rows[w] : w;
+    Row<V, G, R> g;
+    g.load(Gr + row * D, D, l);
+    if (zero_grad) {
+      Row<V, G, R> z;
+      z.zero();
+      z.store(Gr + row * D, D, l);
+    }
+    update_row<V, G, R>(o, P, M, Vv, D, l, row, g);
+  }
+}
+
+static std::atomic<int> g_forced_chunk_len{-1};
+
+static int chunk_len(int64_t B, int G) {
+  int forced = g_forced_chunk_len.load();
+  if (forced < 0) {
+    const char* e = getenv("CMF_CHUNK_LEN");
+    forced = e ? atoi(e) : 0;
+    g_forced_chunk_len.store(forced);
+  }
+  if (forced > 0) return forced;
+  // aim for >= 2 chunks per resident group so the static round-robin stays balanced
+  const int64_t resident = (int64_t)num_sms() * (2048 / G);
+  int L = 16;
+  while (L > 1 && B / L < 2 * resident) L >>= 1;
+  return L;
+}
+
+static int validate_opt(const cmf_opt_t& o, const char* which, const float* m, const float* v) {
+  CMF_REQUIRE(o.rule >= CMF_OPT_SPARSE_ADAM && o.rule <= CMF_OPT_ADAGRAD,
+              "cmf_train_step: unknown %s optimizer rule %d", which, o.rule);
+  const bool need_m = o.rule != CMF_OPT_SGD;
+  const bool need_v = o.rule == CMF_OPT_SPARSE_ADAM || o.rule == CMF_OPT_ADAM;
+  CMF_REQUIRE(!need_m || m, "cmf_train_step: %s optimizer needs its first state tensor", which);
+  CMF_REQUIRE(!need_v || v, "cmf_train_step: %s optimizer needs its second state tensor", which);
+  CMF_REQUIRE(o.step >= 1, "cmf_train_step: %s optimizer step must be >= 1", which);
+  return CMF_OK;
+}
+
+}  // namespace cmf
+
+using namespace cmf;
+
+extern "C" int cmf_set_tuning(int32_t key, int32_t value) {
+  CMF_REQUIRE(key == 0, "cmf_set_tuning: unknown key %d", key);
+  CMF_REQUIRE(value >= 0 && value <= 4096, "cmf_set_tuning: chunk length %d out of range", value);
+  const int prev = g_forced_chunk_len.exchange(value);
+  return prev < 0 ? 0 : prev;
+}
+
+extern "C" size_t cmf_train_workspace_bytes(int64_t max_B, int32_t max_N, int64_t num_users,
+                                            int64_t num_items, int32_t D) {
+  (void)max_N;
+  if (max_B < 1 || num_users < 1 || num_items < 1 || D < 1) return 0;
+  return ws_layout(max_B, num_users, num_items, D).total;
+}
+
+extern "C" int cmf_workspace_init(void* workspace, size_t workspace_bytes, void* stream) {
+  CMF_REQUIRE(workspace && workspace_bytes > 0, "cmf_workspace_init: null workspace");
+  CMF_CUDA(cudaMemsetAsync(workspace, 0, workspace_bytes, (cudaStream_t)stream));
+  return CMF_OK;
+}
+
+extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
+  CMF_REQUIRE(a, "cmf_train_step: null args");
+  CMF_REQUIRE(a->U && a->I && a->bu && a->bi, "cmf_train_step: null parameter table");
+  CMF_REQUIRE(a->num_users > 0 && a->num_items > 0 && a->num_items < (1ll << 31) &&
+                  a->num_users < (1ll << 31), "cmf_train_step: bad table shape");
+  CMF_REQUIRE(geom_supported(a->D), "cmf_train_step: embedding_dim %d unsupported (1..1024)", a->D);
+  CMF_REQUIRE(a->B >= 1 && a->B < (1ll << 31), "cmf_train_step: batch size %lld out of range",
+              (long long)a->B);
+  CMF_REQUIRE(a->users && a->items && a->loss_out, "cmf_train_step: null batch/output pointer");
+  CMF_REQUIRE(a->loss >= CMF_LOSS_BPR && a->loss <= CMF_LOSS_MAE, "cmf_train_step: unknown loss %d",
+              a->loss);
+  const bool implicit = a->loss <= CMF_LOSS_WARP;
+  if (implicit) {
+    CMF_REQUIRE(a->N >= 1 && a->N <= kMaxNeg, "cmf_train_step: num_negative_samples %d not in 1..%d",
+                a->N, kMaxNeg);
+    CMF_REQUIRE(a->loss != CMF_LOSS_WARP || a->N > 1,
+                "Cannot use WARP loss with a single negative sample!");
+    CMF_REQUIRE((a->loss != CMF_LOSS_BPR && a->loss != CMF_LOSS_HINGE) || a->N == 1,
+                "cmf_train_step: bpr/hinge take exactly one negative (use the adaptive form)");
+    CMF_REQUIRE(!a->has_y_range, "cmf_train_step: y_range applies to explicit losses only");
+    CMF_REQUIRE(a->n_meta >= 0 && a->n_meta <= CMF_MAX_METADATA, "cmf_train_step: bad n_meta");
+    double wsum = 0;
+    for (int k = 0; k < a->n_meta; ++k) {
+      CMF_REQUIRE(a->meta[k], "cmf_train_step: null metadata array %d", k);
+      wsum += a->meta_w[k];
+    }
+    CMF_REQUIRE(wsum <= 1.0 + 1e-6, "sum of metadata weights was %g, must be <=1", wsum);
+    CMF_REQUIRE(a->negs_in || a->csr_indptr == nullptr || a->csr_items,
+                "cmf_train_step: csr_items missing for exact sampling");
+  } else {
+    CMF_REQUIRE(a->ratings, "cmf_train_step: explicit loss needs ratings");
+    CMF_REQUIRE(a->N == 0, "cmf_train_step: explicit loss takes no negatives");
+  }
+  if (a->train) {
+    int rc = validate_opt(a->emb_opt, "embedding", a->U_m, a->U_v);
+    if (rc) return rc;
+    rc = validate_opt(a->emb_opt, "embedding", a->I_m, a->I_v);
+    if (rc) return rc;
+    rc = validate_opt(a->bias_opt, "bias", a->bu_m, a->bu_v);
+    if (rc) return rc;
+    rc = validate_opt(a->bias_opt, "bias", a->bi_m, a->bi_v);
+    if (rc) return rc;
+  }
+  const WsLayout w = ws_layout(a->B, a->num_users, a->num_items, a->D);
+  if (!a->workspace || a->workspace_bytes < w.total)
+    return fail(CMF_ERR_WORKSPACE, "cmf_train_step: workspace of %zu bytes needed, %zu given",
+                w.total, a->workspace ? a->workspace_bytes : (size_t)0);
+
+  cudaStream_t s = (cudaStream_t)stream;
+  char* base = (char*)a->workspace;
+  const RowGeom geom = row_geom(a->D);
+
+  StepDev p{};
+  p.U = a->U; p.I = a->I; p.bu = a->bu; p.bi = a->bi;
+  p.U_m = a->U_m; p.U_v = a->U_v; p.bu_m = a->bu_m; p.bu_v = a->bu_v;
+  p.D = a->D;
+  p.num_items = (uint32_t)a->num_items;
+  p.items = a->items; p.ratings = a->ratings; p.negs_in = a->negs_in;
+  p.gidx = a->gidx; p.gidx_base = a->gidx_base;
+  p.B = a->B; p.N = a->N;
+  p.L = chunk_len(a->B, geom.G);
+  p.num_chunks = (a->B + p.L - 1) / p.L;
+  p.seed = a->seed; p.epoch = a->epoch;
+  p.indptr = a->csr_indptr; p.csr_items = a->csr_items;
+  p.max_tries = a->max_tries < 0 ? 0 : a->max_tries;
+  p.loss = a->loss; p.has_range = a->has_y_range; p.y_lo = a->y_lo; p.y_hi = a->y_hi;
+  p.n_meta = implicit ? a->n_meta : 0;
+  for (int k = 0; k < p.n_meta; ++k) { p.meta[k] = a->meta[k]; p.meta_w[k] = a->meta_w[k]; }
+  p.train = a->train ? 1 : 0;
+  if (p.train) { p.emb = make_opt(a->emb_opt); p.bias = make_opt(a->bias_opt); }
+  const int dense = p.train && (p.emb.dense || p.bias.dense);
+  p.user_inplace = p.train && !dense;
+  p.use_lists = p.train && !dense;
+  p.inv_B = 1.0f / (float)a->B;
+  p.GU = (float*)(base + w.GU); p.gbu = (float*)(base + w.gbu);
+  p.GI = (float*)(base + w.GI); p.gbi = (float*)(base + w.gbi);
+  p.user_flag = (int*)(base + w.user_flag); p.item_flag = (int*)(base + w.item_flag);
+  p.user_list = (int*)(base + w.user_list); p.item_list = (int*)(base + w.item_list);
+  p.hdr = (WsHeader*)(base + w.hdr);
+  p.partials = (double*)(base + w.partials);
+  p.loss_out = a->loss_out;
+  p.negs_out = a->negs_out; p.sel_out = a->sel_out;
+  p.pos_out = a->pos_scores_out; p.neg_out = a->neg_scores_out;
+
+  CMF_CUDA(cudaMemsetAsync(p.hdr, 0, sizeof(WsHeader), s));
+
+  // ---- order the batch by user
+  if (a->users_sorted) {
+    p.su = a->users;
+    p.perm = nullptr;
+  } else {
+    uint32_t* iota = (uint32_t*)(base + w.iota);
+    uint32_t* keys_out = (uint32_t*)(base + w.keys_out);
+    uint32_t* vals_out = (uint32_t*)(base + w.vals_out);
+    k_iota<<<(unsigned)((a->B + 255) / 256), 256, 0, s>>>(iota, a->B);
+    CMF_LAUNCH_CHECK();
+    int bits = 1;
+    while (bits < 32 && (1ll << bits) < a->num_users) ++bits;
+    size_t temp = w.cub_temp_bytes;
+    CMF_CUDA(cub::DeviceRadixSort::SortPairs(base + w.cub_temp, temp, (const uint32_t*)a->users,
+                                             keys_out, (const uint32_t*)iota, vals_out, (int)a->B,
+                                             0, bits, s));
+    p.su = (const int32_t*)keys_out;
+    p.perm = vals_out;
+  }
+
+  // ---- fused step
+  {
+    const int groups_per_block = kThreads / geom.G;
+    int64_t blocks = (p.num_chunks + groups_per_block - 1) / groups_per_block;
+    const int64_t cap = (int64_t)num_sms() * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks > kMaxPartials) blocks = kMaxPartials;
+#define CALL(V_, G_, R_) k_fused_step<V_, G_, R_><<<(unsigned)blocks, kThreads, 0, s>>>(p)
+    CMF_DISPATCH_GEOM(geom, CALL);
+#undef CALL
+    CMF_LAUNCH_CHECK();
+  }
+
+  // ---- finish items (always) and the users that were not finished in place
+  if (p.train) {
+    UpdDev q{};
+    q.P[0] = a->I; q.M[0] = a->I_m; q.Vv[0] = a->I_v; q.G[0] = p.GI;
+    q.bP[0] = a->bi; q.bM[0] = a->bi_m; q.bV[0] = a->bi_v; q.bG[0] = p.gbi;
+    q.flag[0] = p.item_flag; q.list[0] = p.item_list; q.rows[0] = a->num_items;
+    q.P[1] = a->U; q.M[1] = a->U_m; q.Vv[1] = a->U_v; q.G[1] = p.GU;
+    q.bP[1] = a->bu; q.bM[1] = a->bu_m; q.bV[1] = a->bu_v; q.bG[1] = p.gbu;
+    q.flag[1] = p.user_flag; q.list[1] = p.user_list; q.rows[1] = a->num_users;
+    q.D = a->D; q.dense = dense; q.emb = p.emb; q.bias = p.bias; q.hdr = p.hdr;
+    const int groups_per_block = kThreads / geom.G;
+    // sparse mode: the list lengths live on the device; size the grid for the worst case but cap it
+    int64_t work = dense ? a->num_items + a->num_users
+                         : std::min<int64_t>(a->num_items, a->B * (int64_t)(a->N + 1)) +
+                               std::min<int64_t>(a->num_users, 2 * p.num_chunks);
+    int64_t blocks = (work + groups_per_block - 1) / groups_per_block;
+    const int64_t cap = (int64_t)num_sms() * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+#define CALL(V_, G_, R_) k_update_rows<V_, G_, R_><<<(unsigned)blocks, kThreads, 0, s>>>(q)
+    CMF_DISPATCH_GEOM(geom, CALL);
+#undef CALL
+    CMF_LAUNCH_CHECK();
+  }
+  return CMF_OK;
+}
+
+extern "C" int cmf_train_step_implicit(const cmf_step_t* a, void* stream) {
+  CMF_REQUIRE(a, "cmf_train_step_implicit: null args");
+  CMF_REQUIRE(a->loss <= CMF_LOSS_WARP, "Explicit loss with implicit data is invalid!");
+  return cmf_train_step(a, stream);
+}
+
+extern "C" int cmf_train_step_explicit(const cmf_step_t* a, void* stream) {
+  CMF_REQUIRE(a, "cmf_train_step_explicit: null args");
+  CMF_REQUIRE(a->loss == CMF_LOSS_MSE || a->loss == CMF_LOSS_MAE,
+              "Implicit loss with explicit data is invalid!");
+  return cmf_train_step(a, stream);
+}
+
+extern "C" int cmf_optimizer_rows(float* P, float* M, float* V, float* G, int64_t num_rows,
+                                  int32_t D, const int32_t* rows, int64_t n_rows,
+                                  const cmf_opt_t* opt, int32_t zero_grad, void* stream) {
+  CMF_REQUIRE(P && G && opt, "cmf_optimizer_rows: null pointer");
+  CMF_REQUIRE(geom_supported(D), "cmf_optimizer_rows: embedding_dim %d unsupported", D);
+  CMF_REQUIRE(opt->rule >= CMF_OPT_SPARSE_ADAM && opt->rule <= CMF_OPT_ADAGRAD,
+              "cmf_optimizer_rows: unknown rule %d", opt->rule);
+  CMF_REQUIRE(opt->rule == CMF_OPT_SGD || M, "cmf_optimizer_rows: state tensor M required");
+  CMF_REQUIRE((opt->rule != CMF_OPT_SPARSE_ADAM && opt->rule != CMF_OPT_ADAM) || V,
+              "cmf_optimizer_rows: state tensor V required");
+  CMF_REQUIRE(opt->step >= 1, "cmf_optimizer_rows: step must be >= 1");
+  const int64_t total = rows ? n_rows : num_rows;
+  if (total <= 0) return CMF_OK;
+  const OptDev o = make_opt(*opt);
+  const RowGeom geom = row_geom(D);
+  const int groups_per_block = kThreads / geom.G;
+  int64_t blocks = (total + groups_per_block - 1) / groups_per_block;
+  const int64_t cap = (int64_t)num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  cudaStream_t s = (cudaStream_t)stream;
+#define CALL(V_, G_, R_)                                                                     \
+  k_optimizer_rows<V_, G_, R_><<<(unsigned)blocks, kThreads, 0, s>>>(P, M, V, G, num_rows, D, \
+                                                                     rows, n_rows, o, zero_grad)
+  CMF_DISPATCH_GEOM(geom, CALL);
+#undef CALL
+  CMF_LAUNCH_CHECK();
+  return CMF_OK;
+}

@@ -1,0 +1,407 @@
+"""Interaction datasets and loaders with the reference's API, resident on the GPU.
+
+Mirrors (same names, argument meaning and error behaviour):
+  collie/interactions/datasets.py   BaseInteractions :17-193, Interactions :196-445,
+                                    ExplicitInteractions :448-562
+  collie/interactions/dataloaders.py InteractionsDataLoader :70-173,
+                                    ApproximateNegativeSamplingInteractionsDataLoader :176-294
+  collie/interactions/samplers.py   ApproximateNegativeSampler :11-64 (shuffled index slices)
+
+What changes: the COO arrays live in HBM as int32 tensors, an epoch's shuffle is one device
+permutation, a batch is a slice of it, and negatives come from the counter-based Philox stream
+(``cmf_sample_negatives``; the fused training step draws the same stream in-kernel). HDF5 loaders
+are out of scope (disk I/O, not this path).
+"""
+import collections
+import textwrap
+import warnings
+from typing import Iterable, Optional, Union
+
+import numpy as np
+import torch
+from scipy.sparse import coo_matrix
+
+from . import _abi
+
+
+def _check_all_ids_present(array, max_value, name):
+    present = np.zeros(int(max_value), dtype=bool)
+    arr = np.asarray(array)
+    if arr.size and (arr.min() < 0 or arr.max() >= max_value):
+        raise ValueError(f'``{name}`` contains ids outside ``[0, {max_value})``.')
+    present[arr] = True
+    if not present.all():
+        raise ValueError(
+            f'``{name}`` does not contain every integer in ``[0, {max_value})``; pass '
+            '``allow_missing_ids=True`` to skip this check.')
+
+
+def _infer_num(num, array):
+    if num == 'infer':
+        return int(np.max(array)) + 1
+    return int(num)
+
+
+class BaseInteractions(torch.utils.data.Dataset):
+    """COO wrapper shared by implicit and explicit data (datasets.py:17-193)."""
+
+    def __init__(self, mat=None, users=None, items=None, ratings=None, allow_missing_ids=False,
+                 remove_duplicate_user_item_pairs=True, num_users='infer', num_items='infer'):
+        if mat is None:
+            assert users is not None and items is not None, (
+                'Either 1) ``mat`` or 2) both ``users`` or ``items`` must be non-null!')
+            if len(users) != len(items):
+                raise ValueError('Lengths of ``users`` and ``items`` must be equal.')
+            users = np.asarray(users)
+            items = np.asarray(items)
+            num_users = _infer_num(num_users, users)
+            num_items = _infer_num(num_items, items)
+            if allow_missing_ids is False:
+                _check_all_ids_present(users, num_users, 'users')
+                _check_all_ids_present(items, num_items, 'items')
+            if ratings is not None:
+                if len(users) != len(ratings):
+                    raise ValueError(
+                        'Length of ``ratings`` must be equal to lengths of ``users``, ``items``.')
+                data = np.asarray(ratings)
+            else:
+                data = np.ones(len(users))
+            mat = coo_matrix((data, (users, items)), shape=(num_users, num_items))
+        else:
+            mat = coo_matrix(mat)
+            if num_users == 'infer':
+                num_users = mat.shape[0]
+            if num_items == 'infer':
+                num_items = mat.shape[1]
+            if allow_missing_ids is False:
+                _check_all_ids_present(mat.row, num_users, 'mat.shape[0]')
+                _check_all_ids_present(mat.col, num_items, 'mat.shape[1]')
+
+        if remove_duplicate_user_item_pairs:
+            # keep the LAST value of a duplicated (user, item) pair, as the reference's
+            # dict-update de-duplication does (datasets.py:137-146)
+            key = mat.row.astype(np.int64) * int(mat.shape[1]) + mat.col.astype(np.int64)
+            _, last_rev = np.unique(key[::-1], return_index=True)
+            keep = np.sort(len(key) - 1 - last_rev)
+            if len(keep) != len(key):
+                mat = coo_matrix((mat.data[keep], (mat.row[keep], mat.col[keep])), shape=mat.shape)
+
+        self.mat = mat
+        self.allow_missing_ids = allow_missing_ids
+        self.remove_duplicate_user_item_pairs = remove_duplicate_user_item_pairs
+        self.num_users = int(num_users)
+        self.num_items = int(num_items)
+        self.num_interactions = self.mat.nnz
+        self.min_rating = self.mat.data.min() if self.mat.nnz else None
+        self.max_rating = self.mat.data.max() if self.mat.nnz else None
+        self._dev = {}
+
+    def __len__(self):
+        return self.num_interactions
+
+    def todense(self):
+        return self.mat.todense()
+
+    def toarray(self):
+        return self.mat.toarray()
+
+    def head(self, n=5):
+        n = self._prep_head_tail_n(n)
+        return self.mat.tocsr()[range(n), :].toarray()
+
+    def tail(self, n=5):
+        n = self._prep_head_tail_n(n)
+        return self.mat.tocsr()[range(-n, 0), :].toarray()
+
+    def _prep_head_tail_n(self, n):
+        if n < 0:
+            n = self.num_users + n
+        return min(n, self.num_users)
+
+    # ---- device residency -------------------------------------------------------------------
+    def device_state(self, device):
+        """int32 COO arrays (and ratings / positives CSR where relevant) on ``device``."""
+        device = torch.device(device)
+        if device.type != 'cuda':
+            raise _abi.CmfError('collie_b200 datasets are consumed on a CUDA device only')
+        key = str(device)
+        if key not in self._dev:
+            st = {
+                'users': torch.from_numpy(self.mat.row.astype(np.int32)).to(device),
+                'items': torch.from_numpy(self.mat.col.astype(np.int32)).to(device),
+            }
+            self._extra_device_state(st, device)
+            self._dev[key] = st
+        return self._dev[key]
+
+    def _extra_device_state(self, st, device):
+        pass
+
+
+class Interactions(BaseInteractions):
+    """Implicit interactions + negative sampling (datasets.py:196-445)."""
+
+    def __init__(self, mat=None, users=None, items=None, ratings=None, num_negative_samples=10,
+                 allow_missing_ids=False, remove_duplicate_user_item_pairs=True,
+                 num_users='infer', num_items='infer', check_num_negative_samples_is_valid=True,
+                 max_number_of_samples_to_consider=200, seed=None):
+        if mat is None and ratings is not None and 0 in set(ratings):
+            warnings.warn('``ratings`` contain ``0``s, which are ignored for implicit data.'
+                          ' Filtering these rows out.')
+            keep = np.asarray(ratings) != 0
+            users = np.asarray(users)[keep]
+            items = np.asarray(items)[keep]
+            ratings = np.asarray(ratings)[keep]
+        super().__init__(mat=mat, users=users, items=items, ratings=ratings,
+                         allow_missing_ids=allow_missing_ids,
+                         remove_duplicate_user_item_pairs=remove_duplicate_user_item_pairs,
+                         num_users=num_users, num_items=num_items)
+        if seed is None:
+            seed = int(np.random.randint(0, 2 ** 31 - 1))
+        self.num_negative_samples = num_negative_samples
+        self.max_number_of_samples_to_consider = max_number_of_samples_to_consider
+        self.check_num_negative_samples_is_valid = check_num_negative_samples_is_valid
+        self.seed = seed
+        self.epoch = 0  # advances the Philox counter so every pass draws fresh negatives
+
+        assert self.num_negative_samples >= 1
+        if (self.num_negative_samples >= self.max_number_of_samples_to_consider
+                and self.max_number_of_samples_to_consider > 0):
+            warnings.warn('``num_negative_samples > max_number_of_samples_to_consider``. '
+                          'Approximate negative sampling will be used.')
+        if self.check_num_negative_samples_is_valid:
+            max_degree = int(np.bincount(self.mat.row, minlength=1).max()) if self.mat.nnz else 0
+            limit = self.num_items - max_degree
+            assert self.num_negative_samples < limit, (
+                f'``num_negative_samples`` must be less than {limit}!')
+
+    @property
+    def exact_sampling(self):
+        # the reference takes the rejection loop whenever the budget is positive (datasets.py:392)
+        return self.max_number_of_samples_to_consider > 0
+
+    def __repr__(self):
+        return textwrap.dedent(f'''
+            Interactions object with {self.num_interactions} interactions between {self.num_users}
+            users and {self.num_items} items, returning {self.num_negative_samples} negative
+            samples per interaction.
+            ''').replace('\n', ' ').strip()
+
+    def _extra_device_state(self, st, device):
+        # positives CSR (sorted item ids per user) replaces the reference's set((row, col))
+        csr = self.mat.tocsr()
+        csr.sort_indices()
+        st['indptr'] = torch.from_numpy(csr.indptr.astype(np.int64)).to(device)
+        st['csr_items'] = torch.from_numpy(csr.indices.astype(np.int32)).to(device)
+
+    def sample_negatives(self, users_dev, gidx_dev, epoch=None):
+        """Negative ids ``[B, N]`` (int64, on device) for interactions at positions ``gidx_dev``."""
+        st = self.device_state(users_dev.device)
+        B = int(users_dev.numel())
+        out = torch.empty((B, self.num_negative_samples), dtype=torch.int64,
+                          device=users_dev.device)
+        exact = self.exact_sampling
+        rc = _abi.lib().cmf_sample_negatives(
+            self.seed, self.epoch if epoch is None else int(epoch), _abi.ptr(gidx_dev), 0,
+            _abi.ptr(users_dev), B, self.num_negative_samples, self.num_items,
+            _abi.ptr(st['indptr']) if exact else None,
+            _abi.ptr(st['csr_items']) if exact else None,
+            int(self.max_number_of_samples_to_consider), _abi.ptr(out),
+            _abi.stream_ptr(users_dev.device))
+        _abi.check(rc, 'cmf_sample_negatives')
+        return out
+
+    def __getitem__(self, index):
+        """``((user_id, item_id), negative_item_ids)`` like the reference (datasets.py:378-388).
+
+        Needs a CUDA device: negatives are drawn by the device sampler.
+        """
+        if not torch.cuda.is_available():
+            raise _abi.CmfError('Interactions.__getitem__ draws negatives on the GPU; no CUDA '
+                                'device is available and collie_b200 has no CPU fallback')
+        user_id = self.mat.row[index]
+        item_id = self.mat.col[index]
+        scalar = np.ndim(index) == 0
+        idx = np.atleast_1d(np.asarray(index, dtype=np.int64))
+        idx = np.where(idx < 0, idx + self.num_interactions, idx)
+        dev = torch.device('cuda', torch.cuda.current_device())
+        negs = self.sample_negatives(
+            torch.from_numpy(np.atleast_1d(user_id).astype(np.int32)).to(dev),
+            torch.from_numpy(idx).to(dev)).cpu().numpy()
+        return (user_id, item_id), (negs[0] if scalar else negs)
+
+
+class ExplicitInteractions(BaseInteractions):
+    """Explicit ratings (datasets.py:448-562)."""
+
+    def __init__(self, mat=None, users=None, items=None, ratings=None, allow_missing_ids=False,
+                 remove_duplicate_user_item_pairs=True, num_users='infer', num_items='infer'):
+        if mat is None and ratings is None:
+            raise ValueError('Ratings must be provided to ``ExplicitInteractions`` with ``mat`` or'
+                             ' ``ratings`` - both cannot be ``None``!')
+        super().__init__(mat=mat, users=users, items=items, ratings=ratings,
+                         allow_missing_ids=allow_missing_ids,
+                         remove_duplicate_user_item_pairs=remove_duplicate_user_item_pairs,
+                         num_users=num_users, num_items=num_items)
+
+    @property
+    def num_negative_samples(self):
+        raise AttributeError('``num_negative_samples`` does not exist for explicit datasets.')
+
+    def __repr__(self):
+        return textwrap.dedent(f'''
+            ExplicitInteractions object with {self.num_interactions} interactions between
+            {self.num_users} users and {self.num_items} items, with minimum rating of
+            {self.min_rating} and maximum rating of {self.max_rating}.
+            ''').replace('\n', ' ').strip()
+
+    def _extra_device_state(self, st, device):
+        st['ratings'] = torch.from_numpy(self.mat.data.astype(np.float32)).to(device)
+
+    def __getitem__(self, index):
+        return self.mat.row[index], self.mat.col[index], self.mat.data[index]
+
+
+_INTERACTIONS_KWARGS = ('num_negative_samples', 'allow_missing_ids',
+                        'remove_duplicate_user_item_pairs', 'num_users', 'num_items',
+                        'check_num_negative_samples_is_valid',
+                        'max_number_of_samples_to_consider', 'seed')
+
+DeviceBatch = collections.namedtuple('DeviceBatch', 'users items gidx ratings')
+
+
+class BaseInteractionsDataLoader(object):
+    """Properties shared by the loaders (dataloaders.py:16-67)."""
+
+    def __init__(self, interactions, batch_size=1024, shuffle=False, drop_last=False, **kwargs):
+        self.interactions = interactions
+        self.dataset = interactions
+        self.batch_size = batch_size
+        self.shuffle = shuffle
+        self.drop_last = drop_last
+        self.loader_kwargs = kwargs  # torch DataLoader kwargs (num_workers, ...) are accepted
+        self._epoch = 0
+
+    @property
+    def num_users(self):
+        return self.interactions.num_users
+
+    @property
+    def num_items(self):
+        return self.interactions.num_items
+
+    @property
+    def num_negative_samples(self):
+        return self.interactions.num_negative_samples
+
+    @property
+    def num_interactions(self):
+        return self.interactions.num_interactions
+
+    @property
+    def mat(self):
+        return self.interactions.mat
+
+    def __len__(self):
+        n, b = self.num_interactions, self.batch_size
+        return n // b if self.drop_last else (n + b - 1) // b
+
+    # ---- device-side epoch plan --------------------------------------------------------------
+    def device_batches(self, device, epoch=None):
+        """Yield ``DeviceBatch`` slices of one pass over the data, all tensors on ``device``.
+
+        Shuffled passes permute the dataset positions once on the device (the reference shuffles
+        an index array on the host, samplers.py:51-60); ``gidx`` keeps the dataset position of each
+        interaction, which keys the negative-sampling stream.
+        """
+        st = self.interactions.device_state(device)
+        n = self.num_interactions
+        if epoch is None:
+            epoch = self._epoch
+            self._epoch += 1
+        if self.shuffle:
+            gen = torch.Generator(device=device)
+            gen.manual_seed((int(getattr(self.interactions, 'seed', 0)) * 1000003 + int(epoch))
+                            % (2 ** 63 - 1))
+            order = torch.randperm(n, device=device, generator=gen)
+            users = st['users'][order]
+            items = st['items'][order]
+            ratings = st['ratings'][order] if 'ratings' in st else None
+        else:
+            order = torch.arange(n, device=device)
+            users, items, ratings = st['users'], st['items'], st.get('ratings')
+        b = self.batch_size
+        stop = (n // b) * b if self.drop_last else n
+        for s in range(0, stop, b):
+            e = min(s + b, n)
+            yield DeviceBatch(users[s:e], items[s:e], order[s:e],
+                              ratings[s:e] if ratings is not None else None)
+
+    def __iter__(self):
+        """Reference-format batches on the current CUDA device:
+        implicit ``((users, items), negatives[B, N])``, explicit ``(users, items, ratings)``."""
+        if not torch.cuda.is_available():
+            raise _abi.CmfError('collie_b200 loaders produce device-resident batches; no CUDA '
+                                'device is available and there is no CPU fallback')
+        dev = torch.device('cuda', torch.cuda.current_device())
+        epoch = self._epoch
+        self._epoch += 1
+        for db in self.device_batches(dev, epoch=epoch):
+            if db.ratings is not None:
+                yield db.users, db.items, db.ratings
+            else:
+                negs = self.interactions.sample_negatives(db.users, db.gidx, epoch=epoch)
+                yield (db.users, db.items), negs
+
+
+class InteractionsDataLoader(BaseInteractionsDataLoader):
+    """dataloaders.py:70-173."""
+
+    def __init__(self, interactions=None, mat=None, users=None, items=None, ratings=None,
+                 batch_size=1024, shuffle=False, **kwargs):
+        if interactions is None:
+            ikw = {k: v for k, v in kwargs.items() if k in _INTERACTIONS_KWARGS}
+            kwargs = {k: v for k, v in kwargs.items() if k not in _INTERACTIONS_KWARGS}
+            interactions = Interactions(mat=mat, users=users, items=items, ratings=ratings, **ikw)
+        super().__init__(interactions=interactions, batch_size=batch_size, shuffle=shuffle,
+                         **kwargs)
+
+    def __repr__(self):
+        if hasattr(self.interactions, 'num_negative_samples'):
+            extra = f'{self.num_negative_samples} negative samples per implicit interaction in'
+        else:
+            extra = 'explicit,'
+        return textwrap.dedent(f'''
+            InteractionsDataLoader object with {self.num_interactions} interactions between
+            {self.num_users} users and {self.num_items} items, returning
+            {extra}
+            {'shuffled' if self.shuffle else 'non-shuffled'} batches of size {self.batch_size}.
+            ''').replace('\n', ' ').strip()
+
+
+class ApproximateNegativeSamplingInteractionsDataLoader(BaseInteractionsDataLoader):
+    """dataloaders.py:176-294: forces approximate (uniform) negatives."""
+
+    def __init__(self, interactions=None, mat=None, users=None, items=None, ratings=None,
+                 batch_size=1024, shuffle=False, **kwargs):
+        if isinstance(interactions, ExplicitInteractions):
+            raise ValueError('``ApproximateNegativeSamplingInteractionsDataLoader`` does not '
+                             'support explicit data types!')
+        if interactions is None:
+            ikw = {k: v for k, v in kwargs.items() if k in _INTERACTIONS_KWARGS}
+            kwargs = {k: v for k, v in kwargs.items() if k not in _INTERACTIONS_KWARGS}
+            ikw['max_number_of_samples_to_consider'] = 0
+            interactions = Interactions(mat=mat, users=users, items=items, ratings=ratings, **ikw)
+        else:
+            interactions.max_number_of_samples_to_consider = 0
+        super().__init__(interactions=interactions, batch_size=batch_size, shuffle=shuffle,
+                         **kwargs)
+
+    def __repr__(self):
+        return textwrap.dedent(f'''
+            ApproximateNegativeSamplingInteractionsDataLoader object with {self.num_interactions}
+            interactions between {self.num_users} users and {self.num_items} items, returning
+            {self.num_negative_samples} negative samples per implicit interaction in
+            {'shuffled' if self.shuffle else 'non-shuffled'} batches of size
+            {self.batch_size}.
+            ''').replace('\n', ' ').strip()

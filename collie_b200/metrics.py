@@ -1,0 +1,223 @@
+"""Evaluation with the reference's API (``collie/metrics.py``), computed by ``cmf_eval_tile``.
+
+Mirrors: ``get_preds`` :77-107, ``mapk`` :144-198, ``mrr`` :201-240, ``auc`` :243-282,
+``evaluate_in_batches`` :285-395 (implicit data; the explicit variant is outside this path).
+
+``evaluate_in_batches`` takes the fused route when every metric is one of ``mapk`` / ``mrr`` /
+``auc`` and the model is this package's ``MatrixFactorizationModel``: the score tile is produced and
+ranked on the device, and only three accumulators come back to the host, once. Any other metric
+callable receives a materialised ``preds`` tile exactly like in the reference. Canonical ranking
+order is score descending, item id ascending (``torch.topk``'s tie order is unpinned there).
+"""
+import numpy as np
+import torch
+from scipy.sparse import csr_matrix
+
+from . import _abi
+from .interactions import Interactions
+
+# users per fused tile; the result does not depend on it (per-user values are summed)
+_TILE_USERS = 256
+_MAX_TILE_BYTES = 1 << 30
+
+
+def _targets_device(targets: csr_matrix, user_ids, device):
+    """CSR rows of ``user_ids`` restricted to entries > 0, item ids sorted, on ``device``."""
+    sub = csr_matrix(targets[np.asarray(user_ids)]).copy()
+    sub.sum_duplicates()
+    sub.data = np.where(sub.data > 0, sub.data, 0)
+    sub.eliminate_zeros()
+    sub.sort_indices()
+    return (torch.from_numpy(sub.indptr.astype(np.int64)).to(device),
+            torch.from_numpy(sub.indices.astype(np.int32)).to(device),
+            torch.from_numpy(np.diff(sub.indptr).astype(np.int64)).to(device))
+
+
+def _eval_tile(device, n_users, n_items, k, indptr, tgt_items, want, tables=None, user_ids=None,
+               scores=None, precision=0, workspace=None):
+    """One ``cmf_eval_tile`` call; returns dict of per-user device tensors."""
+    a = _abi.cmf_eval_t()
+    keep = []
+    if scores is not None:
+        scores = _abi.require_cuda(scores.float().contiguous(), 'preds')
+        a.scores_in = scores.data_ptr()
+        keep.append(scores)
+    else:
+        U, I, bu, bi = tables
+        a.U, a.I, a.bu, a.bi = U.data_ptr(), I.data_ptr(), bu.data_ptr(), bi.data_ptr()
+        a.D = U.shape[1]
+        a.user_ids = user_ids.data_ptr()
+    a.n_users_tile, a.item_offset, a.num_items_shard, a.k = n_users, 0, n_items, k
+    a.tgt_indptr, a.tgt_items = indptr.data_ptr(), tgt_items.data_ptr()
+    a.precision = precision
+    out = {}
+    if 'mapk' in want:
+        out['ap'] = torch.empty(n_users, dtype=torch.float64, device=device)
+        a.ap = out['ap'].data_ptr()
+    if 'topk' in want:
+        out['topk_ids'] = torch.empty((n_users, k), dtype=torch.int32, device=device)
+        out['topk_scores'] = torch.empty((n_users, k), dtype=torch.float32, device=device)
+        a.topk_ids, a.topk_scores = out['topk_ids'].data_ptr(), out['topk_scores'].data_ptr()
+    if 'mrr' in want:
+        a.want_mrr = 1
+        out['n_before_best'] = torch.empty(n_users, dtype=torch.int32, device=device)
+        a.n_before_best = out['n_before_best'].data_ptr()
+    if 'auc' in want:
+        a.want_auc = 1
+        out['auc_pairs'] = torch.empty(n_users, dtype=torch.float64, device=device)
+        a.auc_pairs = out['auc_pairs'].data_ptr()
+    need = _abi.lib().cmf_eval_workspace_bytes(n_users, n_items, int(a.D), k, precision)
+    if workspace is None or workspace.numel() < need:
+        workspace = torch.empty(int(need), dtype=torch.uint8, device=device)
+    a.workspace, a.workspace_bytes = workspace.data_ptr(), workspace.numel()
+    rc = _abi.lib().cmf_eval_tile(_abi.C.byref(a), _abi.stream_ptr(device))
+    _abi.check(rc, 'cmf_eval_tile')
+    out['_workspace'] = workspace
+    return out
+
+
+def _check_k(k, n_items):
+    if k > n_items:
+        raise ValueError(f'Ensure ``k`` ({k}) is less than the number of items ({n_items})')
+
+
+def _per_user(name, res, nnz, n_items):
+    """Per-user metric values (float64, on device) from the kernel's ingredients."""
+    if name == 'mapk':
+        return res['ap']
+    if name == 'mrr':
+        nb = res['n_before_best']
+        return torch.where(nb >= 0, 1.0 / (nb.double() + 1.0), torch.zeros_like(nb,
+                                                                                dtype=torch.float64))
+    if name == 'auc':
+        pos = nnz.double()
+        neg = float(n_items) - pos
+        denom = pos * neg
+        return torch.where(denom > 0, res['auc_pairs'] / denom.clamp(min=1.0),
+                           torch.zeros_like(denom))
+    raise ValueError(name)
+
+
+def _metric_on_preds(name, targets, user_ids, preds, k):
+    preds = torch.as_tensor(preds)
+    if not preds.is_cuda:
+        raise _abi.CmfError('metrics run on the GPU: ``preds`` must be a CUDA tensor '
+                            '(collie_b200 has no CPU path)')
+    n_users, n_items = preds.shape
+    if name == 'mapk':
+        _check_k(k, n_items)
+    indptr, items, nnz = _targets_device(targets, user_ids, preds.device)
+    res = _eval_tile(preds.device, n_users, n_items, k if name == 'mapk' else 1, indptr, items,
+                     {name}, scores=preds)
+    return _per_user(name, res, nnz, n_items).mean().item()
+
+
+def mapk(targets: csr_matrix, user_ids, preds, k: int = 10) -> float:
+    """Mean average precision at ``k`` (collie/metrics.py:144-198)."""
+    return _metric_on_preds('mapk', targets, user_ids, preds, k)
+
+
+def mrr(targets: csr_matrix, user_ids, preds, k=None) -> float:
+    """Mean reciprocal rank of the best-ranked target (collie/metrics.py:201-240)."""
+    return _metric_on_preds('mrr', targets, user_ids, preds, k)
+
+
+def auc(targets: csr_matrix, user_ids, preds, k=None) -> float:
+    """Mean per-user AUROC of ``sigmoid(preds)`` (collie/metrics.py:243-282)."""
+    return _metric_on_preds('auc', targets, user_ids, preds, k)
+
+
+_FUSED = {mapk: 'mapk', mrr: 'mrr', auc: 'auc'}
+
+
+def _model_tables(model):
+    return tuple(_abi.require_cuda(t.data, n) for t, n in (
+        (model.user_embeddings.weight, 'user_embeddings.weight'),
+        (model.item_embeddings.weight, 'item_embeddings.weight'),
+        (model.user_biases.weight, 'user_biases.weight'),
+        (model.item_biases.weight, 'item_biases.weight')))
+
+
+def get_preds(model, user_ids, n_items, device=None):
+    """Scores of every item for ``user_ids``: tensor ``n_users x n_items``
+    (collie/metrics.py:77-107), one tiled kernel instead of ``n_users * n_items`` gathers."""
+    U, I, bu, bi = _model_tables(model)
+    users = torch.as_tensor(np.asarray(user_ids)).to(U.device, torch.int32).contiguous()
+    out = torch.empty((users.shape[0], int(n_items)), dtype=torch.float32, device=U.device)
+    rc = _abi.lib().cmf_score_tile(_abi.ptr(U), _abi.ptr(I), _abi.ptr(bu), _abi.ptr(bi),
+                                   U.shape[1], _abi.ptr(users), users.shape[0], int(n_items),
+                                   _abi.ptr(out), _abi.stream_ptr(U.device))
+    _abi.check(rc, 'cmf_score_tile')
+    return out
+
+
+def evaluate_in_batches(metric_list, test_interactions, model, k=10, batch_size=20, logger=None,
+                        verbose=True, precision=0):
+    """Evaluate a model with potentially several metrics (collie/metrics.py:285-395).
+
+    Returns a float for one metric, else a list, exactly like the reference. ``precision`` selects
+    the scoring arithmetic of the fused route (0: exact fp32; 1: tcgen05 tensor cores).
+    """
+    if not isinstance(test_interactions, Interactions):
+        raise ValueError('``test_interactions`` must be of type ``Interactions``, not '
+                         f'{type(test_interactions)}. Try using ``explicit_evaluate_in_batches`` '
+                         'instead.')
+    if not torch.cuda.is_available():
+        raise _abi.CmfError('evaluate_in_batches runs on a CUDA device; none is available and '
+                            'collie_b200 has no CPU fallback')
+    if not next(model.parameters()).is_cuda:
+        model.to('cuda')
+    model._move_any_external_data_to_device()
+    device = model.device
+
+    test_users = np.unique(test_interactions.mat.row)
+    targets = test_interactions.mat.tocsr()
+    n_items = test_interactions.num_items
+    n_test = len(test_users)
+    names = [_FUSED.get(m) for m in metric_list]
+
+    if all(n is not None for n in names):
+        if 'mapk' in names:
+            _check_k(k, n_items)
+        tables = _model_tables(model)
+        indptr, tgt_items, nnz = _targets_device(targets, test_users, device)
+        users_dev = torch.from_numpy(test_users.astype(np.int32)).to(device)
+        tile = max(1, min(_TILE_USERS, _MAX_TILE_BYTES // max(1, 12 * n_items)))
+        sums = torch.zeros(len(names), dtype=torch.float64, device=device)
+        ws = None
+        for s in range(0, n_test, tile):
+            e = min(s + tile, n_test)
+            res = _eval_tile(device, e - s, n_items, k, indptr[s:e + 1], tgt_items, set(names),
+                             tables=tables, user_ids=users_dev[s:e], precision=precision,
+                             workspace=ws)
+            ws = res['_workspace']
+            for j, name in enumerate(names):
+                sums[j] += _per_user(name, res, nnz[s:e], n_items).sum()
+        all_scores = (sums / n_test).tolist()
+    else:
+        if n_test < batch_size:
+            batch_size = n_test
+        acc = [0.0] * len(metric_list)
+        for i in range(int(np.ceil(n_test / batch_size))):
+            user_range = test_users[i * batch_size:(i + 1) * batch_size]
+            preds = get_preds(model, user_range, n_items, device)
+            for j, metric in enumerate(metric_list):
+                acc[j] += metric(targets=targets, user_ids=user_range, preds=preds, k=k) \
+                    * len(user_range)
+        all_scores = [a / n_test for a in acc]
+
+    if logger is not None:
+        _log_metrics(model, logger, metric_list, all_scores, verbose)
+    return all_scores[0] if len(all_scores) == 1 else all_scores
+
+
+def _log_metrics(model, logger, metric_list, all_scores, verbose):
+    """collie/metrics.py:524-543."""
+    try:
+        step = model.hparams.get('num_epochs_completed')
+    except Exception:
+        step = None
+    metrics_dict = dict(zip([m.__name__ for m in metric_list], all_scores))
+    if verbose:
+        print(f'Logging metrics {metrics_dict} to ``logger``...')
+    logger.log_metrics(metrics=metrics_dict, step=step)

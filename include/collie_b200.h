@@ -1,0 +1,258 @@
+/*
+ * collie_b200 -- C ABI of the B200-native matrix-factorization hot path.
+ *
+ * The reference (ShopRunner/collie v1.3.1, pure Python + stock torch ops) has no FFI seam for this
+ * path; every entry point below states which reference call site(s) it stands in for. Paths are
+ * relative to the reference root. The host-side mirror of the reference API
+ * (collie_b200/model.py, trainer.py, metrics.py, interactions.py) binds these through ctypes; see
+ * INTEGRATION.md for the stub a reference maintainer would add.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless named host_*;
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream);
+ *   - return value 0 on success, negative cmf_status on failure; cmf_last_error() returns a
+ *     thread-local message for the last failure on the calling thread;
+ *   - the library never allocates device memory: scratch comes from the caller, sized by the
+ *     *_workspace_bytes() queries, and initialised once with cmf_workspace_init();
+ *   - all tables are fp32 row-major [rows, D] contiguous, exactly the reference's
+ *     nn.Embedding.weight layout (collie/model/matrix_factorization.py:106-117), so state_dicts
+ *     round-trip; bias tables are [rows, 1].
+ */
+#ifndef COLLIE_B200_H_
+#define COLLIE_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define CMF_API __attribute__((visibility("default")))
+#else
+#define CMF_API
+#endif
+
+typedef enum {
+  CMF_OK = 0,
+  CMF_ERR_INVALID = -1,   /* bad argument (message says which) */
+  CMF_ERR_CUDA = -2,      /* a CUDA runtime call or launch failed */
+  CMF_ERR_WORKSPACE = -3, /* workspace missing or too small */
+  CMF_ERR_UNSUPPORTED = -4
+} cmf_status;
+
+/* loss selected by collie/model/base/base_pipeline.py:277-340 */
+typedef enum {
+  CMF_LOSS_BPR = 0,            /* collie/loss/bpr.py:75-89     (one negative)   */
+  CMF_LOSS_HINGE = 1,          /* collie/loss/hinge.py:71-85   (one negative)   */
+  CMF_LOSS_ADAPTIVE_BPR = 2,   /* collie/loss/bpr.py:153-167                    */
+  CMF_LOSS_ADAPTIVE_HINGE = 3, /* collie/loss/hinge.py:157-171                  */
+  CMF_LOSS_WARP = 4,           /* collie/loss/warp.py:73-154                    */
+  CMF_LOSS_MSE = 5,            /* torch.nn.MSELoss, base_pipeline.py:287-289    */
+  CMF_LOSS_MAE = 6             /* torch.nn.L1Loss,  base_pipeline.py:290-292    */
+} cmf_loss;
+
+/* optimizer built by collie/model/base/base_pipeline.py:406-437 */
+typedef enum {
+  CMF_OPT_SPARSE_ADAM = 0, /* torch.optim.SparseAdam: every gathered row moves, even with g == 0 */
+  CMF_OPT_SGD = 1,         /* torch.optim.SGD (no momentum)                                      */
+  CMF_OPT_ADAM = 2,        /* torch.optim.Adam on dense grads: EVERY row of the table moves      */
+  CMF_OPT_ADAGRAD = 3      /* torch.optim.Adagrad (lr_decay 0, eps 1e-10)                        */
+} cmf_opt_rule;
+
+typedef struct {
+  int32_t rule;        /* cmf_opt_rule */
+  int32_t reserved;
+  double lr;           /* hyper-parameters are doubles, as the Python floats torch receives */
+  double beta1, beta2; /* Adam family */
+  double eps;
+  double weight_decay; /* dense rules only (the reference forces 0 when sparse, base_pipeline.py:230-240) */
+  int64_t step;        /* 1-based step count of this parameter group (torch keeps it per tensor) */
+} cmf_opt_t;
+
+#define CMF_MAX_METADATA 8
+
+/*
+ * One training (or validation) step of MatrixFactorizationModel on one batch:
+ *   negatives (injected or drawn on device) -> forward -> loss -> backward -> optimizer updates.
+ * Stands in for one iteration of CollieMinimalTrainer._train_loop_single_epoch
+ * (collie/model/base/trainer.py:458-470) = BasePipeline.calculate_loss (base_pipeline.py:582-654)
+ * + MatrixFactorizationModel.forward x2 (matrix_factorization.py:120-159) + collie/loss/*.py
+ * + autograd backward + optimizer.step() for both optimizers, and -- when negs_in is NULL -- for
+ * Interactions._negative_sample (collie/interactions/datasets.py:390-445).
+ */
+typedef struct {
+  /* parameter tables and optimizer state (state pointers may be NULL when the rule has none) */
+  float *U, *I, *bu, *bi;
+  float *U_m, *U_v, *I_m, *I_v;
+  float *bu_m, *bu_v, *bi_m, *bi_v;
+  int64_t num_users, num_items;
+  int32_t D;
+
+  /* batch: B interactions. implicit: (users, items) + negatives; explicit: + ratings */
+  const int32_t *users;   /* [B] */
+  const int32_t *items;   /* [B] positive (implicit) or rated (explicit) item ids */
+  const float *ratings;   /* [B], explicit losses only */
+  const int64_t *negs_in; /* [B, N] injected negatives, or NULL to draw them on device */
+  const int64_t *gidx;    /* [B] dataset position of each interaction (RNG counter), or NULL */
+  int64_t gidx_base;      /* used as gidx_base + b when gidx == NULL */
+  int64_t B;
+  int32_t N;              /* negatives per interaction (0 for explicit) */
+  int32_t users_sorted;   /* nonzero: `users` is already non-decreasing, skip the internal sort */
+
+  /* on-device sampler (counter-based Philox4x32-10) */
+  uint64_t seed;
+  uint32_t epoch;
+  const int64_t *csr_indptr; /* [num_users + 1] positives CSR for exact sampling, or NULL */
+  const int32_t *csr_items;  /* sorted item ids per user row */
+  int32_t max_tries;         /* max_number_of_samples_to_consider, datasets.py:291 */
+
+  /* loss */
+  int32_t loss; /* cmf_loss */
+  int32_t has_y_range;
+  float y_lo, y_hi;              /* matrix_factorization.py:152-157 */
+  int32_t n_meta;                /* partial-credit metadata keys, metadata_utils.py:60-71 */
+  const int32_t *meta[CMF_MAX_METADATA]; /* each [num_items] categorical labels */
+  float meta_w[CMF_MAX_METADATA];
+
+  /* optimizers: embeddings and biases are separate groups (base_pipeline.py:450-467) */
+  cmf_opt_t emb_opt, bias_opt;
+  int32_t train; /* 0: loss only (validation step, trainer.py:487-504) */
+
+  /* outputs */
+  float *loss_out;       /* [1] */
+  int64_t *negs_out;     /* [B, N] negatives actually used, or NULL */
+  int32_t *sel_out;      /* [B] selected negative slot (adaptive: argmax; warp: first violation or
+                            N when none; bpr/hinge: 0), or NULL */
+  float *pos_scores_out; /* [B] or NULL */
+  float *neg_scores_out; /* [B, N] or NULL */
+
+  void *workspace;
+  size_t workspace_bytes;
+} cmf_step_t;
+
+/* scratch for cmf_train_step; depends only on the table shapes and the largest batch */
+CMF_API size_t cmf_train_workspace_bytes(int64_t max_B, int32_t max_N, int64_t num_users, int64_t num_items,
+                                 int32_t D);
+/* zero the persistent part of the workspace; call once after allocation (and after a failure) */
+CMF_API int cmf_workspace_init(void *workspace, size_t workspace_bytes, void *stream);
+
+CMF_API int cmf_train_step(const cmf_step_t *args, void *stream);
+/* same call, restricted to the implicit / explicit loss families (base_pipeline.py:603 / :635) */
+CMF_API int cmf_train_step_implicit(const cmf_step_t *args, void *stream);
+CMF_API int cmf_train_step_explicit(const cmf_step_t *args, void *stream);
+
+/*
+ * preds[m] = <U[users[m]], I[items[m]]> + bu[..] + bi[..]  (+ sigmoid range if y_range != NULL).
+ * Replaces MatrixFactorizationModel.forward, collie/model/matrix_factorization.py:120-159.
+ * idx_bytes = 4 (int32 ids) or 8 (int64 ids, what the reference passes after .long()).
+ */
+CMF_API int cmf_forward_scores(const float *U, const float *I, const float *bu, const float *bi, int32_t D,
+                       const void *users, const void *items, int32_t idx_bytes, int64_t M,
+                       const float *host_y_range /* NULL or host float[2] */, float *out,
+                       void *stream);
+
+/*
+ * Backward of cmf_forward_scores: accumulates (atomically) into dense, caller-zeroed gradient
+ * tables gU [num_users,D], gI [num_items,D], gbu, gbi given dL/dpreds. `preds` (the forward output)
+ * is needed only when y_range is set. Replaces autograd through matrix_factorization.py:143-157
+ * (embedding_dense_backward x4), triggered at collie/model/base/trainer.py:463.
+ */
+CMF_API int cmf_backward_scores(const float *U, const float *I, int32_t D, const void *users,
+                        const void *items, int32_t idx_bytes, int64_t M, const float *dpreds,
+                        const float *preds, const float *host_y_range, float *gU, float *gI,
+                        float *gbu, float *gbi, void *stream);
+
+/*
+ * Negative item ids [B, N] for interactions at dataset positions gidx (or gidx_base + b).
+ * Replaces Interactions._negative_sample, collie/interactions/datasets.py:390-445: approximate mode
+ * when csr_indptr == NULL (:433-443), else the exact rejection loop (:399-426).
+ */
+CMF_API int cmf_sample_negatives(uint64_t seed, uint32_t epoch, const int64_t *gidx, int64_t gidx_base,
+                         const int32_t *users, int64_t B, int32_t N, int64_t num_items,
+                         const int64_t *csr_indptr, const int32_t *csr_items, int32_t max_tries,
+                         int64_t *negs_out, void *stream);
+
+/*
+ * Row-wise optimizer on a table given a dense gradient table G [rows, D]:
+ *   rows == NULL: every row (torch.optim.Adam / SGD / Adagrad on dense grads);
+ *   rows != NULL: only the n_rows listed unique rows (torch.optim.SparseAdam on the coalesced
+ *   gradient; SGD / Adagrad on sparse grads). Used rows of G are reset to zero when zero_grad != 0.
+ * Replaces optimizer.step() reached from collie/model/base/trainer.py:465-470 for the optimizers
+ * built at base_pipeline.py:418-433.
+ */
+CMF_API int cmf_optimizer_rows(float *P, float *M, float *V, float *G, int64_t num_rows, int32_t D,
+                       const int32_t *rows, int64_t n_rows, const cmf_opt_t *opt, int32_t zero_grad,
+                       void *stream);
+
+/*
+ * Evaluation of one tile of users against the whole item table (or an item shard):
+ * scores S = U[user_ids] . I^T + bu + bi are never written to HBM; per user the kernel keeps the
+ * top-k (score descending, item id ascending), and -- given the users' target items in CSR form --
+ * the MAP@k / MRR / AUC ingredients. Replaces get_preds + mapk + mrr + auc,
+ * collie/metrics.py:77-107, 144-198, 201-240, 243-282, for one iteration of the loop at :379-384.
+ *
+ *   tgt_indptr [n_users_tile + 1], tgt_items: sorted target item ids per user of the tile (global
+ *   ids); item_offset/num_items_shard describe the item shard this call scores (0 / num_items for
+ *   the unsharded case).
+ * Outputs (any may be NULL): topk_ids [n,k] int32 (global ids, -1 padded), topk_scores [n,k],
+ *   ap [n] double (AP@k per user, fp64 like the reference's weights), n_before_best [n] int32: #items ranked before the user's best-ranked
+ *   target in this shard, best_score/best_id [n]: that target's score/id (-inf/-1 when none),
+ *   auc_pairs [n] double: sum over targets of (#non-targets with lower sigmoid + .5 ties).
+ * precision: 0 = fp32 SIMT scoring (exact fp32), 1 = tcgen05 tensor cores, bf16x3 split operands.
+ */
+typedef struct {
+  const float *U, *I, *bu, *bi;
+  int32_t D;
+  const int32_t *user_ids; /* [n_users_tile] */
+  int64_t n_users_tile;
+  int64_t item_offset, num_items_shard;
+  int32_t k;
+  const int64_t *tgt_indptr;
+  const int32_t *tgt_items;
+  int32_t want_mrr, want_auc;
+  int32_t precision;
+  /* item-sharded second pass (all NULL otherwise): count against the globally best target and
+   * the globally gathered target sigmoids instead of this shard's own */
+  const float *ext_best_score;
+  const int32_t *ext_best_id;
+  int32_t *topk_ids;
+  float *topk_scores;
+  double *ap;
+  int32_t *n_before_best;
+  float *best_score;
+  int32_t *best_id;
+  double *auc_pairs;
+  void *workspace;
+  size_t workspace_bytes;
+  /* optional: rank an already materialised score tile [n_users_tile, num_items_shard] instead of
+   * scoring (the metric callables' `preds` argument, collie/metrics.py:144-147); U/I/bu/bi and
+   * user_ids are then ignored */
+  const float *scores_in;
+} cmf_eval_t;
+
+CMF_API size_t cmf_eval_workspace_bytes(int64_t n_users_tile, int64_t num_items_shard, int32_t D, int32_t k,
+                                int32_t precision);
+CMF_API int cmf_eval_tile(const cmf_eval_t *args, void *stream);
+
+/* Materialised score tile out[n, num_items] (for user-supplied metric callables and get_preds,
+ * collie/metrics.py:77-107). */
+CMF_API int cmf_score_tile(const float *U, const float *I, const float *bu, const float *bi, int32_t D,
+                   const int32_t *user_ids, int64_t n_users_tile, int64_t num_items, float *out,
+                   void *stream);
+
+/* Tuning knobs (process-wide). key 0: chunk length L of the fused step (0 = automatic). Results do
+ * not depend on L beyond fp32 summation order; tests use it to cross-check the in-place and the
+ * accumulate paths. Returns the previous value, or a negative cmf_status for an unknown key. */
+CMF_API int cmf_set_tuning(int32_t key, int32_t value);
+
+CMF_API const char *cmf_last_error(void);
+CMF_API int cmf_version(void);
+/* number of kernels this library has launched since load (process-wide, all streams) */
+CMF_API int64_t cmf_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* COLLIE_B200_H_ */

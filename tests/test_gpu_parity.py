@@ -1,0 +1,477 @@
+"""GPU parity: the CUDA path (through the C ABI) against the oracle and against golden vectors
+produced by the unmodified reference. Tolerances: bit-exact for ids / indices, 1e-5 relative for
+losses, gradients and metrics (north star), 1e-5 relative (+1e-6 absolute) for parameters after k
+optimizer steps."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import scipy.sparse as sp
+import torch
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
+IMPLICIT = sorted(glob.glob(os.path.join(GOLDEN, 'implicit_*.npz')))
+EXPLICIT = sorted(glob.glob(os.path.join(GOLDEN, 'explicit_*.npz')))
+METRICS = sorted(glob.glob(os.path.join(GOLDEN, 'metrics_*.npz')))
+
+GOLDEN_OPT = {
+    'implicit_bpr_n1_sparse_adam': 'sparse_adam', 'implicit_hinge_n1_adam': 'adam',
+    'implicit_adaptive_bpr_n5_sparse_adam': 'sparse_adam',
+    'implicit_adaptive_hinge_n10_adam': 'adam', 'implicit_warp_n7_sparse_adam': 'sparse_adam',
+    'implicit_warp_n4_sgd': 'sgd', 'implicit_adaptive_hinge_meta_n5': 'sparse_adam',
+    'implicit_warp_meta_n6': 'adam', 'implicit_adaptive_bpr_d10_n5': 'adam',
+    'implicit_adaptive_bpr_d30_n3': 'sparse_adam', 'implicit_adaptive_bpr_d128_n5': 'sparse_adam',
+    'implicit_hinge_adagrad': 'adagrad', 'explicit_mse_adam': 'adam',
+    'explicit_mse_sparse_adam_d64': 'sparse_adam', 'explicit_mae_sgd': 'sgd',
+    'explicit_mse_yrange': 'adam',
+}
+LOSS_ARG = {'bpr_loss': 'bpr', 'hinge_loss': 'hinge', 'adaptive_bpr_loss': 'bpr',
+            'adaptive_hinge_loss': 'adaptive', 'warp_loss': 'warp'}
+
+
+def _ids(paths):
+    return [os.path.basename(p)[:-4] for p in paths]
+
+
+def _implicit_data(n_users, n_items, n_neg, seed=0, exact=False, n=400):
+    import collie_b200 as cb
+    rng = np.random.default_rng(seed)
+    flat = rng.choice(n_users * n_items, size=n, replace=False)
+    return cb.Interactions(users=flat // n_items, items=flat % n_items, num_users=n_users,
+                           num_items=n_items, num_negative_samples=n_neg, allow_missing_ids=True,
+                           check_num_negative_samples_is_valid=False,
+                           max_number_of_samples_to_consider=200 if exact else 0, seed=seed + 1)
+
+
+def _model_from_golden(g, opt_name, loss, explicit=False, meta=None):
+    import collie_b200 as cb
+    n_users, n_items, dim = int(g['n_users']), int(g['n_items']), int(g['dim'])
+    if explicit:
+        rng = np.random.default_rng(0)
+        data = cb.ExplicitInteractions(users=rng.integers(0, n_users, 50),
+                                       items=rng.integers(0, n_items, 50),
+                                       ratings=rng.integers(1, 6, 50), num_users=n_users,
+                                       num_items=n_items, allow_missing_ids=True)
+        yr = None if np.isnan(g['y_range']).any() else tuple(g['y_range'].tolist())
+        kw = dict(y_range=yr)
+    else:
+        data = _implicit_data(n_users, n_items, int(g['n_neg']))
+        kw = {}
+        if meta:
+            kw = dict(metadata_for_loss={k: torch.from_numpy(v) for k, v in meta.items()},
+                      metadata_for_loss_weights={'a': 0.2, 'b': 0.3})
+    model = cb.MatrixFactorizationModel(
+        train=data, embedding_dim=dim, sparse=(opt_name == 'sparse_adam'), lr=float(g['lr']),
+        bias_lr=float(g['bias_lr']), optimizer=opt_name, bias_optimizer='sgd', loss=loss,
+        lr_scheduler_func=None, **kw).cuda()
+    with torch.no_grad():
+        model.user_embeddings.weight.copy_(torch.from_numpy(g['init_U']))
+        model.item_embeddings.weight.copy_(torch.from_numpy(g['init_I']))
+        model.user_biases.weight.copy_(torch.from_numpy(g['init_bu']))
+        model.item_biases.weight.copy_(torch.from_numpy(g['init_bi']))
+    return model
+
+
+def _tables(model):
+    return {'U': model.user_embeddings.weight, 'I': model.item_embeddings.weight,
+            'bu': model.user_biases.weight, 'bi': model.item_biases.weight}
+
+
+# ------------------------------------------------------------------------------------ forward
+@pytest.mark.parametrize('dim', [1, 7, 10, 30, 32, 64, 96, 128, 160, 256, 384])
+@pytest.mark.parametrize('idx_dtype', [torch.int64, torch.int32])
+def test_forward_scores_match_oracle(dim, idx_dtype):
+    import collie_b200 as cb
+    from oracle import collie_oracle as O
+    rng = np.random.default_rng(dim)
+    n_users, n_items, m = 61, 77, 1001
+    model = cb.MatrixFactorizationModel(train=_implicit_data(n_users, n_items, 3),
+                                        embedding_dim=dim, lr_scheduler_func=None).cuda()
+    with torch.no_grad():
+        for p in model.parameters():
+            p.copy_(torch.from_numpy(rng.normal(0, 0.5, tuple(p.shape)).astype(np.float32)))
+    users = torch.from_numpy(rng.integers(0, n_users, m)).to(idx_dtype)
+    items = torch.from_numpy(rng.integers(0, n_items, m)).to(idx_dtype)
+    got = model(users.cuda(), items.cuda()).detach().cpu()
+    tabs = [t.detach().cpu() for t in _tables(model).values()]
+    exp = O.mf_forward(*tabs, users, items)
+    np.testing.assert_allclose(got.numpy(), exp.numpy(), rtol=1e-5, atol=1e-6)
+    # empty input
+    assert model(users[:0].cuda(), items[:0].cuda()).shape == (0,)
+
+
+def test_forward_y_range_and_autograd_match_oracle():
+    import collie_b200 as cb
+    from oracle import collie_oracle as O
+    rng = np.random.default_rng(3)
+    n_users, n_items, dim, m = 23, 31, 24, 300
+    data = cb.ExplicitInteractions(users=rng.integers(0, n_users, 60),
+                                   items=rng.integers(0, n_items, 60),
+                                   ratings=rng.integers(1, 6, 60), num_users=n_users,
+                                   num_items=n_items, allow_missing_ids=True)
+    model = cb.MatrixFactorizationModel(train=data, embedding_dim=dim, loss='mse', y_range=(1, 5),
+                                        lr_scheduler_func=None).cuda()
+    ref = O.OracleMF(n_users, n_items, dim)
+    with torch.no_grad():
+        for p in model.parameters():
+            p.copy_(torch.from_numpy(rng.normal(0, 0.5, tuple(p.shape)).astype(np.float32)))
+        for name in ('user_embeddings', 'item_embeddings', 'user_biases', 'item_biases'):
+            getattr(ref, name).weight.copy_(getattr(model, name).weight.cpu())
+    users = torch.from_numpy(rng.integers(0, n_users, m))
+    items = torch.from_numpy(rng.integers(0, n_items, m))
+    w = torch.from_numpy(rng.normal(size=m).astype(np.float32))
+    model.train()
+    out = model(users.cuda(), items.cuda())
+    (out * w.cuda()).sum().backward()
+    exp = ref(users, items, (1.0, 5.0))
+    (exp * w).sum().backward()
+    np.testing.assert_allclose(out.detach().cpu().numpy(), exp.detach().numpy(), rtol=1e-5)
+    for name in ('user_embeddings', 'item_embeddings', 'user_biases', 'item_biases'):
+        np.testing.assert_allclose(getattr(model, name).weight.grad.cpu().numpy(),
+                                   getattr(ref, name).weight.grad.numpy(), rtol=1e-4, atol=1e-6,
+                                   err_msg=name)
+
+
+# ------------------------------------------------------------------------------------ train steps
+@pytest.mark.parametrize('chunk_len', [0, 1, 5])
+@pytest.mark.parametrize('path', IMPLICIT, ids=_ids(IMPLICIT))
+def test_golden_implicit_steps(path, chunk_len):
+    """Losses and final parameters after 3 steps equal what the unmodified reference produced."""
+    from collie_b200 import _abi
+    g = np.load(path)
+    name = os.path.basename(path)[:-4]
+    meta = {k[5:]: g[k] for k in g.files if k.startswith('meta_')}
+    model = _model_from_golden(g, GOLDEN_OPT[name], LOSS_ARG[str(g['loss_name'])], meta=meta)
+    opts = model.configure_optimizers()
+    prev = _abi.lib().cmf_set_tuning(0, chunk_len)
+    try:
+        for s in range(int(g['steps'])):
+            batch = ((torch.from_numpy(g[f'step{s}_users'].astype(np.int32)).cuda(),
+                      torch.from_numpy(g[f'step{s}_pos'].astype(np.int32)).cuda()),
+                     torch.from_numpy(g[f'step{s}_negs']).cuda())
+            val = model.calculate_loss(batch).item()      # loss-only path
+            loss = model.fused_step(batch, optimizers=opts).item()
+            np.testing.assert_allclose(loss, float(g[f'step{s}_loss']), rtol=1e-5)
+            np.testing.assert_allclose(val, loss, rtol=1e-6)
+    finally:
+        _abi.lib().cmf_set_tuning(0, prev)
+    for k, t in _tables(model).items():
+        np.testing.assert_allclose(t.detach().cpu().numpy(), g['final_' + k], rtol=1e-5, atol=1e-6,
+                                   err_msg=k)
+
+
+@pytest.mark.parametrize('path', EXPLICIT, ids=_ids(EXPLICIT))
+def test_golden_explicit_steps(path):
+    g = np.load(path)
+    name = os.path.basename(path)[:-4]
+    model = _model_from_golden(g, GOLDEN_OPT[name], 'mae' if 'mae' in name else 'mse',
+                               explicit=True)
+    opts = model.configure_optimizers()
+    for s in range(int(g['steps'])):
+        batch = (torch.from_numpy(g[f'step{s}_users'].astype(np.int32)).cuda(),
+                 torch.from_numpy(g[f'step{s}_items'].astype(np.int32)).cuda(),
+                 torch.from_numpy(g[f'step{s}_ratings']).cuda())
+        loss = model.fused_step(batch, optimizers=opts).item()
+        np.testing.assert_allclose(loss, float(g[f'step{s}_loss']), rtol=1e-5)
+    for k, t in _tables(model).items():
+        np.testing.assert_allclose(t.detach().cpu().numpy(), g['final_' + k], rtol=1e-5, atol=1e-6,
+                                   err_msg=k)
+
+
+@pytest.mark.parametrize('path', IMPLICIT, ids=_ids(IMPLICIT))
+def test_golden_implicit_gradients(path):
+    """Gradients of all four tables: with plain SGD at lr=1 the fused step moves every parameter by
+    exactly -grad, which is compared with autograd's gradient from the reference run."""
+    g = np.load(path)
+    meta = {k[5:]: g[k] for k in g.files if k.startswith('meta_')}
+    model = _model_from_golden(g, 'sgd', LOSS_ARG[str(g['loss_name'])], meta=meta)
+    model.hparams.lr = 1.0
+    model.hparams.bias_lr = 1.0
+    opts = model.configure_optimizers()
+    before = {k: t.detach().clone() for k, t in _tables(model).items()}
+    batch = ((torch.from_numpy(g['step0_users'].astype(np.int32)).cuda(),
+              torch.from_numpy(g['step0_pos'].astype(np.int32)).cuda()),
+             torch.from_numpy(g['step0_negs']).cuda())
+    model.fused_step(batch, optimizers=opts)
+    for k, t in _tables(model).items():
+        grad = (before[k] - t.detach()).cpu().numpy()
+        ref = g['step0_grad_' + k]
+        scale = np.abs(ref).max() + 1e-12
+        np.testing.assert_allclose(grad, ref, rtol=1e-4, atol=2e-6 * max(1.0, scale), err_msg=k)
+
+
+def test_selected_negative_indices_bit_exact():
+    """argmax slot (adaptive) / first-violation slot (warp) equal the oracle's, bit for bit, on
+    exactly representable weights (multiples of 2^-3) so that ties are genuine."""
+    import collie_b200 as cb
+    from oracle import collie_oracle as O
+    rng = np.random.default_rng(9)
+    n_users, n_items, dim, n_neg, b = 40, 60, 16, 8, 512
+    for loss, oname in (('bpr', 'adaptive_bpr'), ('adaptive', 'adaptive_hinge'), ('warp', 'warp')):
+        model = cb.MatrixFactorizationModel(train=_implicit_data(n_users, n_items, n_neg),
+                                            embedding_dim=dim, loss=loss,
+                                            lr_scheduler_func=None).cuda()
+        with torch.no_grad():
+            for p in model.parameters():
+                p.copy_(torch.from_numpy((rng.integers(-4, 5, tuple(p.shape)) / 8.0)
+                                         .astype(np.float32)))
+        users = torch.from_numpy(rng.integers(0, n_users, b).astype(np.int32))
+        pos = torch.from_numpy(rng.integers(0, n_items, b).astype(np.int32))
+        negs = torch.from_numpy(rng.integers(0, n_items, (b, n_neg)))
+        out = {'sel': None, 'pos_scores': None, 'neg_scores': None}
+        loss_val = model.fused_step(((users.cuda(), pos.cuda()), negs.cuda()), train=False,
+                                    outputs=out).item()
+        tabs = [t.detach().cpu() for t in _tables(model).values()]
+        ps = O.mf_forward(*tabs, users, pos)
+        ns = O.mf_forward(*tabs, users.long().repeat(n_neg), negs.t().flatten()).view(n_neg, b)
+        assert torch.equal(out['pos_scores'].cpu(), ps)
+        assert torch.equal(out['neg_scores'].cpu(), ns.t())
+        if oname == 'warp':
+            exp_sel = O.warp_first_violation(1.0 - ps.view(b, 1) + ns.t())
+            exp_loss = O.warp(ps, ns, n_items)
+        else:
+            exp_sel = torch.max(ns, 0)[1]
+            exp_loss = O.IMPLICIT_LOSSES[oname](ps, ns)
+        assert torch.equal(out['sel'].cpu().long(), exp_sel.long())
+        np.testing.assert_allclose(loss_val, exp_loss.item(), rtol=1e-5)
+
+
+# ------------------------------------------------------------------------------------ sampler
+@pytest.mark.parametrize('exact', [False, True])
+def test_sampled_negatives_bit_exact(exact):
+    """Device sampler == the oracle's statement of the stream, for the stand-alone kernel and for
+    the negatives the fused step draws in-kernel."""
+    import collie_b200 as cb
+    from oracle import collie_oracle as O
+    n_users, n_items, n_neg = 30, 45, 6
+    data = _implicit_data(n_users, n_items, n_neg, seed=4, exact=exact, n=500)
+    st = data.device_state('cuda')
+    gidx = torch.arange(100, 356, device='cuda')
+    users = st['users'][gidx]
+    got = data.sample_negatives(users, gidx, epoch=3).cpu().numpy()
+    csr = data.mat.tocsr()
+    csr.sort_indices()
+    exp = O.philox_negatives(data.seed, 3, gidx.cpu().numpy(), users.cpu().numpy(), n_neg, n_items,
+                             csr.indptr if exact else None, csr.indices if exact else None,
+                             max_tries=200)
+    assert np.array_equal(got, exp)
+    if exact:
+        dense = data.mat.toarray() > 0
+        u = users.cpu().numpy()
+        for r in range(len(u)):
+            assert not dense[u[r], got[r]].any()
+            assert len(set(got[r].tolist())) == n_neg
+    model = cb.MatrixFactorizationModel(train=data, embedding_dim=8, loss='bpr',
+                                        lr_scheduler_func=None).cuda()
+    out = {'negs': None}
+    batch = cb.interactions.DeviceBatch(users, st['items'][gidx], gidx, None)
+    model.fused_step(batch, train=False, interactions=data, epoch=3, outputs=out)
+    assert np.array_equal(out['negs'].cpu().numpy(), exp)
+
+
+def test_exact_sampler_budget_exhaustion_matches_oracle():
+    import collie_b200 as cb
+    from oracle import collie_oracle as O
+    # user 0 has interacted with every item but two: the rejection budget runs out
+    n_items = 12
+    users = np.zeros(10, dtype=np.int64)
+    items = np.arange(10)
+    data = cb.Interactions(users=users, items=items, num_users=1, num_items=n_items,
+                           num_negative_samples=4, allow_missing_ids=True,
+                           check_num_negative_samples_is_valid=False,
+                           max_number_of_samples_to_consider=5, seed=11)
+    gidx = torch.arange(10, device='cuda')
+    u = torch.zeros(10, dtype=torch.int32, device='cuda')
+    got = data.sample_negatives(u, gidx, epoch=0).cpu().numpy()
+    csr = data.mat.tocsr()
+    exp = O.philox_negatives(11, 0, np.arange(10), users, 4, n_items, csr.indptr, csr.indices,
+                             max_tries=5)
+    assert np.array_equal(got, exp)
+
+
+# ------------------------------------------------------------------------------------ metrics
+@pytest.mark.parametrize('path', METRICS, ids=_ids(METRICS))
+def test_golden_metrics(path):
+    """evaluate_in_batches equals the reference's numbers (fused route and materialised route)."""
+    import collie_b200 as cb
+    g = np.load(path)
+    n_users, n_items, dim = int(g['n_users']), int(g['n_items']), int(g['dim'])
+    test = cb.Interactions(users=g['test_users'], items=g['test_items'], num_users=n_users,
+                           num_items=n_items, allow_missing_ids=True,
+                           check_num_negative_samples_is_valid=False,
+                           max_number_of_samples_to_consider=0)
+    model = cb.MatrixFactorizationModel(train=test, embedding_dim=dim,
+                                        lr_scheduler_func=None).cuda()
+    with torch.no_grad():
+        for k, t in _tables(model).items():
+            t.copy_(torch.from_numpy(g[k]))
+    has_ties = 'exact_grid' in path
+    scores = cb.get_preds(model, np.arange(n_users), n_items)
+    np.testing.assert_allclose(scores.cpu().numpy(), g['scores'], rtol=1e-5, atol=1e-6)
+
+    def custom(targets, user_ids, preds, k):   # forces the materialised route
+        return cb.mapk(targets, user_ids, preds, k)
+    for k in (1, 4, 10):
+        exp = g[f'k{k}_bs20']
+        got = cb.evaluate_in_batches([cb.mapk, cb.mrr, cb.auc], test, model, k=k, verbose=False)
+        np.testing.assert_allclose(got[2], exp[2], rtol=1e-5)
+        if not has_ties:
+            np.testing.assert_allclose(got[:2], exp[:2], rtol=1e-5)
+            got2 = cb.evaluate_in_batches([custom, cb.mrr], test, model, k=k, batch_size=7,
+                                          verbose=False)
+            np.testing.assert_allclose(got2, exp[:2], rtol=1e-5)
+        assert isinstance(cb.evaluate_in_batches([cb.mapk], test, model, k=k, verbose=False), float)
+
+
+def test_reference_metric_known_answers_on_gpu():
+    """tests/test_metrics.py:101-154 of the reference, through the CUDA metric callables."""
+    import json
+    import collie_b200 as cb
+    ka = json.load(open(os.path.join(GOLDEN, 'reference_known_answers.json')))
+    users, items = np.array(ka['metrics_users']), np.array(ka['metrics_items'])
+    targets = sp.coo_matrix((np.ones(len(users)), (users, items)), shape=(3, 4)).tocsr()
+    scores = torch.tensor(ka['metrics_scores'], dtype=torch.float32).cuda()
+    assert cb.mapk(targets, np.array([1, 2]), scores[[1, 2]], k=4) == ka['mapk_k4_users_1_2']
+    np.testing.assert_almost_equal(cb.mapk(targets, np.arange(3), scores, k=1), ka['mapk_k1'])
+    np.testing.assert_almost_equal(cb.mrr(targets, np.arange(3), scores), ka['mrr'])
+    from sklearn.metrics import roc_auc_score
+    exp = np.mean([roc_auc_score(targets[i].toarray()[0], scores[i].cpu().numpy())
+                   for i in range(3)])
+    np.testing.assert_almost_equal(cb.auc(targets, np.arange(3), scores), exp)
+    with pytest.raises(ValueError):
+        cb.mapk(targets, np.arange(3), scores, k=5)
+
+
+def test_topk_ids_bit_exact_with_ties():
+    """Top-k item ids equal the oracle's canonical order (score desc, id asc) bit for bit on the
+    exact-arithmetic fixture, which is full of genuine ties."""
+    import collie_b200 as cb
+    from collie_b200 import metrics as M
+    from oracle import collie_oracle as O
+    g = np.load(os.path.join(GOLDEN, 'metrics_exact_grid.npz'))
+    n_users, n_items = int(g['n_users']), int(g['n_items'])
+    tabs = tuple(torch.from_numpy(g[k]).cuda() for k in ('U', 'I', 'bu', 'bi'))
+    users = torch.arange(n_users, dtype=torch.int32, device='cuda')
+    coo = sp.coo_matrix((np.ones(len(g['test_users'])), (g['test_users'], g['test_items'])),
+                        shape=(n_users, n_items))
+    indptr, items, _ = M._targets_device(coo.tocsr(), np.arange(n_users), 'cuda')
+    for k in (1, 10, 37, n_items):
+        res = M._eval_tile('cuda', n_users, n_items, k, indptr, items, {'topk', 'mapk', 'mrr'},
+                           tables=tabs, user_ids=users)
+        exp_ids = O.topk_ids(g['scores'], k)
+        assert np.array_equal(res['topk_ids'].cpu().numpy(), exp_ids)
+        exp_scores = np.take_along_axis(g['scores'], exp_ids, axis=1)
+        assert np.array_equal(res['topk_scores'].cpu().numpy(), exp_scores)
+        np.testing.assert_allclose(res['ap'].cpu().numpy(),
+                                   O.mapk_per_user(coo.tocsr(), np.arange(n_users), g['scores'], k),
+                                   rtol=1e-12)
+        mrr_exp = O.mrr_per_user(coo.tocsr(), np.arange(n_users), g['scores'])
+        nb = res['n_before_best'].cpu().numpy()
+        got = np.where(nb >= 0, 1.0 / (nb + 1.0), 0.0)
+        np.testing.assert_allclose(got, mrr_exp, rtol=1e-12)
+
+
+# ------------------------------------------------------------------------------------ end to end
+def test_trainer_end_to_end_and_checkpoint(tmp_path, capsys):
+    import collie_b200 as cb
+    from oracle import collie_oracle as O
+    rng = np.random.default_rng(5)
+    n_users, n_items = 120, 90
+    # planted structure: user u likes items with the same parity
+    users = rng.integers(0, n_users, 6000)
+    items = (rng.integers(0, n_items // 2, 6000) * 2 + users % 2) % n_items
+    key = np.unique(users * n_items + items)
+    users, items = key // n_items, key % n_items
+    cut = int(0.9 * len(users))
+    perm = rng.permutation(len(users))
+    tr, te = perm[:cut], perm[cut:]
+    kw = dict(num_users=n_users, num_items=n_items, allow_missing_ids=True, seed=7,
+              num_negative_samples=5)
+    train = cb.Interactions(users=users[tr], items=items[tr], **kw)
+    val = cb.Interactions(users=users[te], items=items[te], **kw)
+    model = cb.MatrixFactorizationModel(train=cb.InteractionsDataLoader(train, batch_size=256,
+                                                                        shuffle=True),
+                                        val=cb.InteractionsDataLoader(val, batch_size=256),
+                                        embedding_dim=16, lr=5e-2, sparse=True,
+                                        optimizer='sparse_adam', loss='adaptive')
+    before = None
+    trainer = cb.CollieMinimalTrainer(model, max_epochs=8, verbosity=1,
+                                      early_stopping_patience=None)
+    out = capsys.readouterr().out
+    assert 'Detected GPU. Setting ``gpus`` to 1.' in out
+    trainer.fit(model)
+    out = capsys.readouterr().out
+    assert '| Name            | Type            | Params' in out
+    assert 'Epoch     1: train loss:' in out and 'val loss:' in out
+    assert model.hparams.num_epochs_completed == 8 and trainer.num_epochs_completed == 8
+    trainer.fit(model)                       # same max_epochs: no-op
+    assert trainer.num_epochs_completed == 8
+    trainer.max_epochs += 1
+    trainer.fit(model)
+    assert trainer.num_epochs_completed == 9
+    got = cb.evaluate_in_batches([cb.mapk, cb.mrr, cb.auc], val, model, k=10, verbose=False)
+    tabs = tuple(t.detach().cpu() for t in _tables(model).values())
+    exp = O.evaluate_in_batches(['mapk', 'mrr', 'auc'], val.mat, tabs, k=10)
+    np.testing.assert_allclose(got, exp, rtol=1e-5)
+    assert got[2] > 0.8, got                 # the planted structure is learned
+    # checkpoint round trip with the reference's keys
+    path = tmp_path / 'model.pth'
+    model.save_model(path)
+    blob = torch.load(path, weights_only=False)
+    assert set(blob['state_dict']) == {'user_biases.weight', 'item_biases.weight',
+                                       'user_embeddings.weight', 'item_embeddings.weight'}
+    assert tuple(blob['state_dict']['user_biases.weight'].shape) == (n_users, 1)
+    loaded = cb.MatrixFactorizationModel(load_model_path=path).cuda()
+    assert loaded.hparams.num_epochs_completed == 9
+    u = torch.arange(50, device='cuda')
+    assert torch.equal(loaded(u, u), model(u, u))
+    assert before is None
+
+
+def test_explicit_training_reduces_mse():
+    import collie_b200 as cb
+    rng = np.random.default_rng(6)
+    n_users, n_items, n = 200, 150, 8000
+    users, items = rng.integers(0, n_users, n), rng.integers(0, n_items, n)
+    ratings = (1 + (users % 3) + (items % 3)).astype(np.float32)
+    data = cb.ExplicitInteractions(users=users, items=items, ratings=ratings, num_users=n_users,
+                                   num_items=n_items, allow_missing_ids=True)
+    model = cb.MatrixFactorizationModel(train=cb.InteractionsDataLoader(data, batch_size=512,
+                                                                        shuffle=True),
+                                        embedding_dim=64, lr=1e-2, loss='mse', y_range=(1, 5),
+                                        lr_scheduler_func=None)
+    trainer = cb.CollieTrainer(model, max_epochs=1, verbosity=0, enable_model_summary=False)
+    trainer.fit(model)
+    first = model.calculate_loss(next(iter(model.train_loader))).item()
+    trainer.max_epochs = 15
+    trainer.fit(model)
+    last = model.calculate_loss(next(iter(model.train_loader))).item()
+    assert last < 0.5 * first, (first, last)
+
+
+def test_errors_are_loud():
+    import collie_b200 as cb
+    from collie_b200 import _abi
+    data = _implicit_data(10, 12, 1)
+    with pytest.raises(ValueError, match='WARP'):
+        cb.MatrixFactorizationModel(train=data, loss='warp', lr_scheduler_func=None)
+    with pytest.raises(ValueError, match='not a valid loss'):
+        cb.MatrixFactorizationModel(train=data, loss='nope', lr_scheduler_func=None)
+    model = cb.MatrixFactorizationModel(train=data, lr_scheduler_func=None, optimizer='nope')
+    with pytest.raises(ValueError, match='not a valid optimizer'):
+        model.configure_optimizers()
+    model = cb.MatrixFactorizationModel(train=data, lr_scheduler_func=None)
+    with pytest.raises(_abi.CmfError):          # CPU tensors: no fallback
+        model(torch.zeros(3, dtype=torch.long), torch.zeros(3, dtype=torch.long))
+    model.cuda()
+    with pytest.raises(ValueError, match='Implicit loss with explicit data'):
+        model.calculate_loss((torch.zeros(3), torch.zeros(3), torch.zeros(3)))
+    with pytest.raises(ValueError):
+        model.calculate_loss((torch.zeros(3),))
+    # workspace too small is reported, not ignored
+    a = _abi.cmf_step_t()
+    assert _abi.lib().cmf_train_step(_abi.C.byref(a), None) == -1
+    assert b'null parameter table' in _abi.lib().cmf_last_error()
