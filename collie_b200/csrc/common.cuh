@@ -196,9 +196,12 @@ struct Row {
     for (int i = 0; i < R * V; ++i) s = fmaf(f[i], o.f[i], s);
     return s;
   }
+  // f += round(a * x): the product is rounded BEFORE the add (no FMA), as autograd does when it
+  // scales an embedding row by a gradient coefficient and then sums contributions. This makes
+  // +g*x and -g*x cancel exactly, which sign-sensitive rules (Adam's first steps) depend on.
   __device__ __forceinline__ void axpy(float a, const Row& x) {
 #pragma unroll
-    for (int i = 0; i < R * V; ++i) f[i] = fmaf(a, x.f[i], f[i]);
+    for (int i = 0; i < R * V; ++i) f[i] = __fadd_rn(f[i], __fmul_rn(a, x.f[i]));
   }
 };
 

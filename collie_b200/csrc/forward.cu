@@ -90,12 +90,12 @@ using namespace cmf;
 extern "C" int cmf_forward_scores(const float* U, const float* I, const float* bu, const float* bi,
                                   int32_t D, const void* users, const void* items, int32_t idx_bytes,
                                   int64_t M, const float* host_y_range, float* out, void* stream) {
-  CMF_REQUIRE(U && I && bu && bi && out, "cmf_forward_scores: null table or output pointer");
   CMF_REQUIRE(idx_bytes == 4 || idx_bytes == 8, "cmf_forward_scores: idx_bytes must be 4 or 8");
   CMF_REQUIRE(geom_supported(D), "cmf_forward_scores: embedding_dim %d unsupported (1..1024)", D);
   CMF_REQUIRE(M >= 0, "cmf_forward_scores: negative M");
+  CMF_REQUIRE(U && I && bu && bi, "cmf_forward_scores: null table pointer");
   if (M == 0) return CMF_OK;
-  CMF_REQUIRE(users && items, "cmf_forward_scores: null id pointer");
+  CMF_REQUIRE(users && items && out, "cmf_forward_scores: null id or output pointer");
   const RowGeom g = row_geom(D);
   const int has_range = host_y_range != nullptr;
   const float lo = has_range ? host_y_range[0] : 0.f, hi = has_range ? host_y_range[1] : 1.f;
