@@ -11,7 +11,7 @@ OBJS      := $(patsubst $(SRC_DIR)/%.cu,$(OBJ_DIR)/%.o,$(SRCS))
 
 all: $(LIB)
 
-$(OBJ_DIR)/%.o: $(SRC_DIR)/%.cu $(SRC_DIR)/common.cuh include/collie_b200.h
+$(OBJ_DIR)/%.o: $(SRC_DIR)/%.cu $(wildcard $(SRC_DIR)/*.cuh) include/collie_b200.h
 	@mkdir -p $(OBJ_DIR)
 	$(NVCC) $(NVCCFLAGS) -c $< -o $@
 

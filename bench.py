@@ -1,0 +1,411 @@
+#!/usr/bin/env python
+"""Benchmark of the MF training hot path (BASELINE.json metric) -- see DESIGN.md "Measurement".
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Own arm: one "step" = one fused training step (on-device negative sampling + gather + scores +
+loss + backward + sparse Adam / SGD updates) over one batch of the workload
+  C3 = implicit MF, loss 'bpr' with 5 negatives (-> adaptive BPR), sparse Adam + SGD biases,
+       embedding_dim 128, synthetic MovieLens-20M shape (138,493 users x 26,744 items, 20 M
+       interactions), batch 262,144 interactions per GPU.
+`value` is interactions/s with the batch already in HBM; `e2e` is the same loop fed from pinned
+host memory (H2D of every batch, D2H of every loss) through the public API. The reference arm
+(`--impl reference`) times the oracle's restatement of the reference's own PyTorch CPU path on the
+host cores (the reference is pure Python and cannot travel to the GPU box; oracle/ is used here
+only as the thing being timed for the baseline, never by the product path).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOAD = {
+    'name': 'C3 implicit MF bpr(N=5)->adaptive_bpr, sparse_adam + sgd bias, D=128, '
+            'synthetic ML-20M shape',
+    'num_users': 138493, 'num_items': 26744, 'interactions': 20_000_000, 'dim': 128, 'n_neg': 5,
+    'batch_per_gpu': 262144, 'lr': 1e-3, 'bias_lr': 1e-2, 'seed': 2,
+}
+
+
+def synth_interactions(num_users, num_items, n, seed):
+    """MovieLens-20M-like skew: item popularity ~ 1/(rank+60) (top item ~0.3 % of interactions,
+    like ML-20M's most-rated film), user activity log-normal. CPU generator -> same tensors for
+    every arm and every rank."""
+    g = torch.Generator().manual_seed(seed)
+    item_w = 1.0 / (torch.arange(num_items, dtype=torch.float64) + 61.0)
+    item_cdf = torch.cumsum(item_w / item_w.sum(), 0)
+    user_w = torch.exp(torch.randn(num_users, generator=g, dtype=torch.float64))
+    user_cdf = torch.cumsum(user_w / user_w.sum(), 0)
+    users = torch.searchsorted(user_cdf, torch.rand(n, generator=g, dtype=torch.float64))
+    items = torch.searchsorted(item_cdf, torch.rand(n, generator=g, dtype=torch.float64))
+    # item ids are shuffled so popularity is not monotone in the id
+    relabel = torch.randperm(num_items, generator=g)
+    return (users.clamp_(max=num_users - 1).to(torch.int32),
+            relabel[items.clamp_(max=num_items - 1)].to(torch.int32))
+
+
+# ------------------------------------------------------------------------------------------ clocks
+class ClockSampler(object):
+    QUERY = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,'
+             'clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+             'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, gpu_index):
+        self.gpu_index = gpu_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix='.csv')
+            os.close(fd)
+            self.proc = subprocess.Popen(
+                ['nvidia-smi', f'--id={self.gpu_index}', f'--query-gpu={self.QUERY}',
+                 '--format=csv,noheader,nounits', '-lms', '100'],
+                stdout=open(self.path, 'w'), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': [], 'samples': 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, reasons, mx = [], set(), None
+        try:
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(',')]
+                if len(f) < 9:
+                    continue
+                try:
+                    sm.append(float(f[1]))
+                    mx = float(f[2])
+                except ValueError:
+                    continue
+                for name, val in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown',
+                                      'sw_power_cap'), f[5:9]):
+                    if val.lower().startswith('active'):
+                        reasons.add(name)
+            os.unlink(self.path)
+        except Exception:
+            pass
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=mx, reasons=sorted(reasons),
+                       samples=len(sm))
+        return out
+
+
+# ------------------------------------------------------------------------------------------ CPU arm
+def cpu_port_run(users, items, steps, warmup, batch, threads):
+    """The reference's CPU training step, restated (oracle/collie_oracle.py): nn.Embedding(sparse)
+    x4, forward for positives and for users.repeat(N) negatives, adaptive BPR, autograd backward,
+    torch.optim.SparseAdam + SGD(bias); negatives by np.random.randint like the approximate loader
+    (collie/interactions/datasets.py:439-443). Returns seconds for `steps` timed steps."""
+    from oracle import collie_oracle as O
+    w = WORKLOAD
+    torch.set_num_threads(threads)
+    model = O.OracleMF(w['num_users'], w['num_items'], w['dim'], sparse=True, seed=0)
+    opts = O.make_optimizers(model, 'sparse_adam', 'sgd', w['lr'], w['bias_lr'])
+    rng = np.random.RandomState(w['seed'])
+    n = users.shape[0]
+    t0 = None
+    for s in range(warmup + steps):
+        if s == warmup:
+            t0 = time.perf_counter()
+        a = (s * batch) % max(1, n - batch)
+        bu, bp = users[a:a + batch], items[a:a + batch]
+        negs = torch.from_numpy(rng.randint(0, w['num_items'], size=(batch, w['n_neg'])))
+        O.train_step(model, opts, lambda: model.implicit_loss(bu, bp, negs, 'adaptive_bpr'))
+    return time.perf_counter() - t0
+
+
+def run_reference(args, rank, world):
+    """Reference arm: the reference's CPU path (oracle port) on all host threads. Exactly K timed
+    steps after W warm-up steps; each step is a bounded sample of the workload's batch, sized from
+    one calibration step so that the whole run ends within a few minutes."""
+    if rank != 0:
+        return
+    w = WORKLOAD
+    threads = os.cpu_count() or 1
+    full = w['batch_per_gpu']
+    total_steps = args.steps + args.warmup
+    calib = 32768
+    cu, ci = synth_interactions(w['num_users'], w['num_items'], calib * 3, w['seed'])
+    t_calib = cpu_port_run(cu, ci, 1, 1, calib, threads)          # seconds for one 32k step
+    budget = 150.0
+    batch = full
+    while batch > 4096 and t_calib * (batch / calib) * total_steps > budget:
+        batch //= 2
+    users, items = synth_interactions(w['num_users'], w['num_items'], batch * (total_steps + 1),
+                                      w['seed'])
+    secs = cpu_port_run(users, items, args.steps, args.warmup, batch, threads)
+    value = args.steps * batch / secs
+    sample = (f'{args.steps} timed steps (+{args.warmup} warm-up) of {batch} interactions each '
+              f'(workload batch is {full}); same tables, distributions and hyper-parameters; '
+              'reference CPU path restated in torch (oracle port), all host threads')
+    line = {
+        'impl': 'reference', 'metric': 'MF train interactions/s (fwd+bwd+sparse Adam)',
+        'value': value, 'unit': 'interactions/s', 'n_gpus': args.gpus, 'steps': args.steps,
+        'warmup': args.warmup, 'ms_per_step': 1e3 * secs / args.steps, 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': config_dict(args.gpus),
+        'cpu_baseline': {'value': value, 'unit': 'interactions/s', 'cores': threads,
+                         'kind': 'port', 'sample': sample},
+        'e2e': {'value': value, 'unit': 'interactions/s', 'h2d_bytes_per_step': 0,
+                'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def config_dict(n_gpus):
+    w = WORKLOAD
+    return {'workload': w['name'], 'num_users': w['num_users'], 'num_items': w['num_items'],
+            'interactions': w['interactions'], 'embedding_dim': w['dim'],
+            'num_negative_samples': w['n_neg'], 'loss': 'bpr (adaptive_bpr, N=5)',
+            'optimizer': 'sparse_adam + sgd bias', 'batch_per_gpu': w['batch_per_gpu'],
+            'global_batch': w['batch_per_gpu'] * n_gpus,
+            'parallelism': f'user-partitioned data parallel x{n_gpus}, item table row-sharded'
+            if n_gpus > 1 else 'single GPU',
+            'l2': 'tables + Adam state = 255 MB > 126 MB L2; every step reads a new batch'}
+
+
+# ------------------------------------------------------------------------------------------ GPU arm
+def run_ours(args, rank, world, local_rank):
+    import torch.distributed as dist
+    import collie_b200 as cb
+    from collie_b200 import _abi
+    from collie_b200.interactions import DeviceBatch
+    w = WORKLOAD
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    B = w['batch_per_gpu']
+    steps, warmup = args.steps, max(args.warmup, 3)
+
+    if world > 1:
+        from collie_b200 import distributed as cbd
+        return cbd.bench_sharded(args, rank, world, local_rank, WORKLOAD, synth_interactions,
+                                 config_dict, ClockSampler)
+
+    users, items = synth_interactions(w['num_users'], w['num_items'], w['interactions'], w['seed'])
+    data = cb.Interactions(users=users.numpy(), items=items.numpy(), num_users=w['num_users'],
+                           num_items=w['num_items'], num_negative_samples=w['n_neg'],
+                           allow_missing_ids=True, remove_duplicate_user_item_pairs=False,
+                           check_num_negative_samples_is_valid=False,
+                           max_number_of_samples_to_consider=0, seed=w['seed'])
+    model = cb.MatrixFactorizationModel(train=data, embedding_dim=w['dim'], sparse=True,
+                                        lr=w['lr'], bias_lr=w['bias_lr'], optimizer='sparse_adam',
+                                        bias_optimizer='sgd', loss='bpr',
+                                        lr_scheduler_func=None).to(dev)
+    opts = model.configure_optimizers()
+    n = data.num_interactions
+    g = torch.Generator().manual_seed(w['seed'])
+    perm = torch.randperm(n, generator=g)
+    users_h = users[perm].contiguous().pin_memory()
+    items_h = items[perm].contiguous().pin_memory()
+    gidx_h = perm.contiguous().pin_memory()
+    users_d, items_d, gidx_d = users_h.to(dev), items_h.to(dev), gidx_h.to(dev)
+    n_batches = n // B
+
+    def device_batch(i):
+        a = (i % n_batches) * B
+        return DeviceBatch(users_d[a:a + B], items_d[a:a + B], gidx_d[a:a + B], None)
+
+    def one_step(i):
+        return model.fused_step(device_batch(i), optimizers=opts, interactions=data, epoch=0)
+
+    # ---- device-resident throughput
+    for i in range(warmup):
+        one_step(i)
+    torch.cuda.synchronize()
+    launches0 = _abi.launch_count()
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    ev0.record()
+    for i in range(steps):
+        loss = one_step(warmup + i)
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    clk = clocks.stop()
+    launches = _abi.launch_count() - launches0
+    value = steps * B / (ms * 1e-3)
+
+    # ---- end to end: pinned host batches in, loss out, every step (double-buffered copies)
+    copy_stream = torch.cuda.Stream(dev)
+    main = torch.cuda.current_stream(dev)
+    slots = [dict(u=torch.empty(B, dtype=torch.int32, device=dev),
+                  i=torch.empty(B, dtype=torch.int32, device=dev),
+                  g=torch.empty(B, dtype=torch.int64, device=dev),
+                  ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(2)]
+    loss_host = torch.empty(steps + warmup, dtype=torch.float32).pin_memory()
+
+    def e2e_loop(count, base):
+        for s_ in slots:
+            s_['free'].record(main)
+        for j in range(count):
+            slot = slots[j % 2]
+            a = ((base + j) % n_batches) * B
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(slot['free'])
+                slot['u'].copy_(users_h[a:a + B], non_blocking=True)
+                slot['i'].copy_(items_h[a:a + B], non_blocking=True)
+                slot['g'].copy_(gidx_h[a:a + B], non_blocking=True)
+                slot['ready'].record(copy_stream)
+            main.wait_event(slot['ready'])
+            out = model.fused_step(DeviceBatch(slot['u'], slot['i'], slot['g'], None),
+                                   optimizers=opts, interactions=data, epoch=1)
+            loss_host[j:j + 1].copy_(out.view(1), non_blocking=True)
+            slot['free'].record(main)
+
+    e2e_loop(warmup, 0)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    e2e_loop(steps, warmup)
+    e1.record()
+    torch.cuda.synchronize()
+    e2e_ms = e0.elapsed_time(e1)
+    e2e_value = steps * B / (e2e_ms * 1e-3)
+    h2d = B * (4 + 4 + 8)
+
+    # ---- roofline of the dominant kernel (k_fused_step), timed by events inside the library
+    lib = _abi.lib()
+    lib.cmf_profile_enable(1)
+    prof_steps = min(steps, 20)
+    outs = {'negs': None}
+    for i in range(prof_steps):
+        model.fused_step(device_batch(1000 + i), optimizers=opts, interactions=data, epoch=2,
+                         outputs=outs if i == prof_steps - 1 else None)
+    C = _abi.C
+    t_sort, t_fused, t_upd = C.c_double(), C.c_double(), C.c_double()
+    n_steps, item_rows, user_rows = C.c_int64(), C.c_int64(), C.c_int64()
+    lib.cmf_profile_read(C.byref(t_sort), C.byref(t_fused), C.byref(t_upd), C.byref(n_steps),
+                         C.byref(item_rows), C.byref(user_rows))
+    lib.cmf_profile_enable(0)
+    last = device_batch(1000 + prof_steps - 1)
+    uq = int(torch.unique(last.users).numel())
+    iq = int(torch.unique(torch.cat([outs['negs'].flatten(), last.items.long()])).numel())
+    D, N, T = w['dim'], w['n_neg'], 4
+    gather_bytes = B * (2 + N) * D * T + B * (2 + N) * T + B * 2 * 4
+    inplace_users = uq - int(user_rows.value)
+    fused_bytes = gather_bytes + inplace_users * (6 * D * T + 2 * T)
+    update_bytes = (iq + int(user_rows.value)) * (6 * D * T + 2 * T)
+    step_bytes = gather_bytes + (uq + iq) * (6 * D * T + 2 * T)
+    ns = max(1, n_steps.value)
+    fused_ms = t_fused.value / ns
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+    except Exception:
+        pass
+    peak = float(peaks.get('hbm_gbs', 6650.0))
+    achieved = fused_bytes / (fused_ms * 1e-3) / 1e9
+    roofline = {
+        'bound': 'hbm', 'kernel': 'k_fused_step', 'achieved': achieved, 'peak': peak,
+        'unit': 'GB/s', 'frac': achieved / peak,
+        'peak_source': 'MEASURED_PEAKS.json hbm_gbs (of measured)' if peaks else
+                       'fallback 6650 GB/s (of fallback)',
+        'traffic': None,
+        'algorithmic_bytes_per_launch': fused_bytes, 'kernel_ms': fused_ms,
+        'phase_ms': {'sort': t_sort.value / ns, 'fused': fused_ms, 'update': t_upd.value / ns},
+        'step_algorithmic_bytes': step_bytes,
+        'step_achieved_gbs': step_bytes / (ms / steps * 1e-3) / 1e9,
+        'unique_users': uq, 'unique_items': iq, 'rows_finished_by_update_kernel':
+            {'items': int(item_rows.value), 'users': int(user_rows.value)},
+        'update_kernel_algorithmic_bytes': update_bytes,
+    }
+    traffic_file = os.path.join(ROOT, 'profiles', 'traffic.json')
+    if os.path.exists(traffic_file):
+        try:
+            roofline['traffic'] = json.load(open(traffic_file)).get('k_fused_step')
+        except Exception:
+            pass
+
+    # ---- secondary headline: evaluation users/s (MAP@10, MRR, AUC) on a bounded user sample
+    eval_info = None
+    if not args.no_eval:
+        n_eval_users = 4096
+        tu = torch.arange(n_eval_users, dtype=torch.int32)
+        ti = torch.from_numpy(np.random.default_rng(5).integers(0, w['num_items'],
+                                                                 (n_eval_users, 8))).flatten()
+        test = cb.Interactions(users=tu.repeat_interleave(8).numpy(), items=ti.numpy(),
+                               num_users=w['num_users'], num_items=w['num_items'],
+                               allow_missing_ids=True, check_num_negative_samples_is_valid=False,
+                               max_number_of_samples_to_consider=0)
+        cb.evaluate_in_batches([cb.mapk], test, model, k=10, verbose=False)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        m = cb.evaluate_in_batches([cb.mapk, cb.mrr, cb.auc], test, model, k=10, verbose=False)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        eval_info = {'metric': 'eval users/s (MAP@10 + MRR + AUC)', 'value': n_eval_users / dt,
+                     'unit': 'users/s', 'users': n_eval_users, 'precision': 'fp32 SIMT scoring',
+                     'metrics': m}
+
+    # ---- CPU baseline on a bounded sample (rank 0, N = 1 only)
+    cpu = None
+    if not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        cpu_steps, cpu_warm = 3, 1
+        nb = B * (cpu_steps + cpu_warm + 1)
+        secs = cpu_port_run(users[:nb], items[:nb], cpu_steps, cpu_warm, B, threads)
+        cpu = {'value': cpu_steps * B / secs, 'unit': 'interactions/s', 'cores': threads,
+               'kind': 'port',
+               'sample': f'{cpu_steps} steps of batch {B} (+{cpu_warm} warm-up), same tables and '
+                         'distributions; reference CPU path restated in torch (oracle port)'}
+
+    line = {
+        'metric': 'MF train interactions/s (fwd+bwd+sparse Adam)', 'value': value,
+        'unit': 'interactions/s', 'n_gpus': 1, 'steps': steps, 'warmup': warmup,
+        'ms_per_step': ms / steps, 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': config_dict(1),
+        'roofline': roofline, 'cpu_baseline': cpu,
+        'e2e': {'value': e2e_value, 'unit': 'interactions/s', 'h2d_bytes_per_step': h2d,
+                'd2h_bytes_per_step': 4, 'ms_per_step': e2e_ms / steps},
+        'gpu_launches': int(launches),
+        'gpu_launches_note': 'own kernels per step: k_iota + k_fused_step + k_update_rows; the '
+                             'CUB radix sort adds library launches that are not counted',
+        'clocks': clk, 'final_loss': float(loss), 'eval': eval_info,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=50)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-eval', action='store_true')
+    args = ap.parse_args()
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    if args.impl == 'reference':
+        run_reference(args, rank, world)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py needs a CUDA device: collie_b200 has no CPU path')
+    run_ours(args, rank, world, local_rank)
+
+
+if __name__ == '__main__':
+    main()

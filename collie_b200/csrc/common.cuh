@@ -54,44 +54,49 @@ int num_sms();
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // Row geometry: V floats per vector access, G lanes cooperate on one row, R vectors per lane.
+// A warp works on 32 / G rows (interactions) at once, so a smaller G amortises the per-interaction
+// scalar work (ids, RNG, loss) over more lanes at the price of R * V registers per row fragment.
 struct RowGeom {
   int V, G, R;
 };
-inline RowGeom row_geom(int D) {
+inline RowGeom row_geom(int D, int max_g = 32) {
   RowGeom g;
   g.V = (D % 4 == 0) ? 4 : (D % 2 == 0) ? 2 : 1;
-  int vecs = D / g.V;
+  const int vecs = D / g.V;
+  if (max_g < 8) max_g = 8;
   g.G = 4;
-  while (g.G < 32 && g.G < vecs) g.G <<= 1;
+  while (g.G < max_g && g.G < vecs) g.G <<= 1;
+  if (g.G == 4 && vecs > 4) g.G = 8;
   g.R = (vecs + g.G - 1) / g.G;
+  while (g.G < 32 && (g.R > 4 || (g.G == 4 && g.R > 1))) {  // instantiated shapes only
+    g.G <<= 1;
+    g.R = (vecs + g.G - 1) / g.G;
+  }
   return g;
 }
 
-// Dispatch a functor templated on <V, G, R>. R is rounded up to {1, 2, 4, 8}; D <= 1024.
-#define CMF_DISPATCH_GEOM(geom, CALL)                                         \
-  do {                                                                        \
-    const int _V = (geom).V, _G = (geom).G, _R = (geom).R;                    \
-    if (_R == 1) {                                                            \
-      if (_V == 4) {                                                          \
-        if (_G == 4) { CALL(4, 4, 1); } else if (_G == 8) { CALL(4, 8, 1); }  \
-        else if (_G == 16) { CALL(4, 16, 1); } else { CALL(4, 32, 1); }       \
-      } else if (_V == 2) {                                                   \
-        if (_G == 4) { CALL(2, 4, 1); } else if (_G == 8) { CALL(2, 8, 1); }  \
-        else if (_G == 16) { CALL(2, 16, 1); } else { CALL(2, 32, 1); }       \
-      } else {                                                                \
-        if (_G == 4) { CALL(1, 4, 1); } else if (_G == 8) { CALL(1, 8, 1); }  \
-        else if (_G == 16) { CALL(1, 16, 1); } else { CALL(1, 32, 1); }       \
-      }                                                                       \
-    } else if (_R == 2) {                                                     \
-      if (_V == 4) { CALL(4, 32, 2); } else if (_V == 2) { CALL(2, 32, 2); }  \
-      else { CALL(1, 32, 2); }                                                \
-    } else if (_R <= 4) {                                                     \
-      if (_V == 4) { CALL(4, 32, 4); } else if (_V == 2) { CALL(2, 32, 4); }  \
-      else { CALL(1, 32, 4); }                                                \
-    } else {                                                                  \
-      if (_V == 4) { CALL(4, 32, 8); } else if (_V == 2) { CALL(2, 32, 8); }  \
-      else { CALL(1, 32, 8); }                                                \
-    }                                                                         \
+// Dispatch on <V, G, R>; R is rounded up to the instantiated {1, 2, 4, 8}. D <= 1024.
+#define CMF_DISPATCH_GR(V_, geom, CALL)                                              \
+  do {                                                                               \
+    const int _G = (geom).G, _R = (geom).R;                                          \
+    if (_G == 4) { CALL(V_, 4, 1); }                                                 \
+    else if (_G == 8) {                                                              \
+      if (_R == 1) { CALL(V_, 8, 1); } else if (_R == 2) { CALL(V_, 8, 2); }         \
+      else { CALL(V_, 8, 4); }                                                       \
+    } else if (_G == 16) {                                                           \
+      if (_R == 1) { CALL(V_, 16, 1); } else if (_R == 2) { CALL(V_, 16, 2); }       \
+      else { CALL(V_, 16, 4); }                                                      \
+    } else {                                                                         \
+      if (_R == 1) { CALL(V_, 32, 1); } else if (_R == 2) { CALL(V_, 32, 2); }       \
+      else if (_R <= 4) { CALL(V_, 32, 4); } else { CALL(V_, 32, 8); }               \
+    }                                                                                \
+  } while (0)
+
+#define CMF_DISPATCH_GEOM(geom, CALL)                                   \
+  do {                                                                  \
+    if ((geom).V == 4) { CMF_DISPATCH_GR(4, geom, CALL); }              \
+    else if ((geom).V == 2) { CMF_DISPATCH_GR(2, geom, CALL); }         \
+    else { CMF_DISPATCH_GR(1, geom, CALL); }                            \
   } while (0)
 
 inline bool geom_supported(int D) {

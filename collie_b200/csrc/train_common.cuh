@@ -1,0 +1,172 @@
+// Definitions shared by the training-step kernels (train_step.cu, train_step_v2.cu).
+#pragma once
+
+#include <cmath>
+
+#include "common.cuh"
+
+namespace cmf {
+
+constexpr int kMaxNeg = 64;          // negatives per interaction supported by the fused step
+constexpr int kMaxPartials = 8192;   // upper bound on the fused kernel's grid size
+constexpr int kThreads = 256;
+
+struct WsHeader {
+  int item_count;
+  int user_count;
+  unsigned blocks_done;
+  int pad[61];
+};
+static_assert(sizeof(WsHeader) == 256, "header is one 256-byte line group");
+
+// ------------------------------------------------------------------------------- optimizer rules
+struct OptDev {
+  int rule;
+  int dense;        // every row of the table moves each step
+  float lr, wd, eps;
+  float b2;         // Adam: beta2
+  float omb1, omb2; // 1 - beta
+  float step_size;  // SparseAdam: lr*sqrt(1-b2^t)/(1-b1^t); Adam: lr/(1-b1^t)
+  float bc2_sqrt;   // Adam: sqrt(1-b2^t)
+};
+
+inline OptDev make_opt(const cmf_opt_t& o) {
+  OptDev d{};
+  d.rule = o.rule;
+  d.lr = (float)o.lr;
+  d.wd = (float)o.weight_decay;
+  d.eps = (float)(o.rule == CMF_OPT_ADAGRAD ? 1e-10 : o.eps);
+  d.b2 = (float)o.beta2;
+  d.omb1 = (float)(1.0 - o.beta1);
+  d.omb2 = (float)(1.0 - o.beta2);
+  const double t = (double)(o.step < 1 ? 1 : o.step);
+  const double bc1 = 1.0 - std::pow(o.beta1, t), bc2 = 1.0 - std::pow(o.beta2, t);
+  if (o.rule == CMF_OPT_SPARSE_ADAM) d.step_size = (float)(o.lr * std::sqrt(bc2) / bc1);
+  if (o.rule == CMF_OPT_ADAM) { d.step_size = (float)(o.lr / bc1); d.bc2_sqrt = (float)std::sqrt(bc2); }
+  d.dense = (o.rule == CMF_OPT_ADAM) || (o.weight_decay != 0.0);
+  return d;
+}
+
+// One parameter element. m/v are the rule's state (Adagrad keeps its sum in m).
+__device__ __forceinline__ void apply_rule(const OptDev& o, float& p, float& m, float& v, float g) {
+  switch (o.rule) {
+    case CMF_OPT_SPARSE_ADAM: {  // torch/optim/sparse_adam.py (functional sparse_adam)
+      const float mn = m + (g - m) * o.omb1;
+      const float vn = v + (g * g - v) * o.omb2;
+      m = mn;
+      v = vn;
+      p = p - o.step_size * (mn / (sqrtf(vn) + o.eps));
+      break;
+    }
+    case CMF_OPT_ADAM: {  // torch/optim/adam.py _single_tensor_adam
+      if (o.wd != 0.f) g = g + o.wd * p;
+      m = m + o.omb1 * (g - m);
+      v = v * o.b2 + (o.omb2 * g) * g;
+      const float denom = sqrtf(v) / o.bc2_sqrt + o.eps;
+      p = p - o.step_size * (m / denom);
+      break;
+    }
+    case CMF_OPT_ADAGRAD: {  // torch/optim/adagrad.py _single_tensor_adagrad
+      if (o.wd != 0.f) g = g + o.wd * p;
+      m = m + g * g;
+      p = p - o.lr * (g / (sqrtf(m) + o.eps));
+      break;
+    }
+    default: {  // SGD
+      if (o.wd != 0.f) g = g + o.wd * p;
+      p = p - o.lr * g;
+      break;
+    }
+  }
+}
+
+__device__ __forceinline__ bool rule_has_m(int rule) { return rule != CMF_OPT_SGD; }
+__device__ __forceinline__ bool rule_has_v(int rule) {
+  return rule == CMF_OPT_SPARSE_ADAM || rule == CMF_OPT_ADAM;
+}
+
+template <int V, int G, int R>
+__device__ __forceinline__ void update_row(const OptDev& o, float* __restrict__ P,
+                                           float* __restrict__ M, float* __restrict__ Vv, int D, int l,
+                                           int64_t row, const Row<V, G, R>& g) {
+  Row<V, G, R> p, m, v;
+  p.load(P + row * D, D, l);
+  if (rule_has_m(o.rule)) m.load(M + row * D, D, l); else m.zero();
+  if (rule_has_v(o.rule)) v.load(Vv + row * D, D, l); else v.zero();
+#pragma unroll
+  for (int i = 0; i < R * V; ++i) apply_rule(o, p.f[i], m.f[i], v.f[i], g.f[i]);
+  p.store(P + row * D, D, l);
+  if (rule_has_m(o.rule)) m.store(M + row * D, D, l);
+  if (rule_has_v(o.rule)) v.store(Vv + row * D, D, l);
+}
+
+__device__ __forceinline__ void update_scalar(const OptDev& o, float* P, float* M, float* Vv,
+                                              int64_t row, float g) {
+  float p = P[row];
+  float m = rule_has_m(o.rule) ? M[row] : 0.f;
+  float v = rule_has_v(o.rule) ? Vv[row] : 0.f;
+  apply_rule(o, p, m, v, g);
+  P[row] = p;
+  if (rule_has_m(o.rule)) M[row] = m;
+  if (rule_has_v(o.rule)) Vv[row] = v;
+}
+
+// ------------------------------------------------------------------------------- fused step
+struct StepDev {
+  float *U, *I, *bu, *bi, *U_m, *U_v, *bu_m, *bu_v;
+  int D;
+  uint32_t num_items;
+  const int32_t* su;    // users in sorted order
+  const uint32_t* perm; // sorted position -> batch position (NULL: identity)
+  const int32_t* items;
+  const float* ratings;
+  const int64_t* negs_in;
+  const int64_t* gidx;
+  int64_t gidx_base;
+  int64_t B;
+  int N, L;
+  int64_t num_chunks;
+  uint64_t seed;
+  uint32_t epoch;
+  const int64_t* indptr;
+  const int32_t* csr_items;
+  int max_tries;
+  int loss, has_range;
+  float y_lo, y_hi;
+  int n_meta;
+  const int32_t* meta[CMF_MAX_METADATA];
+  float meta_w[CMF_MAX_METADATA];
+  OptDev emb, bias;
+  int train, user_inplace, use_lists;
+  float inv_B;
+  float *GU, *gbu, *GI, *gbi;
+  int *user_flag, *item_flag, *user_list, *item_list;
+  WsHeader* hdr;
+  double* partials;
+  float* loss_out;
+  int64_t* negs_out;
+  int32_t* sel_out;
+  float* pos_out;
+  float* neg_out;
+};
+
+__device__ __forceinline__ void mark_row(int* flag, int* list, int* count, int id, int use_list) {
+  if (*(volatile int*)(flag + id) == 0) {
+    if (atomicExch(flag + id, 1) == 0 && use_list) list[atomicAdd(count, 1)] = id;
+  }
+}
+
+__device__ __forceinline__ float ideal_of(const StepDev& p, int pos, int neg) {
+  // 1 - sum_k w_k [meta_k[pos] == meta_k[neg]]   (collie/loss/metadata_utils.py:60-71)
+  float frac = 0.f;
+  for (int k = 0; k < p.n_meta; ++k)
+    frac += (p.meta[k][pos] == p.meta[k][neg]) ? p.meta_w[k] : 0.f;
+  return 1.0f - frac;
+}
+
+
+// train_step_v2.cu: TMA-staged fused step. Returns false when the shape is not supported by it
+// (then the caller runs the generic kernel); on a launch error sets *rc.
+bool launch_fused_step_v2(const StepDev& p, int max_chunk_len, cudaStream_t s, int* rc);
+
+}  // namespace cmf

@@ -20,22 +20,11 @@
 
 #include <cmath>
 #include <cstdlib>
+#include <vector>
 
-#include "common.cuh"
+#include "train_common.cuh"
 
 namespace cmf {
-
-constexpr int kMaxNeg = 64;          // negatives per interaction supported by the fused step
-constexpr int kMaxPartials = 8192;   // upper bound on the fused kernel's grid size
-constexpr int kThreads = 256;
-
-struct WsHeader {
-  int item_count;
-  int user_count;
-  unsigned blocks_done;
-  int pad[61];
-};
-static_assert(sizeof(WsHeader) == 256, "header is one 256-byte line group");
 
 struct WsLayout {
   // persistent (zero between steps; the kernels restore the invariant)
@@ -75,151 +64,6 @@ static WsLayout ws_layout(int64_t B, int64_t num_users, int64_t num_items, int D
   w.cub_temp = take(w.cub_temp_bytes);
   w.total = o;
   return w;
-}
-
-// ------------------------------------------------------------------------------- optimizer rules
-struct OptDev {
-  int rule;
-  int dense;        // every row of the table moves each step
-  float lr, wd, eps;
-  float b2;         // Adam: beta2
-  float omb1, omb2; // 1 - beta
-  float step_size;  // SparseAdam: lr*sqrt(1-b2^t)/(1-b1^t); Adam: lr/(1-b1^t)
-  float bc2_sqrt;   // Adam: sqrt(1-b2^t)
-};
-
-static OptDev make_opt(const cmf_opt_t& o) {
-  OptDev d{};
-  d.rule = o.rule;
-  d.lr = (float)o.lr;
-  d.wd = (float)o.weight_decay;
-  d.eps = (float)(o.rule == CMF_OPT_ADAGRAD ? 1e-10 : o.eps);
-  d.b2 = (float)o.beta2;
-  d.omb1 = (float)(1.0 - o.beta1);
-  d.omb2 = (float)(1.0 - o.beta2);
-  const double t = (double)(o.step < 1 ? 1 : o.step);
-  const double bc1 = 1.0 - std::pow(o.beta1, t), bc2 = 1.0 - std::pow(o.beta2, t);
-  if (o.rule == CMF_OPT_SPARSE_ADAM) d.step_size = (float)(o.lr * std::sqrt(bc2) / bc1);
-  if (o.rule == CMF_OPT_ADAM) { d.step_size = (float)(o.lr / bc1); d.bc2_sqrt = (float)std::sqrt(bc2); }
-  d.dense = (o.rule == CMF_OPT_ADAM) || (o.weight_decay != 0.0);
-  return d;
-}
-
-// One parameter element. m/v are the rule's state (Adagrad keeps its sum in m).
-__device__ __forceinline__ void apply_rule(const OptDev& o, float& p, float& m, float& v, float g) {
-  switch (o.rule) {
-    case CMF_OPT_SPARSE_ADAM: {  // torch/optim/sparse_adam.py (functional sparse_adam)
-      const float mn = m + (g - m) * o.omb1;
-      const float vn = v + (g * g - v) * o.omb2;
-      m = mn;
-      v = vn;
-      p = p - o.step_size * (mn / (sqrtf(vn) + o.eps));
-      break;
-    }
-    case CMF_OPT_ADAM: {  // torch/optim/adam.py _single_tensor_adam
-      if (o.wd != 0.f) g = g + o.wd * p;
-      m = m + o.omb1 * (g - m);
-      v = v * o.b2 + (o.omb2 * g) * g;
-      const float denom = sqrtf(v) / o.bc2_sqrt + o.eps;
-      p = p - o.step_size * (m / denom);
-      break;
-    }
-    case CMF_OPT_ADAGRAD: {  // torch/optim/adagrad.py _single_tensor_adagrad
-      if (o.wd != 0.f) g = g + o.wd * p;
-      m = m + g * g;
-      p = p - o.lr * (g / (sqrtf(m) + o.eps));
-      break;
-    }
-    default: {  // SGD
-      if (o.wd != 0.f) g = g + o.wd * p;
-      p = p - o.lr * g;
-      break;
-    }
-  }
-}
-
-__device__ __forceinline__ bool rule_has_m(int rule) { return rule != CMF_OPT_SGD; }
-__device__ __forceinline__ bool rule_has_v(int rule) {
-  return rule == CMF_OPT_SPARSE_ADAM || rule == CMF_OPT_ADAM;
-}
-
-template <int V, int G, int R>
-__device__ __forceinline__ void update_row(const OptDev& o, float* __restrict__ P,
-                                           float* __restrict__ M, float* __restrict__ Vv, int D, int l,
-                                           int64_t row, const Row<V, G, R>& g) {
-  Row<V, G, R> p, m, v;
-  p.load(P + row * D, D, l);
-  if (rule_has_m(o.rule)) m.load(M + row * D, D, l); else m.zero();
-  if (rule_has_v(o.rule)) v.load(Vv + row * D, D, l); else v.zero();
-#pragma unroll
-  for (int i = 0; i < R * V; ++i) apply_rule(o, p.f[i], m.f[i], v.f[i], g.f[i]);
-  p.store(P + row * D, D, l);
-  if (rule_has_m(o.rule)) m.store(M + row * D, D, l);
-  if (rule_has_v(o.rule)) v.store(Vv + row * D, D, l);
-}
-
-__device__ __forceinline__ void update_scalar(const OptDev& o, float* P, float* M, float* Vv,
-                                              int64_t row, float g) {
-  float p = P[row];
-  float m = rule_has_m(o.rule) ? M[row] : 0.f;
-  float v = rule_has_v(o.rule) ? Vv[row] : 0.f;
-  apply_rule(o, p, m, v, g);
-  P[row] = p;
-  if (rule_has_m(o.rule)) M[row] = m;
-  if (rule_has_v(o.rule)) Vv[row] = v;
-}
-
-// ------------------------------------------------------------------------------- fused step
-struct StepDev {
-  float *U, *I, *bu, *bi, *U_m, *U_v, *bu_m, *bu_v;
-  int D;
-  uint32_t num_items;
-  const int32_t* su;    // users in sorted order
-  const uint32_t* perm; // sorted position -> batch position (NULL: identity)
-  const int32_t* items;
-  const float* ratings;
-  const int64_t* negs_in;
-  const int64_t* gidx;
-  int64_t gidx_base;
-  int64_t B;
-  int N, L;
-  int64_t num_chunks;
-  uint64_t seed;
-  uint32_t epoch;
-  const int64_t* indptr;
-  const int32_t* csr_items;
-  int max_tries;
-  int loss, has_range;
-  float y_lo, y_hi;
-  int n_meta;
-  const int32_t* meta[CMF_MAX_METADATA];
-  float meta_w[CMF_MAX_METADATA];
-  OptDev emb, bias;
-  int train, user_inplace, use_lists;
-  float inv_B;
-  float *GU, *gbu, *GI, *gbi;
-  int *user_flag, *item_flag, *user_list, *item_list;
-  WsHeader* hdr;
-  double* partials;
-  float* loss_out;
-  int64_t* negs_out;
-  int32_t* sel_out;
-  float* pos_out;
-  float* neg_out;
-};
-
-__device__ __forceinline__ void mark_row(int* flag, int* list, int* count, int id, int use_list) {
-  if (*(volatile int*)(flag + id) == 0) {
-    if (atomicExch(flag + id, 1) == 0 && use_list) list[atomicAdd(count, 1)] = id;
-  }
-}
-
-__device__ __forceinline__ float ideal_of(const StepDev& p, int pos, int neg) {
-  // 1 - sum_k w_k [meta_k[pos] == meta_k[neg]]   (collie/loss/metadata_utils.py:60-71)
-  float frac = 0.f;
-  for (int k = 0; k < p.n_meta; ++k)
-    frac += (p.meta[k][pos] == p.meta[k][neg]) ? p.meta_w[k] : 0.f;
-  return 1.0f - frac;
 }
 
 template <int V, int G, int R>
@@ -537,6 +381,15 @@ k_optimizer_rows(float* P, float* M, float* Vv, float* Gr, int64_t num_rows, int
 }
 
 static std::atomic<int> g_forced_chunk_len{-1};
+static std::atomic<int> g_max_group{32};
+static std::atomic<int> g_kernel_version{0};  // 0 auto (v2 when the shape allows), 1 generic, 2 v2
+
+// ---- optional phase timing (bench.py roofline): events on the launching stream
+struct ProfRec { cudaEvent_t e[4]; };
+static bool g_prof_on = false;
+static std::vector<ProfRec> g_prof;
+static WsHeader* g_prof_last_hdr = nullptr;
+static cudaStream_t g_prof_stream = nullptr;
 
 static int chunk_len(int64_t B, int G) {
   int forced = g_forced_chunk_len.load();
@@ -569,6 +422,14 @@ static int validate_opt(const cmf_opt_t& o, const char* which, const float* m, c
 using namespace cmf;
 
 extern "C" int cmf_set_tuning(int32_t key, int32_t value) {
+  if (key == 1) {
+    CMF_REQUIRE(value == 8 || value == 16 || value == 32, "cmf_set_tuning: group width %d", value);
+    return g_max_group.exchange(value);
+  }
+  if (key == 2) {
+    CMF_REQUIRE(value >= 0 && value <= 2, "cmf_set_tuning: kernel version %d", value);
+    return g_kernel_version.exchange(value);
+  }
   CMF_REQUIRE(key == 0, "cmf_set_tuning: unknown key %d", key);
   CMF_REQUIRE(value >= 0 && value <= 4096, "cmf_set_tuning: chunk length %d out of range", value);
   const int prev = g_forced_chunk_len.exchange(value);
@@ -638,7 +499,7 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
 
   cudaStream_t s = (cudaStream_t)stream;
   char* base = (char*)a->workspace;
-  const RowGeom geom = row_geom(a->D);
+  const RowGeom geom = row_geom(a->D, g_max_group.load());
 
   StepDev p{};
   p.U = a->U; p.I = a->I; p.bu = a->bu; p.bi = a->bi;
@@ -673,6 +534,11 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
   p.pos_out = a->pos_scores_out; p.neg_out = a->neg_scores_out;
 
   CMF_CUDA(cudaMemsetAsync(p.hdr, 0, sizeof(WsHeader), s));
+  ProfRec prof{};
+  if (g_prof_on) {
+    for (auto& e : prof.e) CMF_CUDA(cudaEventCreate(&e));
+    CMF_CUDA(cudaEventRecord(prof.e[0], s));
+  }
 
   // ---- order the batch by user
   if (a->users_sorted) {
@@ -694,18 +560,33 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
     p.perm = vals_out;
   }
 
-  // ---- fused step
+  if (g_prof_on) CMF_CUDA(cudaEventRecord(prof.e[1], s));
+
+  // ---- fused step: TMA-staged kernel when the shape allows, else the generic one
   {
-    const int groups_per_block = kThreads / geom.G;
-    int64_t blocks = (p.num_chunks + groups_per_block - 1) / groups_per_block;
-    const int64_t cap = (int64_t)num_sms() * 8;
-    if (blocks > cap) blocks = cap;
-    if (blocks > kMaxPartials) blocks = kMaxPartials;
+    bool done = false;
+    if (g_kernel_version.load() != 1) {
+      int rc = CMF_OK;
+      const int forced = g_forced_chunk_len.load();
+      done = launch_fused_step_v2(p, forced > 0 ? forced : 0, s, &rc);
+      if (done && rc != CMF_OK) return rc;
+      CMF_REQUIRE(done || g_kernel_version.load() != 2,
+                  "cmf_train_step: the staged kernel does not support this shape (D=%d, N=%d)",
+                  a->D, a->N);
+    }
+    if (!done) {
+      const int groups_per_block = kThreads / geom.G;
+      int64_t blocks = (p.num_chunks + groups_per_block - 1) / groups_per_block;
+      const int64_t cap = (int64_t)num_sms() * 8;
+      if (blocks > cap) blocks = cap;
+      if (blocks > kMaxPartials) blocks = kMaxPartials;
 #define CALL(V_, G_, R_) k_fused_step<V_, G_, R_><<<(unsigned)blocks, kThreads, 0, s>>>(p)
-    CMF_DISPATCH_GEOM(geom, CALL);
+      CMF_DISPATCH_GEOM(geom, CALL);
 #undef CALL
-    CMF_LAUNCH_CHECK();
+      CMF_LAUNCH_CHECK();
+    }
   }
+  if (g_prof_on) CMF_CUDA(cudaEventRecord(prof.e[2], s));
 
   // ---- finish items (always) and the users that were not finished in place
   if (p.train) {
@@ -721,7 +602,7 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
     // sparse mode: the list lengths live on the device; size the grid for the worst case but cap it
     int64_t work = dense ? a->num_items + a->num_users
                          : std::min<int64_t>(a->num_items, a->B * (int64_t)(a->N + 1)) +
-                               std::min<int64_t>(a->num_users, 2 * p.num_chunks);
+                               std::min<int64_t>(a->num_users, a->B);
     int64_t blocks = (work + groups_per_block - 1) / groups_per_block;
     const int64_t cap = (int64_t)num_sms() * 8;
     if (blocks > cap) blocks = cap;
@@ -731,6 +612,44 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
 #undef CALL
     CMF_LAUNCH_CHECK();
   }
+  if (g_prof_on) {
+    CMF_CUDA(cudaEventRecord(prof.e[3], s));
+    g_prof.push_back(prof);
+    g_prof_last_hdr = p.hdr;
+    g_prof_stream = s;
+  }
+  return CMF_OK;
+}
+
+extern "C" int cmf_profile_enable(int32_t on) {
+  g_prof_on = on != 0;
+  return CMF_OK;
+}
+
+extern "C" int cmf_profile_read(double* ms_sort, double* ms_fused, double* ms_update, int64_t* steps,
+                                int64_t* last_item_rows, int64_t* last_user_rows) {
+  double t[3] = {0, 0, 0};
+  for (auto& r : g_prof) {
+    CMF_CUDA(cudaEventSynchronize(r.e[3]));
+    for (int i = 0; i < 3; ++i) {
+      float ms = 0.f;
+      CMF_CUDA(cudaEventElapsedTime(&ms, r.e[i], r.e[i + 1]));
+      t[i] += ms;
+    }
+    for (auto& e : r.e) cudaEventDestroy(e);
+  }
+  if (ms_sort) *ms_sort = t[0];
+  if (ms_fused) *ms_fused = t[1];
+  if (ms_update) *ms_update = t[2];
+  if (steps) *steps = (int64_t)g_prof.size();
+  if (g_prof_last_hdr && (last_item_rows || last_user_rows)) {
+    WsHeader h{};
+    CMF_CUDA(cudaMemcpyAsync(&h, g_prof_last_hdr, sizeof(h), cudaMemcpyDeviceToHost, g_prof_stream));
+    CMF_CUDA(cudaStreamSynchronize(g_prof_stream));
+    if (last_item_rows) *last_item_rows = h.item_count;
+    if (last_user_rows) *last_user_rows = h.user_count;
+  }
+  g_prof.clear();
   return CMF_OK;
 }
 
