@@ -47,6 +47,10 @@ inline OptDev make_opt(const cmf_opt_t& o) {
   return d;
 }
 
+// sqrt / division of the update term with the SFU approximations (<= 2 ulp each): the term is
+// multiplied by lr before it touches the parameter, so the parameter moves by < 1e-9 relative.
+__device__ __forceinline__ float fast_sqrt(float x) { return x > 0.f ? x * rsqrtf(x) : 0.f; }
+
 // One parameter element. m/v are the rule's state (Adagrad keeps its sum in m).
 __device__ __forceinline__ void apply_rule(const OptDev& o, float& p, float& m, float& v, float g) {
   switch (o.rule) {
@@ -55,21 +59,21 @@ __device__ __forceinline__ void apply_rule(const OptDev& o, float& p, float& m, 
       const float vn = v + (g * g - v) * o.omb2;
       m = mn;
       v = vn;
-      p = p - o.step_size * (mn / (sqrtf(vn) + o.eps));
+      p = p - o.step_size * __fdividef(mn, fast_sqrt(vn) + o.eps);
       break;
     }
     case CMF_OPT_ADAM: {  // torch/optim/adam.py _single_tensor_adam
       if (o.wd != 0.f) g = g + o.wd * p;
       m = m + o.omb1 * (g - m);
       v = v * o.b2 + (o.omb2 * g) * g;
-      const float denom = sqrtf(v) / o.bc2_sqrt + o.eps;
-      p = p - o.step_size * (m / denom);
+      const float denom = __fdividef(fast_sqrt(v), o.bc2_sqrt) + o.eps;
+      p = p - o.step_size * __fdividef(m, denom);
       break;
     }
     case CMF_OPT_ADAGRAD: {  // torch/optim/adagrad.py _single_tensor_adagrad
       if (o.wd != 0.f) g = g + o.wd * p;
       m = m + g * g;
-      p = p - o.lr * (g / (sqrtf(m) + o.eps));
+      p = p - o.lr * __fdividef(g, fast_sqrt(m) + o.eps);
       break;
     }
     default: {  // SGD

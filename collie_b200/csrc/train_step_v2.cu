@@ -1,18 +1,25 @@
-// Fused MF training step, TMA-staged variant (the fast path; D % 4 == 0).
+// Fused MF training step, shared-memory-staged variant (the fast path; D % 4 == 0).
 //
 // Same semantics and work decomposition as k_fused_step in train_step.cu (batch ordered by user,
 // cut into chunks of L interactions, whole user segments finished in place, straddlers and items
 // through vector RED into the gradient tables) -- what changes is how a warp spends instructions:
 //
-//   phase A  per chunk, lanes in parallel: batch positions, item ids, Philox negatives, biases and
-//            "touched" marks of all L * (N + 1) item rows land in a small shared-memory table.
+//   phase A  per chunk, lanes in parallel: batch positions, item ids, Philox negatives, biases,
+//            row offsets and "touched" marks of all L * (N + 1) item rows land in a small
+//            shared-memory table.
 //   phase B  per interaction: the N + 2 rows it needs (user, positive, negatives) are fetched by
-//            1-D TMA bulk copies (cp.async.bulk, one instruction per 512-byte row) into a
-//            kStages-deep shared-memory ring guarded by mbarriers, so the loads of interaction
-//            e + kStages - 1 are in flight while interaction e is being computed; the N + 1 dot
-//            products are done at once with a (row, segment) lane mapping that needs log2(St)
-//            shuffle steps instead of 5 per dot.
+//            asynchronous copies (cp.async, 16 bytes per lane = one 512-byte row per instruction)
+//            into a kStages-deep shared-memory ring, so the loads of interaction e + kStages - 1
+//            are in flight while interaction e is being computed; the N + 1 dot products are done
+//            at once with a (row, segment) lane mapping that needs log2(ST) shuffle steps instead
+//            of 5 per dot; the user's Adam moments are requested when its segment starts and its
+//            row is taken from the staged copy, so finishing a user waits on nothing.
+//            (Measured on B200: the same ring fed by 1-D TMA bulk copies, one cp.async.bulk per
+//            512-byte row issued from the uniform datapath, is no faster; rows this small are
+//            below TMA's efficient grain, so LDGSTS is used.)
 //
+// All shared-memory traffic uses explicit 32-bit shared-space addresses (ld.shared / st.shared):
+// generic pointers into dynamic shared memory cost three extra uniform instructions per access.
 // Persistent launch: one CTA per SM, W warps, W * warp_bytes of dynamic shared memory.
 #include "train_common.cuh"
 
@@ -24,36 +31,37 @@ constexpr int kMaxChunk = 16;
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);
 }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+// 16-byte asynchronous copy global -> shared (SASS: LDGSTS), L2 only
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
-               "r"(bytes)
-               : "memory");
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  uint32_t done;
-  do {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(smem_u32(bar)), "r"(parity)
-        : "memory");
-  } while (!done);
+__device__ __forceinline__ float4 lds_f4(uint32_t a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "r"(a));
+  return v;
 }
-// 1-D TMA bulk copy global -> shared, completion counted on an mbarrier (SASS: UBLKCP)
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-  asm volatile(
-      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-          smem_u32(dst)),
-      "l"(src), "r"(bytes), "r"(smem_u32(bar))
-      : "memory");
+__device__ __forceinline__ float lds_f32(uint32_t a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+  return v;
 }
-__device__ __forceinline__ float4 lds128(const unsigned char* p) {
-  return *reinterpret_cast<const float4*>(p);
+__device__ __forceinline__ int lds_i32(uint32_t a) {
+  int v;
+  asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts_i32(uint32_t a, int v) {
+  asm volatile("st.shared.s32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ void sts_f32(uint32_t a, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory");
 }
 // float -> uint32 whose unsigned order is the float order (NaN aside)
 __device__ __forceinline__ uint32_t float_key(float f) {
@@ -65,48 +73,50 @@ struct V2Cfg {
   int W;            // warps per CTA
   int L;            // interactions per chunk (<= kMaxChunk)
   int NP;           // table columns per interaction: user, positive, N negatives
-  int St, Jt;       // lanes per row segment group / rows handled at once (St * Jt == 32)
+  int Jt;           // rows scored at once
   int D4;           // float4 per row
-  int row_bytes;    // D * 4
   int stride;       // shared-memory row pitch (bank-conflict-free for the (row, segment) mapping)
-  int off_ids, off_bias, off_aux, off_rows, stage_bytes, warp_bytes;
+  int off_ids, off_bias, off_off, off_aux, off_rows, stage_bytes, warp_bytes;
 };
 
-template <int R>  // R float4 per lane hold a 128 * R-float gradient row
+// R float4 per lane hold a 128 * R-float row; JT rows are scored at once by ST = 32 / JT lanes
+// each; FULL: D == 128 * R, no bounds predicates; NPC: compile-time N + 2 (0 = run time).
+template <int R, int JT, bool FULL, int NPC>
 __global__ void __launch_bounds__(512, 1)
 k_fused_step_v2(const StepDev p, const V2Cfg c) {
+  constexpr int ST = 32 / JT;
+  constexpr int KI = (32 * R) / ST;  // float4 per lane in a dot product
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ float s_warp_loss[16];
   __shared__ bool s_last;
 
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
-  unsigned char* wbase = smem + (size_t)warp * c.warp_bytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(wbase);
-  int* ids = reinterpret_cast<int*>(wbase + c.off_ids);       // [L][NP]
-  float* bias = reinterpret_cast<float*>(wbase + c.off_bias); // [L][NP]
-  int* bpos = reinterpret_cast<int*>(wbase + c.off_aux);      // [L] batch position
-  float* aux = reinterpret_cast<float*>(wbase + c.off_aux) + kMaxChunk;  // [L] rating
-  unsigned char* rows = wbase + c.off_rows;
-
-  if (lane == 0) {
-    for (int s = 0; s < kStages; ++s) mbar_init(&bars[s], 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-  }
-  __syncwarp();
-
-  const int D = p.D, N = p.N, NP = c.NP, St = c.St;
+  const int D = p.D, N = p.N;
+  const int NP = NPC ? NPC : c.NP;
+  const int D4 = FULL ? 32 * R : c.D4;
   const int Rw = N + 1;  // item rows per interaction
+  const uint32_t sb = smem_u32(smem) + (uint32_t)(warp * c.warp_bytes);
+  const uint32_t a_ids = sb + c.off_ids;    // [L][NP] int: user, positive, negatives
+  const uint32_t a_bias = sb + c.off_bias;  // [L][NP] float: bu[user], bi[item]...
+  const uint32_t a_off = sb + c.off_off;    // [L][NP] uint: row offsets in 16-byte units
+  const uint32_t a_bpos = sb + c.off_aux;                  // [L] batch position
+  const uint32_t a_aux = a_bpos + 4 * kMaxChunk;           // [L] rating (explicit)
+  const uint32_t a_meta = a_aux + 4 * kMaxChunk;           // user before / after the chunk
+  const uint32_t a_rows = sb + c.off_rows;
+  const char* baseU = reinterpret_cast<const char*>(p.U) + lane * 16;
+  const char* baseI = reinterpret_cast<const char*>(p.I) + lane * 16;
+
   const bool implicit = p.loss <= CMF_LOSS_WARP;
   const bool adaptive = p.loss == CMF_LOSS_ADAPTIVE_BPR || p.loss == CMF_LOSS_ADAPTIVE_HINGE;
+  const bool emb_m = rule_has_m(p.emb.rule), emb_v = rule_has_v(p.emb.rule);
+  const bool bias_m = rule_has_m(p.bias.rule), bias_v = rule_has_v(p.bias.rule);
   const int64_t gwarp = (int64_t)blockIdx.x * c.W + warp;
   const int64_t n_warps = (int64_t)gridDim.x * c.W;
-  const int seg = lane % St;   // (row, segment) mapping of the dot products
-  const int jrow = lane / St;
-  const uint32_t tx_bytes = (uint32_t)(NP * c.row_bytes);
+  const int seg = lane % ST;   // (row, segment) mapping of the dot products
+  const int jrow = lane / ST;
+  const uint32_t d4u = (uint32_t)(D >> 2);  // row length in 16-byte units
 
-  uint32_t issued = 0, consumed = 0;
   float loss_acc = 0.f;
 
   for (int64_t ch = gwarp; ch < p.num_chunks; ch += n_warps) {
@@ -119,42 +129,49 @@ k_fused_step_v2(const StepDev p, const V2Cfg c) {
       const int u = p.su[e];
       const int64_t b = p.perm ? (int64_t)p.perm[e] : e;
       const int pos = p.items[b];
-      ids[lane * NP + 0] = u;
-      ids[lane * NP + 1] = pos;
-      bpos[lane] = (int)b;
-      bias[lane * NP + 0] = p.bu[u];
-      bias[lane * NP + 1] = p.bi[pos];
-      if (!implicit) aux[lane] = p.ratings[b];
+      const uint32_t t = (uint32_t)(lane * NP) * 4;
+      sts_i32(a_ids + t, u);
+      sts_i32(a_ids + t + 4, pos);
+      sts_i32(a_off + t, (int)((uint32_t)u * d4u));
+      sts_i32(a_off + t + 4, (int)((uint32_t)pos * d4u));
+      sts_f32(a_bias + t, p.bu[u]);
+      sts_f32(a_bias + t + 4, p.bi[pos]);
+      sts_i32(a_bpos + lane * 4, (int)b);
+      if (!implicit) sts_f32(a_aux + lane * 4, p.ratings[b]);
     }
+    // the users just outside the chunk decide whether a boundary segment is whole
+    if (lane == 30) sts_i32(a_meta, (e0 > 0) ? p.su[e0 - 1] : -1);
+    if (lane == 31) sts_i32(a_meta + 4, (e0 + n_e < p.B) ? p.su[e0 + n_e] : -1);
     __syncwarp();
     if (implicit) {
       if (p.negs_in) {
         for (int t = lane; t < n_e * N; t += 32) {
           const int le = t / N, n = t - le * N;
-          ids[le * NP + 2 + n] = (int)p.negs_in[(int64_t)bpos[le] * N + n];
+          const int64_t b = lds_i32(a_bpos + le * 4);
+          sts_i32(a_ids + (uint32_t)(le * NP + 2 + n) * 4, (int)p.negs_in[b * N + n]);
         }
       } else if (p.indptr == nullptr) {
         // approximate sampling: one Philox block yields four consecutive draws
         const int nblk = (N + 3) >> 2;
         for (int t = lane; t < n_e * nblk; t += 32) {
           const int le = t / nblk, blk = t - le * nblk;
-          const int64_t b = bpos[le];
+          const int64_t b = lds_i32(a_bpos + le * 4);
           const int64_t gi = p.gidx ? p.gidx[b] : p.gidx_base + b;
           const uint4 w = philox4x32_10(
               make_uint4((uint32_t)gi, (uint32_t)((uint64_t)gi >> 32), p.epoch, (uint32_t)blk),
               make_uint2((uint32_t)p.seed, (uint32_t)(p.seed >> 32)));
-          int* dst = ids + le * NP + 2 + blk * 4;
+          const uint32_t dst = a_ids + (uint32_t)(le * NP + 2 + blk * 4) * 4;
           const int left = N - blk * 4;
-          dst[0] = (int)__umulhi(w.x, p.num_items);
-          if (left > 1) dst[1] = (int)__umulhi(w.y, p.num_items);
-          if (left > 2) dst[2] = (int)__umulhi(w.z, p.num_items);
-          if (left > 3) dst[3] = (int)__umulhi(w.w, p.num_items);
+          sts_i32(dst, (int)__umulhi(w.x, p.num_items));
+          if (left > 1) sts_i32(dst + 4, (int)__umulhi(w.y, p.num_items));
+          if (left > 2) sts_i32(dst + 8, (int)__umulhi(w.z, p.num_items));
+          if (left > 3) sts_i32(dst + 12, (int)__umulhi(w.w, p.num_items));
         }
       } else if (lane < n_e) {
         // exact sampling: the reference's rejection loop (datasets.py:399-426) over our stream
-        int* negs = ids + lane * NP + 2;
-        const int u = ids[lane * NP];
-        const int64_t b = bpos[lane];
+        const uint32_t negs = a_ids + (uint32_t)(lane * NP + 2) * 4;
+        const int u = lds_i32(a_ids + (uint32_t)(lane * NP) * 4);
+        const int64_t b = lds_i32(a_bpos + lane * 4);
         const int64_t gi = p.gidx ? p.gidx[b] : p.gidx_base + b;
         const int64_t lo = p.indptr[u], hi = p.indptr[u + 1];
         uint32_t d = 0;
@@ -163,72 +180,99 @@ k_fused_step_v2(const StepDev p, const V2Cfg c) {
           int cand = draw_item(p.seed, p.epoch, gi, d++, p.num_items);
           for (;;) {
             bool clash = csr_contains(p.csr_items, lo, hi, cand);
-            for (int j = 0; j < taken && !clash; ++j) clash = (negs[j] == cand);
+            for (int j = 0; j < taken && !clash; ++j) clash = (lds_i32(negs + j * 4) == cand);
             if (!clash) break;
             if (checked >= p.max_tries) {
               const int left = N - taken - 1;
               for (int j = 0; j < left; ++j)
-                negs[taken++] = draw_item(p.seed, p.epoch, gi, d++, p.num_items);
+                sts_i32(negs + (taken++) * 4, draw_item(p.seed, p.epoch, gi, d++, p.num_items));
               break;
             }
             cand = draw_item(p.seed, p.epoch, gi, d++, p.num_items);
             ++checked;
           }
-          negs[taken++] = cand;
+          sts_i32(negs + (taken++) * 4, cand);
         }
       }
       __syncwarp();
       for (int t = lane; t < n_e * N; t += 32) {
         const int le = t / N, n = t - le * N;
-        const int id = ids[le * NP + 2 + n];
-        bias[le * NP + 2 + n] = p.bi[id];
-        if (p.negs_out) p.negs_out[(int64_t)bpos[le] * N + n] = id;
+        const uint32_t at = (uint32_t)(le * NP + 2 + n) * 4;
+        const int id = lds_i32(a_ids + at);
+        sts_f32(a_bias + at, p.bi[id]);
+        sts_i32(a_off + at, (int)((uint32_t)id * d4u));
+        if (p.negs_out) p.negs_out[(int64_t)lds_i32(a_bpos + le * 4) * N + n] = id;
       }
     }
     if (p.train) {
       // every gathered item row is "touched" (SparseAdam moves rows whose gradient is zero)
       for (int t = lane; t < n_e * Rw; t += 32) {
         const int le = t / Rw, n = t - le * Rw;
-        mark_row(p.item_flag, p.item_list, &p.hdr->item_count, ids[le * NP + 1 + n], p.use_lists);
+        mark_row(p.item_flag, p.item_list, &p.hdr->item_count,
+                 lds_i32(a_ids + (uint32_t)(le * NP + 1 + n) * 4), p.use_lists);
       }
     }
     __syncwarp();
 
     // ------------------------------------------------------------------ phase B: the row pipeline
+    // every call commits exactly one group (empty past the end of the chunk), so that
+    // "at most kStages - 1 groups pending" always means "the stage about to be read has landed"
+    int fill_stage = 0;
     auto issue = [&](int le) {
-      unsigned char* dst = rows + (size_t)(issued % kStages) * c.stage_bytes;
-      uint64_t* bar = &bars[issued % kStages];
-      if (lane == 0) mbar_expect_tx(bar, tx_bytes);
-      __syncwarp();
-      if (lane < NP) {
-        const int id = ids[le * NP + lane];
-        const float* src = (lane == 0 ? p.U : p.I) + (int64_t)id * D;
-        bulk_g2s(dst + (size_t)lane * c.stride, src, (uint32_t)c.row_bytes, bar);
-      }
-      for (int r = 32; r < NP; r += 32) {  // more than 30 negatives
-        if (r + lane < NP) {
-          const int id = ids[le * NP + r + lane];
-          bulk_g2s(dst + (size_t)(r + lane) * c.stride, p.I + (int64_t)id * D,
-                   (uint32_t)c.row_bytes, bar);
+      if (le < n_e) {
+        uint32_t dst = a_rows + (uint32_t)(fill_stage * c.stage_bytes) + lane * 16;
+        uint32_t t = a_off + (uint32_t)(le * NP) * 4;
+        const char* base = baseU;
+#pragma unroll 4
+        for (int r = 0; r < NP; ++r) {
+          const char* src = base + (uint64_t)(uint32_t)lds_i32(t) * 16u;
+#pragma unroll
+          for (int k = 0; k < R; ++k)
+            if (FULL || k * 32 + lane < D4) cp_async16(dst + k * 512, src + k * 512);
+          dst += c.stride;
+          t += 4;
+          base = baseI;
         }
       }
-      ++issued;
+      cp_async_commit();
+      fill_stage = (fill_stage + 1 == kStages) ? 0 : fill_stage + 1;
     };
-    for (int k = 0; k < kStages - 1 && k < n_e; ++k) issue(k);
+    for (int k = 0; k < kStages - 1; ++k) issue(k);
 
     int cur_user = -1;
     bool left_whole = false;
-    Row<4, 32, R> gu;
-    float gbu_acc = 0.f;
+    Row<4, 32, R> gu, m_pre, v_pre;   // gradient row; Adam moments prefetched at segment start
+    float gbu_acc = 0.f, bu_cur = 0.f, bm_pre = 0.f, bv_pre = 0.f;
+    uint32_t last_st = a_rows;  // stage of the previous interaction (its user row = P)
+    int read_stage = 0;
 
-    auto finish_user = [&](int next_le) {
-      // next_le < n_e: the following entry of this chunk belongs to another user
+    auto finish_user = [&](bool right_whole) {
       if (cur_user < 0 || !p.train) return;
-      const int64_t e1 = e0 + n_e;
-      const bool right_whole = (next_le < n_e) || (e1 == p.B) || (p.su[e1] != cur_user);
       if (left_whole && right_whole && p.user_inplace) {
-        update_row<4, 32, R>(p.emb, p.U, p.U_m, p.U_v, D, lane, cur_user, gu);
-        if (lane == 0) update_scalar(p.bias, p.bu, p.bu_m, p.bu_v, cur_user, gbu_acc);
+        // P comes from the staged user row, m / v were requested when the segment began: nothing
+        // here waits on memory
+        const int64_t off = (int64_t)cur_user * D;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const int i = r * 32 + lane;
+          if (FULL || i < D4) {
+            const float4 p4 = lds_f4(last_st + i * 16);
+            float pw[4] = {p4.x, p4.y, p4.z, p4.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              apply_rule(p.emb, pw[k], m_pre.f[r * 4 + k], v_pre.f[r * 4 + k], gu.f[r * 4 + k]);
+            st_vec<4>(p.U + off + i * 4, pw);
+            if (emb_m) st_vec<4>(p.U_m + off + i * 4, m_pre.f + r * 4);
+            if (emb_v) st_vec<4>(p.U_v + off + i * 4, v_pre.f + r * 4);
+          }
+        }
+        if (lane == 0) {
+          float pb = bu_cur;
+          apply_rule(p.bias, pb, bm_pre, bv_pre, gbu_acc);
+          p.bu[cur_user] = pb;
+          if (bias_m) p.bu_m[cur_user] = bm_pre;
+          if (bias_v) p.bu_v[cur_user] = bv_pre;
+        }
       } else {
         gu.red_add(p.GU + (int64_t)cur_user * D, D, lane);
         if (lane == 0) {
@@ -239,47 +283,70 @@ k_fused_step_v2(const StepDev p, const V2Cfg c) {
     };
 
     for (int le = 0; le < n_e; ++le) {
-      if (le + kStages - 1 < n_e) issue(le + kStages - 1);
-      const unsigned char* st = rows + (size_t)(consumed % kStages) * c.stage_bytes;
-      mbar_wait(&bars[consumed % kStages], (consumed / kStages) & 1u);
-      ++consumed;
-
-      const int* idr = ids + le * NP;
-      const float* br = bias + le * NP;
-      const int u = idr[0];
+      const uint32_t t_ids = a_ids + (uint32_t)(le * NP) * 4;
+      const uint32_t t_bias = a_bias + (uint32_t)(le * NP) * 4;
+      const int u = lds_i32(t_ids);
+      const float b_user = lds_f32(t_bias);
       if (u != cur_user) {
-        finish_user(le);
+        finish_user(true);   // another user follows inside the chunk
         cur_user = u;
-        left_whole = (e0 + le == 0) || (p.su[e0 + le - 1] != u);
+        left_whole = (le > 0) || (lds_i32(a_meta) != u);
         gu.zero();
         gbu_acc = 0.f;
+        bu_cur = b_user;
+        m_pre.zero();
+        v_pre.zero();
+        bm_pre = 0.f;
+        bv_pre = 0.f;
+        if (p.train && p.user_inplace) {
+          const int64_t off = (int64_t)u * D;
+          if (emb_m) m_pre.load(p.U_m + off, D, lane);
+          if (emb_v) v_pre.load(p.U_v + off, D, lane);
+          if (lane == 0) {
+            if (bias_m) bm_pre = p.bu_m[u];
+            if (bias_v) bv_pre = p.bu_v[u];
+          }
+        }
       }
-      const int64_t b = bpos[le];
-      const int pos = idr[1];
-      const unsigned char* urow = st;
+      // refill the stage of the previous interaction only now: finish_user read P from it
+      issue(le + kStages - 1);
+      const uint32_t st = a_rows + (uint32_t)(read_stage * c.stage_bytes);
+      read_stage = (read_stage + 1 == kStages) ? 0 : read_stage + 1;
+      cp_async_wait<kStages - 1>();
+      __syncwarp();   // the other lanes' copies of this stage are visible too
+      last_st = st;
 
-      // ---- all N + 1 dot products at once: lane (jrow, seg) owns float4 seg, seg + St, ... of row
-      float my_score = -INFINITY;  // score of row j0 + jrow (valid when j < Rw), same in all St lanes
+      const int64_t b = lds_i32(a_bpos + le * 4);
+      const int pos = lds_i32(t_ids + 4);
+
+      // ---- all N + 1 dot products at once: lane (jrow, seg) owns float4 seg, seg + ST, ... of row
+      float my_score = -INFINITY;  // score of row j0 + jrow, identical in the ST lanes of the row
       float sp = 0.f;
       int sel = (p.loss == CMF_LOSS_WARP) ? N : 0;
       float sel_s = 0.f, sel_h = 0.f;
       uint32_t best_key = 0;
-      for (int j0 = 0; j0 < Rw; j0 += c.Jt) {
+      for (int j0 = 0; j0 < Rw; j0 += JT) {
         const int j = j0 + jrow;
-        float acc = 0.f;
+        float acc = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
         if (j < Rw) {
-          const unsigned char* rj = st + (size_t)(1 + j) * c.stride;
-          for (int i = seg; i < c.D4; i += St) {
-            const float4 a = lds128(urow + i * 16);
-            const float4 x = lds128(rj + i * 16);
-            acc = fmaf(a.x, x.x, acc);
-            acc = fmaf(a.y, x.y, acc);
-            acc = fmaf(a.z, x.z, acc);
-            acc = fmaf(a.w, x.w, acc);
+          const uint32_t rj = st + (uint32_t)((1 + j) * c.stride) + seg * 16;
+          const uint32_t uj = st + seg * 16;
+#pragma unroll
+          for (int k = 0; k < KI; ++k) {
+            if (FULL || k * ST + seg < D4) {
+              const float4 a = lds_f4(uj + k * (ST * 16));
+              const float4 x = lds_f4(rj + k * (ST * 16));
+              acc = fmaf(a.x, x.x, acc);
+              acc1 = fmaf(a.y, x.y, acc1);
+              acc2 = fmaf(a.z, x.z, acc2);
+              acc3 = fmaf(a.w, x.w, acc3);
+            }
           }
         }
-        for (int o = St >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-        my_score = (j < Rw) ? acc + br[0] + br[1 + j] : -INFINITY;
+        acc = (acc + acc1) + (acc2 + acc3);
+#pragma unroll
+        for (int o = ST >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        my_score = (j < Rw) ? acc + b_user + lds_f32(t_bias + 4 + j * 4) : -INFINITY;
         if (j0 == 0) {
           sp = __shfl_sync(0xffffffffu, my_score, 0);
           if (p.pos_out && lane == 0) p.pos_out[b] = sp;
@@ -290,11 +357,11 @@ k_fused_step_v2(const StepDev p, const V2Cfg c) {
         if (p.loss == CMF_LOSS_WARP) {
           // h = ideal - pos + neg; the first strict violation wins (warp.py:95-105, 136-154)
           float h = 0.f;
-          if (is_neg) h = (ideal_of(p, pos, idr[1 + j]) - sp) + my_score;
+          if (is_neg) h = (ideal_of(p, pos, lds_i32(t_ids + 4 + j * 4)) - sp) + my_score;
           const unsigned viol = __ballot_sync(0xffffffffu, is_neg && h > 0.f);
           if (sel == N && viol) {
             const int src = __ffs(viol) - 1;
-            sel = j0 + src / St - 1;
+            sel = j0 + src / ST - 1;
             sel_h = __shfl_sync(0xffffffffu, h, src);
           }
         } else if (adaptive) {
@@ -304,13 +371,13 @@ k_fused_step_v2(const StepDev p, const V2Cfg c) {
           if (mx > best_key) {
             const unsigned who = __ballot_sync(0xffffffffu, is_neg && key == mx);
             const int src = __ffs(who) - 1;
-            sel = j0 + src / St - 1;
+            sel = j0 + src / ST - 1;
             sel_s = __shfl_sync(0xffffffffu, my_score, src);
             best_key = mx;
           }
         } else if (j0 == 0) {
           sel = 0;
-          sel_s = __shfl_sync(0xffffffffu, my_score, St);
+          sel_s = __shfl_sync(0xffffffffu, my_score, ST);
         }
       }
 
@@ -321,14 +388,14 @@ k_fused_step_v2(const StepDev p, const V2Cfg c) {
         if (p.sel_out && lane == 0) p.sel_out[b] = sel;
         if (p.loss == CMF_LOSS_WARP) {
           if (sel < N) {
-            sel_id = idr[2 + sel];
+            sel_id = lds_i32(t_ids + 8 + sel * 4);
             const float w = logf((float)p.num_items / (float)(sel + 1));
             const float Lw = w * sel_h;
             loss_acc += Lw + Lw * Lw;
             g = -((1.f + 2.f * Lw) * w) * p.inv_B;
           }
         } else {
-          sel_id = idr[2 + sel];
+          sel_id = lds_i32(t_ids + 8 + sel * 4);
           const float ideal = ideal_of(p, pos, sel_id);
           const float x = sp - sel_s;
           if (p.loss == CMF_LOSS_BPR || p.loss == CMF_LOSS_ADAPTIVE_BPR) {
@@ -347,7 +414,7 @@ k_fused_step_v2(const StepDev p, const V2Cfg c) {
         float sg = 0.f, pred = sp;
         if (p.has_range) { sg = sigmoidf_(sp); pred = sg * (p.y_hi - p.y_lo) + p.y_lo; }
         if (p.pos_out && lane == 0) p.pos_out[b] = pred;
-        const float diff = pred - aux[le];
+        const float diff = pred - lds_f32(a_aux + le * 4);
         float dp;
         if (p.loss == CMF_LOSS_MSE) { loss_acc += diff * diff; dp = 2.f * diff * p.inv_B; }
         else { loss_acc += fabsf(diff); dp = (diff > 0.f ? 1.f : (diff < 0.f ? -1.f : 0.f)) * p.inv_B; }
@@ -356,16 +423,16 @@ k_fused_step_v2(const StepDev p, const V2Cfg c) {
 
       // ---- backward: lane owns float4 lane, lane + 32, ... of the gradient rows
       if (p.train && g != 0.f) {
-        const unsigned char* prow = st + c.stride;
-        const unsigned char* srow = implicit ? st + (size_t)(2 + sel) * c.stride : nullptr;
-        float* gi_pos = p.GI + (int64_t)pos * D;
-        float* gi_sel = implicit ? p.GI + (int64_t)sel_id * D : nullptr;
+        const uint32_t prow = st + c.stride + lane * 16;
+        const uint32_t urow = st + lane * 16;
+        const uint32_t srow = st + (uint32_t)((2 + sel) * c.stride) + lane * 16;
+        float* gi_pos = p.GI + (int64_t)pos * D + lane * 4;
+        float* gi_sel = p.GI + (int64_t)(implicit ? sel_id : pos) * D + lane * 4;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-          const int i = r * 32 + lane;
-          if (i < c.D4) {
-            const float4 xp = lds128(prow + i * 16);
-            const float4 xu = lds128(urow + i * 16);
+          if (FULL || r * 32 + lane < D4) {
+            const float4 xp = lds_f4(prow + r * 512);
+            const float4 xu = lds_f4(urow + r * 512);
             float* f = gu.f + r * 4;
             // products rounded before the add, so +g*x and -g*x cancel exactly (see Row::axpy)
             f[0] = __fadd_rn(f[0], __fmul_rn(g, xp.x));
@@ -374,15 +441,15 @@ k_fused_step_v2(const StepDev p, const V2Cfg c) {
             f[3] = __fadd_rn(f[3], __fmul_rn(g, xp.w));
             float t[4] = {__fmul_rn(g, xu.x), __fmul_rn(g, xu.y), __fmul_rn(g, xu.z),
                           __fmul_rn(g, xu.w)};
-            red_vec<4>(gi_pos + i * 4, t);
+            red_vec<4>(gi_pos + r * 128, t);
             if (implicit) {
-              const float4 xs = lds128(srow + i * 16);
+              const float4 xs = lds_f4(srow + r * 512);
               f[0] = __fadd_rn(f[0], __fmul_rn(-g, xs.x));
               f[1] = __fadd_rn(f[1], __fmul_rn(-g, xs.y));
               f[2] = __fadd_rn(f[2], __fmul_rn(-g, xs.z));
               f[3] = __fadd_rn(f[3], __fmul_rn(-g, xs.w));
               t[0] = -t[0]; t[1] = -t[1]; t[2] = -t[2]; t[3] = -t[3];
-              red_vec<4>(gi_sel + i * 4, t);
+              red_vec<4>(gi_sel + r * 128, t);
             }
           }
         }
@@ -398,11 +465,10 @@ k_fused_step_v2(const StepDev p, const V2Cfg c) {
           if (lane == 0) atomicAdd(p.gbi + pos, g);
         }
       }
-      // the stage may be refilled (by the async proxy) only after every lane has read it
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      // the stage may be refilled only after every lane has read it
       __syncwarp();
     }
-    finish_user(n_e);
+    finish_user(lds_i32(a_meta + 4) != cur_user);
     __syncwarp();
   }
 
@@ -426,6 +492,35 @@ k_fused_step_v2(const StepDev p, const V2Cfg c) {
   }
 }
 
+template <int R, int JT, bool FULL, int NPC>
+static cudaError_t launch_one(const StepDev& p, const V2Cfg& c, int blocks, size_t smem,
+                              cudaStream_t s) {
+  cudaError_t e = cudaFuncSetAttribute(k_fused_step_v2<R, JT, FULL, NPC>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  k_fused_step_v2<R, JT, FULL, NPC><<<(unsigned)blocks, 32 * c.W, smem, s>>>(p, c);
+  return cudaGetLastError();
+}
+
+template <int R>
+static cudaError_t launch_generic(const StepDev& p, const V2Cfg& c, int blocks, size_t smem,
+                                  cudaStream_t s) {
+  if (c.Jt == 8) return launch_one<R, 8, false, 0>(p, c, blocks, smem, s);
+  if (c.Jt == 16) return launch_one<R, 16, false, 0>(p, c, blocks, smem, s);
+  return launch_one<R, 32, false, 0>(p, c, blocks, smem, s);
+}
+
+// the shapes the reference's defaults and BASELINE.json's configs hit get compile-time loops
+template <int R>
+static bool launch_special(const StepDev& p, const V2Cfg& c, int blocks, size_t smem,
+                           cudaStream_t s, cudaError_t* e) {
+  if (c.D4 != 32 * R) return false;
+  if (c.NP == 3) { *e = launch_one<R, 8, true, 3>(p, c, blocks, smem, s); return true; }
+  if (c.NP == 7) { *e = launch_one<R, 8, true, 7>(p, c, blocks, smem, s); return true; }
+  if (c.NP == 12) { *e = launch_one<R, 16, true, 12>(p, c, blocks, smem, s); return true; }
+  return false;
+}
+
 bool launch_fused_step_v2(const StepDev& p_in, int max_chunk_len, cudaStream_t s, int* rc) {
   *rc = CMF_OK;
   const int D = p_in.D, N = p_in.N;
@@ -434,14 +529,14 @@ bool launch_fused_step_v2(const StepDev& p_in, int max_chunk_len, cudaStream_t s
   c.NP = N + 2;
   const int Rw = N + 1;
   c.Jt = Rw <= 8 ? 8 : (Rw <= 16 ? 16 : 32);
-  c.St = 32 / c.Jt;
+  const int St = 32 / c.Jt;
   c.D4 = D / 4;
-  c.row_bytes = D * 4;
-  c.stride = (int)align_up((size_t)c.row_bytes, 128) + 16 * c.St;
-  c.off_ids = 64;
+  c.stride = (int)align_up((size_t)D * 4, 128) + 16 * St;
+  c.off_ids = 0;
   c.off_bias = c.off_ids + (int)align_up(sizeof(int) * kMaxChunk * c.NP, 16);
-  c.off_aux = c.off_bias + (int)align_up(sizeof(float) * kMaxChunk * c.NP, 16);
-  c.off_rows = (int)align_up((size_t)c.off_aux + 2 * sizeof(int) * kMaxChunk, 128);
+  c.off_off = c.off_bias + (int)align_up(sizeof(float) * kMaxChunk * c.NP, 16);
+  c.off_aux = c.off_off + (int)align_up(sizeof(int) * kMaxChunk * c.NP, 16);
+  c.off_rows = (int)align_up((size_t)c.off_aux + 2 * sizeof(int) * kMaxChunk + 16, 128);
   c.stage_bytes = c.NP * c.stride;
   c.warp_bytes = (int)align_up((size_t)c.off_rows + (size_t)kStages * c.stage_bytes, 128);
   const int budget = 200 * 1024;
@@ -464,19 +559,15 @@ bool launch_fused_step_v2(const StepDev& p_in, int max_chunk_len, cudaStream_t s
   const size_t smem = (size_t)c.W * c.warp_bytes;
   const int R = (c.D4 + 31) / 32;
   cudaError_t e = cudaSuccess;
-#define V2_LAUNCH(R_)                                                                            \
-  do {                                                                                           \
-    e = cudaFuncSetAttribute(k_fused_step_v2<R_>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
-                             (int)smem);                                                         \
-    if (e == cudaSuccess)                                                                        \
-      k_fused_step_v2<R_><<<(unsigned)blocks, 32 * c.W, smem, s>>>(p, c);                        \
-  } while (0)
-  if (R <= 1) V2_LAUNCH(1);
-  else if (R == 2) V2_LAUNCH(2);
-  else if (R <= 4) V2_LAUNCH(4);
-  else V2_LAUNCH(8);
-#undef V2_LAUNCH
-  if (e == cudaSuccess) e = cudaGetLastError();
+  bool done = false;
+  if (R == 1) done = launch_special<1>(p, c, (int)blocks, smem, s, &e);
+  else if (R == 2) done = launch_special<2>(p, c, (int)blocks, smem, s, &e);
+  if (!done) {
+    if (R <= 1) e = launch_generic<1>(p, c, (int)blocks, smem, s);
+    else if (R == 2) e = launch_generic<2>(p, c, (int)blocks, smem, s);
+    else if (R <= 4) e = launch_generic<4>(p, c, (int)blocks, smem, s);
+    else e = launch_generic<8>(p, c, (int)blocks, smem, s);
+  }
   g_launches.fetch_add(1, std::memory_order_relaxed);
   if (e != cudaSuccess)
     *rc = fail(CMF_ERR_CUDA, "k_fused_step_v2 launch failed: %s", cudaGetErrorString(e));

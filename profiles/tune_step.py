@@ -21,6 +21,7 @@ def main():
     ap.add_argument('--interactions', type=int, default=4_000_000)
     ap.add_argument('--groups', default='8,16,32')
     ap.add_argument('--chunks', default='0,4,8,16')
+    ap.add_argument('--no-train', action='store_true')
     args = ap.parse_args()
     w = bench.WORKLOAD
     users, items = bench.synth_interactions(w['num_users'], w['num_items'], args.interactions,
@@ -49,13 +50,13 @@ def main():
             for k in range(3):
                 a = (k % nb) * B
                 model.fused_step(DeviceBatch(u[a:a + B], i[a:a + B], perm[a:a + B], None),
-                                 optimizers=opts, interactions=data)
+                                 optimizers=opts, interactions=data, train=not args.no_train)
             torch.cuda.synchronize()
             lib.cmf_profile_enable(1)
             for k in range(10):
                 a = ((k + 3) % nb) * B
                 model.fused_step(DeviceBatch(u[a:a + B], i[a:a + B], perm[a:a + B], None),
-                                 optimizers=opts, interactions=data)
+                                 optimizers=opts, interactions=data, train=not args.no_train)
             ts, tf, tu = C.c_double(), C.c_double(), C.c_double()
             n, ir, ur = C.c_int64(), C.c_int64(), C.c_int64()
             lib.cmf_profile_read(C.byref(ts), C.byref(tf), C.byref(tu), C.byref(n), C.byref(ir),
