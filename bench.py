@@ -294,47 +294,58 @@ def run_ours(args, rank, world, local_rank):
         model.fused_step(device_batch(1000 + i), optimizers=opts, interactions=data, epoch=2,
                          outputs=outs if i == prof_steps - 1 else None)
     C = _abi.C
-    t_sort, t_fused, t_upd = C.c_double(), C.c_double(), C.c_double()
+    ms4 = (C.c_double * 4)()
+    split = C.c_int32()
     n_steps, item_rows, user_rows = C.c_int64(), C.c_int64(), C.c_int64()
-    lib.cmf_profile_read(C.byref(t_sort), C.byref(t_fused), C.byref(t_upd), C.byref(n_steps),
-                         C.byref(item_rows), C.byref(user_rows))
+    lib.cmf_profile_read(ms4, C.byref(split), C.byref(n_steps), C.byref(item_rows),
+                         C.byref(user_rows))
     lib.cmf_profile_enable(0)
     last = device_batch(1000 + prof_steps - 1)
     uq = int(torch.unique(last.users).numel())
     iq = int(torch.unique(torch.cat([outs['negs'].flatten(), last.items.long()])).numel())
     D, N, T = w['dim'], w['n_neg'], 4
-    gather_bytes = B * (2 + N) * D * T + B * (2 + N) * T + B * 2 * 4
-    inplace_users = uq - int(user_rows.value)
-    fused_bytes = gather_bytes + inplace_users * (6 * D * T + 2 * T)
-    update_bytes = (iq + int(user_rows.value)) * (6 * D * T + 2 * T)
-    step_bytes = gather_bytes + (uq + iq) * (6 * D * T + 2 * T)
     ns = max(1, n_steps.value)
-    fused_ms = t_fused.value / ns
+    row = D * T
+    # algorithmic bytes: gather B*(2+N) rows + biases + ids; update 6 streams per
+    # unique row + 2 bias streams
+    gather_bytes = B * (2 + N) * row + B * (2 + N) * T + B * 2 * 4
+    update_row = 6 * row + 2 * T
+    step_bytes = gather_bytes + (uq + iq) * update_row
+    inplace_users = uq - int(user_rows.value)
+    if split.value:
+        phases = {'k_fwd_loss': ms4[0] / ns, 'sort_tail': ms4[1] / ns,
+                  'k_bwd_update': ms4[2] / ns, 'k_update_rows': ms4[3] / ns}
+        kernel, kernel_ms, kernel_bytes = 'k_fwd_loss', ms4[0] / ns, gather_bytes
+    else:
+        phases = {'sort': ms4[0] / ns, 'k_fused_step': ms4[1] / ns, 'k_update_rows': ms4[3] / ns}
+        kernel, kernel_ms = 'k_fused_step', ms4[1] / ns
+        kernel_bytes = gather_bytes + inplace_users * update_row
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
     except Exception:
         pass
     peak = float(peaks.get('hbm_gbs', 6650.0))
-    achieved = fused_bytes / (fused_ms * 1e-3) / 1e9
+    achieved = kernel_bytes / (kernel_ms * 1e-3) / 1e9
     roofline = {
-        'bound': 'hbm', 'kernel': 'k_fused_step', 'achieved': achieved, 'peak': peak,
+        'bound': 'hbm', 'kernel': kernel, 'achieved': achieved, 'peak': peak,
         'unit': 'GB/s', 'frac': achieved / peak,
         'peak_source': 'MEASURED_PEAKS.json hbm_gbs (of measured)' if peaks else
                        'fallback 6650 GB/s (of fallback)',
         'traffic': None,
-        'algorithmic_bytes_per_launch': fused_bytes, 'kernel_ms': fused_ms,
-        'phase_ms': {'sort': t_sort.value / ns, 'fused': fused_ms, 'update': t_upd.value / ns},
+        'algorithmic_bytes_per_launch': kernel_bytes, 'kernel_ms': kernel_ms,
+        'phase_ms': phases,
         'step_algorithmic_bytes': step_bytes,
         'step_achieved_gbs': step_bytes / (ms / steps * 1e-3) / 1e9,
+        'step_frac': step_bytes / (ms / steps * 1e-3) / 1e9 / peak,
         'unique_users': uq, 'unique_items': iq, 'rows_finished_by_update_kernel':
             {'items': int(item_rows.value), 'users': int(user_rows.value)},
-        'update_kernel_algorithmic_bytes': update_bytes,
+        'update_phase_algorithmic_bytes': (uq + iq) * update_row,
     }
     traffic_file = os.path.join(ROOT, 'profiles', 'traffic.json')
     if os.path.exists(traffic_file):
         try:
-            roofline['traffic'] = json.load(open(traffic_file)).get('k_fused_step')
+            roofline['traffic'] = json.load(open(traffic_file)).get(kernel)
         except Exception:
             pass
 
@@ -380,8 +391,8 @@ def run_ours(args, rank, world, local_rank):
         'e2e': {'value': e2e_value, 'unit': 'interactions/s', 'h2d_bytes_per_step': h2d,
                 'd2h_bytes_per_step': 4, 'ms_per_step': e2e_ms / steps},
         'gpu_launches': int(launches),
-        'gpu_launches_note': 'own kernels per step: k_iota + k_fused_step + k_update_rows; the '
-                             'CUB radix sort adds library launches that are not counted',
+        'gpu_launches_note': 'own kernels per step: k_iota + k_fwd_loss + k_bwd_update + k_update_rows; '
+                             'the CUB radix sort adds library launches that are not counted',
         'clocks': clk, 'final_loss': float(loss), 'eval': eval_info,
     }
     print(json.dumps(line), flush=True)

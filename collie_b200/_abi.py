@@ -93,7 +93,8 @@ SIGNATURES = {
                                                    C.c_void_p, C.c_void_p]),
     'cmf_set_tuning': (C.c_int, [C.c_int32, C.c_int32]),
     'cmf_profile_enable': (C.c_int, [C.c_int32]),
-    'cmf_profile_read': (C.c_int, [C.POINTER(C.c_double)] * 3 + [C.POINTER(C.c_int64)] * 3),
+    'cmf_profile_read': (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int32)]
+                         + [C.POINTER(C.c_int64)] * 3),
     'cmf_last_error': (C.c_char_p, []),
     'cmf_version': (C.c_int, []),
     'cmf_launch_count': (C.c_int64, []),

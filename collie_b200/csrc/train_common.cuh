@@ -120,6 +120,7 @@ struct StepDev {
   float *U, *I, *bu, *bi, *U_m, *U_v, *bu_m, *bu_v;
   int D;
   uint32_t num_items;
+  const int32_t* users; // users in batch order
   const int32_t* su;    // users in sorted order
   const uint32_t* perm; // sorted position -> batch position (NULL: identity)
   const int32_t* items;
@@ -152,6 +153,8 @@ struct StepDev {
   int32_t* sel_out;
   float* pos_out;
   float* neg_out;
+  float* g_arr;     // [B] d loss / d positive score (split path: k_fwd_loss -> k_bwd_update)
+  int32_t* sel_arr; // [B] item id of the selected negative, -1 when none
 };
 
 __device__ __forceinline__ void mark_row(int* flag, int* list, int* count, int id, int use_list) {
@@ -169,8 +172,9 @@ __device__ __forceinline__ float ideal_of(const StepDev& p, int pos, int neg) {
 }
 
 
-// train_step_v2.cu: TMA-staged fused step. Returns false when the shape is not supported by it
-// (then the caller runs the generic kernel); on a launch error sets *rc.
-bool launch_fused_step_v2(const StepDev& p, int max_chunk_len, cudaStream_t s, int* rc);
+// train_step_v3.cu: the split fast path (k_fwd_loss + k_bwd_update)
+bool v3_supported(int D, int N);
+int launch_fwd_loss_v3(const StepDev& p, cudaStream_t s);
+int launch_bwd_update_v3(const StepDev& p, int max_chunk_len, cudaStream_t s);
 
 }  // namespace cmf

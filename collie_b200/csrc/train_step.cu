@@ -30,7 +30,7 @@ struct WsLayout {
   // persistent (zero between steps; the kernels restore the invariant)
   size_t item_flag, user_flag, GI, gbi, GU, gbu, persistent_end;
   // per step
-  size_t hdr, partials, item_list, user_list, keys_out, vals_in, vals_out, iota, cub_temp;
+  size_t hdr, partials, item_list, user_list, keys_out, vals_in, vals_out, iota, g_arr, sel_arr, cub_temp;
   size_t cub_temp_bytes, total;
 };
 
@@ -60,6 +60,8 @@ static WsLayout ws_layout(int64_t B, int64_t num_users, int64_t num_items, int D
   w.keys_out = take(sizeof(uint32_t) * B);
   w.vals_out = take(sizeof(uint32_t) * B);
   w.iota = take(sizeof(uint32_t) * B);
+  w.g_arr = take(sizeof(float) * B);
+  w.sel_arr = take(sizeof(int32_t) * B);
   w.cub_temp_bytes = cub_sort_bytes(B);
   w.cub_temp = take(w.cub_temp_bytes);
   w.total = o;
@@ -385,11 +387,29 @@ static std::atomic<int> g_max_group{32};
 static std::atomic<int> g_kernel_version{0};  // 0 auto (v2 when the shape allows), 1 generic, 2 v2
 
 // ---- optional phase timing (bench.py roofline): events on the launching stream
-struct ProfRec { cudaEvent_t e[4]; };
+struct ProfRec { cudaEvent_t e[5]; int split; };
 static bool g_prof_on = false;
 static std::vector<ProfRec> g_prof;
 static WsHeader* g_prof_last_hdr = nullptr;
 static cudaStream_t g_prof_stream = nullptr;
+
+// side stream + events that let the batch sort run next to k_fwd_loss (one set per device)
+struct SideStream {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+};
+static SideStream* side_stream() {
+  static SideStream per_dev[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  SideStream& ss = per_dev[dev];
+  if (!ss.stream) {
+    if (cudaStreamCreateWithFlags(&ss.stream, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    cudaEventCreateWithFlags(&ss.fork, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming);
+  }
+  return &ss;
+}
 
 static int chunk_len(int64_t B, int G) {
   int forced = g_forced_chunk_len.load();
@@ -533,60 +553,79 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
   p.negs_out = a->negs_out; p.sel_out = a->sel_out;
   p.pos_out = a->pos_scores_out; p.neg_out = a->neg_scores_out;
 
+  p.users = a->users;
+  p.g_arr = (float*)(base + w.g_arr);
+  p.sel_arr = (int32_t*)(base + w.sel_arr);
+
+  const int version = g_kernel_version.load();
+  const bool split = version != 1 && v3_supported(a->D, a->N);
+  CMF_REQUIRE(split || version != 2,
+              "cmf_train_step: the split kernels do not support this shape (D=%d, N=%d)", a->D, a->N);
+  const int forced_len = g_forced_chunk_len.load() > 0 ? g_forced_chunk_len.load() : 0;
+
   CMF_CUDA(cudaMemsetAsync(p.hdr, 0, sizeof(WsHeader), s));
   ProfRec prof{};
+  prof.split = split ? 1 : 0;
   if (g_prof_on) {
     for (auto& e : prof.e) CMF_CUDA(cudaEventCreate(&e));
     CMF_CUDA(cudaEventRecord(prof.e[0], s));
   }
 
-  // ---- order the batch by user
-  if (a->users_sorted) {
+  // ---- order the batch by user. On the split path only k_bwd_update needs the order, so the sort
+  // runs on a side stream next to k_fwd_loss.
+  const bool need_sort = !a->users_sorted && (p.train || !split);
+  SideStream* side = (split && need_sort) ? side_stream() : nullptr;
+  cudaStream_t sort_stream = side ? side->stream : s;
+  if (side) {
+    CMF_CUDA(cudaEventRecord(side->fork, s));
+    CMF_CUDA(cudaStreamWaitEvent(side->stream, side->fork, 0));
+  }
+  if (!need_sort) {
     p.su = a->users;
     p.perm = nullptr;
   } else {
     uint32_t* iota = (uint32_t*)(base + w.iota);
     uint32_t* keys_out = (uint32_t*)(base + w.keys_out);
     uint32_t* vals_out = (uint32_t*)(base + w.vals_out);
-    k_iota<<<(unsigned)((a->B + 255) / 256), 256, 0, s>>>(iota, a->B);
+    k_iota<<<(unsigned)((a->B + 255) / 256), 256, 0, sort_stream>>>(iota, a->B);
     CMF_LAUNCH_CHECK();
     int bits = 1;
     while (bits < 32 && (1ll << bits) < a->num_users) ++bits;
     size_t temp = w.cub_temp_bytes;
     CMF_CUDA(cub::DeviceRadixSort::SortPairs(base + w.cub_temp, temp, (const uint32_t*)a->users,
                                              keys_out, (const uint32_t*)iota, vals_out, (int)a->B,
-                                             0, bits, s));
+                                             0, bits, sort_stream));
     p.su = (const int32_t*)keys_out;
     p.perm = vals_out;
   }
+  if (side) CMF_CUDA(cudaEventRecord(side->join, side->stream));
 
-  if (g_prof_on) CMF_CUDA(cudaEventRecord(prof.e[1], s));
-
-  // ---- fused step: TMA-staged kernel when the shape allows, else the generic one
-  {
-    bool done = false;
-    if (g_kernel_version.load() != 1) {
-      int rc = CMF_OK;
-      const int forced = g_forced_chunk_len.load();
-      done = launch_fused_step_v2(p, forced > 0 ? forced : 0, s, &rc);
-      if (done && rc != CMF_OK) return rc;
-      CMF_REQUIRE(done || g_kernel_version.load() != 2,
-                  "cmf_train_step: the staged kernel does not support this shape (D=%d, N=%d)",
-                  a->D, a->N);
+  if (split) {
+    // e0 -> e1: k_fwd_loss;  e1 -> e2: what is left of the sort;  e2 -> e3: k_bwd_update
+    int rc = launch_fwd_loss_v3(p, s);
+    if (rc != CMF_OK) return rc;
+    if (g_prof_on) CMF_CUDA(cudaEventRecord(prof.e[1], s));
+    if (side) CMF_CUDA(cudaStreamWaitEvent(s, side->join, 0));
+    if (g_prof_on) CMF_CUDA(cudaEventRecord(prof.e[2], s));
+    if (p.train) {
+      rc = launch_bwd_update_v3(p, forced_len, s);
+      if (rc != CMF_OK) return rc;
     }
-    if (!done) {
-      const int groups_per_block = kThreads / geom.G;
-      int64_t blocks = (p.num_chunks + groups_per_block - 1) / groups_per_block;
-      const int64_t cap = (int64_t)num_sms() * 8;
-      if (blocks > cap) blocks = cap;
-      if (blocks > kMaxPartials) blocks = kMaxPartials;
+  } else {
+    // e0 -> e1: sort;  e1 -> e2: generic fused kernel;  e2 -> e3: nothing
+    if (g_prof_on) CMF_CUDA(cudaEventRecord(prof.e[1], s));
+    const int groups_per_block = kThreads / geom.G;
+    int64_t blocks = (p.num_chunks + groups_per_block - 1) / groups_per_block;
+    const int64_t cap = (int64_t)num_sms() * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks > kMaxPartials) blocks = kMaxPartials;
 #define CALL(V_, G_, R_) k_fused_step<V_, G_, R_><<<(unsigned)blocks, kThreads, 0, s>>>(p)
-      CMF_DISPATCH_GEOM(geom, CALL);
+    CMF_DISPATCH_GEOM(geom, CALL);
 #undef CALL
-      CMF_LAUNCH_CHECK();
-    }
+    CMF_LAUNCH_CHECK();
+    if (g_prof_on) CMF_CUDA(cudaEventRecord(prof.e[2], s));
   }
-  if (g_prof_on) CMF_CUDA(cudaEventRecord(prof.e[2], s));
+  if (g_prof_on) CMF_CUDA(cudaEventRecord(prof.e[3], s));
 
   // ---- finish items (always) and the users that were not finished in place
   if (p.train) {
@@ -613,7 +652,7 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
     CMF_LAUNCH_CHECK();
   }
   if (g_prof_on) {
-    CMF_CUDA(cudaEventRecord(prof.e[3], s));
+    CMF_CUDA(cudaEventRecord(prof.e[4], s));
     g_prof.push_back(prof);
     g_prof_last_hdr = p.hdr;
     g_prof_stream = s;
@@ -626,21 +665,22 @@ extern "C" int cmf_profile_enable(int32_t on) {
   return CMF_OK;
 }
 
-extern "C" int cmf_profile_read(double* ms_sort, double* ms_fused, double* ms_update, int64_t* steps,
+extern "C" int cmf_profile_read(double* host_ms /* [4] */, int32_t* host_split, int64_t* steps,
                                 int64_t* last_item_rows, int64_t* last_user_rows) {
-  double t[3] = {0, 0, 0};
+  double t[4] = {0, 0, 0, 0};
+  int split = 0;
   for (auto& r : g_prof) {
-    CMF_CUDA(cudaEventSynchronize(r.e[3]));
-    for (int i = 0; i < 3; ++i) {
+    CMF_CUDA(cudaEventSynchronize(r.e[4]));
+    for (int i = 0; i < 4; ++i) {
       float ms = 0.f;
       CMF_CUDA(cudaEventElapsedTime(&ms, r.e[i], r.e[i + 1]));
       t[i] += ms;
     }
+    split = r.split;
     for (auto& e : r.e) cudaEventDestroy(e);
   }
-  if (ms_sort) *ms_sort = t[0];
-  if (ms_fused) *ms_fused = t[1];
-  if (ms_update) *ms_update = t[2];
+  if (host_ms) for (int i = 0; i < 4; ++i) host_ms[i] = t[i];
+  if (host_split) *host_split = split;
   if (steps) *steps = (int64_t)g_prof.size();
   if (g_prof_last_hdr && (last_item_rows || last_user_rows)) {
     WsHeader h{};

@@ -243,20 +243,21 @@ CMF_API int cmf_score_tile(const float *U, const float *I, const float *bu, cons
                    void *stream);
 
 /* Tuning knobs (process-wide). key 0: chunk length L of the fused step (0 = automatic); key 1:
- * widest lane group per row in the generic fused kernel (8, 16 or 32); key 2: fused kernel choice
- * (0 automatic, 1 generic, 2 TMA-staged). Results do not depend on any of them beyond
+ * widest lane group per row in the generic fused kernel (8, 16 or 32); key 2: kernel choice
+ * (0 automatic, 1 generic fused kernel, 2 split k_fwd_loss + k_bwd_update). Results do not depend on any of them beyond
  * fp32 summation order; tests use them to cross-check the in-place and the accumulate paths. Returns the previous value, or a negative cmf_status for an unknown key. */
 CMF_API int cmf_set_tuning(int32_t key, int32_t value);
 
 /* Phase timing of cmf_train_step for bench.py's roofline line. While enabled, every step records
- * CUDA events on its launch stream around (sort, fused kernel, row update). cmf_profile_read waits
- * for the recorded events, returns the accumulated milliseconds per phase and the number of steps
- * since the last read, the touched-row list lengths of the LAST step, and clears the record.
+ * CUDA events on its launch stream between its phases. cmf_profile_read waits for them and returns
+ * the accumulated milliseconds of the four intervals, which path ran (*host_split = 1: split
+ * kernels, intervals = k_fwd_loss | rest of the overlapped sort | k_bwd_update | k_update_rows;
+ * 0: generic kernel, intervals = sort | k_fused_step | - | k_update_rows), the number of steps
+ * since the last read and the touched-row list lengths of the LAST step; then clears the record.
  * Not for use inside the timed region of a throughput measurement. */
 CMF_API int cmf_profile_enable(int32_t on);
-CMF_API int cmf_profile_read(double *host_ms_sort, double *host_ms_fused, double *host_ms_update,
-                     int64_t *host_steps, int64_t *host_last_item_rows,
-                     int64_t *host_last_user_rows);
+CMF_API int cmf_profile_read(double *host_ms /* [4] */, int32_t *host_split, int64_t *host_steps,
+                     int64_t *host_last_item_rows, int64_t *host_last_user_rows);
 
 CMF_API const char *cmf_last_error(void);
 CMF_API int cmf_version(void);

@@ -57,13 +57,17 @@ def main():
                 a = ((k + 3) % nb) * B
                 model.fused_step(DeviceBatch(u[a:a + B], i[a:a + B], perm[a:a + B], None),
                                  optimizers=opts, interactions=data, train=not args.no_train)
-            ts, tf, tu = C.c_double(), C.c_double(), C.c_double()
+            ms = (C.c_double * 4)()
+            split = C.c_int32()
             n, ir, ur = C.c_int64(), C.c_int64(), C.c_int64()
-            lib.cmf_profile_read(C.byref(ts), C.byref(tf), C.byref(tu), C.byref(n), C.byref(ir),
-                                 C.byref(ur))
+            lib.cmf_profile_read(ms, C.byref(split), C.byref(n), C.byref(ir), C.byref(ur))
             lib.cmf_profile_enable(0)
-            rec = dict(G=g, L=L, sort_ms=ts.value / n.value, fused_ms=tf.value / n.value,
-                       update_ms=tu.value / n.value, item_rows=ir.value, user_rows=ur.value)
+            names = ['fwd', 'sort_wait', 'bwd', 'update'] if split.value else \
+                ['sort', 'fused', '-', 'update']
+            rec = dict(G=g, L=L, split=split.value, item_rows=ir.value, user_rows=ur.value)
+            for k, nm in enumerate(names):
+                rec[nm + '_ms'] = round(ms[k] / n.value, 4)
+            rec['total_ms'] = round(sum(ms) / n.value, 4)
             out.append(rec)
             print(json.dumps(rec), flush=True)
 
