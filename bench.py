@@ -56,56 +56,64 @@ def synth_interactions(num_users, num_items, n, seed):
 
 # ------------------------------------------------------------------------------------------ clocks
 class ClockSampler(object):
-    QUERY = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,'
-             'clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
-             'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+    """SM clock and throttle reasons sampled through NVML from a thread DURING the timed region."""
 
     def __init__(self, gpu_index):
         self.gpu_index = gpu_index
-        self.proc = None
-        self.path = None
+        self.samples, self.reasons = [], set()
+        self.max_mhz = None
+        self._stop = None
+        self._thread = None
 
     def start(self):
+        import threading
         try:
-            fd, self.path = tempfile.mkstemp(suffix='.csv')
-            os.close(fd)
-            self.proc = subprocess.Popen(
-                ['nvidia-smi', f'--id={self.gpu_index}', f'--query-gpu={self.QUERY}',
-                 '--format=csv,noheader,nounits', '-lms', '100'],
-                stdout=open(self.path, 'w'), stderr=subprocess.DEVNULL)
+            import pynvml
+            pynvml.nvmlInit()
+            uuid = None
+            try:
+                uuid = torch.cuda.get_device_properties(self.gpu_index).uuid
+            except Exception:
+                pass
+            h = None
+            if uuid is not None:
+                try:
+                    h = pynvml.nvmlDeviceGetHandleByUUID(('GPU-' + str(uuid)).encode())
+                except Exception:
+                    h = None
+            if h is None:
+                h = pynvml.nvmlDeviceGetHandleByIndex(self.gpu_index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
         except Exception:
-            self.proc = None
+            return
+        names = {'hw_slowdown': pynvml.nvmlClocksThrottleReasonHwSlowdown,
+                 'hw_thermal_slowdown': pynvml.nvmlClocksThrottleReasonHwThermalSlowdown,
+                 'sw_thermal_slowdown': pynvml.nvmlClocksThrottleReasonSwThermalSlowdown,
+                 'sw_power_cap': pynvml.nvmlClocksThrottleReasonSwPowerCap}
+        self._stop = threading.Event()
+
+        def loop():
+            while not self._stop.is_set():
+                try:
+                    self.samples.append(float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)))
+                    mask = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                    for n_, bit in names.items():
+                        if mask & bit:
+                            self.reasons.add(n_)
+                except Exception:
+                    pass
+                self._stop.wait(0.002)
+        self._thread = threading.Thread(target=loop, daemon=True)
+        self._thread.start()
 
     def stop(self):
-        out = {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': [], 'samples': 0}
-        if self.proc is None:
-            return out
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
-        sm, reasons, mx = [], set(), None
-        try:
-            for line in open(self.path):
-                f = [x.strip() for x in line.split(',')]
-                if len(f) < 9:
-                    continue
-                try:
-                    sm.append(float(f[1]))
-                    mx = float(f[2])
-                except ValueError:
-                    continue
-                for name, val in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown',
-                                      'sw_power_cap'), f[5:9]):
-                    if val.lower().startswith('active'):
-                        reasons.add(name)
-            os.unlink(self.path)
-        except Exception:
-            pass
-        if sm:
-            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=mx, reasons=sorted(reasons),
-                       samples=len(sm))
+        if self._thread is not None:
+            self._stop.set()
+            self._thread.join(timeout=2)
+        out = {'sm_mhz': None, 'sm_max_mhz': self.max_mhz, 'reasons': sorted(self.reasons),
+               'samples': len(self.samples)}
+        if self.samples:
+            out['sm_mhz'] = float(np.median(self.samples))
         return out
 
 
@@ -181,7 +189,9 @@ def config_dict(n_gpus):
             'global_batch': w['batch_per_gpu'] * n_gpus,
             'parallelism': f'user-partitioned data parallel x{n_gpus}, item table row-sharded'
             if n_gpus > 1 else 'single GPU',
-            'l2': 'tables + Adam state = 255 MB > 126 MB L2; every step reads a new batch'}
+            'l2': 'tables + Adam state = 255 MB > 126 MB L2; every step reads a new batch',
+            'timed_region': 'K training steps incl. the device-side epoch plan (shuffle + per-batch '
+                            'user order) of the epoch they belong to'}
 
 
 # ------------------------------------------------------------------------------------------ GPU arm
@@ -220,17 +230,38 @@ def run_ours(args, rank, world, local_rank):
     gidx_h = perm.contiguous().pin_memory()
     users_d, items_d, gidx_d = users_h.to(dev), items_h.to(dev), gidx_h.to(dev)
     n_batches = n // B
+    loader = cb.InteractionsDataLoader(data, batch_size=B, shuffle=True, drop_last=True)
 
     def device_batch(i):
         a = (i % n_batches) * B
         return DeviceBatch(users_d[a:a + B], items_d[a:a + B], gidx_d[a:a + B], None)
 
-    def one_step(i):
-        return model.fused_step(device_batch(i), optimizers=opts, interactions=data, epoch=0)
+    class Batches(object):
+        """Batches the way the trainer gets them: the loader's device-side epoch plan (shuffle +
+        per-batch user order), rebuilt whenever an epoch is exhausted -- inside the timed region."""
+        def __init__(self):
+            self.epoch, self.it = 0, None
+
+        def next(self):
+            while True:
+                if self.it is None:
+                    self.it = loader.device_batches(dev, epoch=self.epoch)
+                    self.epoch += 1
+                try:
+                    return next(self.it), self.epoch
+                except StopIteration:
+                    self.it = None
+
+    feed = Batches()
+
+    def one_step():
+        db, epoch = feed.next()
+        return model.fused_step(db, optimizers=opts, interactions=data, epoch=epoch)
 
     # ---- device-resident throughput
     for i in range(warmup):
-        one_step(i)
+        one_step()
+    feed.it = None          # the timed region pays for its own epoch plan
     torch.cuda.synchronize()
     launches0 = _abi.launch_count()
     clocks = ClockSampler(local_rank)
@@ -239,7 +270,7 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.synchronize()
     ev0.record()
     for i in range(steps):
-        loss = one_step(warmup + i)
+        loss = one_step()
     ev1.record()
     torch.cuda.synchronize()
     ms = ev0.elapsed_time(ev1)

@@ -318,6 +318,63 @@ struct UpdDev {
   WsHeader* hdr;
 };
 
+// One row of one table: everything it needs is requested up front (gradient row, parameter row,
+// moments, bias scalars), so a group has 4 * (number of rows in flight) independent loads
+// outstanding instead of a chain of dependent ones.
+template <int V, int G, int R>
+struct RowJob {
+  Row<V, G, R> g, p, m, v;
+  float gb, pb, mb, vb;
+  int64_t row;
+  int t;
+  bool touched;
+
+  __device__ __forceinline__ void fetch(const UpdDev& q, int64_t w, int64_t n0, int l) {
+    t = w < n0 ? 0 : 1;
+    const int64_t k = t == 0 ? w : w - n0;
+    row = q.dense ? k : (int64_t)q.list[t][k];
+    touched = q.dense ? (q.flag[t][row] != 0) : true;
+    const int64_t off = row * q.D;
+    g.load(q.G[t] + off, q.D, l);
+    p.load(q.P[t] + off, q.D, l);
+    if (rule_has_m(q.emb.rule)) m.load(q.M[t] + off, q.D, l); else m.zero();
+    if (rule_has_v(q.emb.rule)) v.load(q.Vv[t] + off, q.D, l); else v.zero();
+    gb = pb = mb = vb = 0.f;
+    if (l == 0) {
+      gb = q.bG[t][row];
+      pb = q.bP[t][row];
+      if (rule_has_m(q.bias.rule)) mb = q.bM[t][row];
+      if (rule_has_v(q.bias.rule)) vb = q.bV[t][row];
+    }
+  }
+
+  __device__ __forceinline__ void finish(const UpdDev& q, int l) {
+    const int64_t off = row * q.D;
+    if (q.emb.dense || touched) {
+      if (touched) {
+        Row<V, G, R> z;
+        z.zero();
+        z.store(q.G[t] + off, q.D, l);
+      }
+#pragma unroll
+      for (int i = 0; i < R * V; ++i) apply_rule(q.emb, p.f[i], m.f[i], v.f[i], g.f[i]);
+      p.store(q.P[t] + off, q.D, l);
+      if (rule_has_m(q.emb.rule)) m.store(q.M[t] + off, q.D, l);
+      if (rule_has_v(q.emb.rule)) v.store(q.Vv[t] + off, q.D, l);
+    }
+    if (l == 0) {
+      if (q.bias.dense || touched) {
+        if (touched) q.bG[t][row] = 0.f;
+        apply_rule(q.bias, pb, mb, vb, gb);
+        q.bP[t][row] = pb;
+        if (rule_has_m(q.bias.rule)) q.bM[t][row] = mb;
+        if (rule_has_v(q.bias.rule)) q.bV[t][row] = vb;
+      }
+      if (touched) q.flag[t][row] = 0;
+    }
+  }
+};
+
 template <int V, int G, int R>
 __global__ void __launch_bounds__(kThreads)
 k_update_rows(const UpdDev p) {
@@ -327,30 +384,15 @@ k_update_rows(const UpdDev p) {
   const int64_t n_groups = (int64_t)gridDim.x * kGroups;
   const int64_t n0 = p.dense ? p.rows[0] : (int64_t)p.hdr->item_count;
   const int64_t n1 = p.dense ? p.rows[1] : (int64_t)p.hdr->user_count;
-  for (int64_t w = group; w < n0 + n1; w += n_groups) {
-    const int t = w < n0 ? 0 : 1;
-    const int64_t k = t == 0 ? w : w - n0;
-    const int64_t row = p.dense ? k : (int64_t)p.list[t][k];
-    const bool touched = p.flag[t][row] != 0;
-    if (p.emb.dense || touched) {
-      Row<V, G, R> g;
-      float* grow = p.G[t] + row * p.D;
-      g.load(grow, p.D, l);
-      if (touched) {
-        Row<V, G, R> z;
-        z.zero();
-        z.store(grow, p.D, l);
-      }
-      update_row<V, G, R>(p.emb, p.P[t], p.M[t], p.Vv[t], p.D, l, row, g);
-    }
-    if (l == 0) {
-      if (p.bias.dense || touched) {
-        const float gb = p.bG[t][row];
-        if (touched) p.bG[t][row] = 0.f;
-        update_scalar(p.bias, p.bP[t], p.bM[t], p.bV[t], row, gb);
-      }
-      if (touched) p.flag[t][row] = 0;
-    }
+  const int64_t total = n0 + n1;
+  // two rows per round: the second row's loads are in flight while the first is finished
+  for (int64_t w = group; w < total; w += 2 * n_groups) {
+    RowJob<V, G, R> a, b;
+    const bool two = (w + n_groups) < total;
+    a.fetch(p, w, n0, l);
+    if (two) b.fetch(p, w + n_groups, n0, l);
+    a.finish(p, l);
+    if (two) b.finish(p, l);
   }
 }
 

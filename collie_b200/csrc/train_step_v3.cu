@@ -104,6 +104,7 @@ k_fwd_loss(const StepDev p) {
   const char* baseU = reinterpret_cast<const char*>(p.U) + lane * 16;
   const char* baseI = reinterpret_cast<const char*>(p.I) + lane * 16;
   const uint64_t row_bytes = (uint64_t)D * 4;
+  const uint32_t rb32 = FULL ? 512u * R : (uint32_t)D * 4u;
 
   const bool implicit = p.loss <= CMF_LOSS_WARP;
   const bool adaptive = p.loss == CMF_LOSS_ADAPTIVE_BPR || p.loss == CMF_LOSS_ADAPTIVE_HINGE;
@@ -221,7 +222,7 @@ k_fwd_loss(const StepDev p) {
           v[r] = 0.f;
           if (j0 + r < Rw) {   // warp-uniform
             const int id = lds_i32(t_ids + 4 + (j0 + r) * 4);
-            const char* src = baseI + (uint64_t)(uint32_t)id * row_bytes;
+            const char* src = baseI + (uint64_t)(uint32_t)id * rb32;
 #pragma unroll
             for (int k = 0; k < R; ++k) {
               if (FULL || k * 32 + lane < D4) {
@@ -320,6 +321,257 @@ k_fwd_loss(const StepDev p) {
   }
 
   // ---- loss: deterministic two-level reduction (every lane carries the same loss_acc)
+  if (lane == 0) s_warp_loss[warp] = loss_acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double tot = 0.0;
+    for (int w = 0; w < 8; ++w) tot += (double)s_warp_loss[w];
+    p.partials[blockIdx.x] = tot;
+    __threadfence();
+    const unsigned ticket = atomicAdd(&p.hdr->blocks_done, 1u);
+    s_last = (ticket == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (s_last && threadIdx.x == 0) {
+    __threadfence();
+    double tot = 0.0;
+    for (unsigned i = 0; i < gridDim.x; ++i) tot += ((volatile double*)p.partials)[i];
+    p.loss_out[0] = (float)(tot / (double)p.B);
+  }
+}
+
+// ================================================================================ k_fwd_loss_g8
+// Same work as k_fwd_loss for D <= 128: a group of 8 lanes scores one interaction (lane l owns
+// float4 l, l + 8, ... of every row), so one warp instruction serves 4 interactions and the scalar
+// work per interaction (ids, selection, loss) is shared four ways. KQ float4 per lane per row.
+template <int KQ, bool FULL>
+__global__ void __launch_bounds__(256, 2)
+k_fwd_loss_g8(const StepDev p, const int NP) {
+  extern __shared__ int s_dyn[];   // [8 warps][32 interactions][NP]: user, positive, negatives
+  __shared__ float s_warp_loss[8];
+  __shared__ bool s_last;
+
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int grp = lane >> 3, l = lane & 7;
+  const unsigned gmask = 0xFFu << (grp * 8);
+  const int D = p.D, N = p.N;
+  const int D4 = FULL ? 8 * KQ : (D >> 2);
+  const int Rw = N + 1;
+  const uint32_t a_ids = smem_u32(s_dyn) + (uint32_t)(warp * 32 * NP) * 4;
+  const uint32_t row_stride = (uint32_t)NP * 4;
+  const uint32_t rb = FULL ? 128u * KQ : (uint32_t)D * 4u;   // row bytes
+  const char* baseU = reinterpret_cast<const char*>(p.U) + l * 16;
+  const char* baseI = reinterpret_cast<const char*>(p.I) + l * 16;
+
+  const bool implicit = p.loss <= CMF_LOSS_WARP;
+  const bool adaptive = p.loss == CMF_LOSS_ADAPTIVE_BPR || p.loss == CMF_LOSS_ADAPTIVE_HINGE;
+  const bool is_warp = p.loss == CMF_LOSS_WARP;
+  const bool is_bpr = p.loss == CMF_LOSS_BPR || p.loss == CMF_LOSS_ADAPTIVE_BPR;
+  const int64_t gwarp = (int64_t)blockIdx.x * 8 + warp;
+  const int64_t n_warps = (int64_t)gridDim.x * 8;
+  const int64_t n_chunks = (p.B + 31) / 32;
+  float loss_acc = 0.f;
+
+  for (int64_t ch = gwarp; ch < n_chunks; ch += n_warps) {
+    const int64_t b0 = ch * 32;
+    const int n_e = (int)((b0 + 32 < p.B ? b0 + 32 : p.B) - b0);
+
+    // ---- ids of 32 interactions, lanes in parallel
+    if (lane < n_e) {
+      sts_i32(a_ids + lane * row_stride, p.users[b0 + lane]);
+      sts_i32(a_ids + lane * row_stride + 4, p.items[b0 + lane]);
+    }
+    if (implicit) {
+      if (p.negs_in) {
+        for (int t = lane; t < n_e * N; t += 32) {
+          const int le = t / N, n = t - le * N;
+          sts_i32(a_ids + le * row_stride + 8 + n * 4, (int)p.negs_in[(b0 + le) * N + n]);
+        }
+      } else if (p.indptr == nullptr) {
+        // approximate sampling: one Philox block yields four consecutive draws
+        const int nblk = (N + 3) >> 2;
+        for (int t = lane; t < n_e * nblk; t += 32) {
+          const int le = t / nblk, blk = t - le * nblk;
+          const int64_t b = b0 + le;
+          const int64_t gi = p.gidx ? p.gidx[b] : p.gidx_base + b;
+          const uint4 w = philox4x32_10(
+              make_uint4((uint32_t)gi, (uint32_t)((uint64_t)gi >> 32), p.epoch, (uint32_t)blk),
+              make_uint2((uint32_t)p.seed, (uint32_t)(p.seed >> 32)));
+          const uint32_t dst = a_ids + le * row_stride + 8 + blk * 16;
+          const int left = N - blk * 4;
+          sts_i32(dst, (int)__umulhi(w.x, p.num_items));
+          if (left > 1) sts_i32(dst + 4, (int)__umulhi(w.y, p.num_items));
+          if (left > 2) sts_i32(dst + 8, (int)__umulhi(w.z, p.num_items));
+          if (left > 3) sts_i32(dst + 12, (int)__umulhi(w.w, p.num_items));
+        }
+      } else if (lane < n_e) {
+        // exact sampling: the reference's rejection loop (datasets.py:399-426) over our stream
+        const uint32_t negs = a_ids + lane * row_stride + 8;
+        const int64_t b = b0 + lane;
+        const int u = p.users[b];
+        const int64_t gi = p.gidx ? p.gidx[b] : p.gidx_base + b;
+        const int64_t lo = p.indptr[u], hi = p.indptr[u + 1];
+        uint32_t d = 0;
+        int taken = 0, checked = 0;
+        while (taken < N) {
+          int cand = draw_item(p.seed, p.epoch, gi, d++, p.num_items);
+          for (;;) {
+            bool clash = csr_contains(p.csr_items, lo, hi, cand);
+            for (int j = 0; j < taken && !clash; ++j) clash = (lds_i32(negs + j * 4) == cand);
+            if (!clash) break;
+            if (checked >= p.max_tries) {
+              const int left = N - taken - 1;
+              for (int j = 0; j < left; ++j)
+                sts_i32(negs + (taken++) * 4, draw_item(p.seed, p.epoch, gi, d++, p.num_items));
+              break;
+            }
+            cand = draw_item(p.seed, p.epoch, gi, d++, p.num_items);
+            ++checked;
+          }
+          sts_i32(negs + (taken++) * 4, cand);
+        }
+      }
+    }
+    __syncwarp();
+    if (p.negs_out)
+      for (int t = lane; t < n_e * N; t += 32) {
+        const int le = t / N, n = t - le * N;
+        p.negs_out[(b0 + le) * N + n] = lds_i32(a_ids + le * row_stride + 8 + n * 4);
+      }
+    if (p.train) {
+      // every gathered item row is "touched" (SparseAdam moves rows whose gradient is zero)
+      for (int t = lane; t < n_e * Rw; t += 32) {
+        const int le = t / Rw, n = t - le * Rw;
+        mark_row(p.item_flag, p.item_list, &p.hdr->item_count,
+                 lds_i32(a_ids + le * row_stride + 4 + n * 4), p.use_lists);
+      }
+    }
+
+    // ---- 8 rounds; in each, the 4 lane groups score 4 interactions side by side
+    for (int it = 0; it < 8; ++it) {
+      const int le = it * 4 + grp;
+      if (le >= n_e) continue;   // only in the last chunk; shuffles below use the group mask
+      const int64_t b = b0 + le;
+      const uint32_t t_ids = a_ids + le * row_stride;
+      const int u = lds_i32(t_ids);
+      const int pos = lds_i32(t_ids + 4);
+      float4 ur[KQ];
+      {
+        const char* src = baseU + (uint64_t)(uint32_t)u * rb;
+#pragma unroll
+        for (int k = 0; k < KQ; ++k)
+          ur[k] = (FULL || k * 8 + l < D4) ? ldg_f4(src + k * 128) : make_float4(0, 0, 0, 0);
+      }
+      const float b_user = p.bu[u];
+
+      float sp = 0.f, sel_s = -INFINITY, sel_h = 0.f;
+      int sel = is_warp ? N : 0;
+      // rows 0 (positive), 1..N (negatives), three at a time so 3 * KQ loads are in flight
+      for (int j0 = 0; j0 < Rw; j0 += 3) {
+        int id[3];
+        float4 x[3][KQ];
+        float bia[3];
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+          const bool on = j0 + r < Rw;
+          id[r] = on ? lds_i32(t_ids + 4 + (j0 + r) * 4) : pos;
+          const char* src = baseI + (uint64_t)(uint32_t)id[r] * rb;
+#pragma unroll
+          for (int k = 0; k < KQ; ++k)
+            x[r][k] = (FULL || k * 8 + l < D4) ? ldg_f4(src + k * 128) : make_float4(0, 0, 0, 0);
+          bia[r] = p.bi[id[r]];
+        }
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+          float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+          for (int k = 0; k < KQ; ++k) {
+            a0 = fmaf(ur[k].x, x[r][k].x, a0);
+            a1 = fmaf(ur[k].y, x[r][k].y, a1);
+            a0 = fmaf(ur[k].z, x[r][k].z, a0);
+            a1 = fmaf(ur[k].w, x[r][k].w, a1);
+          }
+          float acc = a0 + a1;
+          acc += __shfl_xor_sync(gmask, acc, 4);
+          acc += __shfl_xor_sync(gmask, acc, 2);
+          acc += __shfl_xor_sync(gmask, acc, 1);
+          const int j = j0 + r;
+          if (j >= Rw) continue;
+          const float sc = acc + b_user + bia[r];
+          if (j == 0) {
+            sp = sc;
+            if (p.pos_out && l == 0) p.pos_out[b] = sp;
+            continue;
+          }
+          if (p.neg_out && l == 0) p.neg_out[b * N + (j - 1)] = sc;
+          if (is_warp) {
+            // h = ideal - pos + neg; the first strict violation wins (warp.py:95-105, 136-154)
+            const float h = (ideal_of(p, pos, id[r]) - sp) + sc;
+            if (sel == N && h > 0.f) { sel = j - 1; sel_h = h; }
+          } else if (adaptive) {
+            // torch.max over the N axis: the first index of the maximum (bpr.py:153, hinge.py:157)
+            if (j == 1 || sc > sel_s) { sel = j - 1; sel_s = sc; }
+          } else if (j == 1) {
+            sel = 0;
+            sel_s = sc;
+          }
+        }
+      }
+
+      // ---- loss value and d loss / d score
+      float g = 0.f, lval = 0.f;   // implicit: d/d pos (d/d selected neg is -g)
+      int sel_id = -1;
+      if (implicit) {
+        if (p.sel_out && l == 0) p.sel_out[b] = sel;
+        if (is_warp) {
+          if (sel < N) {
+            sel_id = lds_i32(t_ids + 8 + sel * 4);
+            const float w = logf((float)p.num_items / (float)(sel + 1));
+            const float Lw = w * sel_h;
+            lval = Lw + Lw * Lw;
+            g = -((1.f + 2.f * Lw) * w) * p.inv_B;
+          }
+        } else {
+          sel_id = lds_i32(t_ids + 8 + sel * 4);
+          const float ideal = ideal_of(p, pos, sel_id);
+          const float xd = sp - sel_s;
+          if (is_bpr) {
+            const float sg = sigmoidf_(xd);
+            const float lv = ideal - sg;
+            lval = lv + lv * lv;
+            g = -((1.f + 2.f * lv) * (sg * (1.f - sg))) * p.inv_B;
+          } else {
+            const float raw = ideal - xd;
+            const float lv = raw > 0.f ? raw : 0.f;
+            lval = lv + lv * lv;
+            g = (raw >= 0.f) ? -(1.f + 2.f * lv) * p.inv_B : 0.f;
+          }
+        }
+      } else {
+        float sg = 0.f, pred = sp;
+        if (p.has_range) { sg = sigmoidf_(sp); pred = sg * (p.y_hi - p.y_lo) + p.y_lo; }
+        if (p.pos_out && l == 0) p.pos_out[b] = pred;
+        const float diff = pred - p.ratings[b];
+        float dp;
+        if (p.loss == CMF_LOSS_MSE) { lval = diff * diff; dp = 2.f * diff * p.inv_B; }
+        else { lval = fabsf(diff); dp = (diff > 0.f ? 1.f : (diff < 0.f ? -1.f : 0.f)) * p.inv_B; }
+        g = p.has_range ? dp * (sg * (1.f - sg) * (p.y_hi - p.y_lo)) : dp;
+      }
+      if (l == 0) {
+        loss_acc += lval;
+        if (p.train) {
+          p.g_arr[b] = g;
+          p.sel_arr[b] = sel_id;
+        }
+      }
+    }
+    __syncwarp();   // the id table is rewritten by the next chunk
+  }
+
+  // ---- loss: lane 0 of every group carries its share; deterministic two-level reduction
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) loss_acc += __shfl_xor_sync(0xffffffffu, loss_acc, o);
   if (lane == 0) s_warp_loss[warp] = loss_acc;
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -513,8 +765,43 @@ static int blocks_for(int64_t warps_of_work, int per_sm) {
 
 bool v3_supported(int D, int N) { return D % 4 == 0 && D <= 1024 && N <= kMaxNeg; }
 
+template <int KQ>
+static cudaError_t launch_g8(const StepDev& p, bool full, int grid, cudaStream_t s) {
+  const int NP = p.N + 2;
+  const size_t smem = (size_t)8 * 32 * NP * sizeof(int);
+  cudaError_t e = cudaSuccess;
+  if (full) {
+    if (smem > 48 * 1024)
+      e = cudaFuncSetAttribute(k_fwd_loss_g8<KQ, true>,
+                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) k_fwd_loss_g8<KQ, true><<<grid, 256, smem, s>>>(p, NP);
+  } else {
+    if (smem > 48 * 1024)
+      e = cudaFuncSetAttribute(k_fwd_loss_g8<KQ, false>,
+                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) k_fwd_loss_g8<KQ, false><<<grid, 256, smem, s>>>(p, NP);
+  }
+  return e == cudaSuccess ? cudaGetLastError() : e;
+}
+
 int launch_fwd_loss_v3(const StepDev& p, cudaStream_t s) {
-  const int R = (p.D / 4 + 31) / 32;
+  const int D4 = p.D / 4;
+  if (D4 <= 32) {
+    // 8 lanes per interaction, 4 interactions per warp instruction
+    const int KQ = (D4 + 7) / 8;
+    const bool full = (D4 == 8 * KQ);
+    const int grid = blocks_for((p.B + 31) / 32, 4);
+    cudaError_t e;
+    if (KQ == 1) e = launch_g8<1>(p, full, grid, s);
+    else if (KQ == 2) e = launch_g8<2>(p, full, grid, s);
+    else if (KQ == 3) e = launch_g8<3>(p, full, grid, s);
+    else e = launch_g8<4>(p, full, grid, s);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    if (e != cudaSuccess)
+      return fail(CMF_ERR_CUDA, "k_fwd_loss_g8 launch failed: %s", cudaGetErrorString(e));
+    return CMF_OK;
+  }
+  const int R = (D4 + 31) / 32;
   const bool full = (p.D == 128 * R);
   const int grid = blocks_for((p.B + kChunkA - 1) / kChunkA, 8);
 #define K1(R_)                                                         \
@@ -522,7 +809,7 @@ int launch_fwd_loss_v3(const StepDev& p, cudaStream_t s) {
     if (full) k_fwd_loss<R_, true><<<grid, 256, 0, s>>>(p);            \
     else k_fwd_loss<R_, false><<<grid, 256, 0, s>>>(p);                \
   } while (0)
-  if (R <= 1) K1(1); else if (R == 2) K1(2); else if (R <= 4) K1(4); else K1(8);
+  if (R == 2) K1(2); else if (R <= 4) K1(4); else K1(8);
 #undef K1
   CMF_LAUNCH_CHECK();
   return CMF_OK;

@@ -267,7 +267,8 @@ _INTERACTIONS_KWARGS = ('num_negative_samples', 'allow_missing_ids',
                         'check_num_negative_samples_is_valid',
                         'max_number_of_samples_to_consider', 'seed')
 
-DeviceBatch = collections.namedtuple('DeviceBatch', 'users items gidx ratings')
+DeviceBatch = collections.namedtuple('DeviceBatch', 'users items gidx ratings sorted',
+                                     defaults=(False,))
 
 
 class BaseInteractionsDataLoader(object):
@@ -307,35 +308,52 @@ class BaseInteractionsDataLoader(object):
         return n // b if self.drop_last else (n + b - 1) // b
 
     # ---- device-side epoch plan --------------------------------------------------------------
-    def device_batches(self, device, epoch=None):
+    def device_batches(self, device, epoch=None, sort_within_batch=True):
         """Yield ``DeviceBatch`` slices of one pass over the data, all tensors on ``device``.
 
         Shuffled passes permute the dataset positions once on the device (the reference shuffles
         an index array on the host, samplers.py:51-60); ``gidx`` keeps the dataset position of each
-        interaction, which keys the negative-sampling stream.
+        interaction, which keys the negative-sampling stream. With ``sort_within_batch`` every
+        batch comes ordered by user (``DeviceBatch.sorted``), which changes nothing but the
+        floating-point summation order of a step.
         """
         st = self.interactions.device_state(device)
         n = self.num_interactions
         if epoch is None:
             epoch = self._epoch
             self._epoch += 1
+        b = self.batch_size
         if self.shuffle:
             gen = torch.Generator(device=device)
             gen.manual_seed((int(getattr(self.interactions, 'seed', 0)) * 1000003 + int(epoch))
                             % (2 ** 63 - 1))
             order = torch.randperm(n, device=device, generator=gen)
-            users = st['users'][order]
-            items = st['items'][order]
-            ratings = st['ratings'][order] if 'ratings' in st else None
         else:
             order = torch.arange(n, device=device)
-            users, items, ratings = st['users'], st['items'], st.get('ratings')
-        b = self.batch_size
+        users = st['users'][order] if self.shuffle else st['users']
+        if sort_within_batch and n > 0:
+            # epoch plan: order every batch by user once, on the device (one sort of n 64-bit keys
+            # per epoch), so the training step can skip its own per-batch sort
+            n_batches = (n + b - 1) // b
+            ubits = max(1, int(self.num_users - 1).bit_length())
+            if ubits + max(1, int(n_batches - 1).bit_length()) <= 31:
+                key = (torch.arange(n, device=device, dtype=torch.int32) // b) * (1 << ubits) + users
+                key, idx = torch.sort(key, stable=True)
+                users = key & ((1 << ubits) - 1)
+            else:
+                key = (torch.arange(n, device=device, dtype=torch.int64) // b) * (1 << 32) \
+                    + users.long()
+                key, idx = torch.sort(key, stable=True)
+                users = (key & 0xFFFFFFFF).to(torch.int32)
+            order = order[idx]
+        items = st['items'][order]
+        ratings = st['ratings'][order] if 'ratings' in st else None
         stop = (n // b) * b if self.drop_last else n
         for s in range(0, stop, b):
             e = min(s + b, n)
             yield DeviceBatch(users[s:e], items[s:e], order[s:e],
-                              ratings[s:e] if ratings is not None else None)
+                              ratings[s:e] if ratings is not None else None,
+                              bool(sort_within_batch))
 
     def __iter__(self):
         """Reference-format batches on the current CUDA device:
@@ -346,7 +364,7 @@ class BaseInteractionsDataLoader(object):
         dev = torch.device('cuda', torch.cuda.current_device())
         epoch = self._epoch
         self._epoch += 1
-        for db in self.device_batches(dev, epoch=epoch):
+        for db in self.device_batches(dev, epoch=epoch, sort_within_batch=False):
             if db.ratings is not None:
                 yield db.users, db.items, db.ratings
             else:

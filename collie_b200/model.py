@@ -476,7 +476,7 @@ class MatrixFactorizationModel(torch.nn.Module):
         a.num_users, a.num_items, a.D = h.num_users, h.num_items, h.embedding_dim
         a.users, a.items = users.data_ptr(), items.data_ptr()
         a.B = B
-        a.users_sorted = 1 if users_sorted else 0
+        a.users_sorted = 1 if (users_sorted or getattr(batch, 'sorted', False)) else 0
         keep = [users, items]
         if implicit:
             if ratings is not None and negs is None and gidx is None:
