@@ -330,3 +330,38 @@ extern "C" int cmf_eval_tile(const cmf_eval_t* a, void* stream) {
   CMF_LAUNCH_CHECK();
   return CMF_OK;
 }
+
+// ------------------------------------------------------------------ allocation-free evaluation
+// cmf_eval_tile_noalloc: the same evaluation as cmf_eval_tile, for hosts that must not (or cannot)
+// obtain device memory themselves: the scratch tile lives in the library image.
+namespace cmf {
+constexpr size_t kNoAllocScratchBytes = 16u << 20;   // 16 MiB, resident on every GPU that loads us
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+}  // namespace cmf
+
+extern "C" int cmf_eval_tile_noalloc(const cmf_eval_t* a, void* stream) {
+  CMF_REQUIRE(a, "cmf_eval_tile_noalloc: null args");
+  // In host code `g_noalloc_scratch` is only a handle for the symbol; the device address has to be
+  // asked for, once per device, with that device current.
+  static void* dev_ptr[64] = {nullptr};
+  int dev = -1;
+  CMF_CUDA(cudaGetDevice(&dev));
+  CMF_REQUIRE(dev >= 0 && dev < 64, "cmf_eval_tile_noalloc: device ordinal %d not supported", dev);
+  if (dev_ptr[dev] == nullptr) {
+    void* ptr = nullptr;
+    CMF_CUDA(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+    dev_ptr[dev] = ptr;
+  }
+  const size_t need = cmf_eval_workspace_bytes(a->n_users_tile, a->num_items_shard, a->D, a->k,
+                                               a->precision);
+  if (need > kNoAllocScratchBytes)
+    return fail(CMF_ERR_WORKSPACE,
+                "cmf_eval_tile_noalloc: a tile of %lld users x %lld items needs %zu bytes of scratch, "
+                "the built-in scratch holds %zu; use fewer users per tile or cmf_eval_tile",
+                (long long)a->n_users_tile, (long long)a->num_items_shard, need,
+                (size_t)kNoAllocScratchBytes);
+  cmf_eval_t b = *a;
+  b.workspace = dev_ptr[dev];
+  b.workspace_bytes = kNoAllocScratchBytes;
+  return cmf_eval_tile(&b, stream);
+}

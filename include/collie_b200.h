@@ -236,6 +236,30 @@ CMF_API size_t cmf_eval_workspace_bytes(int64_t n_users_tile, int64_t num_items_
                                 int32_t precision);
 CMF_API int cmf_eval_tile(const cmf_eval_t *args, void *stream);
 
+/*
+ * cmf_eval_tile without a caller-provided workspace. (No counterpart in the reference: Collie's
+ * evaluation allocates freely through torch.)
+ *
+ * For hosts that cannot hand the library device memory: a serving or monitoring process that was
+ * given parameter tables and output buffers by another runtime but has no allocator of its own on
+ * the GPU, or one whose framework has already reserved the whole device so a further cudaMalloc
+ * would fail or stall the device. The scratch is a fixed 16 MiB array inside the library image
+ * (every GPU that loads the library holds it until the process exits); `workspace` and
+ * `workspace_bytes` in `args` are ignored. Inputs and outputs are still the caller's.
+ *
+ *   - Limit: cmf_eval_workspace_bytes(n_users_tile, num_items_shard, ...) must be <= 16 MiB
+ *     (12 bytes per user x item, e.g. 52 users against 26,744 items); larger tiles are refused with
+ *     CMF_ERR_WORKSPACE and a message that names both sizes.
+ *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress);
+ *     make that first call before any stream capture begins.
+ *   - The call itself performs no cudaMalloc / cudaFree and calls no allocating library routine.
+ *   - All calls share the one array and it keeps whatever the previous call left in it. Nothing in
+ *     it has to start at zero (the score tile and the sigmoid buffers are written before they are
+ *     read), but two calls whose kernels overlap on the GPU -- different streams, or different
+ *     host threads -- race on it: serialise them.
+ */
+CMF_API int cmf_eval_tile_noalloc(const cmf_eval_t *args, void *stream);
+
 /* Materialised score tile out[n, num_items] (for user-supplied metric callables and get_preds,
  * collie/metrics.py:77-107). */
 CMF_API int cmf_score_tile(const float *U, const float *I, const float *bu, const float *bi, int32_t D,
