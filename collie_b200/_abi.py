@@ -46,6 +46,7 @@ class cmf_step_t(C.Structure):
         ('loss_out', C.c_void_p), ('negs_out', C.c_void_p), ('sel_out', C.c_void_p),
         ('pos_scores_out', C.c_void_p), ('neg_scores_out', C.c_void_p),
         ('workspace', C.c_void_p), ('workspace_bytes', C.c_size_t),
+        ('B_global', C.c_int64), ('skip_item_update', C.c_int32), ('num_items_logical', C.c_int32),
     ]
 
 
@@ -69,6 +70,12 @@ SIGNATURES = {
     'cmf_train_workspace_bytes': (C.c_size_t, [C.c_int64, C.c_int32, C.c_int64, C.c_int64,
                                                C.c_int32]),
     'cmf_workspace_init': (C.c_int, [C.c_void_p, C.c_size_t, C.c_void_p]),
+    'cmf_train_workspace_items': (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int32,
+                                            C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                            C.POINTER(C.c_void_p)]),
+    'cmf_optimizer_rows_masked': (C.c_int, [C.c_void_p] * 8 + [C.c_int64, C.c_int32, C.c_void_p,
+                                                              C.POINTER(cmf_opt_t),
+                                                              C.POINTER(cmf_opt_t), C.c_void_p]),
     'cmf_train_step': (C.c_int, [C.POINTER(cmf_step_t), C.c_void_p]),
     'cmf_train_step_implicit': (C.c_int, [C.POINTER(cmf_step_t), C.c_void_p]),
     'cmf_train_step_explicit': (C.c_int, [C.POINTER(cmf_step_t), C.c_void_p]),

@@ -144,6 +144,7 @@ struct StepDev {
   OptDev emb, bias;
   int train, user_inplace, use_lists;
   float inv_B;
+  double loss_div;  // the loss is a mean over the (global) batch
   float *GU, *gbu, *GI, *gbi;
   int *user_flag, *item_flag, *user_list, *item_list;
   WsHeader* hdr;

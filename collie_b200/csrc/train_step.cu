@@ -300,7 +300,7 @@ k_fused_step(const StepDev p) {
     __threadfence();
     double tot = 0.0;
     for (unsigned i = 0; i < gridDim.x; ++i) tot += ((volatile double*)p.partials)[i];
-    p.loss_out[0] = (float)(tot / (double)p.B);
+    p.loss_out[0] = (float)(tot / p.loss_div);
   }
 }
 
@@ -314,6 +314,7 @@ struct UpdDev {
   int64_t rows[2];
   int D;
   int dense;  // walk every row instead of the touched lists
+  int skip_items;  // leave the item table (and its gradients) to the caller
   OptDev emb, bias;
   WsHeader* hdr;
 };
@@ -382,7 +383,7 @@ k_update_rows(const UpdDev p) {
   const int l = threadIdx.x & (G - 1);
   const int64_t group = (int64_t)blockIdx.x * kGroups + threadIdx.x / G;
   const int64_t n_groups = (int64_t)gridDim.x * kGroups;
-  const int64_t n0 = p.dense ? p.rows[0] : (int64_t)p.hdr->item_count;
+  const int64_t n0 = p.skip_items ? 0 : (p.dense ? p.rows[0] : (int64_t)p.hdr->item_count);
   const int64_t n1 = p.dense ? p.rows[1] : (int64_t)p.hdr->user_count;
   const int64_t total = n0 + n1;
   // two rows per round: the second row's loads are in flight while the first is finished
@@ -421,6 +422,27 @@ k_optimizer_rows(float* P, float* M, float* Vv, float* Gr, int64_t num_rows, int
       z.store(Gr + row * D, D, l);
     }
     update_row<V, G, R>(o, P, M, Vv, D, l, row, g);
+  }
+}
+
+// owner-side update of a sharded table: rows with touched != 0 (or every row for a dense rule)
+template <int V, int G, int R>
+__global__ void __launch_bounds__(kThreads)
+k_optimizer_rows_masked(float* P, float* M, float* Vv, const float* Gr, float* bP, float* bM,
+                        float* bV, const float* bG, int64_t num_rows, int D,
+                        const int32_t* touched, const OptDev o, const OptDev ob) {
+  constexpr int kGroups = kThreads / G;
+  const int l = threadIdx.x & (G - 1);
+  const int64_t group = (int64_t)blockIdx.x * kGroups + threadIdx.x / G;
+  const int64_t n_groups = (int64_t)gridDim.x * kGroups;
+  for (int64_t row = group; row < num_rows; row += n_groups) {
+    const bool t = touched[row] != 0;
+    if (o.dense || t) {
+      Row<V, G, R> g;
+      g.load(Gr + row * D, D, l);
+      update_row<V, G, R>(o, P, M, Vv, D, l, row, g);
+    }
+    if (bG && l == 0 && (ob.dense || t)) update_scalar(ob, bP, bM, bV, row, bG[row]);
   }
 }
 
@@ -505,6 +527,50 @@ extern "C" size_t cmf_train_workspace_bytes(int64_t max_B, int32_t max_N, int64_
   return ws_layout(max_B, num_users, num_items, D).total;
 }
 
+extern "C" int cmf_train_workspace_items(void* workspace, int64_t num_users, int64_t num_items,
+                                         int32_t D, float** GI, float** gbi, int32_t** item_flag) {
+  CMF_REQUIRE(workspace && num_users > 0 && num_items > 0 && D > 0,
+              "cmf_train_workspace_items: bad arguments");
+  const WsLayout w = ws_layout(1, num_users, num_items, D);   // the persistent part ignores B
+  char* base = (char*)workspace;
+  if (GI) *GI = (float*)(base + w.GI);
+  if (gbi) *gbi = (float*)(base + w.gbi);
+  if (item_flag) *item_flag = (int32_t*)(base + w.item_flag);
+  return CMF_OK;
+}
+
+extern "C" int cmf_optimizer_rows_masked(float* P, float* M, float* V, const float* G, float* bP,
+                                         float* bM, float* bV, const float* bG, int64_t num_rows,
+                                         int32_t D, const int32_t* touched, const cmf_opt_t* opt,
+                                         const cmf_opt_t* bias_opt, void* stream) {
+  CMF_REQUIRE(P && G && touched && opt, "cmf_optimizer_rows_masked: null pointer");
+  CMF_REQUIRE(geom_supported(D), "cmf_optimizer_rows_masked: embedding_dim %d unsupported", D);
+  int rc = validate_opt(*opt, "embedding", M, V);
+  if (rc) return rc;
+  OptDev ob{};
+  if (bG) {
+    CMF_REQUIRE(bP && bias_opt, "cmf_optimizer_rows_masked: bias table / rule missing");
+    rc = validate_opt(*bias_opt, "bias", bM, bV);
+    if (rc) return rc;
+    ob = make_opt(*bias_opt);
+  }
+  if (num_rows <= 0) return CMF_OK;
+  const OptDev o = make_opt(*opt);
+  const RowGeom geom = row_geom(D);
+  const int groups_per_block = kThreads / geom.G;
+  int64_t blocks = (num_rows + groups_per_block - 1) / groups_per_block;
+  const int64_t cap = (int64_t)num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  cudaStream_t s = (cudaStream_t)stream;
+#define CALL(V_, G_, R_)                                                                     \
+  k_optimizer_rows_masked<V_, G_, R_><<<(unsigned)blocks, kThreads, 0, s>>>(                 \
+      P, M, V, G, bP, bM, bV, bG, num_rows, D, touched, o, ob)
+  CMF_DISPATCH_GEOM(geom, CALL);
+#undef CALL
+  CMF_LAUNCH_CHECK();
+  return CMF_OK;
+}
+
 extern "C" int cmf_workspace_init(void* workspace, size_t workspace_bytes, void* stream) {
   CMF_REQUIRE(workspace && workspace_bytes > 0, "cmf_workspace_init: null workspace");
   CMF_CUDA(cudaMemsetAsync(workspace, 0, workspace_bytes, (cudaStream_t)stream));
@@ -567,7 +633,9 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
   p.U = a->U; p.I = a->I; p.bu = a->bu; p.bi = a->bi;
   p.U_m = a->U_m; p.U_v = a->U_v; p.bu_m = a->bu_m; p.bu_v = a->bu_v;
   p.D = a->D;
-  p.num_items = (uint32_t)a->num_items;
+  CMF_REQUIRE(a->num_items_logical >= 0 && a->num_items_logical <= a->num_items,
+              "cmf_train_step: num_items_logical out of range");
+  p.num_items = (uint32_t)(a->num_items_logical > 0 ? a->num_items_logical : a->num_items);
   p.items = a->items; p.ratings = a->ratings; p.negs_in = a->negs_in;
   p.gidx = a->gidx; p.gidx_base = a->gidx_base;
   p.B = a->B; p.N = a->N;
@@ -581,10 +649,14 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
   for (int k = 0; k < p.n_meta; ++k) { p.meta[k] = a->meta[k]; p.meta_w[k] = a->meta_w[k]; }
   p.train = a->train ? 1 : 0;
   if (p.train) { p.emb = make_opt(a->emb_opt); p.bias = make_opt(a->bias_opt); }
+  CMF_REQUIRE(a->B_global == 0 || a->B_global >= a->B, "cmf_train_step: B_global smaller than B");
   const int dense = p.train && (p.emb.dense || p.bias.dense);
+  CMF_REQUIRE(!(a->skip_item_update && dense),
+              "cmf_train_step: skip_item_update needs sparse-row rules (sparse_adam / sgd / adagrad)");
   p.user_inplace = p.train && !dense;
   p.use_lists = p.train && !dense;
-  p.inv_B = 1.0f / (float)a->B;
+  p.inv_B = 1.0f / (float)(a->B_global > 0 ? a->B_global : a->B);
+  p.loss_div = (double)(a->B_global > 0 ? a->B_global : a->B);
   p.GU = (float*)(base + w.GU); p.gbu = (float*)(base + w.gbu);
   p.GI = (float*)(base + w.GI); p.gbi = (float*)(base + w.gbi);
   p.user_flag = (int*)(base + w.user_flag); p.item_flag = (int*)(base + w.item_flag);
@@ -679,6 +751,7 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
     q.bP[1] = a->bu; q.bM[1] = a->bu_m; q.bV[1] = a->bu_v; q.bG[1] = p.gbu;
     q.flag[1] = p.user_flag; q.list[1] = p.user_list; q.rows[1] = a->num_users;
     q.D = a->D; q.dense = dense; q.emb = p.emb; q.bias = p.bias; q.hdr = p.hdr;
+    q.skip_items = a->skip_item_update ? 1 : 0;
     const int groups_per_block = kThreads / geom.G;
     // sparse mode: the list lengths live on the device; size the grid for the worst case but cap it
     int64_t work = dense ? a->num_items + a->num_users

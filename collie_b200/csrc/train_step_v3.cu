@@ -336,7 +336,7 @@ k_fwd_loss(const StepDev p) {
     __threadfence();
     double tot = 0.0;
     for (unsigned i = 0; i < gridDim.x; ++i) tot += ((volatile double*)p.partials)[i];
-    p.loss_out[0] = (float)(tot / (double)p.B);
+    p.loss_out[0] = (float)(tot / p.loss_div);
   }
 }
 
@@ -587,7 +587,7 @@ k_fwd_loss_g8(const StepDev p, const int NP) {
     __threadfence();
     double tot = 0.0;
     for (unsigned i = 0; i < gridDim.x; ++i) tot += ((volatile double*)p.partials)[i];
-    p.loss_out[0] = (float)(tot / (double)p.B);
+    p.loss_out[0] = (float)(tot / p.loss_div);
   }
 }
 

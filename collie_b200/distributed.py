@@ -1,0 +1,318 @@
+"""Multi-GPU matrix-factorization training: one process per GPU over ``torch.distributed``.
+
+The reference has no multi-GPU code of its own; this is the B200 design of SURVEY 8(e):
+
+* **users are partitioned** (``owner(u) = u % world``, local id ``u // world``): a rank trains on the
+  interactions of its own users, so user rows, their Adam moments and biases are always local and
+  are finished in place by the fused step -- no user-side communication at all;
+* **the item table is row-sharded** (contiguous blocks of ``ceil(I / world)`` rows, padded): every
+  rank owns one block of rows with its optimizer state. One step =
+    1. ``all_gather`` of the item rows (+ biases) into each rank's full-width working copy,
+    2. the local fused step on the rank's batch (``skip_item_update``: item-row gradients, bias
+       gradients and "touched" flags stay in the step's workspace; the loss and the gradients are
+       scaled for the GLOBAL batch of ``world * B`` interactions),
+    3. ``reduce_scatter`` (sum) of the three item-side accumulators to the owners,
+    4. the owner's masked row update (``cmf_optimizer_rows_masked``: SparseAdam moves every row some
+       rank gathered) and a clear of the local accumulators.
+  With MovieLens-like catalogues every step touches nearly every item row, so dense collectives over
+  NVLink are the right exchange (13.7 MB per direction per step at the 20M shape); a catalogue
+  whose steps touch a small fraction of the rows would swap 1 and 3 for all-to-all(v) of the
+  de-duplicated row lists -- same ownership, same owner-side update.
+
+Global semantics: one batch of ``world * B`` interactions per step, one optimizer step per unique
+row. Negatives are keyed by the interaction's global dataset position, so they do not depend on the
+number of GPUs. The collectives take any backend: NCCL on GPUs, gloo in the CPU tests (which
+exercise the plumbing, not the kernels).
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _abi
+
+
+def owner_of_user(users, world):
+    return users % world
+
+
+def local_user_id(users, world):
+    return users // world
+
+
+def shard_rows(num_items, world):
+    """Rows per rank and padded row count of the row-sharded item table."""
+    per_rank = (int(num_items) + world - 1) // world
+    return per_rank, per_rank * world
+
+
+def partition_interactions(users, items, rank, world, extra=None):
+    """Interactions of the users this rank owns, with local user ids and their global dataset
+    positions (``gidx``, the RNG key)."""
+    users = np.asarray(users)
+    mine = np.nonzero(owner_of_user(users, world) == rank)[0]
+    out = [local_user_id(users[mine], world), np.asarray(items)[mine], mine.astype(np.int64)]
+    if extra is not None:
+        out.append(np.asarray(extra)[mine])
+    return tuple(out)
+
+
+def num_local_users(num_users, rank, world):
+    return (int(num_users) - rank + world - 1) // world
+
+
+def all_gather_rows(full, shard, group=None):
+    """``full[r * rows : (r + 1) * rows] = shard of rank r`` for every r (in place when ``shard`` is
+    this rank's slice of ``full``)."""
+    dist.all_gather_into_tensor(full, shard, group=group)
+    return full
+
+
+def reduce_scatter_sum(out_shard, full, group=None):
+    """Owner r receives the sum over ranks of ``full[r * rows : (r + 1) * rows]``."""
+    try:
+        dist.reduce_scatter_tensor(out_shard, full, op=dist.ReduceOp.SUM, group=group)
+    except (RuntimeError, NotImplementedError, ValueError):
+        # backends without reduce_scatter (gloo): all_reduce + slice, same result
+        tmp = full.clone()
+        dist.all_reduce(tmp, op=dist.ReduceOp.SUM, group=group)
+        rows = out_shard.shape[0]
+        r = dist.get_rank(group)
+        out_shard.copy_(tmp[r * rows:(r + 1) * rows])
+    return out_shard
+
+
+class ShardedMatrixFactorization(object):
+    """A ``MatrixFactorizationModel`` trained across ``world`` GPUs (see the module docstring).
+
+    ``model`` is this rank's local model: its user tables hold the rank's own users
+    (``num_local_users``), its item tables are the full-width working copy (padded to
+    ``shard_rows``); ``model.hparams.num_items`` is the padded count.
+    """
+
+    def __init__(self, model, true_num_items, group=None):
+        self.model = model
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.per_rank, padded = shard_rows(true_num_items, self.world)
+        if model.hparams.num_items != padded:
+            raise ValueError(f'the local model must hold the padded item table ({padded} rows), '
+                             f'not {model.hparams.num_items}')
+        self.true_num_items = int(true_num_items)
+        lo, hi = self.rank * self.per_rank, (self.rank + 1) * self.per_rank
+        self.I_full = model.item_embeddings.weight.data
+        self.bi_full = model.item_biases.weight.data
+        self.I_shard = self.I_full[lo:hi]
+        self.bi_shard = self.bi_full[lo:hi]
+        self._state = None
+        self._step = 0
+        # every rank starts from rank 0's item table (user tables are disjoint)
+        dist.broadcast(self.I_full, src=self._global_rank(0), group=group)
+        dist.broadcast(self.bi_full, src=self._global_rank(0), group=group)
+
+    def _global_rank(self, r):
+        return dist.get_global_rank(self.group, r) if self.group is not None else r
+
+    def _item_state(self, main, bias):
+        if self._state is None:
+            dev, D = self.I_full.device, self.I_full.shape[1]
+            z = lambda *shape: torch.zeros(shape, dtype=torch.float32, device=dev)
+            self._state = dict(
+                m=z(self.per_rank, D) if main.rule != 'sgd' else None,
+                v=z(self.per_rank, D) if main.rule in ('adam', 'sparse_adam') else None,
+                bm=z(self.per_rank) if bias.rule != 'sgd' else None,
+                bv=z(self.per_rank) if bias.rule in ('adam', 'sparse_adam') else None,
+                g=z(self.per_rank, D), gb=z(self.per_rank),
+                flag=torch.zeros(self.per_rank, dtype=torch.int32, device=dev))
+        return self._state
+
+    def _workspace_views(self):
+        m, h = self.model, self.model.hparams
+        C = _abi.C
+        GI, gbi, flag = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        _abi.check(_abi.lib().cmf_train_workspace_items(
+            _abi.ptr(m._workspace), h.num_users, h.num_items, h.embedding_dim, C.byref(GI),
+            C.byref(gbi), C.byref(flag)), 'cmf_train_workspace_items')
+        base = m._workspace.data_ptr()
+        n, D = h.num_items, h.embedding_dim
+
+        def view(p, dtype, count, shape):
+            off = p.value - base
+            return m._workspace[off:off + count * 4].view(dtype).view(shape)
+        return (view(GI, torch.float32, n * D, (n, D)), view(gbi, torch.float32, n, (n,)),
+                view(flag, torch.int32, n, (n,)))
+
+    def train_step(self, batch, optimizers, interactions=None, epoch=0, global_batch=None,
+                   reduce_loss=True):
+        """One global step; returns the global mean loss (0-d tensor, identical on every rank).
+        ``global_batch``: total interactions of this step over all ranks (asked of the ranks when
+        ``None``, which costs a host round trip; equal-sized batches pass ``world * B``)."""
+        m = self.model
+        if isinstance(optimizers, tuple):
+            optimizers = optimizers[0]
+        if not isinstance(optimizers, (list, tuple)):
+            optimizers = [optimizers]
+        main, bias = optimizers[0], optimizers[1] if len(optimizers) > 1 else optimizers[0]
+        st = self._item_state(main, bias)
+        if global_batch is None:
+            t = torch.tensor([int(batch.users.shape[0])], dtype=torch.int64,
+                             device=self.I_full.device)
+            dist.all_reduce(t, group=self.group)
+            global_batch = int(t.item())
+        # 1. everyone gets the current item rows
+        all_gather_rows(self.I_full, self.I_shard, self.group)
+        all_gather_rows(self.bi_full.view(-1), self.bi_shard.reshape(-1), self.group)
+        # 2. local fused step, item side left in the workspace
+        loss = m.fused_step(batch, optimizers=optimizers, interactions=interactions, epoch=epoch,
+                            global_batch=int(global_batch), skip_item_update=True,
+                            num_items_logical=self.true_num_items)
+        GI, gbi, flag = self._workspace_views()
+        # 3. gradients and touched flags to the owners
+        reduce_scatter_sum(st['g'], GI, self.group)
+        reduce_scatter_sum(st['gb'], gbi, self.group)
+        reduce_scatter_sum(st['flag'], flag, self.group)
+        GI.zero_()
+        gbi.zero_()
+        flag.zero_()
+        # 4. owner-side masked update of this rank's rows (written straight into the working copy)
+        self._step += 1
+        g_main, g_bias = main.param_groups[0], bias.param_groups[0]
+        o = _abi.make_opt(main.rule, g_main['lr'], self._step, g_main.get('betas', (0.9, 0.999)),
+                          g_main.get('eps', 1e-8), 0.0)
+        ob = _abi.make_opt(bias.rule, g_bias['lr'], self._step, g_bias.get('betas', (0.9, 0.999)),
+                           g_bias.get('eps', 1e-8), 0.0)
+        rc = _abi.lib().cmf_optimizer_rows_masked(
+            _abi.ptr(self.I_shard), _abi.ptr(st['m']), _abi.ptr(st['v']), _abi.ptr(st['g']),
+            _abi.ptr(self.bi_shard), _abi.ptr(st['bm']), _abi.ptr(st['bv']), _abi.ptr(st['gb']),
+            self.per_rank, self.I_full.shape[1], _abi.ptr(st['flag']), o, ob,
+            _abi.stream_ptr(self.I_full.device))
+        _abi.check(rc, 'cmf_optimizer_rows_masked')
+        if reduce_loss:
+            dist.all_reduce(loss, group=self.group)
+        return loss
+
+    def gather_item_table(self):
+        """The up-to-date, unpadded item table and biases on every rank (for checkpoints / eval)."""
+        all_gather_rows(self.I_full, self.I_shard, self.group)
+        all_gather_rows(self.bi_full.view(-1), self.bi_shard.reshape(-1), self.group)
+        return self.I_full[:self.true_num_items], self.bi_full[:self.true_num_items]
+
+
+def evaluate_sharded(metric_list, local_test, model, k=10, group=None, **kwargs):
+    """``evaluate_in_batches`` over user shards: every rank scores its own test users against the
+    (gathered) item table; per-metric sums and user counts are all-reduced."""
+    from .metrics import evaluate_in_batches
+    n_local = int(len(np.unique(local_test.mat.row)))
+    if n_local:
+        res = evaluate_in_batches(metric_list, local_test, model, k=k, verbose=False, **kwargs)
+        res = res if isinstance(res, list) else [res]
+    else:
+        res = [0.0] * len(metric_list)
+    dev = next(model.parameters()).device
+    t = torch.tensor([r * n_local for r in res] + [float(n_local)], dtype=torch.float64,
+                     device=dev)
+    dist.all_reduce(t, group=group)
+    out = (t[:-1] / t[-1]).tolist()
+    return out[0] if len(out) == 1 else out
+
+
+def merge_topk(scores, ids, k):
+    """Merge per-shard top-k candidates ``[n, shards * k]`` into the global top-k in canonical order
+    (score descending, item id ascending); ids < 0 are padding. Returns ``(scores, ids)``."""
+    key = ids.long() + (ids < 0).long() * (1 << 40)          # padding last
+    by_id = torch.argsort(key, dim=1, stable=True)
+    s = torch.gather(scores, 1, by_id)
+    i = torch.gather(ids, 1, by_id)
+    s_cmp = torch.where(i < 0, torch.full_like(s, -float('inf')), s)
+    # a stable sort by descending score keeps the ascending id order among equal scores
+    top = torch.argsort(-s_cmp, dim=1, stable=True)[:, :k]
+    return torch.gather(s, 1, top), torch.gather(i, 1, top)
+
+
+def bench_sharded(args, rank, world, local_rank, workload, synth, config_dict, ClockSampler):
+    """``bench.py --gpus N`` for N > 1: weak scaling (the per-GPU batch is fixed), device timing,
+    max over ranks, one JSON line from rank 0."""
+    import json
+    import collie_b200 as cb
+    w = workload
+    dev = torch.device('cuda', local_rank)
+    if not dist.is_initialized():
+        dist.init_process_group('nccl', device_id=dev)
+    B = w['batch_per_gpu']
+    steps, warmup = args.steps, max(args.warmup, 3)
+    users, items = synth(w['num_users'], w['num_items'], w['interactions'], w['seed'])
+    lu, li, gpos = partition_interactions(users.numpy(), items.numpy(), rank, world)
+    per_rank, padded = shard_rows(w['num_items'], world)
+    data = cb.Interactions(users=lu, items=li, num_users=num_local_users(w['num_users'], rank, world),
+                           num_items=padded, num_negative_samples=w['n_neg'],
+                           allow_missing_ids=True, remove_duplicate_user_item_pairs=False,
+                           check_num_negative_samples_is_valid=False,
+                           max_number_of_samples_to_consider=0, seed=w['seed'])
+    data.global_positions = gpos
+    model = cb.MatrixFactorizationModel(train=data, embedding_dim=w['dim'], sparse=True,
+                                        lr=w['lr'], bias_lr=w['bias_lr'], optimizer='sparse_adam',
+                                        bias_optimizer='sgd', loss='bpr',
+                                        lr_scheduler_func=None).to(dev)
+    sharded = ShardedMatrixFactorization(model, w['num_items'])
+    opts = model.configure_optimizers()
+    loader = cb.InteractionsDataLoader(data, batch_size=B, shuffle=True, drop_last=True)
+
+    state = {'epoch': 0, 'it': None}
+
+    def next_batch():
+        while True:
+            if state['it'] is None:
+                state['it'] = loader.device_batches(dev, epoch=state['epoch'])
+                state['epoch'] += 1
+            try:
+                return next(state['it']), state['epoch']
+            except StopIteration:
+                state['it'] = None
+
+    def one_step():
+        db, epoch = next_batch()
+        return sharded.train_step(db, opts, interactions=data, epoch=epoch, global_batch=world * B,
+                                  reduce_loss=False)
+
+    for _ in range(warmup):
+        one_step()
+    state['it'] = None
+    torch.cuda.synchronize()
+    launches0 = _abi.launch_count()
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        loss = one_step()
+    e1.record()
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    clk = clocks.stop()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    launches = _abi.launch_count() - launches0
+    dist.all_reduce(loss)
+    value = steps * B * world / (ms * 1e-3)
+    if rank == 0:
+        D, N, T = w['dim'], w['n_neg'], 4
+        exchange = 2 * padded * (D + 2) * T * (world - 1) / world   # all-gather + reduce-scatter
+        line = {
+            'metric': 'MF train interactions/s (fwd+bwd+sparse Adam)', 'value': value,
+            'unit': 'interactions/s', 'n_gpus': world, 'steps': steps, 'warmup': warmup,
+            'ms_per_step': ms / steps, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': config_dict(world),
+            'roofline': None, 'cpu_baseline': None,
+            'e2e': None, 'gpu_launches': int(launches),
+            'gpu_launches_note': 'rank 0; own kernels per step: k_fwd_loss + k_bwd_update + '
+                                 'k_update_rows + k_optimizer_rows_masked (+ NCCL collectives)',
+            'exchange_bytes_per_step_per_gpu': exchange,
+            'clocks': clk, 'final_loss': float(loss),
+        }
+        print(json.dumps(line), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()

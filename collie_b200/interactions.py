@@ -95,6 +95,8 @@ class BaseInteractions(torch.utils.data.Dataset):
         self.min_rating = self.mat.data.min() if self.mat.nnz else None
         self.max_rating = self.mat.data.max() if self.mat.nnz else None
         self._dev = {}
+        # dataset positions in a larger (global) dataset this one was cut from; keys the RNG
+        self.global_positions = None
 
     def __len__(self):
         return self.num_interactions
@@ -130,6 +132,9 @@ class BaseInteractions(torch.utils.data.Dataset):
                 'users': torch.from_numpy(self.mat.row.astype(np.int32)).to(device),
                 'items': torch.from_numpy(self.mat.col.astype(np.int32)).to(device),
             }
+            if self.global_positions is not None:
+                st['gpos'] = torch.from_numpy(
+                    np.asarray(self.global_positions, dtype=np.int64)).to(device)
             self._extra_device_state(st, device)
             self._dev[key] = st
         return self._dev[key]
@@ -348,10 +353,11 @@ class BaseInteractionsDataLoader(object):
             order = order[idx]
         items = st['items'][order]
         ratings = st['ratings'][order] if 'ratings' in st else None
+        gidx = st['gpos'][order] if 'gpos' in st else order
         stop = (n // b) * b if self.drop_last else n
         for s in range(0, stop, b):
             e = min(s + b, n)
-            yield DeviceBatch(users[s:e], items[s:e], order[s:e],
+            yield DeviceBatch(users[s:e], items[s:e], gidx[s:e],
                               ratings[s:e] if ratings is not None else None,
                               bool(sort_within_batch))
 

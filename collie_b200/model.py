@@ -449,13 +449,17 @@ class MatrixFactorizationModel(torch.nn.Module):
         raise ValueError(f'Unexpected format for batch: {batch}. See docs for expected format.')
 
     def fused_step(self, batch, optimizers=None, train=True, interactions=None, epoch=0,
-                   outputs=None, users_sorted=False):
+                   outputs=None, users_sorted=False, global_batch=0, skip_item_update=False,
+                   num_items_logical=0):
         """One step through ``cmf_train_step``; returns the loss as a 0-d device tensor.
 
         ``optimizers``: what ``configure_optimizers`` returned (one optimizer, or [main, bias]).
         ``interactions``: the dataset behind a ``DeviceBatch`` (seed / exact-sampling CSR).
         ``outputs``: optional dict; keys among ``negs``, ``sel``, ``pos_scores``, ``neg_scores`` are
         filled with device tensors for inspection.
+        ``global_batch`` / ``skip_item_update``: multi-GPU hooks (``collie_b200.distributed``): the
+        loss is a mean over the global batch, and the item-row gradients stay in the workspace
+        for the caller to reduce across ranks.
         """
         if self._loss_name is None:
             raise _abi.CmfError('a custom loss callable cannot run inside the fused step; use one '
@@ -561,6 +565,9 @@ class MatrixFactorizationModel(torch.nn.Module):
                 a.neg_scores_out = outputs['neg_scores'].data_ptr()
         ws = self._workspace_for(B, int(a.N))
         a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
+        a.B_global = int(global_batch)
+        a.skip_item_update = 1 if skip_item_update else 0
+        a.num_items_logical = int(num_items_logical)
         rc = _abi.lib().cmf_train_step(_abi.C.byref(a), _abi.stream_ptr(self.device))
         _abi.check(rc, 'cmf_train_step')
         return loss_out[0]

@@ -130,11 +130,30 @@ typedef struct {
 
   void *workspace;
   size_t workspace_bytes;
+
+  /* multi-GPU (one process per GPU; 0 / 0 on a single GPU):
+   * B_global: interactions in the global batch; the loss is a mean over it, so gradients and the
+   * returned loss are scaled by 1 / B_global and the ranks' losses add up to the global loss.
+   * skip_item_update: leave the item-row gradients (and item "touched" flags) in the workspace
+   * for the caller to reduce across ranks (cmf_train_workspace_items) instead of applying them. */
+  int64_t B_global;
+  int32_t skip_item_update;
+  /* number of real items when the item table is padded to a multiple of the rank count: negatives
+   * are drawn from [0, num_items_logical) and WARP weights use it (0 = num_items) */
+  int32_t num_items_logical;
 } cmf_step_t;
 
 /* scratch for cmf_train_step; depends only on the table shapes and the largest batch */
 CMF_API size_t cmf_train_workspace_bytes(int64_t max_B, int32_t max_N, int64_t num_users, int64_t num_items,
                                  int32_t D);
+/* Views of the item-side accumulators inside a training workspace (layout depends only on the
+ * table shapes): GI [num_items, D] fp32 gradient rows, gbi [num_items] fp32 bias gradients,
+ * item_flag [num_items] int32 (non-zero = the row was gathered this step). With
+ * skip_item_update the caller sums them over ranks, applies cmf_optimizer_rows_masked to the rows
+ * it owns and zeroes all three again before the next step. */
+CMF_API int cmf_train_workspace_items(void *workspace, int64_t num_users, int64_t num_items, int32_t D,
+                              float **GI, float **gbi, int32_t **item_flag);
+
 /* zero the persistent part of the workspace; call once after allocation (and after a failure) */
 CMF_API int cmf_workspace_init(void *workspace, size_t workspace_bytes, void *stream);
 
@@ -185,6 +204,18 @@ CMF_API int cmf_sample_negatives(uint64_t seed, uint32_t epoch, const int64_t *g
 CMF_API int cmf_optimizer_rows(float *P, float *M, float *V, float *G, int64_t num_rows, int32_t D,
                        const int32_t *rows, int64_t n_rows, const cmf_opt_t *opt, int32_t zero_grad,
                        void *stream);
+
+/*
+ * cmf_optimizer_rows restricted to the rows whose touched[row] != 0 (all other rows are left
+ * alone unless the rule is dense); biases ride along: bP/bM/bV/bG are [num_rows] (bG may be NULL
+ * to skip them). This is the owner-side update of a row-sharded table after the ranks'
+ * gradients have been reduced: SparseAdam moves every row some rank gathered, even with a zero
+ * gradient (torch.optim.SparseAdam on the coalesced sparse gradient, base_pipeline.py:430-433).
+ */
+CMF_API int cmf_optimizer_rows_masked(float *P, float *M, float *V, const float *G, float *bP, float *bM,
+                              float *bV, const float *bG, int64_t num_rows, int32_t D,
+                              const int32_t *touched, const cmf_opt_t *opt,
+                              const cmf_opt_t *bias_opt, void *stream);
 
 /*
  * Evaluation of one tile of users against the whole item table (or an item shard):
