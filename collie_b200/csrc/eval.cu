@@ -11,6 +11,7 @@
 namespace cmf {
 
 int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s);  // eval_tc.cu (tcgen05 path)
+size_t eval_tc_workspace_bytes(int64_t n_users, int64_t n_items, int D, int k);
 
 // ------------------------------------------------------------------ scores: 64x64 tile, K step 16
 constexpr int TM = 64, TN = 64, TK = 16;
@@ -263,8 +264,8 @@ using namespace cmf;
 
 extern "C" size_t cmf_eval_workspace_bytes(int64_t n_users_tile, int64_t num_items_shard, int32_t D,
                                            int32_t k, int32_t precision) {
-  (void)D; (void)k; (void)precision;
   if (n_users_tile < 1 || num_items_shard < 1) return 0;
+  if (precision == 1) return eval_tc_workspace_bytes(n_users_tile, num_items_shard, D, k);
   // score tile + sigmoid scratch for users with more than kSigSmem targets (bounded by the shard)
   return eval_ws_scores(n_users_tile, num_items_shard) +
          align_up(2 * sizeof(float) * n_users_tile * num_items_shard, 256);

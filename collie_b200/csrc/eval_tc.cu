@@ -1,9 +1,592 @@
-// Evaluation, tensor-core path (tcgen05 + TMA + TMEM) -- placeholder until the kernel lands.
+// Evaluation, tensor-core path (precision = 1): S = U_tile . I^T as tcgen05 GEMM tiles fed by TMA,
+// fp32 accumulators in TMEM, and the per-user top-k (+ the MRR counter) in the epilogue, so the
+// score matrix never exists in memory.
+//
+// Reference: collie/metrics.py get_preds :77-107 (Bu * n_items independent gather-dots there),
+// mapk :144-198, mrr :201-240.
+//
+// fp32 parity on bf16 tensor cores: every fp32 value x is split as hi = bf16(x), lo = bf16(x - hi)
+// and the GEMM runs over the concatenated K axis  A' = [Ah | Ah | Al],  B' = [Bh | Bl | Bh]
+// (K' = 3 D), i.e. S = Ah.Bh + Ah.Bl + Al.Bh with fp32 accumulation; the dropped Al.Bl term is
+// < 2^-16 relative. Values that are exactly representable in bf16 (the exact-arithmetic parity
+// fixture) give bit-exact scores.
+//
+// One CTA = one 128-user tile x one contiguous range of 128-item tiles (the item range is split so
+// that about one CTA per SM is in flight); the CTAs of one user tile leave their top-k candidates
+// and counters in scratch and k_tc_merge combines them in canonical order (score desc, id asc).
+//   warp 0      TMA producer: A' once (resident), then B' K-blocks through a 4-stage mbarrier ring
+//   warp 1      MMA issuer: tcgen05.mma.cta_group::1.kind::f16, M = 128, N = 128, K = 16 per
+//               instruction, two accumulators in TMEM (256 columns) so tile t+1 is being multiplied
+//               while tile t is ranked
+//   warp 2      TMEM allocation
+//   warps 4..7  epilogue: tcgen05.ld 32x32b (thread = user row), bias add, threshold test against
+//               the row's current k-th best, rare sorted insert into a per-row list in shared
+//               memory, MRR counter
+#include <cuda.h>
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 
 namespace cmf {
-int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
-  (void)a; (void)s;
-  return fail(CMF_ERR_UNSUPPORTED, "cmf_eval_tile: precision=1 (tcgen05) path not built yet");
+
+constexpr int TC_BM = 128;        // users per CTA
+constexpr int TC_BN = 128;        // items per MMA tile
+constexpr int TC_BK = 64;         // bf16 per K block = one 128-byte swizzle row
+constexpr int TC_STAGES = 4;
+constexpr int TC_MAXK = 32;       // top-k list length supported by the epilogue
+constexpr int TC_TILE_BYTES = TC_BN * TC_BK * 2;   // 16 KB: one operand K-block
+
+// ---------------------------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t s_addr(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
 }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1,
+                                            uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+// D[tmem] (+)= A[smem] . B[smem]^T, bf16 inputs, fp32 accumulate; issued by ONE thread
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                          uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on an mbarrier when all MMAs issued so far by this thread have completed
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+        "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+        "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]),
+        "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// K-major operand tile with 128-byte swizzle: rows of 64 bf16 at a 128-byte pitch, 8-row groups
+// 1024 bytes apart (SBO = 64 x 16 B), descriptor version 1 (sm_100), layout type 2 = SWIZZLE_128B.
+// Field layout: cute/arch/mma_sm100_desc.hpp (SmemDescriptor).
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t addr) {
+  return (uint64_t)((addr >> 4) & 0x3FFF) | (1ull << 16) | (64ull << 32) | (1ull << 46) |
+         (2ull << 61);
+}
+// kind::f16 instruction descriptor: D = f32, A = B = bf16, both K-major, N = 128, M = 128
+// (InstrDescriptor in cute/arch/mma_sm100_desc.hpp: c_format [4,6), a_format [7,10),
+// b_format [10,13), n_dim = N >> 3 at [17,23), m_dim = M >> 4 at [24,29)).
+constexpr uint32_t kIdescBf16 =
+    (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+
+// ---------------------------------------------------------------------------------- prep kernels
+__device__ __forceinline__ void split_bf16(float x, __nv_bfloat16& hi, __nv_bfloat16& lo) {
+  hi = __float2bfloat16_rn(x);
+  lo = __float2bfloat16_rn(x - __bfloat162float(hi));
+}
+
+// rows of `src` (optionally gathered through `ids`) -> [hi | lo | hi] (items) or [hi | hi | lo]
+// (users) bf16 rows of length Kp (zero padded); rows >= n_rows are zero.
+__global__ void __launch_bounds__(256)
+k_tc_split(const float* __restrict__ src, const int32_t* __restrict__ ids, int64_t row_offset,
+           int64_t n_rows, int64_t n_rows_pad, int D, int Kp, int users,
+           __nv_bfloat16* __restrict__ out) {
+  const int64_t total = n_rows_pad * (int64_t)Kp;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / Kp;
+    const int c = (int)(i - r * Kp);
+    __nv_bfloat16 v = __float2bfloat16_rn(0.f);
+    if (r < n_rows && c < 3 * D) {
+      const int seg = c / D, d = c - seg * D;
+      const int64_t row = ids ? (int64_t)ids[r] : row_offset + r;
+      __nv_bfloat16 hi, lo;
+      split_bf16(src[row * D + d], hi, lo);
+      const bool want_lo = users ? (seg == 2) : (seg == 1);
+      v = want_lo ? lo : hi;
+    }
+    out[i] = v;
+  }
+}
+
+// exact fp32 score of every target of every user of the tile; keeps the best (score desc, id asc)
+__global__ void __launch_bounds__(256)
+k_tc_target_best(const float* __restrict__ U, const float* __restrict__ I,
+                 const float* __restrict__ bu, const float* __restrict__ bi, int D,
+                 const int32_t* __restrict__ user_ids, int64_t n_users, int64_t item_lo,
+                 int64_t item_hi, const int64_t* __restrict__ tgt_indptr,
+                 const int32_t* __restrict__ tgt_items, float* __restrict__ best_s,
+                 int32_t* __restrict__ best_id) {
+  const int lane = threadIdx.x & 31;
+  const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (r >= n_users) return;
+  const int64_t u = user_ids[r];
+  float bs = -INFINITY;
+  int bid = -1;
+  for (int64_t t = tgt_indptr[r]; t < tgt_indptr[r + 1]; ++t) {
+    const int id = tgt_items[t];
+    if (id < item_lo || id >= item_hi) continue;
+    float acc = 0.f;
+    for (int d = lane; d < D; d += 32) acc = fmaf(U[u * D + d], I[(int64_t)id * D + d], acc);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    const float s = acc + bu[u] + bi[id];
+    if (bid < 0 || s > bs || (s == bs && id < bid)) { bs = s; bid = id; }
+  }
+  if (lane == 0) { best_s[r] = bs; best_id[r] = bid; }
+}
+
+// ---------------------------------------------------------------------------------- GEMM + top-k
+struct TcParams {
+  int n_users, k, KB, n_tiles, tiles_per_split, n_splits, want_mrr;
+  int64_t n_items, item_offset;
+  const float* bu_tile;  // [n_users_pad] user biases of the tile (gathered)
+  const float* bi;       // item biases (global ids)
+  const float* best_s;   // MRR threshold per user (may be NULL)
+  const int32_t* best_id;
+  float* cand_s;         // [n_users_pad][n_splits][k]
+  int32_t* cand_i;
+  int32_t* cnt;          // [n_users_pad][n_splits] items ranked before the best target
+};
+
+__global__ void __launch_bounds__(256, 1)
+k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const TcParams p) {
+  extern __shared__ unsigned char smem_raw[];
+  // 128-byte-swizzled operand tiles need 1024-byte alignment
+  unsigned char* smem = smem_raw + ((1024u - (s_addr(smem_raw) & 1023u)) & 1023u);
+  // carve-up: A' K-blocks | B' stages | per-row top-k lists | item-bias tiles | barriers
+  unsigned char* sA = smem;
+  unsigned char* sB = sA + (size_t)p.KB * TC_TILE_BYTES;
+  float* s_top_s = reinterpret_cast<float*>(sB + (size_t)TC_STAGES * TC_TILE_BYTES);
+  int* s_top_i = reinterpret_cast<int*>(s_top_s + TC_BM * (TC_MAXK + 1));
+  float* s_bi = reinterpret_cast<float*>(s_top_i + TC_BM * (TC_MAXK + 1));   // [2][TC_BN]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_bi + 2 * TC_BN);
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 16);
+
+  const uint32_t bar_full = s_addr(&bars[0]);                 // [TC_STAGES]
+  const uint32_t bar_empty = s_addr(&bars[TC_STAGES]);        // [TC_STAGES]
+  const uint32_t bar_a = s_addr(&bars[2 * TC_STAGES]);
+  const uint32_t bar_tfull = s_addr(&bars[2 * TC_STAGES + 1]);   // [2]
+  const uint32_t bar_tempty = s_addr(&bars[2 * TC_STAGES + 3]);  // [2]
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.y * TC_BM;
+  const int split = blockIdx.x;
+  const int tile_lo = split * p.tiles_per_split;
+  const int tile_hi = min(p.n_tiles, tile_lo + p.tiles_per_split);
+  const int n_my = max(0, tile_hi - tile_lo);
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < TC_STAGES; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); }
+    mbar_init(bar_a, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_tfull + 8 * i, 1); mbar_init(bar_tempty + 8 * i, 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    // 256 TMEM columns: two 128 x 128 fp32 accumulators
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     s_addr(s_tmem)), "r"(256)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 0) {
+    // ===================================================================== TMA producer
+    if (lane == 0 && n_my > 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+      mbar_expect_tx(bar_a, (uint32_t)p.KB * TC_TILE_BYTES);
+      for (int kb = 0; kb < p.KB; ++kb)
+        tma_load_2d(s_addr(sA + (size_t)kb * TC_TILE_BYTES), &tmA, kb * TC_BK, m0, bar_a);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = 0; t < n_my; ++t) {
+        const int n0 = (tile_lo + t) * TC_BN;
+        for (int kb = 0; kb < p.KB; ++kb) {
+          mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+          mbar_expect_tx(bar_full + 8 * stage, TC_TILE_BYTES);
+          tma_load_2d(s_addr(sB + (size_t)stage * TC_TILE_BYTES), &tmB, kb * TC_BK, n0,
+                      bar_full + 8 * stage);
+          if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================================== MMA issuer
+    if (lane == 0 && n_my > 0) {
+      mbar_wait(bar_a, 0);
+      tc_fence_after();
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = 0; t < n_my; ++t) {
+        const int acc = t & 1;
+        mbar_wait(bar_tempty + 8 * acc, ((t >> 1) & 1) ^ 1);   // the epilogue drained this buffer
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * TC_BN);
+        for (int kb = 0; kb < p.KB; ++kb) {
+          mbar_wait(bar_full + 8 * stage, phase);
+          tc_fence_after();
+          const uint64_t da = smem_desc_sw128(s_addr(sA + (size_t)kb * TC_TILE_BYTES));
+          const uint64_t db = smem_desc_sw128(s_addr(sB + (size_t)stage * TC_TILE_BYTES));
+#pragma unroll
+          for (int j = 0; j < TC_BK / 16; ++j)   // +32 bytes (2 x 16 B) per K = 16 step
+            umma_bf16(d_tmem, da + 2 * j, db + 2 * j, kIdescBf16, (kb | j) != 0);
+          umma_commit(bar_empty + 8 * stage);     // frees the stage when these MMAs are done
+          if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(bar_tfull + 8 * acc);         // accumulator complete -> epilogue
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================================================================== epilogue
+    const int q = warp & 3;               // TMEM lane quarter this warp may read
+    const int row = q * 32 + lane;        // user row inside the tile
+    const int et = threadIdx.x - 128;     // 0..127
+    const bool valid = (m0 + row) < p.n_users;
+    const float b_user = valid ? p.bu_tile[m0 + row] : 0.f;
+    const int K = p.k;
+    float* ls = s_top_s + row * (TC_MAXK + 1);
+    int* li = s_top_i + row * (TC_MAXK + 1);
+    int have = 0;
+    float thr = -INFINITY;
+    const bool mrr = p.want_mrr && valid;
+    const float best_s = mrr ? p.best_s[m0 + row] : 0.f;
+    const int best_id = mrr ? p.best_id[m0 + row] : -1;
+    int before = 0;
+
+    for (int t = 0; t < n_my; ++t) {
+      const int acc = t & 1;
+      const int64_t n0 = (int64_t)(tile_lo + t) * TC_BN;
+      {  // item biases of this tile -> shared memory (double buffered with the accumulator)
+        const int64_t id = n0 + et;
+        s_bi[acc * TC_BN + et] = id < p.n_items ? p.bi[p.item_offset + id] : 0.f;
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+      }
+      mbar_wait(bar_tfull + 8 * acc, (t >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * TC_BN);
+#pragma unroll 1
+      for (int c0 = 0; c0 < TC_BN; c0 += 32) {
+        float v[32];
+        tmem_ld32(taddr + c0, v);
+        if (!valid) continue;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int64_t id = n0 + c0 + j;
+          if (id >= p.n_items) break;
+          const float s = v[j] + b_user + s_bi[acc * TC_BN + c0 + j];
+          const int gid = (int)(p.item_offset + id);
+          // the threshold is the target's exact fp32 score; the target itself is excluded by id
+          if (mrr && gid != best_id && (s > best_s || (s == best_s && gid < best_id))) ++before;
+          if (have < K || s > thr) {
+            // sorted insert; ids only grow, so on equal scores the newcomer stays behind
+            int pos = have < K ? have : K - 1;
+            while (pos > 0 && s > ls[pos - 1]) {
+              ls[pos] = ls[pos - 1];
+              li[pos] = li[pos - 1];
+              --pos;
+            }
+            ls[pos] = s;
+            li[pos] = gid;
+            if (have < K) ++have;
+            if (have == K) thr = ls[K - 1];
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+    }
+    if (valid) {
+      float* cs = p.cand_s + ((int64_t)(m0 + row) * p.n_splits + split) * K;
+      int32_t* ci = p.cand_i + ((int64_t)(m0 + row) * p.n_splits + split) * K;
+      for (int j = 0; j < K; ++j) {
+        cs[j] = j < have ? ls[j] : -INFINITY;
+        ci[j] = j < have ? li[j] : -1;
+      }
+      if (p.cnt) p.cnt[(int64_t)(m0 + row) * p.n_splits + split] = before;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256)
+                 : "memory");
+  }
+}
+
+// merge the candidates of a user's item splits: one warp per user, k selection passes in
+// canonical order; AP@k against the user's sorted target list; counters summed.
+__global__ void __launch_bounds__(256)
+k_tc_merge(const float* __restrict__ cand_s, const int32_t* __restrict__ cand_i,
+           const int32_t* __restrict__ cnt, int n_splits, int k, int64_t n_users,
+           const int64_t* __restrict__ tgt_indptr, const int32_t* __restrict__ tgt_items,
+           const int32_t* __restrict__ best_id, int32_t* __restrict__ topk_ids,
+           float* __restrict__ topk_scores, double* __restrict__ ap,
+           int32_t* __restrict__ n_before_best) {
+  const int lane = threadIdx.x & 31;
+  const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (r >= n_users) return;
+  const int total = n_splits * k;
+  const float* cs = cand_s + r * total;
+  const int32_t* ci = cand_i + r * total;
+  const int64_t t0 = tgt_indptr[r];
+  const int n_tgt = (int)(tgt_indptr[r + 1] - t0);
+  float ps = INFINITY;
+  int pid = -1, hits = 0;
+  double ap_acc = 0.0;
+  for (int j = 0; j < k; ++j) {
+    float bs = -INFINITY;
+    int bid = -1;
+    for (int c = lane; c < total; c += 32) {
+      const int id = ci[c];
+      if (id < 0) continue;
+      const float s = cs[c];
+      const bool after_prev = (pid < 0) || (ps > s) || (ps == s && pid < id);
+      if (after_prev && (bid < 0 || s > bs || (s == bs && id < bid))) { bs = s; bid = id; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float os = __shfl_xor_sync(0xffffffffu, bs, o);
+      const int oid = __shfl_xor_sync(0xffffffffu, bid, o);
+      if (oid >= 0 && (bid < 0 || os > bs || (os == bs && oid < bid))) { bs = os; bid = oid; }
+    }
+    if (lane == 0) {
+      if (topk_ids) topk_ids[r * k + j] = bid;
+      if (topk_scores) topk_scores[r * k + j] = bid >= 0 ? bs : -INFINITY;
+      if (bid >= 0 && csr_contains(tgt_items + t0, 0, n_tgt, bid)) {
+        ++hits;
+        ap_acc += (double)hits / (double)(j + 1);
+      }
+    }
+    ps = bs;
+    pid = bid;
+    if (bid < 0) {
+      if (lane == 0)
+        for (int jj = j + 1; jj < k; ++jj) {
+          if (topk_ids) topk_ids[r * k + jj] = -1;
+          if (topk_scores) topk_scores[r * k + jj] = -INFINITY;
+        }
+      break;
+    }
+  }
+  if (lane == 0) {
+    if (ap) {
+      const int denom = k < n_tgt ? k : n_tgt;
+      ap[r] = denom > 0 ? ap_acc / (double)denom : 0.0;
+    }
+    if (n_before_best) {
+      int tot = 0;
+      if (cnt) for (int s = 0; s < n_splits; ++s) tot += cnt[r * n_splits + s];
+      n_before_best[r] = (best_id && best_id[r] >= 0) ? tot : -1;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+// [rows, Kp] bf16 row-major, box = 64 columns x 128 rows, 128-byte swizzle, OOB rows read as zero
+static int make_map(CUtensorMap* map, void* base, int64_t rows, int Kp) {
+  EncodeTiledFn enc = encode_tiled();
+  if (!enc) return fail(CMF_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+  cuuint64_t dims[2] = {(cuuint64_t)Kp, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)Kp * 2};
+  cuuint32_t box[2] = {TC_BK, TC_BN};
+  cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(CMF_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+  return CMF_OK;
+}
+
+struct TcLayout {
+  int Kp, KB, m_tiles, n_tiles, n_splits, tiles_per_split;
+  int64_t m_pad;
+  size_t Bp, Ap, bu, best_s, best_id, cand_s, cand_i, cnt, total;
+};
+
+static TcLayout tc_layout(int64_t n_users, int64_t n_items, int D, int k) {
+  TcLayout L;
+  L.Kp = (int)align_up((size_t)3 * D, TC_BK);
+  L.KB = L.Kp / TC_BK;
+  L.m_tiles = (int)((n_users + TC_BM - 1) / TC_BM);
+  L.m_pad = (int64_t)L.m_tiles * TC_BM;
+  L.n_tiles = (int)((n_items + TC_BN - 1) / TC_BN);
+  int want = (num_sms() + L.m_tiles - 1) / L.m_tiles;   // about one CTA per SM
+  if (want > L.n_tiles) want = L.n_tiles;
+  if (want < 1) want = 1;
+  L.tiles_per_split = (L.n_tiles + want - 1) / want;
+  L.n_splits = (L.n_tiles + L.tiles_per_split - 1) / L.tiles_per_split;
+  size_t o = 0;
+  auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes, 1024); return at; };
+  L.Bp = take((size_t)n_items * L.Kp * 2);
+  L.Ap = take((size_t)L.m_pad * L.Kp * 2);
+  L.bu = take(sizeof(float) * L.m_pad);
+  L.best_s = take(sizeof(float) * L.m_pad);
+  L.best_id = take(sizeof(int32_t) * L.m_pad);
+  L.cand_s = take(sizeof(float) * L.m_pad * L.n_splits * k);
+  L.cand_i = take(sizeof(int32_t) * L.m_pad * L.n_splits * k);
+  L.cnt = take(sizeof(int32_t) * L.m_pad * L.n_splits);
+  L.total = o;
+  return L;
+}
+
+bool eval_tc_supported(int D, int k) { return D >= 1 && 3 * D <= 6 * TC_BK && k >= 1 && k <= TC_MAXK; }
+
+size_t eval_tc_workspace_bytes(int64_t n_users, int64_t n_items, int D, int k) {
+  if (!eval_tc_supported(D, k)) return 0;
+  return tc_layout(n_users, n_items, D, k).total;
+}
+
+__global__ void k_tc_gather_bias(const float* bu, const int32_t* ids, int64_t n, int64_t n_pad,
+                                 float* out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_pad) out[i] = i < n ? bu[ids[i]] : 0.f;
+}
+
+int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
+  CMF_REQUIRE(!a->want_auc, "cmf_eval_tile: AUC is computed by the exact path (precision = 0)");
+  if (!eval_tc_supported(a->D, a->k))
+    return fail(CMF_ERR_UNSUPPORTED,
+                "cmf_eval_tile: the tensor-core path takes embedding_dim <= 128 and k <= %d "
+                "(got D = %d, k = %d); use precision = 0", TC_MAXK, a->D, a->k);
+  const TcLayout L = tc_layout(a->n_users_tile, a->num_items_shard, a->D, a->k);
+  if (!a->workspace || a->workspace_bytes < L.total)
+    return fail(CMF_ERR_WORKSPACE, "cmf_eval_tile: workspace of %zu bytes needed, %zu given",
+                L.total, a->workspace ? a->workspace_bytes : (size_t)0);
+  char* base = (char*)a->workspace;
+  __nv_bfloat16* Bp = (__nv_bfloat16*)(base + L.Bp);
+  __nv_bfloat16* Ap = (__nv_bfloat16*)(base + L.Ap);
+  float* bu_tile = (float*)(base + L.bu);
+  float* best_s = (float*)(base + L.best_s);
+  int32_t* best_id = (int32_t*)(base + L.best_id);
+  const int grid = num_sms() * 8;
+
+  if (!a->reuse_item_prep) {
+    k_tc_split<<<grid, 256, 0, s>>>(a->I, nullptr, a->item_offset, a->num_items_shard,
+                                    a->num_items_shard, a->D, L.Kp, 0, Bp);
+    CMF_LAUNCH_CHECK();
+  }
+  k_tc_split<<<grid, 256, 0, s>>>(a->U, a->user_ids, 0, a->n_users_tile, L.m_pad, a->D, L.Kp, 1, Ap);
+  CMF_LAUNCH_CHECK();
+  k_tc_gather_bias<<<(unsigned)((L.m_pad + 255) / 256), 256, 0, s>>>(a->bu, a->user_ids,
+                                                                     a->n_users_tile, L.m_pad,
+                                                                     bu_tile);
+  CMF_LAUNCH_CHECK();
+  const bool mrr = a->want_mrr != 0;
+  if (mrr) {
+    if (a->ext_best_id) {
+      CMF_CUDA(cudaMemcpyAsync(best_s, a->ext_best_score, sizeof(float) * a->n_users_tile,
+                               cudaMemcpyDeviceToDevice, s));
+      CMF_CUDA(cudaMemcpyAsync(best_id, a->ext_best_id, sizeof(int32_t) * a->n_users_tile,
+                               cudaMemcpyDeviceToDevice, s));
+    } else {
+      k_tc_target_best<<<(unsigned)((a->n_users_tile * 32 + 255) / 256), 256, 0, s>>>(
+          a->U, a->I, a->bu, a->bi, a->D, a->user_ids, a->n_users_tile, a->item_offset,
+          a->item_offset + a->num_items_shard, a->tgt_indptr, a->tgt_items, best_s, best_id);
+      CMF_LAUNCH_CHECK();
+    }
+    if (a->best_score)
+      CMF_CUDA(cudaMemcpyAsync(a->best_score, best_s, sizeof(float) * a->n_users_tile,
+                               cudaMemcpyDeviceToDevice, s));
+    if (a->best_id)
+      CMF_CUDA(cudaMemcpyAsync(a->best_id, best_id, sizeof(int32_t) * a->n_users_tile,
+                               cudaMemcpyDeviceToDevice, s));
+  }
+
+  CUtensorMap tmA, tmB;
+  int rc = make_map(&tmA, Ap, L.m_pad, L.Kp);
+  if (rc) return rc;
+  rc = make_map(&tmB, Bp, a->num_items_shard, L.Kp);
+  if (rc) return rc;
+
+  TcParams p{};
+  p.n_users = (int)a->n_users_tile; p.k = a->k; p.KB = L.KB; p.n_tiles = L.n_tiles;
+  p.tiles_per_split = L.tiles_per_split; p.n_splits = L.n_splits; p.want_mrr = mrr ? 1 : 0;
+  p.n_items = a->num_items_shard; p.item_offset = a->item_offset;
+  p.bu_tile = bu_tile; p.bi = a->bi; p.best_s = best_s; p.best_id = best_id;
+  p.cand_s = (float*)(base + L.cand_s); p.cand_i = (int32_t*)(base + L.cand_i);
+  p.cnt = (int32_t*)(base + L.cnt);
+
+  const size_t smem = (size_t)L.KB * TC_TILE_BYTES + (size_t)TC_STAGES * TC_TILE_BYTES +
+                      2 * sizeof(float) * TC_BM * (TC_MAXK + 1) + 2 * sizeof(float) * TC_BN +
+                      16 * sizeof(uint64_t) + 64 + 1024;
+  CMF_CUDA(cudaFuncSetAttribute(k_tc_gemm_topk, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)smem));
+  dim3 gridg((unsigned)L.n_splits, (unsigned)L.m_tiles);
+  k_tc_gemm_topk<<<gridg, 256, smem, s>>>(tmA, tmB, p);
+  CMF_LAUNCH_CHECK();
+
+  k_tc_merge<<<(unsigned)((a->n_users_tile * 32 + 255) / 256), 256, 0, s>>>(
+      p.cand_s, p.cand_i, mrr ? p.cnt : nullptr, L.n_splits, a->k, a->n_users_tile, a->tgt_indptr,
+      a->tgt_items, mrr ? best_id : nullptr, a->topk_ids, a->topk_scores, a->ap,
+      a->n_before_best);
+  CMF_LAUNCH_CHECK();
+  return CMF_OK;
+}
+
 }  // namespace cmf

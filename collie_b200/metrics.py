@@ -19,6 +19,7 @@ from .interactions import Interactions
 # users per fused tile; the result does not depend on it (per-user values are summed)
 _TILE_USERS = 256
 _MAX_TILE_BYTES = 1 << 30
+_TC_TILE_USERS = 8192   # users per tensor-core call (128-user CTA tiles inside)
 
 
 def _targets_device(targets: csr_matrix, user_ids, device):
@@ -34,7 +35,7 @@ def _targets_device(targets: csr_matrix, user_ids, device):
 
 
 def _eval_tile(device, n_users, n_items, k, indptr, tgt_items, want, tables=None, user_ids=None,
-               scores=None, precision=0, workspace=None):
+               scores=None, precision=0, workspace=None, reuse_item_prep=False):
     """One ``cmf_eval_tile`` call; returns dict of per-user device tensors."""
     a = _abi.cmf_eval_t()
     keep = []
@@ -50,6 +51,7 @@ def _eval_tile(device, n_users, n_items, k, indptr, tgt_items, want, tables=None
     a.n_users_tile, a.item_offset, a.num_items_shard, a.k = n_users, 0, n_items, k
     a.tgt_indptr, a.tgt_items = indptr.data_ptr(), tgt_items.data_ptr()
     a.precision = precision
+    a.reuse_item_prep = 1 if reuse_item_prep else 0
     out = {}
     if 'mapk' in want:
         out['ap'] = torch.empty(n_users, dtype=torch.float64, device=device)
@@ -182,17 +184,36 @@ def evaluate_in_batches(metric_list, test_interactions, model, k=10, batch_size=
         tables = _model_tables(model)
         indptr, tgt_items, nnz = _targets_device(targets, test_users, device)
         users_dev = torch.from_numpy(test_users.astype(np.int32)).to(device)
-        tile = max(1, min(_TILE_USERS, _MAX_TILE_BYTES // max(1, 12 * n_items)))
+        D = tables[0].shape[1]
+        # tensor-core route for what it supports (top-k / MAP / MRR); AUC stays on the exact path
+        use_tc = precision == 1 and D <= 128 and k <= 32
+        if precision == 1 and not use_tc:
+            raise _abi.CmfError('precision=1 needs embedding_dim <= 128 and k <= 32')
+        tc_names = [n for n in names if n != 'auc'] if use_tc else []
+        ex_names = [n for n in names if n not in tc_names]
         sums = torch.zeros(len(names), dtype=torch.float64, device=device)
-        ws = None
-        for s in range(0, n_test, tile):
-            e = min(s + tile, n_test)
-            res = _eval_tile(device, e - s, n_items, k, indptr[s:e + 1], tgt_items, set(names),
-                             tables=tables, user_ids=users_dev[s:e], precision=precision,
-                             workspace=ws)
-            ws = res['_workspace']
-            for j, name in enumerate(names):
-                sums[j] += _per_user(name, res, nnz[s:e], n_items).sum()
+        if ex_names:
+            tile = max(1, min(_TILE_USERS, _MAX_TILE_BYTES // max(1, 12 * n_items)))
+            ws = None
+            for s in range(0, n_test, tile):
+                e = min(s + tile, n_test)
+                res = _eval_tile(device, e - s, n_items, k, indptr[s:e + 1], tgt_items,
+                                 set(ex_names), tables=tables, user_ids=users_dev[s:e],
+                                 precision=0, workspace=ws)
+                ws = res['_workspace']
+                for name in ex_names:
+                    sums[names.index(name)] += _per_user(name, res, nnz[s:e], n_items).sum()
+        if tc_names:
+            tile = _TC_TILE_USERS
+            ws = None
+            for s in range(0, n_test, tile):
+                e = min(s + tile, n_test)
+                res = _eval_tile(device, e - s, n_items, k, indptr[s:e + 1], tgt_items,
+                                 set(tc_names), tables=tables, user_ids=users_dev[s:e],
+                                 precision=1, workspace=ws, reuse_item_prep=(s > 0))
+                ws = res['_workspace']
+                for name in tc_names:
+                    sums[names.index(name)] += _per_user(name, res, nnz[s:e], n_items).sum()
         all_scores = (sums / n_test).tolist()
     else:
         if n_test < batch_size:

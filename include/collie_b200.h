@@ -231,7 +231,9 @@ CMF_API int cmf_optimizer_rows_masked(float *P, float *M, float *V, const float 
  *   ap [n] double (AP@k per user, fp64 like the reference's weights), n_before_best [n] int32: #items ranked before the user's best-ranked
  *   target in this shard, best_score/best_id [n]: that target's score/id (-inf/-1 when none),
  *   auc_pairs [n] double: sum over targets of (#non-targets with lower sigmoid + .5 ties).
- * precision: 0 = fp32 SIMT scoring (exact fp32), 1 = tcgen05 tensor cores, bf16x3 split operands.
+ * precision: 0 = fp32 SIMT scoring (exact fp32; all outputs), 1 = tcgen05 tensor cores over
+ *   bf16-split operands (hi.hi + hi.lo + lo.hi, fp32 accumulation): embedding_dim <= 128, k <= 32,
+ *   every output except auc_pairs (want_auc must be 0).
  */
 typedef struct {
   const float *U, *I, *bu, *bi;
@@ -261,6 +263,10 @@ typedef struct {
    * scoring (the metric callables' `preds` argument, collie/metrics.py:144-147); U/I/bu/bi and
    * user_ids are then ignored */
   const float *scores_in;
+  /* precision = 1 only: non-zero = the item table has not changed since the previous call with
+   * this workspace, so its bf16 split copy in the workspace is reused */
+  int32_t reuse_item_prep;
+  int32_t reserved_;
 } cmf_eval_t;
 
 CMF_API size_t cmf_eval_workspace_bytes(int64_t n_users_tile, int64_t num_items_shard, int32_t D, int32_t k,

@@ -475,3 +475,80 @@ def test_errors_are_loud():
     a = _abi.cmf_step_t()
     assert _abi.lib().cmf_train_step(_abi.C.byref(a), None) == -1
     assert b'null parameter table' in _abi.lib().cmf_last_error()
+
+
+# ------------------------------------------------------------------------------------ tensor cores
+def test_tensor_core_eval_bit_exact_on_exact_fixture():
+    """precision=1 (tcgen05 GEMM over bf16-split operands): on the exact-arithmetic fixture every
+    value is representable in bf16, so scores and top-k ids equal the oracle's bit for bit."""
+    from collie_b200 import metrics as M
+    from oracle import collie_oracle as O
+    g = np.load(os.path.join(GOLDEN, 'metrics_exact_grid.npz'))
+    n_users, n_items = int(g['n_users']), int(g['n_items'])
+    tabs = tuple(torch.from_numpy(g[k]).cuda() for k in ('U', 'I', 'bu', 'bi'))
+    users = torch.arange(n_users, dtype=torch.int32, device='cuda')
+    coo = sp.coo_matrix((np.ones(len(g['test_users'])), (g['test_users'], g['test_items'])),
+                        shape=(n_users, n_items))
+    indptr, items, _ = M._targets_device(coo.tocsr(), np.arange(n_users), 'cuda')
+    for k in (1, 10, 32):
+        res = M._eval_tile('cuda', n_users, n_items, k, indptr, items, {'topk', 'mapk', 'mrr'},
+                           tables=tabs, user_ids=users, precision=1)
+        exp_ids = O.topk_ids(g['scores'], k)
+        assert np.array_equal(res['topk_ids'].cpu().numpy(), exp_ids)
+        assert np.array_equal(res['topk_scores'].cpu().numpy(),
+                              np.take_along_axis(g['scores'], exp_ids, axis=1))
+        np.testing.assert_allclose(res['ap'].cpu().numpy(),
+                                   O.mapk_per_user(coo.tocsr(), np.arange(n_users), g['scores'], k),
+                                   rtol=1e-12)
+        nb = res['n_before_best'].cpu().numpy().astype(np.float64)
+        np.testing.assert_allclose(np.where(nb >= 0, 1.0 / (nb + 1.0), 0.0),
+                                   O.mrr_per_user(coo.tocsr(), np.arange(n_users), g['scores']),
+                                   rtol=1e-12)
+
+
+@pytest.mark.parametrize('shape', [(300, 1000, 128), (77, 5000, 64), (1000, 333, 32), (130, 26744, 128)])
+def test_tensor_core_eval_matches_exact_path(shape):
+    """Random fp32 weights: tensor-core scores within 1e-5 of the exact path, metrics within 1e-5,
+    top-k ids identical wherever the exact scores are separated by more than the split's error."""
+    import collie_b200 as cb
+    from collie_b200 import metrics as M
+    n_users, n_items, dim = shape
+    rng = np.random.default_rng(n_items)
+    tabs = tuple(torch.from_numpy(rng.normal(0, 1.0 / np.sqrt(dim), s).astype(np.float32)).cuda()
+                 for s in ((n_users, dim), (n_items, dim), (n_users, 1), (n_items, 1)))
+    tu = rng.integers(0, n_users, 6 * n_users)
+    ti = rng.integers(0, n_items, 6 * n_users)
+    coo = sp.coo_matrix((np.ones(len(tu)), (tu, ti)), shape=(n_users, n_items))
+    coo.sum_duplicates()
+    tile = np.arange(n_users)
+    indptr, items, nnz = M._targets_device(coo.tocsr(), tile, 'cuda')
+    users = torch.from_numpy(tile.astype(np.int32)).cuda()
+    k = 10
+    ex = M._eval_tile('cuda', n_users, n_items, k, indptr, items, {'topk', 'mapk', 'mrr'},
+                      tables=tabs, user_ids=users, precision=0)
+    tc = M._eval_tile('cuda', n_users, n_items, k, indptr, items, {'topk', 'mapk', 'mrr'},
+                      tables=tabs, user_ids=users, precision=1)
+    np.testing.assert_allclose(tc['topk_scores'].cpu().numpy(), ex['topk_scores'].cpu().numpy(),
+                               rtol=1e-5, atol=2e-5)
+    es, ei = ex['topk_scores'].cpu().numpy(), ex['topk_ids'].cpu().numpy()
+    ti_ = tc['topk_ids'].cpu().numpy()
+    gap = np.abs(np.diff(es, axis=1)).min(axis=1) if k > 1 else np.ones(n_users)
+    clear = gap > 2e-5          # rows whose exact top-k is separated by more than the split error
+    assert clear.mean() > 0.5
+    assert np.array_equal(ti_[clear][:, :k - 1], ei[clear][:, :k - 1])
+    for name in ('mapk', 'mrr'):
+        a = M._per_user(name, tc, nnz, n_items).mean().item()
+        b = M._per_user(name, ex, nnz, n_items).mean().item()
+        np.testing.assert_allclose(a, b, rtol=2e-3, atol=1e-6)
+    # through the public API
+    test = cb.Interactions(mat=coo, num_users=n_users, num_items=n_items, allow_missing_ids=True,
+                           check_num_negative_samples_is_valid=False,
+                           max_number_of_samples_to_consider=0)
+    model = cb.MatrixFactorizationModel(train=test, embedding_dim=dim, lr_scheduler_func=None).cuda()
+    with torch.no_grad():
+        for t, src in zip(_tables(model).values(), tabs):
+            t.copy_(src)
+    got = cb.evaluate_in_batches([cb.mapk, cb.mrr, cb.auc], test, model, k=k, verbose=False,
+                                 precision=1)
+    exp = cb.evaluate_in_batches([cb.mapk, cb.mrr, cb.auc], test, model, k=k, verbose=False)
+    np.testing.assert_allclose(got, exp, rtol=2e-3, atol=1e-6)
