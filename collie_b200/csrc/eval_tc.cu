@@ -7,7 +7,7 @@
 //
 // fp32 parity on bf16 tensor cores: every fp32 value x is split as hi = bf16(x), lo = bf16(x - hi)
 // and the GEMM runs over the concatenated K axis  A' = [Ah | Ah | Al],  B' = [Bh | Bl | Bh]
-// (K' = 3 D), i.e. S = Ah.Bh + Ah.Bl + Al.Bh with fp32 accumulation; the dropped Al.Bl term is
+// (K' = 3 D + 4 bias slots), i.e. S = Ah.Bh + Ah.Bl + Al.Bh with fp32 accumulation; the dropped Al.Bl term is
 // < 2^-16 relative. Values that are exactly representable in bf16 (the exact-arithmetic parity
 // fixture) give bit-exact scores.
 //
@@ -19,9 +19,10 @@
 //               instruction, two accumulators in TMEM (256 columns) so tile t+1 is being multiplied
 //               while tile t is ranked
 //   warp 2      TMEM allocation
-//   warps 4..7  epilogue: tcgen05.ld 32x32b (thread = user row), bias add, threshold test against
-//               the row's current k-th best, rare sorted insert into a per-row list in shared
-//               memory, MRR counter
+//   warps 4..7  epilogue: tcgen05.ld 32x32b (thread = user row); the biases are folded into the GEMM
+//               (four extra K slots), so the accumulator IS the score: a branch-free pass builds
+//               32-bit predicate masks per 32 columns (beats the row's k-th best / beats the best
+//               target), then a rare sorted insert into the row's list in shared memory
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -126,25 +127,35 @@ __device__ __forceinline__ void split_bf16(float x, __nv_bfloat16& hi, __nv_bflo
   lo = __float2bfloat16_rn(x - __bfloat162float(hi));
 }
 
-// rows of `src` (optionally gathered through `ids`) -> [hi | lo | hi] (items) or [hi | hi | lo]
-// (users) bf16 rows of length Kp (zero padded); rows >= n_rows are zero.
+// rows of `src` (optionally gathered through `ids`) -> bf16 rows of length Kp:
+//   items: [hi | lo | hi | 1, 1, bi_hi, bi_lo | 0...]   users: [hi | hi | lo | bu_hi, bu_lo, 1, 1 | 0...]
+// so the GEMM yields  <u, i> + bu + bi  directly (the biases are split like the rows). Rows
+// >= n_rows are zero.
 __global__ void __launch_bounds__(256)
-k_tc_split(const float* __restrict__ src, const int32_t* __restrict__ ids, int64_t row_offset,
-           int64_t n_rows, int64_t n_rows_pad, int D, int Kp, int users,
-           __nv_bfloat16* __restrict__ out) {
+k_tc_split(const float* __restrict__ src, const float* __restrict__ bias,
+           const int32_t* __restrict__ ids, int64_t row_offset, int64_t n_rows, int64_t n_rows_pad,
+           int D, int Kp, int users, __nv_bfloat16* __restrict__ out) {
   const int64_t total = n_rows_pad * (int64_t)Kp;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = i / Kp;
     const int c = (int)(i - r * Kp);
     __nv_bfloat16 v = __float2bfloat16_rn(0.f);
-    if (r < n_rows && c < 3 * D) {
-      const int seg = c / D, d = c - seg * D;
+    if (r < n_rows) {
       const int64_t row = ids ? (int64_t)ids[r] : row_offset + r;
-      __nv_bfloat16 hi, lo;
-      split_bf16(src[row * D + d], hi, lo);
-      const bool want_lo = users ? (seg == 2) : (seg == 1);
-      v = want_lo ? lo : hi;
+      if (c < 3 * D) {
+        const int seg = c / D, d = c - seg * D;
+        __nv_bfloat16 hi, lo;
+        split_bf16(src[row * D + d], hi, lo);
+        const bool want_lo = users ? (seg == 2) : (seg == 1);
+        v = want_lo ? lo : hi;
+      } else if (c < 3 * D + 4) {
+        const int q = c - 3 * D;
+        __nv_bfloat16 hi, lo;
+        split_bf16(bias[row], hi, lo);
+        const bool own = users ? (q < 2) : (q >= 2);     // own bias in two slots, 1.0 in the others
+        v = own ? ((q & 1) ? lo : hi) : __float2bfloat16_rn(1.f);
+      }
     }
     out[i] = v;
   }
@@ -181,8 +192,6 @@ k_tc_target_best(const float* __restrict__ U, const float* __restrict__ I,
 struct TcParams {
   int n_users, k, KB, n_tiles, tiles_per_split, n_splits, want_mrr;
   int64_t n_items, item_offset;
-  const float* bu_tile;  // [n_users_pad] user biases of the tile (gathered)
-  const float* bi;       // item biases (global ids)
   const float* best_s;   // MRR threshold per user (may be NULL)
   const int32_t* best_id;
   float* cand_s;         // [n_users_pad][n_splits][k]
@@ -196,13 +205,12 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   extern __shared__ unsigned char smem_raw[];
   // 128-byte-swizzled operand tiles need 1024-byte alignment
   unsigned char* smem = smem_raw + ((1024u - (s_addr(smem_raw) & 1023u)) & 1023u);
-  // carve-up: A' K-blocks | B' stages | per-row top-k lists | item-bias tiles | barriers
+  // carve-up: A' K-blocks | B' stages | per-row top-k lists | barriers
   unsigned char* sA = smem;
   unsigned char* sB = sA + (size_t)p.KB * TC_TILE_BYTES;
   float* s_top_s = reinterpret_cast<float*>(sB + (size_t)TC_STAGES * TC_TILE_BYTES);
   int* s_top_i = reinterpret_cast<int*>(s_top_s + TC_BM * (TC_MAXK + 1));
-  float* s_bi = reinterpret_cast<float*>(s_top_i + TC_BM * (TC_MAXK + 1));   // [2][TC_BN]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_bi + 2 * TC_BN);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_top_i + TC_BM * (TC_MAXK + 1));
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 16);
 
   const uint32_t bar_full = s_addr(&bars[0]);                 // [TC_STAGES]
@@ -287,55 +295,67 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ===================================================================== epilogue
     const int q = warp & 3;               // TMEM lane quarter this warp may read
     const int row = q * 32 + lane;        // user row inside the tile
-    const int et = threadIdx.x - 128;     // 0..127
     const bool valid = (m0 + row) < p.n_users;
-    const float b_user = valid ? p.bu_tile[m0 + row] : 0.f;
     const int K = p.k;
     float* ls = s_top_s + row * (TC_MAXK + 1);
     int* li = s_top_i + row * (TC_MAXK + 1);
     int have = 0;
-    float thr = -INFINITY;
+    float thr = -INFINITY;   // -inf until the list holds K entries: one compare covers both cases
     const bool mrr = p.want_mrr && valid;
-    const float best_s = mrr ? p.best_s[m0 + row] : 0.f;
+    const float best_s = mrr ? p.best_s[m0 + row] : INFINITY;
     const int best_id = mrr ? p.best_id[m0 + row] : -1;
     int before = 0;
 
     for (int t = 0; t < n_my; ++t) {
       const int acc = t & 1;
       const int64_t n0 = (int64_t)(tile_lo + t) * TC_BN;
-      {  // item biases of this tile -> shared memory (double buffered with the accumulator)
-        const int64_t id = n0 + et;
-        s_bi[acc * TC_BN + et] = id < p.n_items ? p.bi[p.item_offset + id] : 0.f;
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-      }
       mbar_wait(bar_tfull + 8 * acc, (t >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * TC_BN);
+      const int ncols = (int)min((int64_t)TC_BN, p.n_items - n0);   // < TC_BN only in the last tile
+      const int gid0 = (int)(p.item_offset + n0);
 #pragma unroll 1
       for (int c0 = 0; c0 < TC_BN; c0 += 32) {
         float v[32];
         tmem_ld32(taddr + c0, v);
         if (!valid) continue;
+        // branch-free pass: bit j of each mask = predicate of column c0 + j
+        uint32_t m_ins = 0, m_gt = 0, m_ge = 0;
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-          const int64_t id = n0 + c0 + j;
-          if (id >= p.n_items) break;
-          const float s = v[j] + b_user + s_bi[acc * TC_BN + c0 + j];
-          const int gid = (int)(p.item_offset + id);
-          // the threshold is the target's exact fp32 score; the target itself is excluded by id
-          if (mrr && gid != best_id && (s > best_s || (s == best_s && gid < best_id))) ++before;
-          if (have < K || s > thr) {
-            // sorted insert; ids only grow, so on equal scores the newcomer stays behind
-            int pos = have < K ? have : K - 1;
-            while (pos > 0 && s > ls[pos - 1]) {
-              ls[pos] = ls[pos - 1];
-              li[pos] = li[pos - 1];
-              --pos;
+          m_ins |= (v[j] > thr ? 1u : 0u) << j;
+          if (mrr) {
+            m_gt |= (v[j] > best_s ? 1u : 0u) << j;
+            m_ge |= (v[j] >= best_s ? 1u : 0u) << j;
+          }
+        }
+        const int left = ncols - c0;
+        const uint32_t m_rng = left >= 32 ? 0xffffffffu : (left > 0 ? ((1u << left) - 1u) : 0u);
+        if (mrr) {
+          // ties with the best target count when their id is smaller; the target itself never does
+          const int d = best_id - (gid0 + c0);      // columns with gid < best_id: j < d
+          const uint32_t m_idlt = d >= 32 ? 0xffffffffu : (d > 0 ? ((1u << d) - 1u) : 0u);
+          const uint32_t m_self = (d >= 0 && d < 32) ? (1u << d) : 0u;
+          before += __popc(m_gt & m_rng & ~m_self) + __popc((m_ge & ~m_gt) & m_rng & m_idlt);
+        }
+        m_ins &= m_rng;
+        if (m_ins) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            if (((m_ins >> j) & 1u) && v[j] > thr) {   // thr may have risen within the chunk
+              // sorted insert; ids only grow, so on equal scores the newcomer stays behind
+              const float sc = v[j];
+              int pos = have < K ? have : K - 1;
+              while (pos > 0 && sc > ls[pos - 1]) {
+                ls[pos] = ls[pos - 1];
+                li[pos] = li[pos - 1];
+                --pos;
+              }
+              ls[pos] = sc;
+              li[pos] = gid0 + c0 + j;
+              if (have < K) ++have;
+              if (have == K) thr = ls[K - 1];
             }
-            ls[pos] = s;
-            li[pos] = gid;
-            if (have < K) ++have;
-            if (have == K) thr = ls[K - 1];
           }
         }
       }
@@ -471,7 +491,7 @@ struct TcLayout {
 
 static TcLayout tc_layout(int64_t n_users, int64_t n_items, int D, int k) {
   TcLayout L;
-  L.Kp = (int)align_up((size_t)3 * D, TC_BK);
+  L.Kp = (int)align_up((size_t)3 * D + 4, TC_BK);   // + the bias slots
   L.KB = L.Kp / TC_BK;
   L.m_tiles = (int)((n_users + TC_BM - 1) / TC_BM);
   L.m_pad = (int64_t)L.m_tiles * TC_BM;
@@ -495,17 +515,11 @@ static TcLayout tc_layout(int64_t n_users, int64_t n_items, int D, int k) {
   return L;
 }
 
-bool eval_tc_supported(int D, int k) { return D >= 1 && 3 * D <= 6 * TC_BK && k >= 1 && k <= TC_MAXK; }
+bool eval_tc_supported(int D, int k) { return D >= 1 && D <= 128 && k >= 1 && k <= TC_MAXK; }
 
 size_t eval_tc_workspace_bytes(int64_t n_users, int64_t n_items, int D, int k) {
   if (!eval_tc_supported(D, k)) return 0;
   return tc_layout(n_users, n_items, D, k).total;
-}
-
-__global__ void k_tc_gather_bias(const float* bu, const int32_t* ids, int64_t n, int64_t n_pad,
-                                 float* out) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n_pad) out[i] = i < n ? bu[ids[i]] : 0.f;
 }
 
 int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
@@ -521,21 +535,17 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   char* base = (char*)a->workspace;
   __nv_bfloat16* Bp = (__nv_bfloat16*)(base + L.Bp);
   __nv_bfloat16* Ap = (__nv_bfloat16*)(base + L.Ap);
-  float* bu_tile = (float*)(base + L.bu);
   float* best_s = (float*)(base + L.best_s);
   int32_t* best_id = (int32_t*)(base + L.best_id);
   const int grid = num_sms() * 8;
 
   if (!a->reuse_item_prep) {
-    k_tc_split<<<grid, 256, 0, s>>>(a->I, nullptr, a->item_offset, a->num_items_shard,
+    k_tc_split<<<grid, 256, 0, s>>>(a->I, a->bi, nullptr, a->item_offset, a->num_items_shard,
                                     a->num_items_shard, a->D, L.Kp, 0, Bp);
     CMF_LAUNCH_CHECK();
   }
-  k_tc_split<<<grid, 256, 0, s>>>(a->U, a->user_ids, 0, a->n_users_tile, L.m_pad, a->D, L.Kp, 1, Ap);
-  CMF_LAUNCH_CHECK();
-  k_tc_gather_bias<<<(unsigned)((L.m_pad + 255) / 256), 256, 0, s>>>(a->bu, a->user_ids,
-                                                                     a->n_users_tile, L.m_pad,
-                                                                     bu_tile);
+  k_tc_split<<<grid, 256, 0, s>>>(a->U, a->bu, a->user_ids, 0, a->n_users_tile, L.m_pad, a->D,
+                                  L.Kp, 1, Ap);
   CMF_LAUNCH_CHECK();
   const bool mrr = a->want_mrr != 0;
   if (mrr) {
@@ -568,12 +578,12 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   p.n_users = (int)a->n_users_tile; p.k = a->k; p.KB = L.KB; p.n_tiles = L.n_tiles;
   p.tiles_per_split = L.tiles_per_split; p.n_splits = L.n_splits; p.want_mrr = mrr ? 1 : 0;
   p.n_items = a->num_items_shard; p.item_offset = a->item_offset;
-  p.bu_tile = bu_tile; p.bi = a->bi; p.best_s = best_s; p.best_id = best_id;
+  p.best_s = best_s; p.best_id = best_id;
   p.cand_s = (float*)(base + L.cand_s); p.cand_i = (int32_t*)(base + L.cand_i);
   p.cnt = (int32_t*)(base + L.cnt);
 
   const size_t smem = (size_t)L.KB * TC_TILE_BYTES + (size_t)TC_STAGES * TC_TILE_BYTES +
-                      2 * sizeof(float) * TC_BM * (TC_MAXK + 1) + 2 * sizeof(float) * TC_BN +
+                      2 * sizeof(float) * TC_BM * (TC_MAXK + 1) +
                       16 * sizeof(uint64_t) + 64 + 1024;
   CMF_CUDA(cudaFuncSetAttribute(k_tc_gemm_topk, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)smem));
