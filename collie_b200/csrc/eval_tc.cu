@@ -30,6 +30,8 @@
 
 namespace cmf {
 
+int g_tc_debug = 0;   // experiments only (cmf_set_tuning key 3): 1 = epilogue skips the ranking
+
 constexpr int TC_BM = 128;        // users per CTA
 constexpr int TC_BN = 128;        // items per MMA tile
 constexpr int TC_BK = 64;         // bf16 per K block = one 128-byte swizzle row
@@ -190,7 +192,7 @@ k_tc_target_best(const float* __restrict__ U, const float* __restrict__ I,
 
 // ---------------------------------------------------------------------------------- GEMM + top-k
 struct TcParams {
-  int n_users, k, KB, n_tiles, tiles_per_split, n_splits, want_mrr;
+  int n_users, k, KB, n_tiles, tiles_per_split, n_splits, want_mrr, debug;
   int64_t n_items, item_offset;
   const float* best_s;   // MRR threshold per user (may be NULL)
   const int32_t* best_id;
@@ -299,7 +301,7 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int K = p.k;
     float* ls = s_top_s + row * (TC_MAXK + 1);
     int* li = s_top_i + row * (TC_MAXK + 1);
-    int have = 0;
+    int have = 0, minpos = 0;
     float thr = -INFINITY;   // -inf until the list holds K entries: one compare covers both cases
     const bool mrr = p.want_mrr && valid;
     const float best_s = mrr ? p.best_s[m0 + row] : INFINITY;
@@ -318,19 +320,23 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int c0 = 0; c0 < TC_BN; c0 += 32) {
         float v[32];
         tmem_ld32(taddr + c0, v);
-        if (!valid) continue;
+        if (p.debug == 1) continue;
         // branch-free pass: bit j of each mask = predicate of column c0 + j
         uint32_t m_ins = 0, m_gt = 0, m_ge = 0;
+        if (mrr) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          m_ins |= (v[j] > thr ? 1u : 0u) << j;
-          if (mrr) {
+          for (int j = 0; j < 32; ++j) {
+            m_ins |= (v[j] > thr ? 1u : 0u) << j;
             m_gt |= (v[j] > best_s ? 1u : 0u) << j;
             m_ge |= (v[j] >= best_s ? 1u : 0u) << j;
           }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) m_ins |= (v[j] > thr ? 1u : 0u) << j;
         }
         const int left = ncols - c0;
-        const uint32_t m_rng = left >= 32 ? 0xffffffffu : (left > 0 ? ((1u << left) - 1u) : 0u);
+        const uint32_t m_rng = (!valid || left <= 0) ? 0u
+                               : (left >= 32 ? 0xffffffffu : ((1u << left) - 1u));
         if (mrr) {
           // ties with the best target count when their id is smaller; the target itself never does
           const int d = best_id - (gid0 + c0);      // columns with gid < best_id: j < d
@@ -339,22 +345,36 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           before += __popc(m_gt & m_rng & ~m_self) + __popc((m_ge & ~m_gt) & m_rng & m_idlt);
         }
         m_ins &= m_rng;
-        if (m_ins) {
+        if (__any_sync(0xffffffffu, m_ins != 0)) {
+          // lanes insert side by side, each its own next candidate: the chunk goes to local memory
+          // so that a lane can pick column j at run time
+          float vl[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            if (((m_ins >> j) & 1u) && v[j] > thr) {   // thr may have risen within the chunk
-              // sorted insert; ids only grow, so on equal scores the newcomer stays behind
-              const float sc = v[j];
-              int pos = have < K ? have : K - 1;
-              while (pos > 0 && sc > ls[pos - 1]) {
-                ls[pos] = ls[pos - 1];
-                li[pos] = li[pos - 1];
-                --pos;
+          for (int j = 0; j < 32; ++j) vl[j] = v[j];
+          while (__any_sync(0xffffffffu, m_ins != 0)) {
+            if (m_ins) {
+              const int j = __ffs(m_ins) - 1;
+              m_ins &= m_ins - 1;
+              const float sc = vl[j];
+              if (sc > thr) {     // thr may have risen within the chunk
+                // unsorted list: fill, then always replace the current minimum; equal scores never
+                // displace (ids only grow), and among equal minima the largest id goes first
+                const int pos = have < K ? have : minpos;
+                ls[pos] = sc;
+                li[pos] = gid0 + c0 + j;
+                if (have < K) ++have;
+                if (have == K) {
+                  float ms = ls[0];
+                  int mi = li[0], mp = 0;
+                  for (int e = 1; e < K; ++e) {
+                    const float es = ls[e];
+                    const int ei = li[e];
+                    if (es < ms || (es == ms && ei > mi)) { ms = es; mi = ei; mp = e; }
+                  }
+                  thr = ms;
+                  minpos = mp;
+                }
               }
-              ls[pos] = sc;
-              li[pos] = gid0 + c0 + j;
-              if (have < K) ++have;
-              if (have == K) thr = ls[K - 1];
             }
           }
         }
@@ -577,7 +597,7 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   TcParams p{};
   p.n_users = (int)a->n_users_tile; p.k = a->k; p.KB = L.KB; p.n_tiles = L.n_tiles;
   p.tiles_per_split = L.tiles_per_split; p.n_splits = L.n_splits; p.want_mrr = mrr ? 1 : 0;
-  p.n_items = a->num_items_shard; p.item_offset = a->item_offset;
+  p.n_items = a->num_items_shard; p.item_offset = a->item_offset; p.debug = g_tc_debug;
   p.best_s = best_s; p.best_id = best_id;
   p.cand_s = (float*)(base + L.cand_s); p.cand_i = (int32_t*)(base + L.cand_i);
   p.cnt = (int32_t*)(base + L.cnt);

@@ -26,6 +26,8 @@
 
 namespace cmf {
 
+extern int g_tc_debug;
+
 struct WsLayout {
   // persistent (zero between steps; the kernels restore the invariant)
   size_t item_flag, user_flag, GI, gbi, GU, gbu, persistent_end;
@@ -509,6 +511,11 @@ extern "C" int cmf_set_tuning(int32_t key, int32_t value) {
   if (key == 1) {
     CMF_REQUIRE(value == 8 || value == 16 || value == 32, "cmf_set_tuning: group width %d", value);
     return g_max_group.exchange(value);
+  }
+  if (key == 3) {
+    const int prev = g_tc_debug;
+    g_tc_debug = value;
+    return prev;
   }
   if (key == 2) {
     CMF_REQUIRE(value >= 0 && value <= 2, "cmf_set_tuning: kernel version %d", value);

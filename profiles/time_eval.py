@@ -23,6 +23,9 @@ coo = sp.coo_matrix((np.ones(len(tu)), (tu, ti)), shape=(n_users, n_items))
 coo.sum_duplicates()
 indptr, items, nnz = M._targets_device(coo.tocsr(), np.arange(nt), 'cuda')
 users = torch.arange(nt, dtype=torch.int32, device='cuda')
+import collie_b200._abi as _abi
+if len(sys.argv) > 2:
+    _abi.lib().cmf_set_tuning(3, int(sys.argv[2]))
 for prec, want, tile in ((1, {'mapk'}, nt), (1, {'mapk', 'mrr'}, nt), (0, {'mapk'}, 256),
                          (0, {'mapk', 'mrr', 'auc'}, 256)):
     ws = None
