@@ -128,6 +128,9 @@ class ShardedMatrixFactorization(object):
 
     def _workspace_views(self):
         m, h = self.model, self.model.hparams
+        cached = getattr(self, '_views', None)
+        if cached is not None and cached[0] == m._workspace.data_ptr():
+            return cached[1]
         C = _abi.C
         GI, gbi, flag = C.c_void_p(), C.c_void_p(), C.c_void_p()
         _abi.check(_abi.lib().cmf_train_workspace_items(
@@ -139,8 +142,10 @@ class ShardedMatrixFactorization(object):
         def view(p, dtype, count, shape):
             off = p.value - base
             return m._workspace[off:off + count * 4].view(dtype).view(shape)
-        return (view(GI, torch.float32, n * D, (n, D)), view(gbi, torch.float32, n, (n,)),
-                view(flag, torch.int32, n, (n,)))
+        views = (view(GI, torch.float32, n * D, (n, D)), view(gbi, torch.float32, n, (n,)),
+                 view(flag, torch.int32, n, (n,)))
+        self._views = (base, views)
+        return views
 
     def train_step(self, batch, optimizers, interactions=None, epoch=0, global_batch=None,
                    reduce_loss=True):
