@@ -34,6 +34,26 @@ def _targets_device(targets: csr_matrix, user_ids, device):
             torch.from_numpy(np.diff(sub.indptr).astype(np.int64)).to(device))
 
 
+def _targets_all_users_device(targets: csr_matrix, test_users, device):
+    """Same as ``_targets_device(targets, test_users, ...)`` when ``test_users`` are exactly the rows
+    of ``targets`` that hold entries: dropping the empty rows of a CSR leaves ``indices`` as it is,
+    so no row gather is needed on the host."""
+    sub = targets
+    if not sub.has_canonical_format:
+        sub = sub.copy()
+        sub.sum_duplicates()
+    if sub.nnz and (sub.data <= 0).any():
+        return _targets_device(targets, test_users, device)
+    counts = np.diff(sub.indptr)[np.asarray(test_users)]
+    if int(counts.sum()) != sub.nnz:
+        return _targets_device(targets, test_users, device)
+    indptr = np.zeros(len(counts) + 1, dtype=np.int64)
+    np.cumsum(counts, out=indptr[1:])
+    return (torch.from_numpy(indptr).to(device),
+            torch.from_numpy(sub.indices.astype(np.int32, copy=False)).to(device),
+            torch.from_numpy(counts.astype(np.int64)).to(device))
+
+
 def _eval_tile(device, n_users, n_items, k, indptr, tgt_items, want, tables=None, user_ids=None,
                scores=None, precision=0, workspace=None, reuse_item_prep=False):
     """One ``cmf_eval_tile`` call; returns dict of per-user device tensors."""
@@ -182,7 +202,7 @@ def evaluate_in_batches(metric_list, test_interactions, model, k=10, batch_size=
         if 'mapk' in names:
             _check_k(k, n_items)
         tables = _model_tables(model)
-        indptr, tgt_items, nnz = _targets_device(targets, test_users, device)
+        indptr, tgt_items, nnz = _targets_all_users_device(targets, test_users, device)
         users_dev = torch.from_numpy(test_users.astype(np.int32)).to(device)
         D = tables[0].shape[1]
         # tensor-core route for what it supports (top-k / MAP / MRR); AUC stays on the exact path
