@@ -11,18 +11,20 @@
 // < 2^-16 relative. Values that are exactly representable in bf16 (the exact-arithmetic parity
 // fixture) give bit-exact scores.
 //
-// One CTA = one 128-user tile x one contiguous range of 128-item tiles (the item range is split so
-// that about one CTA per SM is in flight); the CTAs of one user tile leave their top-k candidates
-// and counters in scratch and k_tc_merge combines them in canonical order (score desc, id asc).
+// The (128-user tile, 128-item tile) pairs are cut into equal contiguous chunks, one per CTA, one
+// CTA per SM: a CTA walks its chunk as segments that each lie inside one user tile, leaves every
+// segment's top-k candidates and counters in scratch, and k_tc_merge combines the segments of a
+// user in canonical order (score desc, id asc).
 //   warp 0      TMA producer: A' once (resident), then B' K-blocks through a 4-stage mbarrier ring
 //   warp 1      MMA issuer: tcgen05.mma.cta_group::1.kind::f16, M = 128, N = 128, K = 16 per
 //               instruction, two accumulators in TMEM (256 columns) so tile t+1 is being multiplied
 //               while tile t is ranked
 //   warp 2      TMEM allocation
-//   warps 4..7  epilogue: tcgen05.ld 32x32b (thread = user row); the biases are folded into the GEMM
-//               (four extra K slots), so the accumulator IS the score: a branch-free pass builds
-//               32-bit predicate masks per 32 columns (beats the row's k-th best / beats the best
-//               target), then a rare sorted insert into the row's list in shared memory
+//   warps 4..11 epilogue, two warps per scheduler (each takes 64 of a tile's 128 columns):
+//               tcgen05.ld 32x32b (thread = user row); the biases are folded into the GEMM (four
+//               extra K slots), so the accumulator IS the score: a branch-free pass builds 32-bit
+//               predicate masks per 32 columns (beats the row's k-th best / beats the best
+//               target), then lane-parallel inserts into an unsorted per-row list in shared memory
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -36,7 +38,7 @@ constexpr int TC_BM = 128;        // users per CTA
 constexpr int TC_BN = 128;        // items per MMA tile
 constexpr int TC_BK = 64;         // bf16 per K block = one 128-byte swizzle row
 constexpr int TC_STAGES = 4;
-constexpr int TC_MAXK = 32;       // top-k list length supported by the epilogue
+constexpr int TC_MAXK = 16;       // top-k list length supported by the epilogue
 constexpr int TC_TILE_BYTES = TC_BN * TC_BK * 2;   // 16 KB: one operand K-block
 
 // ---------------------------------------------------------------------------------- PTX wrappers
@@ -123,6 +125,20 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t addr) {
 constexpr uint32_t kIdescBf16 =
     (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
 
+// v[j] for a run-time j without spilling v to local memory (whose traffic would compete with the
+// MMA's operand reads for the shared-memory pipe): a 5-level select tree, 31 selects
+__device__ __forceinline__ float pick32(const float (&v)[32], int j) {
+  float a[16], b[8], c[4];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) a[i] = (j & 1) ? v[2 * i + 1] : v[2 * i];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) b[i] = (j & 2) ? a[2 * i + 1] : a[2 * i];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) c[i] = (j & 4) ? b[2 * i + 1] : b[2 * i];
+  const float d0 = (j & 8) ? c[1] : c[0], d1 = (j & 8) ? c[3] : c[2];
+  return (j & 16) ? d1 : d0;
+}
+
 // ---------------------------------------------------------------------------------- prep kernels
 __device__ __forceinline__ void split_bf16(float x, __nv_bfloat16& hi, __nv_bfloat16& lo) {
   hi = __float2bfloat16_rn(x);
@@ -192,46 +208,55 @@ k_tc_target_best(const float* __restrict__ U, const float* __restrict__ I,
 
 // ---------------------------------------------------------------------------------- GEMM + top-k
 struct TcParams {
-  int n_users, k, KB, n_tiles, tiles_per_split, n_splits, want_mrr, debug;
+  int n_users, k, KB, n_tiles, m_tiles, n_slots, want_mrr, debug;
+  int64_t chunk, total_work;   // tiles per CTA / tiles in all (m_tiles * n_tiles)
   int64_t n_items, item_offset;
   const float* best_s;   // MRR threshold per user (may be NULL)
   const int32_t* best_id;
-  float* cand_s;         // [n_users_pad][n_splits][k]
+  float* cand_s;         // [n_users_pad][n_slots][k]
   int32_t* cand_i;
-  int32_t* cnt;          // [n_users_pad][n_splits] items ranked before the best target
+  int32_t* cnt;          // [n_users_pad][n_slots] items ranked before the best target
 };
 
-__global__ void __launch_bounds__(256, 1)
+// The (user tile, item tile) pairs are numbered m * n_tiles + n and cut into equal contiguous
+// chunks, one per CTA (about one CTA per SM, whatever the tile counts): a CTA walks its chunk as
+// one or more segments, each inside a single user tile. Slot of a segment inside its user tile:
+__device__ __forceinline__ int tc_slot(int64_t lin_start, int m, int n_tiles, int64_t chunk) {
+  return (int)(lin_start / chunk - ((int64_t)m * n_tiles) / chunk);
+}
+
+constexpr int TC_EPI_WARPS = 8;   // two per scheduler; each pair splits a tile's columns in halves
+constexpr int TC_THREADS = 128 + 32 * TC_EPI_WARPS;
+
+template <int KL>   // per-row list length kept in registers, >= k
+__global__ void __launch_bounds__(TC_THREADS, 1)
 k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const TcParams p) {
   extern __shared__ unsigned char smem_raw[];
   // 128-byte-swizzled operand tiles need 1024-byte alignment
   unsigned char* smem = smem_raw + ((1024u - (s_addr(smem_raw) & 1023u)) & 1023u);
-  // carve-up: A' K-blocks | B' stages | per-row top-k lists | barriers
+  // carve-up: A' K-blocks | B' stages | barriers
   unsigned char* sA = smem;
   unsigned char* sB = sA + (size_t)p.KB * TC_TILE_BYTES;
-  float* s_top_s = reinterpret_cast<float*>(sB + (size_t)TC_STAGES * TC_TILE_BYTES);
-  int* s_top_i = reinterpret_cast<int*>(s_top_s + TC_BM * (TC_MAXK + 1));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_top_i + TC_BM * (TC_MAXK + 1));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + (size_t)TC_STAGES * TC_TILE_BYTES);
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 16);
 
   const uint32_t bar_full = s_addr(&bars[0]);                 // [TC_STAGES]
   const uint32_t bar_empty = s_addr(&bars[TC_STAGES]);        // [TC_STAGES]
-  const uint32_t bar_a = s_addr(&bars[2 * TC_STAGES]);
-  const uint32_t bar_tfull = s_addr(&bars[2 * TC_STAGES + 1]);   // [2]
-  const uint32_t bar_tempty = s_addr(&bars[2 * TC_STAGES + 3]);  // [2]
+  const uint32_t bar_a = s_addr(&bars[2 * TC_STAGES]);           // A' of the segment has landed
+  const uint32_t bar_afree = s_addr(&bars[2 * TC_STAGES + 1]);   // A' is no longer read
+  const uint32_t bar_tfull = s_addr(&bars[2 * TC_STAGES + 2]);   // [2]
+  const uint32_t bar_tempty = s_addr(&bars[2 * TC_STAGES + 4]);  // [2]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.y * TC_BM;
-  const int split = blockIdx.x;
-  const int tile_lo = split * p.tiles_per_split;
-  const int tile_hi = min(p.n_tiles, tile_lo + p.tiles_per_split);
-  const int n_my = max(0, tile_hi - tile_lo);
+  const int64_t w_lo = (int64_t)blockIdx.x * p.chunk;
+  const int64_t w_hi = min(p.total_work, w_lo + p.chunk);
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < TC_STAGES; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); }
     mbar_init(bar_a, 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(bar_tfull + 8 * i, 1); mbar_init(bar_tempty + 8 * i, 4); }
+    mbar_init(bar_afree, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_tfull + 8 * i, 1); mbar_init(bar_tempty + 8 * i, TC_EPI_WARPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -248,149 +273,163 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   if (warp == 0) {
     // ===================================================================== TMA producer
-    if (lane == 0 && n_my > 0) {
+    if (lane == 0 && w_lo < w_hi) {
       asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
-      mbar_expect_tx(bar_a, (uint32_t)p.KB * TC_TILE_BYTES);
-      for (int kb = 0; kb < p.KB; ++kb)
-        tma_load_2d(s_addr(sA + (size_t)kb * TC_TILE_BYTES), &tmA, kb * TC_BK, m0, bar_a);
-      int stage = 0;
+      int stage = 0, seg = 0;
       uint32_t phase = 0;
-      for (int t = 0; t < n_my; ++t) {
-        const int n0 = (tile_lo + t) * TC_BN;
-        for (int kb = 0; kb < p.KB; ++kb) {
-          mbar_wait(bar_empty + 8 * stage, phase ^ 1);
-          mbar_expect_tx(bar_full + 8 * stage, TC_TILE_BYTES);
-          tma_load_2d(s_addr(sB + (size_t)stage * TC_TILE_BYTES), &tmB, kb * TC_BK, n0,
-                      bar_full + 8 * stage);
-          if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+      for (int64_t w = w_lo; w < w_hi; ++seg) {
+        const int m = (int)(w / p.n_tiles);
+        const int64_t seg_hi = min(w_hi, (int64_t)(m + 1) * p.n_tiles);
+        if (seg > 0) mbar_wait(bar_afree, (seg - 1) & 1);   // the previous segment's MMAs are done
+        mbar_expect_tx(bar_a, (uint32_t)p.KB * TC_TILE_BYTES);
+        for (int kb = 0; kb < p.KB; ++kb)
+          tma_load_2d(s_addr(sA + (size_t)kb * TC_TILE_BYTES), &tmA, kb * TC_BK, m * TC_BM, bar_a);
+        for (; w < seg_hi; ++w) {
+          const int n0 = (int)(w - (int64_t)m * p.n_tiles) * TC_BN;
+          for (int kb = 0; kb < p.KB; ++kb) {
+            mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+            mbar_expect_tx(bar_full + 8 * stage, TC_TILE_BYTES);
+            tma_load_2d(s_addr(sB + (size_t)stage * TC_TILE_BYTES), &tmB, kb * TC_BK, n0,
+                        bar_full + 8 * stage);
+            if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+          }
         }
       }
     }
   } else if (warp == 1) {
     // ===================================================================== MMA issuer
-    if (lane == 0 && n_my > 0) {
-      mbar_wait(bar_a, 0);
-      tc_fence_after();
-      int stage = 0;
+    if (lane == 0 && w_lo < w_hi) {
+      int stage = 0, seg = 0, t = 0;
       uint32_t phase = 0;
-      for (int t = 0; t < n_my; ++t) {
-        const int acc = t & 1;
-        mbar_wait(bar_tempty + 8 * acc, ((t >> 1) & 1) ^ 1);   // the epilogue drained this buffer
+      for (int64_t w = w_lo; w < w_hi; ++seg) {
+        const int m = (int)(w / p.n_tiles);
+        const int64_t seg_hi = min(w_hi, (int64_t)(m + 1) * p.n_tiles);
+        mbar_wait(bar_a, seg & 1);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * TC_BN);
-        for (int kb = 0; kb < p.KB; ++kb) {
-          mbar_wait(bar_full + 8 * stage, phase);
+        for (; w < seg_hi; ++w, ++t) {
+          const int acc = t & 1;
+          mbar_wait(bar_tempty + 8 * acc, ((t >> 1) & 1) ^ 1);   // the epilogue drained this buffer
           tc_fence_after();
-          const uint64_t da = smem_desc_sw128(s_addr(sA + (size_t)kb * TC_TILE_BYTES));
-          const uint64_t db = smem_desc_sw128(s_addr(sB + (size_t)stage * TC_TILE_BYTES));
+          const uint32_t d_tmem = tmem_base + (uint32_t)(acc * TC_BN);
+          for (int kb = 0; kb < p.KB; ++kb) {
+            mbar_wait(bar_full + 8 * stage, phase);
+            tc_fence_after();
+            const uint64_t da = smem_desc_sw128(s_addr(sA + (size_t)kb * TC_TILE_BYTES));
+            const uint64_t db = smem_desc_sw128(s_addr(sB + (size_t)stage * TC_TILE_BYTES));
 #pragma unroll
-          for (int j = 0; j < TC_BK / 16; ++j)   // +32 bytes (2 x 16 B) per K = 16 step
-            umma_bf16(d_tmem, da + 2 * j, db + 2 * j, kIdescBf16, (kb | j) != 0);
-          umma_commit(bar_empty + 8 * stage);     // frees the stage when these MMAs are done
-          if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+            for (int j = 0; j < TC_BK / 16; ++j)   // +32 bytes (2 x 16 B) per K = 16 step
+              umma_bf16(d_tmem, da + 2 * j, db + 2 * j, kIdescBf16, (kb | j) != 0);
+            umma_commit(bar_empty + 8 * stage);     // frees the stage when these MMAs are done
+            if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+          }
+          umma_commit(bar_tfull + 8 * acc);         // accumulator complete -> epilogue
         }
-        umma_commit(bar_tfull + 8 * acc);         // accumulator complete -> epilogue
+        umma_commit(bar_afree);                     // A' may be overwritten by the next segment
       }
     }
   } else if (warp >= 4) {
     // ===================================================================== epilogue
     const int q = warp & 3;               // TMEM lane quarter this warp may read
+    const int half = (warp - 4) >> 2;     // which 64 columns of every 128-column tile
     const int row = q * 32 + lane;        // user row inside the tile
-    const bool valid = (m0 + row) < p.n_users;
-    const int K = p.k;
-    float* ls = s_top_s + row * (TC_MAXK + 1);
-    int* li = s_top_i + row * (TC_MAXK + 1);
-    int have = 0, minpos = 0;
-    float thr = -INFINITY;   // -inf until the list holds K entries: one compare covers both cases
-    const bool mrr = p.want_mrr && valid;
-    const float best_s = mrr ? p.best_s[m0 + row] : INFINITY;
-    const int best_id = mrr ? p.best_id[m0 + row] : -1;
-    int before = 0;
+    int t = 0;
+    for (int64_t w = w_lo; w < w_hi;) {
+      const int m = (int)(w / p.n_tiles);
+      const int64_t seg_hi = min(w_hi, (int64_t)(m + 1) * p.n_tiles);
+      const int slot = tc_slot(w, m, p.n_tiles, p.chunk) * 2 + half;
+      const int urow = m * TC_BM + row;
+      const bool valid = urow < p.n_users;
+      // the row's best KL so far, sorted (score desc, id asc), in registers; thr = the last one
+      float ls[KL];
+      int li[KL];
+#pragma unroll
+      for (int e = 0; e < KL; ++e) { ls[e] = -INFINITY; li[e] = -1; }
+      float thr = -INFINITY;
+      const bool mrr = p.want_mrr && valid;
+      const float best_s = mrr ? p.best_s[urow] : INFINITY;
+      const int best_id = mrr ? p.best_id[urow] : -1;
+      int before = 0;
 
-    for (int t = 0; t < n_my; ++t) {
-      const int acc = t & 1;
-      const int64_t n0 = (int64_t)(tile_lo + t) * TC_BN;
-      mbar_wait(bar_tfull + 8 * acc, (t >> 1) & 1);
-      tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * TC_BN);
-      const int ncols = (int)min((int64_t)TC_BN, p.n_items - n0);   // < TC_BN only in the last tile
-      const int gid0 = (int)(p.item_offset + n0);
+      for (; w < seg_hi; ++w, ++t) {
+        const int acc = t & 1;
+        const int64_t n0 = (w - (int64_t)m * p.n_tiles) * TC_BN;
+        mbar_wait(bar_tfull + 8 * acc, (t >> 1) & 1);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * TC_BN);
+        const int ncols = (int)min((int64_t)TC_BN, p.n_items - n0);   // < TC_BN only in the last tile
+        const int gid0 = (int)(p.item_offset + n0);
 #pragma unroll 1
-      for (int c0 = 0; c0 < TC_BN; c0 += 32) {
-        float v[32];
-        tmem_ld32(taddr + c0, v);
-        if (p.debug == 1) continue;
-        // branch-free pass: bit j of each mask = predicate of column c0 + j
-        uint32_t m_ins = 0, m_gt = 0, m_ge = 0;
-        if (mrr) {
+        for (int c0 = half * 64; c0 < half * 64 + 64; c0 += 32) {
+          float v[32];
+          tmem_ld32(taddr + c0, v);
+          if (p.debug == 1) continue;
+          // branch-free pass: bit j of each mask = predicate of column c0 + j
+          uint32_t m_ins = 0, m_gt = 0, m_ge = 0;
+          if (mrr) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            m_ins |= (v[j] > thr ? 1u : 0u) << j;
-            m_gt |= (v[j] > best_s ? 1u : 0u) << j;
-            m_ge |= (v[j] >= best_s ? 1u : 0u) << j;
+            for (int j = 0; j < 32; ++j) {
+              m_ins |= (v[j] > thr ? 1u : 0u) << j;
+              m_gt |= (v[j] > best_s ? 1u : 0u) << j;
+              m_ge |= (v[j] >= best_s ? 1u : 0u) << j;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) m_ins |= (v[j] > thr ? 1u : 0u) << j;
           }
-        } else {
+          const int left = ncols - c0;
+          const uint32_t m_rng = (!valid || left <= 0) ? 0u
+                                 : (left >= 32 ? 0xffffffffu : ((1u << left) - 1u));
+          if (mrr) {
+            // ties with the best target count when their id is smaller; the target never does
+            const int d = best_id - (gid0 + c0);      // columns with gid < best_id: j < d
+            const uint32_t m_idlt = d >= 32 ? 0xffffffffu : (d > 0 ? ((1u << d) - 1u) : 0u);
+            const uint32_t m_self = (d >= 0 && d < 32) ? (1u << d) : 0u;
+            before += __popc(m_gt & m_rng & ~m_self) + __popc((m_ge & ~m_gt) & m_rng & m_idlt);
+          }
+          m_ins &= m_rng;
+          if (__any_sync(0xffffffffu, m_ins != 0)) {
+            // lanes insert side by side, each its own next candidate (column j differs per lane)
+            while (__any_sync(0xffffffffu, m_ins != 0)) {
+              if (m_ins) {
+                const int j = __ffs(m_ins) - 1;
+                m_ins &= m_ins - 1;
+                const float sc = pick32(v, j);
+                if (sc > thr) {     // thr may have risen within the chunk
+                  // sorted insert; an equal score stays behind the entries already there (ids
+                  // only grow along a segment), which is the canonical order
+                  float cs = sc;
+                  int ci = gid0 + c0 + j;
+                  bool up = false;   // sticky: below the insertion point everything shifts down
 #pragma unroll
-          for (int j = 0; j < 32; ++j) m_ins |= (v[j] > thr ? 1u : 0u) << j;
-        }
-        const int left = ncols - c0;
-        const uint32_t m_rng = (!valid || left <= 0) ? 0u
-                               : (left >= 32 ? 0xffffffffu : ((1u << left) - 1u));
-        if (mrr) {
-          // ties with the best target count when their id is smaller; the target itself never does
-          const int d = best_id - (gid0 + c0);      // columns with gid < best_id: j < d
-          const uint32_t m_idlt = d >= 32 ? 0xffffffffu : (d > 0 ? ((1u << d) - 1u) : 0u);
-          const uint32_t m_self = (d >= 0 && d < 32) ? (1u << d) : 0u;
-          before += __popc(m_gt & m_rng & ~m_self) + __popc((m_ge & ~m_gt) & m_rng & m_idlt);
-        }
-        m_ins &= m_rng;
-        if (__any_sync(0xffffffffu, m_ins != 0)) {
-          // lanes insert side by side, each its own next candidate: the chunk goes to local memory
-          // so that a lane can pick column j at run time
-          float vl[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) vl[j] = v[j];
-          while (__any_sync(0xffffffffu, m_ins != 0)) {
-            if (m_ins) {
-              const int j = __ffs(m_ins) - 1;
-              m_ins &= m_ins - 1;
-              const float sc = vl[j];
-              if (sc > thr) {     // thr may have risen within the chunk
-                // unsorted list: fill, then always replace the current minimum; equal scores never
-                // displace (ids only grow), and among equal minima the largest id goes first
-                const int pos = have < K ? have : minpos;
-                ls[pos] = sc;
-                li[pos] = gid0 + c0 + j;
-                if (have < K) ++have;
-                if (have == K) {
-                  float ms = ls[0];
-                  int mi = li[0], mp = 0;
-                  for (int e = 1; e < K; ++e) {
-                    const float es = ls[e];
-                    const int ei = li[e];
-                    if (es < ms || (es == ms && ei > mi)) { ms = es; mi = ei; mp = e; }
+                  for (int e = 0; e < KL; ++e) {
+                    up = up || cs > ls[e];
+                    const float os = ls[e];
+                    const int oi = li[e];
+                    ls[e] = up ? cs : os;
+                    li[e] = up ? ci : oi;
+                    cs = up ? os : cs;
+                    ci = up ? oi : ci;
                   }
-                  thr = ms;
-                  minpos = mp;
+                  thr = ls[KL - 1];
                 }
               }
             }
           }
         }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
-    }
-    if (valid) {
-      float* cs = p.cand_s + ((int64_t)(m0 + row) * p.n_splits + split) * K;
-      int32_t* ci = p.cand_i + ((int64_t)(m0 + row) * p.n_splits + split) * K;
-      for (int j = 0; j < K; ++j) {
-        cs[j] = j < have ? ls[j] : -INFINITY;
-        ci[j] = j < have ? li[j] : -1;
+      if (valid) {
+        const int K = p.k;
+        float* cs = p.cand_s + ((int64_t)urow * p.n_slots + slot) * K;
+        int32_t* ci = p.cand_i + ((int64_t)urow * p.n_slots + slot) * K;
+#pragma unroll
+        for (int j = 0; j < KL; ++j)
+          if (j < K) { cs[j] = ls[j]; ci[j] = li[j]; }
+        if (p.cnt) p.cnt[(int64_t)urow * p.n_slots + slot] = before;
       }
-      if (p.cnt) p.cnt[(int64_t)(m0 + row) * p.n_splits + split] = before;
     }
   }
 
@@ -504,8 +543,8 @@ static int make_map(CUtensorMap* map, void* base, int64_t rows, int Kp) {
 }
 
 struct TcLayout {
-  int Kp, KB, m_tiles, n_tiles, n_splits, tiles_per_split;
-  int64_t m_pad;
+  int Kp, KB, m_tiles, n_tiles, n_ctas, n_slots;
+  int64_t m_pad, chunk, total_work;
   size_t Bp, Ap, bu, best_s, best_id, cand_s, cand_i, cnt, total;
 };
 
@@ -516,11 +555,14 @@ static TcLayout tc_layout(int64_t n_users, int64_t n_items, int D, int k) {
   L.m_tiles = (int)((n_users + TC_BM - 1) / TC_BM);
   L.m_pad = (int64_t)L.m_tiles * TC_BM;
   L.n_tiles = (int)((n_items + TC_BN - 1) / TC_BN);
-  int want = (num_sms() + L.m_tiles - 1) / L.m_tiles;   // about one CTA per SM
-  if (want > L.n_tiles) want = L.n_tiles;
-  if (want < 1) want = 1;
-  L.tiles_per_split = (L.n_tiles + want - 1) / want;
-  L.n_splits = (L.n_tiles + L.tiles_per_split - 1) / L.tiles_per_split;
+  // equal contiguous chunks of the (user tile, item tile) pairs, one per CTA, one CTA per SM
+  L.total_work = (int64_t)L.m_tiles * L.n_tiles;
+  int64_t ctas = num_sms();
+  if (ctas > L.total_work) ctas = L.total_work;
+  L.chunk = (L.total_work + ctas - 1) / ctas;
+  L.n_ctas = (int)((L.total_work + L.chunk - 1) / L.chunk);
+  // segments a user tile can be cut into (x 2: the epilogue keeps one list per column half)
+  L.n_slots = 2 * (int)((L.n_tiles + L.chunk - 1) / L.chunk + 1);
   size_t o = 0;
   auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes, 1024); return at; };
   L.Bp = take((size_t)n_items * L.Kp * 2);
@@ -528,9 +570,9 @@ static TcLayout tc_layout(int64_t n_users, int64_t n_items, int D, int k) {
   L.bu = take(sizeof(float) * L.m_pad);
   L.best_s = take(sizeof(float) * L.m_pad);
   L.best_id = take(sizeof(int32_t) * L.m_pad);
-  L.cand_s = take(sizeof(float) * L.m_pad * L.n_splits * k);
-  L.cand_i = take(sizeof(int32_t) * L.m_pad * L.n_splits * k);
-  L.cnt = take(sizeof(int32_t) * L.m_pad * L.n_splits);
+  L.cand_s = take(sizeof(float) * L.m_pad * L.n_slots * k);
+  L.cand_i = take(sizeof(int32_t) * L.m_pad * L.n_slots * k);
+  L.cnt = take(sizeof(int32_t) * L.m_pad * L.n_slots);
   L.total = o;
   return L;
 }
@@ -596,23 +638,34 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
 
   TcParams p{};
   p.n_users = (int)a->n_users_tile; p.k = a->k; p.KB = L.KB; p.n_tiles = L.n_tiles;
-  p.tiles_per_split = L.tiles_per_split; p.n_splits = L.n_splits; p.want_mrr = mrr ? 1 : 0;
+  p.m_tiles = L.m_tiles; p.n_slots = L.n_slots; p.chunk = L.chunk; p.total_work = L.total_work;
+  p.want_mrr = mrr ? 1 : 0;
   p.n_items = a->num_items_shard; p.item_offset = a->item_offset; p.debug = g_tc_debug;
   p.best_s = best_s; p.best_id = best_id;
   p.cand_s = (float*)(base + L.cand_s); p.cand_i = (int32_t*)(base + L.cand_i);
   p.cnt = (int32_t*)(base + L.cnt);
 
   const size_t smem = (size_t)L.KB * TC_TILE_BYTES + (size_t)TC_STAGES * TC_TILE_BYTES +
-                      2 * sizeof(float) * TC_BM * (TC_MAXK + 1) +
                       16 * sizeof(uint64_t) + 64 + 1024;
-  CMF_CUDA(cudaFuncSetAttribute(k_tc_gemm_topk, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)smem));
-  dim3 gridg((unsigned)L.n_splits, (unsigned)L.m_tiles);
-  k_tc_gemm_topk<<<gridg, 256, smem, s>>>(tmA, tmB, p);
+  // slots a user tile does not use stay empty
+  CMF_CUDA(cudaMemsetAsync(p.cand_i, 0xFF, sizeof(int32_t) * L.m_pad * L.n_slots * a->k, s));
+  CMF_CUDA(cudaMemsetAsync(p.cnt, 0, sizeof(int32_t) * L.m_pad * L.n_slots, s));
+  // list length: the smallest instantiation that holds k
+#define CMF_TC_LAUNCH(KL)                                                                        \
+  do {                                                                                           \
+    CMF_CUDA(cudaFuncSetAttribute(k_tc_gemm_topk<KL>,                                            \
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));      \
+    k_tc_gemm_topk<KL><<<(unsigned)L.n_ctas, TC_THREADS, smem, s>>>(tmA, tmB, p);                \
+  } while (0)
+  if (a->k <= 4) CMF_TC_LAUNCH(4);
+  else if (a->k <= 8) CMF_TC_LAUNCH(8);
+  else if (a->k <= 10) CMF_TC_LAUNCH(10);
+  else CMF_TC_LAUNCH(16);
+#undef CMF_TC_LAUNCH
   CMF_LAUNCH_CHECK();
 
   k_tc_merge<<<(unsigned)((a->n_users_tile * 32 + 255) / 256), 256, 0, s>>>(
-      p.cand_s, p.cand_i, mrr ? p.cnt : nullptr, L.n_splits, a->k, a->n_users_tile, a->tgt_indptr,
+      p.cand_s, p.cand_i, mrr ? p.cnt : nullptr, L.n_slots, a->k, a->n_users_tile, a->tgt_indptr,
       a->tgt_items, mrr ? best_id : nullptr, a->topk_ids, a->topk_scores, a->ap,
       a->n_before_best);
   CMF_LAUNCH_CHECK();

@@ -206,9 +206,9 @@ def evaluate_in_batches(metric_list, test_interactions, model, k=10, batch_size=
         users_dev = torch.from_numpy(test_users.astype(np.int32)).to(device)
         D = tables[0].shape[1]
         # tensor-core route for what it supports (top-k / MAP / MRR); AUC stays on the exact path
-        use_tc = precision == 1 and D <= 128 and k <= 32
+        use_tc = precision == 1 and D <= 128 and k <= 16
         if precision == 1 and not use_tc:
-            raise _abi.CmfError('precision=1 needs embedding_dim <= 128 and k <= 32')
+            raise _abi.CmfError('precision=1 needs embedding_dim <= 128 and k <= 16')
         tc_names = [n for n in names if n != 'auc'] if use_tc else []
         ex_names = [n for n in names if n not in tc_names]
         sums = torch.zeros(len(names), dtype=torch.float64, device=device)

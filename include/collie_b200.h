@@ -232,7 +232,7 @@ CMF_API int cmf_optimizer_rows_masked(float *P, float *M, float *V, const float 
  *   target in this shard, best_score/best_id [n]: that target's score/id (-inf/-1 when none),
  *   auc_pairs [n] double: sum over targets of (#non-targets with lower sigmoid + .5 ties).
  * precision: 0 = fp32 SIMT scoring (exact fp32; all outputs), 1 = tcgen05 tensor cores over
- *   bf16-split operands (hi.hi + hi.lo + lo.hi, fp32 accumulation): embedding_dim <= 128, k <= 32,
+ *   bf16-split operands (hi.hi + hi.lo + lo.hi, fp32 accumulation): embedding_dim <= 128, k <= 16,
  *   every output except auc_pairs (want_auc must be 0).
  */
 typedef struct {
