@@ -37,7 +37,7 @@ int g_tc_debug = 0;   // experiments only (cmf_set_tuning key 3): 1 = epilogue s
 constexpr int TC_BM = 128;        // users per CTA
 constexpr int TC_BN = 128;        // items per MMA tile
 constexpr int TC_BK = 64;         // bf16 per K block = one 128-byte swizzle row
-constexpr int TC_STAGES = 4;
+constexpr int TC_STAGES = 7;
 constexpr int TC_MAXK = 16;       // top-k list length supported by the epilogue
 constexpr int TC_TILE_BYTES = TC_BN * TC_BK * 2;   // 16 KB: one operand K-block
 
@@ -73,6 +73,16 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
+}
+// one lane of the (converged) warp, the same one every time
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
 }
 __device__ __forceinline__ void tc_fence_before() {
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -118,6 +128,13 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t addr) {
   return (uint64_t)((addr >> 4) & 0x3FFF) | (1ull << 16) | (64ull << 32) | (1ull << 46) |
          (2ull << 61);
+}
+// the same descriptor from its low word (address field + LBO); the high word is constant
+__device__ __forceinline__ uint32_t smem_desc_lo(uint32_t addr) {
+  return ((addr >> 4) & 0x3FFF) | (1u << 16);
+}
+__device__ __forceinline__ uint64_t smem_desc_from_lo(uint32_t lo) {
+  return ((uint64_t)0x40004040u << 32) | lo;
 }
 // kind::f16 instruction descriptor: D = f32, A = B = bf16, both K-major, N = 128, M = 128
 // (InstrDescriptor in cute/arch/mma_sm100_desc.hpp: c_format [4,6), a_format [7,10),
@@ -239,7 +256,7 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   unsigned char* sA = smem;
   unsigned char* sB = sA + (size_t)p.KB * TC_TILE_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sB + (size_t)TC_STAGES * TC_TILE_BYTES);
-  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 16);
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 2 * TC_STAGES + 6);
 
   const uint32_t bar_full = s_addr(&bars[0]);                 // [TC_STAGES]
   const uint32_t bar_empty = s_addr(&bars[TC_STAGES]);        // [TC_STAGES]
@@ -248,7 +265,8 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const uint32_t bar_tfull = s_addr(&bars[2 * TC_STAGES + 2]);   // [2]
   const uint32_t bar_tempty = s_addr(&bars[2 * TC_STAGES + 4]);  // [2]
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp index through a shuffle: the compiler then treats it (and the role branches) as uniform
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const int64_t w_lo = (int64_t)blockIdx.x * p.chunk;
   const int64_t w_hi = min(p.total_work, w_lo + p.chunk);
 
@@ -273,25 +291,35 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   if (warp == 0) {
     // ===================================================================== TMA producer
-    if (lane == 0 && w_lo < w_hi) {
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+    // (whole warp in the loop, one elected lane issues: see the MMA warp)
+    if (w_lo < w_hi) {
+      if (elect_one()) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+      }
       int stage = 0, seg = 0;
       uint32_t phase = 0;
+      const uint32_t sA0 = s_addr(sA), sB0 = s_addr(sB);
       for (int64_t w = w_lo; w < w_hi; ++seg) {
         const int m = (int)(w / p.n_tiles);
         const int64_t seg_hi = min(w_hi, (int64_t)(m + 1) * p.n_tiles);
         if (seg > 0) mbar_wait(bar_afree, (seg - 1) & 1);   // the previous segment's MMAs are done
-        mbar_expect_tx(bar_a, (uint32_t)p.KB * TC_TILE_BYTES);
-        for (int kb = 0; kb < p.KB; ++kb)
-          tma_load_2d(s_addr(sA + (size_t)kb * TC_TILE_BYTES), &tmA, kb * TC_BK, m * TC_BM, bar_a);
+        if (elect_one()) {
+          mbar_expect_tx(bar_a, (uint32_t)p.KB * TC_TILE_BYTES);
+          for (int kb = 0; kb < p.KB; ++kb)
+            tma_load_2d(sA0 + (uint32_t)kb * TC_TILE_BYTES, &tmA, kb * TC_BK, m * TC_BM, bar_a);
+        }
+        __syncwarp();
         for (; w < seg_hi; ++w) {
           const int n0 = (int)(w - (int64_t)m * p.n_tiles) * TC_BN;
           for (int kb = 0; kb < p.KB; ++kb) {
             mbar_wait(bar_empty + 8 * stage, phase ^ 1);
-            mbar_expect_tx(bar_full + 8 * stage, TC_TILE_BYTES);
-            tma_load_2d(s_addr(sB + (size_t)stage * TC_TILE_BYTES), &tmB, kb * TC_BK, n0,
-                        bar_full + 8 * stage);
+            if (elect_one()) {
+              mbar_expect_tx(bar_full + 8 * stage, TC_TILE_BYTES);
+              tma_load_2d(sB0 + (uint32_t)stage * TC_TILE_BYTES, &tmB, kb * TC_BK, n0,
+                          bar_full + 8 * stage);
+            }
+            __syncwarp();
             if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
           }
         }
@@ -299,9 +327,14 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
   } else if (warp == 1) {
     // ===================================================================== MMA issuer
-    if (lane == 0 && w_lo < w_hi) {
+    // The whole warp walks the loop (warp-uniform control flow and operands, so the descriptors
+    // live in uniform registers) and one elected lane issues: with a `lane == 0` branch around
+    // the loop the compiler wrapped every tcgen05 instruction in an elect/R2UR/branch sequence,
+    // ~100 issue slots per K block, and the tensor pipe idled 60% of the time behind it.
+    if (w_lo < w_hi) {
       int stage = 0, seg = 0, t = 0;
       uint32_t phase = 0;
+      const uint32_t a_lo0 = smem_desc_lo(s_addr(sA)), b_lo0 = smem_desc_lo(s_addr(sB));
       for (int64_t w = w_lo; w < w_hi; ++seg) {
         const int m = (int)(w / p.n_tiles);
         const int64_t seg_hi = min(w_hi, (int64_t)(m + 1) * p.n_tiles);
@@ -315,17 +348,23 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           for (int kb = 0; kb < p.KB; ++kb) {
             mbar_wait(bar_full + 8 * stage, phase);
             tc_fence_after();
-            const uint64_t da = smem_desc_sw128(s_addr(sA + (size_t)kb * TC_TILE_BYTES));
-            const uint64_t db = smem_desc_sw128(s_addr(sB + (size_t)stage * TC_TILE_BYTES));
+            const uint32_t a_lo = a_lo0 + (uint32_t)kb * (TC_TILE_BYTES >> 4);
+            const uint32_t b_lo = b_lo0 + (uint32_t)stage * (TC_TILE_BYTES >> 4);
+            if (elect_one()) {
 #pragma unroll
-            for (int j = 0; j < TC_BK / 16; ++j)   // +32 bytes (2 x 16 B) per K = 16 step
-              umma_bf16(d_tmem, da + 2 * j, db + 2 * j, kIdescBf16, (kb | j) != 0);
-            umma_commit(bar_empty + 8 * stage);     // frees the stage when these MMAs are done
+              for (int j = 0; j < TC_BK / 16; ++j)   // +32 bytes (2 x 16 B) per K = 16 step
+                umma_bf16(d_tmem, smem_desc_from_lo(a_lo + 2 * j), smem_desc_from_lo(b_lo + 2 * j),
+                          kIdescBf16, (kb | j) != 0);
+              umma_commit(bar_empty + 8 * stage);   // frees the stage when these MMAs are done
+            }
+            __syncwarp();
             if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
           }
-          umma_commit(bar_tfull + 8 * acc);         // accumulator complete -> epilogue
+          if (elect_one()) umma_commit(bar_tfull + 8 * acc);   // accumulator complete -> epilogue
+          __syncwarp();
         }
-        umma_commit(bar_afree);                     // A' may be overwritten by the next segment
+        if (elect_one()) umma_commit(bar_afree);   // A' may be overwritten by the next segment
+        __syncwarp();
       }
     }
   } else if (warp >= 4) {
@@ -646,7 +685,7 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   p.cnt = (int32_t*)(base + L.cnt);
 
   const size_t smem = (size_t)L.KB * TC_TILE_BYTES + (size_t)TC_STAGES * TC_TILE_BYTES +
-                      16 * sizeof(uint64_t) + 64 + 1024;
+                      (2 * TC_STAGES + 6) * sizeof(uint64_t) + 64 + 1024;
   // slots a user tile does not use stay empty
   CMF_CUDA(cudaMemsetAsync(p.cand_i, 0xFF, sizeof(int32_t) * L.m_pad * L.n_slots * a->k, s));
   CMF_CUDA(cudaMemsetAsync(p.cnt, 0, sizeof(int32_t) * L.m_pad * L.n_slots, s));
