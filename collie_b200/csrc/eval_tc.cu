@@ -11,16 +11,16 @@
 // < 2^-16 relative. Values that are exactly representable in bf16 (the exact-arithmetic parity
 // fixture) give bit-exact scores.
 //
-// The (128-user tile, 128-item tile) pairs are cut into equal contiguous chunks, one per CTA, one
+// The (128-user tile, 256-item tile) pairs are cut into equal contiguous chunks, one per CTA, one
 // CTA per SM: a CTA walks its chunk as segments that each lie inside one user tile, leaves every
 // segment's top-k candidates and counters in scratch, and k_tc_merge combines the segments of a
 // user in canonical order (score desc, id asc).
-//   warp 0      TMA producer: A' once (resident), then B' K-blocks through a 4-stage mbarrier ring
-//   warp 1      MMA issuer: tcgen05.mma.cta_group::1.kind::f16, M = 128, N = 128, K = 16 per
-//               instruction, two accumulators in TMEM (256 columns) so tile t+1 is being multiplied
+//   warp 0      TMA producer: A' once per segment (resident), then B' K-blocks through a 3-stage mbarrier ring
+//   warp 1      MMA issuer: tcgen05.mma.cta_group::1.kind::f16, M = 128, N = 256, K = 16 per
+//               instruction, two accumulators in TMEM (all 512 columns) so tile t+1 is being multiplied
 //               while tile t is ranked
 //   warp 2      TMEM allocation
-//   warps 4..11 epilogue, two warps per scheduler (each takes 64 of a tile's 128 columns):
+//   warps 4..11 epilogue, two warps per scheduler (each takes half of a tile's columns):
 //               tcgen05.ld 32x32b (thread = user row); the biases are folded into the GEMM (four
 //               extra K slots), so the accumulator IS the score: a branch-free pass builds 32-bit
 //               predicate masks per 32 columns (beats the row's k-th best / beats the best
@@ -35,11 +35,12 @@ namespace cmf {
 int g_tc_debug = 0;   // experiments only (cmf_set_tuning key 3): 1 = epilogue skips the ranking
 
 constexpr int TC_BM = 128;        // users per CTA
-constexpr int TC_BN = 128;        // items per MMA tile
+constexpr int TC_BN = 256;        // items per MMA tile (one instruction: M = 128, N = 256, K = 16)
 constexpr int TC_BK = 64;         // bf16 per K block = one 128-byte swizzle row
-constexpr int TC_STAGES = 7;
+constexpr int TC_STAGES = 3;
 constexpr int TC_MAXK = 16;       // top-k list length supported by the epilogue
-constexpr int TC_TILE_BYTES = TC_BN * TC_BK * 2;   // 16 KB: one operand K-block
+constexpr int TC_A_BYTES = TC_BM * TC_BK * 2;   // 16 KB: one K-block of the user tile
+constexpr int TC_B_BYTES = TC_BN * TC_BK * 2;   // 32 KB: one K-block of an item tile
 
 // ---------------------------------------------------------------------------------- PTX wrappers
 __device__ __forceinline__ uint32_t s_addr(const void* p) {
@@ -105,6 +106,30 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
                : "memory");
 }
+// 32 columns of this thread's TMEM lane; the caller issues tcgen05.wait::ld before reading v
+__device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, float (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]),
+        "=f"(v[7]), "=f"(v[8]), "=f"(v[9]), "=f"(v[10]), "=f"(v[11]), "=f"(v[12]), "=f"(v[13]),
+        "=f"(v[14]), "=f"(v[15]), "=f"(v[16]), "=f"(v[17]), "=f"(v[18]), "=f"(v[19]), "=f"(v[20]),
+        "=f"(v[21]), "=f"(v[22]), "=f"(v[23]), "=f"(v[24]), "=f"(v[25]), "=f"(v[26]), "=f"(v[27]),
+        "=f"(v[28]), "=f"(v[29]), "=f"(v[30]), "=f"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
+// tcgen05.wait::ld with the loaded registers as in/out operands, so that no use of them can be
+// scheduled above the wait (an empty `ins` makes it a pure dependency carrier)
+#define CMF_V32_INOUT "+f"(v[0]), "+f"(v[1]), "+f"(v[2]), "+f"(v[3]), "+f"(v[4]), "+f"(v[5]), "+f"(v[6]), "+f"(v[7]), "+f"(v[8]), "+f"(v[9]), "+f"(v[10]), "+f"(v[11]), "+f"(v[12]), "+f"(v[13]), "+f"(v[14]), "+f"(v[15]), \
+  "+f"(v[16]), "+f"(v[17]), "+f"(v[18]), "+f"(v[19]), "+f"(v[20]), "+f"(v[21]), "+f"(v[22]), "+f"(v[23]), "+f"(v[24]), "+f"(v[25]), "+f"(v[26]), "+f"(v[27]), "+f"(v[28]), "+f"(v[29]), "+f"(v[30]), "+f"(v[31])
+__device__ __forceinline__ void tmem_wait_ld(float (&v)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : CMF_V32_INOUT : : "memory");
+}
+__device__ __forceinline__ void tmem_ld_dep(float (&v)[32]) {
+  asm volatile("" : CMF_V32_INOUT : : "memory");
+}
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
   uint32_t r[32];
   asm volatile(
@@ -136,7 +161,7 @@ __device__ __forceinline__ uint32_t smem_desc_lo(uint32_t addr) {
 __device__ __forceinline__ uint64_t smem_desc_from_lo(uint32_t lo) {
   return ((uint64_t)0x40004040u << 32) | lo;
 }
-// kind::f16 instruction descriptor: D = f32, A = B = bf16, both K-major, N = 128, M = 128
+// kind::f16 instruction descriptor: D = f32, A = B = bf16, both K-major, N = TC_BN, M = 128
 // (InstrDescriptor in cute/arch/mma_sm100_desc.hpp: c_format [4,6), a_format [7,10),
 // b_format [10,13), n_dim = N >> 3 at [17,23), m_dim = M >> 4 at [24,29)).
 constexpr uint32_t kIdescBf16 =
@@ -254,8 +279,8 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   unsigned char* smem = smem_raw + ((1024u - (s_addr(smem_raw) & 1023u)) & 1023u);
   // carve-up: A' K-blocks | B' stages | barriers
   unsigned char* sA = smem;
-  unsigned char* sB = sA + (size_t)p.KB * TC_TILE_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + (size_t)TC_STAGES * TC_TILE_BYTES);
+  unsigned char* sB = sA + (size_t)p.KB * TC_A_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + (size_t)TC_STAGES * TC_B_BYTES);
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 2 * TC_STAGES + 6);
 
   const uint32_t bar_full = s_addr(&bars[0]);                 // [TC_STAGES]
@@ -278,9 +303,9 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
-    // 256 TMEM columns: two 128 x 128 fp32 accumulators
+    // all 512 TMEM columns: two 128 x 256 fp32 accumulators
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
-                     s_addr(s_tmem)), "r"(256)
+                     s_addr(s_tmem)), "r"(2 * TC_BN)
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
@@ -305,9 +330,9 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int64_t seg_hi = min(w_hi, (int64_t)(m + 1) * p.n_tiles);
         if (seg > 0) mbar_wait(bar_afree, (seg - 1) & 1);   // the previous segment's MMAs are done
         if (elect_one()) {
-          mbar_expect_tx(bar_a, (uint32_t)p.KB * TC_TILE_BYTES);
+          mbar_expect_tx(bar_a, (uint32_t)p.KB * TC_A_BYTES);
           for (int kb = 0; kb < p.KB; ++kb)
-            tma_load_2d(sA0 + (uint32_t)kb * TC_TILE_BYTES, &tmA, kb * TC_BK, m * TC_BM, bar_a);
+            tma_load_2d(sA0 + (uint32_t)kb * TC_A_BYTES, &tmA, kb * TC_BK, m * TC_BM, bar_a);
         }
         __syncwarp();
         for (; w < seg_hi; ++w) {
@@ -315,8 +340,8 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           for (int kb = 0; kb < p.KB; ++kb) {
             mbar_wait(bar_empty + 8 * stage, phase ^ 1);
             if (elect_one()) {
-              mbar_expect_tx(bar_full + 8 * stage, TC_TILE_BYTES);
-              tma_load_2d(sB0 + (uint32_t)stage * TC_TILE_BYTES, &tmB, kb * TC_BK, n0,
+              mbar_expect_tx(bar_full + 8 * stage, TC_B_BYTES);
+              tma_load_2d(sB0 + (uint32_t)stage * TC_B_BYTES, &tmB, kb * TC_BK, n0,
                           bar_full + 8 * stage);
             }
             __syncwarp();
@@ -348,8 +373,8 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           for (int kb = 0; kb < p.KB; ++kb) {
             mbar_wait(bar_full + 8 * stage, phase);
             tc_fence_after();
-            const uint32_t a_lo = a_lo0 + (uint32_t)kb * (TC_TILE_BYTES >> 4);
-            const uint32_t b_lo = b_lo0 + (uint32_t)stage * (TC_TILE_BYTES >> 4);
+            const uint32_t a_lo = a_lo0 + (uint32_t)kb * (TC_A_BYTES >> 4);
+            const uint32_t b_lo = b_lo0 + (uint32_t)stage * (TC_B_BYTES >> 4);
             if (elect_one()) {
 #pragma unroll
               for (int j = 0; j < TC_BK / 16; ++j)   // +32 bytes (2 x 16 B) per K = 16 step
@@ -370,7 +395,7 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp >= 4) {
     // ===================================================================== epilogue
     const int q = warp & 3;               // TMEM lane quarter this warp may read
-    const int half = (warp - 4) >> 2;     // which 64 columns of every 128-column tile
+    const int half = (warp - 4) >> 2;     // which half of every tile's columns
     const int row = q * 32 + lane;        // user row inside the tile
     int t = 0;
     for (int64_t w = w_lo; w < w_hi;) {
@@ -386,7 +411,7 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int e = 0; e < KL; ++e) { ls[e] = -INFINITY; li[e] = -1; }
       float thr = -INFINITY;
       const bool mrr = p.want_mrr && valid;
-      const float best_s = mrr ? p.best_s[urow] : INFINITY;
+      const float best_s = mrr ? p.best_s[urow] : INFINITY;   // (rows past the end: m_rng is 0)
       const int best_id = mrr ? p.best_id[urow] : -1;
       int before = 0;
 
@@ -395,70 +420,92 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int64_t n0 = (w - (int64_t)m * p.n_tiles) * TC_BN;
         mbar_wait(bar_tfull + 8 * acc, (t >> 1) & 1);
         tc_fence_after();
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * TC_BN);
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) +
+                               (uint32_t)(acc * TC_BN + half * (TC_BN / 2));
         const int ncols = (int)min((int64_t)TC_BN, p.n_items - n0);   // < TC_BN only in the last tile
         const int gid0 = (int)(p.item_offset + n0);
+        // 64 columns at a time go to registers; the accumulator is handed back as soon as the
+        // last of them has been read, before they are ranked
 #pragma unroll 1
-        for (int c0 = half * 64; c0 < half * 64 + 64; c0 += 32) {
-          float v[32];
-          tmem_ld32(taddr + c0, v);
-          if (p.debug == 1) continue;
-          // branch-free pass: bit j of each mask = predicate of column c0 + j
-          uint32_t m_ins = 0, m_gt = 0, m_ge = 0;
-          if (mrr) {
+        for (int pp = 0; pp < TC_BN / 128; ++pp) {
+        float v[2][32];
+        tmem_ld32_nowait(taddr + pp * 64, v[0]);
+        tmem_ld32_nowait(taddr + pp * 64 + 32, v[1]);
+        tmem_wait_ld(v[0]);
+        tmem_ld_dep(v[1]);
+        if (pp == TC_BN / 128 - 1) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+        }
+        if (p.debug == 1) continue;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              m_ins |= (v[j] > thr ? 1u : 0u) << j;
-              m_gt |= (v[j] > best_s ? 1u : 0u) << j;
-              m_ge |= (v[j] >= best_s ? 1u : 0u) << j;
-            }
-          } else {
+        for (int h = 0; h < 2; ++h) {
+          const int c0 = half * (TC_BN / 2) + pp * 64 + h * 32;
+          // branch-free pass: bit j of each mask = predicate of column c0 + j. x > y <=> the sign
+          // bit of (y - x) (no flush-to-zero here, so a nonzero difference keeps its sign; equal
+          // values give +0), and one funnel shift moves that bit into the mask: two instructions
+          // per column and mask, in four independent chains
+          uint32_t mi[4] = {0, 0, 0, 0};
 #pragma unroll
-            for (int j = 0; j < 32; ++j) m_ins |= (v[j] > thr ? 1u : 0u) << j;
+          for (int j = 7; j >= 0; --j) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+              mi[c] = __funnelshift_l(__float_as_uint(thr - v[h][8 * c + j]), mi[c], 1);
           }
+          uint32_t m_ins = mi[0] | (mi[1] << 8) | (mi[2] << 16) | (mi[3] << 24);
           const int left = ncols - c0;
           const uint32_t m_rng = (!valid || left <= 0) ? 0u
                                  : (left >= 32 ? 0xffffffffu : ((1u << left) - 1u));
-          if (mrr) {
+          if (p.want_mrr) {   // (uniform branch: no predicated-off copies on the top-k-only path)
+            uint32_t mg[4] = {0, 0, 0, 0}, ml[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int j = 7; j >= 0; --j) {
+#pragma unroll
+              for (int c = 0; c < 4; ++c) {
+                const float x = v[h][8 * c + j];
+                mg[c] = __funnelshift_l(__float_as_uint(best_s - x), mg[c], 1);   // x > best
+                ml[c] = __funnelshift_l(__float_as_uint(x - best_s), ml[c], 1);   // x < best
+              }
+            }
+            const uint32_t m_gt = mg[0] | (mg[1] << 8) | (mg[2] << 16) | (mg[3] << 24);
+            const uint32_t m_eq = ~(m_gt | ml[0] | (ml[1] << 8) | (ml[2] << 16) | (ml[3] << 24));
             // ties with the best target count when their id is smaller; the target never does
             const int d = best_id - (gid0 + c0);      // columns with gid < best_id: j < d
             const uint32_t m_idlt = d >= 32 ? 0xffffffffu : (d > 0 ? ((1u << d) - 1u) : 0u);
             const uint32_t m_self = (d >= 0 && d < 32) ? (1u << d) : 0u;
-            before += __popc(m_gt & m_rng & ~m_self) + __popc((m_ge & ~m_gt) & m_rng & m_idlt);
+            before += __popc(m_gt & m_rng & ~m_self) + __popc(m_eq & m_rng & m_idlt);
           }
           m_ins &= m_rng;
-          if (__any_sync(0xffffffffu, m_ins != 0)) {
-            // lanes insert side by side, each its own next candidate (column j differs per lane)
-            while (__any_sync(0xffffffffu, m_ins != 0)) {
-              if (m_ins) {
-                const int j = __ffs(m_ins) - 1;
-                m_ins &= m_ins - 1;
-                const float sc = pick32(v, j);
-                if (sc > thr) {     // thr may have risen within the chunk
-                  // sorted insert; an equal score stays behind the entries already there (ids
-                  // only grow along a segment), which is the canonical order
-                  float cs = sc;
-                  int ci = gid0 + c0 + j;
-                  bool up = false;   // sticky: below the insertion point everything shifts down
+          if (p.debug == 2) m_ins &= 1u;   // experiments: (almost) no inserts
+          // lanes insert side by side, each its own next candidate (column j differs per lane)
+          while (__any_sync(0xffffffffu, m_ins != 0)) {
+            if (m_ins) {
+              const int j = __ffs(m_ins) - 1;
+              m_ins &= m_ins - 1;
+              const float sc = pick32(v[h], j);
+              if (sc > thr) {     // thr may have risen within the chunk
+                // sorted insert; an equal score stays behind the entries already there (ids
+                // only grow along a segment), which is the canonical order
+                float cs = sc;
+                int ci = gid0 + c0 + j;
+                bool up = false;   // sticky: below the insertion point everything shifts down
 #pragma unroll
-                  for (int e = 0; e < KL; ++e) {
-                    up = up || cs > ls[e];
-                    const float os = ls[e];
-                    const int oi = li[e];
-                    ls[e] = up ? cs : os;
-                    li[e] = up ? ci : oi;
-                    cs = up ? os : cs;
-                    ci = up ? oi : ci;
-                  }
-                  thr = ls[KL - 1];
+                for (int e = 0; e < KL; ++e) {
+                  up = up || cs > ls[e];
+                  const float os = ls[e];
+                  const int oi = li[e];
+                  ls[e] = up ? cs : os;
+                  li[e] = up ? ci : oi;
+                  cs = up ? os : cs;
+                  ci = up ? oi : ci;
                 }
+                thr = ls[KL - 1];
               }
             }
           }
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+        }
       }
       if (valid) {
         const int K = p.k;
@@ -475,7 +522,7 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   tc_fence_before();
   __syncthreads();
   if (warp == 2) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * TC_BN)
                  : "memory");
   }
 }
@@ -566,13 +613,13 @@ static EncodeTiledFn encode_tiled() {
   return fn;
 }
 
-// [rows, Kp] bf16 row-major, box = 64 columns x 128 rows, 128-byte swizzle, OOB rows read as zero
-static int make_map(CUtensorMap* map, void* base, int64_t rows, int Kp) {
+// [rows, Kp] bf16 row-major, box = 64 columns x box_rows rows, 128-byte swizzle, OOB rows read as zero
+static int make_map(CUtensorMap* map, void* base, int64_t rows, int Kp, int box_rows) {
   EncodeTiledFn enc = encode_tiled();
   if (!enc) return fail(CMF_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
   cuuint64_t dims[2] = {(cuuint64_t)Kp, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)Kp * 2};
-  cuuint32_t box[2] = {TC_BK, TC_BN};
+  cuuint32_t box[2] = {TC_BK, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims, strides, box, estr,
                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -670,9 +717,9 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   }
 
   CUtensorMap tmA, tmB;
-  int rc = make_map(&tmA, Ap, L.m_pad, L.Kp);
+  int rc = make_map(&tmA, Ap, L.m_pad, L.Kp, TC_BM);
   if (rc) return rc;
-  rc = make_map(&tmB, Bp, a->num_items_shard, L.Kp);
+  rc = make_map(&tmB, Bp, a->num_items_shard, L.Kp, TC_BN);
   if (rc) return rc;
 
   TcParams p{};
@@ -684,7 +731,7 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   p.cand_s = (float*)(base + L.cand_s); p.cand_i = (int32_t*)(base + L.cand_i);
   p.cnt = (int32_t*)(base + L.cnt);
 
-  const size_t smem = (size_t)L.KB * TC_TILE_BYTES + (size_t)TC_STAGES * TC_TILE_BYTES +
+  const size_t smem = (size_t)L.KB * TC_A_BYTES + (size_t)TC_STAGES * TC_B_BYTES +
                       (2 * TC_STAGES + 6) * sizeof(uint64_t) + 64 + 1024;
   // slots a user tile does not use stay empty
   CMF_CUDA(cudaMemsetAsync(p.cand_i, 0xFF, sizeof(int32_t) * L.m_pad * L.n_slots * a->k, s));
