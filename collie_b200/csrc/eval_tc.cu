@@ -191,33 +191,49 @@ __device__ __forceinline__ void split_bf16(float x, __nv_bfloat16& hi, __nv_bflo
 //   items: [hi | lo | hi | 1, 1, bi_hi, bi_lo | 0...]   users: [hi | hi | lo | bu_hi, bu_lo, 1, 1 | 0...]
 // so the GEMM yields  <u, i> + bu + bi  directly (the biases are split like the rows). Rows
 // >= n_rows are zero.
+// One warp per row; a lane produces two adjacent bf16 at a time (one 4-byte store, 128 bytes per
+// warp), the row id is read once per row.
+__device__ __forceinline__ __nv_bfloat16 tc_split_elem(const float* __restrict__ srow, float b,
+                                                       int c, int D, int users) {
+  if (c < 3 * D) {
+    const int seg = c / D, d = c - seg * D;
+    __nv_bfloat16 hi, lo;
+    split_bf16(srow[d], hi, lo);
+    const bool want_lo = users ? (seg == 2) : (seg == 1);
+    return want_lo ? lo : hi;
+  }
+  if (c < 3 * D + 4) {
+    const int q = c - 3 * D;
+    __nv_bfloat16 hi, lo;
+    split_bf16(b, hi, lo);
+    const bool own = users ? (q < 2) : (q >= 2);     // own bias in two slots, 1.0 in the others
+    return own ? ((q & 1) ? lo : hi) : __float2bfloat16_rn(1.f);
+  }
+  return __float2bfloat16_rn(0.f);
+}
+
 __global__ void __launch_bounds__(256)
 k_tc_split(const float* __restrict__ src, const float* __restrict__ bias,
            const int32_t* __restrict__ ids, int64_t row_offset, int64_t n_rows, int64_t n_rows_pad,
            int D, int Kp, int users, __nv_bfloat16* __restrict__ out) {
-  const int64_t total = n_rows_pad * (int64_t)Kp;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t r = i / Kp;
-    const int c = (int)(i - r * Kp);
-    __nv_bfloat16 v = __float2bfloat16_rn(0.f);
-    if (r < n_rows) {
-      const int64_t row = ids ? (int64_t)ids[r] : row_offset + r;
-      if (c < 3 * D) {
-        const int seg = c / D, d = c - seg * D;
-        __nv_bfloat16 hi, lo;
-        split_bf16(src[row * D + d], hi, lo);
-        const bool want_lo = users ? (seg == 2) : (seg == 1);
-        v = want_lo ? lo : hi;
-      } else if (c < 3 * D + 4) {
-        const int q = c - 3 * D;
-        __nv_bfloat16 hi, lo;
-        split_bf16(bias[row], hi, lo);
-        const bool own = users ? (q < 2) : (q >= 2);     // own bias in two slots, 1.0 in the others
-        v = own ? ((q & 1) ? lo : hi) : __float2bfloat16_rn(1.f);
-      }
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp0; r < n_rows_pad; r += n_warps) {
+    __nv_bfloat162* orow = reinterpret_cast<__nv_bfloat162*>(out + r * Kp);   // Kp is even
+    if (r >= n_rows) {
+      for (int c2 = lane; c2 < Kp / 2; c2 += 32) orow[c2] = __floats2bfloat162_rn(0.f, 0.f);
+      continue;
     }
-    out[i] = v;
+    const int64_t row = ids ? (int64_t)ids[r] : row_offset + r;
+    const float* srow = src + row * D;
+    const float b = bias[row];
+    for (int c2 = lane; c2 < Kp / 2; c2 += 32) {
+      __nv_bfloat162 v;
+      v.x = tc_split_elem(srow, b, 2 * c2, D, users);
+      v.y = tc_split_elem(srow, b, 2 * c2 + 1, D, users);
+      orow[c2] = v;
+    }
   }
 }
 
@@ -251,6 +267,7 @@ k_tc_target_best(const float* __restrict__ U, const float* __restrict__ I,
 // ---------------------------------------------------------------------------------- GEMM + top-k
 struct TcParams {
   int n_users, k, KB, n_tiles, m_tiles, n_slots, want_mrr, debug;
+  int last_steps;        // K = 16 steps of the last K block that hold data (1..4)
   int64_t chunk, total_work;   // tiles per CTA / tiles in all (m_tiles * n_tiles)
   int64_t n_items, item_offset;
   const float* best_s;   // MRR threshold per user (may be NULL)
@@ -375,11 +392,14 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             tc_fence_after();
             const uint32_t a_lo = a_lo0 + (uint32_t)kb * (TC_A_BYTES >> 4);
             const uint32_t b_lo = b_lo0 + (uint32_t)stage * (TC_B_BYTES >> 4);
+            // (the zero-padded tail of the last K block is not multiplied)
+            const int steps = kb == p.KB - 1 ? p.last_steps : TC_BK / 16;
             if (elect_one()) {
 #pragma unroll
               for (int j = 0; j < TC_BK / 16; ++j)   // +32 bytes (2 x 16 B) per K = 16 step
-                umma_bf16(d_tmem, smem_desc_from_lo(a_lo + 2 * j), smem_desc_from_lo(b_lo + 2 * j),
-                          kIdescBf16, (kb | j) != 0);
+                if (j < steps)
+                  umma_bf16(d_tmem, smem_desc_from_lo(a_lo + 2 * j),
+                            smem_desc_from_lo(b_lo + 2 * j), kIdescBf16, (kb | j) != 0);
               umma_commit(bar_empty + 8 * stage);   // frees the stage when these MMAs are done
             }
             __syncwarp();
@@ -527,11 +547,16 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 }
 
-// merge the candidates of a user's item splits: one warp per user, k selection passes in
-// canonical order; AP@k against the user's sorted target list; counters summed.
+// merge the candidates of a user's segments: one warp per user, k selection rounds in canonical
+// order over candidates held in registers (lane j keeps the j-th pick), then the target lookups
+// of all k picks side by side, AP@k from the hit mask in rank order, counters summed.
+__device__ __forceinline__ bool tc_before(float s, int id, float bs, int bid) {
+  return id >= 0 && (bid < 0 || s > bs || (s == bs && id < bid));
+}
+
 __global__ void __launch_bounds__(256)
 k_tc_merge(const float* __restrict__ cand_s, const int32_t* __restrict__ cand_i,
-           const int32_t* __restrict__ cnt, int n_splits, int k, int64_t n_users,
+           const int32_t* __restrict__ cnt, int n_slots, int k, int64_t n_users,
            const int64_t* __restrict__ tgt_indptr, const int32_t* __restrict__ tgt_items,
            const int32_t* __restrict__ best_id, int32_t* __restrict__ topk_ids,
            float* __restrict__ topk_scores, double* __restrict__ ap,
@@ -539,57 +564,65 @@ k_tc_merge(const float* __restrict__ cand_s, const int32_t* __restrict__ cand_i,
   const int lane = threadIdx.x & 31;
   const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (r >= n_users) return;
-  const int total = n_splits * k;
+  const int total = n_slots * k;
   const float* cs = cand_s + r * total;
   const int32_t* ci = cand_i + r * total;
-  const int64_t t0 = tgt_indptr[r];
-  const int n_tgt = (int)(tgt_indptr[r + 1] - t0);
-  float ps = INFINITY;
-  int pid = -1, hits = 0;
-  double ap_acc = 0.0;
+  const bool in_regs = total <= 64;
+  float s0 = -INFINITY, s1 = -INFINITY;
+  int i0 = -1, i1 = -1;
+  if (in_regs) {
+    if (lane < total) { i0 = ci[lane]; s0 = cs[lane]; }
+    if (lane + 32 < total) { i1 = ci[lane + 32]; s1 = cs[lane + 32]; }
+  }
+  float my_s = -INFINITY, ps = INFINITY;
+  int my_id = -1, pid = -1;
   for (int j = 0; j < k; ++j) {
     float bs = -INFINITY;
     int bid = -1;
-    for (int c = lane; c < total; c += 32) {
-      const int id = ci[c];
-      if (id < 0) continue;
-      const float s = cs[c];
-      const bool after_prev = (pid < 0) || (ps > s) || (ps == s && pid < id);
-      if (after_prev && (bid < 0 || s > bs || (s == bs && id < bid))) { bs = s; bid = id; }
+    if (in_regs) {
+      if (tc_before(s0, i0, bs, bid)) { bs = s0; bid = i0; }
+      if (tc_before(s1, i1, bs, bid)) { bs = s1; bid = i1; }
+    } else {
+      for (int c = lane; c < total; c += 32) {
+        const int id = ci[c];
+        const float s = cs[c];
+        const bool after_prev = (pid < 0) || (ps > s) || (ps == s && pid < id);
+        if (after_prev && tc_before(s, id, bs, bid)) { bs = s; bid = id; }
+      }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       const float os = __shfl_xor_sync(0xffffffffu, bs, o);
       const int oid = __shfl_xor_sync(0xffffffffu, bid, o);
-      if (oid >= 0 && (bid < 0 || os > bs || (os == bs && oid < bid))) { bs = os; bid = oid; }
+      if (tc_before(os, oid, bs, bid)) { bs = os; bid = oid; }
     }
-    if (lane == 0) {
-      if (topk_ids) topk_ids[r * k + j] = bid;
-      if (topk_scores) topk_scores[r * k + j] = bid >= 0 ? bs : -INFINITY;
-      if (bid >= 0 && csr_contains(tgt_items + t0, 0, n_tgt, bid)) {
-        ++hits;
-        ap_acc += (double)hits / (double)(j + 1);
-      }
-    }
+    if (bid < 0) break;
+    if (lane == j) { my_s = bs; my_id = bid; }
+    if (i0 == bid) i0 = -1;     // item ids are unique across a user's segments
+    if (i1 == bid) i1 = -1;
     ps = bs;
     pid = bid;
-    if (bid < 0) {
-      if (lane == 0)
-        for (int jj = j + 1; jj < k; ++jj) {
-          if (topk_ids) topk_ids[r * k + jj] = -1;
-          if (topk_scores) topk_scores[r * k + jj] = -INFINITY;
-        }
-      break;
-    }
+  }
+  const int64_t t0 = tgt_indptr[r];
+  const int n_tgt = (int)(tgt_indptr[r + 1] - t0);
+  const bool hit = lane < k && my_id >= 0 && csr_contains(tgt_items + t0, 0, n_tgt, my_id);
+  const uint32_t hit_mask = __ballot_sync(0xffffffffu, hit);
+  if (lane < k) {
+    if (topk_ids) topk_ids[r * k + lane] = my_id;
+    if (topk_scores) topk_scores[r * k + lane] = my_s;
   }
   if (lane == 0) {
     if (ap) {
+      double ap_acc = 0.0;
+      for (int j = 0; j < k; ++j)
+        if ((hit_mask >> j) & 1u)
+          ap_acc += (double)__popc(hit_mask & ((2u << j) - 1u)) / (double)(j + 1);
       const int denom = k < n_tgt ? k : n_tgt;
       ap[r] = denom > 0 ? ap_acc / (double)denom : 0.0;
     }
     if (n_before_best) {
       int tot = 0;
-      if (cnt) for (int s = 0; s < n_splits; ++s) tot += cnt[r * n_splits + s];
+      if (cnt) for (int sl = 0; sl < n_slots; ++sl) tot += cnt[r * n_slots + sl];
       n_before_best[r] = (best_id && best_id[r] >= 0) ? tot : -1;
     }
   }
@@ -724,6 +757,7 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
 
   TcParams p{};
   p.n_users = (int)a->n_users_tile; p.k = a->k; p.KB = L.KB; p.n_tiles = L.n_tiles;
+  p.last_steps = (3 * a->D + 4 - (L.KB - 1) * TC_BK + 15) / 16;
   p.m_tiles = L.m_tiles; p.n_slots = L.n_slots; p.chunk = L.chunk; p.total_work = L.total_work;
   p.want_mrr = mrr ? 1 : 0;
   p.n_items = a->num_items_shard; p.item_offset = a->item_offset; p.debug = g_tc_debug;
