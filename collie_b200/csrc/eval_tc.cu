@@ -228,6 +228,25 @@ k_tc_split(const float* __restrict__ src, const float* __restrict__ bias,
     const int64_t row = ids ? (int64_t)ids[r] : row_offset + r;
     const float* srow = src + row * D;
     const float b = bias[row];
+    if ((D & 1) == 0 && (reinterpret_cast<uintptr_t>(src) & 7) == 0) {
+      // each value is split once and stored to its three segments
+      for (int d2 = lane; d2 < D / 2; d2 += 32) {
+        const float2 x = *reinterpret_cast<const float2*>(srow + 2 * d2);
+        __nv_bfloat162 hi, lo;
+        split_bf16(x.x, hi.x, lo.x);
+        split_bf16(x.y, hi.y, lo.y);
+        orow[d2] = hi;
+        orow[D / 2 + d2] = users ? hi : lo;
+        orow[D + d2] = users ? lo : hi;
+      }
+      for (int c2 = 3 * D / 2 + lane; c2 < Kp / 2; c2 += 32) {   // bias slots + zero tail
+        __nv_bfloat162 v;
+        v.x = tc_split_elem(srow, b, 2 * c2, D, users);
+        v.y = tc_split_elem(srow, b, 2 * c2 + 1, D, users);
+        orow[c2] = v;
+      }
+      continue;
+    }
     for (int c2 = lane; c2 < Kp / 2; c2 += 32) {
       __nv_bfloat162 v;
       v.x = tc_split_elem(srow, b, 2 * c2, D, users);
@@ -547,13 +566,25 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 }
 
-// merge the candidates of a user's segments: one warp per user, k selection rounds in canonical
-// order over candidates held in registers (lane j keeps the j-th pick), then the target lookups
-// of all k picks side by side, AP@k from the hit mask in rank order, counters summed.
-__device__ __forceinline__ bool tc_before(float s, int id, float bs, int bid) {
-  return id >= 0 && (bid < 0 || s > bs || (s == bs && id < bid));
+// Merge the candidates of a user's segments. Every slot list arrives sorted (score desc, id asc)
+// and item ids are unique across a user's slots, so this is a k-round merge of sorted lists: G
+// lanes per user (G = n_slots rounded up to a power of two, 32 / G users per warp), one slot per
+// lane with its head as a 64-bit key (ordered score bits | inverted id; larger = ranked first), a
+// log2(G)-level max per round, the winning lane advances. The picks go through shared memory so
+// the target lookups of all k picks run side by side; AP@k from the hit mask in rank order.
+__device__ __forceinline__ uint64_t tc_key(float s, int id) {
+  if (id < 0) return 0ull;
+  uint32_t u = __float_as_uint(s + 0.0f);            // (-0 -> +0: equal scores, equal keys)
+  u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);   // monotone: larger float -> larger uint
+  return ((uint64_t)u << 32) | (uint32_t)(0x7fffffff - id);
+}
+__device__ __forceinline__ float tc_key_score(uint64_t key) {
+  uint32_t u = (uint32_t)(key >> 32);
+  u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+  return __uint_as_float(u);
 }
 
+template <int G>
 __global__ void __launch_bounds__(256)
 k_tc_merge(const float* __restrict__ cand_s, const int32_t* __restrict__ cand_i,
            const int32_t* __restrict__ cnt, int n_slots, int k, int64_t n_users,
@@ -561,62 +592,71 @@ k_tc_merge(const float* __restrict__ cand_s, const int32_t* __restrict__ cand_i,
            const int32_t* __restrict__ best_id, int32_t* __restrict__ topk_ids,
            float* __restrict__ topk_scores, double* __restrict__ ap,
            int32_t* __restrict__ n_before_best) {
-  const int lane = threadIdx.x & 31;
-  const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (r >= n_users) return;
+  constexpr int UPW = 32 / G;                       // users per warp
+  __shared__ uint64_t s_pick[8][UPW][TC_MAXK];      // [warp][user][rank]
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int gl = lane & (G - 1), ug = lane / G;
+  const int64_t r = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * UPW + ug;
+  const bool live = r < n_users;
+  // slots gl, gl + G, ...: (only n_slots > 32 gives a lane more than one; then the best head of
+  // its slots is found by a scan every round)
   const int total = n_slots * k;
-  const float* cs = cand_s + r * total;
-  const int32_t* ci = cand_i + r * total;
-  const bool in_regs = total <= 64;
-  float s0 = -INFINITY, s1 = -INFINITY;
-  int i0 = -1, i1 = -1;
-  if (in_regs) {
-    if (lane < total) { i0 = ci[lane]; s0 = cs[lane]; }
-    if (lane + 32 < total) { i1 = ci[lane + 32]; s1 = cs[lane + 32]; }
-  }
-  float my_s = -INFINITY, ps = INFINITY;
-  int my_id = -1, pid = -1;
-  for (int j = 0; j < k; ++j) {
-    float bs = -INFINITY;
-    int bid = -1;
-    if (in_regs) {
-      if (tc_before(s0, i0, bs, bid)) { bs = s0; bid = i0; }
-      if (tc_before(s1, i1, bs, bid)) { bs = s1; bid = i1; }
+  const float* cs = cand_s + (live ? r : 0) * total;
+  const int32_t* ci = cand_i + (live ? r : 0) * total;
+  int head = 0;                                     // (G >= n_slots: position in slot gl)
+  uint64_t key = 0;
+  uint64_t prev = ~0ull;
+  auto load_head = [&]() {
+    if (G >= 32 && n_slots > 32) {
+      // several slots per lane: best candidate below the previous pick
+      key = 0;
+      for (int sl = gl; sl < n_slots; sl += G)
+        for (int e = 0; e < k; ++e) {
+          const uint64_t kk = tc_key(cs[sl * k + e], ci[sl * k + e]);
+          if (kk < prev && kk > key) key = kk;
+        }
     } else {
-      for (int c = lane; c < total; c += 32) {
-        const int id = ci[c];
-        const float s = cs[c];
-        const bool after_prev = (pid < 0) || (ps > s) || (ps == s && pid < id);
-        if (after_prev && tc_before(s, id, bs, bid)) { bs = s; bid = id; }
-      }
+      key = (live && gl < n_slots && head < k) ? tc_key(cs[gl * k + head], ci[gl * k + head]) : 0ull;
     }
+  };
+  load_head();
+  for (int j = 0; j < k; ++j) {
+    uint64_t best = key;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const float os = __shfl_xor_sync(0xffffffffu, bs, o);
-      const int oid = __shfl_xor_sync(0xffffffffu, bid, o);
-      if (tc_before(os, oid, bs, bid)) { bs = os; bid = oid; }
+    for (int o = G / 2; o > 0; o >>= 1) {
+      const uint64_t other = __shfl_xor_sync(0xffffffffu, best, o);
+      best = other > best ? other : best;
     }
-    if (bid < 0) break;
-    if (lane == j) { my_s = bs; my_id = bid; }
-    if (i0 == bid) i0 = -1;     // item ids are unique across a user's segments
-    if (i1 == bid) i1 = -1;
-    ps = bs;
-    pid = bid;
+    if (gl == 0) s_pick[wib][ug][j] = best;
+    if (best != 0 && key == best) {   // the winner moves on
+      ++head;
+      prev = best;
+      load_head();
+    } else if (G >= 32) {
+      prev = best ? best : prev;
+    }
   }
-  const int64_t t0 = tgt_indptr[r];
-  const int n_tgt = (int)(tgt_indptr[r + 1] - t0);
-  const bool hit = lane < k && my_id >= 0 && csr_contains(tgt_items + t0, 0, n_tgt, my_id);
-  const uint32_t hit_mask = __ballot_sync(0xffffffffu, hit);
-  if (lane < k) {
-    if (topk_ids) topk_ids[r * k + lane] = my_id;
-    if (topk_scores) topk_scores[r * k + lane] = my_s;
+  __syncwarp();
+  int64_t t0 = 0;
+  int n_tgt = 0;
+  if (live) { t0 = tgt_indptr[r]; n_tgt = (int)(tgt_indptr[r + 1] - t0); }
+  uint32_t hits = 0;
+  for (int j = gl; j < k; j += G) {
+    const uint64_t pk = s_pick[wib][ug][j];
+    const int id = pk ? 0x7fffffff - (int)(uint32_t)pk : -1;
+    if (live) {
+      if (topk_ids) topk_ids[r * k + j] = id;
+      if (topk_scores) topk_scores[r * k + j] = pk ? tc_key_score(pk) : -INFINITY;
+      if (id >= 0 && csr_contains(tgt_items + t0, 0, n_tgt, id)) hits |= 1u << j;
+    }
   }
-  if (lane == 0) {
+#pragma unroll
+  for (int o = G / 2; o > 0; o >>= 1) hits |= __shfl_xor_sync(0xffffffffu, hits, o);
+  if (live && gl == 0) {
     if (ap) {
       double ap_acc = 0.0;
       for (int j = 0; j < k; ++j)
-        if ((hit_mask >> j) & 1u)
-          ap_acc += (double)__popc(hit_mask & ((2u << j) - 1u)) / (double)(j + 1);
+        if ((hits >> j) & 1u) ap_acc += (double)__popc(hits & ((2u << j) - 1u)) / (double)(j + 1);
       const int denom = k < n_tgt ? k : n_tgt;
       ap[r] = denom > 0 ? ap_acc / (double)denom : 0.0;
     }
@@ -784,10 +824,13 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
 #undef CMF_TC_LAUNCH
   CMF_LAUNCH_CHECK();
 
-  k_tc_merge<<<(unsigned)((a->n_users_tile * 32 + 255) / 256), 256, 0, s>>>(
-      p.cand_s, p.cand_i, mrr ? p.cnt : nullptr, L.n_slots, a->k, a->n_users_tile, a->tgt_indptr,
-      a->tgt_items, mrr ? best_id : nullptr, a->topk_ids, a->topk_scores, a->ap,
-      a->n_before_best);
+#define CMF_TC_MERGE(G)                                                                         \
+  k_tc_merge<G><<<(unsigned)((a->n_users_tile * (G) + 255) / 256), 256, 0, s>>>(p.cand_s, p.cand_i, mrr ? p.cnt : nullptr, L.n_slots, a->k, a->n_users_tile, a->tgt_indptr, a->tgt_items, mrr ? best_id : nullptr, a->topk_ids, a->topk_scores, a->ap, a->n_before_best)
+  if (L.n_slots <= 4) CMF_TC_MERGE(4);
+  else if (L.n_slots <= 8) CMF_TC_MERGE(8);
+  else if (L.n_slots <= 16) CMF_TC_MERGE(16);
+  else CMF_TC_MERGE(32);
+#undef CMF_TC_MERGE
   CMF_LAUNCH_CHECK();
   return CMF_OK;
 }
