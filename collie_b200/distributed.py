@@ -290,8 +290,11 @@ def bench_sharded(args, rank, world, local_rank, workload, synth, config_dict, C
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
+    import time as _time
+    h0 = _time.perf_counter()
     for _ in range(steps):
         loss = one_step()
+    host_ms = (_time.perf_counter() - h0) * 1e3      # host time to ISSUE the steps (no sync)
     e1.record()
     torch.cuda.synchronize()
     dist.barrier()
@@ -316,6 +319,7 @@ def bench_sharded(args, rank, world, local_rank, workload, synth, config_dict, C
             'gpu_launches_note': 'rank 0; own kernels per step: k_fwd_loss + k_bwd_update + '
                                  'k_update_rows + k_optimizer_rows_masked (+ NCCL collectives)',
             'exchange_bytes_per_step_per_gpu': exchange,
+            'host_issue_ms_per_step': host_ms / steps,
             'clocks': clk, 'final_loss': float(loss),
         }
         print(json.dumps(line), flush=True)

@@ -328,32 +328,31 @@ class BaseInteractionsDataLoader(object):
             epoch = self._epoch
             self._epoch += 1
         b = self.batch_size
-        if self.shuffle:
-            gen = torch.Generator(device=device)
-            gen.manual_seed((int(getattr(self.interactions, 'seed', 0)) * 1000003 + int(epoch))
-                            % (2 ** 63 - 1))
-            order = torch.randperm(n, device=device, generator=gen)
-        else:
-            order = torch.arange(n, device=device)
-        users = st['users'][order] if self.shuffle else st['users']
-        if sort_within_batch and n > 0:
-            # epoch plan: order every batch by user once, on the device (one sort of n 64-bit keys
-            # per epoch), so the training step can skip its own per-batch sort
-            n_batches = (n + b - 1) // b
-            ubits = max(1, int(self.num_users - 1).bit_length())
-            if ubits + max(1, int(n_batches - 1).bit_length()) <= 31:
-                key = (torch.arange(n, device=device, dtype=torch.int32) // b) * (1 << ubits) + users
-                key, idx = torch.sort(key, stable=True)
-                users = key & ((1 << ubits) - 1)
-            else:
-                key = (torch.arange(n, device=device, dtype=torch.int64) // b) * (1 << 32) \
-                    + users.long()
-                key, idx = torch.sort(key, stable=True)
-                users = (key & 0xFFFFFFFF).to(torch.int32)
-            order = order[idx]
-        items = st['items'][order]
-        ratings = st['ratings'][order] if 'ratings' in st else None
-        gidx = st['gpos'][order] if 'gpos' in st else order
+        device = torch.device(device)
+        has_ratings = 'ratings' in st
+        users = torch.empty(n, dtype=torch.int32, device=device)
+        items = torch.empty(n, dtype=torch.int32, device=device)
+        gidx = torch.empty(n, dtype=torch.int64, device=device)
+        ratings = torch.empty(n, dtype=torch.float32, device=device) if has_ratings else None
+        if n > 0:
+            # the whole plan is one native call (cmf_epoch_plan: Philox keys -> radix sort = the
+            # permutation; (batch, user) keys -> radix sort; one gather)
+            lib = _abi.lib()
+            need = int(lib.cmf_epoch_plan_workspace_bytes(n))
+            ws = self._plan_ws.get(str(device)) if hasattr(self, '_plan_ws') else None
+            if ws is None or ws.numel() < need:
+                ws = torch.empty(need, dtype=torch.uint8, device=device)
+                self._plan_ws = {str(device): ws}
+            with torch.cuda.device(device):
+                _abi.check(lib.cmf_epoch_plan(
+                    _abi.ptr(st['users']), _abi.ptr(st['items']),
+                    _abi.ptr(st['ratings']) if has_ratings else None, _abi.ptr(st.get('gpos')),
+                    n, b, int(self.num_users), int(bool(self.shuffle)),
+                    int(bool(sort_within_batch)),
+                    int(getattr(self.interactions, 'seed', 0) or 0) & (2 ** 64 - 1),
+                    int(epoch) & 0xFFFFFFFF, _abi.ptr(users), _abi.ptr(items), _abi.ptr(ratings),
+                    _abi.ptr(gidx), _abi.ptr(ws), ws.numel(), _abi.stream_ptr(device)),
+                    'cmf_epoch_plan')
         stop = (n // b) * b if self.drop_last else n
         for s in range(0, stop, b):
             e = min(s + b, n)

@@ -194,6 +194,23 @@ CMF_API int cmf_sample_negatives(uint64_t seed, uint32_t epoch, const int64_t *g
                          int64_t *negs_out, void *stream);
 
 /*
+ * Epoch plan of a data loader, on the device: one pass over the n dataset positions as a random
+ * permutation (shuffle != 0; keyed by (seed, epoch)) cut into batches of `batch`, every batch
+ * ordered by user when sort_within_batch != 0 (ties keep the permutation's order). Outputs, all
+ * of length n: the users / items (/ ratings) in plan order and out_gidx = the dataset position of
+ * every entry (gpos[position] when gpos != NULL: positions in a global, unsharded dataset), which
+ * keys the negative sampler. n < 2^31.
+ * Replaces the host-side shuffle + batch slicing of the reference's loaders:
+ * collie/interactions/samplers.py:51-60 (index shuffle) under dataloaders.py:70-173.
+ */
+CMF_API size_t cmf_epoch_plan_workspace_bytes(int64_t n);
+CMF_API int cmf_epoch_plan(const int32_t *users, const int32_t *items, const float *ratings,
+                   const int64_t *gpos, int64_t n, int64_t batch, int64_t num_users,
+                   int32_t shuffle, int32_t sort_within_batch, uint64_t seed, uint32_t epoch,
+                   int32_t *out_users, int32_t *out_items, float *out_ratings, int64_t *out_gidx,
+                   void *workspace, size_t workspace_bytes, void *stream);
+
+/*
  * Row-wise optimizer on a table given a dense gradient table G [rows, D]:
  *   rows == NULL: every row (torch.optim.Adam / SGD / Adagrad on dense grads);
  *   rows != NULL: only the n_rows listed unique rows (torch.optim.SparseAdam on the coalesced

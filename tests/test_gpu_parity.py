@@ -552,3 +552,62 @@ def test_tensor_core_eval_matches_exact_path(shape):
                                  precision=1)
     exp = cb.evaluate_in_batches([cb.mapk, cb.mrr, cb.auc], test, model, k=k, verbose=False)
     np.testing.assert_allclose(got, exp, rtol=2e-3, atol=1e-6)
+
+
+# ------------------------------------------------------------------------------------ epoch plan
+@pytest.mark.gpu
+@pytest.mark.parametrize('n,batch,n_users,with_gpos', [(10_000, 256, 300, False),
+                                                       (100_003, 4096, 70_000, True),
+                                                       (777, 1000, 5, False)])
+def test_epoch_plan_properties(n, batch, n_users, with_gpos):
+    """cmf_epoch_plan (loader): a permutation of the dataset, cut into batches ordered by user,
+    reproducible per (seed, epoch) and different across epochs (samplers.py:51-60 shuffles on the
+    host; the order inside a batch is free there)."""
+    import collie_b200 as cb
+    rng = np.random.default_rng(n)
+    users = rng.integers(0, n_users, n).astype(np.int32)
+    items = rng.integers(0, 1000, n).astype(np.int32)
+    data = cb.Interactions(users=users, items=items, num_users=n_users, num_items=1000,
+                           allow_missing_ids=True, remove_duplicate_user_item_pairs=False,
+                           check_num_negative_samples_is_valid=False,
+                           max_number_of_samples_to_consider=0, seed=11)
+    d_users, d_items = data.mat.row.astype(np.int32), data.mat.col.astype(np.int32)
+    gpos = None
+    if with_gpos:
+        gpos = rng.permutation(10 * n)[:n].astype(np.int64)
+        data.global_positions = gpos
+    loader = cb.InteractionsDataLoader(data, batch_size=batch, shuffle=True, drop_last=False)
+
+    def epoch(e, sort=True):
+        bs = list(loader.device_batches('cuda', epoch=e, sort_within_batch=sort))
+        return (torch.cat([b.users for b in bs]).cpu().numpy(),
+                torch.cat([b.items for b in bs]).cpu().numpy(),
+                torch.cat([b.gidx for b in bs]).cpu().numpy(), bs)
+
+    u, i, g, bs = epoch(3)
+    assert len(bs) == (n + batch - 1) // batch and all(b.sorted for b in bs)
+    pos = g if gpos is None else np.argsort(gpos)[np.searchsorted(np.sort(gpos), g)]
+    assert np.array_equal(np.sort(pos), np.arange(n))            # a permutation of the dataset
+    assert np.array_equal(u, d_users[pos]) and np.array_equal(i, d_items[pos])
+    for s in range(0, n, batch):                                 # every batch ordered by user
+        assert np.all(np.diff(u[s:s + batch]) >= 0)
+    u2, i2, g2, _ = epoch(3)
+    assert np.array_equal(g, g2)                                 # same (seed, epoch), same plan
+    _, _, g3, _ = epoch(4)
+    assert not np.array_equal(g, g3)
+    # without the in-batch sort the same permutation comes out in its own order
+    _, _, g4, bs4 = epoch(3, sort=False)
+    assert not any(b.sorted for b in bs4)
+    for s in range(0, n, batch):
+        assert np.array_equal(np.sort(g4[s:s + batch]), np.sort(g[s:s + batch]))
+    # the shuffle is not the identity and spreads the dataset over the batches
+    p4 = g4 if gpos is None else np.argsort(gpos)[np.searchsorted(np.sort(gpos), g4)]
+    assert np.mean(p4 == np.arange(n)) < 0.01 + 2.0 / n
+    if n >= 10_000:
+        first = p4[:batch]
+        assert abs(first.mean() / n - 0.5) < 0.05
+    # unshuffled: dataset order, batch by batch
+    plain = cb.InteractionsDataLoader(data, batch_size=batch, shuffle=False)
+    gp = torch.cat([b.gidx for b in plain.device_batches('cuda', epoch=0,
+                                                         sort_within_batch=False)]).cpu().numpy()
+    assert np.array_equal(gp, np.arange(n) if gpos is None else gpos)
