@@ -94,6 +94,9 @@ SIGNATURES = {
     'cmf_epoch_plan': (C.c_int, [C.c_void_p] * 4 + [C.c_int64, C.c_int64, C.c_int64, C.c_int32,
                                                C.c_int32, C.c_uint64, C.c_uint32] +
                        [C.c_void_p] * 5 + [C.c_size_t, C.c_void_p]),
+    'cmf_epoch_plan_presorted': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64,
+                                          C.c_uint64, C.c_uint32] + [C.c_void_p] * 5 +
+                                 [C.c_size_t, C.c_void_p]),
     'cmf_optimizer_rows': (C.c_int, [C.c_void_p] * 4 + [C.c_int64, C.c_int32, C.c_void_p,
                                                        C.c_int64, C.POINTER(cmf_opt_t), C.c_int32,
                                                        C.c_void_p]),

@@ -82,6 +82,57 @@ k_plan_gather(const uint32_t* __restrict__ perm, const int32_t* __restrict__ use
   out_gidx[r] = gpos ? gpos[p] : (int64_t)p;
 }
 
+// ---- fast path: the dataset arrives ordered by user ------------------------------------------
+// A keyed bijection sigma of [0, n) (balanced Feistel network over the next even number of bits,
+// cycle-walked back into range) is the epoch's permutation: entry p goes to batch sigma(p) / batch.
+// A STABLE partition of the user-ordered entries by batch number (one radix pass per 8 bits of
+// batch number) then leaves every batch ordered by user with no further sort.
+struct FeistelKey { uint32_t k[6]; int half_bits; };
+
+__device__ __forceinline__ uint32_t fmix32(uint32_t h) {
+  h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16;
+  return h;
+}
+__device__ __forceinline__ uint32_t feistel_perm(uint32_t x, const FeistelKey& fk, uint32_t n) {
+  const uint32_t mask = (1u << fk.half_bits) - 1u;
+  do {
+    uint32_t l = x >> fk.half_bits, r = x & mask;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+      const uint32_t t = l ^ (fmix32(r * 0x9e3779b1u + fk.k[i]) & mask);
+      l = r;
+      r = t;
+    }
+    x = (l << fk.half_bits) | r;
+  } while (x >= n);   // the domain is < 4 n: a few turns at most on average
+  return x;
+}
+
+__global__ void __launch_bounds__(256)
+k_plan_batch_of(FeistelKey fk, int64_t n, int64_t batch, uint32_t* __restrict__ keys,
+                uint32_t* __restrict__ pos) {
+  const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n) return;
+  keys[p] = (uint32_t)(feistel_perm((uint32_t)p, fk, (uint32_t)n) / (uint64_t)batch);
+  pos[p] = (uint32_t)p;
+}
+
+// rec[p] = {user, item, gidx low, gidx high} of the p-th entry in user order
+__global__ void __launch_bounds__(256)
+k_plan_gather_rec(const uint32_t* __restrict__ perm, const uint4* __restrict__ rec,
+                  const float* __restrict__ ratings, int64_t n, int32_t* __restrict__ out_users,
+                  int32_t* __restrict__ out_items, float* __restrict__ out_ratings,
+                  int64_t* __restrict__ out_gidx) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  const uint32_t p = perm[r];
+  const uint4 e = __ldg(rec + p);
+  out_users[r] = (int32_t)e.x;
+  out_items[r] = (int32_t)e.y;
+  out_gidx[r] = (int64_t)(((uint64_t)e.w << 32) | e.z);
+  if (out_ratings) out_ratings[r] = ratings[p];
+}
+
 static int bits_for(int64_t count) {   // bits that hold 0 .. count - 1
   int b = 1;
   while (b < 63 && ((int64_t)1 << b) < count) ++b;
@@ -157,6 +208,58 @@ extern "C" int cmf_epoch_plan(const int32_t* users, const int32_t* items, const 
   }
   k_plan_gather<<<blocks, 256, 0, s>>>(perm, users, items, ratings, gpos, n, out_users, out_items,
                                        out_ratings, out_gidx);
+  CMF_LAUNCH_CHECK();
+  return CMF_OK;
+}
+
+extern "C" int cmf_epoch_plan_presorted(const void* rec, const float* ratings, int64_t n,
+                                        int64_t batch, uint64_t seed, uint32_t epoch,
+                                        int32_t* out_users, int32_t* out_items, float* out_ratings,
+                                        int64_t* out_gidx, void* workspace, size_t workspace_bytes,
+                                        void* stream) {
+  if (n == 0) return CMF_OK;
+  if (n < 0 || n >= ((int64_t)1 << 31))
+    return fail(CMF_ERR_INVALID, "cmf_epoch_plan_presorted: n = %lld is outside [0, 2^31)",
+                (long long)n);
+  if (batch <= 0) return fail(CMF_ERR_INVALID, "cmf_epoch_plan_presorted: batch must be positive");
+  if (!rec || !out_users || !out_items || !out_gidx)
+    return fail(CMF_ERR_INVALID, "cmf_epoch_plan_presorted: null record / output pointer");
+  if ((reinterpret_cast<uintptr_t>(rec) & 15) != 0)
+    return fail(CMF_ERR_INVALID, "cmf_epoch_plan_presorted: records must be 16-byte aligned");
+  if ((out_ratings != nullptr) != (ratings != nullptr))
+    return fail(CMF_ERR_INVALID, "cmf_epoch_plan_presorted: ratings and out_ratings go together");
+  const PlanLayout L = plan_layout(n);
+  if (!workspace || workspace_bytes < L.total)
+    return fail(CMF_ERR_WORKSPACE,
+                "cmf_epoch_plan_presorted: workspace of %zu bytes needed, %zu given", L.total,
+                workspace ? workspace_bytes : (size_t)0);
+  cudaStream_t s = (cudaStream_t)stream;
+  char* base = (char*)workspace;
+  uint32_t* kA = (uint32_t*)(base + L.kA);
+  uint32_t* kB = (uint32_t*)(base + L.kB);
+  uint32_t* vA = (uint32_t*)(base + L.vA);
+  uint32_t* vB = (uint32_t*)(base + L.vB);
+  // round keys of this (seed, epoch): splitmix64 on the host
+  FeistelKey fk;
+  uint64_t z = seed * 0x9e3779b97f4a7c15ull + ((uint64_t)epoch << 32 | 0x706c616eu);
+  for (int i = 0; i < 6; ++i) {
+    z += 0x9e3779b97f4a7c15ull;
+    uint64_t x = z;
+    x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ull;
+    x = (x ^ (x >> 27)) * 0x94d049bb133111ebull;
+    fk.k[i] = (uint32_t)((x ^ (x >> 31)) >> 16);
+  }
+  int bits = bits_for(n);
+  if (bits < 2) bits = 2;
+  fk.half_bits = (bits + 1) / 2;
+  const unsigned blocks = (unsigned)((n + 255) / 256);
+  k_plan_batch_of<<<blocks, 256, 0, s>>>(fk, n, batch, kA, vA);
+  CMF_LAUNCH_CHECK();
+  size_t temp = L.temp_bytes;
+  CMF_CUDA(cub::DeviceRadixSort::SortPairs(base + L.temp, temp, kA, kB, vA, vB, (int)n, 0,
+                                           bits_for((n + batch - 1) / batch), s));
+  k_plan_gather_rec<<<blocks, 256, 0, s>>>(vB, (const uint4*)rec, ratings, n, out_users, out_items,
+                                           out_ratings, out_gidx);
   CMF_LAUNCH_CHECK();
   return CMF_OK;
 }

@@ -238,6 +238,7 @@ def bench_sharded(args, rank, world, local_rank, workload, synth, config_dict, C
     """``bench.py --gpus N`` for N > 1: weak scaling (the per-GPU batch is fixed), device timing,
     max over ranks, one JSON line from rank 0."""
     import json
+    import os
     import collie_b200 as cb
     w = workload
     dev = torch.device('cuda', local_rank)
@@ -292,8 +293,10 @@ def bench_sharded(args, rank, world, local_rank, workload, synth, config_dict, C
     e0.record()
     import time as _time
     h0 = _time.perf_counter()
-    for _ in range(steps):
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+    for i_ in range(steps):
         loss = one_step()
+        marks[i_].record()
     host_ms = (_time.perf_counter() - h0) * 1e3      # host time to ISSUE the steps (no sync)
     e1.record()
     torch.cuda.synchronize()
@@ -303,23 +306,114 @@ def bench_sharded(args, rank, world, local_rank, workload, synth, config_dict, C
     ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms = float(ms.item())
+    step_ms = [e0.elapsed_time(marks[0])] + [marks[i_].elapsed_time(marks[i_ + 1])
+                                             for i_ in range(steps - 1)]
     launches = _abi.launch_count() - launches0
     dist.all_reduce(loss)
     value = steps * B * world / (ms * 1e-3)
+
+    # ---- end to end: this rank's batches come from pinned host memory every step (double-buffered
+    # copies on a side stream), the step's loss goes back to the host every step
+    from .interactions import DeviceBatch
+    n_local = data.num_interactions
+    g = torch.Generator().manual_seed(w['seed'] + rank)
+    perm = torch.randperm(n_local, generator=g)
+    users_h = torch.from_numpy(data.mat.row.astype(np.int32))[perm].contiguous().pin_memory()
+    items_h = torch.from_numpy(data.mat.col.astype(np.int32))[perm].contiguous().pin_memory()
+    gidx_h = torch.from_numpy(np.asarray(gpos, dtype=np.int64))[perm].contiguous().pin_memory()
+    n_batches = n_local // B
+    copy_stream = torch.cuda.Stream(dev)
+    main = torch.cuda.current_stream(dev)
+    slots = [dict(u=torch.empty(B, dtype=torch.int32, device=dev),
+                  i=torch.empty(B, dtype=torch.int32, device=dev),
+                  g=torch.empty(B, dtype=torch.int64, device=dev),
+                  ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(2)]
+    loss_host = torch.empty(steps + warmup, dtype=torch.float32).pin_memory()
+
+    def e2e_loop(count, base):
+        for s_ in slots:
+            s_['free'].record(main)
+        for j in range(count):
+            slot = slots[j % 2]
+            a = ((base + j) % n_batches) * B
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(slot['free'])
+                slot['u'].copy_(users_h[a:a + B], non_blocking=True)
+                slot['i'].copy_(items_h[a:a + B], non_blocking=True)
+                slot['g'].copy_(gidx_h[a:a + B], non_blocking=True)
+                slot['ready'].record(copy_stream)
+            main.wait_event(slot['ready'])
+            out = sharded.train_step(DeviceBatch(slot['u'], slot['i'], slot['g'], None, False),
+                                     opts, interactions=data, epoch=1, global_batch=world * B,
+                                     reduce_loss=True)
+            loss_host[base + j:base + j + 1].copy_(out.view(1), non_blocking=True)
+            slot['free'].record(main)
+
+    e2e_loop(warmup, 0)
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    e2e_loop(steps, warmup)
+    e1.record()
+    torch.cuda.synchronize()
+    dist.barrier()
+    e2e_ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+    e2e_ms = float(e2e_ms.item())
+
+    # ---- the local kernels of a step, timed by events inside the library (rank 0's numbers)
+    lib = _abi.lib()
+    lib.cmf_profile_enable(1)
+    prof_steps = min(steps, 20)
+    for _ in range(prof_steps):
+        one_step()
+    C = _abi.C
+    ms4 = (C.c_double * 4)()
+    split = C.c_int32()
+    n_steps, item_rows, user_rows = C.c_int64(), C.c_int64(), C.c_int64()
+    lib.cmf_profile_read(ms4, C.byref(split), C.byref(n_steps), C.byref(item_rows),
+                         C.byref(user_rows))
+    lib.cmf_profile_enable(0)
+    torch.cuda.synchronize()
     if rank == 0:
         D, N, T = w['dim'], w['n_neg'], 4
         exchange = 2 * padded * (D + 2) * T * (world - 1) / world   # all-gather + reduce-scatter
+        ns = max(1, n_steps.value)
+        gather_bytes = B * (2 + N) * D * T + B * (2 + N) * T + B * 2 * 4
+        kernel_ms = ms4[0] / ns
+        try:
+            peaks = json.load(open(os.path.join(os.path.dirname(os.path.dirname(
+                os.path.abspath(__file__))), 'MEASURED_PEAKS.json')))
+        except Exception:
+            peaks = {}
+        peak = float(peaks.get('hbm_gbs', 6650.0))
+        achieved = gather_bytes / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else 0.0
+        roofline = {
+            'bound': 'hbm', 'kernel': 'k_fwd_loss (rank 0)', 'achieved': achieved, 'peak': peak,
+            'unit': 'GB/s', 'frac': achieved / peak,
+            'peak_source': 'MEASURED_PEAKS.json hbm_gbs (of measured)' if peaks else
+                           'fallback 6650 GB/s (of fallback)',
+            'traffic': None, 'algorithmic_bytes_per_launch': gather_bytes, 'kernel_ms': kernel_ms,
+            'phase_ms': {'k_fwd_loss': ms4[0] / ns, 'sort_tail': ms4[1] / ns,
+                         'k_bwd_update': ms4[2] / ns, 'k_update_rows': ms4[3] / ns},
+        }
         line = {
             'metric': 'MF train interactions/s (fwd+bwd+sparse Adam)', 'value': value,
             'unit': 'interactions/s', 'n_gpus': world, 'steps': steps, 'warmup': warmup,
             'ms_per_step': ms / steps, 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': config_dict(world),
-            'roofline': None, 'cpu_baseline': None,
-            'e2e': None, 'gpu_launches': int(launches),
+            'roofline': roofline, 'cpu_baseline': None,
+            'e2e': {'value': steps * B * world / (e2e_ms * 1e-3), 'unit': 'interactions/s',
+                    'h2d_bytes_per_step': world * B * (4 + 4 + 8), 'd2h_bytes_per_step': 4 * world,
+                    'ms_per_step': e2e_ms / steps},
+            'gpu_launches': int(launches),
             'gpu_launches_note': 'rank 0; own kernels per step: k_fwd_loss + k_bwd_update + '
                                  'k_update_rows + k_optimizer_rows_masked (+ NCCL collectives)',
             'exchange_bytes_per_step_per_gpu': exchange,
             'host_issue_ms_per_step': host_ms / steps,
+            'step_ms_rank0': {'median': float(np.median(step_ms)), 'max': float(np.max(step_ms)),
+                              'slowest_step': int(np.argmax(step_ms))},
             'clocks': clk, 'final_loss': float(loss),
         }
         print(json.dumps(line), flush=True)

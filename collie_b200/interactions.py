@@ -142,6 +142,25 @@ class BaseInteractions(torch.utils.data.Dataset):
     def _extra_device_state(self, st, device):
         pass
 
+    def device_records_by_user(self, device):
+        """The dataset ordered by user (equal users in dataset order), built once per device:
+        ``rec[p] = (user, item, gidx low word, gidx high word)`` as int32 ``[n, 4]`` and the ratings
+        alongside (or ``None``); ``gidx`` = the entry's dataset position (``global_positions`` of
+        it when set). Input of ``cmf_epoch_plan_presorted``."""
+        st = self.device_state(device)
+        if 'rec_by_user' not in st:
+            users = st['users']
+            n = users.shape[0]
+            order = torch.sort(users.long(), stable=True)[1]
+            gidx = st['gpos'][order] if 'gpos' in st else order
+            rec = torch.empty((n, 4), dtype=torch.int32, device=users.device)
+            rec[:, 0] = users[order]
+            rec[:, 1] = st['items'][order]
+            rec[:, 2:] = gidx.contiguous().view(torch.int32).view(n, 2)   # little endian: low, high
+            st['rec_by_user'] = rec
+            st['ratings_by_user'] = st['ratings'][order].contiguous() if 'ratings' in st else None
+        return st['rec_by_user'], st['ratings_by_user']
+
 
 class Interactions(BaseInteractions):
     """Implicit interactions + negative sampling (datasets.py:196-445)."""
@@ -335,24 +354,34 @@ class BaseInteractionsDataLoader(object):
         gidx = torch.empty(n, dtype=torch.int64, device=device)
         ratings = torch.empty(n, dtype=torch.float32, device=device) if has_ratings else None
         if n > 0:
-            # the whole plan is one native call (cmf_epoch_plan: Philox keys -> radix sort = the
-            # permutation; (batch, user) keys -> radix sort; one gather)
+            # the whole plan is one native call
             lib = _abi.lib()
             need = int(lib.cmf_epoch_plan_workspace_bytes(n))
             ws = self._plan_ws.get(str(device)) if hasattr(self, '_plan_ws') else None
             if ws is None or ws.numel() < need:
                 ws = torch.empty(need, dtype=torch.uint8, device=device)
                 self._plan_ws = {str(device): ws}
+            seed = int(getattr(self.interactions, 'seed', 0) or 0) & (2 ** 64 - 1)
             with torch.cuda.device(device):
-                _abi.check(lib.cmf_epoch_plan(
-                    _abi.ptr(st['users']), _abi.ptr(st['items']),
-                    _abi.ptr(st['ratings']) if has_ratings else None, _abi.ptr(st.get('gpos')),
-                    n, b, int(self.num_users), int(bool(self.shuffle)),
-                    int(bool(sort_within_batch)),
-                    int(getattr(self.interactions, 'seed', 0) or 0) & (2 ** 64 - 1),
-                    int(epoch) & 0xFFFFFFFF, _abi.ptr(users), _abi.ptr(items), _abi.ptr(ratings),
-                    _abi.ptr(gidx), _abi.ptr(ws), ws.numel(), _abi.stream_ptr(device)),
-                    'cmf_epoch_plan')
+                if self.shuffle and sort_within_batch:
+                    # fast path: the entries ordered by user once per dataset, then per epoch a
+                    # keyed bijection picks every entry's batch and one stable radix partition
+                    # lays the batches out (already ordered by user)
+                    rec, rat = self.interactions.device_records_by_user(device)
+                    _abi.check(lib.cmf_epoch_plan_presorted(
+                        _abi.ptr(rec), _abi.ptr(rat), n, b, seed, int(epoch) & 0xFFFFFFFF,
+                        _abi.ptr(users), _abi.ptr(items), _abi.ptr(ratings), _abi.ptr(gidx),
+                        _abi.ptr(ws), ws.numel(), _abi.stream_ptr(device)),
+                        'cmf_epoch_plan_presorted')
+                else:
+                    _abi.check(lib.cmf_epoch_plan(
+                        _abi.ptr(st['users']), _abi.ptr(st['items']),
+                        _abi.ptr(st['ratings']) if has_ratings else None,
+                        _abi.ptr(st.get('gpos')), n, b, int(self.num_users),
+                        int(bool(self.shuffle)), int(bool(sort_within_batch)), seed,
+                        int(epoch) & 0xFFFFFFFF, _abi.ptr(users), _abi.ptr(items),
+                        _abi.ptr(ratings), _abi.ptr(gidx), _abi.ptr(ws), ws.numel(),
+                        _abi.stream_ptr(device)), 'cmf_epoch_plan')
         stop = (n // b) * b if self.drop_last else n
         for s in range(0, stop, b):
             e = min(s + b, n)

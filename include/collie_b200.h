@@ -211,6 +211,18 @@ CMF_API int cmf_epoch_plan(const int32_t *users, const int32_t *items, const flo
                    void *workspace, size_t workspace_bytes, void *stream);
 
 /*
+ * The same plan (shuffled, every batch ordered by user) when the dataset is handed over ordered by
+ * user: rec[p] = {user, item, gidx low word, gidx high word} (16 bytes) of the p-th entry in user
+ * order, ratings[p] alongside (or NULL). A keyed bijection of [0, n) sends entry p to batch
+ * sigma(p) / batch and one stable radix partition by batch number leaves every batch ordered by
+ * user (equal users in dataset order): no sort by user per epoch. Same workspace size.
+ */
+CMF_API int cmf_epoch_plan_presorted(const void *rec, const float *ratings, int64_t n, int64_t batch,
+                             uint64_t seed, uint32_t epoch, int32_t *out_users,
+                             int32_t *out_items, float *out_ratings, int64_t *out_gidx,
+                             void *workspace, size_t workspace_bytes, void *stream);
+
+/*
  * Row-wise optimizer on a table given a dense gradient table G [rows, D]:
  *   rows == NULL: every row (torch.optim.Adam / SGD / Adagrad on dense grads);
  *   rows != NULL: only the n_rows listed unique rows (torch.optim.SparseAdam on the coalesced

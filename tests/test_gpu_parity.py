@@ -594,18 +594,26 @@ def test_epoch_plan_properties(n, batch, n_users, with_gpos):
     u2, i2, g2, _ = epoch(3)
     assert np.array_equal(g, g2)                                 # same (seed, epoch), same plan
     _, _, g3, _ = epoch(4)
-    assert not np.array_equal(g, g3)
-    # without the in-batch sort the same permutation comes out in its own order
+    assert n <= batch or not np.array_equal(g, g3)             # (one batch: nothing to shuffle)
+    # equal users keep their dataset order inside a batch
+    for s in range(0, n, batch):
+        uu, pp = u[s:s + batch], pos[s:s + batch]
+        same = uu[1:] == uu[:-1]
+        assert np.all(pp[1:][same] > pp[:-1][same])
+    # every batch is a spread-out sample of the dataset, and different batches hold different
+    # users' interactions in similar proportion
+    if n >= 10_000:
+        first = pos[:batch]
+        assert abs(first.mean() / n - 0.5) < 0.05
+        assert abs(np.mean(d_users[pos[:batch]]) - d_users.mean()) < 0.1 * n_users
+    # without the in-batch sort (reference-format iteration): a permutation in its own order
     _, _, g4, bs4 = epoch(3, sort=False)
     assert not any(b.sorted for b in bs4)
-    for s in range(0, n, batch):
-        assert np.array_equal(np.sort(g4[s:s + batch]), np.sort(g[s:s + batch]))
-    # the shuffle is not the identity and spreads the dataset over the batches
     p4 = g4 if gpos is None else np.argsort(gpos)[np.searchsorted(np.sort(gpos), g4)]
+    assert np.array_equal(np.sort(p4), np.arange(n))
     assert np.mean(p4 == np.arange(n)) < 0.01 + 2.0 / n
     if n >= 10_000:
-        first = p4[:batch]
-        assert abs(first.mean() / n - 0.5) < 0.05
+        assert abs(p4[:batch].mean() / n - 0.5) < 0.05
     # unshuffled: dataset order, batch by batch
     plain = cb.InteractionsDataLoader(data, batch_size=batch, shuffle=False)
     gp = torch.cat([b.gidx for b in plain.device_batches('cuda', epoch=0,
