@@ -28,6 +28,17 @@ class cmf_opt_t(C.Structure):
                 ('weight_decay', C.c_double), ('step', C.c_int64)]
 
 
+CMF_MAX_PEERS = 8
+
+
+class cmf_peers_t(C.Structure):
+    _fields_ = [('rank', C.c_int32), ('world', C.c_int32), ('D', C.c_int32),
+                ('reserved', C.c_int32), ('rows_per_rank', C.c_int64),
+                ('I', C.c_void_p * CMF_MAX_PEERS), ('bi', C.c_void_p * CMF_MAX_PEERS),
+                ('GI', C.c_void_p * CMF_MAX_PEERS), ('gbi', C.c_void_p * CMF_MAX_PEERS),
+                ('flag', C.c_void_p * CMF_MAX_PEERS)]
+
+
 class cmf_step_t(C.Structure):
     _fields_ = [
         ('U', C.c_void_p), ('I', C.c_void_p), ('bu', C.c_void_p), ('bi', C.c_void_p),
@@ -100,6 +111,8 @@ SIGNATURES = {
     'cmf_optimizer_rows': (C.c_int, [C.c_void_p] * 4 + [C.c_int64, C.c_int32, C.c_void_p,
                                                        C.c_int64, C.POINTER(cmf_opt_t), C.c_int32,
                                                        C.c_void_p]),
+    'cmf_item_exchange_update': (C.c_int, [C.POINTER(cmf_peers_t)] + [C.c_void_p] * 4 +
+                                 [C.POINTER(cmf_opt_t), C.POINTER(cmf_opt_t), C.c_void_p]),
     'cmf_eval_workspace_bytes': (C.c_size_t, [C.c_int64, C.c_int64, C.c_int32, C.c_int32,
                                               C.c_int32]),
     'cmf_eval_tile': (C.c_int, [C.POINTER(cmf_eval_t), C.c_void_p]),

@@ -47,6 +47,17 @@ inline OptDev make_opt(const cmf_opt_t& o) {
   return d;
 }
 
+inline int validate_opt(const cmf_opt_t& o, const char* which, const float* m, const float* v) {
+  CMF_REQUIRE(o.rule >= CMF_OPT_SPARSE_ADAM && o.rule <= CMF_OPT_ADAGRAD,
+              "cmf_train_step: unknown %s optimizer rule %d", which, o.rule);
+  const bool need_m = o.rule != CMF_OPT_SGD;
+  const bool need_v = o.rule == CMF_OPT_SPARSE_ADAM || o.rule == CMF_OPT_ADAM;
+  CMF_REQUIRE(!need_m || m, "cmf_train_step: %s optimizer needs its first state tensor", which);
+  CMF_REQUIRE(!need_v || v, "cmf_train_step: %s optimizer needs its second state tensor", which);
+  CMF_REQUIRE(o.step >= 1, "cmf_train_step: %s optimizer step must be >= 1", which);
+  return CMF_OK;
+}
+
 // sqrt / division of the update term with the SFU approximations (<= 2 ulp each): the term is
 // multiplied by lr before it touches the parameter, so the parameter moves by < 1e-9 relative.
 __device__ __forceinline__ float fast_sqrt(float x) { return x > 0.f ? x * rsqrtf(x) : 0.f; }

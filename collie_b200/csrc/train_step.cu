@@ -492,17 +492,6 @@ static int chunk_len(int64_t B, int G) {
   return L;
 }
 
-static int validate_opt(const cmf_opt_t& o, const char* which, const float* m, const float* v) {
-  CMF_REQUIRE(o.rule >= CMF_OPT_SPARSE_ADAM && o.rule <= CMF_OPT_ADAGRAD,
-              "cmf_train_step: unknown %s optimizer rule %d", which, o.rule);
-  const bool need_m = o.rule != CMF_OPT_SGD;
-  const bool need_v = o.rule == CMF_OPT_SPARSE_ADAM || o.rule == CMF_OPT_ADAM;
-  CMF_REQUIRE(!need_m || m, "cmf_train_step: %s optimizer needs its first state tensor", which);
-  CMF_REQUIRE(!need_v || v, "cmf_train_step: %s optimizer needs its second state tensor", which);
-  CMF_REQUIRE(o.step >= 1, "cmf_train_step: %s optimizer step must be >= 1", which);
-  return CMF_OK;
-}
-
 }  // namespace cmf
 
 using namespace cmf;

@@ -89,9 +89,18 @@ class ShardedMatrixFactorization(object):
     ``shard_rows``); ``model.hparams.num_items`` is the padded count.
     """
 
-    def __init__(self, model, true_num_items, group=None):
+    def __init__(self, model, true_num_items, group=None, exchange='auto', max_batch=None,
+                 max_negatives=None):
+        """``exchange``: ``'p2p'`` = the owner-side kernel over peer memory
+        (``cmf_item_exchange_update``; needs NCCL ranks of one node and symmetric memory),
+        ``'nccl'`` = all-gather / reduce-scatter collectives, ``'auto'`` = p2p when it can be set
+        up. ``max_batch`` / ``max_negatives`` size the symmetric training workspace of the p2p
+        mode (default: the first step's batch, over all ranks, plus 25 %)."""
         self.model = model
         self.group = group
+        self.exchange = exchange
+        self._max_batch, self._max_negatives = max_batch, max_negatives
+        self._p2p = None
         self.rank = dist.get_rank(group)
         self.world = dist.get_world_size(group)
         self.per_rank, padded = shard_rows(true_num_items, self.world)
@@ -109,6 +118,136 @@ class ShardedMatrixFactorization(object):
         # every rank starts from rank 0's item table (user tables are disjoint)
         dist.broadcast(self.I_full, src=self._global_rank(0), group=group)
         dist.broadcast(self.bi_full, src=self._global_rank(0), group=group)
+        if exchange not in ('auto', 'p2p', 'nccl'):
+            raise ValueError("exchange must be 'auto', 'p2p' or 'nccl'")
+        if exchange != 'nccl':
+            self._setup_tables_p2p()
+
+    # ---- peer-memory exchange ---------------------------------------------------------------
+    def _symm(self):
+        import torch.distributed._symmetric_memory as symm
+        return symm
+
+    def _setup_tables_p2p(self):
+        """Move the item table and biases into symmetric memory (every rank maps every rank's
+        copy). Falls back to the collectives in 'auto' mode when that is not possible."""
+        try:
+            if dist.get_backend(self.group) != 'nccl' or not self.I_full.is_cuda:
+                raise RuntimeError('the p2p exchange needs NCCL ranks on CUDA devices')
+            if self.world > _abi.CMF_MAX_PEERS:
+                raise RuntimeError(f'the p2p exchange takes at most {_abi.CMF_MAX_PEERS} ranks')
+            symm = self._symm()
+            grp = self.group if self.group is not None else dist.group.WORLD
+            m = self.model
+            I_sym = symm.empty(tuple(self.I_full.shape), dtype=torch.float32,
+                               device=self.I_full.device)
+            bi_sym = symm.empty(tuple(self.bi_full.shape), dtype=torch.float32,
+                                device=self.I_full.device)
+            hI, hb = symm.rendezvous(I_sym, grp), symm.rendezvous(bi_sym, grp)
+            I_sym.copy_(self.I_full)
+            bi_sym.copy_(self.bi_full)
+            m.item_embeddings.weight.data = I_sym
+            m.item_biases.weight.data = bi_sym
+            self.I_full, self.bi_full = I_sym, bi_sym
+            lo, hi = self.rank * self.per_rank, (self.rank + 1) * self.per_rank
+            self.I_shard, self.bi_shard = I_sym[lo:hi], bi_sym[lo:hi]
+            self._p2p = {'I': [int(p) for p in hI.buffer_ptrs],
+                         'bi': [int(p) for p in hb.buffer_ptrs], 'handles': [hI, hb]}
+            self._tick = torch.zeros(1, dtype=torch.float32, device=self.I_full.device)
+        except Exception as e:
+            if self.exchange == 'p2p':
+                raise _abi.CmfError(f'p2p exchange unavailable: {e}')
+            self._p2p = None
+
+    def _setup_workspace_p2p(self, batch, n_neg):
+        """The training workspace in symmetric memory (collective: every rank calls it at its
+        first step); records every rank's accumulator addresses."""
+        m, h = self.model, self.model.hparams
+        symm = self._symm()
+        grp = self.group if self.group is not None else dist.group.WORLD
+        dev = self.I_full.device
+        want = torch.tensor([int(self._max_batch or int(batch * 1.25) + 1),
+                             int(self._max_negatives or n_neg)], dtype=torch.int64, device=dev)
+        dist.all_reduce(want, op=dist.ReduceOp.MAX, group=self.group)
+        cap_b, cap_n = int(want[0].item()), int(want[1].item())
+        need = torch.tensor([int(_abi.lib().cmf_train_workspace_bytes(
+            cap_b, cap_n, h.num_users, h.num_items, h.embedding_dim))], dtype=torch.int64,
+            device=dev)
+        dist.all_reduce(need, op=dist.ReduceOp.MAX, group=self.group)
+        ws = symm.empty(int(need.item()), dtype=torch.uint8, device=dev)
+        hw = symm.rendezvous(ws, grp)
+        _abi.check(_abi.lib().cmf_workspace_init(_abi.ptr(ws), ws.numel(), _abi.stream_ptr(dev)),
+                   'cmf_workspace_init')
+        m._workspace, m._workspace_B = ws, cap_b
+        C = _abi.C
+        GI, gbi, flag = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        _abi.check(_abi.lib().cmf_train_workspace_items(
+            _abi.ptr(ws), h.num_users, h.num_items, h.embedding_dim, C.byref(GI), C.byref(gbi),
+            C.byref(flag)), 'cmf_train_workspace_items')
+        base = ws.data_ptr()
+        # the layout depends on the local user count, which differs between ranks by one
+        offs = torch.tensor([GI.value - base, gbi.value - base, flag.value - base],
+                            dtype=torch.int64, device=dev)
+        all_offs = [torch.zeros_like(offs) for _ in range(self.world)]
+        dist.all_gather(all_offs, offs, group=self.group)
+        bases = [int(p) for p in hw.buffer_ptrs]
+        self._p2p.update(
+            GI=[bases[q] + int(all_offs[q][0]) for q in range(self.world)],
+            gbi=[bases[q] + int(all_offs[q][1]) for q in range(self.world)],
+            flag=[bases[q] + int(all_offs[q][2]) for q in range(self.world)],
+            cap=(cap_b, cap_n), ws=ws)
+        self._p2p['handles'].append(hw)
+        peers = _abi.cmf_peers_t()
+        peers.rank, peers.world, peers.D = self.rank, self.world, int(h.embedding_dim)
+        peers.rows_per_rank = self.per_rank
+        for q in range(self.world):
+            peers.I[q], peers.bi[q] = self._p2p['I'][q], self._p2p['bi'][q]
+            peers.GI[q], peers.gbi[q] = self._p2p['GI'][q], self._p2p['gbi'][q]
+            peers.flag[q] = self._p2p['flag'][q]
+        self._p2p['peers'] = peers
+
+    def _fence(self):
+        """Stream-ordered rendezvous of all ranks: nobody's later work starts before everybody's
+        earlier work is done (a one-element all-reduce: each rank's result needs each rank's
+        input)."""
+        dist.all_reduce(self._tick, group=self.group)
+
+    def _train_step_p2p(self, batch, optimizers, main, bias, st, interactions, epoch, global_batch,
+                        reduce_loss):
+        m = self.model
+        B = int(batch.users.shape[0])
+        n_neg = int(getattr(interactions, 'num_negative_samples', 0) or 0)
+        if 'peers' not in self._p2p:
+            self._setup_workspace_p2p(B, n_neg)
+        cap_b, cap_n = self._p2p['cap']
+        if B > cap_b or n_neg > cap_n or m._workspace is not self._p2p['ws']:
+            raise _abi.CmfError(
+                f'batch of {B} x {n_neg} negatives exceeds the symmetric training workspace '
+                f'({cap_b} x {cap_n}); pass max_batch / max_negatives to '
+                'ShardedMatrixFactorization')
+        loss = m.fused_step(batch, optimizers=optimizers, interactions=interactions, epoch=epoch,
+                            global_batch=int(global_batch), skip_item_update=True,
+                            num_items_logical=self.true_num_items)
+        if m._workspace is not self._p2p['ws']:
+            raise _abi.CmfError('the model replaced its symmetric training workspace')
+        # every rank's accumulators are complete ...
+        if reduce_loss:
+            dist.all_reduce(loss, group=self.group)     # (doubles as the rendezvous)
+        else:
+            self._fence()
+        self._step += 1
+        g_main, g_bias = main.param_groups[0], bias.param_groups[0]
+        o = _abi.make_opt(main.rule, g_main['lr'], self._step, g_main.get('betas', (0.9, 0.999)),
+                          g_main.get('eps', 1e-8), 0.0)
+        ob = _abi.make_opt(bias.rule, g_bias['lr'], self._step, g_bias.get('betas', (0.9, 0.999)),
+                           g_bias.get('eps', 1e-8), 0.0)
+        _abi.check(_abi.lib().cmf_item_exchange_update(
+            _abi.C.byref(self._p2p['peers']), _abi.ptr(st['m']), _abi.ptr(st['v']),
+            _abi.ptr(st['bm']), _abi.ptr(st['bv']), o, ob, _abi.stream_ptr(self.I_full.device)),
+            'cmf_item_exchange_update')
+        # ... and every rank's table copy is complete before anybody's next step reads it
+        self._fence()
+        return loss
 
     def _global_rank(self, r):
         return dist.get_global_rank(self.group, r) if self.group is not None else r
@@ -164,6 +303,9 @@ class ShardedMatrixFactorization(object):
                              device=self.I_full.device)
             dist.all_reduce(t, group=self.group)
             global_batch = int(t.item())
+        if self._p2p is not None:
+            return self._train_step_p2p(batch, optimizers, main, bias, st, interactions, epoch,
+                                        global_batch, reduce_loss)
         # 1. everyone gets the current item rows
         all_gather_rows(self.I_full, self.I_shard, self.group)
         all_gather_rows(self.bi_full.view(-1), self.bi_shard.reshape(-1), self.group)
@@ -198,6 +340,8 @@ class ShardedMatrixFactorization(object):
 
     def gather_item_table(self):
         """The up-to-date, unpadded item table and biases on every rank (for checkpoints / eval)."""
+        if self._p2p is not None:      # the owners already stored their rows everywhere
+            return self.I_full[:self.true_num_items], self.bi_full[:self.true_num_items]
         all_gather_rows(self.I_full, self.I_shard, self.group)
         all_gather_rows(self.bi_full.view(-1), self.bi_shard.reshape(-1), self.group)
         return self.I_full[:self.true_num_items], self.bi_full[:self.true_num_items]

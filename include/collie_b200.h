@@ -247,6 +247,30 @@ CMF_API int cmf_optimizer_rows_masked(float *P, float *M, float *V, const float 
                               const cmf_opt_t *bias_opt, void *stream);
 
 /*
+ * Item-side exchange of a data-parallel step (users partitioned over the ranks, item table
+ * row-sharded in contiguous blocks of rows_per_rank), done by the owner of each row in ONE kernel
+ * over peer memory: sum the ranks' gradient rows (GI / gbi, read out of every rank's training
+ * workspace, only where that rank's item_flag is set), apply the rule to the owned rows (state
+ * M / V / bM / bV are [rows_per_rank, D] / [rows_per_rank], local), store the new rows into every
+ * rank's table copy I / bi and clear the accumulators that were consumed. All pointers of rank q
+ * must be addresses valid in THIS process (peer mappings). The caller orders it across ranks:
+ * all ranks' cmf_train_step(skip_item_update) before, all ranks' next step after.
+ * Replaces the gradient all-reduce + replicated optimizer.step of Lightning DDP around
+ * collie/model/base/trainer.py:463-470.
+ */
+#define CMF_MAX_PEERS 8
+typedef struct cmf_peers_t {
+  int32_t rank, world;
+  int32_t D, reserved;
+  int64_t rows_per_rank;
+  float *I[CMF_MAX_PEERS], *bi[CMF_MAX_PEERS];
+  float *GI[CMF_MAX_PEERS], *gbi[CMF_MAX_PEERS];
+  int32_t *flag[CMF_MAX_PEERS];
+} cmf_peers_t;
+CMF_API int cmf_item_exchange_update(const cmf_peers_t *peers, float *M, float *V, float *bM, float *bV,
+                             const cmf_opt_t *opt, const cmf_opt_t *bias_opt, void *stream);
+
+/*
  * Evaluation of one tile of users against the whole item table (or an item shard):
  * scores S = U[user_ids] . I^T + bu + bi are never written to HBM; per user the kernel keeps the
  * top-k (score descending, item id ascending), and -- given the users' target items in CSR form --

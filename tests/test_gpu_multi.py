@@ -33,6 +33,19 @@ def _rank_main(rank, world, port, ret):
     dev = torch.device('cuda', rank)
     dist.init_process_group('nccl', rank=rank, world_size=world, device_id=dev)
     try:
+        for mode in ('nccl', 'p2p'):
+            _check_mode(mode, rank, world, dev, dist, cb, D, DeviceBatch)
+        ret[rank] = 'ok'
+    except Exception as e:  # pragma: no cover
+        import traceback
+        ret[rank] = traceback.format_exc()
+    finally:
+        dist.destroy_process_group()
+
+
+def _check_mode(mode, rank, world, dev, dist, cb, D, DeviceBatch):
+    """mode: how the item side is exchanged ('nccl' collectives or the 'p2p' owner-side kernel)."""
+    if True:
         n_users, n_items, dim, n_neg, steps = 61, 45, 32, 4, 3     # 45 items -> padded to 46
         rng = np.random.default_rng(7)                              # identical on every rank
         flat = rng.choice(n_users * n_items, size=1500, replace=False)
@@ -67,7 +80,8 @@ def _rank_main(rank, world, port, ret):
             if rank == 0:       # rank 0's item table is broadcast by the wrapper
                 model.item_embeddings.weight[:n_items].copy_(ref.item_embeddings.weight)
                 model.item_biases.weight[:n_items].copy_(ref.item_biases.weight)
-        sharded = D.ShardedMatrixFactorization(model, n_items)
+        sharded = D.ShardedMatrixFactorization(model, n_items, exchange=mode)
+        assert (sharded._p2p is not None) == (mode == 'p2p')
         opts = model.configure_optimizers()
         st_full, st_loc = full.device_state(dev), local.device_state(dev)
         for step in range(steps):
@@ -80,14 +94,15 @@ def _rank_main(rank, world, port, ret):
             lb = DeviceBatch(st_loc['users'][lsel], st_loc['items'][lsel], st_loc['gpos'][lsel], None)
             loss = sharded.train_step(lb, opts, interactions=local, epoch=step)
             np.testing.assert_allclose(loss.item(), ref_loss.item(), rtol=1e-5)
+        # (fp32 sums of the same contributions in a different order, then Adam's normalisation)
         I, bi = sharded.gather_item_table()
         np.testing.assert_allclose(I.cpu().numpy(), ref.item_embeddings.weight.detach().cpu().numpy(),
-                                   rtol=1e-5, atol=1e-6)
+                                   rtol=1e-4, atol=1e-5)
         np.testing.assert_allclose(bi.cpu().numpy(), ref.item_biases.weight.detach().cpu().numpy(),
-                                   rtol=1e-5, atol=1e-6)
+                                   rtol=1e-4, atol=1e-5)
         np.testing.assert_allclose(model.user_embeddings.weight.detach().cpu().numpy(),
                                    ref.user_embeddings.weight[mine].detach().cpu().numpy(),
-                                   rtol=1e-5, atol=1e-6)
+                                   rtol=1e-4, atol=1e-5)
         # user-sharded evaluation == single-GPU evaluation
         test_flat = rng.choice(n_users * n_items, size=300, replace=False)
         tu, ti = test_flat // n_items, test_flat % n_items
@@ -99,12 +114,6 @@ def _rank_main(rank, world, port, ret):
                                    num_items=n_items, **kw)
         got = D.evaluate_sharded([cb.mapk, cb.mrr, cb.auc], test_loc, model, k=5)
         np.testing.assert_allclose(got, exp, rtol=1e-5)
-        ret[rank] = 'ok'
-    except Exception as e:  # pragma: no cover
-        import traceback
-        ret[rank] = traceback.format_exc()
-    finally:
-        dist.destroy_process_group()
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs 2 GPUs')
