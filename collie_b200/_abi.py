@@ -36,7 +36,9 @@ class cmf_peers_t(C.Structure):
                 ('reserved', C.c_int32), ('rows_per_rank', C.c_int64),
                 ('I', C.c_void_p * CMF_MAX_PEERS), ('bi', C.c_void_p * CMF_MAX_PEERS),
                 ('GI', C.c_void_p * CMF_MAX_PEERS), ('gbi', C.c_void_p * CMF_MAX_PEERS),
-                ('flag', C.c_void_p * CMF_MAX_PEERS)]
+                ('flag', C.c_void_p * CMF_MAX_PEERS),
+                ('mc_I', C.c_void_p), ('mc_bi', C.c_void_p), ('mc_GI', C.c_void_p),
+                ('mc_gbi', C.c_void_p), ('mc_flag', C.c_void_p)]
 
 
 class cmf_step_t(C.Structure):

@@ -48,10 +48,12 @@ static WsLayout ws_layout(int64_t B, int64_t num_users, int64_t num_items, int D
   WsLayout w;
   size_t o = 0;
   auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes, 256); return at; };
+  // item side first: its offsets depend only on (num_items, D), so they are the same on every
+  // rank of a user-partitioned job (the multicast view of the workspaces relies on that)
   w.item_flag = take(sizeof(int) * num_items);
-  w.user_flag = take(sizeof(int) * num_users);
   w.GI = take(sizeof(float) * num_items * D);
   w.gbi = take(sizeof(float) * num_items);
+  w.user_flag = take(sizeof(int) * num_users);
   w.GU = take(sizeof(float) * num_users * D);
   w.gbu = take(sizeof(float) * num_users);
   w.persistent_end = o;

@@ -253,7 +253,8 @@ CMF_API int cmf_optimizer_rows_masked(float *P, float *M, float *V, const float 
  * workspace, only where that rank's item_flag is set), apply the rule to the owned rows (state
  * M / V / bM / bV are [rows_per_rank, D] / [rows_per_rank], local), store the new rows into every
  * rank's table copy I / bi and clear the accumulators that were consumed. All pointers of rank q
- * must be addresses valid in THIS process (peer mappings). The caller orders it across ranks:
+ * must be addresses valid in THIS process (peer mappings), at the same offset of equally sized
+ * buffers when the multicast addresses are given. The caller orders it across ranks:
  * all ranks' cmf_train_step(skip_item_update) before, all ranks' next step after.
  * Replaces the gradient all-reduce + replicated optimizer.step of Lightning DDP around
  * collie/model/base/trainer.py:463-470.
@@ -266,6 +267,11 @@ typedef struct cmf_peers_t {
   float *I[CMF_MAX_PEERS], *bi[CMF_MAX_PEERS];
   float *GI[CMF_MAX_PEERS], *gbi[CMF_MAX_PEERS];
   int32_t *flag[CMF_MAX_PEERS];
+  /* NVSwitch multicast addresses of the same five buffers (one address = that offset in every
+   * rank's buffer), or all NULL: with them the sums are multimem.ld_reduce (reduced in the
+   * switch) and the stores multimem.st, so the kernel's NVLink traffic does not grow with world */
+  float *mc_I, *mc_bi, *mc_GI, *mc_gbi;
+  int32_t *mc_flag;
 } cmf_peers_t;
 CMF_API int cmf_item_exchange_update(const cmf_peers_t *peers, float *M, float *V, float *bM, float *bV,
                              const cmf_opt_t *opt, const cmf_opt_t *bias_opt, void *stream);
