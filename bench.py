@@ -187,7 +187,8 @@ def config_dict(n_gpus):
             'num_negative_samples': w['n_neg'], 'loss': 'bpr (adaptive_bpr, N=5)',
             'optimizer': 'sparse_adam + sgd bias', 'batch_per_gpu': w['batch_per_gpu'],
             'global_batch': w['batch_per_gpu'] * n_gpus,
-            'parallelism': f'user-partitioned data parallel x{n_gpus}, item table row-sharded'
+            'parallelism': f'user-partitioned data parallel x{n_gpus}, item table row-sharded, '
+                           'item-side exchange in one kernel over NVLink peer memory'
             if n_gpus > 1 else 'single GPU',
             'l2': 'tables + Adam state = 255 MB > 126 MB L2; every step reads a new batch',
             'timed_region': 'K training steps incl. the device-side epoch plan (shuffle + per-batch '
@@ -424,15 +425,16 @@ def run_ours(args, rank, world, local_rank):
         torch.cuda.synchronize()
         api_tc_s = time.perf_counter() - t0
         flops = 2.0 * n_eval_users * w['num_items'] * w['dim']
-        kp = ((3 * w['dim'] + 4 + 63) // 64) * 64
+        kp = ((3 * w['dim'] + 4 + 15) // 16) * 16       # K = 16 steps that are issued
         issued = 2.0 * n_eval_users * w['num_items'] * kp
         tpeak = float(peaks.get('bf16_tflops', 1590.0))
         eval_info = {
             'metric': 'eval users/s MAP@10', 'value': n_eval_users / (tc_ms * 1e-3),
             'unit': 'users/s', 'users': n_eval_users,
-            'path': 'cmf_eval_tile precision=1: tcgen05/TMA GEMM over bf16-split operands '
-                    '(hi.hi + hi.lo + lo.hi), top-k + MRR counter in the epilogue; device time of '
-                    'the whole call (operand split, GEMM + top-k, merge)',
+            'path': 'cmf_eval_tile precision=1, MAP@10 + MRR: tcgen05/TMA GEMM over bf16-split '
+                    'operands (hi.hi + hi.lo + lo.hi), top-k + MRR counter in the epilogue; device '
+                    'time of the whole call (operand split, exact target scores, GEMM + top-k, '
+                    'merge)',
             'ms': tc_ms, 'map10': map10,
             'roofline': {'bound': 'tensor', 'achieved': issued / (tc_ms * 1e-3) / 1e12,
                          'useful_tflops': flops / (tc_ms * 1e-3) / 1e12, 'peak': tpeak,

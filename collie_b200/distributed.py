@@ -6,18 +6,26 @@ The reference has no multi-GPU code of its own; this is the B200 de
   interactions of its own users, so user rows, their Adam moments and biases are always local and
   are finished in place by the fused step -- no user-side communication at all;
 * **the item table is row-sharded** (contiguous blocks of ``ceil(I / world)`` rows, padded): every
-  rank owns one block of rows with its optimizer state. One step =
-    1. ``all_gather`` of the item rows (+ biases) into each rank's full-width working copy,
-    2. the local fused step on the rank's batch (``skip_item_update``: item-row gradients, bias
+  rank owns one block of rows with its optimizer state and keeps a full-width working copy for
+  its gathers. One step =
+    1. the local fused step on the rank's batch (``skip_item_update``: item-row gradients, bias
        gradients and "touched" flags stay in the step's workspace; the loss and the gradients are
        scaled for the GLOBAL batch of ``world * B`` interactions),
-    3. ``reduce_scatter`` (sum) of the three item-side accumulators to the owners,
-    4. the owner's masked row update (``cmf_optimizer_rows_masked``: SparseAdam moves every row some
-       rank gathered) and a clear of the local accumulators.
-  With MovieLens-like catalogues every step touches nearly every item row, so dense collectives over
-  NVLink are the right exchange (13.7 MB per direction per step at the 20M shape); a catalogue
-  whose steps touch a small fraction of the rows would swap 1 and 3 for all-to-all(v) of the
-  de-duplicated row lists -- same ownership, same owner-side update.
+    2. a fence (all ranks' accumulators are complete),
+    3. ``cmf_item_exchange_update``: ONE kernel over peer memory in which the owner of a row sums
+       the ranks' gradient rows out of their workspaces, applies the rule to its shard (SparseAdam
+       moves every row some rank gathered), stores the new row into every rank's copy and clears
+       what it consumed -- plain peer loads / stores for two ranks, NVSwitch multicast
+       (``multimem.ld_reduce`` / ``multimem.st``) for more,
+    4. a fence (all copies are complete before anybody's next forward).
+  Tables and workspaces live in symmetric memory (``torch.distributed._symmetric_memory``); the
+  fence is its signal-pad barrier. ``exchange='nccl'`` (and any backend without peer memory, e.g.
+  gloo in the CPU tests) uses collectives instead: ``all_gather`` of the item rows, the local step,
+  ``reduce_scatter`` of the three accumulators, the owner's ``cmf_optimizer_rows_masked``.
+  With MovieLens-like catalogues every step touches nearly every item row, so a dense exchange is
+  the right one (13.7 MB per direction per step at the 20M shape); a catalogue whose steps touch a
+  small fraction of the rows would exchange de-duplicated row lists -- same ownership, same
+  owner-side update.
 
 Global semantics: one batch of ``world * B`` interactions per step, one optimizer step per unique
 row. Negatives are keyed by the interaction's global dataset position, so they do not depend on the
