@@ -419,11 +419,19 @@ def run_ours(args, rank, world, local_rank):
         m_all = cb.evaluate_in_batches([cb.mapk, cb.mrr, cb.auc], test, model, k=10, verbose=False)
         torch.cuda.synchronize()
         api_exact_s = time.perf_counter() - t0
+        # wall clock of the public call, results on the host: the first call on a test set (derives
+        # its device-side form) and a later one (every following epoch's validation)
         t0 = time.perf_counter()
         m_tc = cb.evaluate_in_batches([cb.mapk, cb.mrr], test, model, k=10, verbose=False,
                                       precision=1)
         torch.cuda.synchronize()
-        api_tc_s = time.perf_counter() - t0
+        api_tc_first_s = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        for _ in range(3):
+            m_tc = cb.evaluate_in_batches([cb.mapk, cb.mrr], test, model, k=10, verbose=False,
+                                          precision=1)
+        torch.cuda.synchronize()
+        api_tc_s = (time.perf_counter() - t0) / 3
         flops = 2.0 * n_eval_users * w['num_items'] * w['dim']
         kp = ((3 * w['dim'] + 4 + 15) // 16) * 16       # K = 16 steps that are issued
         issued = 2.0 * n_eval_users * w['num_items'] * kp
@@ -443,6 +451,8 @@ def run_ours(args, rank, world, local_rank):
                                  'slots); useful = 2 * users * items * D'},
             'api_users_per_s': {'evaluate_in_batches([mapk, mrr], precision=1)':
                                 n_eval_users / api_tc_s,
+                                'evaluate_in_batches([mapk, mrr], precision=1), first call':
+                                n_eval_users / api_tc_first_s,
                                 'evaluate_in_batches([mapk, mrr, auc]) exact fp32':
                                 n_eval_users / api_exact_s},
             'metrics_exact': m_all, 'metrics_tc': m_tc,

@@ -19,7 +19,7 @@ from .interactions import Interactions
 # users per fused tile; the result does not depend on it (per-user values are summed)
 _TILE_USERS = 256
 _MAX_TILE_BYTES = 1 << 30
-_TC_TILE_USERS = 8192   # users per tensor-core call (128-user CTA tiles inside)
+_TC_TILE_USERS = 32768   # users per tensor-core call (128-user CTA tiles inside)
 
 
 def _targets_device(targets: csr_matrix, user_ids, device):
@@ -192,8 +192,17 @@ def evaluate_in_batches(metric_list, test_interactions, model, k=10, batch_size=
     model._move_any_external_data_to_device()
     device = model.device
 
-    test_users = np.unique(test_interactions.mat.row)
-    targets = test_interactions.mat.tocsr()
+    # the test set in the form the kernels take it (users with targets, their targets as CSR on
+    # the device) is derived once per Interactions object and device: a validation set is evaluated
+    # every epoch, and the host-side derivation costs far more than the evaluation itself
+    cache = test_interactions.__dict__.setdefault('_cmf_eval_cache', {})
+    key = (str(device), id(test_interactions.mat), test_interactions.mat.nnz)
+    if cache.get('key') != key:
+        cache.clear()
+        cache['key'] = key
+        cache['test_users'] = np.unique(test_interactions.mat.row)
+        cache['targets'] = test_interactions.mat.tocsr()
+    test_users, targets = cache['test_users'], cache['targets']
     n_items = test_interactions.num_items
     n_test = len(test_users)
     names = [_FUSED.get(m) for m in metric_list]
@@ -202,8 +211,10 @@ def evaluate_in_batches(metric_list, test_interactions, model, k=10, batch_size=
         if 'mapk' in names:
             _check_k(k, n_items)
         tables = _model_tables(model)
-        indptr, tgt_items, nnz = _targets_all_users_device(targets, test_users, device)
-        users_dev = torch.from_numpy(test_users.astype(np.int32)).to(device)
+        if 'dev' not in cache:
+            cache['dev'] = _targets_all_users_device(targets, test_users, device) + (
+                torch.from_numpy(test_users.astype(np.int32)).to(device),)
+        indptr, tgt_items, nnz, users_dev = cache['dev']
         D = tables[0].shape[1]
         # tensor-core route for what it supports (top-k / MAP / MRR); AUC stays on the exact path
         use_tc = precision == 1 and D <= 128 and k <= 16
