@@ -100,6 +100,8 @@ SIGNATURES = {
                                       C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
                                       C.POINTER(C.c_float), C.c_void_p, C.c_void_p, C.c_void_p,
                                       C.c_void_p, C.c_void_p]),
+    'cmf_row_similarity': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p,
+                                    C.c_void_p]),
     'cmf_sample_negatives': (C.c_int, [C.c_uint64, C.c_uint32, C.c_void_p, C.c_int64, C.c_void_p,
                                        C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
                                        C.c_int32, C.c_void_p, C.c_void_p]),

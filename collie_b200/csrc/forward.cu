@@ -114,6 +114,59 @@ extern "C" int cmf_forward_scores(const float* U, const float* I, const float* b
   return CMF_OK;
 }
 
+// ---- cosine similarity of one row against every row of a table
+// (BasePipeline._calculate_embedding_similarity, collie/model/base/base_pipeline.py:849-859:
+//  rows are divided by their L2 norm, then dotted with the normalised seed row)
+template <int V, int G, int R>
+__global__ void __launch_bounds__(256)
+k_row_similarity(const float* __restrict__ E, int64_t rows, int D, int64_t id,
+                 float* __restrict__ out) {
+  constexpr int kGroups = 256 / G;
+  const int lane_w = threadIdx.x & 31;
+  const int l = threadIdx.x & (G - 1);
+  const unsigned mask = group_mask<G>(lane_w);
+  const int64_t group = (int64_t)blockIdx.x * kGroups + threadIdx.x / G;
+  const int64_t n_groups = (int64_t)gridDim.x * kGroups;
+  Row<V, G, R> seed;
+  seed.load(E + id * D, D, l);
+  float sn = seed.dot(seed);
+#pragma unroll
+  for (int o = G / 2; o > 0; o >>= 1) sn += __shfl_xor_sync(mask, sn, o);
+  sn = sqrtf(sn);
+#pragma unroll
+  for (int i = 0; i < R * V; ++i) seed.f[i] = seed.f[i] / sn;
+  for (int64_t r = group; r < rows; r += n_groups) {
+    Row<V, G, R> x;
+    x.load(E + r * D, D, l);
+    float n = x.dot(x);
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) n += __shfl_xor_sync(mask, n, o);
+    n = sqrtf(n);
+    float acc = 0.f;
+#pragma unroll
+    for (int i = 0; i < R * V; ++i) acc = fmaf(x.f[i] / n, seed.f[i], acc);
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) acc += __shfl_xor_sync(mask, acc, o);
+    if (l == 0) out[r] = acc;
+  }
+}
+
+extern "C" int cmf_row_similarity(const float* E, int64_t rows, int32_t D, int64_t id, float* out,
+                                  void* stream) {
+  CMF_REQUIRE(E && out, "cmf_row_similarity: null pointer");
+  CMF_REQUIRE(geom_supported(D), "cmf_row_similarity: embedding_dim %d unsupported (1..1024)", D);
+  CMF_REQUIRE(id >= 0 && id < rows, "cmf_row_similarity: id %lld is not a row of the table",
+              (long long)id);
+  const RowGeom g = row_geom(D);
+  cudaStream_t s = (cudaStream_t)stream;
+  const int grid = grid_for(rows, g.G);
+#define CALL(V_, G_, R_) k_row_similarity<V_, G_, R_><<<grid, 256, 0, s>>>(E, rows, D, id, out)
+  CMF_DISPATCH_GEOM(g, CALL);
+#undef CALL
+  CMF_LAUNCH_CHECK();
+  return CMF_OK;
+}
+
 extern "C" int cmf_backward_scores(const float* U, const float* I, int32_t D, const void* users,
                                    const void* items, int32_t idx_bytes, int64_t M,
                                    const float* dpreds, const float* preds,

@@ -622,6 +622,36 @@ class MatrixFactorizationModel(torch.nn.Module):
             preds = preds.drop(np.concatenate(seen))
         return preds
 
+    def item_item_similarity(self, item_id):
+        """base_pipeline.py:783-815: cosine similarity of ``item_id`` to every item, sorted
+        descending (the item itself comes first)."""
+        h = self.hparams
+        if item_id >= h.num_items:
+            raise ValueError(
+                f'``item_id`` {item_id} is not in the model. Expected ID between ``0`` and '
+                f'``self.hparams.num_items - 1`` (``{h.num_items - 1}``), not ``{item_id}``')
+        return self._calculate_embedding_similarity(self._get_item_embeddings(), item_id)
+
+    def user_user_similarity(self, user_id):
+        """base_pipeline.py:817-847."""
+        h = self.hparams
+        if user_id >= h.num_users:
+            raise ValueError(
+                f'``user_id`` {user_id} is not in the model. Expected ID between ``0`` and '
+                f'``self.hparams.num_users - 1`` (``{h.num_users - 1}``), not ``{user_id}``')
+        return self._calculate_embedding_similarity(self._get_user_embeddings(), user_id)
+
+    def _calculate_embedding_similarity(self, embeddings, id):
+        """base_pipeline.py:849-859 through ``cmf_row_similarity``."""
+        import pandas as pd
+        E = _abi.require_cuda(embeddings, 'embeddings')
+        out = torch.empty(E.shape[0], dtype=torch.float32, device=E.device)
+        with torch.cuda.device(E.device):
+            _abi.check(_abi.lib().cmf_row_similarity(_abi.ptr(E), E.shape[0], E.shape[1], int(id),
+                                                     _abi.ptr(out), _abi.stream_ptr(E.device)),
+                       'cmf_row_similarity')
+        return pd.Series(out.cpu().numpy()).sort_values(ascending=False)
+
     def save_model(self, filename='model.pth'):
         """``{'state_dict', 'hparams'}`` exactly as the reference writes it
         (base_pipeline.py:880-900); optimizer state and datasets are not saved."""

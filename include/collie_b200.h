@@ -184,6 +184,15 @@ CMF_API int cmf_backward_scores(const float *U, const float *I, int32_t D, const
                         float *gbu, float *gbi, void *stream);
 
 /*
+ * out[r] = cosine similarity of row r with row id of the table E [rows, D] (each row divided by
+ * its L2 norm, then dotted). Replaces BasePipeline._calculate_embedding_similarity,
+ * collie/model/base/base_pipeline.py:849-859 (item_item_similarity :783-815, user_user_similarity
+ * :817-847).
+ */
+CMF_API int cmf_row_similarity(const float *E, int64_t rows, int32_t D, int64_t id, float *out,
+                       void *stream);
+
+/*
  * Negative item ids [B, N] for interactions at dataset positions gidx (or gidx_base + b).
  * Replaces Interactions._negative_sample, collie/interactions/datasets.py:390-445: approximate mode
  * when csr_indptr == NULL (:433-443), else the exact rejection loop (:399-426).

@@ -65,6 +65,13 @@ def mf_forward(U: torch.Tensor, I: torch.Tensor, bu: torch.Tensor, bi: torch.Ten
 # ------------------------------------------------------------------------------------------------
 
 
+def embedding_similarity(E: torch.Tensor, id: int) -> torch.Tensor:
+    """BasePipeline._calculate_embedding_similarity (collie/model/base/base_pipeline.py:849-859):
+    rows divided by their L2 norm, seed row times the transposed table (before the host sort)."""
+    En = E / E.norm(dim=1)[:, None]
+    return torch.matmul(En[[id], :], En.transpose(1, 0)).squeeze(0)
+
+
 def ideal_difference(pos_items: torch.Tensor, neg_items: torch.Tensor,
                      metadata: Optional[Dict[str, torch.Tensor]],
                      weights: Optional[Dict[str, float]]):

@@ -189,6 +189,28 @@ def metrics_case(seed, n_users=37, n_items=101, dim=12, n_test=260, exact_grid=F
     return out
 
 
+def similarity_case(seed, n_users=23, n_items=57, dim=20):
+    """item_item_similarity / user_user_similarity (base_pipeline.py:783-859), in id order."""
+    rng = np.random.default_rng(seed)
+    users, items = synthetic_pairs(rng, n_users, n_items, 200)
+    data = Interactions(users=users, items=items, ratings=np.ones(len(users)), num_users=n_users,
+                        num_items=n_items, allow_missing_ids=True,
+                        remove_duplicate_user_item_pairs=False,
+                        check_num_negative_samples_is_valid=False)
+    model = MatrixFactorizationModel(train=data, embedding_dim=dim, lr_scheduler_func=None)
+    randomize(model, rng, scale=0.7)
+    model.eval()
+    out = {'n_users': n_users, 'n_items': n_items, 'dim': dim,
+           'item_ids': np.array([0, 7, n_items - 1]), 'user_ids': np.array([0, 11, n_users - 1])}
+    for k, v in state(model).items():
+        out[k] = v
+    for i in out['item_ids']:
+        out[f'item_sim_{i}'] = model.item_item_similarity(int(i)).sort_index().values
+    for u in out['user_ids']:
+        out[f'user_sim_{u}'] = model.user_user_similarity(int(u)).sort_index().values
+    return out
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     cases = {
@@ -213,6 +235,10 @@ def main():
         'metrics_exact_grid': metrics_case(42, exact_grid=True),
         'metrics_d128': metrics_case(43, n_users=64, n_items=333, dim=128, n_test=700),
     }
+    if len(sys.argv) > 1 and sys.argv[1] == 'similarity':     # only the cases added later
+        cases = {}
+    cases['similarity_random'] = similarity_case(51)
+    cases['similarity_d128'] = similarity_case(52, n_users=40, n_items=90, dim=128)
     for name, arrays in cases.items():
         np.savez_compressed(os.path.join(OUT, name + '.npz'), **arrays)
         print(name, 'ok')

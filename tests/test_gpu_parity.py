@@ -619,3 +619,41 @@ def test_epoch_plan_properties(n, batch, n_users, with_gpos):
     gp = torch.cat([b.gidx for b in plain.device_batches('cuda', epoch=0,
                                                          sort_within_batch=False)]).cpu().numpy()
     assert np.array_equal(gp, np.arange(n) if gpos is None else gpos)
+
+
+# ------------------------------------------------------------------------------------ similarity
+@pytest.mark.gpu
+@pytest.mark.parametrize('name', ['similarity_random', 'similarity_d128'])
+def test_golden_similarity(name):
+    """item_item_similarity / user_user_similarity equal the reference's series
+    (base_pipeline.py:783-859): same values per id, sorted descending, the seed first."""
+    import collie_b200 as cb
+    from oracle import collie_oracle as O
+    g = np.load(os.path.join(GOLDEN, name + '.npz'))
+    n_users, n_items, dim = int(g['n_users']), int(g['n_items']), int(g['dim'])
+    data = cb.Interactions(users=np.arange(n_users) % n_users, items=np.arange(n_users) % n_items,
+                           num_users=n_users, num_items=n_items, allow_missing_ids=True,
+                           check_num_negative_samples_is_valid=False,
+                           max_number_of_samples_to_consider=0)
+    model = cb.MatrixFactorizationModel(train=data, embedding_dim=dim,
+                                        lr_scheduler_func=None).cuda()
+    with torch.no_grad():
+        for k, t in _tables(model).items():
+            t.copy_(torch.from_numpy(g[k]))
+    for i in g['item_ids']:
+        got = model.item_item_similarity(int(i))
+        assert got.index[0] == i and np.all(np.diff(got.values) <= 0)
+        np.testing.assert_allclose(got.sort_index().values, g[f'item_sim_{i}'], rtol=1e-5,
+                                   atol=1e-6)
+        np.testing.assert_allclose(got.sort_index().values,
+                                   O.embedding_similarity(torch.from_numpy(g['I']), int(i)).numpy(),
+                                   rtol=1e-5, atol=1e-6)
+    for u in g['user_ids']:
+        got = model.user_user_similarity(int(u))
+        assert got.index[0] == u and len(got) == n_users
+        np.testing.assert_allclose(got.sort_index().values, g[f'user_sim_{u}'], rtol=1e-5,
+                                   atol=1e-6)
+    with pytest.raises(ValueError, match='is not in the model'):
+        model.item_item_similarity(n_items)
+    with pytest.raises(ValueError, match='is not in the model'):
+        model.user_user_similarity(n_users)

@@ -213,6 +213,19 @@ def test_golden_metrics(path):
                 np.testing.assert_allclose(got[:2], exp[:2], rtol=1e-6)
 
 
+@pytest.mark.parametrize('name', ['similarity_random', 'similarity_d128'])
+def test_golden_similarity(name):
+    """item_item_similarity / user_user_similarity of the reference (base_pipeline.py:783-859)."""
+    g = np.load(os.path.join(GOLDEN, name + '.npz'))
+    U, I = torch.from_numpy(g['U']), torch.from_numpy(g['I'])
+    for i in g['item_ids']:
+        np.testing.assert_allclose(O.embedding_similarity(I, int(i)).numpy(), g[f'item_sim_{i}'],
+                                   rtol=1e-6, atol=1e-7)
+    for u in g['user_ids']:
+        np.testing.assert_allclose(O.embedding_similarity(U, int(u)).numpy(), g[f'user_sim_{u}'],
+                                   rtol=1e-6, atol=1e-7)
+
+
 # ---------------------------------------------------------------- third-party optimizer algorithms
 
 def test_optimizer_formulas_match_torch_optim():
