@@ -10,7 +10,8 @@ PyTorch fallback -- a missing library or a non-CUDA tensor raises.
 from . import _abi
 from .interactions import (ApproximateNegativeSamplingInteractionsDataLoader,
                            ExplicitInteractions, Interactions, InteractionsDataLoader)
-from .metrics import auc, evaluate_in_batches, get_preds, mapk, mrr
+from .metrics import (MeanAbsoluteError, MeanSquaredError, auc, evaluate_in_batches,
+                      explicit_evaluate_in_batches, get_preds, mapk, mrr)
 from .model import (MatrixFactorizationModel, RowOptimizer, ScaledEmbedding, ZeroEmbedding)
 from .trainer import CollieMinimalTrainer, CollieTrainer
 
@@ -19,6 +20,7 @@ __version__ = '0.1.0'
 __all__ = [
     'ApproximateNegativeSamplingInteractionsDataLoader', 'CollieMinimalTrainer', 'CollieTrainer',
     'ExplicitInteractions', 'Interactions', 'InteractionsDataLoader', 'MatrixFactorizationModel',
+    'MeanAbsoluteError', 'MeanSquaredError', 'explicit_evaluate_in_batches',
     'RowOptimizer', 'ScaledEmbedding', 'ZeroEmbedding', 'auc', 'evaluate_in_batches', 'get_preds',
     'mapk', 'mrr',
 ]

@@ -263,13 +263,90 @@ def evaluate_in_batches(metric_list, test_interactions, model, k=10, batch_size=
     return all_scores[0] if len(all_scores) == 1 else all_scores
 
 
+class _ErrorMetric(object):
+    """Stand-ins for ``torchmetrics.MeanSquaredError`` / ``MeanAbsoluteError`` (the package is not
+    in this image): ``metric(preds, target)`` accumulates, ``compute()`` returns the mean,
+    ``reset()`` clears. The sums stay on the device of the inputs (float64)."""
+    def __init__(self):
+        self.reset()
+
+    def reset(self):
+        self._sum, self._n = None, 0
+
+    def _err(self, d):
+        raise NotImplementedError
+
+    def __call__(self, preds, target):
+        d = preds.detach().double().flatten() - target.detach().double().flatten().to(preds.device)
+        s = self._err(d).sum()
+        self._sum = s if self._sum is None else self._sum + s
+        self._n += d.numel()
+
+    update = __call__
+
+    def compute(self):
+        if self._n == 0:
+            return torch.tensor(float('nan'))
+        return (self._sum / self._n).float().cpu()
+
+
+class MeanSquaredError(_ErrorMetric):
+    def _err(self, d):
+        return d * d
+
+
+class MeanAbsoluteError(_ErrorMetric):
+    def _err(self, d):
+        return d.abs()
+
+
+def explicit_evaluate_in_batches(metric_list, test_interactions, model, logger=None, verbose=True,
+                                 **kwargs):
+    """Evaluate an explicit model with ``torchmetrics``-style metric objects
+    (collie/metrics.py:398-502): batches of ``(users, items, ratings)`` from an
+    ``InteractionsDataLoader`` over ``test_interactions`` (``**kwargs`` go to it), ``preds =
+    model(users, items)`` through the CUDA forward, every metric called as ``metric(preds, ratings)``
+    and ``compute()``d at the end; metrics are ``reset()`` on the way out. The stand-ins of this
+    module take the predictions on the device; any other metric object gets CPU tensors like in the
+    reference."""
+    from .interactions import ExplicitInteractions, InteractionsDataLoader
+    if not isinstance(test_interactions, ExplicitInteractions):
+        raise ValueError('``test_interactions`` must be of type ``ExplicitInteractions``, not '
+                         f'{type(test_interactions)}. Try using ``evaluate_in_batches`` instead.')
+    if not torch.cuda.is_available():
+        raise _abi.CmfError('explicit_evaluate_in_batches runs on a CUDA device; none is available '
+                            'and collie_b200 has no CPU fallback')
+    try:
+        if not next(model.parameters()).is_cuda:
+            model.to('cuda')
+        model._move_any_external_data_to_device()
+        kwargs.setdefault('batch_size', 1 << 16)
+        loader = InteractionsDataLoader(interactions=test_interactions, **kwargs)
+        with torch.no_grad():
+            for users, items, ratings in loader:
+                preds = model(users, items)
+                for metric in metric_list:
+                    if isinstance(metric, _ErrorMetric):
+                        metric(preds, ratings)
+                    else:
+                        metric(preds.cpu(), ratings.cpu())
+        all_scores = [metric.compute() for metric in metric_list]
+        if logger is not None:
+            _log_metrics(model, logger, metric_list, all_scores, verbose)
+        return all_scores[0] if len(all_scores) == 1 else all_scores
+    finally:
+        for metric in metric_list:
+            metric.reset()
+
+
 def _log_metrics(model, logger, metric_list, all_scores, verbose):
     """collie/metrics.py:524-543."""
     try:
         step = model.hparams.get('num_epochs_completed')
     except Exception:
         step = None
-    metrics_dict = dict(zip([m.__name__ for m in metric_list], all_scores))
+    metrics_dict = dict(zip([getattr(m, '__name__', type(m).__name__) for m in metric_list],
+                            all_scores))
     if verbose:
         print(f'Logging metrics {metrics_dict} to ``logger``...')
     logger.log_metrics(metrics=metrics_dict, step=step)

@@ -450,6 +450,40 @@ def test_explicit_training_reduces_mse():
     trainer.fit(model)
     last = model.calculate_loss(next(iter(model.train_loader))).item()
     assert last < 0.5 * first, (first, last)
+    # explicit_evaluate_in_batches (collie/metrics.py:398-502) against the same numbers on the host
+    with torch.no_grad():
+        preds = model(torch.from_numpy(data.mat.row).cuda(),
+                      torch.from_numpy(data.mat.col).cuda()).cpu().numpy().astype(np.float64)
+    truth = data.mat.data.astype(np.float64)
+
+    class HostMSE(object):       # a foreign metric object: gets CPU tensors like in the reference
+        def __init__(self):
+            self.reset()
+
+        def reset(self):
+            self.s, self.n = 0.0, 0
+
+        def __call__(self, p, t):
+            assert not p.is_cuda and not t.is_cuda
+            self.s += float(((p.double() - t.double()) ** 2).sum())
+            self.n += p.numel()
+
+        def compute(self):
+            return self.s / self.n
+    host = HostMSE()
+    mse, mae, mse_host = cb.explicit_evaluate_in_batches(
+        [cb.MeanSquaredError(), cb.MeanAbsoluteError(), host], data, model, verbose=False,
+        batch_size=1000)
+    np.testing.assert_allclose(float(mse), np.mean((preds - truth) ** 2), rtol=1e-5)
+    np.testing.assert_allclose(float(mae), np.mean(np.abs(preds - truth)), rtol=1e-5)
+    np.testing.assert_allclose(mse_host, float(mse), rtol=1e-6)
+    assert host.n == 0                                        # metrics are reset on the way out
+    one = cb.explicit_evaluate_in_batches([cb.MeanSquaredError()], data, model, verbose=False)
+    np.testing.assert_allclose(float(one), float(mse), rtol=1e-6)
+    implicit = cb.Interactions(users=users, items=items, num_users=n_users, num_items=n_items,
+                               allow_missing_ids=True, check_num_negative_samples_is_valid=False)
+    with pytest.raises(ValueError, match='must be of type ``ExplicitInteractions``'):
+        cb.explicit_evaluate_in_batches([cb.MeanSquaredError()], implicit, model)
 
 
 def test_errors_are_loud():
