@@ -498,6 +498,12 @@ def main():
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
     local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    # stdout carries the JSON line and nothing else: libraries that print from C (NCCL's version
+    # banner) are sent to stderr by pointing fd 1 there and keeping the real stdout for the line
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), 'w')
+    os.dup2(2, 1)
+    sys.stdout = real_stdout
     if args.impl == 'reference':
         run_reference(args, rank, world)
         return
