@@ -282,9 +282,11 @@ def run_ours(args, rank, world, local_rank):
     # ---- end to end: pinned host batches in, loss out, every step (double-buffered copies)
     copy_stream = torch.cuda.Stream(dev)
     main = torch.cuda.current_stream(dev)
+    from collie_b200.interactions import BatchSorter
     slots = [dict(u=torch.empty(B, dtype=torch.int32, device=dev),
                   i=torch.empty(B, dtype=torch.int32, device=dev),
                   g=torch.empty(B, dtype=torch.int64, device=dev),
+                  sort=BatchSorter(B, w['num_users'], dev),
                   ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(2)]
     loss_host = torch.empty(steps + warmup, dtype=torch.float32).pin_memory()
 
@@ -295,14 +297,16 @@ def run_ours(args, rank, world, local_rank):
             slot = slots[j % 2]
             a = ((base + j) % n_batches) * B
             with torch.cuda.stream(copy_stream):
+                # copy stream: the batch comes in and is ordered by user while the previous
+                # step is still running on the main stream
                 copy_stream.wait_event(slot['free'])
                 slot['u'].copy_(users_h[a:a + B], non_blocking=True)
                 slot['i'].copy_(items_h[a:a + B], non_blocking=True)
                 slot['g'].copy_(gidx_h[a:a + B], non_blocking=True)
+                db = slot['sort'](slot['u'], slot['i'], slot['g'])
                 slot['ready'].record(copy_stream)
             main.wait_event(slot['ready'])
-            out = model.fused_step(DeviceBatch(slot['u'], slot['i'], slot['g'], None),
-                                   optimizers=opts, interactions=data, epoch=1)
+            out = model.fused_step(db, optimizers=opts, interactions=data, epoch=1)
             loss_host[j:j + 1].copy_(out.view(1), non_blocking=True)
             slot['free'].record(main)
 

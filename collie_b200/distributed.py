@@ -485,7 +485,7 @@ def bench_sharded(args, rank, world, local_rank, workload, synth, config_dict, C
 
     # ---- end to end: this rank's batches come from pinned host memory every step (double-buffered
     # copies on a side stream), the step's loss goes back to the host every step
-    from .interactions import DeviceBatch
+    from .interactions import BatchSorter
     n_local = data.num_interactions
     g = torch.Generator().manual_seed(w['seed'] + rank)
     perm = torch.randperm(n_local, generator=g)
@@ -498,6 +498,7 @@ def bench_sharded(args, rank, world, local_rank, workload, synth, config_dict, C
     slots = [dict(u=torch.empty(B, dtype=torch.int32, device=dev),
                   i=torch.empty(B, dtype=torch.int32, device=dev),
                   g=torch.empty(B, dtype=torch.int64, device=dev),
+                  sort=BatchSorter(B, data.num_users, dev),
                   ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(2)]
     loss_host = torch.empty(steps + warmup, dtype=torch.float32).pin_memory()
 
@@ -512,10 +513,10 @@ def bench_sharded(args, rank, world, local_rank, workload, synth, config_dict, C
                 slot['u'].copy_(users_h[a:a + B], non_blocking=True)
                 slot['i'].copy_(items_h[a:a + B], non_blocking=True)
                 slot['g'].copy_(gidx_h[a:a + B], non_blocking=True)
-                slot['ready'].record(copy_stream)
+                db = slot['sort'](slot['u'], slot['i'], slot['g'])   # ordered by user, off the
+                slot['ready'].record(copy_stream)                    # main stream
             main.wait_event(slot['ready'])
-            out = sharded.train_step(DeviceBatch(slot['u'], slot['i'], slot['g'], None, False),
-                                     opts, interactions=data, epoch=1, global_batch=world * B,
+            out = sharded.train_step(db, opts, interactions=data, epoch=1, global_batch=world * B,
                                      reduce_loss=True)
             loss_host[base + j:base + j + 1].copy_(out.view(1), non_blocking=True)
             slot['free'].record(main)

@@ -295,6 +295,41 @@ DeviceBatch = collections.namedtuple('DeviceBatch', 'users items gidx ratings so
                                      defaults=(False,))
 
 
+class BatchSorter(object):
+    """Orders device batches by user on whatever stream is current (``cmf_epoch_plan`` over one
+    batch), so a host-fed pipeline can do it on its copy stream, next to the previous step, and hand
+    ``fused_step`` a ``DeviceBatch`` with ``sorted=True`` (which then skips its own sort).
+    Holds the output buffers and the scratch for batches of up to ``max_batch`` interactions."""
+
+    def __init__(self, max_batch, num_users, device, with_ratings=False):
+        self.max_batch, self.num_users = int(max_batch), int(num_users)
+        self.device = torch.device(device)
+        n = self.max_batch
+        self.users = torch.empty(n, dtype=torch.int32, device=self.device)
+        self.items = torch.empty(n, dtype=torch.int32, device=self.device)
+        self.gidx = torch.empty(n, dtype=torch.int64, device=self.device)
+        self.ratings = torch.empty(n, dtype=torch.float32, device=self.device) \
+            if with_ratings else None
+        need = int(_abi.lib().cmf_epoch_plan_workspace_bytes(n))
+        self.ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+
+    def __call__(self, users, items, gidx, ratings=None):
+        """``users`` / ``items`` int32, ``gidx`` int64 (dataset positions), on the device."""
+        n = int(users.shape[0])
+        if n > self.max_batch:
+            raise ValueError(f'batch of {n} exceeds this sorter ({self.max_batch})')
+        if (ratings is not None) != (self.ratings is not None):
+            raise ValueError('ratings given to a sorter built without them, or the reverse')
+        with torch.cuda.device(self.device):
+            _abi.check(_abi.lib().cmf_epoch_plan(
+                _abi.ptr(users), _abi.ptr(items), _abi.ptr(ratings), _abi.ptr(gidx), n, max(n, 1),
+                self.num_users, 0, 1, 0, 0, _abi.ptr(self.users), _abi.ptr(self.items),
+                _abi.ptr(self.ratings), _abi.ptr(self.gidx), _abi.ptr(self.ws), self.ws.numel(),
+                _abi.stream_ptr(self.device)), 'cmf_epoch_plan')
+        return DeviceBatch(self.users[:n], self.items[:n], self.gidx[:n],
+                           self.ratings[:n] if ratings is not None else None, True)
+
+
 class BaseInteractionsDataLoader(object):
     """Properties shared by the loaders (dataloaders.py:16-67)."""
 

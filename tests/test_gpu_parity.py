@@ -691,3 +691,47 @@ def test_golden_similarity(name):
         model.item_item_similarity(n_items)
     with pytest.raises(ValueError, match='is not in the model'):
         model.user_user_similarity(n_users)
+
+
+@pytest.mark.gpu
+def test_batch_sorter_orders_by_user_and_keeps_rows_together():
+    """BatchSorter (host-fed pipelines): a stable sort of one batch by user on the current stream;
+    a step on the sorted batch equals the step on the unsorted one."""
+    import collie_b200 as cb
+    from collie_b200.interactions import BatchSorter, DeviceBatch
+    rng = np.random.default_rng(3)
+    n_users, n_items, n = 500, 300, 4000
+    users = rng.integers(0, n_users, n).astype(np.int32)
+    items = rng.integers(0, n_items, n).astype(np.int32)
+    gidx = rng.permutation(10 * n)[:n].astype(np.int64)
+    u, i, g = (torch.from_numpy(x).cuda() for x in (users, items, gidx))
+    sorter = BatchSorter(n + 7, n_users, 'cuda')
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        db = sorter(u, i, g)
+    torch.cuda.current_stream().wait_stream(side)
+    assert db.sorted and db.ratings is None
+    order = np.argsort(users, kind='stable')
+    assert np.array_equal(db.users.cpu().numpy(), users[order])
+    assert np.array_equal(db.items.cpu().numpy(), items[order])
+    assert np.array_equal(db.gidx.cpu().numpy(), gidx[order])
+    with pytest.raises(ValueError, match='exceeds this sorter'):
+        sorter(torch.cat([u, u]), torch.cat([i, i]), torch.cat([g, g]))
+    # the same training step either way (negatives are keyed by gidx, not by batch position)
+    data = cb.Interactions(users=users, items=items, num_users=n_users, num_items=n_items,
+                           num_negative_samples=3, allow_missing_ids=True, seed=9,
+                           remove_duplicate_user_item_pairs=False,
+                           check_num_negative_samples_is_valid=False,
+                           max_number_of_samples_to_consider=0)
+    losses, tables = [], []
+    for batch in (DeviceBatch(u, i, g, None), db):
+        torch.manual_seed(0)
+        model = cb.MatrixFactorizationModel(train=data, embedding_dim=32, sparse=True, lr=1e-2,
+                                            optimizer='sparse_adam', loss='bpr',
+                                            lr_scheduler_func=None).cuda()
+        opts = model.configure_optimizers()
+        losses.append(model.fused_step(batch, optimizers=opts, interactions=data, epoch=0).item())
+        tables.append(model.item_embeddings.weight.detach().cpu().numpy().copy())
+    np.testing.assert_allclose(losses[0], losses[1], rtol=1e-6)
+    np.testing.assert_allclose(tables[0], tables[1], rtol=1e-4, atol=1e-6)
