@@ -83,37 +83,41 @@ k_plan_gather(const uint32_t* __restrict__ perm, const int32_t* __restrict__ use
 }
 
 // ---- fast path: the dataset arrives ordered by user ------------------------------------------
-// A keyed bijection sigma of [0, n) (balanced Feistel network over the next even number of bits,
-// cycle-walked back into range) is the epoch's permutation: entry p goes to batch sigma(p) / batch.
+// A keyed bijection sigma of [0, n) (Feistel network over the bits of n - 1, cycle-walked back into
+// range) is the epoch's permutation: entry p goes to batch sigma(p) / batch.
 // A STABLE partition of the user-ordered entries by batch number (one radix pass per 8 bits of
 // batch number) then leaves every batch ordered by user with no further sort.
-struct FeistelKey { uint32_t k[6]; int half_bits; };
+struct FeistelKey { uint32_t k[6]; int lbits, rbits; };   // lbits + rbits = bits of n - 1
 
 __device__ __forceinline__ uint32_t fmix32(uint32_t h) {
   h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16;
   return h;
 }
+// Unbalanced Feistel network over exactly the bits of n - 1 (the halves swap sizes every round;
+// an even number of rounds brings them back), cycle-walked into [0, n): the domain is < 2 n, so
+// fewer than two turns on average.
 __device__ __forceinline__ uint32_t feistel_perm(uint32_t x, const FeistelKey& fk, uint32_t n) {
-  const uint32_t mask = (1u << fk.half_bits) - 1u;
   do {
-    uint32_t l = x >> fk.half_bits, r = x & mask;
+    int lb = fk.lbits, rb = fk.rbits;
+    uint32_t l = x >> rb, r = x & ((1u << rb) - 1u);
 #pragma unroll
     for (int i = 0; i < 6; ++i) {
-      const uint32_t t = l ^ (fmix32(r * 0x9e3779b1u + fk.k[i]) & mask);
+      const uint32_t t = l ^ (fmix32(r * 0x9e3779b1u + fk.k[i]) & ((1u << lb) - 1u));
       l = r;
       r = t;
+      const int tmp = lb; lb = rb; rb = tmp;
     }
-    x = (l << fk.half_bits) | r;
-  } while (x >= n);   // the domain is < 4 n: a few turns at most on average
+    x = (l << rb) | r;
+  } while (x >= n);
   return x;
 }
 
 __global__ void __launch_bounds__(256)
-k_plan_batch_of(FeistelKey fk, int64_t n, int64_t batch, uint32_t* __restrict__ keys,
+k_plan_batch_of(FeistelKey fk, int64_t n, uint32_t batch, uint32_t* __restrict__ keys,
                 uint32_t* __restrict__ pos) {
   const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= n) return;
-  keys[p] = (uint32_t)(feistel_perm((uint32_t)p, fk, (uint32_t)n) / (uint64_t)batch);
+  keys[p] = feistel_perm((uint32_t)p, fk, (uint32_t)n) / (uint32_t)batch;
   pos[p] = (uint32_t)p;
 }
 
@@ -251,9 +255,11 @@ extern "C" int cmf_epoch_plan_presorted(const void* rec, const float* ratings, i
   }
   int bits = bits_for(n);
   if (bits < 2) bits = 2;
-  fk.half_bits = (bits + 1) / 2;
+  fk.lbits = bits / 2;
+  fk.rbits = bits - fk.lbits;
   const unsigned blocks = (unsigned)((n + 255) / 256);
-  k_plan_batch_of<<<blocks, 256, 0, s>>>(fk, n, batch, kA, vA);
+  // (a batch larger than the dataset is one batch)
+  k_plan_batch_of<<<blocks, 256, 0, s>>>(fk, n, (uint32_t)(batch < n ? batch : n), kA, vA);
   CMF_LAUNCH_CHECK();
   size_t temp = L.temp_bytes;
   CMF_CUDA(cub::DeviceRadixSort::SortPairs(base + L.temp, temp, kA, kB, vA, vB, (int)n, 0,
