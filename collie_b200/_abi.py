@@ -105,6 +105,7 @@ SIGNATURES = {
     'cmf_sample_negatives': (C.c_int, [C.c_uint64, C.c_uint32, C.c_void_p, C.c_int64, C.c_void_p,
                                        C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
                                        C.c_int32, C.c_void_p, C.c_void_p]),
+    'cmf_train_epoch': (C.c_int, [C.POINTER(cmf_step_t), C.c_int64, C.c_void_p, C.c_void_p]),
     'cmf_epoch_plan_workspace_bytes': (C.c_size_t, [C.c_int64]),
     'cmf_epoch_plan': (C.c_int, [C.c_void_p] * 4 + [C.c_int64, C.c_int64, C.c_int64, C.c_int32,
                                                C.c_int32, C.c_uint64, C.c_uint32] +

@@ -847,3 +847,34 @@ extern "C" int cmf_optimizer_rows(float* P, float* M, float* V, float* G, int64_
   CMF_LAUNCH_CHECK();
   return CMF_OK;
 }
+
+// One pass over a planned epoch (collie_b200 loaders lay an epoch out as contiguous arrays, every
+// batch already ordered by user): the steps are issued back to back from here, so a small-batch
+// job is not paced by its host language's per-step overhead.
+extern "C" int cmf_train_epoch(const cmf_step_t* first, int64_t n_total, float* losses,
+                               void* stream) {
+  CMF_REQUIRE(first && losses, "cmf_train_epoch: null argument");
+  CMF_REQUIRE(first->B >= 1, "cmf_train_epoch: batch size must be positive");
+  CMF_REQUIRE(n_total >= 0, "cmf_train_epoch: negative length");
+  CMF_REQUIRE(!first->negs_out && !first->sel_out && !first->pos_scores_out &&
+                  !first->neg_scores_out,
+              "cmf_train_epoch: per-batch inspection outputs are not available here");
+  const int64_t B = first->B;
+  int64_t s = 0;
+  for (int64_t off = 0; off < n_total; off += B, ++s) {
+    cmf_step_t a = *first;
+    a.B = n_total - off < B ? n_total - off : B;
+    a.users = first->users + off;
+    a.items = first->items + off;
+    if (first->ratings) a.ratings = first->ratings + off;
+    if (first->negs_in) a.negs_in = first->negs_in + off * first->N;
+    if (first->gidx) a.gidx = first->gidx + off;
+    a.gidx_base = first->gidx_base + off;
+    a.emb_opt.step = first->emb_opt.step + s;
+    a.bias_opt.step = first->bias_opt.step + s;
+    a.loss_out = losses + s;
+    const int rc = cmf_train_step(&a, stream);
+    if (rc != CMF_OK) return rc;
+  }
+  return CMF_OK;
+}

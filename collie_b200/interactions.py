@@ -368,7 +368,20 @@ class BaseInteractionsDataLoader(object):
 
     # ---- device-side epoch plan --------------------------------------------------------------
     def device_batches(self, device, epoch=None, sort_within_batch=True):
-        """Yield ``DeviceBatch`` slices of one pass over the data, all tensors on ``device``.
+        """Yield ``DeviceBatch`` slices of one pass over the data, all tensors on ``device``
+        (slices of ``epoch_plan``)."""
+        plan = self.epoch_plan(device, epoch=epoch, sort_within_batch=sort_within_batch)
+        n, b = plan.users.shape[0], self.batch_size
+        for s in range(0, n, b):
+            e = min(s + b, n)
+            yield DeviceBatch(plan.users[s:e], plan.items[s:e], plan.gidx[s:e],
+                              plan.ratings[s:e] if plan.ratings is not None else None,
+                              plan.sorted)
+
+    def epoch_plan(self, device, epoch=None, sort_within_batch=True):
+        """One pass over the data as ONE ``DeviceBatch`` of contiguous arrays laid out batch after
+        batch (``drop_last`` already applied): what ``device_batches`` slices and what
+        ``fused_step(..., epoch_batch_size=...)`` consumes whole.
 
         Shuffled passes permute the dataset positions once on the device (the reference shuffles
         an index array on the host, samplers.py:51-60); ``gidx`` keeps the dataset position of each
@@ -418,11 +431,9 @@ class BaseInteractionsDataLoader(object):
                         _abi.ptr(ratings), _abi.ptr(gidx), _abi.ptr(ws), ws.numel(),
                         _abi.stream_ptr(device)), 'cmf_epoch_plan')
         stop = (n // b) * b if self.drop_last else n
-        for s in range(0, stop, b):
-            e = min(s + b, n)
-            yield DeviceBatch(users[s:e], items[s:e], gidx[s:e],
-                              ratings[s:e] if ratings is not None else None,
-                              bool(sort_within_batch))
+        return DeviceBatch(users[:stop], items[:stop], gidx[:stop],
+                           ratings[:stop] if ratings is not None else None,
+                           bool(sort_within_batch))
 
     def __iter__(self):
         """Reference-format batches on the current CUDA device:

@@ -450,13 +450,16 @@ class MatrixFactorizationModel(torch.nn.Module):
 
     def fused_step(self, batch, optimizers=None, train=True, interactions=None, epoch=0,
                    outputs=None, users_sorted=False, global_batch=0, skip_item_update=False,
-                   num_items_logical=0):
+                   num_items_logical=0, epoch_batch_size=None):
         """One step through ``cmf_train_step``; returns the loss as a 0-d device tensor.
 
         ``optimizers``: what ``configure_optimizers`` returned (one optimizer, or [main, bias]).
         ``interactions``: the dataset behind a ``DeviceBatch`` (seed / exact-sampling CSR).
         ``outputs``: optional dict; keys among ``negs``, ``sel``, ``pos_scores``, ``neg_scores`` are
         filled with device tensors for inspection.
+        ``epoch_batch_size``: ``batch`` is a whole planned epoch (``loader.epoch_plan``); all its
+        steps of that batch size run in ONE library call (``cmf_train_epoch``) and the per-step
+        losses come back as a 1-d device tensor.
         ``global_batch`` / ``skip_item_update``: multi-GPU hooks (``collie_b200.distributed``): the
         loss is a mean over the global batch, and the item-row gradients stay in the workspace
         for the caller to reduce across ranks.
@@ -474,7 +477,16 @@ class MatrixFactorizationModel(torch.nn.Module):
         bu = _abi.require_cuda(self.user_biases.weight.data, 'user_biases.weight')
         bi = _abi.require_cuda(self.item_biases.weight.data, 'item_biases.weight')
         implicit = self._loss_name not in ('mse', 'mae')
-        B = int(users.shape[0])
+        n_total = int(users.shape[0])
+        B = n_total if epoch_batch_size is None else int(epoch_batch_size)
+        if epoch_batch_size is not None:
+            if B < 1:
+                raise ValueError('epoch_batch_size must be positive')
+            if outputs is not None:
+                raise ValueError('inspection outputs are per batch; not available for a whole epoch')
+            if skip_item_update:
+                raise ValueError('a whole epoch cannot leave its item updates to the caller')
+        n_steps = (n_total + B - 1) // B if epoch_batch_size is not None else 1
         a = _abi.cmf_step_t()
         a.U, a.I, a.bu, a.bi = U.data_ptr(), I.data_ptr(), bu.data_ptr(), bi.data_ptr()
         a.num_users, a.num_items, a.D = h.num_users, h.num_items, h.embedding_dim
@@ -486,7 +498,7 @@ class MatrixFactorizationModel(torch.nn.Module):
             if ratings is not None and negs is None and gidx is None:
                 raise ValueError('Implicit loss with explicit data is invalid!')
             if negs is not None:
-                if negs.shape[0] != B:
+                if negs.shape[0] != n_total:
                     raise ValueError('negative samples must have one row per interaction')
                 a.N = int(negs.shape[1])
                 a.negs_in = negs.data_ptr()
@@ -538,6 +550,8 @@ class MatrixFactorizationModel(torch.nn.Module):
             _, sI = main.abi_opt(pI)
             a.bias_opt, sbu = bias.abi_opt(pbu)
             _, sbi = bias.abi_opt(pbi)
+            for st_ in (sU, sI, sbu, sbi):       # one optimizer step per batch of the epoch
+                st_['step'] += n_steps - 1
 
             def sp(st, key):
                 t = st.get(key)
@@ -546,7 +560,7 @@ class MatrixFactorizationModel(torch.nn.Module):
             a.I_m, a.I_v = sp(sI, 'exp_avg'), sp(sI, 'exp_avg_sq')
             a.bu_m, a.bu_v = sp(sbu, 'exp_avg'), sp(sbu, 'exp_avg_sq')
             a.bi_m, a.bi_v = sp(sbi, 'exp_avg'), sp(sbi, 'exp_avg_sq')
-        loss_out = torch.empty(1, dtype=torch.float32, device=self.device)
+        loss_out = torch.empty(max(n_steps, 1), dtype=torch.float32, device=self.device)
         a.loss_out = loss_out.data_ptr()
         if outputs is not None:
             N = max(int(a.N), 1)
@@ -568,6 +582,11 @@ class MatrixFactorizationModel(torch.nn.Module):
         a.B_global = int(global_batch)
         a.skip_item_update = 1 if skip_item_update else 0
         a.num_items_logical = int(num_items_logical)
+        if epoch_batch_size is not None:
+            rc = _abi.lib().cmf_train_epoch(_abi.C.byref(a), n_total, loss_out.data_ptr(),
+                                            _abi.stream_ptr(self.device))
+            _abi.check(rc, 'cmf_train_epoch')
+            return loss_out[:n_steps]
         rc = _abi.lib().cmf_train_step(_abi.C.byref(a), _abi.stream_ptr(self.device))
         _abi.check(rc, 'cmf_train_step')
         return loss_out[0]

@@ -184,6 +184,20 @@ class CollieMinimalTrainer(object):
                 yield batch, None
 
     def _train_loop_single_epoch(self, model, epoch):
+        loader = self.train_dataloader
+        if self.logger is None and hasattr(loader, 'epoch_plan'):
+            # no per-step logging to do: the whole epoch is one library call (cmf_train_epoch)
+            plan = loader.epoch_plan(model.device, epoch=epoch)
+            if plan.users.shape[0] == 0:
+                return 0.0
+            losses = model.fused_step(plan, optimizers=self.optimizer.optimizers, train=True,
+                                      interactions=loader.interactions, epoch=epoch,
+                                      epoch_batch_size=loader.batch_size)
+            self.train_steps += int(losses.shape[0])
+            mean = losses.mean()
+            if self.detect_anomaly and not bool(torch.isfinite(mean)):
+                raise RuntimeError('non-finite training loss detected')
+            return mean.item()
         total_loss = torch.zeros((), dtype=torch.float32, device=model.device)
         n = 0
         for batch_idx, (batch, data) in enumerate(self._batches(self.train_dataloader, model,

@@ -158,6 +158,16 @@ CMF_API int cmf_train_workspace_items(void *workspace, int64_t num_users, int64_
 CMF_API int cmf_workspace_init(void *workspace, size_t workspace_bytes, void *stream);
 
 CMF_API int cmf_train_step(const cmf_step_t *args, void *stream);
+
+/*
+ * All steps of one epoch in one call: `first` describes step 0 (B = the batch size; users / items /
+ * ratings / gidx / negs_in point at arrays of n_total entries laid out batch after batch, e.g. by
+ * cmf_epoch_plan*); step s takes entries [s B, min((s + 1) B, n_total)), the optimizers' step
+ * counters advance by one per step, losses[s] receives the loss of step s (device memory,
+ * ceil(n_total / B) floats). Replaces the for-loop of
+ * CollieMinimalTrainer._train_loop_single_epoch, collie/model/base/trainer.py:451-478.
+ */
+CMF_API int cmf_train_epoch(const cmf_step_t *first, int64_t n_total, float *losses, void *stream);
 /* same call, restricted to the implicit / explicit loss families (base_pipeline.py:603 / :635) */
 CMF_API int cmf_train_step_implicit(const cmf_step_t *args, void *stream);
 CMF_API int cmf_train_step_explicit(const cmf_step_t *args, void *stream);

@@ -735,3 +735,61 @@ def test_batch_sorter_orders_by_user_and_keeps_rows_together():
         tables.append(model.item_embeddings.weight.detach().cpu().numpy().copy())
     np.testing.assert_allclose(losses[0], losses[1], rtol=1e-6)
     np.testing.assert_allclose(tables[0], tables[1], rtol=1e-4, atol=1e-6)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('explicit', [False, True])
+def test_whole_epoch_call_equals_the_step_loop(explicit):
+    """cmf_train_epoch (one call per epoch, trainer.py:451-478's loop moved into the library) =
+    the same steps issued one by one: per-step losses, tables, optimizer step counters."""
+    import collie_b200 as cb
+    rng = np.random.default_rng(12)
+    n_users, n_items, n, bsz = 300, 200, 5000, 512            # 9 full batches + a ragged one
+    users, items = rng.integers(0, n_users, n), rng.integers(0, n_items, n)
+    if explicit:
+        data = cb.ExplicitInteractions(users=users, items=items,
+                                       ratings=rng.integers(1, 6, n).astype(np.float32),
+                                       num_users=n_users, num_items=n_items,
+                                       allow_missing_ids=True,
+                                       remove_duplicate_user_item_pairs=False)
+        kw = dict(loss='mse', optimizer='adam', sparse=False)
+    else:
+        data = cb.Interactions(users=users, items=items, num_users=n_users, num_items=n_items,
+                               num_negative_samples=4, allow_missing_ids=True, seed=2,
+                               remove_duplicate_user_item_pairs=False,
+                               check_num_negative_samples_is_valid=False,
+                               max_number_of_samples_to_consider=0)
+        kw = dict(loss='bpr', optimizer='sparse_adam', sparse=True)
+    loader = cb.InteractionsDataLoader(data, batch_size=bsz, shuffle=True, drop_last=False)
+
+    def fresh():
+        torch.manual_seed(4)
+        m = cb.MatrixFactorizationModel(train=loader, embedding_dim=24, lr=1e-2,
+                                        lr_scheduler_func=None, **kw).cuda()
+        return m, m.configure_optimizers()
+    a, oa = fresh()
+    b, ob = fresh()
+    for epoch in (1, 2):        # the trainers number epochs from 1
+        step_losses = [a.fused_step(db, optimizers=oa, interactions=data, epoch=epoch)
+                       for db in loader.device_batches('cuda', epoch=epoch)]
+        plan = loader.epoch_plan('cuda', epoch=epoch)
+        epoch_losses = b.fused_step(plan, optimizers=ob, interactions=data, epoch=epoch,
+                                    epoch_batch_size=bsz)
+        assert epoch_losses.shape == (10,)
+        np.testing.assert_allclose(epoch_losses.cpu().numpy(),
+                                   torch.stack(step_losses).cpu().numpy(), rtol=2e-5)
+    for ta, tb in zip(_tables(a).values(), _tables(b).values()):
+        np.testing.assert_allclose(tb.detach().cpu().numpy(), ta.detach().cpu().numpy(),
+                                   rtol=1e-4, atol=1e-6, err_msg='epoch call vs step loop')
+    opt_a = oa[0] if isinstance(oa, (list, tuple)) else oa
+    opt_b = ob[0] if isinstance(ob, (list, tuple)) else ob
+    pa, pb = a.user_embeddings.weight, b.user_embeddings.weight
+    assert opt_a.state_for(pa)['step'] == opt_b.state_for(pb)['step'] == 20
+    # the trainer takes the one-call route when nothing has to be logged per step
+    c, _ = fresh()
+    t = cb.CollieTrainer(c, max_epochs=2, verbosity=0, enable_model_summary=False)
+    t.fit(c)
+    assert t.train_steps == 20
+    for ta, tc in zip(_tables(a).values(), _tables(c).values()):
+        np.testing.assert_allclose(tc.detach().cpu().numpy(), ta.detach().cpu().numpy(),
+                                   rtol=1e-4, atol=1e-6)
