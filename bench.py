@@ -378,6 +378,25 @@ def run_ours(args, rank, world, local_rank):
             {'items': int(item_rows.value), 'users': int(user_rows.value)},
         'update_phase_algorithmic_bytes': (uq + iq) * update_row,
     }
+    # the forward kernel's rows come out of L2 (item table 13.7 MB, the step's user rows 46 MB),
+    # so next to the HBM roofline: live probes of read bandwidth (cmf_read_probe, a persistent
+    # grid of 16-byte loads) over an L2-resident buffer and over one far larger than L2
+    def read_probe(nbytes, repeats):
+        buf = torch.ones(nbytes // 4, dtype=torch.float32, device=dev)
+        sink = torch.zeros(1, dtype=torch.float32, device=dev)
+        call = lambda: _abi.check(lib.cmf_read_probe(_abi.ptr(buf), nbytes, repeats, _abi.ptr(sink),
+                                                     _abi.stream_ptr(dev)), 'cmf_read_probe')
+        call()
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        p0.record()
+        call()
+        p1.record()
+        torch.cuda.synchronize()
+        return nbytes * repeats / (p0.elapsed_time(p1) * 1e-3) / 1e9
+    l2_gbs = read_probe(48 << 20, 200)
+    hbm_read_gbs = read_probe(4 << 30, 2)
+    roofline['read_probe_gbs'] = {'l2_resident_48MB': l2_gbs, 'hbm_4GB': hbm_read_gbs}
+    roofline['kernel_frac_of_l2_read_probe'] = achieved / l2_gbs
     traffic_file = os.path.join(ROOT, 'profiles', 'traffic.json')
     if os.path.exists(traffic_file):
         try:

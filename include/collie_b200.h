@@ -381,6 +381,11 @@ CMF_API int cmf_score_tile(const float *U, const float *I, const float *bu, cons
                    const int32_t *user_ids, int64_t n_users_tile, int64_t num_items, float *out,
                    void *stream);
 
+/* Measurement helper (no reference counterpart): reads `bytes` of `buf` `repeats` times with a
+ * persistent grid of 16-byte loads; timed by the caller, it gives the read bandwidth of L2 (buffer
+ * below the L2 size) or of HBM (buffer far above it) that bench.py quotes next to its kernels. */
+CMF_API int cmf_read_probe(const void *buf, size_t bytes, int32_t repeats, float *out, void *stream);
+
 /* Tuning knobs (process-wide). key 0: chunk length L of the fused step (0 = automatic); key 1:
  * widest lane group per row in the generic fused kernel (8, 16 or 32); key 2: kernel choice
  * (0 automatic, 1 generic fused kernel, 2 split k_fwd_loss + k_bwd_update). Results do not depend on any of them beyond
