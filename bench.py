@@ -326,8 +326,10 @@ def run_ours(args, rank, world, local_rank):
     lib.cmf_profile_enable(1)
     prof_steps = min(steps, 20)
     outs = {'negs': None}
-    for i in range(prof_steps):
-        model.fused_step(device_batch(1000 + i), optimizers=opts, interactions=data, epoch=2,
+    last = None
+    for i in range(prof_steps):          # the same batches as the timed loop: the loader's plan
+        last, ep_ = feed.next()
+        model.fused_step(last, optimizers=opts, interactions=data, epoch=ep_,
                          outputs=outs if i == prof_steps - 1 else None)
     C = _abi.C
     ms4 = (C.c_double * 4)()
@@ -336,7 +338,6 @@ def run_ours(args, rank, world, local_rank):
     lib.cmf_profile_read(ms4, C.byref(split), C.byref(n_steps), C.byref(item_rows),
                          C.byref(user_rows))
     lib.cmf_profile_enable(0)
-    last = device_batch(1000 + prof_steps - 1)
     uq = int(torch.unique(last.users).numel())
     iq = int(torch.unique(torch.cat([outs['negs'].flatten(), last.items.long()])).numel())
     D, N, T = w['dim'], w['n_neg'], 4
@@ -395,8 +396,30 @@ def run_ours(args, rank, world, local_rank):
         return nbytes * repeats / (p0.elapsed_time(p1) * 1e-3) / 1e9
     l2_gbs = read_probe(48 << 20, 200)
     hbm_read_gbs = read_probe(4 << 30, 2)
-    roofline['read_probe_gbs'] = {'l2_resident_48MB': l2_gbs, 'hbm_4GB': hbm_read_gbs}
+    # ... and of the kernel's own access pattern without its arithmetic: the same number of random
+    # 512-byte rows of the item table, 16 loads in flight per lane (cmf_gather_probe)
+    gather_gbs = None
+    if D == 128:
+        n_rows = B * (2 + N)
+        idx = torch.randint(0, w['num_items'], (n_rows,), dtype=torch.int32, device=dev)
+        sink = torch.zeros(1, dtype=torch.float32, device=dev)
+        tab = model.item_embeddings.weight.data
+        gp = lambda: _abi.check(lib.cmf_gather_probe(_abi.ptr(tab), _abi.ptr(idx), n_rows, 4, 1, 4,
+                                                     _abi.ptr(sink), _abi.stream_ptr(dev)),
+                                'cmf_gather_probe')
+        gp()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        for _ in range(5):
+            gp()
+        g1.record()
+        torch.cuda.synchronize()
+        gather_gbs = 5 * n_rows * 512 / (g0.elapsed_time(g1) * 1e-3) / 1e9
+    roofline['read_probe_gbs'] = {'l2_resident_48MB': l2_gbs, 'hbm_4GB': hbm_read_gbs,
+                                  'gather_512B_rows_l2': gather_gbs}
     roofline['kernel_frac_of_l2_read_probe'] = achieved / l2_gbs
+    if gather_gbs:
+        roofline['kernel_frac_of_gather_probe'] = achieved / gather_gbs
     traffic_file = os.path.join(ROOT, 'profiles', 'traffic.json')
     if os.path.exists(traffic_file):
         try:

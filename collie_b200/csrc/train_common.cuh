@@ -186,7 +186,7 @@ __device__ __forceinline__ float ideal_of(const StepDev& p, int pos, int neg) {
 
 // train_step_v3.cu: the split fast path (k_fwd_loss + k_bwd_update)
 bool v3_supported(int D, int N);
-int launch_fwd_loss_v3(const StepDev& p, cudaStream_t s);
+int launch_fwd_loss_v3(const StepDev& p, bool sort_runs_alongside, cudaStream_t s);
 int launch_bwd_update_v3(const StepDev& p, int max_chunk_len, cudaStream_t s);
 
 }  // namespace cmf

@@ -714,7 +714,7 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
 
   if (split) {
     // e0 -> e1: k_fwd_loss;  e1 -> e2: what is left of the sort;  e2 -> e3: k_bwd_update
-    int rc = launch_fwd_loss_v3(p, s);
+    int rc = launch_fwd_loss_v3(p, side != nullptr, s);
     if (rc != CMF_OK) return rc;
     if (g_prof_on) CMF_CUDA(cudaEventRecord(prof.e[1], s));
     if (side) CMF_CUDA(cudaStreamWaitEvent(s, side->join, 0));

@@ -784,13 +784,16 @@ static cudaError_t launch_g8(const StepDev& p, bool full, int grid, cudaStream_t
   return e == cudaSuccess ? cudaGetLastError() : e;
 }
 
-int launch_fwd_loss_v3(const StepDev& p, cudaStream_t s) {
+int launch_fwd_loss_v3(const StepDev& p, bool sort_runs_alongside, cudaStream_t s) {
   const int D4 = p.D / 4;
   if (D4 <= 32) {
     // 8 lanes per interaction, 4 interactions per warp instruction
     const int KQ = (D4 + 7) / 8;
     const bool full = (D4 == 8 * KQ);
-    const int grid = blocks_for((p.B + 31) / 32, 4);
+    // one resident wave (2 CTAs of 124 registers per SM): a second wave costs 8 % of the kernel.
+    // With the batch sort running next to it on the side stream, smaller CTAs-in-waves leave the
+    // sort's kernels a way in.
+    const int grid = blocks_for((p.B + 31) / 32, sort_runs_alongside ? 4 : 2);
     cudaError_t e;
     if (KQ == 1) e = launch_g8<1>(p, full, grid, s);
     else if (KQ == 2) e = launch_g8<2>(p, full, grid, s);

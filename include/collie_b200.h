@@ -385,6 +385,11 @@ CMF_API int cmf_score_tile(const float *U, const float *I, const float *bu, cons
  * persistent grid of 16-byte loads; timed by the caller, it gives the read bandwidth of L2 (buffer
  * below the L2 size) or of HBM (buffer far above it) that bench.py quotes next to its kernels. */
 CMF_API int cmf_read_probe(const void *buf, size_t bytes, int32_t repeats, float *out, void *stream);
+/* Same idea for the training step's access pattern: reads the 512-byte rows idx[0..n_idx) of
+ * `table` ([rows, 128] fp32), `unroll` rows in flight per warp, layout 0 = one row per warp
+ * instruction, 1 = the 8-lanes-per-row layout of the forward kernel. */
+CMF_API int cmf_gather_probe(const void *table, const int32_t *idx, int64_t n_idx, int32_t unroll,
+                     int32_t layout, int32_t ctas_per_sm, float *out, void *stream);
 
 /* Tuning knobs (process-wide). key 0: chunk length L of the fused step (0 = automatic); key 1:
  * widest lane group per row in the generic fused kernel (8, 16 or 32); key 2: kernel choice
