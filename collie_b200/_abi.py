@@ -127,6 +127,7 @@ SIGNATURES = {
     'cmf_read_probe': (C.c_int, [C.c_void_p, C.c_size_t, C.c_int32, C.c_void_p, C.c_void_p]),
     'cmf_gather_probe': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
                                   C.c_int32, C.c_void_p, C.c_void_p]),
+    'cmf_red_probe': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
     'cmf_set_tuning': (C.c_int, [C.c_int32, C.c_int32]),
     'cmf_profile_enable': (C.c_int, [C.c_int32]),
     'cmf_profile_read': (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int32)]

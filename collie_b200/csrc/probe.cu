@@ -80,6 +80,29 @@ k_gather_probe(const float4* __restrict__ table, const int32_t* __restrict__ idx
 
 }  // namespace cmf
 
+namespace cmf {
+// RED probe: vector atomic adds of 512-byte rows into `table` at idx[...] (k_bwd_update's item
+// gradient pattern): one row per warp instruction, fire and forget.
+__global__ void __launch_bounds__(256)
+k_red_probe(float4* __restrict__ table, const int32_t* __restrict__ idx, int64_t n_idx) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const float4 one = make_float4(1.f, 1.f, 1.f, 1.f);
+  for (int64_t i = warp; i < n_idx; i += n_warps)
+    atomicAdd(table + (int64_t)idx[i] * 32 + lane, one);
+}
+}  // namespace cmf
+
+extern "C" int cmf_red_probe(void* table, const int32_t* idx, int64_t n_idx, int32_t ctas_per_sm,
+                             void* stream) {
+  CMF_REQUIRE(table && idx && n_idx > 0 && ctas_per_sm >= 1 && ctas_per_sm <= 8,
+              "cmf_red_probe: bad argument");
+  k_red_probe<<<num_sms() * ctas_per_sm, 256, 0, (cudaStream_t)stream>>>((float4*)table, idx, n_idx);
+  CMF_LAUNCH_CHECK();
+  return CMF_OK;
+}
+
 extern "C" int cmf_gather_probe(const void* table, const int32_t* idx, int64_t n_idx,
                                 int32_t unroll, int32_t layout, int32_t ctas_per_sm, float* out,
                                 void* stream) {

@@ -388,6 +388,10 @@ CMF_API int cmf_read_probe(const void *buf, size_t bytes, int32_t repeats, float
 /* Same idea for the training step's access pattern: reads the 512-byte rows idx[0..n_idx) of
  * `table` ([rows, 128] fp32), `unroll` rows in flight per warp, layout 0 = one row per warp
  * instruction, 1 = the 8-lanes-per-row layout of the forward kernel. */
+/* ... and for the backward kernel's item-gradient pattern: vector atomic adds (RED) of 512-byte
+ * rows into `table` at idx[0..n_idx). */
+CMF_API int cmf_red_probe(void *table, const int32_t *idx, int64_t n_idx, int32_t ctas_per_sm,
+                  void *stream);
 CMF_API int cmf_gather_probe(const void *table, const int32_t *idx, int64_t n_idx, int32_t unroll,
                      int32_t layout, int32_t ctas_per_sm, float *out, void *stream);
 
