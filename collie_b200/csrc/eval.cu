@@ -125,6 +125,12 @@ struct RankDev {
   float* sig_scratch;  // [total targets of the tile], same offsets as tgt_items (minus indptr[0])
 };
 
+constexpr int kListK = 12;   // k up to which the one-pass ranking keeps per-thread lists
+
+// One CTA per user row. Everything that needs the whole row is gathered in ONE pass over it:
+// per-thread top-k lists (shared memory, sorted), the count of items ranked before the best
+// target (MRR), the Mann-Whitney pair count against the sorted target sigmoids (AUC); the lists
+// are then merged by k block-wide selections. k > kListK falls back to k selection passes.
 __global__ void __launch_bounds__(256)
 k_rank_rows(const RankDev p) {
   __shared__ Key s_key[8];
@@ -132,63 +138,25 @@ k_rank_rows(const RankDev p) {
   __shared__ double s_dbl[8];
   __shared__ float s_sig[kSigSmem];
   __shared__ float s_raw[kSigSmem];
+  __shared__ float s_ls[kListK][256];   // [rank in the thread's list][thread]: conflict-free
+  __shared__ int s_li[kListK][256];
+  const int tid = threadIdx.x;
   const int r = blockIdx.x;
   const float* row = p.S + (int64_t)r * p.ld;
   const int64_t t0 = p.tgt_indptr ? p.tgt_indptr[r] : 0, t1 = p.tgt_indptr ? p.tgt_indptr[r + 1] : 0;
   const int n_tgt = (int)(t1 - t0);
   const int32_t* tgt = p.tgt_items + t0;
   const int lo_id = (int)p.item_offset, hi_id = (int)(p.item_offset + p.n_items);
+  const int K = p.k;
+  const bool want_topk = p.topk_ids || p.topk_scores || p.ap;
+  const bool lists = want_topk && K <= kListK;
 
-  // ---- top-k: k selection passes, each finds the best key strictly after the previous one
-  if (p.topk_ids || p.topk_scores || p.ap) {
-    int hits = 0;
-    double ap_acc = 0.0;
-    Key prev;
-    prev.s = INFINITY;
-    prev.id = -1;
-    for (int j = 0; j < p.k; ++j) {
-      Key best;
-      best.s = -INFINITY;
-      best.id = -1;
-      for (int64_t c = threadIdx.x; c < p.n_items; c += blockDim.x) {
-        Key cur;
-        cur.s = row[c];
-        cur.id = (int)(p.item_offset + c);
-        const bool after_prev = (prev.id < 0) || before(prev, cur);
-        if (after_prev && (best.id < 0 || before(cur, best))) best = cur;
-      }
-      best = block_best(best, s_key);
-      if (threadIdx.x == 0) {
-        if (p.topk_ids) p.topk_ids[(int64_t)r * p.k + j] = best.id;
-        if (p.topk_scores) p.topk_scores[(int64_t)r * p.k + j] = best.id >= 0 ? best.s : -INFINITY;
-        if (best.id >= 0 && csr_contains(tgt, 0, n_tgt, best.id)) {
-          ++hits;
-          ap_acc += (double)hits / (double)(j + 1);
-        }
-      }
-      prev = best;
-      if (best.id < 0) {  // fewer than k items in this shard: pad
-        if (threadIdx.x == 0)
-          for (int jj = j + 1; jj < p.k; ++jj) {
-            if (p.topk_ids) p.topk_ids[(int64_t)r * p.k + jj] = -1;
-            if (p.topk_scores) p.topk_scores[(int64_t)r * p.k + jj] = -INFINITY;
-          }
-        break;
-      }
-    }
-    if (threadIdx.x == 0 && p.ap) {
-      // AP@k = sum_j acc_j * cumsum_j / j / min(k, nnz_u); 0 when the user has no targets
-      const int denom = p.k < n_tgt ? p.k : n_tgt;
-      p.ap[r] = denom > 0 ? ap_acc / (double)denom : 0.0;
-    }
-  }
-
-  // ---- MRR ingredient: the best-ranked target and how many items precede it
+  // ---- MRR: the best-ranked target (its row entry is read directly)
+  Key best;
+  best.s = -INFINITY;
+  best.id = -1;
   if (p.want_mrr) {
-    Key best;
-    best.s = -INFINITY;
-    best.id = -1;
-    for (int t = threadIdx.x; t < n_tgt; t += blockDim.x) {
+    for (int t = tid; t < n_tgt; t += blockDim.x) {
       const int id = tgt[t];
       if (id < lo_id || id >= hi_id) continue;
       Key cur;
@@ -197,7 +165,7 @@ k_rank_rows(const RankDev p) {
       if (best.id < 0 || before(cur, best)) best = cur;
     }
     best = block_best(best, s_key);
-    if (threadIdx.x == 0) {
+    if (tid == 0) {
       if (p.best_score) p.best_score[r] = best.id >= 0 ? best.s : -INFINITY;
       if (p.best_id) p.best_id[r] = best.id;
     }
@@ -205,42 +173,57 @@ k_rank_rows(const RankDev p) {
       best.id = p.ext_best_id[r];
       best.s = p.ext_best_score[r];
     }
-    long long cnt = 0;
-    if (best.id >= 0) {
-      for (int64_t c = threadIdx.x; c < p.n_items; c += blockDim.x) {
-        Key cur;
-        cur.s = row[c];
-        cur.id = (int)(p.item_offset + c);
-        cnt += before(cur, best) ? 1 : 0;
-      }
-    }
-    cnt = block_sum<long long>(cnt, s_ll);
-    if (threadIdx.x == 0 && p.n_before_best) p.n_before_best[r] = best.id >= 0 ? (int)cnt : -1;
   }
 
-  // ---- AUC ingredient: sum over targets of (#non-targets with lower sigmoid + ties / 2)
-  if (p.want_auc) {
-    double total = 0.0;
-    if (n_tgt > 0) {
-      const bool in_smem = n_tgt <= kSigSmem;
-      float* sig = in_smem ? s_sig : p.sig_scratch + 2 * (t0 - p.tgt_indptr[0]);
-      float* raw = in_smem ? s_raw : sig + n_tgt;
-      for (int t = threadIdx.x; t < n_tgt; t += blockDim.x) raw[t] = sigmoidf_(row[tgt[t] - lo_id]);
-      __syncthreads();
-      // rank-sort the targets' sigmoids (ascending) by counting
-      for (int t = threadIdx.x; t < n_tgt; t += blockDim.x) {
-        const float v = raw[t];
-        int rank = 0;
-        for (int q = 0; q < n_tgt; ++q) {
-          const float w = raw[q];
-          rank += (w < v || (w == v && q < t)) ? 1 : 0;
-        }
-        sig[rank] = v;
+  // ---- AUC: the targets' sigmoids, rank-sorted ascending by counting
+  const bool auc = p.want_auc && n_tgt > 0;
+  float* sig = s_sig;
+  if (auc) {
+    const bool in_smem = n_tgt <= kSigSmem;
+    sig = in_smem ? s_sig : p.sig_scratch + 2 * (t0 - p.tgt_indptr[0]);
+    float* raw = in_smem ? s_raw : sig + n_tgt;
+    for (int t = tid; t < n_tgt; t += blockDim.x) raw[t] = sigmoidf_(row[tgt[t] - lo_id]);
+    __syncthreads();
+    for (int t = tid; t < n_tgt; t += blockDim.x) {
+      const float v = raw[t];
+      int rank = 0;
+      for (int q = 0; q < n_tgt; ++q) {
+        const float w = raw[q];
+        rank += (w < v || (w == v && q < t)) ? 1 : 0;
       }
-      __syncthreads();
-      // every item adds (#targets above it) + (#targets equal to it) / 2
-      for (int64_t c = threadIdx.x; c < p.n_items; c += blockDim.x) {
-        const float v = sigmoidf_(row[c]);
+      sig[rank] = v;
+    }
+    __syncthreads();
+  }
+
+  // ---- the pass over the row
+  int have = 0;             // entries in this thread's list
+  float worst = -INFINITY;  // score of the list's last entry once it is full
+  long long cnt = 0;
+  double total = 0.0;
+  const bool one_pass = lists || (p.want_mrr && best.id >= 0) || auc;
+  if (one_pass) {
+    for (int64_t c = tid; c < p.n_items; c += blockDim.x) {
+      Key cur;
+      cur.s = row[c];
+      cur.id = (int)(p.item_offset + c);
+      if (lists && (have < K || cur.s > worst)) {
+        // ids grow along a thread's walk: an equal score never displaces an entry; sorted insert
+        int pos = have < K ? have : K - 1;
+        while (pos > 0 && s_ls[pos - 1][tid] < cur.s) {
+          s_ls[pos][tid] = s_ls[pos - 1][tid];
+          s_li[pos][tid] = s_li[pos - 1][tid];
+          --pos;
+        }
+        s_ls[pos][tid] = cur.s;
+        s_li[pos][tid] = cur.id;
+        if (have < K) ++have;
+        if (have == K) worst = s_ls[K - 1][tid];
+      }
+      if (p.want_mrr && best.id >= 0) cnt += before(cur, best) ? 1 : 0;
+      if (auc) {
+        // every item adds (#targets above it) + (#targets equal to it) / 2
+        const float v = sigmoidf_(cur.s);
         int lo = 0, hi = n_tgt;  // lower_bound
         while (lo < hi) { const int mid = (lo + hi) >> 1; if (sig[mid] < v) lo = mid + 1; else hi = mid; }
         const int lb = lo;
@@ -249,9 +232,65 @@ k_rank_rows(const RankDev p) {
         total += (double)(n_tgt - lo) + 0.5 * (double)(lo - lb);
       }
     }
+  }
+
+  // ---- top-k: k block-wide selections, over the list heads (or over the row when k is large)
+  if (want_topk) {
+    int hits = 0, head = 0;
+    double ap_acc = 0.0;
+    Key prev;
+    prev.s = INFINITY;
+    prev.id = -1;
+    for (int j = 0; j < K; ++j) {
+      Key mine;
+      mine.s = -INFINITY;
+      mine.id = -1;
+      if (lists) {
+        if (head < have) { mine.s = s_ls[head][tid]; mine.id = s_li[head][tid]; }
+      } else {
+        for (int64_t c = tid; c < p.n_items; c += blockDim.x) {
+          Key cur;
+          cur.s = row[c];
+          cur.id = (int)(p.item_offset + c);
+          const bool after_prev = (prev.id < 0) || before(prev, cur);
+          if (after_prev && (mine.id < 0 || before(cur, mine))) mine = cur;
+        }
+      }
+      const Key pick = block_best(mine, s_key);
+      if (lists && pick.id >= 0 && pick.id == mine.id) ++head;
+      if (tid == 0) {
+        if (p.topk_ids) p.topk_ids[(int64_t)r * K + j] = pick.id;
+        if (p.topk_scores) p.topk_scores[(int64_t)r * K + j] = pick.id >= 0 ? pick.s : -INFINITY;
+        if (pick.id >= 0 && csr_contains(tgt, 0, n_tgt, pick.id)) {
+          ++hits;
+          ap_acc += (double)hits / (double)(j + 1);
+        }
+      }
+      prev = pick;
+      if (pick.id < 0) {  // fewer than k items in this shard: pad
+        if (tid == 0)
+          for (int jj = j + 1; jj < K; ++jj) {
+            if (p.topk_ids) p.topk_ids[(int64_t)r * K + jj] = -1;
+            if (p.topk_scores) p.topk_scores[(int64_t)r * K + jj] = -INFINITY;
+          }
+        break;
+      }
+    }
+    if (tid == 0 && p.ap) {
+      // AP@k = sum_j acc_j * cumsum_j / j / min(k, nnz_u); 0 when the user has no targets
+      const int denom = K < n_tgt ? K : n_tgt;
+      p.ap[r] = denom > 0 ? ap_acc / (double)denom : 0.0;
+    }
+  }
+
+  if (p.want_mrr) {
+    cnt = block_sum<long long>(cnt, s_ll);
+    if (tid == 0 && p.n_before_best) p.n_before_best[r] = best.id >= 0 ? (int)cnt : -1;
+  }
+  if (p.want_auc) {
     total = block_sum<double>(total, s_dbl);
     // target-target pairs (self pairs included) contribute exactly n_tgt^2 / 2
-    if (threadIdx.x == 0 && p.auc_pairs)
+    if (tid == 0 && p.auc_pairs)
       p.auc_pairs[r] = n_tgt > 0 ? total - 0.5 * (double)n_tgt * (double)n_tgt : 0.0;
   }
 }

@@ -17,7 +17,7 @@ from . import _abi
 from .interactions import Interactions
 
 # users per fused tile; the result does not depend on it (per-user values are summed)
-_TILE_USERS = 256
+_TILE_USERS = 512
 _MAX_TILE_BYTES = 1 << 30
 _TC_TILE_USERS = 32768   # users per tensor-core call (128-user CTA tiles inside)
 
