@@ -63,6 +63,94 @@ k_score_tile(const float* __restrict__ U, const float* __restrict__ I, const flo
   }
 }
 
+// ---- the same contraction for full-size tiles: 128 x 128 outputs per CTA, 8 x 8 per thread
+// (two 4-wide halves 64 apart on each axis, so shared-memory reads are conflict-free float4s), K step
+// 8, global loads of the next K step in flight while the current one is multiplied. Every output is
+// accumulated over d in ascending order with fmaf, exactly like k_score_tile: same bits.
+constexpr int BM = 128, BN = 128, BK = 8;
+
+__global__ void __launch_bounds__(256)
+k_score_tile_128(const float* __restrict__ U, const float* __restrict__ I,
+                 const float* __restrict__ bu, const float* __restrict__ bi, int D,
+                 const int32_t* __restrict__ user_ids, int64_t n_users, int64_t item_offset,
+                 int64_t n_items, float* __restrict__ out, int64_t ld_out) {
+  __shared__ __align__(16) float As[2][BK][BM];
+  __shared__ __align__(16) float Bs[2][BK][BN];
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int64_t row0 = (int64_t)blockIdx.y * BM, col0 = (int64_t)blockIdx.x * BN;
+  // loader: thread -> (row = tid / 2, four consecutive k's)
+  const int lr = tid >> 1, lk = (tid & 1) * 4;
+  const int64_t arow = row0 + lr, brow = col0 + lr;
+  const float* aptr = (arow < n_users) ? U + (int64_t)user_ids[arow] * D : nullptr;
+  const float* bptr = (brow < n_items) ? I + (item_offset + brow) * D : nullptr;
+  const bool vec = (D & 3) == 0;
+  auto fetch = [&](const float* src, int k0, float (&v)[4]) {
+    const int d = k0 + lk;
+    if (src && vec && d + 3 < D) {
+      const float4 t = *reinterpret_cast<const float4*>(src + d);
+      v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] = (src && d + j < D) ? src[d + j] : 0.f;
+    }
+  };
+  float acc[8][8] = {};
+  float ra[4], rb[4];
+  fetch(aptr, 0, ra);
+  fetch(bptr, 0, rb);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) { As[0][lk + j][lr] = ra[j]; Bs[0][lk + j][lr] = rb[j]; }
+  __syncthreads();
+  int buf = 0;
+  for (int k0 = 0; k0 < D; k0 += BK) {
+    const bool more = k0 + BK < D;
+    if (more) { fetch(aptr, k0 + BK, ra); fetch(bptr, k0 + BK, rb); }
+#pragma unroll
+    for (int k = 0; k < BK; ++k) {
+      const float4 a0 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 4]);
+      const float4 a1 = *reinterpret_cast<const float4*>(&As[buf][k][64 + ty * 4]);
+      const float4 b0 = *reinterpret_cast<const float4*>(&Bs[buf][k][tx * 4]);
+      const float4 b1 = *reinterpret_cast<const float4*>(&Bs[buf][k][64 + tx * 4]);
+      const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    if (more) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { As[buf ^ 1][lk + j][lr] = ra[j]; Bs[buf ^ 1][lk + j][lr] = rb[j]; }
+    }
+    __syncthreads();
+    buf ^= 1;
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int64_t r = row0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
+    if (r >= n_users) continue;
+    const float ub = bu[user_ids[r]];
+#pragma unroll
+    for (int jh = 0; jh < 2; ++jh) {
+      const int64_t c = col0 + jh * 64 + tx * 4;
+      if (c + 3 < n_items && ((ld_out & 3) == 0) &&
+          ((reinterpret_cast<uintptr_t>(out) & 15) == 0)) {
+        float4 o;
+        o.x = acc[i][jh * 4 + 0] + ub + bi[item_offset + c + 0];
+        o.y = acc[i][jh * 4 + 1] + ub + bi[item_offset + c + 1];
+        o.z = acc[i][jh * 4 + 2] + ub + bi[item_offset + c + 2];
+        o.w = acc[i][jh * 4 + 3] + ub + bi[item_offset + c + 3];
+        *reinterpret_cast<float4*>(out + r * ld_out + c) = o;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (c + j < n_items) out[r * ld_out + c + j] = acc[i][jh * 4 + j] + ub + bi[item_offset + c + j];
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------ ranking: one CTA per user row
 struct Key {
   float s;
@@ -297,6 +385,21 @@ k_rank_rows(const RankDev p) {
 
 static size_t eval_ws_scores(int64_t n, int64_t items) { return align_up(sizeof(float) * n * items, 256); }
 
+// 128 x 128 tiles when the user tile fills them, else the 64 x 64 kernel (identical results)
+static void launch_score_tile(const float* U, const float* I, const float* bu, const float* bi,
+                              int D, const int32_t* user_ids, int64_t n_users, int64_t item_offset,
+                              int64_t n_items, float* out, int64_t ld_out, cudaStream_t s) {
+  if (n_users >= 96 && n_items >= 96) {
+    dim3 grid((unsigned)((n_items + BN - 1) / BN), (unsigned)((n_users + BM - 1) / BM));
+    k_score_tile_128<<<grid, 256, 0, s>>>(U, I, bu, bi, D, user_ids, n_users, item_offset, n_items,
+                                          out, ld_out);
+  } else {
+    dim3 grid((unsigned)((n_items + TN - 1) / TN), (unsigned)((n_users + TM - 1) / TM));
+    k_score_tile<<<grid, 256, 0, s>>>(U, I, bu, bi, D, user_ids, n_users, item_offset, n_items, out,
+                                      ld_out);
+  }
+}
+
 }  // namespace cmf
 
 using namespace cmf;
@@ -317,9 +420,8 @@ extern "C" int cmf_score_tile(const float* U, const float* I, const float* bu, c
   CMF_REQUIRE(D >= 1, "cmf_score_tile: bad embedding_dim");
   if (n_users_tile == 0 || num_items == 0) return CMF_OK;
   CMF_REQUIRE(user_ids, "cmf_score_tile: null user ids");
-  dim3 grid((unsigned)((num_items + TN - 1) / TN), (unsigned)((n_users_tile + TM - 1) / TM));
-  k_score_tile<<<grid, 256, 0, (cudaStream_t)stream>>>(U, I, bu, bi, D, user_ids, n_users_tile, 0,
-                                                       num_items, out, num_items);
+  launch_score_tile(U, I, bu, bi, D, user_ids, n_users_tile, 0, num_items, out, num_items,
+                    (cudaStream_t)stream);
   CMF_LAUNCH_CHECK();
   return CMF_OK;
 }
@@ -351,10 +453,8 @@ extern "C" int cmf_eval_tile(const cmf_eval_t* a, void* stream) {
   float* sig = (float*)((char*)a->workspace + eval_ws_scores(a->n_users_tile, a->num_items_shard));
   if (!S) {
     float* Sw = (float*)a->workspace;
-    dim3 grid((unsigned)((a->num_items_shard + TN - 1) / TN),
-              (unsigned)((a->n_users_tile + TM - 1) / TM));
-    k_score_tile<<<grid, 256, 0, s>>>(a->U, a->I, a->bu, a->bi, a->D, a->user_ids, a->n_users_tile,
-                                      a->item_offset, a->num_items_shard, Sw, a->num_items_shard);
+    launch_score_tile(a->U, a->I, a->bu, a->bi, a->D, a->user_ids, a->n_users_tile, a->item_offset,
+                      a->num_items_shard, Sw, a->num_items_shard, s);
     CMF_LAUNCH_CHECK();
     S = Sw;
   }
