@@ -34,6 +34,8 @@ struct WsLayout {
   // per step
   size_t hdr, partials, item_list, user_list, keys_out, vals_in, vals_out, iota, g_arr, sel_arr, cub_temp;
   size_t cub_temp_bytes, total;
+  // large item tables: the touched-row list sorted by row, so the update streams through memory
+  size_t item_list_sorted, cub_items_temp, cub_items_temp_bytes;
 };
 
 static size_t cub_sort_bytes(int64_t B) {
@@ -68,6 +70,11 @@ static WsLayout ws_layout(int64_t B, int64_t num_users, int64_t num_items, int D
   w.sel_arr = take(sizeof(int32_t) * B);
   w.cub_temp_bytes = cub_sort_bytes(B);
   w.cub_temp = take(w.cub_temp_bytes);
+  w.item_list_sorted = take(sizeof(int) * num_items);
+  w.cub_items_temp_bytes = 0;
+  cub::DeviceRadixSort::SortKeys((void*)nullptr, w.cub_items_temp_bytes, (const uint32_t*)nullptr,
+                                 (uint32_t*)nullptr, (int)num_items, 0, 32, (cudaStream_t)0);
+  w.cub_items_temp = take(w.cub_items_temp_bytes);
   w.total = o;
   return w;
 }
@@ -390,14 +397,16 @@ k_update_rows(const UpdDev p) {
   const int64_t n0 = p.skip_items ? 0 : (p.dense ? p.rows[0] : (int64_t)p.hdr->item_count);
   const int64_t n1 = p.dense ? p.rows[1] : (int64_t)p.hdr->user_count;
   const int64_t total = n0 + n1;
-  // two rows per round: the second row's loads are in flight while the first is finished
-  for (int64_t w = group; w < total; w += 2 * n_groups) {
-    RowJob<V, G, R> a, b;
-    const bool two = (w + n_groups) < total;
-    a.fetch(p, w, n0, l);
-    if (two) b.fetch(p, w + n_groups, n0, l);
-    a.finish(p, l);
-    if (two) b.finish(p, l);
+  // NJ rows per round: all their loads are requested before the first one is finished
+  constexpr int NJ = (R * V <= 4) ? 4 : 2;
+  for (int64_t w = group; w < total; w += NJ * n_groups) {
+    RowJob<V, G, R> job[NJ];
+#pragma unroll
+    for (int j = 0; j < NJ; ++j)
+      if (w + j * n_groups < total) job[j].fetch(p, w + j * n_groups, n0, l);
+#pragma unroll
+    for (int j = 0; j < NJ; ++j)
+      if (w + j * n_groups < total) job[j].finish(p, l);
   }
 }
 
@@ -676,6 +685,14 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
   const int forced_len = g_forced_chunk_len.load() > 0 ? g_forced_chunk_len.load() : 0;
 
   CMF_CUDA(cudaMemsetAsync(p.hdr, 0, sizeof(WsHeader), s));
+  // Item tables that do not stay in L2: k_update_rows walks the touched rows in row order (the
+  // list is sorted before it runs), so its reads and writes stream instead of landing in
+  // first-touch order. The unused tail of the list is pre-set above every valid id.
+  const int64_t list_cap = std::min<int64_t>(a->num_items, a->B * (int64_t)(a->N + 1));
+  const bool sort_item_list = p.train && p.use_lists && !a->skip_item_update &&
+                              (int64_t)a->num_items * a->D * 4 * 3 > ((int64_t)64 << 20);
+  if (sort_item_list)
+    CMF_CUDA(cudaMemsetAsync(p.item_list, 0x7F, sizeof(int) * (size_t)list_cap, s));
   ProfRec prof{};
   prof.split = split ? 1 : 0;
   if (g_prof_on) {
@@ -745,6 +762,17 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
     q.P[0] = a->I; q.M[0] = a->I_m; q.Vv[0] = a->I_v; q.G[0] = p.GI;
     q.bP[0] = a->bi; q.bM[0] = a->bi_m; q.bV[0] = a->bi_v; q.bG[0] = p.gbi;
     q.flag[0] = p.item_flag; q.list[0] = p.item_list; q.rows[0] = a->num_items;
+    if (sort_item_list) {
+      int bits = 1;
+      while (bits < 31 && ((int64_t)1 << bits) < a->num_items) ++bits;
+      size_t temp = w.cub_items_temp_bytes;
+      uint32_t* sorted = (uint32_t*)(base + w.item_list_sorted);
+      CMF_CUDA(cub::DeviceRadixSort::SortKeys(base + w.cub_items_temp, temp,
+                                              (const uint32_t*)p.item_list, sorted, (int)list_cap,
+                                              0, 31, s));
+      (void)bits;
+      q.list[0] = (const int*)sorted;
+    }
     q.P[1] = a->U; q.M[1] = a->U_m; q.Vv[1] = a->U_v; q.G[1] = p.GU;
     q.bP[1] = a->bu; q.bM[1] = a->bu_m; q.bV[1] = a->bu_v; q.bG[1] = p.gbu;
     q.flag[1] = p.user_flag; q.list[1] = p.user_list; q.rows[1] = a->num_users;

@@ -201,3 +201,44 @@ def test_evaluation_paths_agree_at_full_item_count(world):
     assert (ids_exact == k1[0][0]).float().mean().item() > 0.999   # (bf16-split rounding: rare swaps)
     tc2, k2 = run(1, n_u)
     assert tc2 == tc and torch.equal(k2[0][0], k1[0][0]) and torch.equal(k2[0][1], k1[0][1])
+
+
+def test_large_item_table_update_path_matches_oracle():
+    """Item tables that do not stay in L2 (> 64 MB of parameter + moment rows) take the sorted
+    touched-row list in front of k_update_rows: two steps against the oracle on a 60,000 x 128
+    item table."""
+    import collie_b200 as cb
+    from oracle import collie_oracle as O
+    rng = np.random.default_rng(33)
+    n_users, n_items, dim, n_neg, batch = 3000, 60_000, 128, 3, 4096
+    users = rng.integers(0, n_users, 3 * batch).astype(np.int32)
+    items = rng.integers(0, n_items, 3 * batch).astype(np.int32)
+    data = cb.Interactions(users=users, items=items, num_users=n_users, num_items=n_items,
+                           num_negative_samples=n_neg, allow_missing_ids=True, seed=6,
+                           remove_duplicate_user_item_pairs=False,
+                           check_num_negative_samples_is_valid=False,
+                           max_number_of_samples_to_consider=0)
+    torch.manual_seed(2)
+    model = cb.MatrixFactorizationModel(train=data, embedding_dim=dim, sparse=True, lr=1e-2,
+                                        optimizer='sparse_adam', loss='bpr',
+                                        lr_scheduler_func=None).cuda()
+    ref = O.OracleMF(n_users, n_items, dim, sparse=True)
+    names = ('user_embeddings', 'item_embeddings', 'user_biases', 'item_biases')
+    with torch.no_grad():
+        for name in names:
+            getattr(model, name).weight.mul_(8.0)        # gradients well above fp32 noise
+            getattr(ref, name).weight.copy_(getattr(model, name).weight.cpu())
+    opts = model.configure_optimizers()
+    ref_opts = O.make_optimizers(ref, 'sparse_adam', 'sgd', 1e-2, 1e-2)
+    for step in range(2):
+        sl = slice(step * batch, (step + 1) * batch)
+        bu, bp = torch.from_numpy(users[sl]), torch.from_numpy(items[sl])
+        bn = torch.from_numpy(rng.integers(0, n_items, (batch, n_neg)))
+        loss = model.fused_step(((bu.cuda(), bp.cuda()), bn.cuda()), optimizers=opts).item()
+        ref_loss = O.train_step(ref, ref_opts,
+                                lambda: ref.implicit_loss(bu, bp, bn, 'adaptive_bpr'))
+        np.testing.assert_allclose(loss, ref_loss, rtol=1e-5)
+    for name in names:
+        np.testing.assert_allclose(getattr(model, name).weight.detach().cpu().numpy(),
+                                   getattr(ref, name).weight.detach().numpy(), rtol=1e-4,
+                                   atol=1e-6, err_msg=name)
