@@ -316,6 +316,7 @@ class ShardedMatrixFactorization(object):
     def train_step(self, batch, optimizers, interactions=None, epoch=0, global_batch=None,
                    reduce_loss=True):
         """One global step; returns the global mean loss (0-d tensor, identical on every rank).
+        Collective: every rank must call it the same number of times (``common_steps_per_epoch``).
         ``global_batch``: total interactions of this step over all ranks (asked of the ranks when
         ``None``, which costs a host round trip; equal-sized batches pass ``world * B``)."""
         m = self.model
@@ -372,6 +373,18 @@ class ShardedMatrixFactorization(object):
         all_gather_rows(self.I_full, self.I_shard, self.group)
         all_gather_rows(self.bi_full.view(-1), self.bi_shard.reshape(-1), self.group)
         return self.I_full[:self.true_num_items], self.bi_full[:self.true_num_items]
+
+
+def common_steps_per_epoch(loader, group=None):
+    """Steps every rank can take in one epoch: the minimum of ``len(loader)`` over the ranks. The
+    user partition gives the ranks slightly different numbers of interactions, and
+    ``ShardedMatrixFactorization.train_step`` is collective -- a rank that took one more step than
+    the others would wait for them forever."""
+    dev = torch.device('cuda', torch.cuda.current_device()) \
+        if dist.get_backend(group) == 'nccl' else torch.device('cpu')
+    t = torch.tensor([len(loader)], dtype=torch.int64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
+    return int(t.item())
 
 
 def evaluate_sharded(metric_list, local_test, model, k=10, group=None, **kwargs):

@@ -78,6 +78,8 @@ def _collectives(rank, world):
     fo = torch.zeros(per, dtype=torch.int32)
     D.reduce_scatter_sum(fo, flags)
     assert fo.tolist() == ([1, 0, 1, 2] if rank == 0 else [0, 0, 1, 0])
+    # ranks with different numbers of batches agree on the smaller one
+    assert D.common_steps_per_epoch([0] * (5 + rank)) == 5
     # loss pieces add up to the global mean
     loss = torch.tensor(float(rank + 1)) / world
     dist.all_reduce(loss)
