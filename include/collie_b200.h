@@ -397,8 +397,11 @@ CMF_API int cmf_gather_probe(const void *table, const int32_t *idx, int64_t n_id
 
 /* Tuning knobs (process-wide). key 0: chunk length L of the fused step (0 = automatic); key 1:
  * widest lane group per row in the generic fused kernel (8, 16 or 32); key 2: kernel choice
- * (0 automatic, 1 generic fused kernel, 2 split k_fwd_loss + k_bwd_update). Results do not depend on any of them beyond
- * fp32 summation order; tests use them to cross-check the in-place and the accumulate paths. Returns the previous value, or a negative cmf_status for an unknown key. */
+ * (0 automatic, 1 generic fused kernel, 2 split k_fwd_loss + k_bwd_update); key 3: experiments on
+ * the tensor-core evaluation kernel (0 = off; 1 = skip the ranking, 2 = skip the inserts: timing
+ * only, results are then meaningless). Results do not depend on keys 0-2 beyond fp32 summation
+ * order; tests use them to cross-check the in-place and the accumulate paths. Returns the previous
+ * value, or a negative cmf_status for an unknown key. */
 CMF_API int cmf_set_tuning(int32_t key, int32_t value);
 
 /* Phase timing of cmf_train_step for bench.py's roofline line. While enabled, every step records
