@@ -213,6 +213,15 @@ class CollieMinimalTrainer(object):
         return (total_loss / max(n, 1)).item()
 
     def _val_loop_single_epoch(self, model, epoch=0):
+        loader = self.val_dataloader
+        if self.logger is None and hasattr(loader, 'epoch_plan'):
+            plan = loader.epoch_plan(model.device, epoch=epoch)
+            if plan.users.shape[0] == 0:
+                return 0.0
+            losses = model.fused_step(plan, train=False, interactions=loader.interactions,
+                                      epoch=epoch, epoch_batch_size=loader.batch_size)
+            self.val_steps += int(losses.shape[0])
+            return losses.mean().item()
         total_loss = torch.zeros((), dtype=torch.float32, device=model.device)
         n = 0
         for batch_idx, (batch, data) in enumerate(self._batches(self.val_dataloader, model,
