@@ -308,7 +308,8 @@ k_rank_rows(const RankDev p) {
         if (have < K) ++have;
         if (have == K) worst = s_ls[K - 1][tid];
       }
-      if (p.want_mrr && best.id >= 0) cnt += before(cur, best) ? 1 : 0;
+      // (the target never precedes itself, whatever arithmetic produced an external threshold)
+      if (p.want_mrr && best.id >= 0) cnt += (cur.id != best.id && before(cur, best)) ? 1 : 0;
       if (auc) {
         // every item adds (#targets above it) + (#targets equal to it) / 2
         const float v = sigmoidf_(cur.s);

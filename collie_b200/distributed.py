@@ -405,6 +405,127 @@ def evaluate_sharded(metric_list, local_test, model, k=10, group=None, **kwargs)
     return out[0] if len(out) == 1 else out
 
 
+def evaluate_item_sharded(metric_list, test_interactions, model, k=10, group=None, precision=0,
+                          tile_users=512):
+    """``evaluate_in_batches`` for ``mapk`` / ``mrr`` with the ITEM axis sharded (for
+    catalogues too large to score on one GPU): every rank holds the same test users and scores
+    them against its own contiguous block of item rows.
+
+    Per user tile: (1) the targets' exact scores come from the shard that owns each target; the
+    best target per user (score descending, id ascending) is agreed with two all-reduces;
+    (2) one ``cmf_eval_tile`` per rank over its item block gives the local top-k and the number of
+    local items ranked before that best target; (3) the local top-k lists are all-gathered and
+    merged in canonical order (``merge_topk``), AP@k is read off the merged ids; the counters are
+    summed by all-reduce. Returns what ``evaluate_in_batches`` returns, identical on every rank.
+    ``model`` holds the full-width table (e.g. the working copy of ``ShardedMatrixFactorization``);
+    only this rank's block of it is read.
+    """
+    from . import metrics as M
+    names = [M._FUSED.get(m) for m in metric_list]
+    if any(n not in ('mapk', 'mrr') for n in names):
+        raise ValueError('evaluate_item_sharded computes mapk and mrr; use evaluate_sharded '
+                         '(user-sharded) for auc or custom metrics')
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    tables = M._model_tables(model)
+    dev = tables[0].device
+    n_items = int(test_interactions.num_items)
+    if 'mapk' in names:
+        M._check_k(k, n_items)
+    per_rank = (n_items + world - 1) // world
+    lo = min(rank * per_rank, n_items)
+    hi = min(lo + per_rank, n_items)
+    n_loc = hi - lo
+    test_users = np.unique(test_interactions.mat.row)
+    indptr, tgt_items, nnz = M._targets_all_users_device(test_interactions.mat.tocsr(), test_users,
+                                                         dev)
+    users_dev = torch.from_numpy(test_users.astype(np.int32)).to(dev)
+    n_test = len(test_users)
+    # ---- (1) best target per user over all shards
+    counts = nnz.long()
+    row_of = torch.repeat_interleave(torch.arange(n_test, device=dev), counts)
+    mine = (tgt_items >= lo) & (tgt_items < hi)
+    best_s = torch.full((n_test,), -float('inf'), dtype=torch.float32, device=dev)
+    big = torch.iinfo(torch.int32).max
+    best_id = torch.full((n_test,), big, dtype=torch.int32, device=dev)
+    any_mine = bool(mine.any())
+    if any_mine:
+        with torch.no_grad():
+            sc = model(users_dev.long()[row_of[mine]], tgt_items[mine].long()).float()
+        best_s.scatter_reduce_(0, row_of[mine], sc, reduce='amax', include_self=True)
+    dist.all_reduce(best_s, op=dist.ReduceOp.MAX, group=group)
+    if any_mine:
+        at_best = sc == best_s[row_of[mine]]
+        best_id.scatter_reduce_(0, row_of[mine][at_best], tgt_items[mine][at_best].int(),
+                                reduce='amin', include_self=True)
+    dist.all_reduce(best_id, op=dist.ReduceOp.MIN, group=group)
+    best_id = torch.where(best_id == big, torch.full_like(best_id, -1), best_id)
+    return _item_sharded_tiles(M, names, k, group, world, precision, tile_users, tables, dev,
+                               n_items, lo, n_loc, indptr, tgt_items, counts, row_of, users_dev,
+                               n_test, best_s, best_id)
+
+
+def _item_sharded_tiles(M, names, k, group, world, precision, tile_users, tables, dev, n_items,
+                        lo, n_loc, indptr, tgt_items, counts, row_of, users_dev, n_test, best_s,
+                        best_id):
+    """Steps (2) and (3) of ``evaluate_item_sharded``, tile by tile."""
+    want = {'topk'} | ({'mrr'} if 'mrr' in names else set())
+    sums = {n_: torch.zeros((), dtype=torch.float64, device=dev) for n_ in names}
+    tgt_keys = row_of.long() * n_items + tgt_items.long()      # sorted: CSR order
+    ws = None
+    for s0 in range(0, n_test, tile_users):
+        e0 = min(s0 + tile_users, n_test)
+        nt = e0 - s0
+        loc_ids = torch.full((nt, k), -1, dtype=torch.int32, device=dev)
+        loc_s = torch.full((nt, k), -float('inf'), dtype=torch.float32, device=dev)
+        before = torch.zeros(nt, dtype=torch.long, device=dev)
+        if n_loc > 0:       # (more ranks than item blocks: nothing to score on the last ones)
+            kk = min(k, n_loc)
+            res = M._eval_tile(dev, nt, n_loc, kk, indptr[s0:e0 + 1], tgt_items, want,
+                               tables=tables, user_ids=users_dev[s0:e0], precision=precision,
+                               workspace=ws, item_offset=lo,
+                               ext_best=(best_s[s0:e0].contiguous(), best_id[s0:e0].contiguous()))
+            ws = res['_workspace']
+            loc_ids[:, :kk], loc_s[:, :kk] = res['topk_ids'], res['topk_scores']
+            if 'mrr' in names:
+                before = res['n_before_best'].clamp(min=0).long()
+        if 'mapk' in names:
+            all_ids = [torch.empty_like(loc_ids) for _ in range(world)]
+            all_s = [torch.empty_like(loc_s) for _ in range(world)]
+            dist.all_gather(all_ids, loc_ids, group=group)
+            dist.all_gather(all_s, loc_s, group=group)
+            _, top = merge_topk(torch.cat(all_s, dim=1), torch.cat(all_ids, dim=1), k)
+            ap = ap_from_topk_ids(top, torch.arange(s0, e0, device=dev), tgt_keys, counts[s0:e0],
+                                  n_items)
+            sums['mapk'] += ap.sum()
+        if 'mrr' in names:
+            dist.all_reduce(before, group=group)
+            has = best_id[s0:e0] >= 0
+            sums['mrr'] += torch.where(has, 1.0 / (before.double() + 1.0),
+                                       torch.zeros(nt, dtype=torch.float64, device=dev)).sum()
+    out = [float(sums[n_] / n_test) for n_ in names]
+    return out[0] if len(out) == 1 else out
+
+
+def ap_from_topk_ids(top_ids, rows, tgt_keys, n_targets, n_items):
+    """AP@k per user from ranked ids ``[n, k]`` (-1 = padding): ``tgt_keys`` = sorted
+    ``row * n_items + item`` of every (user row, target) pair, ``rows`` = the user row of each line
+    of ``top_ids``, ``n_targets`` = targets per user. Same formula as ``mapk``
+    (collie/metrics.py:176-196): sum_j hit_j * precision@j / min(k, n_targets); 0 without targets."""
+    k = top_ids.shape[1]
+    q = rows.view(-1, 1).long() * n_items + top_ids.long()
+    if len(tgt_keys):
+        at = torch.searchsorted(tgt_keys, q.clamp(min=0)).clamp(max=len(tgt_keys) - 1)
+        hit = (top_ids >= 0) & (tgt_keys[at] == q)
+    else:
+        hit = torch.zeros_like(top_ids, dtype=torch.bool)
+    hit = hit.double()
+    prec = torch.cumsum(hit, dim=1) / torch.arange(1, k + 1, device=top_ids.device,
+                                                   dtype=torch.float64)
+    denom = torch.minimum(n_targets.long(), torch.full_like(n_targets.long(), k)).double()
+    return torch.where(denom > 0, (prec * hit).sum(dim=1) / denom.clamp(min=1),
+                       torch.zeros_like(denom))
+
+
 def merge_topk(scores, ids, k):
     """Merge per-shard top-k candidates ``[n, shards * k]`` into the global top-k in canonical order
     (score descending, item id ascending); ids < 0 are padding. Returns ``(scores, ids)``."""

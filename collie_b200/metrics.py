@@ -55,8 +55,11 @@ def _targets_all_users_device(targets: csr_matrix, test_users, device):
 
 
 def _eval_tile(device, n_users, n_items, k, indptr, tgt_items, want, tables=None, user_ids=None,
-               scores=None, precision=0, workspace=None, reuse_item_prep=False):
-    """One ``cmf_eval_tile`` call; returns dict of per-user device tensors."""
+               scores=None, precision=0, workspace=None, reuse_item_prep=False, item_offset=0,
+               ext_best=None):
+    """One ``cmf_eval_tile`` call; returns dict of per-user device tensors. ``item_offset`` /
+    ``n_items`` select an item shard of the table (global ids come back); ``ext_best`` = (score,
+    id) of every user's best target over ALL shards, against which the MRR counter counts."""
     a = _abi.cmf_eval_t()
     keep = []
     if scores is not None:
@@ -68,7 +71,10 @@ def _eval_tile(device, n_users, n_items, k, indptr, tgt_items, want, tables=None
         a.U, a.I, a.bu, a.bi = U.data_ptr(), I.data_ptr(), bu.data_ptr(), bi.data_ptr()
         a.D = U.shape[1]
         a.user_ids = user_ids.data_ptr()
-    a.n_users_tile, a.item_offset, a.num_items_shard, a.k = n_users, 0, n_items, k
+    a.n_users_tile, a.item_offset, a.num_items_shard, a.k = n_users, int(item_offset), n_items, k
+    if ext_best is not None:
+        a.ext_best_score, a.ext_best_id = ext_best[0].data_ptr(), ext_best[1].data_ptr()
+        keep.extend(ext_best)
     a.tgt_indptr, a.tgt_items = indptr.data_ptr(), tgt_items.data_ptr()
     a.precision = precision
     a.reuse_item_prep = 1 if reuse_item_prep else 0

@@ -115,3 +115,35 @@ def test_merge_topk_canonical_order():
         assert i[r].tolist() == order
         assert s[r].tolist() == [float(scores[r, j]) for j in order]
     del masked, drop
+
+
+def test_ap_from_merged_topk_ids_equals_oracle_mapk():
+    """The AP@k that item-sharded evaluation reads off the merged top-k ids (distributed.
+    ap_from_topk_ids) = the oracle's per-user MAP@k (collie/metrics.py:144-198)."""
+    import scipy.sparse as sp
+    from oracle import collie_oracle as O
+    rng = np.random.default_rng(4)
+    n_users, n_items, k = 23, 57, 6
+    scores = rng.normal(size=(n_users, n_items)).astype(np.float32)
+    tu = rng.integers(0, n_users, 90)
+    tu = tu[tu != 7]                                   # a user without targets
+    ti = rng.integers(0, n_items, len(tu))
+    coo = sp.coo_matrix((np.ones(len(tu)), (tu, ti)), shape=(n_users, n_items))
+    coo.sum_duplicates()
+    csr = coo.tocsr()
+    csr.sort_indices()
+    users = np.arange(n_users)
+    top = torch.from_numpy(O.topk_ids(scores, k).astype(np.int32))
+    top[3, -2:] = -1                                   # padding entries are never hits
+    counts = torch.from_numpy(np.diff(csr.indptr).astype(np.int64))
+    rows = torch.repeat_interleave(torch.arange(n_users), counts)
+    keys = rows * n_items + torch.from_numpy(csr.indices.astype(np.int64))
+    got = D.ap_from_topk_ids(top, torch.arange(n_users), keys, counts, n_items).numpy()
+    exp = O.mapk_per_user(csr, users, scores, k)
+    keep = np.ones(n_users, dtype=bool)
+    keep[3] = False
+    np.testing.assert_allclose(got[keep], exp[keep], rtol=1e-12)
+    assert got[7] == 0.0
+    sub = torch.tensor([5, 11])                        # explicit row numbers
+    np.testing.assert_allclose(D.ap_from_topk_ids(top[sub], sub, keys, counts[sub], n_items).numpy(),
+                               exp[[5, 11]], rtol=1e-12)

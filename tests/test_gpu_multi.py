@@ -114,6 +114,14 @@ def _check_mode(mode, rank, world, dev, dist, cb, D, DeviceBatch):
                                    num_items=n_items, **kw)
         got = D.evaluate_sharded([cb.mapk, cb.mrr, cb.auc], test_loc, model, k=5)
         np.testing.assert_allclose(got, exp, rtol=1e-5)
+        # item-sharded evaluation (every rank scores all users against its block of item rows,
+        # partial top-k lists merged, counters summed) == single-GPU evaluation, both arithmetics
+        for precision in (0, 1):
+            got_i = D.evaluate_item_sharded([cb.mapk, cb.mrr], test_full, ref, k=5,
+                                            precision=precision, tile_users=16)
+            np.testing.assert_allclose(got_i, exp[:2], rtol=1e-5)
+        only = D.evaluate_item_sharded([cb.mrr], test_full, ref, k=5)
+        np.testing.assert_allclose(only, exp[1], rtol=1e-5)
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs 2 GPUs')
