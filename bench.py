@@ -200,7 +200,6 @@ def run_ours(args, rank, world, local_rank):
     import torch.distributed as dist
     import collie_b200 as cb
     from collie_b200 import _abi
-    from collie_b200.interactions import DeviceBatch
     w = WORKLOAD
     torch.cuda.set_device(local_rank)
     dev = torch.device('cuda', local_rank)
@@ -229,13 +228,8 @@ def run_ours(args, rank, world, local_rank):
     users_h = users[perm].contiguous().pin_memory()
     items_h = items[perm].contiguous().pin_memory()
     gidx_h = perm.contiguous().pin_memory()
-    users_d, items_d, gidx_d = users_h.to(dev), items_h.to(dev), gidx_h.to(dev)
     n_batches = n // B
     loader = cb.InteractionsDataLoader(data, batch_size=B, shuffle=True, drop_last=True)
-
-    def device_batch(i):
-        a = (i % n_batches) * B
-        return DeviceBatch(users_d[a:a + B], items_d[a:a + B], gidx_d[a:a + B], None)
 
     class Batches(object):
         """Batches the way the trainer gets them: the loader's device-side epoch plan (shuffle +
@@ -464,6 +458,10 @@ def run_ours(args, rank, world, local_rank):
         t0 = time.perf_counter()
         m_all = cb.evaluate_in_batches([cb.mapk, cb.mrr, cb.auc], test, model, k=10, verbose=False)
         torch.cuda.synchronize()
+        api_exact_first_s = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        m_all = cb.evaluate_in_batches([cb.mapk, cb.mrr, cb.auc], test, model, k=10, verbose=False)
+        torch.cuda.synchronize()
         api_exact_s = time.perf_counter() - t0
         # wall clock of the public call, results on the host: the first call on a test set (derives
         # its device-side form) and a later one (every following epoch's validation)
@@ -500,7 +498,9 @@ def run_ours(args, rank, world, local_rank):
                                 'evaluate_in_batches([mapk, mrr], precision=1), first call':
                                 n_eval_users / api_tc_first_s,
                                 'evaluate_in_batches([mapk, mrr, auc]) exact fp32':
-                                n_eval_users / api_exact_s},
+                                n_eval_users / api_exact_s,
+                                'evaluate_in_batches([mapk, mrr, auc]) exact fp32, first call':
+                                n_eval_users / api_exact_first_s},
             'metrics_exact': m_all, 'metrics_tc': m_tc,
         }
 
