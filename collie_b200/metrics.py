@@ -56,10 +56,12 @@ def _targets_all_users_device(targets: csr_matrix, test_users, device):
 
 def _eval_tile(device, n_users, n_items, k, indptr, tgt_items, want, tables=None, user_ids=None,
                scores=None, precision=0, workspace=None, reuse_item_prep=False, item_offset=0,
-               ext_best=None):
+               ext_best=None, into=None):
     """One ``cmf_eval_tile`` call; returns dict of per-user device tensors. ``item_offset`` /
     ``n_items`` select an item shard of the table (global ids come back); ``ext_best`` = (score,
-    id) of every user's best target over ALL shards, against which the MRR counter counts."""
+    id) of every user's best target over ALL shards, against which the MRR counter counts;
+    ``into`` = (dict of whole-evaluation output tensors, first row): the tile's per-user outputs are
+    written there instead of into fresh tensors."""
     a = _abi.cmf_eval_t()
     keep = []
     if scores is not None:
@@ -79,8 +81,13 @@ def _eval_tile(device, n_users, n_items, k, indptr, tgt_items, want, tables=None
     a.precision = precision
     a.reuse_item_prep = 1 if reuse_item_prep else 0
     out = {}
+
+    def vec(name, dtype):
+        if into is not None and name in into[0]:
+            return into[0][name][into[1]:into[1] + n_users]
+        return torch.empty(n_users, dtype=dtype, device=device)
     if 'mapk' in want:
-        out['ap'] = torch.empty(n_users, dtype=torch.float64, device=device)
+        out['ap'] = vec('ap', torch.float64)
         a.ap = out['ap'].data_ptr()
     if 'topk' in want:
         out['topk_ids'] = torch.empty((n_users, k), dtype=torch.int32, device=device)
@@ -88,11 +95,11 @@ def _eval_tile(device, n_users, n_items, k, indptr, tgt_items, want, tables=None
         a.topk_ids, a.topk_scores = out['topk_ids'].data_ptr(), out['topk_scores'].data_ptr()
     if 'mrr' in want:
         a.want_mrr = 1
-        out['n_before_best'] = torch.empty(n_users, dtype=torch.int32, device=device)
+        out['n_before_best'] = vec('n_before_best', torch.int32)
         a.n_before_best = out['n_before_best'].data_ptr()
     if 'auc' in want:
         a.want_auc = 1
-        out['auc_pairs'] = torch.empty(n_users, dtype=torch.float64, device=device)
+        out['auc_pairs'] = vec('auc_pairs', torch.float64)
         a.auc_pairs = out['auc_pairs'].data_ptr()
     need = _abi.lib().cmf_eval_workspace_bytes(n_users, n_items, int(a.D), k, precision)
     if workspace is None or workspace.numel() < need:
@@ -229,28 +236,30 @@ def evaluate_in_batches(metric_list, test_interactions, model, k=10, batch_size=
         tc_names = [n for n in names if n != 'auc'] if use_tc else []
         ex_names = [n for n in names if n not in tc_names]
         sums = torch.zeros(len(names), dtype=torch.float64, device=device)
+        # per-user ingredients of the whole evaluation, filled tile by tile, reduced once
+        _ING = {'mapk': ('ap', torch.float64), 'mrr': ('n_before_best', torch.int32),
+                'auc': ('auc_pairs', torch.float64)}
+        whole = {_ING[n_][0]: torch.empty(n_test, dtype=_ING[n_][1], device=device)
+                 for n_ in names}
         if ex_names:
             tile = max(1, min(_TILE_USERS, _MAX_TILE_BYTES // max(1, 12 * n_items)))
             ws = None
             for s in range(0, n_test, tile):
                 e = min(s + tile, n_test)
-                res = _eval_tile(device, e - s, n_items, k, indptr[s:e + 1], tgt_items,
-                                 set(ex_names), tables=tables, user_ids=users_dev[s:e],
-                                 precision=0, workspace=ws)
-                ws = res['_workspace']
-                for name in ex_names:
-                    sums[names.index(name)] += _per_user(name, res, nnz[s:e], n_items).sum()
+                ws = _eval_tile(device, e - s, n_items, k, indptr[s:e + 1], tgt_items,
+                                set(ex_names), tables=tables, user_ids=users_dev[s:e],
+                                precision=0, workspace=ws, into=(whole, s))['_workspace']
         if tc_names:
             tile = _TC_TILE_USERS
             ws = None
             for s in range(0, n_test, tile):
                 e = min(s + tile, n_test)
-                res = _eval_tile(device, e - s, n_items, k, indptr[s:e + 1], tgt_items,
-                                 set(tc_names), tables=tables, user_ids=users_dev[s:e],
-                                 precision=1, workspace=ws, reuse_item_prep=(s > 0))
-                ws = res['_workspace']
-                for name in tc_names:
-                    sums[names.index(name)] += _per_user(name, res, nnz[s:e], n_items).sum()
+                ws = _eval_tile(device, e - s, n_items, k, indptr[s:e + 1], tgt_items,
+                                set(tc_names), tables=tables, user_ids=users_dev[s:e],
+                                precision=1, workspace=ws, reuse_item_prep=(s > 0),
+                                into=(whole, s))['_workspace']
+        for j, name in enumerate(names):
+            sums[j] = _per_user(name, whole, nnz, n_items).sum()
         all_scores = (sums / n_test).tolist()
     else:
         if n_test < batch_size:
