@@ -793,3 +793,47 @@ def test_whole_epoch_call_equals_the_step_loop(explicit):
     for ta, tc in zip(_tables(a).values(), _tables(c).values()):
         np.testing.assert_allclose(tc.detach().cpu().numpy(), ta.detach().cpu().numpy(),
                                    rtol=1e-4, atol=1e-6)
+
+
+# ------------------------------------------------------------------------------------ size limits
+@pytest.mark.gpu
+@pytest.mark.parametrize('dim,n_neg,loss,oname', [(256, 3, 'bpr', 'adaptive_bpr'),
+                                                  (1024, 2, 'adaptive', 'adaptive_hinge'),
+                                                  (64, 64, 'warp', 'warp'),
+                                                  (12, 64, 'bpr', 'adaptive_bpr')])
+def test_steps_at_the_size_limits_match_oracle(dim, n_neg, loss, oname):
+    """The widest rows (embedding_dim 1024), rows wider than one 128-float slice, and the largest
+    negative count (64) go through other kernel instantiations than the golden cases: two
+    sparse-Adam steps against the oracle."""
+    import collie_b200 as cb
+    from oracle import collie_oracle as O
+    rng = np.random.default_rng(dim + n_neg)
+    n_users, n_items, batch = 90, 150, 700
+    data = _implicit_data(n_users, n_items, n_neg)
+    torch.manual_seed(dim)
+    model = cb.MatrixFactorizationModel(train=data, embedding_dim=dim, sparse=True, lr=1e-2,
+                                        optimizer='sparse_adam', loss=loss,
+                                        lr_scheduler_func=None).cuda()
+    ref = O.OracleMF(n_users, n_items, dim, sparse=True)
+    names = ('user_embeddings', 'item_embeddings', 'user_biases', 'item_biases')
+    with torch.no_grad():
+        for name in names:
+            w = torch.from_numpy(rng.normal(0, 0.4 / np.sqrt(dim) if 'emb' in name else 0.1,
+                                            tuple(getattr(model, name).weight.shape))
+                                 .astype(np.float32))
+            getattr(model, name).weight.copy_(w)
+            getattr(ref, name).weight.copy_(w)
+    opts = model.configure_optimizers()
+    ref_opts = O.make_optimizers(ref, 'sparse_adam', 'sgd', 1e-2, 1e-2)
+    for step in range(2):
+        bu = torch.from_numpy(rng.integers(0, n_users, batch).astype(np.int32))
+        bp = torch.from_numpy(rng.integers(0, n_items, batch).astype(np.int32))
+        bn = torch.from_numpy(rng.integers(0, n_items, (batch, n_neg)))
+        got = model.fused_step(((bu.cuda(), bp.cuda()), bn.cuda()), optimizers=opts).item()
+        exp = O.train_step(ref, ref_opts, lambda: ref.implicit_loss(bu, bp, bn, oname))
+        np.testing.assert_allclose(got, exp, rtol=2e-5)
+    for name in names:
+        np.testing.assert_allclose(getattr(model, name).weight.detach().cpu().numpy(),
+                                   getattr(ref, name).weight.detach().numpy(), rtol=2e-4,
+                                   atol=5e-5, err_msg=name)   # Adam divides by sqrt(v): where a
+    # row's contributions nearly cancel, the summation order shows up as a fraction of lr = 1e-2
