@@ -837,3 +837,29 @@ def test_steps_at_the_size_limits_match_oracle(dim, n_neg, loss, oname):
                                    getattr(ref, name).weight.detach().numpy(), rtol=2e-4,
                                    atol=5e-5, err_msg=name)   # Adam divides by sqrt(v): where a
     # row's contributions nearly cancel, the summation order shows up as a fraction of lr = 1e-2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('dim', [10, 128, 200])
+def test_score_tile_kernels_agree_bit_for_bit(dim):
+    """The 128 x 128 contraction (full tiles) and the 64 x 64 one (small tiles) accumulate every
+    score in the same order: identical bits; both equal the oracle's scores to fp32 tolerance."""
+    import collie_b200 as cb
+    from oracle import collie_oracle as O
+    rng = np.random.default_rng(dim)
+    n_users, n_items = 230, 333
+    model = cb.MatrixFactorizationModel(train=_implicit_data(n_users, n_items, 3),
+                                        embedding_dim=dim, lr_scheduler_func=None).cuda()
+    with torch.no_grad():
+        for p in model.parameters():
+            p.copy_(torch.from_numpy(rng.normal(0, 0.5, tuple(p.shape)).astype(np.float32)))
+    users = rng.permutation(n_users)
+    whole = cb.get_preds(model, users, n_items)                       # 230 users: 128-wide tiles
+    parts = torch.cat([cb.get_preds(model, users[s:s + 50], n_items)  # 50 users: 64-wide tiles
+                       for s in range(0, n_users, 50)])
+    assert torch.equal(whole, parts)
+    tabs = [t.detach().cpu() for t in _tables(model).values()]
+    uu = torch.from_numpy(users).repeat_interleave(n_items)
+    ii = torch.arange(n_items).repeat(n_users)
+    exp = O.mf_forward(*tabs, uu, ii).view(n_users, n_items)
+    np.testing.assert_allclose(whole.cpu().numpy(), exp.numpy(), rtol=1e-5, atol=1e-5)
