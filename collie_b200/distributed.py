@@ -170,6 +170,14 @@ class ShardedMatrixFactorization(object):
             if self.exchange == 'p2p':
                 raise _abi.CmfError(f'p2p exchange unavailable: {e}')
             self._p2p = None
+        if not self._all_ranks(self._p2p is not None):
+            self._p2p = None       # one mode for everybody: some rank could not set it up
+
+    def _all_ranks(self, ok):
+        """True when ``ok`` holds on every rank (so that the ranks take the same exchange path)."""
+        t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=self.I_full.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN, group=self.group)
+        return bool(t.item())
 
     def _setup_workspace_p2p(self, batch, n_neg):
         """The training workspace in symmetric memory (collective: every rank calls it at its
@@ -245,7 +253,17 @@ class ShardedMatrixFactorization(object):
         B = int(batch.users.shape[0])
         n_neg = int(getattr(interactions, 'num_negative_samples', 0) or 0)
         if 'peers' not in self._p2p:
-            self._setup_workspace_p2p(B, n_neg)
+            err = None
+            try:
+                self._setup_workspace_p2p(B, n_neg)
+            except Exception as e:          # (checked on all ranks together below)
+                err = e
+            if not self._all_ranks(err is None):
+                if self.exchange == 'p2p':
+                    raise _abi.CmfError(f'p2p exchange unavailable: {err}')
+                self._p2p = None            # collectives from here on, on every rank
+                m._workspace = None
+                return None
         cap_b, cap_n = self._p2p['cap']
         if B > cap_b or n_neg > cap_n or m._workspace is not self._p2p['ws']:
             raise _abi.CmfError(
@@ -332,8 +350,10 @@ class ShardedMatrixFactorization(object):
             dist.all_reduce(t, group=self.group)
             global_batch = int(t.item())
         if self._p2p is not None:
-            return self._train_step_p2p(batch, optimizers, main, bias, st, interactions, epoch,
+            done = self._train_step_p2p(batch, optimizers, main, bias, st, interactions, epoch,
                                         global_batch, reduce_loss)
+            if done is not None:
+                return done
         # 1. everyone gets the current item rows
         all_gather_rows(self.I_full, self.I_shard, self.group)
         all_gather_rows(self.bi_full.view(-1), self.bi_shard.reshape(-1), self.group)
