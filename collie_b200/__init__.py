@@ -8,6 +8,7 @@ All arithmetic runs in ``lib/libcollie_b200.so`` (``include/collie_b200.h``); th
 PyTorch fallback -- a missing library or a non-CUDA tensor raises.
 """
 from . import _abi
+from . import cross_validation  # noqa: F401  (random_split, stratified_split)
 from .interactions import (ApproximateNegativeSamplingInteractionsDataLoader,
                            ExplicitInteractions, Interactions, InteractionsDataLoader)
 from .metrics import (MeanAbsoluteError, MeanSquaredError, auc, evaluate_in_batches,

@@ -211,6 +211,32 @@ def similarity_case(seed, n_users=23, n_items=57, dim=20):
     return out
 
 
+def split_case(seed, n_users=40, n_items=70, n=900):
+    """random_split (exact entries) and stratified_split (per-user sizes) of the reference
+    (collie/cross_validation.py:51-306)."""
+    from collie.cross_validation import random_split, stratified_split
+    rng = np.random.default_rng(seed)
+    users, items = synthetic_pairs(rng, n_users, n_items, n)
+    users[:3] = n_users - 1                      # a user with exactly three interactions
+    keep = np.ones(n, dtype=bool)
+    keep[3:] = users[3:] != n_users - 1
+    users, items = users[keep], items[keep]
+    data = Interactions(users=users, items=items, ratings=np.ones(len(users)), num_users=n_users,
+                        num_items=n_items, allow_missing_ids=True,
+                        remove_duplicate_user_item_pairs=False,
+                        check_num_negative_samples_is_valid=False)
+    out = {'n_users': n_users, 'n_items': n_items, 'users': data.mat.row, 'items': data.mat.col}
+    for tag, (vp, tp) in {'a': (0.0, 0.2), 'b': (0.1, 0.25)}.items():
+        parts = random_split(data, val_p=vp, test_p=tp, seed=seed + 1)
+        for name, part in zip(('train', 'val', 'test') if vp > 0 else ('train', 'test'), parts):
+            out[f'random_{tag}_{name}_users'] = part.mat.row
+            out[f'random_{tag}_{name}_items'] = part.mat.col
+        parts = stratified_split(data, val_p=vp, test_p=tp, seed=seed + 2, processes=0)
+        for name, part in zip(('train', 'val', 'test') if vp > 0 else ('train', 'test'), parts):
+            out[f'strat_{tag}_{name}_counts'] = np.bincount(part.mat.row, minlength=n_users)
+    return out
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     cases = {
@@ -237,6 +263,7 @@ def main():
     }
     if len(sys.argv) > 1 and sys.argv[1] == 'similarity':     # only the cases added later
         cases = {}
+    cases['splits'] = split_case(61)
     cases['similarity_random'] = similarity_case(51)
     cases['similarity_d128'] = similarity_case(52, n_users=40, n_items=90, dim=128)
     for name, arrays in cases.items():
