@@ -540,7 +540,8 @@ def test_tensor_core_eval_bit_exact_on_exact_fixture():
                                    rtol=1e-12)
 
 
-@pytest.mark.parametrize('shape', [(300, 1000, 128), (77, 5000, 64), (1000, 333, 32), (130, 26744, 128)])
+@pytest.mark.parametrize('shape', [(300, 1000, 128), (77, 5000, 64), (1000, 333, 32), (130, 26744, 128),
+                                   (50, 700, 5), (200, 300, 33), (64, 257, 100), (3, 40, 1)])
 def test_tensor_core_eval_matches_exact_path(shape):
     """Random fp32 weights: tensor-core scores within 1e-5 of the exact path, metrics within 1e-5,
     top-k ids identical wherever the exact scores are separated by more than the split's error."""
