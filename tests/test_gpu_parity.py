@@ -864,3 +864,85 @@ def test_score_tile_kernels_agree_bit_for_bit(dim):
     ii = torch.arange(n_items).repeat(n_users)
     exp = O.mf_forward(*tabs, uu, ii).view(n_users, n_items)
     np.testing.assert_allclose(whole.cpu().numpy(), exp.numpy(), rtol=1e-5, atol=1e-5)
+
+
+# ------------------------------------------------------------------------------------ memory safety
+def _guarded(nbytes, pad=4096):
+    """``nbytes`` of device scratch with canary bytes on both sides: (whole buffer, interior view)."""
+    whole = torch.full((nbytes + 2 * pad,), 0xA5, dtype=torch.uint8, device='cuda')
+    return whole, whole[pad:pad + nbytes], pad
+
+
+def _intact(whole, pad):
+    return bool((whole[:pad] == 0xA5).all()) and bool((whole[-pad:] == 0xA5).all())
+
+
+@pytest.mark.gpu
+def test_kernels_stay_inside_their_workspaces():
+    """Every scratch area is handed over at exactly the size the library asks for, with canary
+    bytes around it: training step (split kernels and the generic kernel), epoch plan (both
+    forms), exact and tensor-core evaluation tiles. (Stands in for a memory checker.)"""
+    import collie_b200 as cb
+    from collie_b200 import _abi, metrics as M
+    lib = _abi.lib()
+    rng = np.random.default_rng(77)
+    n_users, n_items, n = 333, 517, 6000
+    users, items = rng.integers(0, n_users, n), rng.integers(0, n_items, n)
+    for dim, n_neg in ((128, 5), (10, 3), (260, 2)):
+        data = cb.Interactions(users=users, items=items, num_users=n_users, num_items=n_items,
+                               num_negative_samples=n_neg, allow_missing_ids=True, seed=1,
+                               remove_duplicate_user_item_pairs=False,
+                               check_num_negative_samples_is_valid=False,
+                               max_number_of_samples_to_consider=0)
+        loader = cb.InteractionsDataLoader(data, batch_size=1000, shuffle=True)
+        model = cb.MatrixFactorizationModel(train=loader, embedding_dim=dim, sparse=True,
+                                            optimizer='sparse_adam', loss='bpr',
+                                            lr_scheduler_func=None).cuda()
+        opts = model.configure_optimizers()
+        # ---- epoch plan workspace (shuffled + ordered by user: the presorted form)
+        need = int(lib.cmf_epoch_plan_workspace_bytes(n))
+        pw, pv, pad = _guarded(need)
+        loader._plan_ws = {'cuda:0': pv, str(torch.device('cuda', 0)): pv}
+        plan = loader.epoch_plan(torch.device('cuda', 0), epoch=1)
+        torch.cuda.synchronize()
+        assert _intact(pw, pad) and plan.users.shape[0] == n
+        # ---- training workspace, whole epoch through cmf_train_epoch (ragged last batch)
+        need = int(lib.cmf_train_workspace_bytes(1000, n_neg, n_users, n_items, dim))
+        tw, tv, pad = _guarded(need)
+        _abi.check(lib.cmf_workspace_init(_abi.ptr(tv), need, _abi.stream_ptr('cuda')), 'init')
+        model._workspace, model._workspace_B = tv, 1000
+        losses = model.fused_step(plan, optimizers=opts, interactions=data, epoch=1,
+                                  epoch_batch_size=1000)
+        # an unsorted batch too: the in-step sort uses the per-step part of the workspace
+        st = data.device_state('cuda')
+        from collie_b200.interactions import DeviceBatch
+        idx = torch.arange(700, device='cuda')
+        model.fused_step(DeviceBatch(st['users'][:700], st['items'][:700], idx, None),
+                         optimizers=opts, interactions=data, epoch=2)
+        torch.cuda.synchronize()
+        assert model._workspace is tv and _intact(tw, pad)
+        assert bool(torch.isfinite(losses).all()) and losses.shape == (6,)
+        # ---- the general plan form (no shuffle)
+        plain = cb.InteractionsDataLoader(data, batch_size=1000, shuffle=False)
+        pw2, pv2, pad = _guarded(int(lib.cmf_epoch_plan_workspace_bytes(n)))
+        plain._plan_ws = {'cuda:0': pv2}
+        plain.epoch_plan(torch.device('cuda', 0), epoch=0)
+        torch.cuda.synchronize()
+        assert _intact(pw2, pad)
+        # ---- evaluation tiles
+        tabs = M._model_tables(model)
+        import scipy.sparse as sp
+        coo = sp.coo_matrix((np.ones(n), (users, items)), shape=(n_users, n_items))
+        coo.sum_duplicates()
+        tile = np.arange(200)
+        indptr, tgt, nnz = M._targets_device(coo.tocsr(), tile, 'cuda')
+        uid = torch.arange(200, dtype=torch.int32, device='cuda')
+        for precision in ((0, 1) if dim <= 128 else (0,)):
+            need = int(lib.cmf_eval_workspace_bytes(200, n_items, dim, 7, precision))
+            ew, ev, pad = _guarded(need)
+            want = {'topk', 'mapk', 'mrr'} | ({'auc'} if precision == 0 else set())
+            res = M._eval_tile('cuda', 200, n_items, 7, indptr, tgt, want, tables=tabs,
+                               user_ids=uid, precision=precision, workspace=ev)
+            torch.cuda.synchronize()
+            assert res['_workspace'] is ev and _intact(ew, pad)
+            assert int(res['topk_ids'].min()) >= 0 and int(res['topk_ids'].max()) < n_items
