@@ -946,3 +946,25 @@ def test_kernels_stay_inside_their_workspaces():
             torch.cuda.synchronize()
             assert res['_workspace'] is ev and _intact(ew, pad)
             assert int(res['topk_ids'].min()) >= 0 and int(res['topk_ids'].max()) < n_items
+
+
+@pytest.mark.gpu
+def test_batch_sorter_carries_ratings():
+    """Explicit batches: the ratings travel with their interactions through the sorter."""
+    from collie_b200.interactions import BatchSorter
+    rng = np.random.default_rng(8)
+    n = 3000
+    users = rng.integers(0, 50, n).astype(np.int32)
+    items = rng.integers(0, 90, n).astype(np.int32)
+    ratings = rng.integers(1, 6, n).astype(np.float32)
+    gidx = np.arange(n, dtype=np.int64) + 10
+    sorter = BatchSorter(n, 50, 'cuda', with_ratings=True)
+    db = sorter(*(torch.from_numpy(x).cuda() for x in (users, items, gidx)),
+                ratings=torch.from_numpy(ratings).cuda())
+    order = np.argsort(users, kind='stable')
+    assert db.sorted and np.array_equal(db.users.cpu().numpy(), users[order])
+    assert np.array_equal(db.items.cpu().numpy(), items[order])
+    assert np.array_equal(db.ratings.cpu().numpy(), ratings[order])
+    assert np.array_equal(db.gidx.cpu().numpy(), gidx[order])
+    with pytest.raises(ValueError, match='ratings'):
+        sorter(*(torch.from_numpy(x).cuda() for x in (users, items, gidx)))
