@@ -27,6 +27,7 @@
 namespace cmf {
 
 extern int g_tc_debug;
+extern int g_pdl;
 
 struct WsLayout {
   // persistent (zero between steps; the kernels restore the invariant)
@@ -390,6 +391,7 @@ struct RowJob {
 template <int V, int G, int R>
 __global__ void __launch_bounds__(kThreads)
 k_update_rows(const UpdDev p) {
+  asm volatile("griddepcontrol.wait;" ::: "memory");   // (programmatic dependent of k_bwd_update)
   constexpr int kGroups = kThreads / G;
   const int l = threadIdx.x & (G - 1);
   const int64_t group = (int64_t)blockIdx.x * kGroups + threadIdx.x / G;
@@ -515,6 +517,11 @@ extern "C" int cmf_set_tuning(int32_t key, int32_t value) {
   if (key == 3) {
     const int prev = g_tc_debug;
     g_tc_debug = value;
+    return prev;
+  }
+  if (key == 6) {
+    const int prev = g_pdl;
+    g_pdl = value;
     return prev;
   }
   if (key == 2) {
@@ -787,7 +794,16 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
     const int64_t cap = (int64_t)num_sms() * 8;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-#define CALL(V_, G_, R_) k_update_rows<V_, G_, R_><<<(unsigned)blocks, kThreads, 0, s>>>(q)
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)blocks);
+    cfg.blockDim = dim3(kThreads);
+    cfg.stream = s;
+    cudaLaunchAttribute pdl[1];
+    pdl[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    pdl[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = pdl;
+    cfg.numAttrs = (g_pdl && split) ? 1 : 0;
+#define CALL(V_, G_, R_) cudaLaunchKernelEx(&cfg, k_update_rows<V_, G_, R_>, q)
     CMF_DISPATCH_GEOM(geom, CALL);
 #undef CALL
     CMF_LAUNCH_CHECK();

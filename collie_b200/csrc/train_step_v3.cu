@@ -347,6 +347,9 @@ k_fwd_loss(const StepDev p) {
 template <int KQ, bool FULL>
 __global__ void __launch_bounds__(256, 2)
 k_fwd_loss_g8(const StepDev p, const int NP) {
+  // the backward kernel may become resident as this grid's CTAs retire (it waits for the whole
+  // grid before it reads anything)
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   extern __shared__ int s_dyn[];   // [8 warps][32 interactions][NP]: user, positive, negatives
   __shared__ float s_warp_loss[8];
   __shared__ bool s_last;
@@ -595,6 +598,9 @@ k_fwd_loss_g8(const StepDev p, const int NP) {
 template <int R, bool FULL>
 __global__ void __launch_bounds__(256)
 k_bwd_update(const StepDev p) {
+  // (launched as a programmatic dependent of the forward kernel: resident early, starts here)
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // k_update_rows may line up
   // per warp and interaction of the chunk: user, positive, selected negative, coefficient
   __shared__ int s_tab[8][kMaxChunkB][4];
   __shared__ int s_meta[8][2];
@@ -818,6 +824,8 @@ int launch_fwd_loss_v3(const StepDev& p, bool sort_runs_alongside, cudaStream_t 
   return CMF_OK;
 }
 
+int g_pdl = 1;   // cmf_set_tuning key 6: programmatic dependent launch of the step's kernels
+
 int launch_bwd_update_v3(const StepDev& p_in, int max_chunk_len, cudaStream_t s) {
   StepDev p = p_in;
   const int R = (p.D / 4 + 31) / 32;
@@ -830,10 +838,19 @@ int launch_bwd_update_v3(const StepDev& p_in, int max_chunk_len, cudaStream_t s)
   p.L = L;
   p.num_chunks = (p.B + L - 1) / L;
   const int grid = blocks_for(p.num_chunks, 8);
-#define K2(R_)                                                         \
-  do {                                                                 \
-    if (full) k_bwd_update<R_, true><<<grid, 256, 0, s>>>(p);          \
-    else k_bwd_update<R_, false><<<grid, 256, 0, s>>>(p);              \
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(256);
+  cfg.stream = s;
+  cudaLaunchAttribute pdl[1];
+  pdl[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  pdl[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = pdl;
+  cfg.numAttrs = g_pdl ? 1 : 0;
+#define K2(R_)                                                                       \
+  do {                                                                               \
+    if (full) cudaLaunchKernelEx(&cfg, k_bwd_update<R_, true>, p);                   \
+    else cudaLaunchKernelEx(&cfg, k_bwd_update<R_, false>, p);                       \
   } while (0)
   if (R <= 1) K2(1); else if (R == 2) K2(2); else if (R <= 4) K2(4); else K2(8);
 #undef K2
