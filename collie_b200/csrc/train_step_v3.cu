@@ -16,6 +16,8 @@
 //                 Replaces loss.backward() + optimizer.step() (trainer.py:463-470).
 //
 // k_update_rows (train_step.cu) then finishes the item rows and the users that straddle chunks.
+#include <cstdlib>
+
 #include "train_common.cuh"
 
 namespace cmf {
@@ -824,7 +826,15 @@ int launch_fwd_loss_v3(const StepDev& p, bool sort_runs_alongside, cudaStream_t 
   return CMF_OK;
 }
 
-int g_pdl = 1;   // cmf_set_tuning key 6: programmatic dependent launch of the step's kernels
+static int pdl_default() {
+  const char* e = getenv("CMF_PDL");
+  return e ? atoi(e) : 0;
+}
+// cmf_set_tuning key 6 (or CMF_PDL=1): programmatic dependent launch of k_bwd_update / k_update_rows.
+// Off by default: it takes 1.3 % off a device-resident step, but the dependents fill every SM the
+// moment the previous grid drains, so kernels of OTHER streams (a host-fed pipeline's batch sort on
+// its copy stream) find no way in until the step ends: end-to-end throughput fell by 12 %.
+int g_pdl = pdl_default();
 
 int launch_bwd_update_v3(const StepDev& p_in, int max_chunk_len, cudaStream_t s) {
   StepDev p = p_in;
