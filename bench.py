@@ -274,7 +274,9 @@ def run_ours(args, rank, world, local_rank):
     value = steps * B / (ms * 1e-3)
 
     # ---- end to end: pinned host batches in, loss out, every step (double-buffered copies)
-    copy_stream = torch.cuda.Stream(dev)
+    # high priority: the small sort kernels of the next batch get SMs as soon as some free up,
+    # instead of queueing behind the step's big grids
+    copy_stream = torch.cuda.Stream(dev, priority=-1)
     main = torch.cuda.current_stream(dev)
     from collie_b200.interactions import BatchSorter
     slots = [dict(u=torch.empty(B, dtype=torch.int32, device=dev),

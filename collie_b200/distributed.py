@@ -647,7 +647,9 @@ def bench_sharded(args, rank, world, local_rank, workload, synth, config_dict, C
     items_h = torch.from_numpy(data.mat.col.astype(np.int32))[perm].contiguous().pin_memory()
     gidx_h = torch.from_numpy(np.asarray(gpos, dtype=np.int64))[perm].contiguous().pin_memory()
     n_batches = n_local // B
-    copy_stream = torch.cuda.Stream(dev)
+    # high priority: the small sort kernels of the next batch get SMs as soon as some free up,
+    # instead of queueing behind the step's big grids
+    copy_stream = torch.cuda.Stream(dev, priority=-1)
     main = torch.cuda.current_stream(dev)
     slots = [dict(u=torch.empty(B, dtype=torch.int32, device=dev),
                   i=torch.empty(B, dtype=torch.int32, device=dev),
