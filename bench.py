@@ -1,25 +1,35 @@
 #!/usr/bin/env python
-"""Benchmark of the MF training hot path (BASELINE.json metric) -- see DESIGN.md "Measurement".
+"""Benchmark of the MF training + evaluation hot path (BASELINE.json metric) -- DESIGN.md section 5.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config c3|c5]
 
-Own arm: one "step" = one fused training step (on-device negative sampling + gather + scores +
-loss + backward + sparse Adam / SGD updates) over one batch of the workload
-  C3 = implicit MF, loss 'bpr' with 5 negatives (-> adaptive BPR), sparse Adam + SGD biases,
+For N > 1 launch it as the driver does:
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+
+Own arm. One "step" = one fused training step (on-device negative sampling + gather + scores + loss
++ backward + sparse Adam / SGD updates) over one batch of the workload
+  c3 = implicit MF, loss 'bpr' with 5 negatives (-> adaptive BPR), sparse Adam + SGD biases,
        embedding_dim 128, synthetic MovieLens-20M shape (138,493 users x 26,744 items, 20 M
-       interactions), batch 262,144 interactions per GPU.
-`value` is interactions/s with the batch already in HBM; `e2e` is the same loop fed from pinned
-host memory (H2D of every batch, D2H of every loss) through the public API. The reference arm
-(`--impl reference`) times the oracle's restatement of the reference's own PyTorch CPU path on the
-host cores (the reference is pure Python and cannot travel to the GPU box; oracle/ is used here
-only as the thing being timed for the baseline, never by the product path).
+       interactions), batch 262,144 interactions per GPU  (BASELINE.json configs[2], the config the
+       metric is quoted on);
+  c5 = 10 M users x 2 M items, WARP with 10 negatives, item table row-sharded (configs[4]).
+`value` = interactions/s over all GPUs with the batches already in HBM (max over ranks, CUDA
+events); `e2e` = the same loop fed from pinned host memory through the public API (H2D of every
+batch, D2H of every step's loss). `eval` = the other half of the metric: users/s of
+evaluate_in_batches (MAP@10, MRR, AUC) user-sharded over the GPUs, and item-sharded. `parity`
+(N > 1) = three extra global steps replayed by rank 0 on a single-GPU copy of all tables and compared.
+
+Reference arm (`--impl reference`): the reference's own CPU implementation of the path on the host
+cores -- the unmodified collie package from oracle/_ref (copied there by __graft_entry__.build())
+driven through its CollieMinimalTrainer.fit / evaluate_in_batches; the oracle's torch restatement
+("port") when oracle/_ref is absent. oracle/ is only ever the thing timed here, never on the
+product path.
 """
 import argparse
 import json
 import os
-import subprocess
 import sys
-import tempfile
 import time
 
 import numpy as np
@@ -29,12 +39,27 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-WORKLOAD = {
-    'name': 'C3 implicit MF bpr(N=5)->adaptive_bpr, sparse_adam + sgd bias, D=128, '
-            'synthetic ML-20M shape',
-    'num_users': 138493, 'num_items': 26744, 'interactions': 20_000_000, 'dim': 128, 'n_neg': 5,
-    'batch_per_gpu': 262144, 'lr': 1e-3, 'bias_lr': 1e-2, 'seed': 2,
+WORKLOADS = {
+    'c3': {
+        'key': 'c3',
+        'name': 'C3 implicit MF bpr(N=5)->adaptive_bpr, sparse_adam + sgd bias, D=128, '
+                'synthetic ML-20M shape',
+        'num_users': 138493, 'num_items': 26744, 'interactions': 20_000_000, 'dim': 128,
+        'n_neg': 5, 'loss': 'bpr', 'loss_resolved': 'adaptive_bpr', 'batch_per_gpu': 262144,
+        'lr': 1e-3, 'bias_lr': 1e-2, 'seed': 2, 'eval_users': 32768,
+    },
+    'c5': {
+        'key': 'c5',
+        'name': 'C5 implicit MF warp(N=10), sparse_adam + sgd bias, D=128, 10M users x 2M items, '
+                'item table row-sharded',
+        'num_users': 10_000_000, 'num_items': 2_000_000, 'interactions': None, 'dim': 128,
+        'n_neg': 10, 'loss': 'warp', 'loss_resolved': 'warp', 'batch_per_gpu': 262144,
+        'lr': 1e-3, 'bias_lr': 1e-2, 'seed': 3, 'eval_users': 4096,
+    },
 }
+METRIC = 'MF train interactions/s (fwd+bwd+sparse Adam)'
+NVLINK_GBS_PER_DIR = 900.0
+LOG_EVERY = 50          # the reference trainer's default log interval (trainer.py:226)
 
 
 def synth_interactions(num_users, num_items, n, seed):
@@ -52,6 +77,27 @@ def synth_interactions(num_users, num_items, n, seed):
     relabel = torch.randperm(num_items, generator=g)
     return (users.clamp_(max=num_users - 1).to(torch.int32),
             relabel[items.clamp_(max=num_items - 1)].to(torch.int32))
+
+
+def workload_interactions(w, world):
+    """The synthetic dataset of a workload. c5's nominal 200 M interactions are represented by a
+    bounded sample (4 batches per GPU): a step's cost does not depend on the dataset length."""
+    n = w['interactions'] or 4 * w['batch_per_gpu'] * world
+    return synth_interactions(w['num_users'], w['num_items'], n, w['seed'])
+
+
+def eval_test_set(w, n_users, seed=5, per_user=8):
+    """Hold-out stand-in: the first ``n_users`` users, ``per_user`` uniform target items each."""
+    tu = np.repeat(np.arange(n_users, dtype=np.int64), per_user)
+    ti = np.random.default_rng(seed).integers(0, w['num_items'], (n_users, per_user)).reshape(-1)
+    return tu, ti
+
+
+def load_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+    except Exception:
+        return {}
 
 
 # ------------------------------------------------------------------------------------------ clocks
@@ -85,7 +131,7 @@ class ClockSampler(object):
                 h = pynvml.nvmlDeviceGetHandleByIndex(self.gpu_index)
             self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
         except Exception:
-            return
+            return self
         names = {'hw_slowdown': pynvml.nvmlClocksThrottleReasonHwSlowdown,
                  'hw_thermal_slowdown': pynvml.nvmlClocksThrottleReasonHwThermalSlowdown,
                  'sw_thermal_slowdown': pynvml.nvmlClocksThrottleReasonSwThermalSlowdown,
@@ -105,6 +151,7 @@ class ClockSampler(object):
                 self._stop.wait(0.002)
         self._thread = threading.Thread(target=loop, daemon=True)
         self._thread.start()
+        return self
 
     def stop(self):
         if self._thread is not None:
@@ -117,14 +164,13 @@ class ClockSampler(object):
         return out
 
 
-# ------------------------------------------------------------------------------------------ CPU arm
-def cpu_port_run(users, items, steps, warmup, batch, threads):
-    """The reference's CPU training step, restated (oracle/collie_oracle.py): nn.Embedding(sparse)
-    x4, forward for positives and for users.repeat(N) negatives, adaptive BPR, autograd backward,
-    torch.optim.SparseAdam + SGD(bias); negatives by np.random.randint like the approximate loader
-    (collie/interactions/datasets.py:439-443). Returns seconds for `steps` timed steps."""
+# ------------------------------------------------------------------------------------- CPU arms
+def cpu_port_train_seconds(w, users, items, steps, warmup, batch, threads):
+    """The reference's CPU training step restated in torch (oracle/collie_oracle.py): sparse
+    nn.Embedding x4, forward for positives and for users.repeat(N) negatives, the loss, autograd
+    backward, torch.optim.SparseAdam + SGD(bias); negatives by np.random.randint like the
+    approximate loader (collie/interactions/datasets.py:439-443). Seconds for `steps` steps."""
     from oracle import collie_oracle as O
-    w = WORKLOAD
     torch.set_num_threads(threads)
     model = O.OracleMF(w['num_users'], w['num_items'], w['dim'], sparse=True, seed=0)
     opts = O.make_optimizers(model, 'sparse_adam', 'sgd', w['lr'], w['bias_lr'])
@@ -137,164 +183,329 @@ def cpu_port_run(users, items, steps, warmup, batch, threads):
         a = (s * batch) % max(1, n - batch)
         bu, bp = users[a:a + batch], items[a:a + batch]
         negs = torch.from_numpy(rng.randint(0, w['num_items'], size=(batch, w['n_neg'])))
-        O.train_step(model, opts, lambda: model.implicit_loss(bu, bp, negs, 'adaptive_bpr'))
+        O.train_step(model, opts,
+                     lambda: model.implicit_loss(bu, bp, negs, w['loss_resolved']))
     return time.perf_counter() - t0
 
 
-def run_reference(args, rank, world):
-    """Reference arm: the reference's CPU path (oracle port) on all host threads. Exactly K timed
-    steps after W warm-up steps; each step is a bounded sample of the workload's batch, sized from
-    one calibration step so that the whole run ends within a few minutes."""
+def cpu_train_baseline(w, users, items, steps, warmup, budget_s, threads, want_port=True):
+    """Times the reference's CPU training path on a bounded sample of the workload.
+
+    Preferred: the UNMODIFIED reference (oracle/_ref) through CollieMinimalTrainer.fit with the
+    ApproximateNegativeSamplingInteractionsDataLoader (BASELINE.md section 3) -> kind "reference";
+    the oracle port is timed as a labelled second row, and stands in when oracle/_ref is absent.
+    A step here = one batch of `batch` interactions of the same tables / distributions /
+    hyper-parameters; `batch` is the workload's batch, halved until the run fits `budget_s`."""
+    from oracle import ref_runner as R
+    full = w['batch_per_gpu']
+    total = steps + warmup
+    out = {}
+    if R.available():
+        calib = 16384
+        t_cal = R.train_seconds(users[:2 * calib].numpy(), items[:2 * calib].numpy(),
+                                w['num_users'], w['num_items'], w['dim'], w['n_neg'], calib, 1, 1,
+                                w['lr'], w['bias_lr'], loss=w['loss'], threads=threads)
+        batch = full
+        while batch > 4096 and t_cal * (batch / calib) * total > budget_s:
+            batch //= 2
+        need = batch * total
+        secs = R.train_seconds(users[:need].numpy(), items[:need].numpy(), w['num_users'],
+                               w['num_items'], w['dim'], w['n_neg'], batch, steps, warmup,
+                               w['lr'], w['bias_lr'], loss=w['loss'], threads=threads)
+        out['reference'] = {
+            'value': steps * batch / secs, 'unit': 'interactions/s', 'cores': threads,
+            'kind': 'reference', 'seconds': secs, 'batch': batch,
+            'sample': f'{steps} timed steps (+{warmup} warm-up) of {batch} interactions each '
+                      f'(workload batch is {full}); unmodified collie 1.3.1 from oracle/_ref: '
+                      'CollieMinimalTrainer.fit + ApproximateNegativeSamplingInteractionsDataLoader, '
+                      'same tables, distributions and hyper-parameters; torch CPU, all host threads'}
+        # second figure: the default loader with exact negative sampling (per-sample Python
+        # __getitem__, collie/interactions/datasets.py:399-426), on a small sample
+        try:
+            eb = 4096
+            es = R.train_seconds(users[:2 * eb].numpy(), items[:2 * eb].numpy(), w['num_users'],
+                                 w['num_items'], w['dim'], w['n_neg'], eb, 1, 1, w['lr'],
+                                 w['bias_lr'], loss=w['loss'], loader='exact', threads=threads)
+            out['reference']['default_loader_exact_sampling'] = {
+                'value': eb / es, 'unit': 'interactions/s',
+                'sample': f'1 step of {eb} interactions through InteractionsDataLoader'}
+        except Exception as e:  # pragma: no cover
+            out['reference']['default_loader_exact_sampling'] = {'error': repr(e)[:200]}
+    if want_port or not out:
+        calib = 32768
+        t_cal = cpu_port_train_seconds(w, users[:3 * calib], items[:3 * calib], 1, 1, calib,
+                                       threads)
+        batch = full
+        p_steps, p_warm = (steps, warmup) if not out else (min(steps, 3), 1)
+        while batch > 4096 and t_cal * (batch / calib) * (p_steps + p_warm) > budget_s:
+            batch //= 2
+        nb = batch * (p_steps + p_warm + 1)
+        secs = cpu_port_train_seconds(w, users[:nb], items[:nb], p_steps, p_warm, batch, threads)
+        out['port'] = {
+            'value': p_steps * batch / secs, 'unit': 'interactions/s', 'cores': threads,
+            'kind': 'port', 'seconds': secs, 'batch': batch,
+            'sample': f'{p_steps} timed steps (+{p_warm} warm-up) of {batch} interactions each; '
+                      'the reference CPU step restated in torch (oracle port, no loader / trainer '
+                      'overhead), all host threads'}
+    return out
+
+
+def cpu_eval_baseline(w, budget_s, threads, min_users=1000):
+    """evaluate_in_batches([mapk, mrr, auc], k=10, batch_size=20) of the reference (or of the
+    oracle port) on the host cores, on a bounded sample of the workload's test users."""
+    from oracle import ref_runner as R
+    g = torch.Generator().manual_seed(11)
+    U = torch.randn(w['num_users'], w['dim'], generator=g) / (2.5 * w['dim'])
+    I = torch.randn(w['num_items'], w['dim'], generator=g) / (2.5 * w['dim'])
+    bu = torch.zeros(w['num_users'])
+    bi = torch.randn(w['num_items'], generator=g) * 0.01
+
+    def run(n_users):
+        tu, ti = eval_test_set(w, n_users)
+        if R.available():
+            secs, vals, n = R.eval_seconds((U, I, bu, bi), tu, ti, w['num_users'], w['num_items'],
+                                           k=10, batch_size=20, threads=threads)
+            return secs, vals, n, 'reference'
+        from oracle import collie_oracle as O
+        import scipy.sparse as sp
+        torch.set_num_threads(threads)
+        mat = sp.coo_matrix((np.ones(len(tu)), (tu, ti)), shape=(w['num_users'], w['num_items']))
+        t0 = time.perf_counter()
+        vals = O.evaluate_in_batches(['mapk', 'mrr', 'auc'], mat,
+                                     (U, I, bu.view(-1, 1), bi.view(-1, 1)), k=10)
+        return time.perf_counter() - t0, list(vals), n_users, 'port'
+    t_cal, _, n_cal, kind = run(40)
+    n_users = int(min(w['eval_users'], max(min_users if t_cal / n_cal * min_users <= 2 * budget_s
+                                             else 200, budget_s / (t_cal / n_cal))))
+    n_users = max(40, (n_users // 20) * 20)
+    secs, vals, n, kind = run(n_users)
+    return {'value': n / secs, 'unit': 'users/s', 'cores': threads, 'kind': kind,
+            'seconds': secs, 'metrics': vals,
+            'sample': f'{n} test users x {w["num_items"]} items, D={w["dim"]}, '
+                      'evaluate_in_batches([mapk, mrr, auc], k=10, batch_size=20) of '
+                      + ('the unmodified reference (oracle/_ref)' if kind == 'reference'
+                         else 'the oracle port') + ', torch CPU, all host threads'}
+
+
+def run_reference(args, rank, world, w):
+    """Reference arm: the reference's CPU path on all host threads; rank 0 alone works. Exactly K
+    timed steps after W warm-up steps; each step is a bounded sample of the workload's batch."""
     if rank != 0:
         return
-    w = WORKLOAD
     threads = os.cpu_count() or 1
-    full = w['batch_per_gpu']
-    total_steps = args.steps + args.warmup
-    calib = 32768
-    cu, ci = synth_interactions(w['num_users'], w['num_items'], calib * 3, w['seed'])
-    t_calib = cpu_port_run(cu, ci, 1, 1, calib, threads)          # seconds for one 32k step
-    budget = 150.0
-    batch = full
-    while batch > 4096 and t_calib * (batch / calib) * total_steps > budget:
-        batch //= 2
-    users, items = synth_interactions(w['num_users'], w['num_items'], batch * (total_steps + 1),
-                                      w['seed'])
-    secs = cpu_port_run(users, items, args.steps, args.warmup, batch, threads)
-    value = args.steps * batch / secs
-    sample = (f'{args.steps} timed steps (+{args.warmup} warm-up) of {batch} interactions each '
-              f'(workload batch is {full}); same tables, distributions and hyper-parameters; '
-              'reference CPU path restated in torch (oracle port), all host threads')
+    total = args.steps + args.warmup
+    users, items = synth_interactions(w['num_users'], w['num_items'],
+                                      w['batch_per_gpu'] * (total + 1), w['seed'])
+    res = cpu_train_baseline(w, users, items, args.steps, args.warmup, 150.0, threads,
+                             want_port=True)
+    main = res.get('reference') or res['port']
+    ev = None
+    if not args.no_eval:
+        try:
+            ev = cpu_eval_baseline(w, 25.0, threads)
+        except Exception as e:  # pragma: no cover
+            ev = {'error': repr(e)[:300]}
     line = {
-        'impl': 'reference', 'metric': 'MF train interactions/s (fwd+bwd+sparse Adam)',
-        'value': value, 'unit': 'interactions/s', 'n_gpus': args.gpus, 'steps': args.steps,
-        'warmup': args.warmup, 'ms_per_step': 1e3 * secs / args.steps, 'higher_is_better': True,
+        'impl': 'reference', 'metric': METRIC, 'value': main['value'], 'unit': 'interactions/s',
+        'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
+        'ms_per_step': 1e3 * main['seconds'] / args.steps, 'higher_is_better': True,
         'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-        'config': config_dict(args.gpus),
-        'cpu_baseline': {'value': value, 'unit': 'interactions/s', 'cores': threads,
-                         'kind': 'port', 'sample': sample},
-        'e2e': {'value': value, 'unit': 'interactions/s', 'h2d_bytes_per_step': 0,
+        'config': config_dict(w, args.gpus),
+        'cpu_baseline': {k: main[k] for k in ('value', 'unit', 'cores', 'kind', 'sample')},
+        'cpu_baseline_port': res.get('port') if main is not res.get('port') else None,
+        'default_loader_exact_sampling': main.get('default_loader_exact_sampling'),
+        'e2e': {'value': main['value'], 'unit': 'interactions/s', 'h2d_bytes_per_step': 0,
                 'd2h_bytes_per_step': 0},
+        'eval': ({'metric': 'eval users/s MAP@10 + MRR + AUC', 'value': ev.get('value'),
+                  'unit': 'users/s', 'cpu_baseline': ev} if ev else None),
         'gpu_launches': 0,
     }
     print(json.dumps(line), flush=True)
 
 
-def config_dict(n_gpus):
-    w = WORKLOAD
+def config_dict(w, n_gpus):
     return {'workload': w['name'], 'num_users': w['num_users'], 'num_items': w['num_items'],
-            'interactions': w['interactions'], 'embedding_dim': w['dim'],
-            'num_negative_samples': w['n_neg'], 'loss': 'bpr (adaptive_bpr, N=5)',
+            'interactions': w['interactions'] or 4 * w['batch_per_gpu'] * n_gpus,
+            'embedding_dim': w['dim'], 'num_negative_samples': w['n_neg'],
+            'loss': f"{w['loss']} ({w['loss_resolved']}, N={w['n_neg']})",
             'optimizer': 'sparse_adam + sgd bias', 'batch_per_gpu': w['batch_per_gpu'],
             'global_batch': w['batch_per_gpu'] * n_gpus,
             'parallelism': f'user-partitioned data parallel x{n_gpus}, item table row-sharded, '
                            'item-side exchange in one kernel over NVLink peer memory'
             if n_gpus > 1 else 'single GPU',
-            'l2': 'tables + Adam state = 255 MB > 126 MB L2; every step reads a new batch',
+            'l2': 'tables + Adam state exceed the 126 MB L2; every step reads a new batch',
             'timed_region': 'K training steps incl. the device-side epoch plan (shuffle + per-batch '
                             'user order) of the epoch they belong to'}
 
 
 # ------------------------------------------------------------------------------------------ GPU arm
-def run_ours(args, rank, world, local_rank):
-    import torch.distributed as dist
-    import collie_b200 as cb
-    from collie_b200 import _abi
-    w = WORKLOAD
-    torch.cuda.set_device(local_rank)
-    dev = torch.device('cuda', local_rank)
-    B = w['batch_per_gpu']
-    steps, warmup = args.steps, max(args.warmup, 3)
+class Job(object):
+    """The training job of one rank: dataset shard, model, optimizers, loader and the step."""
 
-    if world > 1:
-        from collie_b200 import distributed as cbd
-        return cbd.bench_sharded(args, rank, world, local_rank, WORKLOAD, synth_interactions,
-                                 config_dict, ClockSampler)
+    def __init__(self, w, rank, world, dev, users, items, batch=None):
+        import collie_b200 as cb
+        from collie_b200 import distributed as D
+        self.w, self.rank, self.world, self.dev = w, rank, world, dev
+        self.B = int(batch or w['batch_per_gpu'])
+        ikw = dict(num_negative_samples=w['n_neg'], allow_missing_ids=True,
+                   remove_duplicate_user_item_pairs=False,
+                   check_num_negative_samples_is_valid=False,
+                   max_number_of_samples_to_consider=0, seed=w['seed'])
+        mkw = dict(embedding_dim=w['dim'], sparse=True, lr=w['lr'], bias_lr=w['bias_lr'],
+                   optimizer='sparse_adam', bias_optimizer='sgd', loss=w['loss'],
+                   lr_scheduler_func=None)
+        if world == 1:
+            self.gpos = None
+            self.data = cb.Interactions(users=users.numpy(), items=items.numpy(),
+                                        num_users=w['num_users'], num_items=w['num_items'], **ikw)
+            self.model = cb.MatrixFactorizationModel(train=self.data, **mkw).to(dev)
+            self.sharded = None
+        else:
+            lu, li, gpos = D.partition_interactions(users.numpy(), items.numpy(), rank, world)
+            per_rank, padded = D.shard_rows(w['num_items'], world)
+            self.gpos = gpos
+            self.data = cb.Interactions(users=lu, items=li,
+                                        num_users=D.num_local_users(w['num_users'], rank, world),
+                                        num_items=padded, **ikw)
+            self.data.global_positions = gpos
+            self.model = cb.MatrixFactorizationModel(train=self.data, **mkw).to(dev)
+            self.sharded = D.ShardedMatrixFactorization(self.model, w['num_items'],
+                                                        max_batch=self.B + self.B // 4)
+        self.opts = self.model.configure_optimizers()
+        bsz = min(self.B, (self.data.num_interactions // 2) // 1024 * 1024)
+        if world > 1:       # equal batches on every rank
+            import torch.distributed as dist
+            t = torch.tensor([bsz], dtype=torch.int64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            bsz = int(t.item())
+        self.B = bsz
+        self.loader = cb.InteractionsDataLoader(self.data, batch_size=self.B, shuffle=True,
+                                                drop_last=True)
+        self.epoch, self.it = 0, None
 
-    users, items = synth_interactions(w['num_users'], w['num_items'], w['interactions'], w['seed'])
-    data = cb.Interactions(users=users.numpy(), items=items.numpy(), num_users=w['num_users'],
-                           num_items=w['num_items'], num_negative_samples=w['n_neg'],
-                           allow_missing_ids=True, remove_duplicate_user_item_pairs=False,
-                           check_num_negative_samples_is_valid=False,
-                           max_number_of_samples_to_consider=0, seed=w['seed'])
-    model = cb.MatrixFactorizationModel(train=data, embedding_dim=w['dim'], sparse=True,
-                                        lr=w['lr'], bias_lr=w['bias_lr'], optimizer='sparse_adam',
-                                        bias_optimizer='sgd', loss='bpr',
-                                        lr_scheduler_func=None).to(dev)
-    opts = model.configure_optimizers()
-    n = data.num_interactions
-    g = torch.Generator().manual_seed(w['seed'])
-    perm = torch.randperm(n, generator=g)
-    users_h = users[perm].contiguous().pin_memory()
-    items_h = items[perm].contiguous().pin_memory()
-    gidx_h = perm.contiguous().pin_memory()
-    n_batches = n // B
-    loader = cb.InteractionsDataLoader(data, batch_size=B, shuffle=True, drop_last=True)
-
-    class Batches(object):
+    def next_batch(self):
         """Batches the way the trainer gets them: the loader's device-side epoch plan (shuffle +
         per-batch user order), rebuilt whenever an epoch is exhausted -- inside the timed region."""
-        def __init__(self):
-            self.epoch, self.it = 0, None
+        while True:
+            if self.it is None:
+                self.it = self.loader.device_batches(self.dev, epoch=self.epoch)
+                self.epoch += 1
+            try:
+                return next(self.it), self.epoch
+            except StopIteration:
+                self.it = None
 
-        def next(self):
-            while True:
-                if self.it is None:
-                    self.it = loader.device_batches(dev, epoch=self.epoch)
-                    self.epoch += 1
-                try:
-                    return next(self.it), self.epoch
-                except StopIteration:
-                    self.it = None
+    def step(self, db, epoch, reduce_loss=False, outputs=None):
+        if self.sharded is None:
+            return self.model.fused_step(db, optimizers=self.opts, interactions=self.data,
+                                         epoch=epoch, outputs=outputs)
+        return self.sharded.train_step(db, self.opts, interactions=self.data, epoch=epoch,
+                                       global_batch=self.world * self.B, reduce_loss=reduce_loss)
 
-    feed = Batches()
+    def exchange_name(self):
+        s = self.sharded
+        if s is None:
+            return None
+        if s._p2p is None:
+            return 'nccl all-gather + reduce-scatter'
+        return ('p2p kernel over symmetric memory, fence=' + s._fence_kind + ', multicast='
+                + str(s._p2p.get('multicast')))
 
-    def one_step():
-        db, epoch = feed.next()
-        return model.fused_step(db, optimizers=opts, interactions=data, epoch=epoch)
 
-    # ---- device-resident throughput
-    for i in range(warmup):
-        one_step()
-    feed.it = None          # the timed region pays for its own epoch plan
+def _barrier(world):
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
     torch.cuda.synchronize()
+
+
+def _max_over_ranks(x, world, dev):
+    if world == 1:
+        return float(x)
+    import torch.distributed as dist
+    t = torch.tensor([float(x)], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def _sum_over_ranks(x, world, dev):
+    if world == 1:
+        return float(x)
+    import torch.distributed as dist
+    t = torch.tensor([float(x)], dtype=torch.float64, device=dev)
+    dist.all_reduce(t)
+    return float(t.item())
+
+
+def time_device_steps(job, steps, warmup):
+    """K steps with the batches resident in HBM; barrier + synchronize on both sides, CUDA events,
+    max over ranks. Returns (ms total, last loss, own-kernel launches, clocks, per-step ms)."""
+    from collie_b200 import _abi
+    for _ in range(warmup):
+        job.step(*job.next_batch())
+    job.it = None          # the timed region pays for its own epoch plan
+    _barrier(job.world)
     launches0 = _abi.launch_count()
-    clocks = ClockSampler(local_rank)
-    clocks.start()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize()
-    ev0.record()
+    clocks = ClockSampler(job.dev.index).start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+    _barrier(job.world)
+    e0.record()
+    h0 = time.perf_counter()
+    loss = None
     for i in range(steps):
-        loss = one_step()
-    ev1.record()
-    torch.cuda.synchronize()
-    ms = ev0.elapsed_time(ev1)
+        loss = job.step(*job.next_batch())
+        marks[i].record()
+    host_ms = (time.perf_counter() - h0) * 1e3
+    e1.record()
+    _barrier(job.world)
     clk = clocks.stop()
-    launches = _abi.launch_count() - launches0
-    value = steps * B / (ms * 1e-3)
+    ms = _max_over_ranks(e0.elapsed_time(e1), job.world, job.dev)
+    step_ms = [e0.elapsed_time(marks[0])] + [marks[i].elapsed_time(marks[i + 1])
+                                             for i in range(steps - 1)]
+    return ms, loss, _abi.launch_count() - launches0, clk, step_ms, host_ms
 
-    # ---- end to end: pinned host batches in, loss out, every step (double-buffered copies)
-    # high priority: the small sort kernels of the next batch get SMs as soon as some free up,
-    # instead of queueing behind the step's big grids
+
+def time_e2e_steps(job, steps, warmup):
+    """The same steps fed from pinned HOST memory through the public API: every step copies its
+    batch (users, items, dataset positions: 16 B / interaction) to the device on a copy stream,
+    orders it by user there (BatchSorter) while the previous step runs, runs the step, and copies
+    the step's loss back to pinned host memory. With N > 1 the loss that comes back every step is
+    the rank's share of the global mean; the shares are summed over the ranks once per log
+    interval of the reference trainer (50 steps), SURVEY 8(e)."""
+    import torch.distributed as dist
+    from collie_b200.interactions import BatchSorter
+    w, dev, B = job.w, job.dev, job.B
+    data = job.data
+    n_local = data.num_interactions
+    g = torch.Generator().manual_seed(w['seed'] + job.rank)
+    perm = torch.randperm(n_local, generator=g)
+    users_h = torch.from_numpy(data.mat.row.astype(np.int32))[perm].contiguous().pin_memory()
+    items_h = torch.from_numpy(data.mat.col.astype(np.int32))[perm].contiguous().pin_memory()
+    gsrc = torch.from_numpy(np.asarray(job.gpos, dtype=np.int64)) if job.gpos is not None \
+        else torch.arange(n_local, dtype=torch.int64)
+    gidx_h = gsrc[perm].contiguous().pin_memory()
+    n_batches = n_local // B
+    # high priority: the small copy / sort kernels of the next batch get SMs as soon as some free
+    # up, instead of queueing behind the step's big grids
     copy_stream = torch.cuda.Stream(dev, priority=-1)
     main = torch.cuda.current_stream(dev)
-    from collie_b200.interactions import BatchSorter
     slots = [dict(u=torch.empty(B, dtype=torch.int32, device=dev),
                   i=torch.empty(B, dtype=torch.int32, device=dev),
                   g=torch.empty(B, dtype=torch.int64, device=dev),
-                  sort=BatchSorter(B, w['num_users'], dev),
+                  sort=BatchSorter(B, data.num_users, dev),
                   ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(2)]
     loss_host = torch.empty(steps + warmup, dtype=torch.float32).pin_memory()
+    acc = torch.zeros(1, dtype=torch.float32, device=dev)
+    reduced = []
 
-    def e2e_loop(count, base):
+    def loop(count, base):
         for s_ in slots:
             s_['free'].record(main)
         for j in range(count):
             slot = slots[j % 2]
             a = ((base + j) % n_batches) * B
             with torch.cuda.stream(copy_stream):
-                # copy stream: the batch comes in and is ordered by user while the previous
-                # step is still running on the main stream
                 copy_stream.wait_event(slot['free'])
                 slot['u'].copy_(users_h[a:a + B], non_blocking=True)
                 slot['i'].copy_(items_h[a:a + B], non_blocking=True)
@@ -302,82 +513,81 @@ def run_ours(args, rank, world, local_rank):
                 db = slot['sort'](slot['u'], slot['i'], slot['g'])
                 slot['ready'].record(copy_stream)
             main.wait_event(slot['ready'])
-            out = model.fused_step(db, optimizers=opts, interactions=data, epoch=1)
-            loss_host[j:j + 1].copy_(out.view(1), non_blocking=True)
+            out = job.step(db, 1)
+            loss_host[base + j:base + j + 1].copy_(out.view(1), non_blocking=True)
             slot['free'].record(main)
+            if job.world > 1:
+                acc.add_(out.view(1))
+                if (j + 1) % LOG_EVERY == 0 or j == count - 1:
+                    dist.all_reduce(acc)
+                    reduced.append(acc.clone())
+                    acc.zero_()
 
-    e2e_loop(warmup, 0)
-    torch.cuda.synchronize()
+    loop(warmup, 0)
+    _barrier(job.world)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    e2e_loop(steps, warmup)
+    loop(steps, warmup)
     e1.record()
-    torch.cuda.synchronize()
-    e2e_ms = e0.elapsed_time(e1)
-    e2e_value = steps * B / (e2e_ms * 1e-3)
-    h2d = B * (4 + 4 + 8)
+    _barrier(job.world)
+    ms = _max_over_ranks(e0.elapsed_time(e1), job.world, dev)
+    return ms, B * (4 + 4 + 8), float(loss_host[warmup + steps - 1])
 
-    # ---- roofline of the dominant kernel (k_fused_step), timed by events inside the library
+
+def step_profile(job, prof_steps):
+    """Per-kernel phase times (CUDA events inside the library, on the launching stream) of
+    `prof_steps` further steps on this rank; the last batch's unique users / items; the exchange
+    phases when the job is sharded."""
+    from collie_b200 import _abi
     lib = _abi.lib()
-    lib.cmf_profile_enable(1)
-    prof_steps = min(steps, 20)
-    outs = {'negs': None}
-    last = None
-    for i in range(prof_steps):          # the same batches as the timed loop: the loader's plan
-        last, ep_ = feed.next()
-        model.fused_step(last, optimizers=opts, interactions=data, epoch=ep_,
-                         outputs=outs if i == prof_steps - 1 else None)
     C = _abi.C
+    lib.cmf_profile_enable(1)
+    if job.sharded is not None:
+        job.sharded.timing = []
+    last = None
+    for i in range(prof_steps):
+        last, ep = job.next_batch()
+        job.step(last, ep)
     ms4 = (C.c_double * 4)()
     split = C.c_int32()
     n_steps, item_rows, user_rows = C.c_int64(), C.c_int64(), C.c_int64()
     lib.cmf_profile_read(ms4, C.byref(split), C.byref(n_steps), C.byref(item_rows),
                          C.byref(user_rows))
     lib.cmf_profile_enable(0)
-    uq = int(torch.unique(last.users).numel())
-    iq = int(torch.unique(torch.cat([outs['negs'].flatten(), last.items.long()])).numel())
-    D, N, T = w['dim'], w['n_neg'], 4
+    torch.cuda.synchronize()
     ns = max(1, n_steps.value)
-    row = D * T
-    # algorithmic bytes: gather B*(2+N) rows + biases + ids; update 6 streams per
-    # unique row + 2 bias streams
-    gather_bytes = B * (2 + N) * row + B * (2 + N) * T + B * 2 * 4
-    update_row = 6 * row + 2 * T
-    step_bytes = gather_bytes + (uq + iq) * update_row
-    inplace_users = uq - int(user_rows.value)
+    # the batch's unique rows: the negatives are a pure function of (seed, epoch, position)
+    negs = job.data.sample_negatives(last.users, last.gidx, epoch=ep)
+    if job.sharded is not None:
+        negs = negs.clamp(max=job.w['num_items'] - 1)
+    uq = int(torch.unique(last.users).numel())
+    iq = int(torch.unique(torch.cat([negs.flatten(), last.items.long()])).numel())
     if split.value:
         phases = {'k_fwd_loss': ms4[0] / ns, 'sort_tail': ms4[1] / ns,
                   'k_bwd_update': ms4[2] / ns, 'k_update_rows': ms4[3] / ns}
-        kernel, kernel_ms, kernel_bytes = 'k_fwd_loss', ms4[0] / ns, gather_bytes
     else:
         phases = {'sort': ms4[0] / ns, 'k_fused_step': ms4[1] / ns, 'k_update_rows': ms4[3] / ns}
-        kernel, kernel_ms = 'k_fused_step', ms4[1] / ns
-        kernel_bytes = gather_bytes + inplace_users * update_row
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
-    except Exception:
-        pass
-    peak = float(peaks.get('hbm_gbs', 6650.0))
-    achieved = kernel_bytes / (kernel_ms * 1e-3) / 1e9
-    roofline = {
-        'bound': 'hbm', 'kernel': kernel, 'achieved': achieved, 'peak': peak,
-        'unit': 'GB/s', 'frac': achieved / peak,
-        'peak_source': 'MEASURED_PEAKS.json hbm_gbs (of measured)' if peaks else
-                       'fallback 6650 GB/s (of fallback)',
-        'traffic': None,
-        'algorithmic_bytes_per_launch': kernel_bytes, 'kernel_ms': kernel_ms,
-        'phase_ms': phases,
-        'step_algorithmic_bytes': step_bytes,
-        'step_achieved_gbs': step_bytes / (ms / steps * 1e-3) / 1e9,
-        'step_frac': step_bytes / (ms / steps * 1e-3) / 1e9 / peak,
-        'unique_users': uq, 'unique_items': iq, 'rows_finished_by_update_kernel':
-            {'items': int(item_rows.value), 'users': int(user_rows.value)},
-        'update_phase_algorithmic_bytes': (uq + iq) * update_row,
-    }
-    # the forward kernel's rows come out of L2 (item table 13.7 MB, the step's user rows 46 MB),
-    # so next to the HBM roofline: live probes of read bandwidth (cmf_read_probe, a persistent
-    # grid of 16-byte loads) over an L2-resident buffer and over one far larger than L2
+    ex = None
+    if job.sharded is not None and job.sharded.timing:
+        t = job.sharded.timing
+        job.sharded.timing = None
+        torch.cuda.synchronize()
+        cols = list(zip(*[[a.elapsed_time(b) for a, b in zip(r[:-1], r[1:])] for r in t]))
+        ex = {'fence_before_ms': float(np.mean(cols[0])), 'kernel_ms': float(np.mean(cols[1])),
+              'fence_after_ms': float(np.mean(cols[2]))}
+    return {'phases': phases, 'split': bool(split.value), 'unique_users': uq, 'unique_items': iq,
+            'rows_finished_by_update_kernel': {'items': int(item_rows.value),
+                                               'users': int(user_rows.value)},
+            'exchange': ex}
+
+
+def read_probes(job):
+    """Live probes next to the HBM roofline (csrc/probe.cu): coalesced reads of an L2-resident
+    buffer and of one far larger than L2, and the forward kernel's own access pattern without its
+    arithmetic (random 512-byte rows of the item table, 16 loads in flight per lane)."""
+    from collie_b200 import _abi
+    lib, dev, w = _abi.lib(), job.dev, job.w
+
     def read_probe(nbytes, repeats):
         buf = torch.ones(nbytes // 4, dtype=torch.float32, device=dev)
         sink = torch.zeros(1, dtype=torch.float32, device=dev)
@@ -390,16 +600,13 @@ def run_ours(args, rank, world, local_rank):
         p1.record()
         torch.cuda.synchronize()
         return nbytes * repeats / (p0.elapsed_time(p1) * 1e-3) / 1e9
-    l2_gbs = read_probe(48 << 20, 200)
-    hbm_read_gbs = read_probe(4 << 30, 2)
-    # ... and of the kernel's own access pattern without its arithmetic: the same number of random
-    # 512-byte rows of the item table, 16 loads in flight per lane (cmf_gather_probe)
-    gather_gbs = None
-    if D == 128:
-        n_rows = B * (2 + N)
+    out = {'l2_resident_48MB': read_probe(48 << 20, 200), 'hbm_4GB': read_probe(4 << 30, 2),
+           'gather_512B_rows_l2': None}
+    if w['dim'] == 128:
+        n_rows = job.B * (2 + w['n_neg'])
         idx = torch.randint(0, w['num_items'], (n_rows,), dtype=torch.int32, device=dev)
         sink = torch.zeros(1, dtype=torch.float32, device=dev)
-        tab = model.item_embeddings.weight.data
+        tab = job.model.item_embeddings.weight.data
         gp = lambda: _abi.check(lib.cmf_gather_probe(_abi.ptr(tab), _abi.ptr(idx), n_rows, 4, 1, 4,
                                                      _abi.ptr(sink), _abi.stream_ptr(dev)),
                                 'cmf_gather_probe')
@@ -410,128 +617,451 @@ def run_ours(args, rank, world, local_rank):
             gp()
         g1.record()
         torch.cuda.synchronize()
-        gather_gbs = 5 * n_rows * 512 / (g0.elapsed_time(g1) * 1e-3) / 1e9
-    roofline['read_probe_gbs'] = {'l2_resident_48MB': l2_gbs, 'hbm_4GB': hbm_read_gbs,
-                                  'gather_512B_rows_l2': gather_gbs}
-    roofline['kernel_frac_of_l2_read_probe'] = achieved / l2_gbs
-    if gather_gbs:
-        roofline['kernel_frac_of_gather_probe'] = achieved / gather_gbs
+        out['gather_512B_rows_l2'] = 5 * n_rows * 512 / (g0.elapsed_time(g1) * 1e-3) / 1e9
+    return out
+
+
+def build_roofline(job, prof, ms_per_step, peaks, with_probes):
+    """algorithmic bytes per step = gather B*(2+N) rows + biases + ids, update 6
+    streams per unique row + 2 bias streams; per GPU (this rank's batch and unique rows)."""
+    w, B = job.w, job.B
+    D, N, T = w['dim'], w['n_neg'], 4
+    row = D * T
+    gather_bytes = B * (2 + N) * row + B * (2 + N) * T + B * 2 * 4
+    update_row = 6 * row + 2 * T
+    uq, iq = prof['unique_users'], prof['unique_items']
+    # sharded: this rank finishes its own users and only the item rows it owns
+    iq_local = iq if job.world == 1 else min(iq, -(-w['num_items'] // job.world))
+    step_bytes = gather_bytes + (uq + iq_local) * update_row
+    phases = prof['phases']
+    if prof['split']:
+        kernel, kernel_ms, kernel_bytes = 'k_fwd_loss', phases['k_fwd_loss'], gather_bytes
+    else:
+        kernel, kernel_ms = 'k_fused_step', phases['k_fused_step']
+        kernel_bytes = gather_bytes + (uq - prof['rows_finished_by_update_kernel']['users']) \
+            * update_row
+    peak = float(peaks.get('hbm_gbs', 6650.0))
+    achieved = kernel_bytes / (kernel_ms * 1e-3) / 1e9
+    step_gbs = step_bytes / (ms_per_step * 1e-3) / 1e9
+    upd_ms = phases.get('k_bwd_update', 0.0) + phases.get('k_update_rows', 0.0)
+    r = {
+        'bound': 'hbm', 'kernel': kernel + (' (rank 0)' if job.world > 1 else ''),
+        'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
+        'peak_source': 'MEASURED_PEAKS.json hbm_gbs (of measured)' if peaks else
+                       'fallback 6650 GB/s (of fallback)',
+        'traffic': None,
+        'note': 'achieved = ALGORITHMIC bytes / kernel time; the rows of k_fwd_loss are mostly L2 '
+                'hits (see traffic = DRAM bytes per launch), so this fraction can exceed 1; '
+                'step_frac is the HBM fraction of the whole step',
+        'algorithmic_bytes_per_launch': kernel_bytes, 'kernel_ms': kernel_ms, 'phase_ms': phases,
+        'step_algorithmic_bytes': step_bytes, 'step_achieved_gbs': step_gbs,
+        'step_frac': step_gbs / peak, 'step_frac_of_8TBs': step_gbs / 8000.0,
+        'unique_users': uq, 'unique_items': iq, 'item_rows_updated_here': iq_local,
+        'rows_finished_by_update_kernel': prof['rows_finished_by_update_kernel'],
+        'update_phase_algorithmic_bytes': (uq + iq_local) * update_row,
+        'update_phase_ms': upd_ms,
+        'update_phase_frac': ((uq + iq_local) * update_row / (upd_ms * 1e-3) / 1e9 / peak)
+        if upd_ms > 0 else None,
+    }
     traffic_file = os.path.join(ROOT, 'profiles', 'traffic.json')
     if os.path.exists(traffic_file):
         try:
-            roofline['traffic'] = json.load(open(traffic_file)).get(kernel)
+            t = json.load(open(traffic_file))
+            if t.get('workload', 'c3') == w['key'] and job.world == 1:
+                r['traffic'] = t.get(kernel)
+                r['traffic_static'] = True     # from the committed ncu capture, not this run
+                r['traffic_source'] = t.get('source')
         except Exception:
             pass
+    if job.world > 1 and prof.get('exchange'):
+        ex = prof['exchange']
+        per_rank = -(-w['num_items'] // job.world)
+        remote = (job.world - 1) / job.world
+        # per GPU and direction: the owner reads the other ranks' gradient rows of its shard (in)
+        # and stores its updated rows into the other ranks' copies (out); multicast: one reduced
+        # load and one store per row go through the switch
+        moved = per_rank * (D + 2) * T * (job.world - 1)
+        r['exchange'] = {
+            'bytes_per_step_per_gpu_per_direction': moved,
+            'kernel_ms': ex['kernel_ms'], 'fence_before_ms': ex['fence_before_ms'],
+            'fence_after_ms': ex['fence_after_ms'],
+            'nvlink_gbs_per_direction': moved / (ex['kernel_ms'] * 1e-3) / 1e9
+            if ex['kernel_ms'] > 0 else None,
+            'nvlink_peak_gbs_per_direction': NVLINK_GBS_PER_DIR,
+            'nvlink_frac': moved / (ex['kernel_ms'] * 1e-3) / 1e9 / NVLINK_GBS_PER_DIR
+            if ex['kernel_ms'] > 0 else None,
+            'remote_fraction': remote, 'how': job.exchange_name()}
+    if with_probes:
+        probes = read_probes(job)
+        r['read_probe_gbs'] = probes
+        r['kernel_frac_of_l2_read_probe'] = achieved / probes['l2_resident_48MB']
+        if probes['gather_512B_rows_l2']:
+            r['kernel_frac_of_gather_probe'] = achieved / probes['gather_512B_rows_l2']
+    return r
 
-    # ---- secondary headline: evaluation users/s (MAP@10 through the tensor-core path; MRR + AUC
-    # through the exact path), on a bounded user sample, timed on the device
+
+# ---------------------------------------------------------------------------------------- parity
+def parity_block(job, n_steps=3):
+    """N > 1: `n_steps` further global steps, replayed by rank 0 on a single-GPU copy of ALL tables
+    and optimizer state; compares the item table, its biases and every rank's user rows afterwards
+    (one optimizer step per unique row per global batch, collie/model/base/trainer.py:459-470)."""
+    import torch.distributed as dist
+    import collie_b200 as cb
+    from collie_b200.interactions import DeviceBatch
+    w, dev, world, rank = job.w, job.dev, job.world, job.rank
+    sh, model = job.sharded, job.model
+    main_opt, bias_opt = job.opts[0], job.opts[1]
+    nu, ni, D = w['num_users'], w['num_items'], w['dim']
+    n_max = -(-nu // world)
+
+    def gather_rows(t):
+        """[n_local, ...] of every rank -> list of world tensors on every rank."""
+        pad = torch.zeros((n_max,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev)
+        pad[:t.shape[0]] = t
+        outs = [torch.empty_like(pad) for _ in range(world)]
+        dist.all_gather(outs, pad)
+        return outs
+
+    def full_users(t):
+        outs = gather_rows(t)
+        full = torch.empty((nu,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev)
+        for q in range(world):
+            nq = (nu - q + world - 1) // world
+            full[q::world] = outs[q][:nq]
+        return full
+
+    def user_state():
+        pU, pbu = model.user_embeddings.weight, model.user_biases.weight
+        sU = main_opt.state_for(pU)
+        return (full_users(pU.data), full_users(pbu.data), full_users(sU['exp_avg']),
+                full_users(sU['exp_avg_sq']), int(sU['step']))
+
+    U, bu, Um, Uv, ustep = user_state()
+    st = sh._item_state(main_opt, bias_opt)
+    Im = torch.empty((sh.per_rank * world, D), dtype=torch.float32, device=dev)
+    Iv = torch.empty_like(Im)
+    dist.all_gather_into_tensor(Im, st['m'])
+    dist.all_gather_into_tensor(Iv, st['v'])
+    I, bi = sh.gather_item_table()
+    ref = ref_opts = None
+    if rank == 0:
+        tiny = cb.Interactions(users=np.zeros(1, dtype=np.int64), items=np.zeros(1, dtype=np.int64),
+                               num_users=nu, num_items=ni, num_negative_samples=w['n_neg'],
+                               allow_missing_ids=True, seed=w['seed'],
+                               check_num_negative_samples_is_valid=False,
+                               max_number_of_samples_to_consider=0)
+        ref = cb.MatrixFactorizationModel(train=tiny, embedding_dim=D, sparse=True, lr=w['lr'],
+                                          bias_lr=w['bias_lr'], optimizer='sparse_adam',
+                                          bias_optimizer='sgd', loss=w['loss'],
+                                          lr_scheduler_func=None).to(dev)
+        with torch.no_grad():
+            ref.user_embeddings.weight.copy_(U)
+            ref.user_biases.weight.copy_(bu)
+            ref.item_embeddings.weight.copy_(I[:ni])
+            ref.item_biases.weight.copy_(bi[:ni])
+        ref_opts = ref.configure_optimizers()
+        sU = ref_opts[0].state_for(ref.user_embeddings.weight)
+        sI = ref_opts[0].state_for(ref.item_embeddings.weight)
+        sU['exp_avg'].copy_(Um)
+        sU['exp_avg_sq'].copy_(Uv)
+        sI['exp_avg'].copy_(Im[:ni])
+        sI['exp_avg_sq'].copy_(Iv[:ni])
+        sU['step'] = ustep
+        sI['step'] = sh._step
+        for p in (ref.user_biases.weight, ref.item_biases.weight):
+            ref_opts[1].state_for(p)['step'] = ustep
+    del U, bu, Um, Uv, Im, Iv
+    loss_pairs = []
+    for _ in range(n_steps):
+        db, ep = job.next_batch()
+        gu = [torch.empty_like(db.users) for _ in range(world)]
+        gi = [torch.empty_like(db.items) for _ in range(world)]
+        gg = [torch.empty_like(db.gidx) for _ in range(world)]
+        dist.all_gather(gu, db.users.contiguous())
+        dist.all_gather(gi, db.items.contiguous())
+        dist.all_gather(gg, db.gidx.contiguous())
+        loss = job.step(db, ep, reduce_loss=True)
+        if rank == 0:
+            users_g = torch.cat([gu[q] * world + q for q in range(world)])
+            gb = DeviceBatch(users_g, torch.cat(gi), torch.cat(gg), None)
+            ref_loss = ref.fused_step(gb, optimizers=ref_opts, interactions=tiny, epoch=ep)
+            loss_pairs.append((float(loss), float(ref_loss)))
+    U, bu, _, _, _ = user_state()
+    I, bi = sh.gather_item_table()
+    out = None
+    if rank == 0:
+        rtol, atol = 1e-5, 1e-6
+        worst, bad, total = 0.0, 0, 0
+        for got, exp in ((I[:ni], ref.item_embeddings.weight.data),
+                         (bi[:ni], ref.item_biases.weight.data),
+                         (U, ref.user_embeddings.weight.data), (bu, ref.user_biases.weight.data)):
+            err = (got - exp).abs()
+            tol = atol + rtol * exp.abs()
+            worst = max(worst, float((err / tol).max()))
+            bad += int((err > tol).sum())
+            total += err.numel()
+        loss_rel = max(abs(a - b) / max(abs(b), 1e-30) for a, b in loss_pairs)
+        out = {'ok': bool(bad == 0 and loss_rel <= 1e-5), 'steps': n_steps,
+               'compared': 'item embeddings + item biases + every rank\'s user embeddings + user '
+                           'biases after the steps, vs rank 0 replaying the same global batches '
+                           'on a single-GPU copy of all tables and optimizer state',
+               'rtol': rtol, 'atol': atol, 'max_err_over_tol': worst, 'elements': total,
+               'elements_out_of_tol': bad, 'loss_max_rel': loss_rel,
+               'exchange': job.exchange_name(), 'world': world}
+    return out
+
+
+# ------------------------------------------------------------------------------------------ eval
+def eval_block(job, peaks, with_cpu):
+    """The evaluation half of the metric on this workload's shape: users/s of
+    evaluate_in_batches over `eval_users` test users, sharded over the GPUs (user-sharded: the item
+    table on every rank; item-sharded: every rank scores all users against its block of item
+    rows). Device time (CUDA events, max over ranks) and end to end (host ids in, host metrics
+    out, wall clock of the public call)."""
+    import collie_b200 as cb
+    from collie_b200 import distributed as D
+    w, dev, world, rank = job.w, job.dev, job.world, job.rank
+    n_eval = w['eval_users']
+    tu, ti = eval_test_set(w, n_eval)
+    ikw = dict(allow_missing_ids=True, check_num_negative_samples_is_valid=False,
+               remove_duplicate_user_item_pairs=False, max_number_of_samples_to_consider=0)
+    model = job.model
+    ni = w['num_items']
+    if world == 1:
+        local = cb.Interactions(users=tu, items=ti, num_users=w['num_users'], num_items=ni, **ikw)
+        n_local = n_eval
+
+        def run(metrics, precision):
+            return cb.evaluate_in_batches(metrics, local, model, k=10, verbose=False,
+                                          precision=precision)
+    else:
+        ltu, lti, _ = D.partition_interactions(tu, ti, rank, world)
+        local = cb.Interactions(users=ltu, items=lti,
+                                num_users=D.num_local_users(w['num_users'], rank, world),
+                                num_items=ni, **ikw)
+        n_local = len(np.unique(ltu))
+
+        def run(metrics, precision):
+            return D.evaluate_sharded(metrics, local, model, k=10, precision=precision)
+
+    def timed(fn, reps):
+        fn()                                       # first call: derives the device-side test set
+        _barrier(world)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(reps):
+            res = fn()
+        e1.record()
+        torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) / reps
+        _barrier(world)
+        dev_ms = _max_over_ranks(e0.elapsed_time(e1) / reps, world, dev)
+        wall = _max_over_ranks(wall, world, dev)
+        return dev_ms, wall, res
+
+    flops = 2.0 * n_eval * ni * w['dim']
+    tpeak = float(peaks.get('bf16_tflops', 1590.0))
+    out = {'metric': 'eval users/s MAP@10', 'unit': 'users/s', 'users': n_eval, 'n_gpus': world,
+           'sharding': 'user-sharded (item table on every rank)' if world > 1 else 'single GPU',
+           'test_set': f'{n_eval} users x 8 uniform targets, scored against all {ni} items, k=10'}
+    variants = {}
+    for label, metrics, precision in (
+            ('mapk_mrr_tensor_core', [cb.mapk, cb.mrr], 1),
+            ('mapk_mrr_auc_tensor_core', [cb.mapk, cb.mrr, cb.auc], 1),
+            ('mapk_mrr_auc_exact_fp32', [cb.mapk, cb.mrr, cb.auc], 0)):
+        try:
+            dev_ms, wall, res = timed(lambda: run(metrics, precision), 3)
+        except Exception as e:
+            variants[label] = {'error': repr(e)[:300]}
+            continue
+        useful = flops / (dev_ms * 1e-3) / 1e12
+        variants[label] = {
+            'value': n_eval / (dev_ms * 1e-3), 'unit': 'users/s', 'ms': dev_ms,
+            'e2e': {'value': n_eval / wall, 'unit': 'users/s',
+                    'what': 'wall clock of the public call (evaluate_in_batches / '
+                            'evaluate_sharded): test users already derived, metrics on the host'},
+            'metrics': res if isinstance(res, list) else [res],
+            'useful_tflops': useful, 'useful_frac_of_bf16_peak': useful / tpeak}
+    out['variants'] = variants
+    head = variants.get('mapk_mrr_tensor_core', {})
+    if 'value' in head:
+        out.update(value=head['value'], ms=head['ms'], e2e=head['e2e'],
+                   path='evaluate_in_batches([mapk, mrr], precision=1): tcgen05/TMA GEMM over '
+                        'bf16 operands with exact fp32 re-scoring, top-k + counters in the '
+                        'epilogue; whole call on the device clock')
+        from collie_b200 import _abi
+        info = (_abi.C.c_double * 4)()
+        try:
+            _abi.lib().cmf_eval_tc_info(w['dim'], info)
+            issued = 2.0 * n_eval * ni * info[0]
+            out['roofline'] = {
+                'bound': 'tensor', 'achieved': issued / (head['ms'] * 1e-3) / 1e12,
+                'useful_tflops': head['useful_tflops'], 'peak': tpeak, 'unit': 'TFLOP/s',
+                'frac': issued / (head['ms'] * 1e-3) / 1e12 / tpeak,
+                'issued_k': info[0],
+                'peak_source': 'MEASURED_PEAKS.json bf16_tflops (burst)' if peaks else 'fallback',
+                'note': 'achieved counts the issued bf16 MMA flops (2 * users * items * issued_k, '
+                        'issued_k = K extent the GEMM runs over); useful = 2 * users * items * D; '
+                        'time = the whole evaluation call, not the GEMM kernel alone'}
+        except Exception as e:
+            out['roofline'] = {'bound': 'tensor', 'error': repr(e)[:200]}
+    # item-sharded (every rank: all users x its block of items; partial top-k merged)
+    if world > 1:
+        full = cb.Interactions(users=tu, items=ti, num_users=w['num_users'], num_items=ni, **ikw)
+        # the working copy of the item table is complete on every rank; user rows are not, so the
+        # item-sharded run scores the users rank 0 owns (identical ids on all ranks)
+        try:
+            own = np.arange(0, min(n_eval * world, w['num_users']), world)[:n_eval]
+            tu0 = np.repeat(np.arange(len(own)), 8)
+            full0 = cb.Interactions(users=tu0, items=ti[:len(tu0)], num_users=model.hparams.num_users,
+                                    num_items=ni, **ikw)
+            um = _rank0_user_model(job, full0)
+            dev_ms, wall, res = timed(lambda: D.evaluate_item_sharded(
+                [cb.mapk, cb.mrr], full0, um, k=10, precision=1), 2)
+            out['item_sharded'] = {'value': len(own) / (dev_ms * 1e-3), 'unit': 'users/s',
+                                   'ms': dev_ms, 'users': int(len(own)),
+                                   'e2e': {'value': len(own) / wall, 'unit': 'users/s'},
+                                   'metrics': res,
+                                   'what': 'evaluate_item_sharded([mapk, mrr], precision=1): every '
+                                           'rank scores all users against its 1/N block of item '
+                                           'rows, partial top-k merged on the device'}
+        except Exception as e:
+            out['item_sharded'] = {'error': repr(e)[:300]}
+        del full
+    if with_cpu and rank == 0:
+        try:
+            out['cpu_baseline'] = cpu_eval_baseline(w, 25.0, os.cpu_count() or 1)
+        except Exception as e:  # pragma: no cover
+            out['cpu_baseline'] = {'error': repr(e)[:300]}
+    return out
+
+
+def _rank0_user_model(job, test):
+    """A model whose user tables are rank 0's (broadcast) and whose item tables are this rank's
+    working copy: what evaluate_item_sharded needs (same users everywhere, item blocks per rank)."""
+    import torch.distributed as dist
+    import collie_b200 as cb
+    w, dev = job.w, job.dev
+    n0 = (w['num_users'] + job.world - 1) // job.world
+    tiny = cb.Interactions(users=np.zeros(1, dtype=np.int64), items=np.zeros(1, dtype=np.int64),
+                           num_users=n0, num_items=w['num_items'], allow_missing_ids=True,
+                           check_num_negative_samples_is_valid=False,
+                           max_number_of_samples_to_consider=0)
+    m = cb.MatrixFactorizationModel(train=tiny, embedding_dim=w['dim'], sparse=True,
+                                    lr_scheduler_func=None, loss=w['loss']).to(dev)
+    with torch.no_grad():
+        if job.rank == 0:
+            m.user_embeddings.weight.copy_(job.model.user_embeddings.weight[:n0])
+            m.user_biases.weight.copy_(job.model.user_biases.weight[:n0])
+        dist.broadcast(m.user_embeddings.weight.data, src=0)
+        dist.broadcast(m.user_biases.weight.data, src=0)
+        I, bi = job.sharded.gather_item_table()
+        m.item_embeddings.weight.copy_(I)
+        m.item_biases.weight.copy_(bi)
+    return m
+
+
+# ------------------------------------------------------------------------------------------- main
+def run_ours(args, rank, world, local_rank, w):
+    import torch.distributed as dist
+    from collie_b200 import _abi
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    if world > 1 and not dist.is_initialized():
+        dist.init_process_group('nccl', device_id=dev)
+    steps, warmup = args.steps, max(args.warmup, 3)
+    peaks = load_peaks()
+    users, items = workload_interactions(w, world)
+    job = Job(w, rank, world, dev, users, items)
+    B = job.B
+
+    ms, loss, launches, clk, step_ms, host_ms = time_device_steps(job, steps, warmup)
+    value = steps * B * world / (ms * 1e-3)
+    if world > 1:
+        loss = loss.clone()
+        dist.all_reduce(loss)
+    e2e_ms, h2d, _ = time_e2e_steps(job, steps, warmup)
+    prof = step_profile(job, min(steps, 20))
+    roofline = build_roofline(job, prof, ms / steps, peaks, with_probes=(world == 1))
+    if world > 1:
+        tot_u = _sum_over_ranks(prof['unique_users'], world, dev)
+        roofline['unique_users_all_ranks'] = int(tot_u)
+
+    parity = None
+    if world > 1 and not args.no_parity:
+        try:
+            parity = parity_block(job)
+        except Exception as e:
+            parity = {'ok': False, 'error': repr(e)[:400]}
+            raise
+
     eval_info = None
     if not args.no_eval:
-        n_eval_users = 32768
-        tu = torch.arange(n_eval_users, dtype=torch.int32)
-        ti = torch.from_numpy(np.random.default_rng(5).integers(0, w['num_items'],
-                                                                 (n_eval_users, 8))).flatten()
-        test = cb.Interactions(users=tu.repeat_interleave(8).numpy(), items=ti.numpy(),
-                               num_users=w['num_users'], num_items=w['num_items'],
-                               allow_missing_ids=True, check_num_negative_samples_is_valid=False,
-                               remove_duplicate_user_item_pairs=False,
-                               max_number_of_samples_to_consider=0)
-        from collie_b200 import metrics as M
-        tables = M._model_tables(model)
-        test_users = np.unique(test.mat.row)
-        indptr, tgt_items, nnz = M._targets_device(test.mat.tocsr(), test_users, dev)
-        users_dev = torch.from_numpy(test_users.astype(np.int32)).to(dev)
+        eval_info = eval_block(job, peaks, with_cpu=(world == 1 and not args.no_cpu_baseline))
 
-        def tc_pass(ws=None):
-            return M._eval_tile(dev, n_eval_users, w['num_items'], 10, indptr, tgt_items,
-                                {'mapk', 'mrr'}, tables=tables, user_ids=users_dev, precision=1,
-                                workspace=ws)
-        ws = tc_pass()['_workspace']
-        torch.cuda.synchronize()
-        t0e, t1e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        reps = 5
-        t0e.record()
-        for _ in range(reps):
-            res = tc_pass(ws)
-        t1e.record()
-        torch.cuda.synchronize()
-        tc_ms = t0e.elapsed_time(t1e) / reps
-        map10 = M._per_user('mapk', res, nnz, w['num_items']).mean().item()
-        t0 = time.perf_counter()
-        m_all = cb.evaluate_in_batches([cb.mapk, cb.mrr, cb.auc], test, model, k=10, verbose=False)
-        torch.cuda.synchronize()
-        api_exact_first_s = time.perf_counter() - t0
-        t0 = time.perf_counter()
-        m_all = cb.evaluate_in_batches([cb.mapk, cb.mrr, cb.auc], test, model, k=10, verbose=False)
-        torch.cuda.synchronize()
-        api_exact_s = time.perf_counter() - t0
-        # wall clock of the public call, results on the host: the first call on a test set (derives
-        # its device-side form) and a later one (every following epoch's validation)
-        t0 = time.perf_counter()
-        m_tc = cb.evaluate_in_batches([cb.mapk, cb.mrr], test, model, k=10, verbose=False,
-                                      precision=1)
-        torch.cuda.synchronize()
-        api_tc_first_s = time.perf_counter() - t0
-        t0 = time.perf_counter()
-        for _ in range(3):
-            m_tc = cb.evaluate_in_batches([cb.mapk, cb.mrr], test, model, k=10, verbose=False,
-                                          precision=1)
-        torch.cuda.synchronize()
-        api_tc_s = (time.perf_counter() - t0) / 3
-        flops = 2.0 * n_eval_users * w['num_items'] * w['dim']
-        kp = ((3 * w['dim'] + 4 + 15) // 16) * 16       # K = 16 steps that are issued
-        issued = 2.0 * n_eval_users * w['num_items'] * kp
-        tpeak = float(peaks.get('bf16_tflops', 1590.0))
-        eval_info = {
-            'metric': 'eval users/s MAP@10', 'value': n_eval_users / (tc_ms * 1e-3),
-            'unit': 'users/s', 'users': n_eval_users,
-            'path': 'cmf_eval_tile precision=1, MAP@10 + MRR: tcgen05/TMA GEMM over bf16-split '
-                    'operands (hi.hi + hi.lo + lo.hi), top-k + MRR counter in the epilogue; device '
-                    'time of the whole call (operand split, exact target scores, GEMM + top-k, '
-                    'merge)',
-            'ms': tc_ms, 'map10': map10,
-            'roofline': {'bound': 'tensor', 'achieved': issued / (tc_ms * 1e-3) / 1e12,
-                         'useful_tflops': flops / (tc_ms * 1e-3) / 1e12, 'peak': tpeak,
-                         'unit': 'TFLOP/s', 'frac': issued / (tc_ms * 1e-3) / 1e12 / tpeak,
-                         'note': 'achieved counts the issued bf16 MMA flops (3 split terms + bias '
-                                 'slots); useful = 2 * users * items * D'},
-            'api_users_per_s': {'evaluate_in_batches([mapk, mrr], precision=1)':
-                                n_eval_users / api_tc_s,
-                                'evaluate_in_batches([mapk, mrr], precision=1), first call':
-                                n_eval_users / api_tc_first_s,
-                                'evaluate_in_batches([mapk, mrr, auc]) exact fp32':
-                                n_eval_users / api_exact_s,
-                                'evaluate_in_batches([mapk, mrr, auc]) exact fp32, first call':
-                                n_eval_users / api_exact_first_s},
-            'metrics_exact': m_all, 'metrics_tc': m_tc,
-        }
+    # one constant-GLOBAL-work point (strong scaling): 2,097,152 interactions per global step,
+    # i.e. 2,097,152 / N per GPU, so the weak-scaling curve above (whose per-rank user set shrinks
+    # with N) has a fixed-work companion
+    strong = None
+    if not args.no_strong and w['key'] == 'c3':
+        gb = 2097152
+        del job.loader
+        job2 = job
+        job2.B = gb // world
+        import collie_b200 as cb
+        job2.loader = cb.InteractionsDataLoader(job.data, batch_size=job2.B, shuffle=True,
+                                                drop_last=True)
+        job2.it = None
+        if job2.sharded is not None and job2.B > job2.sharded._p2p['cap'][0] \
+                if (job2.sharded is not None and job2.sharded._p2p) else False:
+            strong = {'skipped': 'symmetric workspace smaller than the strong-scaling batch'}
+        else:
+            s_steps = max(4, min(steps, 12))
+            ms2, _, _, _, _, _ = time_device_steps(job2, s_steps, 3)
+            strong = {'global_batch': gb, 'batch_per_gpu': job2.B, 'steps': s_steps,
+                      'ms_per_step': ms2 / s_steps, 'scaling': 'strong',
+                      'value': s_steps * job2.B * world / (ms2 * 1e-3), 'unit': 'interactions/s'}
 
-    # ---- CPU baseline on a bounded sample (rank 0, N = 1 only)
     cpu = None
-    if not args.no_cpu_baseline:
-        threads = os.cpu_count() or 1
-        cpu_steps, cpu_warm = 3, 1
-        nb = B * (cpu_steps + cpu_warm + 1)
-        secs = cpu_port_run(users[:nb], items[:nb], cpu_steps, cpu_warm, B, threads)
-        cpu = {'value': cpu_steps * B / secs, 'unit': 'interactions/s', 'cores': threads,
-               'kind': 'port',
-               'sample': f'{cpu_steps} steps of batch {B} (+{cpu_warm} warm-up), same tables and '
-                         'distributions; reference CPU path restated in torch (oracle port)'}
+    if world == 1 and rank == 0 and not args.no_cpu_baseline:
+        res = cpu_train_baseline(w, users, items, 3, 1, 30.0, os.cpu_count() or 1)
+        main = res.get('reference') or res['port']
+        cpu = {k: main[k] for k in ('value', 'unit', 'cores', 'kind', 'sample')}
+        if main is not res.get('port') and res.get('port'):
+            cpu['port'] = {k: res['port'][k] for k in ('value', 'unit', 'cores', 'kind', 'sample')}
+        if main.get('default_loader_exact_sampling'):
+            cpu['default_loader_exact_sampling'] = main['default_loader_exact_sampling']
 
-    line = {
-        'metric': 'MF train interactions/s (fwd+bwd+sparse Adam)', 'value': value,
-        'unit': 'interactions/s', 'n_gpus': 1, 'steps': steps, 'warmup': warmup,
-        'ms_per_step': ms / steps, 'higher_is_better': True, 'scaling': 'weak',
-        'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': config_dict(1),
-        'roofline': roofline, 'cpu_baseline': cpu,
-        'e2e': {'value': e2e_value, 'unit': 'interactions/s', 'h2d_bytes_per_step': h2d,
-                'd2h_bytes_per_step': 4, 'ms_per_step': e2e_ms / steps},
-        'gpu_launches': int(launches),
-        'gpu_launches_note': 'own kernels per step: k_iota + k_fwd_loss + k_bwd_update + k_update_rows; '
-                             'the CUB radix sort adds library launches that are not counted',
-        'clocks': clk, 'final_loss': float(loss), 'eval': eval_info,
-    }
-    print(json.dumps(line), flush=True)
+    if rank == 0:
+        line = {
+            'metric': METRIC, 'value': value, 'unit': 'interactions/s', 'n_gpus': world,
+            'steps': steps, 'warmup': warmup, 'ms_per_step': ms / steps, 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': dict(config_dict(w, world), batch_per_gpu=B, global_batch=B * world),
+            'roofline': roofline, 'cpu_baseline': cpu,
+            'e2e': {'value': steps * B * world / (e2e_ms * 1e-3), 'unit': 'interactions/s',
+                    'h2d_bytes_per_step': world * h2d, 'd2h_bytes_per_step': 4 * world,
+                    'ms_per_step': e2e_ms / steps,
+                    'loss_reduction': None if world == 1 else
+                    f'rank-local loss D2H every step; all-reduce every {LOG_EVERY} steps'},
+            'gpu_launches': int(launches),
+            'gpu_launches_note': 'own kernels launched by rank 0 inside the timed region (k_fwd_loss '
+                                 '+ k_bwd_update + k_update_rows per step'
+                                 + (' + the exchange kernel' if world > 1 else '')
+                                 + ', epoch-plan kernels once per epoch); CUB radix-sort launches '
+                                   'are library kernels and are not counted',
+            'exchange': job.exchange_name(),
+            'host_issue_ms_per_step': host_ms / steps,
+            'step_ms_rank0': {'median': float(np.median(step_ms)), 'max': float(np.max(step_ms)),
+                              'slowest_step': int(np.argmax(step_ms))},
+            'clocks': clk, 'final_loss': float(loss), 'parity': parity, 'eval': eval_info,
+            'fixed_global_work': strong,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
 
 
 def main():
@@ -540,12 +1070,16 @@ def main():
     ap.add_argument('--steps', type=int, default=50)
     ap.add_argument('--warmup', type=int, default=5)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--config', default='c3', choices=sorted(WORKLOADS))
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-eval', action='store_true')
+    ap.add_argument('--no-parity', action='store_true')
+    ap.add_argument('--no-strong', action='store_true')
     args = ap.parse_args()
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
     local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    w = WORKLOADS[args.config]
     # stdout carries the JSON line and nothing else: libraries that print from C (NCCL's version
     # banner) are sent to stderr by pointing fd 1 there and keeping the real stdout for the line
     sys.stdout.flush()
@@ -553,11 +1087,11 @@ def main():
     os.dup2(2, 1)
     sys.stdout = real_stdout
     if args.impl == 'reference':
-        run_reference(args, rank, world)
+        run_reference(args, rank, world, w)
         return
     if not torch.cuda.is_available():
         raise SystemExit('bench.py needs a CUDA device: collie_b200 has no CPU path')
-    run_ours(args, rank, world, local_rank)
+    run_ours(args, rank, world, local_rank, w)
 
 
 if __name__ == '__main__':

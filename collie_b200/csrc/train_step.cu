@@ -665,8 +665,6 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
   if (p.train) { p.emb = make_opt(a->emb_opt); p.bias = make_opt(a->bias_opt); }
   CMF_REQUIRE(a->B_global == 0 || a->B_global >= a->B, "cmf_train_step: B_global smaller than B");
   const int dense = p.train && (p.emb.dense || p.bias.dense);
-  CMF_REQUIRE(!(a->skip_item_update && dense),
-              "cmf_train_step: skip_item_update needs sparse-row rules (sparse_adam / sgd / adagrad)");
   p.user_inplace = p.train && !dense;
   p.use_lists = p.train && !dense;
   p.inv_B = 1.0f / (float)(a->B_global > 0 ? a->B_global : a->B);

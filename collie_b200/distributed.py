@@ -98,12 +98,16 @@ class ShardedMatrixFactorization(object):
     """
 
     def __init__(self, model, true_num_items, group=None, exchange='auto', max_batch=None,
-                 max_negatives=None):
+                 max_negatives=None, multicast='auto'):
         """``exchange``: ``'p2p'`` = the owner-side kernel over peer memory
         (``cmf_item_exchange_update``; needs NCCL ranks of one node and symmetric memory),
         ``'nccl'`` = all-gather / reduce-scatter collectives, ``'auto'`` = p2p when it can be set
         up. ``max_batch`` / ``max_negatives`` size the symmetric training workspace of the p2p
-        mode (default: the first step's batch, over all ranks, plus 25 %)."""
+        mode (default: the first step's batch, over all ranks, plus 25 %). ``multicast``: whether
+        the p2p kernel reduces and broadcasts through NVSwitch multicast addresses
+        (``multimem.ld_reduce`` / ``multimem.st``): ``'auto'`` = for more than two ranks when the
+        allocator provides them (env ``CMF_MULTICAST=0`` turns it off), ``True`` = required (raises
+        when unavailable), ``False`` = plain peer loads / stores."""
         self.model = model
         self.group = group
         self.exchange = exchange
@@ -111,7 +115,11 @@ class ShardedMatrixFactorization(object):
         self._p2p = None
         import os
         self._fence_kind = os.environ.get('CMF_FENCE', 'symm')     # 'symm' | 'nccl'
-        self._use_multicast = os.environ.get('CMF_MULTICAST', '1') != '0'
+        if multicast not in ('auto', True, False):
+            raise ValueError("multicast must be 'auto', True or False")
+        if multicast == 'auto' and os.environ.get('CMF_MULTICAST', '1') == '0':
+            multicast = False
+        self._multicast = multicast
         self.rank = dist.get_rank(group)
         self.world = dist.get_world_size(group)
         self.per_rank, padded = shard_rows(true_num_items, self.world)
@@ -126,6 +134,9 @@ class ShardedMatrixFactorization(object):
         self.bi_shard = self.bi_full[lo:hi]
         self._state = None
         self._step = 0
+        # set to a list to have every p2p step append four CUDA events (after the local step,
+        # after the first fence, after the exchange kernel, after the second fence)
+        self.timing = None
         # every rank starts from rank 0's item table (user tables are disjoint)
         dist.broadcast(self.I_full, src=self._global_rank(0), group=group)
         dist.broadcast(self.bi_full, src=self._global_rank(0), group=group)
@@ -228,8 +239,13 @@ class ShardedMatrixFactorization(object):
         # at the same offset on every rank
         mc = [int(getattr(h_, 'multicast_ptr', 0) or 0) for h_ in self._p2p['handles']]
         same = all(bool(torch.equal(all_offs[q], offs)) for q in range(self.world))
-        if self._use_multicast and self.world > 2 and all(mc) and same:   # (measured: 2 ranks
-            # are ~2 % faster with plain peer loads / stores, 4 ranks ~2 % faster with multicast)
+        if self._multicast is True and not (all(mc) and same):
+            raise RuntimeError('NVSwitch multicast addresses are not available for the symmetric '
+                               'buffers (or the accumulators sit at different offsets)')
+        # (measured: 2 ranks are ~2 % faster with plain peer loads / stores, 4 ranks ~2 % faster
+        # with multicast)
+        if (self._multicast is True or (self._multicast == 'auto' and self.world > 2)) \
+                and all(mc) and same:
             peers.mc_I, peers.mc_bi = mc[0], mc[1]
             peers.mc_GI = mc[2] + int(offs[0])
             peers.mc_gbi = mc[2] + int(offs[1])
@@ -275,23 +291,34 @@ class ShardedMatrixFactorization(object):
                             num_items_logical=self.true_num_items)
         if m._workspace is not self._p2p['ws']:
             raise _abi.CmfError('the model replaced its symmetric training workspace')
+        ev = None
+        if self.timing is not None:
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+            ev[0].record()
         # every rank's accumulators are complete ...
         if reduce_loss:
             dist.all_reduce(loss, group=self.group)     # (doubles as the rendezvous)
         else:
             self._fence()
+        if ev:
+            ev[1].record()
         self._step += 1
         g_main, g_bias = main.param_groups[0], bias.param_groups[0]
         o = _abi.make_opt(main.rule, g_main['lr'], self._step, g_main.get('betas', (0.9, 0.999)),
-                          g_main.get('eps', 1e-8), 0.0)
+                          g_main.get('eps', 1e-8), g_main.get('weight_decay', 0.0))
         ob = _abi.make_opt(bias.rule, g_bias['lr'], self._step, g_bias.get('betas', (0.9, 0.999)),
-                           g_bias.get('eps', 1e-8), 0.0)
+                           g_bias.get('eps', 1e-8), g_bias.get('weight_decay', 0.0))
         _abi.check(_abi.lib().cmf_item_exchange_update(
             _abi.C.byref(self._p2p['peers']), _abi.ptr(st['m']), _abi.ptr(st['v']),
             _abi.ptr(st['bm']), _abi.ptr(st['bv']), o, ob, _abi.stream_ptr(self.I_full.device)),
             'cmf_item_exchange_update')
+        if ev:
+            ev[2].record()
         # ... and every rank's table copy is complete before anybody's next step reads it
         self._fence()
+        if ev:
+            ev[3].record()
+            self.timing.append(ev)
         return loss
 
     def _global_rank(self, r):
@@ -373,9 +400,9 @@ class ShardedMatrixFactorization(object):
         self._step += 1
         g_main, g_bias = main.param_groups[0], bias.param_groups[0]
         o = _abi.make_opt(main.rule, g_main['lr'], self._step, g_main.get('betas', (0.9, 0.999)),
-                          g_main.get('eps', 1e-8), 0.0)
+                          g_main.get('eps', 1e-8), g_main.get('weight_decay', 0.0))
         ob = _abi.make_opt(bias.rule, g_bias['lr'], self._step, g_bias.get('betas', (0.9, 0.999)),
-                           g_bias.get('eps', 1e-8), 0.0)
+                           g_bias.get('eps', 1e-8), g_bias.get('weight_decay', 0.0))
         rc = _abi.lib().cmf_optimizer_rows_masked(
             _abi.ptr(self.I_shard), _abi.ptr(st['m']), _abi.ptr(st['v']), _abi.ptr(st['g']),
             _abi.ptr(self.bi_shard), _abi.ptr(st['bm']), _abi.ptr(st['bv']), _abi.ptr(st['gb']),
@@ -557,196 +584,3 @@ def merge_topk(scores, ids, k):
     # a stable sort by descending score keeps the ascending id order among equal scores
     top = torch.argsort(-s_cmp, dim=1, stable=True)[:, :k]
     return torch.gather(s, 1, top), torch.gather(i, 1, top)
-
-
-def bench_sharded(args, rank, world, local_rank, workload, synth, config_dict, ClockSampler):
-    """``bench.py --gpus N`` for N > 1: weak scaling (the per-GPU batch is fixed), device timing,
-    max over ranks, one JSON line from rank 0."""
-    import json
-    import os
-    import collie_b200 as cb
-    w = workload
-    dev = torch.device('cuda', local_rank)
-    if not dist.is_initialized():
-        dist.init_process_group('nccl', device_id=dev)
-    B = w['batch_per_gpu']
-    steps, warmup = args.steps, max(args.warmup, 3)
-    users, items = synth(w['num_users'], w['num_items'], w['interactions'], w['seed'])
-    lu, li, gpos = partition_interactions(users.numpy(), items.numpy(), rank, world)
-    per_rank, padded = shard_rows(w['num_items'], world)
-    data = cb.Interactions(users=lu, items=li, num_users=num_local_users(w['num_users'], rank, world),
-                           num_items=padded, num_negative_samples=w['n_neg'],
-                           allow_missing_ids=True, remove_duplicate_user_item_pairs=False,
-                           check_num_negative_samples_is_valid=False,
-                           max_number_of_samples_to_consider=0, seed=w['seed'])
-    data.global_positions = gpos
-    model = cb.MatrixFactorizationModel(train=data, embedding_dim=w['dim'], sparse=True,
-                                        lr=w['lr'], bias_lr=w['bias_lr'], optimizer='sparse_adam',
-                                        bias_optimizer='sgd', loss='bpr',
-                                        lr_scheduler_func=None).to(dev)
-    sharded = ShardedMatrixFactorization(model, w['num_items'])
-    opts = model.configure_optimizers()
-    loader = cb.InteractionsDataLoader(data, batch_size=B, shuffle=True, drop_last=True)
-
-    state = {'epoch': 0, 'it': None}
-
-    def next_batch():
-        while True:
-            if state['it'] is None:
-                state['it'] = loader.device_batches(dev, epoch=state['epoch'])
-                state['epoch'] += 1
-            try:
-                return next(state['it']), state['epoch']
-            except StopIteration:
-                state['it'] = None
-
-    def one_step():
-        db, epoch = next_batch()
-        return sharded.train_step(db, opts, interactions=data, epoch=epoch, global_batch=world * B,
-                                  reduce_loss=False)
-
-    for _ in range(warmup):
-        one_step()
-    state['it'] = None
-    torch.cuda.synchronize()
-    launches0 = _abi.launch_count()
-    clocks = ClockSampler(local_rank)
-    clocks.start()
-    dist.barrier()
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    import time as _time
-    h0 = _time.perf_counter()
-    marks = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
-    for i_ in range(steps):
-        loss = one_step()
-        marks[i_].record()
-    host_ms = (_time.perf_counter() - h0) * 1e3      # host time to ISSUE the steps (no sync)
-    e1.record()
-    torch.cuda.synchronize()
-    dist.barrier()
-    torch.cuda.synchronize()
-    clk = clocks.stop()
-    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms = float(ms.item())
-    step_ms = [e0.elapsed_time(marks[0])] + [marks[i_].elapsed_time(marks[i_ + 1])
-                                             for i_ in range(steps - 1)]
-    launches = _abi.launch_count() - launches0
-    dist.all_reduce(loss)
-    value = steps * B * world / (ms * 1e-3)
-
-    # ---- end to end: this rank's batches come from pinned host memory every step (double-buffered
-    # copies on a side stream), the step's loss goes back to the host every step
-    from .interactions import BatchSorter
-    n_local = data.num_interactions
-    g = torch.Generator().manual_seed(w['seed'] + rank)
-    perm = torch.randperm(n_local, generator=g)
-    users_h = torch.from_numpy(data.mat.row.astype(np.int32))[perm].contiguous().pin_memory()
-    items_h = torch.from_numpy(data.mat.col.astype(np.int32))[perm].contiguous().pin_memory()
-    gidx_h = torch.from_numpy(np.asarray(gpos, dtype=np.int64))[perm].contiguous().pin_memory()
-    n_batches = n_local // B
-    # high priority: the small sort kernels of the next batch get SMs as soon as some free up,
-    # instead of queueing behind the step's big grids
-    copy_stream = torch.cuda.Stream(dev, priority=-1)
-    main = torch.cuda.current_stream(dev)
-    slots = [dict(u=torch.empty(B, dtype=torch.int32, device=dev),
-                  i=torch.empty(B, dtype=torch.int32, device=dev),
-                  g=torch.empty(B, dtype=torch.int64, device=dev),
-                  sort=BatchSorter(B, data.num_users, dev),
-                  ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(2)]
-    loss_host = torch.empty(steps + warmup, dtype=torch.float32).pin_memory()
-
-    def e2e_loop(count, base):
-        for s_ in slots:
-            s_['free'].record(main)
-        for j in range(count):
-            slot = slots[j % 2]
-            a = ((base + j) % n_batches) * B
-            with torch.cuda.stream(copy_stream):
-                copy_stream.wait_event(slot['free'])
-                slot['u'].copy_(users_h[a:a + B], non_blocking=True)
-                slot['i'].copy_(items_h[a:a + B], non_blocking=True)
-                slot['g'].copy_(gidx_h[a:a + B], non_blocking=True)
-                db = slot['sort'](slot['u'], slot['i'], slot['g'])   # ordered by user, off the
-                slot['ready'].record(copy_stream)                    # main stream
-            main.wait_event(slot['ready'])
-            out = sharded.train_step(db, opts, interactions=data, epoch=1, global_batch=world * B,
-                                     reduce_loss=True)
-            loss_host[base + j:base + j + 1].copy_(out.view(1), non_blocking=True)
-            slot['free'].record(main)
-
-    e2e_loop(warmup, 0)
-    torch.cuda.synchronize()
-    dist.barrier()
-    torch.cuda.synchronize()
-    e0.record()
-    e2e_loop(steps, warmup)
-    e1.record()
-    torch.cuda.synchronize()
-    dist.barrier()
-    e2e_ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
-    e2e_ms = float(e2e_ms.item())
-
-    # ---- the local kernels of a step, timed by events inside the library (rank 0's numbers)
-    lib = _abi.lib()
-    lib.cmf_profile_enable(1)
-    prof_steps = min(steps, 20)
-    for _ in range(prof_steps):
-        one_step()
-    C = _abi.C
-    ms4 = (C.c_double * 4)()
-    split = C.c_int32()
-    n_steps, item_rows, user_rows = C.c_int64(), C.c_int64(), C.c_int64()
-    lib.cmf_profile_read(ms4, C.byref(split), C.byref(n_steps), C.byref(item_rows),
-                         C.byref(user_rows))
-    lib.cmf_profile_enable(0)
-    torch.cuda.synchronize()
-    if rank == 0:
-        D, N, T = w['dim'], w['n_neg'], 4
-        exchange = 2 * padded * (D + 2) * T * (world - 1) / world   # all-gather + reduce-scatter
-        ns = max(1, n_steps.value)
-        gather_bytes = B * (2 + N) * D * T + B * (2 + N) * T + B * 2 * 4
-        kernel_ms = ms4[0] / ns
-        try:
-            peaks = json.load(open(os.path.join(os.path.dirname(os.path.dirname(
-                os.path.abspath(__file__))), 'MEASURED_PEAKS.json')))
-        except Exception:
-            peaks = {}
-        peak = float(peaks.get('hbm_gbs', 6650.0))
-        achieved = gather_bytes / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else 0.0
-        roofline = {
-            'bound': 'hbm', 'kernel': 'k_fwd_loss (rank 0)', 'achieved': achieved, 'peak': peak,
-            'unit': 'GB/s', 'frac': achieved / peak,
-            'peak_source': 'MEASURED_PEAKS.json hbm_gbs (of measured)' if peaks else
-                           'fallback 6650 GB/s (of fallback)',
-            'traffic': None, 'algorithmic_bytes_per_launch': gather_bytes, 'kernel_ms': kernel_ms,
-            'phase_ms': {'k_fwd_loss': ms4[0] / ns, 'sort_tail': ms4[1] / ns,
-                         'k_bwd_update': ms4[2] / ns, 'k_update_rows': ms4[3] / ns},
-        }
-        line = {
-            'metric': 'MF train interactions/s (fwd+bwd+sparse Adam)', 'value': value,
-            'unit': 'interactions/s', 'n_gpus': world, 'steps': steps, 'warmup': warmup,
-            'ms_per_step': ms / steps, 'higher_is_better': True, 'scaling': 'weak',
-            'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': config_dict(world),
-            'roofline': roofline, 'cpu_baseline': None,
-            'e2e': {'value': steps * B * world / (e2e_ms * 1e-3), 'unit': 'interactions/s',
-                    'h2d_bytes_per_step': world * B * (4 + 4 + 8), 'd2h_bytes_per_step': 4 * world,
-                    'ms_per_step': e2e_ms / steps},
-            'gpu_launches': int(launches),
-            'gpu_launches_note': 'rank 0; own kernels per step: k_fwd_loss + k_bwd_update + '
-                                 'k_update_rows + k_optimizer_rows_masked (+ NCCL collectives)',
-            'exchange_bytes_per_step_per_gpu': exchange,
-            'host_issue_ms_per_step': host_ms / steps,
-            'exchange': ('p2p kernel over symmetric memory, fence=' + sharded._fence_kind +
-                         ', multicast=' + str(sharded._p2p.get('multicast')))
-            if sharded._p2p is not None else 'nccl all-gather + reduce-scatter',
-            'step_ms_rank0': {'median': float(np.median(step_ms)), 'max': float(np.max(step_ms)),
-                              'slowest_step': int(np.argmax(step_ms))},
-            'clocks': clk, 'final_loss': float(loss),
-        }
-        print(json.dumps(line), flush=True)
-    dist.barrier()
-    dist.destroy_process_group()
