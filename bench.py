@@ -46,7 +46,7 @@ WORKLOADS = {
                 'synthetic ML-20M shape',
         'num_users': 138493, 'num_items': 26744, 'interactions': 20_000_000, 'dim': 128,
         'n_neg': 5, 'loss': 'bpr', 'loss_resolved': 'adaptive_bpr', 'batch_per_gpu': 262144,
-        'lr': 1e-3, 'bias_lr': 1e-2, 'seed': 2, 'eval_users': 32768,
+        'lr': 1e-3, 'bias_lr': 1e-2, 'seed': 2, 'eval_users': 131072,
     },
     'c5': {
         'key': 'c5',
@@ -59,6 +59,7 @@ WORKLOADS = {
 }
 METRIC = 'MF train interactions/s (fwd+bwd+sparse Adam)'
 NVLINK_GBS_PER_DIR = 900.0
+STRONG_GLOBAL_BATCH = 2097152
 LOG_EVERY = 50          # the reference trainer's default log interval (trainer.py:226)
 
 
@@ -369,8 +370,10 @@ class Job(object):
                                         num_items=padded, **ikw)
             self.data.global_positions = gpos
             self.model = cb.MatrixFactorizationModel(train=self.data, **mkw).to(dev)
+            cap = max(self.B + self.B // 4, (STRONG_GLOBAL_BATCH // world) if w['key'] == 'c3'
+                      else 0)
             self.sharded = D.ShardedMatrixFactorization(self.model, w['num_items'],
-                                                        max_batch=self.B + self.B // 4)
+                                                        max_batch=cap)
         self.opts = self.model.configure_optimizers()
         bsz = min(self.B, (self.data.num_interactions // 2) // 1024 * 1024)
         if world > 1:       # equal batches on every rank
@@ -1005,7 +1008,7 @@ def run_ours(args, rank, world, local_rank, w):
     # with N) has a fixed-work companion
     strong = None
     if not args.no_strong and w['key'] == 'c3':
-        gb = 2097152
+        gb = STRONG_GLOBAL_BATCH
         del job.loader
         job2 = job
         job2.B = gb // world

@@ -438,7 +438,11 @@ def evaluate_sharded(metric_list, local_test, model, k=10, group=None, **kwargs)
     """``evaluate_in_batches`` over user shards: every rank scores its own test users against the
     (gathered) item table; per-metric sums and user counts are all-reduced."""
     from .metrics import evaluate_in_batches
-    n_local = int(len(np.unique(local_test.mat.row)))
+    cache = local_test.__dict__.setdefault('_cmf_n_test_users', {})
+    key = (id(local_test.mat), local_test.mat.nnz)
+    if cache.get('key') != key:
+        cache.update(key=key, n=int(len(np.unique(local_test.mat.row))))
+    n_local = cache['n']
     if n_local:
         res = evaluate_in_batches(metric_list, local_test, model, k=k, verbose=False, **kwargs)
         res = res if isinstance(res, list) else [res]

@@ -131,7 +131,7 @@ def test_forward_y_range_and_autograd_match_oracle():
     np.testing.assert_allclose(out.detach().cpu().numpy(), exp.detach().numpy(), rtol=1e-5)
     for name in ('user_embeddings', 'item_embeddings', 'user_biases', 'item_biases'):
         np.testing.assert_allclose(getattr(model, name).weight.grad.cpu().numpy(),
-                                   getattr(ref, name).weight.grad.numpy(), rtol=1e-4, atol=1e-6,
+                                   getattr(ref, name).weight.grad.numpy(), rtol=1e-5, atol=1e-6,
                                    err_msg=name)
 
 
@@ -200,7 +200,10 @@ def test_golden_implicit_gradients(path):
         grad = (before[k] - t.detach()).cpu().numpy()
         ref = g['step0_grad_' + k]
         scale = np.abs(ref).max() + 1e-12
-        np.testing.assert_allclose(grad, ref, rtol=1e-4, atol=2e-6 * max(1.0, scale), err_msg=k)
+        # the gradient is recovered as before - after of an SGD step with lr = 1: the updated
+        # parameter is rounded to fp32 at ITS magnitude (|p| < 4 here, half an ulp = 2.4e-7), so
+        # every recovered element carries up to that absolute error whatever its own size
+        np.testing.assert_allclose(grad, ref, rtol=1e-5, atol=5e-7 * max(1.0, scale), err_msg=k)
 
 
 def test_selected_negative_indices_bit_exact():
