@@ -60,6 +60,7 @@ WORKLOADS = {
 METRIC = 'MF train interactions/s (fwd+bwd+sparse Adam)'
 NVLINK_GBS_PER_DIR = 900.0
 STRONG_GLOBAL_BATCH = 2097152
+OUT = sys.stdout
 LOG_EVERY = 50          # the reference trainer's default log interval (trainer.py:226)
 
 
@@ -220,6 +221,19 @@ def cpu_train_baseline(w, users, items, steps, warmup, budget_s, threads, want_p
                       f'(workload batch is {full}); unmodified collie 1.3.1 from oracle/_ref: '
                       'CollieMinimalTrainer.fit + ApproximateNegativeSamplingInteractionsDataLoader, '
                       'same tables, distributions and hyper-parameters; torch CPU, all host threads'}
+        # informative extra: the same unmodified reference on this box's GPU with stock torch
+        if torch.cuda.is_available():
+            try:
+                gb = full
+                gs = R.train_seconds(users[:gb * 4].numpy(), items[:gb * 4].numpy(),
+                                     w['num_users'], w['num_items'], w['dim'], w['n_neg'], gb, 3, 1,
+                                     w['lr'], w['bias_lr'], loss=w['loss'], threads=threads, gpus=1)
+                out['reference']['reference_on_this_gpu_stock_torch'] = {
+                    'value': 3 * gb / gs, 'unit': 'interactions/s',
+                    'sample': f'3 steps of {gb} interactions, CollieMinimalTrainer(gpus=1), '
+                              'torch eager kernels'}
+            except Exception as e:  # pragma: no cover
+                out['reference']['reference_on_this_gpu_stock_torch'] = {'error': repr(e)[:200]}
         # second figure: the default loader with exact negative sampling (per-sample Python
         # __getitem__, collie/interactions/datasets.py:399-426), on a small sample
         try:
@@ -315,13 +329,14 @@ def run_reference(args, rank, world, w):
         'cpu_baseline': {k: main[k] for k in ('value', 'unit', 'cores', 'kind', 'sample')},
         'cpu_baseline_port': res.get('port') if main is not res.get('port') else None,
         'default_loader_exact_sampling': main.get('default_loader_exact_sampling'),
+        'reference_on_this_gpu_stock_torch': main.get('reference_on_this_gpu_stock_torch'),
         'e2e': {'value': main['value'], 'unit': 'interactions/s', 'h2d_bytes_per_step': 0,
                 'd2h_bytes_per_step': 0},
         'eval': ({'metric': 'eval users/s MAP@10 + MRR + AUC', 'value': ev.get('value'),
                   'unit': 'users/s', 'cpu_baseline': ev} if ev else None),
         'gpu_launches': 0,
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=OUT, flush=True)
 
 
 def config_dict(w, n_gpus):
@@ -1033,8 +1048,9 @@ def run_ours(args, rank, world, local_rank, w):
         cpu = {k: main[k] for k in ('value', 'unit', 'cores', 'kind', 'sample')}
         if main is not res.get('port') and res.get('port'):
             cpu['port'] = {k: res['port'][k] for k in ('value', 'unit', 'cores', 'kind', 'sample')}
-        if main.get('default_loader_exact_sampling'):
-            cpu['default_loader_exact_sampling'] = main['default_loader_exact_sampling']
+        for extra in ('default_loader_exact_sampling', 'reference_on_this_gpu_stock_torch'):
+            if main.get(extra):
+                cpu[extra] = main[extra]
 
     if rank == 0:
         line = {
@@ -1061,7 +1077,7 @@ def run_ours(args, rank, world, local_rank, w):
             'clocks': clk, 'final_loss': float(loss), 'parity': parity, 'eval': eval_info,
             'fixed_global_work': strong,
         }
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=OUT, flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -1085,10 +1101,11 @@ def main():
     w = WORKLOADS[args.config]
     # stdout carries the JSON line and nothing else: libraries that print from C (NCCL's version
     # banner) are sent to stderr by pointing fd 1 there and keeping the real stdout for the line
+    # (and Python-level prints of the reference arm: sys.stdout now writes to fd 1 = stderr)
+    global OUT
     sys.stdout.flush()
-    real_stdout = os.fdopen(os.dup(1), 'w')
+    OUT = os.fdopen(os.dup(1), 'w')
     os.dup2(2, 1)
-    sys.stdout = real_stdout
     if args.impl == 'reference':
         run_reference(args, rank, world, w)
         return

@@ -38,7 +38,10 @@ class cmf_peers_t(C.Structure):
                 ('GI', C.c_void_p * CMF_MAX_PEERS), ('gbi', C.c_void_p * CMF_MAX_PEERS),
                 ('flag', C.c_void_p * CMF_MAX_PEERS),
                 ('mc_I', C.c_void_p), ('mc_bi', C.c_void_p), ('mc_GI', C.c_void_p),
-                ('mc_gbi', C.c_void_p), ('mc_flag', C.c_void_p)]
+                ('mc_gbi', C.c_void_p), ('mc_flag', C.c_void_p),
+                ('pad', C.c_void_p * CMF_MAX_PEERS), ('epoch', C.c_uint32),
+                ('reserved2', C.c_uint32), ('clear_ptr', C.c_void_p),
+                ('clear_bytes', C.c_size_t)]
 
 
 class cmf_step_t(C.Structure):
@@ -60,6 +63,7 @@ class cmf_step_t(C.Structure):
         ('pos_scores_out', C.c_void_p), ('neg_scores_out', C.c_void_p),
         ('workspace', C.c_void_p), ('workspace_bytes', C.c_size_t),
         ('B_global', C.c_int64), ('skip_item_update', C.c_int32), ('num_items_logical', C.c_int32),
+        ('item_grads_ready_event', C.c_void_p),
     ]
 
 
@@ -118,6 +122,7 @@ SIGNATURES = {
                                                        C.c_void_p]),
     'cmf_item_exchange_update': (C.c_int, [C.POINTER(cmf_peers_t)] + [C.c_void_p] * 4 +
                                  [C.POINTER(cmf_opt_t), C.POINTER(cmf_opt_t), C.c_void_p]),
+    'cmf_exchange_pad_bytes': (C.c_size_t, []),
     'cmf_eval_workspace_bytes': (C.c_size_t, [C.c_int64, C.c_int64, C.c_int32, C.c_int32,
                                               C.c_int32]),
     'cmf_eval_tile': (C.c_int, [C.POINTER(cmf_eval_t), C.c_void_p]),

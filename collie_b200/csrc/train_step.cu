@@ -760,6 +760,9 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
     if (g_prof_on) CMF_CUDA(cudaEventRecord(prof.e[2], s));
   }
   if (g_prof_on) CMF_CUDA(cudaEventRecord(prof.e[3], s));
+  // the item-side accumulators are complete from here on
+  if (a->item_grads_ready_event)
+    CMF_CUDA(cudaEventRecord((cudaEvent_t)a->item_grads_ready_event, s));
 
   // ---- finish items (always) and the users that were not finished in place
   if (p.train) {

@@ -114,7 +114,13 @@ class ShardedMatrixFactorization(object):
         self._max_batch, self._max_negatives = max_batch, max_negatives
         self._p2p = None
         import os
-        self._fence_kind = os.environ.get('CMF_FENCE', 'symm')     # 'symm' | 'nccl'
+        # how the ranks rendezvous around the exchange kernel: 'kernel' = barriers inside the
+        # kernel itself (signal pad in symmetric memory), on a side stream next to the step's
+        # remaining user-row updates; 'symm' / 'nccl' = a fence before and after it on the main
+        # stream (symmetric-memory barrier kernel / one-element all-reduce)
+        self._fence_kind = os.environ.get('CMF_FENCE', 'kernel')
+        if self._fence_kind not in ('kernel', 'symm', 'nccl'):
+            raise ValueError("CMF_FENCE must be 'kernel', 'symm' or 'nccl'")
         if multicast not in ('auto', True, False):
             raise ValueError("multicast must be 'auto', True or False")
         if multicast == 'auto' and os.environ.get('CMF_MULTICAST', '1') == '0':
@@ -177,6 +183,21 @@ class ShardedMatrixFactorization(object):
                          'bi': [int(p) for p in hb.buffer_ptrs], 'handles': [hI, hb]}
             self._tick = torch.zeros(1, dtype=torch.float32, device=self.I_full.device)
             self._p2p['multicast'] = False
+            # signal pad of the in-kernel barriers, the stream the exchange runs on and the events
+            # that tie it to the main stream
+            pad = symm.empty(int(_abi.lib().cmf_exchange_pad_bytes()) // 4, dtype=torch.int32,
+                             device=self.I_full.device)
+            pad.zero_()
+            hp = symm.rendezvous(pad, grp)
+            self._p2p.update(pad=pad, pad_ptrs=[int(p) for p in hp.buffer_ptrs])
+            self._p2p['handles'].append(hp)
+            dev = self.I_full.device
+            self._xstream = torch.cuda.Stream(dev, priority=-1)
+            self._ev_grads, self._ev_done = torch.cuda.Event(), torch.cuda.Event()
+            self._ev_grads.record(torch.cuda.current_stream(dev))
+            self._ev_done.record(torch.cuda.current_stream(dev))
+            torch.cuda.synchronize(dev)
+            hp.barrier(channel=0)        # every rank's pad is zero before anybody signals
         except Exception as e:
             if self.exchange == 'p2p':
                 raise _abi.CmfError(f'p2p exchange unavailable: {e}')
@@ -237,7 +258,8 @@ class ShardedMatrixFactorization(object):
             peers.flag[q] = self._p2p['flag'][q]
         # NVSwitch multicast views (NVLS), when the allocator made them and the accumulators sit
         # at the same offset on every rank
-        mc = [int(getattr(h_, 'multicast_ptr', 0) or 0) for h_ in self._p2p['handles']]
+        hI, hb = self._p2p['handles'][0], self._p2p['handles'][1]
+        mc = [int(getattr(h_, 'multicast_ptr', 0) or 0) for h_ in (hI, hb, hw)]
         same = all(bool(torch.equal(all_offs[q], offs)) for q in range(self.world))
         if self._multicast is True and not (all(mc) and same):
             raise RuntimeError('NVSwitch multicast addresses are not available for the symmetric '
@@ -251,6 +273,16 @@ class ShardedMatrixFactorization(object):
             peers.mc_gbi = mc[2] + int(offs[1])
             peers.mc_flag = mc[2] + int(offs[2])
             self._p2p['multicast'] = True
+        if self._fence_kind == 'kernel':
+            for q in range(self.world):
+                peers.pad[q] = self._p2p['pad_ptrs'][q]
+            # this rank's own accumulators: item_flag, GI, gbi are the first three areas of the
+            # workspace (cmf_train_workspace_items), cleared as one span
+            lo = min(int(offs[0]), int(offs[1]), int(offs[2]))
+            hi = int(offs[1]) + 4 * int(h.num_items)
+            hi += (-(hi - lo)) % 16      # (the areas are 256-byte aligned: the slack is unused)
+            peers.clear_ptr = base + lo
+            peers.clear_bytes = hi - lo
         self._p2p['peers'] = peers
 
     def _fence(self):
@@ -286,38 +318,67 @@ class ShardedMatrixFactorization(object):
                 f'batch of {B} x {n_neg} negatives exceeds the symmetric training workspace '
                 f'({cap_b} x {cap_n}); pass max_batch / max_negatives to '
                 'ShardedMatrixFactorization')
+        in_kernel = self._fence_kind == 'kernel'
         loss = m.fused_step(batch, optimizers=optimizers, interactions=interactions, epoch=epoch,
                             global_batch=int(global_batch), skip_item_update=True,
-                            num_items_logical=self.true_num_items)
+                            num_items_logical=self.true_num_items,
+                            item_grads_event=self._ev_grads if in_kernel else None)
         if m._workspace is not self._p2p['ws']:
             raise _abi.CmfError('the model replaced its symmetric training workspace')
-        ev = None
-        if self.timing is not None:
-            ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
-            ev[0].record()
-        # every rank's accumulators are complete ...
-        if reduce_loss:
-            dist.all_reduce(loss, group=self.group)     # (doubles as the rendezvous)
-        else:
-            self._fence()
-        if ev:
-            ev[1].record()
         self._step += 1
         g_main, g_bias = main.param_groups[0], bias.param_groups[0]
         o = _abi.make_opt(main.rule, g_main['lr'], self._step, g_main.get('betas', (0.9, 0.999)),
                           g_main.get('eps', 1e-8), g_main.get('weight_decay', 0.0))
         ob = _abi.make_opt(bias.rule, g_bias['lr'], self._step, g_bias.get('betas', (0.9, 0.999)),
                            g_bias.get('eps', 1e-8), g_bias.get('weight_decay', 0.0))
-        _abi.check(_abi.lib().cmf_item_exchange_update(
-            _abi.C.byref(self._p2p['peers']), _abi.ptr(st['m']), _abi.ptr(st['v']),
-            _abi.ptr(st['bm']), _abi.ptr(st['bv']), o, ob, _abi.stream_ptr(self.I_full.device)),
-            'cmf_item_exchange_update')
+        peers = self._p2p['peers']
+        dev = self.I_full.device
+        ev = None
+        if self.timing is not None:
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+
+        def launch(stream_ptr):
+            _abi.check(_abi.lib().cmf_item_exchange_update(
+                _abi.C.byref(peers), _abi.ptr(st['m']), _abi.ptr(st['v']), _abi.ptr(st['bm']),
+                _abi.ptr(st['bv']), o, ob, stream_ptr), 'cmf_item_exchange_update')
+
+        if in_kernel:
+            # ONE kernel, entry and exit barriers inside, on its own stream: it starts when this
+            # rank's item-side accumulators are complete and runs next to the step's remaining
+            # user-row updates; the next step's forward waits for it
+            peers.epoch = self._step & 0xFFFFFFFF or 1
+            main_stream = torch.cuda.current_stream(dev)
+            with torch.cuda.stream(self._xstream):
+                self._xstream.wait_event(self._ev_grads)
+                if ev:
+                    ev[0].record()
+                    ev[1].record()
+                launch(self._xstream.cuda_stream)
+                if ev:
+                    ev[2].record()
+                    ev[3].record()
+                self._ev_done.record(self._xstream)
+            if reduce_loss:
+                dist.all_reduce(loss, group=self.group)
+            main_stream.wait_event(self._ev_done)
+        else:
+            if ev:
+                ev[0].record()
+            # every rank's accumulators are complete ...
+            if reduce_loss:
+                dist.all_reduce(loss, group=self.group)     # (doubles as the rendezvous)
+            else:
+                self._fence()
+            if ev:
+                ev[1].record()
+            launch(_abi.stream_ptr(dev))
+            if ev:
+                ev[2].record()
+            # ... and every rank's table copy is complete before anybody's next step reads it
+            self._fence()
+            if ev:
+                ev[3].record()
         if ev:
-            ev[2].record()
-        # ... and every rank's table copy is complete before anybody's next step reads it
-        self._fence()
-        if ev:
-            ev[3].record()
             self.timing.append(ev)
         return loss
 

@@ -450,7 +450,7 @@ class MatrixFactorizationModel(torch.nn.Module):
 
     def fused_step(self, batch, optimizers=None, train=True, interactions=None, epoch=0,
                    outputs=None, users_sorted=False, global_batch=0, skip_item_update=False,
-                   num_items_logical=0, epoch_batch_size=None):
+                   num_items_logical=0, epoch_batch_size=None, item_grads_event=None):
         """One step through ``cmf_train_step``; returns the loss as a 0-d device tensor.
 
         ``optimizers``: what ``configure_optimizers`` returned (one optimizer, or [main, bias]).
@@ -462,7 +462,8 @@ class MatrixFactorizationModel(torch.nn.Module):
         losses come back as a 1-d device tensor.
         ``global_batch`` / ``skip_item_update``: multi-GPU hooks (``collie_b200.distributed``): the
         loss is a mean over the global batch, and the item-row gradients stay in the workspace
-        for the caller to reduce across ranks.
+        for the caller to reduce across ranks; ``item_grads_event`` (a ``torch.cuda.Event`` that
+        has been recorded once) is recorded again as soon as those gradients are complete.
         """
         if self._loss_name is None:
             raise _abi.CmfError('a custom loss callable cannot run inside the fused step; use one '
@@ -582,6 +583,8 @@ class MatrixFactorizationModel(torch.nn.Module):
         a.B_global = int(global_batch)
         a.skip_item_update = 1 if skip_item_update else 0
         a.num_items_logical = int(num_items_logical)
+        if item_grads_event is not None:
+            a.item_grads_ready_event = int(item_grads_event.cuda_event)
         if epoch_batch_size is not None:
             rc = _abi.lib().cmf_train_epoch(_abi.C.byref(a), n_total, loss_out.data_ptr(),
                                             _abi.stream_ptr(self.device))

@@ -141,6 +141,11 @@ typedef struct {
   /* number of real items when the item table is padded to a multiple of the rank count: negatives
    * are drawn from [0, num_items_logical) and WARP weights use it (0 = num_items) */
   int32_t num_items_logical;
+  /* optional cudaEvent_t recorded on the stream once the item-side accumulators of this step are
+   * complete (after k_bwd_update / the fused kernel, before the row-update kernel): with
+   * skip_item_update a caller can start the exchange on another stream while the remaining
+   * user-row updates run */
+  void *item_grads_ready_event;
 } cmf_step_t;
 
 /* scratch for cmf_train_step; depends only on the table shapes and the largest batch */
@@ -291,7 +296,21 @@ typedef struct cmf_peers_t {
    * switch) and the stores multimem.st, so the kernel's NVLink traffic does not grow with world */
   float *mc_I, *mc_bi, *mc_GI, *mc_gbi;
   int32_t *mc_flag;
+  /* Rendezvous inside the kernel (all NULL / 0: the caller fences, and the owner clears the
+   * accumulators it consumed on every rank). pad[q] = rank q's signal pad, cmf_exchange_pad_bytes()
+   * bytes of zero-initialised peer-mapped memory; epoch = 1, 2, 3, ... one value per call, the
+   * same on every rank. The kernel then (1) waits until every rank has entered it -- so it must
+   * be stream-ordered after this rank's cmf_train_step(skip_item_update) --, (2) leaves only when
+   * every rank's stores have landed everywhere, and (3) clears [clear_ptr, clear_ptr +
+   * clear_bytes) = this rank's own accumulators (item_flag .. gbi of its workspace) itself. Its
+   * grid is sized to be resident at once; a peer that never arrives makes it trap after 20 s
+   * instead of hanging the GPU. */
+  uint32_t *pad[CMF_MAX_PEERS];
+  uint32_t epoch, reserved2;
+  void *clear_ptr;
+  size_t clear_bytes;
 } cmf_peers_t;
+CMF_API size_t cmf_exchange_pad_bytes(void);
 CMF_API int cmf_item_exchange_update(const cmf_peers_t *peers, float *M, float *V, float *bM, float *bV,
                              const cmf_opt_t *opt, const cmf_opt_t *bias_opt, void *stream);
 

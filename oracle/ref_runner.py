@@ -59,11 +59,13 @@ def _implicit_data(collie, users, items, num_users, num_items, n_neg, exact):
 
 def train_seconds(users, items, num_users, num_items, dim, n_neg, batch, steps, warmup, lr,
                   bias_lr, loss='bpr', optimizer='sparse_adam', sparse=True, loader='approximate',
-                  threads=None, seed=0):
+                  threads=None, seed=0, gpus=0):
     """Seconds the reference's ``CollieMinimalTrainer.fit`` takes for ``steps`` batches of
     ``batch`` interactions (one epoch over ``steps * batch`` interactions), after a warm-up fit of
     ``warmup`` batches on the same model. ``users`` / ``items`` must hold at least
-    ``(steps + warmup) * batch`` entries."""
+    ``(steps + warmup) * batch`` entries. ``gpus=0`` keeps the reference on the host cores (its
+    trainer moves the model to a GPU by itself when one is visible, trainer.py:234-237);
+    ``gpus=1`` is the reference's stock-torch GPU path, timed as an informative extra."""
     import numpy as np
     import torch
     collie = import_reference()
@@ -95,10 +97,12 @@ def train_seconds(users, items, num_users, num_items, dim, n_neg, batch, steps, 
 
     def fit(train_loader):
         model.train_loader = train_loader
-        trainer = CollieMinimalTrainer(model, max_epochs=1, logger=None, verbosity=0,
+        trainer = CollieMinimalTrainer(model, max_epochs=1, gpus=gpus, logger=None, verbosity=0,
                                        enable_model_summary=False, early_stopping_patience=None)
         t0 = time.perf_counter()
         trainer.fit(model)
+        if gpus:
+            torch.cuda.synchronize()
         return time.perf_counter() - t0
 
     if warmup > 0:
