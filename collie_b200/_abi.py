@@ -79,6 +79,7 @@ class cmf_eval_t(C.Structure):
         ('n_before_best', C.c_void_p), ('best_score', C.c_void_p), ('best_id', C.c_void_p),
         ('auc_pairs', C.c_void_p), ('workspace', C.c_void_p), ('workspace_bytes', C.c_size_t),
         ('scores_in', C.c_void_p), ('reuse_item_prep', C.c_int32), ('reserved_', C.c_int32),
+        ('tc_status', C.c_void_p),
     ]
 
 
@@ -126,6 +127,7 @@ SIGNATURES = {
     'cmf_eval_workspace_bytes': (C.c_size_t, [C.c_int64, C.c_int64, C.c_int32, C.c_int32,
                                               C.c_int32]),
     'cmf_eval_tile': (C.c_int, [C.POINTER(cmf_eval_t), C.c_void_p]),
+    'cmf_eval_tc_info': (C.c_int, [C.c_int32, C.POINTER(C.c_double)]),
     'cmf_eval_tile_noalloc': (C.c_int, [C.POINTER(cmf_eval_t), C.c_void_p]),
     'cmf_score_tile': (C.c_int, [C.c_void_p] * 4 + [C.c_int32, C.c_void_p, C.c_int64, C.c_int64,
                                                    C.c_void_p, C.c_void_p]),

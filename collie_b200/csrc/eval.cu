@@ -211,6 +211,11 @@ struct RankDev {
   int32_t* best_id;
   double* auc_pairs;
   float* sig_scratch;  // [total targets of the tile], same offsets as tgt_items (minus indptr[0])
+  // optional indirection (the tensor-core path's hand-over): score row b belongs to user
+  // row_map[b]; only the first min(*row_count, row_cap) rows exist
+  const int32_t* row_map;
+  const int32_t* row_count;
+  int row_cap;
 };
 
 constexpr int kListK = 12;   // k up to which the one-pass ranking keeps per-thread lists
@@ -229,8 +234,13 @@ k_rank_rows(const RankDev p) {
   __shared__ float s_ls[kListK][256];   // [rank in the thread's list][thread]: conflict-free
   __shared__ int s_li[kListK][256];
   const int tid = threadIdx.x;
-  const int r = blockIdx.x;
-  const float* row = p.S + (int64_t)r * p.ld;
+  int r = blockIdx.x;
+  const float* row = p.S + (int64_t)blockIdx.x * p.ld;
+  if (p.row_map) {
+    const int n_rows = *p.row_count < p.row_cap ? *p.row_count : p.row_cap;
+    if ((int)blockIdx.x >= n_rows) return;
+    r = p.row_map[blockIdx.x];
+  }
   const int64_t t0 = p.tgt_indptr ? p.tgt_indptr[r] : 0, t1 = p.tgt_indptr ? p.tgt_indptr[r + 1] : 0;
   const int n_tgt = (int)(t1 - t0);
   const int32_t* tgt = p.tgt_items + t0;
@@ -401,6 +411,28 @@ static void launch_score_tile(const float* U, const float* I, const float* bu, c
   }
 }
 
+static RankDev rank_args(const cmf_eval_t* a, const float* S, float* sig) {
+  RankDev p{};
+  p.S = S; p.ld = a->num_items_shard; p.n_items = a->num_items_shard; p.item_offset = a->item_offset;
+  p.k = a->k; p.tgt_indptr = a->tgt_indptr; p.tgt_items = a->tgt_items;
+  p.want_mrr = a->want_mrr; p.want_auc = a->want_auc;
+  p.ext_best_score = a->ext_best_score; p.ext_best_id = a->ext_best_id;
+  p.topk_ids = a->topk_ids; p.topk_scores = a->topk_scores; p.ap = a->ap;
+  p.n_before_best = a->n_before_best; p.best_score = a->best_score; p.best_id = a->best_id;
+  p.auc_pairs = a->auc_pairs; p.sig_scratch = sig;
+  return p;
+}
+
+int launch_rank_rows_mapped(const cmf_eval_t* a, const float* scores, float* sig_scratch,
+                            const int32_t* row_map, const int32_t* row_count, int row_cap,
+                            cudaStream_t s) {
+  RankDev p = rank_args(a, scores, sig_scratch);
+  p.row_map = row_map; p.row_count = row_count; p.row_cap = row_cap;
+  k_rank_rows<<<(unsigned)row_cap, 256, 0, s>>>(p);
+  CMF_LAUNCH_CHECK();
+  return CMF_OK;
+}
+
 }  // namespace cmf
 
 using namespace cmf;
@@ -459,14 +491,7 @@ extern "C" int cmf_eval_tile(const cmf_eval_t* a, void* stream) {
     CMF_LAUNCH_CHECK();
     S = Sw;
   }
-  RankDev p{};
-  p.S = S; p.ld = a->num_items_shard; p.n_items = a->num_items_shard; p.item_offset = a->item_offset;
-  p.k = a->k; p.tgt_indptr = a->tgt_indptr; p.tgt_items = a->tgt_items;
-  p.want_mrr = a->want_mrr; p.want_auc = a->want_auc;
-  p.ext_best_score = a->ext_best_score; p.ext_best_id = a->ext_best_id;
-  p.topk_ids = a->topk_ids; p.topk_scores = a->topk_scores; p.ap = a->ap;
-  p.n_before_best = a->n_before_best; p.best_score = a->best_score; p.best_id = a->best_id;
-  p.auc_pairs = a->auc_pairs; p.sig_scratch = sig;
+  const RankDev p = rank_args(a, S, sig);
   k_rank_rows<<<(unsigned)a->n_users_tile, 256, 0, s>>>(p);
   CMF_LAUNCH_CHECK();
   return CMF_OK;

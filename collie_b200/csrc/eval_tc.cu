@@ -1,20 +1,27 @@
 // Evaluation, tensor-core path (precision = 1): S = U_tile . I^T as tcgen05 GEMM tiles fed by TMA,
-// fp32 accumulators in TMEM, and the per-user top-k (+ the MRR counter) in the epilogue, so the
-// score matrix never exists in memory.
+// fp32 accumulators in TMEM, and the per-user ranking in the epilogue, so the score matrix never
+// exists in memory. The tensor cores SELECT, fp32 decides: the GEMM's scores carry a stated error
+// bound, the epilogue keeps every item that could be in the top-k (and every item whose order
+// against the best target is in doubt), and a small kernel re-scores exactly those in fp32 in the
+// exact path's own summation order (eval.cu). Ids, scores, AP@k and the MRR counter therefore
+// equal precision = 0 bit for bit on arbitrary fp32 weights; users for which the bound cannot
+// separate the candidates (more near-ties than the lists hold) are re-ranked by the exact path.
 //
 // Reference: collie/metrics.py get_preds :77-107 (Bu * n_items independent gather-dots there),
 // mapk :144-198, mrr :201-240.
 //
-// fp32 parity on bf16 tensor cores: every fp32 value x is split as hi = bf16(x), lo = bf16(x - hi)
-// and the GEMM runs over the concatenated K axis  A' = [Ah | Ah | Al],  B' = [Bh | Bl | Bh]
-// (K' = 3 D + 4 bias slots), i.e. S = Ah.Bh + Ah.Bl + Al.Bh with fp32 accumulation; the dropped Al.Bl term is
-// < 2^-16 relative. Values that are exactly representable in bf16 (the exact-arithmetic parity
-// fixture) give bit-exact scores.
+// Operands: x = hi + lo with hi = bf16(x), lo = bf16(x - hi).
+//   terms = 1 (top-k / MAP@k only):  A' = [Uh | bu_hi, bu_lo, 1, 1],  B' = [Ih | 1, 1, bi_hi, bi_lo]
+//     K' = D + 4: one bf16 product per element. |S~ - S| <= c1 |u| |i| + 2^-15 (|bu| + |bi|),
+//     c1 = 4.1e-3 (2^-8 for the two roundings, Cauchy-Schwarz over d, plus both accumulations).
+//   terms = 3 (with the MRR counter): A' = [Uh | Uh | Ul | ...], B' = [Ih | Il | Ih | ...],
+//     K' = 3 D + 4, S~ = Uh.Ih + Uh.Il + Ul.Ih: c3 = 8e-5 (3 * 2^-18 for the dropped terms, the
+//     rest for fp32 accumulation of 3 D + 4 products), a band of a few items per user.
+//   Per user the margin uses the largest item norm of the shard: E_u = c |u| max|i| + ...
 //
 // The (128-user tile, 256-item tile) pairs are cut into equal contiguous chunks, one per CTA, one
-// CTA per SM: a CTA walks its chunk as segments that each lie inside one user tile, leaves every
-// segment's top-k candidates and counters in scratch, and k_tc_merge combines the segments of a
-// user in canonical order (score desc, id asc).
+// CTA per SM: a CTA walks its chunk as segments that each lie inside one user tile and leaves every
+// segment's best KL > k candidates (per column half) in a scratch slot.
 //   warp 0      TMA producer: A' once per segment (resident), then B' K-blocks through a 3-stage mbarrier ring
 //   warp 1      MMA issuer: tcgen05.mma.cta_group::1.kind::f16, M = 128, N = 256, K = 16 per
 //               instruction, two accumulators in TMEM (all 512 columns) so tile t+1 is being multiplied
@@ -23,8 +30,11 @@
 //   warps 4..11 epilogue, two warps per scheduler (each takes half of a tile's columns):
 //               tcgen05.ld 32x32b (thread = user row); the biases are folded into the GEMM (four
 //               extra K slots), so the accumulator IS the score: a branch-free pass builds 32-bit
-//               predicate masks per 32 columns (beats the row's k-th best / beats the best
-//               target), then lane-parallel inserts into an unsorted per-row list in shared memory
+//               predicate masks per 32 columns (beats the row's KL-th best / surely beats the best
+//               target / cannot be told from it), then lane-parallel inserts into a sorted list
+//               held in registers
+// k_tc_finish (one warp per user): k-th best of the union of the slots' lists, the proof that
+// nothing outside the lists can reach the top-k, exact re-scoring, exact top-k, AP@k, MRR counter.
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -38,7 +48,8 @@ constexpr int TC_BM = 128;        // users per CTA
 constexpr int TC_BN = 256;        // items per MMA tile (one instruction: M = 128, N = 256, K = 16)
 constexpr int TC_BK = 64;         // bf16 per K block = one 128-byte swizzle row
 constexpr int TC_STAGES = 3;
-constexpr int TC_MAXK = 16;       // top-k list length supported by the epilogue
+constexpr int TC_MAXK = 16;       // largest k
+constexpr int TC_BCAP = 16;       // band entries kept per (user, slot) for the MRR counter
 constexpr int TC_A_BYTES = TC_BM * TC_BK * 2;   // 16 KB: one K-block of the user tile
 constexpr int TC_B_BYTES = TC_BN * TC_BK * 2;   // 32 KB: one K-block of an item tile
 
@@ -187,23 +198,31 @@ __device__ __forceinline__ void split_bf16(float x, __nv_bfloat16& hi, __nv_bflo
   lo = __float2bfloat16_rn(x - __bfloat162float(hi));
 }
 
-// rows of `src` (optionally gathered through `ids`) -> bf16 rows of length Kp:
-//   items: [hi | lo | hi | 1, 1, bi_hi, bi_lo | 0...]   users: [hi | hi | lo | bu_hi, bu_lo, 1, 1 | 0...]
+// Error-bound coefficients (see the file header). Kept generous: a bound that is too large only
+// sends a few more items to the exact re-scoring, one that is too small breaks parity.
+constexpr float kTcC1 = 4.1e-3f;
+constexpr float kTcC3 = 8.0e-5f;
+constexpr float kTcCBias = 3.0517578125e-5f;   // 2^-15
+
+// rows of `src` (optionally gathered through `ids`) -> bf16 rows of length Kp, T = 1 or 3 terms:
+//   T = 3  items: [hi | lo | hi | 1, 1, bi_hi, bi_lo | 0...]   users: [hi | hi | lo | bu_hi, bu_lo, 1, 1 | 0...]
+//   T = 1  items: [hi | 1, 1, bi_hi, bi_lo | 0...]             users: [hi | bu_hi, bu_lo, 1, 1 | 0...]
 // so the GEMM yields  <u, i> + bu + bi  directly (the biases are split like the rows). Rows
-// >= n_rows are zero.
+// >= n_rows are zero. Also the row's L2 norm and |bias| (users: per row; items: the maximum over
+// the shard, by atomicMax on the bit pattern of a non-negative float).
 // One warp per row; a lane produces two adjacent bf16 at a time (one 4-byte store, 128 bytes per
 // warp), the row id is read once per row.
 __device__ __forceinline__ __nv_bfloat16 tc_split_elem(const float* __restrict__ srow, float b,
-                                                       int c, int D, int users) {
-  if (c < 3 * D) {
+                                                       int c, int D, int users, int T) {
+  if (c < T * D) {
     const int seg = c / D, d = c - seg * D;
     __nv_bfloat16 hi, lo;
     split_bf16(srow[d], hi, lo);
-    const bool want_lo = users ? (seg == 2) : (seg == 1);
+    const bool want_lo = T == 3 && (users ? (seg == 2) : (seg == 1));
     return want_lo ? lo : hi;
   }
-  if (c < 3 * D + 4) {
-    const int q = c - 3 * D;
+  if (c < T * D + 4) {
+    const int q = c - T * D;
     __nv_bfloat16 hi, lo;
     split_bf16(b, hi, lo);
     const bool own = users ? (q < 2) : (q >= 2);     // own bias in two slots, 1.0 in the others
@@ -215,7 +234,8 @@ __device__ __forceinline__ __nv_bfloat16 tc_split_elem(const float* __restrict__
 __global__ void __launch_bounds__(256)
 k_tc_split(const float* __restrict__ src, const float* __restrict__ bias,
            const int32_t* __restrict__ ids, int64_t row_offset, int64_t n_rows, int64_t n_rows_pad,
-           int D, int Kp, int users, __nv_bfloat16* __restrict__ out) {
+           int D, int Kp, int users, int T, __nv_bfloat16* __restrict__ out,
+           float* __restrict__ row_norm, float* __restrict__ row_absb, uint32_t* __restrict__ stats) {
   const int lane = threadIdx.x & 31;
   const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -223,37 +243,85 @@ k_tc_split(const float* __restrict__ src, const float* __restrict__ bias,
     __nv_bfloat162* orow = reinterpret_cast<__nv_bfloat162*>(out + r * Kp);   // Kp is even
     if (r >= n_rows) {
       for (int c2 = lane; c2 < Kp / 2; c2 += 32) orow[c2] = __floats2bfloat162_rn(0.f, 0.f);
+      if (lane == 0 && row_norm) { row_norm[r] = 0.f; row_absb[r] = 0.f; }
       continue;
     }
     const int64_t row = ids ? (int64_t)ids[r] : row_offset + r;
     const float* srow = src + row * D;
     const float b = bias[row];
+    float ss = 0.f;
     if ((D & 1) == 0 && (reinterpret_cast<uintptr_t>(src) & 7) == 0) {
-      // each value is split once and stored to its three segments
+      // each value is split once and stored to its segments
       for (int d2 = lane; d2 < D / 2; d2 += 32) {
         const float2 x = *reinterpret_cast<const float2*>(srow + 2 * d2);
+        ss = fmaf(x.x, x.x, ss);
+        ss = fmaf(x.y, x.y, ss);
         __nv_bfloat162 hi, lo;
         split_bf16(x.x, hi.x, lo.x);
         split_bf16(x.y, hi.y, lo.y);
         orow[d2] = hi;
-        orow[D / 2 + d2] = users ? hi : lo;
-        orow[D + d2] = users ? lo : hi;
+        if (T == 3) {
+          orow[D / 2 + d2] = users ? hi : lo;
+          orow[D + d2] = users ? lo : hi;
+        }
       }
-      for (int c2 = 3 * D / 2 + lane; c2 < Kp / 2; c2 += 32) {   // bias slots + zero tail
+      for (int c2 = T * D / 2 + lane; c2 < Kp / 2; c2 += 32) {   // bias slots + zero tail
         __nv_bfloat162 v;
-        v.x = tc_split_elem(srow, b, 2 * c2, D, users);
-        v.y = tc_split_elem(srow, b, 2 * c2 + 1, D, users);
+        v.x = tc_split_elem(srow, b, 2 * c2, D, users, T);
+        v.y = tc_split_elem(srow, b, 2 * c2 + 1, D, users, T);
         orow[c2] = v;
       }
-      continue;
+    } else {
+      for (int d = lane; d < D; d += 32) ss = fmaf(srow[d], srow[d], ss);
+      for (int c2 = lane; c2 < Kp / 2; c2 += 32) {
+        __nv_bfloat162 v;
+        v.x = tc_split_elem(srow, b, 2 * c2, D, users, T);
+        v.y = tc_split_elem(srow, b, 2 * c2 + 1, D, users, T);
+        orow[c2] = v;
+      }
     }
-    for (int c2 = lane; c2 < Kp / 2; c2 += 32) {
-      __nv_bfloat162 v;
-      v.x = tc_split_elem(srow, b, 2 * c2, D, users);
-      v.y = tc_split_elem(srow, b, 2 * c2 + 1, D, users);
-      orow[c2] = v;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    if (lane == 0) {
+      const float nrm = sqrtf(ss) * 1.00002f;     // (fp32 sum of squares: D * 2^-24 relative)
+      if (row_norm) { row_norm[r] = nrm; row_absb[r] = fabsf(b); }
+      if (stats) {
+        atomicMax(stats + 0, __float_as_uint(nrm));
+        atomicMax(stats + 1, __float_as_uint(fabsf(b)));
+      }
     }
   }
+}
+
+// per-user margin E_u = c |u| max|i| + 2^-15 (|bu| + max|bi|)
+__global__ void k_tc_margin(const float* __restrict__ unorm, const float* __restrict__ uabsb,
+                            const uint32_t* __restrict__ stats, float c, int64_t n,
+                            float* __restrict__ E) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  const float imax = __uint_as_float(stats[0]), bmax = __uint_as_float(stats[1]);
+  E[r] = c * unorm[r] * imax + kTcCBias * (uabsb[r] + bmax) + 1e-37f;
+}
+
+// the exact path's score of one (user, item) pair: fmaf over d ascending from 0, then + bu, + bi
+// (k_score_tile / k_score_tile_128 in eval.cu): same bits
+__device__ __forceinline__ float tc_exact_score(const float* __restrict__ urow,
+                                                const float* __restrict__ irow, int D, float ub,
+                                                float ib) {
+  float acc = 0.f;
+  if ((D & 3) == 0 && ((reinterpret_cast<uintptr_t>(urow) | reinterpret_cast<uintptr_t>(irow)) & 15) == 0) {
+    for (int d = 0; d < D; d += 4) {
+      const float4 a = *reinterpret_cast<const float4*>(urow + d);
+      const float4 b = *reinterpret_cast<const float4*>(irow + d);
+      acc = fmaf(a.x, b.x, acc);
+      acc = fmaf(a.y, b.y, acc);
+      acc = fmaf(a.z, b.z, acc);
+      acc = fmaf(a.w, b.w, acc);
+    }
+  } else {
+    for (int d = 0; d < D; ++d) acc = fmaf(urow[d], irow[d], acc);
+  }
+  return acc + ub + ib;
 }
 
 // exact fp32 score of every target of every user of the tile; keeps the best (score desc, id asc)
@@ -268,17 +336,21 @@ k_tc_target_best(const float* __restrict__ U, const float* __restrict__ I,
   const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (r >= n_users) return;
   const int64_t u = user_ids[r];
+  const float ub = bu[u];
   float bs = -INFINITY;
   int bid = -1;
-  for (int64_t t = tgt_indptr[r]; t < tgt_indptr[r + 1]; ++t) {
+  // lanes take targets side by side; every score is one lane's sequential sum (the exact order)
+  for (int64_t t = tgt_indptr[r] + lane; t < tgt_indptr[r + 1]; t += 32) {
     const int id = tgt_items[t];
     if (id < item_lo || id >= item_hi) continue;
-    float acc = 0.f;
-    for (int d = lane; d < D; d += 32) acc = fmaf(U[u * D + d], I[(int64_t)id * D + d], acc);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    const float s = acc + bu[u] + bi[id];
+    const float s = tc_exact_score(U + u * D, I + (int64_t)id * D, D, ub, bi[id]);
     if (bid < 0 || s > bs || (s == bs && id < bid)) { bs = s; bid = id; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float os = __shfl_xor_sync(0xffffffffu, bs, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bid, o);
+    if (oi >= 0 && (bid < 0 || os > bs || (os == bs && oi < bid))) { bs = os; bid = oi; }
   }
   if (lane == 0) { best_s[r] = bs; best_id[r] = bid; }
 }
@@ -289,11 +361,14 @@ struct TcParams {
   int last_steps;        // K = 16 steps of the last K block that hold data (1..4)
   int64_t chunk, total_work;   // tiles per CTA / tiles in all (m_tiles * n_tiles)
   int64_t n_items, item_offset;
-  const float* best_s;   // MRR threshold per user (may be NULL)
+  const float* best_s;   // exact score of the user's best target (MRR), may be NULL
   const int32_t* best_id;
-  float* cand_s;         // [n_users_pad][n_slots][k]
+  const float* margin;   // E_u per user row
+  float* cand_s;         // [n_users_pad][n_slots][KL]
   int32_t* cand_i;
-  int32_t* cnt;          // [n_users_pad][n_slots] items ranked before the best target
+  int32_t* cnt;          // [n_users_pad][n_slots] items surely ranked before the best target
+  int32_t* bcnt;         // [n_users_pad][n_slots] items in the band around it (may exceed TC_BCAP)
+  int32_t* band_i;       // [n_users_pad][n_slots][TC_BCAP] their ids
 };
 
 // The (user tile, item tile) pairs are numbered m * n_tiles + n and cut into equal contiguous
@@ -306,7 +381,7 @@ __device__ __forceinline__ int tc_slot(int64_t lin_start, int m, int n_tiles, in
 constexpr int TC_EPI_WARPS = 8;   // two per scheduler; each pair splits a tile's columns in halves
 constexpr int TC_THREADS = 128 + 32 * TC_EPI_WARPS;
 
-template <int KL>   // per-row list length kept in registers, >= k
+template <int KL>   // per-row list length kept in registers, > k
 __global__ void __launch_bounds__(TC_THREADS, 1)
 k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const TcParams p) {
@@ -449,10 +524,17 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
       for (int e = 0; e < KL; ++e) { ls[e] = -INFINITY; li[e] = -1; }
       float thr = -INFINITY;
-      const bool mrr = p.want_mrr && valid;
-      const float best_s = mrr ? p.best_s[urow] : INFINITY;   // (rows past the end: m_rng is 0)
-      const int best_id = mrr ? p.best_id[urow] : -1;
-      int before = 0;
+      // MRR: x > t_hi is surely ranked before the best target, x < t_lo surely after it; what
+      // lies between cannot be told from it with these scores and is re-scored by k_tc_finish
+      const bool mrr = p.want_mrr && valid && p.best_id[urow] >= 0;
+      float t_hi = INFINITY, t_lo = INFINITY;   // (no target: nothing before, nothing in the band)
+      if (mrr) {
+        const float bs = p.best_s[urow], E = p.margin[urow];
+        t_hi = bs + E;
+        t_lo = bs - E;
+      }
+      int before = 0, nband = 0;
+      int32_t* band = p.band_i + ((int64_t)urow * p.n_slots + slot) * TC_BCAP;
 
       for (; w < seg_hi; ++w, ++t) {
         const int acc = t & 1;
@@ -503,17 +585,20 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
               for (int c = 0; c < 4; ++c) {
                 const float x = v[h][8 * c + j];
-                mg[c] = __funnelshift_l(__float_as_uint(best_s - x), mg[c], 1);   // x > best
-                ml[c] = __funnelshift_l(__float_as_uint(x - best_s), ml[c], 1);   // x < best
+                mg[c] = __funnelshift_l(__float_as_uint(t_hi - x), mg[c], 1);   // x > t_hi
+                ml[c] = __funnelshift_l(__float_as_uint(x - t_lo), ml[c], 1);   // x < t_lo
               }
             }
             const uint32_t m_gt = mg[0] | (mg[1] << 8) | (mg[2] << 16) | (mg[3] << 24);
-            const uint32_t m_eq = ~(m_gt | ml[0] | (ml[1] << 8) | (ml[2] << 16) | (ml[3] << 24));
-            // ties with the best target count when their id is smaller; the target never does
-            const int d = best_id - (gid0 + c0);      // columns with gid < best_id: j < d
-            const uint32_t m_idlt = d >= 32 ? 0xffffffffu : (d > 0 ? ((1u << d) - 1u) : 0u);
-            const uint32_t m_self = (d >= 0 && d < 32) ? (1u << d) : 0u;
-            before += __popc(m_gt & m_rng & ~m_self) + __popc(m_eq & m_rng & m_idlt);
+            const uint32_t m_lt = ml[0] | (ml[1] << 8) | (ml[2] << 16) | (ml[3] << 24);
+            before += __popc(m_gt & m_rng);
+            uint32_t m_band = mrr ? (~(m_gt | m_lt) & m_rng) : 0u;
+            while (m_band) {          // rare: a handful of items per user
+              const int j = __ffs(m_band) - 1;
+              m_band &= m_band - 1;
+              if (nband < TC_BCAP) band[nband] = gid0 + c0 + j;
+              ++nband;
+            }
           }
           m_ins &= m_rng;
           if (p.debug == 2) m_ins &= 1u;   // experiments: (almost) no inserts
@@ -547,13 +632,14 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
       }
       if (valid) {
-        const int K = p.k;
-        float* cs = p.cand_s + ((int64_t)urow * p.n_slots + slot) * K;
-        int32_t* ci = p.cand_i + ((int64_t)urow * p.n_slots + slot) * K;
+        float* cs = p.cand_s + ((int64_t)urow * p.n_slots + slot) * KL;
+        int32_t* ci = p.cand_i + ((int64_t)urow * p.n_slots + slot) * KL;
 #pragma unroll
-        for (int j = 0; j < KL; ++j)
-          if (j < K) { cs[j] = ls[j]; ci[j] = li[j]; }
-        if (p.cnt) p.cnt[(int64_t)urow * p.n_slots + slot] = before;
+        for (int j = 0; j < KL; ++j) { cs[j] = ls[j]; ci[j] = li[j]; }
+        if (p.want_mrr) {
+          p.cnt[(int64_t)urow * p.n_slots + slot] = before;
+          p.bcnt[(int64_t)urow * p.n_slots + slot] = nband;
+        }
       }
     }
   }
@@ -566,12 +652,8 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 }
 
-// Merge the candidates of a user's segments. Every slot list arrives sorted (score desc, id asc)
-// and item ids are unique across a user's slots, so this is a k-round merge of sorted lists: G
-// lanes per user (G = n_slots rounded up to a power of two, 32 / G users per warp), one slot per
-// lane with its head as a 64-bit key (ordered score bits | inverted id; larger = ranked first), a
-// log2(G)-level max per round, the winning lane advances. The picks go through shared memory so
-// the target lookups of all k picks run side by side; AP@k from the hit mask in rank order.
+// ---------------------------------------------------------------------------------- finish
+// 64-bit ranking key: larger = ranked first (score descending, item id ascending)
 __device__ __forceinline__ uint64_t tc_key(float s, int id) {
   if (id < 0) return 0ull;
   uint32_t u = __float_as_uint(s + 0.0f);            // (-0 -> +0: equal scores, equal keys)
@@ -583,89 +665,193 @@ __device__ __forceinline__ float tc_key_score(uint64_t key) {
   u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
   return __uint_as_float(u);
 }
+__device__ __forceinline__ int tc_key_id(uint64_t key) { return 0x7fffffff - (int)(uint32_t)key; }
+__device__ __forceinline__ uint64_t warp_max_u64(uint64_t v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const uint64_t w = __shfl_xor_sync(0xffffffffu, v, o);
+    v = w > v ? w : v;
+  }
+  return v;
+}
 
-template <int G>
+struct TcFinish {
+  const float* cand_s;
+  const int32_t* cand_i;
+  const int32_t *cnt, *bcnt, *band_i;
+  int n_slots, KL, k, D, want_mrr;
+  int64_t n_users;
+  const float* margin;
+  const float *U, *I, *bu, *bi;
+  const int32_t* user_ids;
+  const int64_t* tgt_indptr;
+  const int32_t* tgt_items;
+  const float* best_s;
+  const int32_t* best_id;
+  int32_t* topk_ids;
+  float* topk_scores;
+  double* ap;
+  int32_t* n_before_best;
+  int32_t* fb_list;     // users handed to the exact path
+  int32_t* status;      // [0] their number, [1] how many did not fit into fb_list
+  int fb_cap;
+};
+
+constexpr int TC_LANE_CAND = 6;   // exact re-scorings one lane can hold; more -> the exact path
+
+// One warp per user. (1) A_k = the k-th best key of the union of the slots' lists; T = the best
+// score any item OUTSIDE the lists can have (the largest last entry of a full list). (2) If
+// T < A_k - 2 E, every item of the true top-k is inside the lists and has S~ >= A_k - 2 E: those
+// entries are re-scored exactly and ranked; otherwise the user goes to the exact path. (3) MRR:
+// the slots' sure counts plus the exact verdict on every band item.
 __global__ void __launch_bounds__(256)
-k_tc_merge(const float* __restrict__ cand_s, const int32_t* __restrict__ cand_i,
-           const int32_t* __restrict__ cnt, int n_slots, int k, int64_t n_users,
-           const int64_t* __restrict__ tgt_indptr, const int32_t* __restrict__ tgt_items,
-           const int32_t* __restrict__ best_id, int32_t* __restrict__ topk_ids,
-           float* __restrict__ topk_scores, double* __restrict__ ap,
-           int32_t* __restrict__ n_before_best) {
-  constexpr int UPW = 32 / G;                       // users per warp
-  __shared__ uint64_t s_pick[8][UPW][TC_MAXK];      // [warp][user][rank]
-  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  const int gl = lane & (G - 1), ug = lane / G;
-  const int64_t r = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * UPW + ug;
-  const bool live = r < n_users;
-  // slots gl, gl + G, ...: (only n_slots > 32 gives a lane more than one; then the best head of
-  // its slots is found by a scan every round)
-  const int total = n_slots * k;
-  const float* cs = cand_s + (live ? r : 0) * total;
-  const int32_t* ci = cand_i + (live ? r : 0) * total;
-  int head = 0;                                     // (G >= n_slots: position in slot gl)
-  uint64_t key = 0;
-  uint64_t prev = ~0ull;
-  auto load_head = [&]() {
-    if (G >= 32 && n_slots > 32) {
-      // several slots per lane: best candidate below the previous pick
-      key = 0;
-      for (int sl = gl; sl < n_slots; sl += G)
-        for (int e = 0; e < k; ++e) {
-          const uint64_t kk = tc_key(cs[sl * k + e], ci[sl * k + e]);
-          if (kk < prev && kk > key) key = kk;
-        }
-    } else {
-      key = (live && gl < n_slots && head < k) ? tc_key(cs[gl * k + head], ci[gl * k + head]) : 0ull;
-    }
+k_tc_finish(const TcFinish p) {
+  const int lane = threadIdx.x & 31;
+  const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (r >= p.n_users) return;
+  const int n_ent = p.n_slots * p.KL;
+  const float* cs = p.cand_s + r * n_ent;
+  const int32_t* ci = p.cand_i + r * n_ent;
+  const float E = p.margin[r];
+  // entry e of the walk = rank j of slot s with e = j * n_slots + s: the heads of the lists,
+  // where the candidates are, spread over the lanes
+  auto entry = [&](int e, float& s, int& id) {
+    const int j = e / p.n_slots, sl = e - j * p.n_slots;
+    s = cs[sl * p.KL + j];
+    id = ci[sl * p.KL + j];
   };
-  load_head();
-  for (int j = 0; j < k; ++j) {
-    uint64_t best = key;
+  bool fallback = false;
+  // ---- (1)
+  uint64_t prev = ~0ull;
+  int found = 0;
+  for (int round = 0; round < p.k; ++round) {
+    uint64_t best = 0;
+    for (int e = lane; e < n_ent; e += 32) {
+      float s; int id;
+      entry(e, s, id);
+      const uint64_t key = tc_key(s, id);
+      if (key < prev && key > best) best = key;
+    }
+    best = warp_max_u64(best);
+    if (best == 0) break;
+    prev = best;
+    ++found;
+  }
+  float T = -INFINITY;
+  for (int sl = lane; sl < p.n_slots; sl += 32)
+    if (ci[sl * p.KL + p.KL - 1] >= 0) T = fmaxf(T, cs[sl * p.KL + p.KL - 1]);
 #pragma unroll
-    for (int o = G / 2; o > 0; o >>= 1) {
-      const uint64_t other = __shfl_xor_sync(0xffffffffu, best, o);
-      best = other > best ? other : best;
-    }
-    if (gl == 0) s_pick[wib][ug][j] = best;
-    if (best != 0 && key == best) {   // the winner moves on
-      ++head;
-      prev = best;
-      load_head();
-    } else if (G >= 32) {
-      prev = best ? best : prev;
-    }
-  }
-  __syncwarp();
-  int64_t t0 = 0;
-  int n_tgt = 0;
-  if (live) { t0 = tgt_indptr[r]; n_tgt = (int)(tgt_indptr[r + 1] - t0); }
-  uint32_t hits = 0;
-  for (int j = gl; j < k; j += G) {
-    const uint64_t pk = s_pick[wib][ug][j];
-    const int id = pk ? 0x7fffffff - (int)(uint32_t)pk : -1;
-    if (live) {
-      if (topk_ids) topk_ids[r * k + j] = id;
-      if (topk_scores) topk_scores[r * k + j] = pk ? tc_key_score(pk) : -INFINITY;
-      if (id >= 0 && csr_contains(tgt_items + t0, 0, n_tgt, id)) hits |= 1u << j;
+  for (int o = 16; o > 0; o >>= 1) T = fmaxf(T, __shfl_xor_sync(0xffffffffu, T, o));
+  const float thresh = found == p.k ? tc_key_score(prev) - 2.f * E : -INFINITY;
+  if (!(T < thresh) && T != -INFINITY) fallback = true;
+  // ---- MRR ingredients (before anything is written: a band that overflowed also falls back)
+  const bool mrr = p.want_mrr != 0;
+  const int bid = mrr ? p.best_id[r] : -1;
+  const float bs = mrr && bid >= 0 ? p.best_s[r] : 0.f;
+  int sure = 0;
+  if (mrr && bid >= 0) {
+    for (int sl = lane; sl < p.n_slots; sl += 32) {
+      sure += p.cnt[r * p.n_slots + sl];
+      if (p.bcnt[r * p.n_slots + sl] > TC_BCAP) fallback = true;
     }
   }
+  // ---- (2) this lane's candidates
+  const int64_t u = p.user_ids[r];
+  const float* urow = p.U + u * p.D;
+  const float ub = p.bu[u];
+  uint64_t ek[TC_LANE_CAND];
+  int n_mine = 0;
 #pragma unroll
-  for (int o = G / 2; o > 0; o >>= 1) hits |= __shfl_xor_sync(0xffffffffu, hits, o);
-  if (live && gl == 0) {
-    if (ap) {
-      double ap_acc = 0.0;
-      for (int j = 0; j < k; ++j)
-        if ((hits >> j) & 1u) ap_acc += (double)__popc(hits & ((2u << j) - 1u)) / (double)(j + 1);
-      const int denom = k < n_tgt ? k : n_tgt;
-      ap[r] = denom > 0 ? ap_acc / (double)denom : 0.0;
-    }
-    if (n_before_best) {
-      int tot = 0;
-      if (cnt) for (int sl = 0; sl < n_slots; ++sl) tot += cnt[r * n_slots + sl];
-      n_before_best[r] = (best_id && best_id[r] >= 0) ? tot : -1;
-    }
+  for (int c = 0; c < TC_LANE_CAND; ++c) ek[c] = 0;
+  for (int e = lane; e < n_ent; e += 32) {
+    float s; int id;
+    entry(e, s, id);
+    if (id < 0 || !(s >= thresh)) continue;
+    if (n_mine == TC_LANE_CAND) { fallback = true; break; }
+    const float ex = tc_exact_score(urow, p.I + (int64_t)id * p.D, p.D, ub, p.bi[id]);
+    const uint64_t key = tc_key(ex, id);
+#pragma unroll
+    for (int c = 0; c < TC_LANE_CAND; ++c)
+      if (c == n_mine) ek[c] = key;
+    ++n_mine;
   }
+  fallback = __any_sync(0xffffffffu, fallback);
+  if (fallback) {
+    if (lane == 0) {
+      const int at = atomicAdd(p.status + 0, 1);
+      if (at < p.fb_cap) p.fb_list[at] = (int32_t)r;
+      else atomicAdd(p.status + 1, 1);
+    }
+    return;
+  }
+  // ---- exact top-k of the candidates: k rounds of "best key below the previous pick"
+  const int64_t t0 = p.tgt_indptr[r];
+  const int n_tgt = (int)(p.tgt_indptr[r + 1] - t0);
+  uint64_t my_pick = 0;
+  prev = ~0ull;
+  for (int round = 0; round < p.k; ++round) {
+    uint64_t best = 0;
+#pragma unroll
+    for (int c = 0; c < TC_LANE_CAND; ++c)
+      if (ek[c] < prev && ek[c] > best) best = ek[c];
+    best = warp_max_u64(best);
+    if (round == lane) my_pick = best;
+    if (best == 0) break;
+    prev = best;
+  }
+  bool hit = false;
+  if (lane < p.k) {
+    const int id = my_pick ? tc_key_id(my_pick) : -1;
+    if (p.topk_ids) p.topk_ids[r * p.k + lane] = id;
+    if (p.topk_scores) p.topk_scores[r * p.k + lane] = my_pick ? tc_key_score(my_pick) : -INFINITY;
+    hit = id >= 0 && csr_contains(p.tgt_items + t0, 0, n_tgt, id);
+  }
+  const uint32_t hits = __ballot_sync(0xffffffffu, hit);
+  if (lane == 0 && p.ap) {
+    double ap_acc = 0.0;
+    for (int j = 0; j < p.k; ++j)
+      if ((hits >> j) & 1u) ap_acc += (double)__popc(hits & ((2u << j) - 1u)) / (double)(j + 1);
+    const int denom = p.k < n_tgt ? p.k : n_tgt;
+    p.ap[r] = denom > 0 ? ap_acc / (double)denom : 0.0;
+  }
+  // ---- (3)
+  if (mrr && p.n_before_best) {
+    int more = 0;
+    if (bid >= 0) {
+      for (int e = lane; e < p.n_slots * TC_BCAP; e += 32) {
+        const int sl = e / TC_BCAP, n = e - sl * TC_BCAP;
+        if (n >= p.bcnt[r * p.n_slots + sl]) continue;
+        const int id = p.band_i[(r * p.n_slots + sl) * TC_BCAP + n];
+        if (id == bid) continue;     // the target never precedes itself
+        const float ex = tc_exact_score(urow, p.I + (int64_t)id * p.D, p.D, ub, p.bi[id]);
+        more += (ex > bs || (ex == bs && id < bid)) ? 1 : 0;
+      }
+    }
+    int tot = sure + more;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+    if (lane == 0) p.n_before_best[r] = bid >= 0 ? tot : -1;
+  }
+}
+
+// exact scores of the users handed to the exact path: one CTA per such user, fb_scores[b][c]
+__global__ void __launch_bounds__(256)
+k_tc_fb_scores(const float* __restrict__ U, const float* __restrict__ I,
+               const float* __restrict__ bu, const float* __restrict__ bi, int D,
+               const int32_t* __restrict__ user_ids, int64_t item_offset, int64_t n_items,
+               const int32_t* __restrict__ fb_list, const int32_t* __restrict__ status, int fb_cap,
+               float* __restrict__ fb_scores) {
+  const int n_fb = min(status[0], fb_cap);
+  if ((int)blockIdx.x >= n_fb) return;
+  const int64_t u = user_ids[fb_list[blockIdx.x]];
+  const float ub = bu[u];
+  float* out = fb_scores + (int64_t)blockIdx.x * n_items;
+  for (int64_t c = threadIdx.x; c < n_items; c += blockDim.x)
+    out[c] = tc_exact_score(U + u * D, I + (item_offset + c) * D, D, ub, bi[item_offset + c]);
+}
+
+__global__ void k_tc_status_add(const int32_t* __restrict__ status, int32_t* __restrict__ out) {
+  if (threadIdx.x < 2 && status[threadIdx.x]) atomicAdd(out + threadIdx.x, status[threadIdx.x]);
 }
 
 // ---------------------------------------------------------------------------------- host side
@@ -701,16 +887,24 @@ static int make_map(CUtensorMap* map, void* base, int64_t rows, int Kp, int box_
   return CMF_OK;
 }
 
+int g_tc_terms = 0;   // cmf_set_tuning key 4: 0 = automatic (1 without the MRR counter, else 3)
+
+static int tc_list_len(int k) { return k <= 4 ? 8 : (k <= 10 ? 16 : 24); }
+
 struct TcLayout {
-  int Kp, KB, m_tiles, n_tiles, n_ctas, n_slots;
+  int Kp, KB, KL, m_tiles, n_tiles, n_ctas, n_slots, fb_cap;
   int64_t m_pad, chunk, total_work;
-  size_t Bp, Ap, bu, best_s, best_id, cand_s, cand_i, cnt, total;
+  size_t Bp, Ap, unorm, uabsb, margin, stats, best_s, best_id, cand_s, cand_i, cnt, bcnt, band_i,
+      fb_list, status, fb_scores, fb_sig, total;
 };
 
-static TcLayout tc_layout(int64_t n_users, int64_t n_items, int D, int k) {
+// (the layout is sized for three terms, so one workspace serves both forms)
+static TcLayout tc_layout(int64_t n_users, int64_t n_items, int D, int k, int terms) {
   TcLayout L;
-  L.Kp = (int)align_up((size_t)3 * D + 4, TC_BK);   // + the bias slots
+  const int Kp_max = (int)align_up((size_t)3 * D + 4, TC_BK);
+  L.Kp = (int)align_up((size_t)terms * D + 4, TC_BK);   // + the bias slots
   L.KB = L.Kp / TC_BK;
+  L.KL = tc_list_len(k);
   L.m_tiles = (int)((n_users + TC_BM - 1) / TC_BM);
   L.m_pad = (int64_t)L.m_tiles * TC_BM;
   L.n_tiles = (int)((n_items + TC_BN - 1) / TC_BN);
@@ -722,16 +916,29 @@ static TcLayout tc_layout(int64_t n_users, int64_t n_items, int D, int k) {
   L.n_ctas = (int)((L.total_work + L.chunk - 1) / L.chunk);
   // segments a user tile can be cut into (x 2: the epilogue keeps one list per column half)
   L.n_slots = 2 * (int)((L.n_tiles + L.chunk - 1) / L.chunk + 1);
+  // users the exact path can take over per call: up to 64 MB of score rows
+  int64_t cap = ((int64_t)64 << 20) / (int64_t)(sizeof(float) * (size_t)n_items);
+  L.fb_cap = (int)(cap < 1 ? 1 : (cap > 256 ? 256 : cap));
+  if (L.fb_cap > n_users) L.fb_cap = (int)n_users;
   size_t o = 0;
   auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes, 1024); return at; };
-  L.Bp = take((size_t)n_items * L.Kp * 2);
-  L.Ap = take((size_t)L.m_pad * L.Kp * 2);
-  L.bu = take(sizeof(float) * L.m_pad);
+  L.Bp = take((size_t)n_items * Kp_max * 2);
+  L.Ap = take((size_t)L.m_pad * Kp_max * 2);
+  L.unorm = take(sizeof(float) * L.m_pad);
+  L.uabsb = take(sizeof(float) * L.m_pad);
+  L.margin = take(sizeof(float) * L.m_pad);
+  L.stats = take(sizeof(uint32_t) * 8);     // [0..1] of the items split with 1 term, [2..3] with 3, [4] which one Bp holds
   L.best_s = take(sizeof(float) * L.m_pad);
   L.best_id = take(sizeof(int32_t) * L.m_pad);
-  L.cand_s = take(sizeof(float) * L.m_pad * L.n_slots * k);
-  L.cand_i = take(sizeof(int32_t) * L.m_pad * L.n_slots * k);
+  L.cand_s = take(sizeof(float) * L.m_pad * L.n_slots * L.KL);
+  L.cand_i = take(sizeof(int32_t) * L.m_pad * L.n_slots * L.KL);
   L.cnt = take(sizeof(int32_t) * L.m_pad * L.n_slots);
+  L.bcnt = take(sizeof(int32_t) * L.m_pad * L.n_slots);
+  L.band_i = take(sizeof(int32_t) * L.m_pad * L.n_slots * TC_BCAP);
+  L.fb_list = take(sizeof(int32_t) * L.fb_cap);
+  L.status = take(sizeof(int32_t) * 8);
+  L.fb_scores = take(sizeof(float) * (size_t)L.fb_cap * n_items);
+  L.fb_sig = take(2 * sizeof(float) * (size_t)L.fb_cap * n_items);
   L.total = o;
   return L;
 }
@@ -740,8 +947,13 @@ bool eval_tc_supported(int D, int k) { return D >= 1 && D <= 128 && k >= 1 && k 
 
 size_t eval_tc_workspace_bytes(int64_t n_users, int64_t n_items, int D, int k) {
   if (!eval_tc_supported(D, k)) return 0;
-  return tc_layout(n_users, n_items, D, k).total;
+  return tc_layout(n_users, n_items, D, k, 3).total;
 }
+
+// eval.cu: k_rank_rows over score rows [n_rows][n_items] whose user is row_map[row]
+int launch_rank_rows_mapped(const cmf_eval_t* a, const float* scores, float* sig_scratch,
+                            const int32_t* row_map, const int32_t* row_count, int row_cap,
+                            cudaStream_t s);
 
 int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   CMF_REQUIRE(!a->want_auc, "cmf_eval_tile: AUC is computed by the exact path (precision = 0)");
@@ -749,26 +961,40 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
     return fail(CMF_ERR_UNSUPPORTED,
                 "cmf_eval_tile: the tensor-core path takes embedding_dim <= 128 and k <= %d "
                 "(got D = %d, k = %d); use precision = 0", TC_MAXK, a->D, a->k);
-  const TcLayout L = tc_layout(a->n_users_tile, a->num_items_shard, a->D, a->k);
-  if (!a->workspace || a->workspace_bytes < L.total)
+  const bool mrr = a->want_mrr != 0;
+  const int terms = g_tc_terms == 1 || g_tc_terms == 3 ? g_tc_terms : (mrr ? 3 : 1);
+  const TcLayout L = tc_layout(a->n_users_tile, a->num_items_shard, a->D, a->k, terms);
+  const size_t need = eval_tc_workspace_bytes(a->n_users_tile, a->num_items_shard, a->D, a->k);
+  if (!a->workspace || a->workspace_bytes < need)
     return fail(CMF_ERR_WORKSPACE, "cmf_eval_tile: workspace of %zu bytes needed, %zu given",
-                L.total, a->workspace ? a->workspace_bytes : (size_t)0);
+                need, a->workspace ? a->workspace_bytes : (size_t)0);
   char* base = (char*)a->workspace;
   __nv_bfloat16* Bp = (__nv_bfloat16*)(base + L.Bp);
   __nv_bfloat16* Ap = (__nv_bfloat16*)(base + L.Ap);
+  float* unorm = (float*)(base + L.unorm);
+  float* uabsb = (float*)(base + L.uabsb);
+  float* margin = (float*)(base + L.margin);
+  uint32_t* stats = (uint32_t*)(base + L.stats);
   float* best_s = (float*)(base + L.best_s);
   int32_t* best_id = (int32_t*)(base + L.best_id);
+  int32_t* status = (int32_t*)(base + L.status);
   const int grid = num_sms() * 8;
 
-  if (!a->reuse_item_prep) {
+  // the item side of the workspace (split copy + largest norm) is reused across calls on request
+  const bool reuse = a->reuse_item_prep != 0;
+  if (!reuse) {
+    CMF_CUDA(cudaMemsetAsync(stats, 0, sizeof(uint32_t) * 8, s));
     k_tc_split<<<grid, 256, 0, s>>>(a->I, a->bi, nullptr, a->item_offset, a->num_items_shard,
-                                    a->num_items_shard, a->D, L.Kp, 0, Bp);
+                                    a->num_items_shard, a->D, L.Kp, 0, terms, Bp, nullptr, nullptr,
+                                    stats);
     CMF_LAUNCH_CHECK();
   }
   k_tc_split<<<grid, 256, 0, s>>>(a->U, a->bu, a->user_ids, 0, a->n_users_tile, L.m_pad, a->D,
-                                  L.Kp, 1, Ap);
+                                  L.Kp, 1, terms, Ap, unorm, uabsb, nullptr);
   CMF_LAUNCH_CHECK();
-  const bool mrr = a->want_mrr != 0;
+  k_tc_margin<<<(unsigned)((L.m_pad + 255) / 256), 256, 0, s>>>(
+      unorm, uabsb, stats, terms == 1 ? kTcC1 : kTcC3, L.m_pad, margin);
+  CMF_LAUNCH_CHECK();
   if (mrr) {
     if (a->ext_best_id) {
       CMF_CUDA(cudaMemcpyAsync(best_s, a->ext_best_score, sizeof(float) * a->n_users_tile,
@@ -797,42 +1023,78 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
 
   TcParams p{};
   p.n_users = (int)a->n_users_tile; p.k = a->k; p.KB = L.KB; p.n_tiles = L.n_tiles;
-  p.last_steps = (3 * a->D + 4 - (L.KB - 1) * TC_BK + 15) / 16;
+  p.last_steps = (terms * a->D + 4 - (L.KB - 1) * TC_BK + 15) / 16;
   p.m_tiles = L.m_tiles; p.n_slots = L.n_slots; p.chunk = L.chunk; p.total_work = L.total_work;
   p.want_mrr = mrr ? 1 : 0;
   p.n_items = a->num_items_shard; p.item_offset = a->item_offset; p.debug = g_tc_debug;
-  p.best_s = best_s; p.best_id = best_id;
+  p.best_s = best_s; p.best_id = best_id; p.margin = margin;
   p.cand_s = (float*)(base + L.cand_s); p.cand_i = (int32_t*)(base + L.cand_i);
-  p.cnt = (int32_t*)(base + L.cnt);
+  p.cnt = (int32_t*)(base + L.cnt); p.bcnt = (int32_t*)(base + L.bcnt);
+  p.band_i = (int32_t*)(base + L.band_i);
 
   const size_t smem = (size_t)L.KB * TC_A_BYTES + (size_t)TC_STAGES * TC_B_BYTES +
                       (2 * TC_STAGES + 6) * sizeof(uint64_t) + 64 + 1024;
   // slots a user tile does not use stay empty
-  CMF_CUDA(cudaMemsetAsync(p.cand_i, 0xFF, sizeof(int32_t) * L.m_pad * L.n_slots * a->k, s));
-  CMF_CUDA(cudaMemsetAsync(p.cnt, 0, sizeof(int32_t) * L.m_pad * L.n_slots, s));
-  // list length: the smallest instantiation that holds k
+  CMF_CUDA(cudaMemsetAsync(p.cand_i, 0xFF, sizeof(int32_t) * L.m_pad * L.n_slots * L.KL, s));
+  if (mrr) {
+    CMF_CUDA(cudaMemsetAsync(p.cnt, 0, sizeof(int32_t) * L.m_pad * L.n_slots, s));
+    CMF_CUDA(cudaMemsetAsync(p.bcnt, 0, sizeof(int32_t) * L.m_pad * L.n_slots, s));
+  }
+  CMF_CUDA(cudaMemsetAsync(status, 0, sizeof(int32_t) * 8, s));
+  // list length: the smallest instantiation that leaves a margin above k
 #define CMF_TC_LAUNCH(KL)                                                                        \
   do {                                                                                           \
     CMF_CUDA(cudaFuncSetAttribute(k_tc_gemm_topk<KL>,                                            \
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));      \
     k_tc_gemm_topk<KL><<<(unsigned)L.n_ctas, TC_THREADS, smem, s>>>(tmA, tmB, p);                \
   } while (0)
-  if (a->k <= 4) CMF_TC_LAUNCH(4);
-  else if (a->k <= 8) CMF_TC_LAUNCH(8);
-  else if (a->k <= 10) CMF_TC_LAUNCH(10);
-  else CMF_TC_LAUNCH(16);
+  if (L.KL == 8) CMF_TC_LAUNCH(8);
+  else if (L.KL == 16) CMF_TC_LAUNCH(16);
+  else CMF_TC_LAUNCH(24);
 #undef CMF_TC_LAUNCH
   CMF_LAUNCH_CHECK();
 
-#define CMF_TC_MERGE(G)                                                                         \
-  k_tc_merge<G><<<(unsigned)((a->n_users_tile * (G) + 255) / 256), 256, 0, s>>>(p.cand_s, p.cand_i, mrr ? p.cnt : nullptr, L.n_slots, a->k, a->n_users_tile, a->tgt_indptr, a->tgt_items, mrr ? best_id : nullptr, a->topk_ids, a->topk_scores, a->ap, a->n_before_best)
-  if (L.n_slots <= 4) CMF_TC_MERGE(4);
-  else if (L.n_slots <= 8) CMF_TC_MERGE(8);
-  else if (L.n_slots <= 16) CMF_TC_MERGE(16);
-  else CMF_TC_MERGE(32);
-#undef CMF_TC_MERGE
+  TcFinish f{};
+  f.cand_s = p.cand_s; f.cand_i = p.cand_i; f.cnt = p.cnt; f.bcnt = p.bcnt; f.band_i = p.band_i;
+  f.n_slots = L.n_slots; f.KL = L.KL; f.k = a->k; f.D = a->D; f.want_mrr = mrr ? 1 : 0;
+  f.n_users = a->n_users_tile; f.margin = margin;
+  f.U = a->U; f.I = a->I; f.bu = a->bu; f.bi = a->bi; f.user_ids = a->user_ids;
+  f.tgt_indptr = a->tgt_indptr; f.tgt_items = a->tgt_items;
+  f.best_s = best_s; f.best_id = best_id;
+  f.topk_ids = a->topk_ids; f.topk_scores = a->topk_scores; f.ap = a->ap;
+  f.n_before_best = a->n_before_best;
+  f.fb_list = (int32_t*)(base + L.fb_list); f.status = status; f.fb_cap = L.fb_cap;
+  k_tc_finish<<<(unsigned)((a->n_users_tile * 32 + 255) / 256), 256, 0, s>>>(f);
   CMF_LAUNCH_CHECK();
+
+  // the users the bound could not settle: exact scores of their rows, ranked by the exact path's
+  // own kernel (both grids are sized for fb_cap users and return at once when there are none)
+  float* fb_scores = (float*)(base + L.fb_scores);
+  k_tc_fb_scores<<<(unsigned)L.fb_cap, 256, 0, s>>>(a->U, a->I, a->bu, a->bi, a->D, a->user_ids,
+                                                    a->item_offset, a->num_items_shard, f.fb_list,
+                                                    status, L.fb_cap, fb_scores);
+  CMF_LAUNCH_CHECK();
+  cmf_eval_t b = *a;
+  if (mrr) { b.ext_best_score = best_s; b.ext_best_id = best_id; b.best_score = nullptr; b.best_id = nullptr; }
+  rc = launch_rank_rows_mapped(&b, fb_scores, (float*)(base + L.fb_sig), f.fb_list, status,
+                               L.fb_cap, s);
+  if (rc) return rc;
+  if (a->tc_status) {
+    k_tc_status_add<<<1, 32, 0, s>>>(status, a->tc_status);
+    CMF_LAUNCH_CHECK();
+  }
   return CMF_OK;
 }
 
 }  // namespace cmf
+
+using namespace cmf;
+
+extern "C" int cmf_eval_tc_info(int32_t D, double* out /* [4] */) {
+  CMF_REQUIRE(out && D >= 1, "cmf_eval_tc_info: bad arguments");
+  out[0] = (double)(((D + 4) + 15) / 16 * 16);        // K extent issued per output, 1 term
+  out[1] = (double)(((3 * D + 4) + 15) / 16 * 16);    // ... 3 terms
+  out[2] = (double)kTcC1;
+  out[3] = (double)kTcC3;
+  return CMF_OK;
+}

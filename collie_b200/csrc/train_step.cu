@@ -27,6 +27,7 @@
 namespace cmf {
 
 extern int g_tc_debug;
+extern int g_tc_terms;
 extern int g_pdl;
 
 struct WsLayout {
@@ -517,6 +518,12 @@ extern "C" int cmf_set_tuning(int32_t key, int32_t value) {
   if (key == 3) {
     const int prev = g_tc_debug;
     g_tc_debug = value;
+    return prev;
+  }
+  if (key == 4) {
+    CMF_REQUIRE(value == 0 || value == 1 || value == 3, "cmf_set_tuning: terms %d", value);
+    const int prev = g_tc_terms;
+    g_tc_terms = value;
     return prev;
   }
   if (key == 6) {

@@ -582,6 +582,7 @@ def _item_sharded_tiles(M, names, k, group, world, precision, tile_users, tables
     """Steps (2) and (3) of ``evaluate_item_sharded``, tile by tile."""
     want = {'topk'} | ({'mrr'} if 'mrr' in names else set())
     sums = {n_: torch.zeros((), dtype=torch.float64, device=dev) for n_ in names}
+    status = torch.zeros(2, dtype=torch.int32, device=dev) if precision == 1 else None
     tgt_keys = row_of.long() * n_items + tgt_items.long()      # sorted: CSR order
     ws = None
     for s0 in range(0, n_test, tile_users):
@@ -594,7 +595,8 @@ def _item_sharded_tiles(M, names, k, group, world, precision, tile_users, tables
             kk = min(k, n_loc)
             res = M._eval_tile(dev, nt, n_loc, kk, indptr[s0:e0 + 1], tgt_items, want,
                                tables=tables, user_ids=users_dev[s0:e0], precision=precision,
-                               workspace=ws, item_offset=lo,
+                               workspace=ws, item_offset=lo, reuse_item_prep=(s0 > 0),
+                               tc_status=status,
                                ext_best=(best_s[s0:e0].contiguous(), best_id[s0:e0].contiguous()))
             ws = res['_workspace']
             loc_ids[:, :kk], loc_s[:, :kk] = res['topk_ids'], res['topk_scores']
@@ -614,6 +616,12 @@ def _item_sharded_tiles(M, names, k, group, world, precision, tile_users, tables
             has = best_id[s0:e0] >= 0
             sums['mrr'] += torch.where(has, 1.0 / (before.double() + 1.0),
                                        torch.zeros(nt, dtype=torch.float64, device=dev)).sum()
+    if status is not None:
+        dist.all_reduce(status, group=group)
+        if int(status[1].item()) != 0:      # (see evaluate_in_batches: the exact path takes over)
+            return _item_sharded_tiles(M, names, k, group, world, 0, tile_users, tables, dev,
+                                       n_items, lo, n_loc, indptr, tgt_items, counts, row_of,
+                                       users_dev, n_test, best_s, best_id)
     out = [float(sums[n_] / n_test) for n_ in names]
     return out[0] if len(out) == 1 else out
 

@@ -56,12 +56,14 @@ def _targets_all_users_device(targets: csr_matrix, test_users, device):
 
 def _eval_tile(device, n_users, n_items, k, indptr, tgt_items, want, tables=None, user_ids=None,
                scores=None, precision=0, workspace=None, reuse_item_prep=False, item_offset=0,
-               ext_best=None, into=None):
+               ext_best=None, into=None, tc_status=None):
     """One ``cmf_eval_tile`` call; returns dict of per-user device tensors. ``item_offset`` /
     ``n_items`` select an item shard of the table (global ids come back); ``ext_best`` = (score,
     id) of every user's best target over ALL shards, against which the MRR counter counts;
     ``into`` = (dict of whole-evaluation output tensors, first row): the tile's per-user outputs are
-    written there instead of into fresh tensors."""
+    written there instead of into fresh tensors. ``tc_status`` (precision 1): int32[2] device
+    tensor the call adds to -- [0] users ranked by the exact path inside the call, [1] users it
+    could not take over (their outputs are not written: repeat the tile with precision 0)."""
     a = _abi.cmf_eval_t()
     keep = []
     if scores is not None:
@@ -80,6 +82,9 @@ def _eval_tile(device, n_users, n_items, k, indptr, tgt_items, want, tables=None
     a.tgt_indptr, a.tgt_items = indptr.data_ptr(), tgt_items.data_ptr()
     a.precision = precision
     a.reuse_item_prep = 1 if reuse_item_prep else 0
+    if tc_status is not None:
+        a.tc_status = tc_status.data_ptr()
+        keep.append(tc_status)
     out = {}
 
     def vec(name, dtype):
@@ -249,18 +254,31 @@ def evaluate_in_batches(metric_list, test_interactions, model, k=10, batch_size=
                 ws = _eval_tile(device, e - s, n_items, k, indptr[s:e + 1], tgt_items,
                                 set(ex_names), tables=tables, user_ids=users_dev[s:e],
                                 precision=0, workspace=ws, into=(whole, s))['_workspace']
+        status = None
         if tc_names:
             tile = _TC_TILE_USERS
             ws = None
+            status = torch.zeros(2, dtype=torch.int32, device=device)
             for s in range(0, n_test, tile):
                 e = min(s + tile, n_test)
                 ws = _eval_tile(device, e - s, n_items, k, indptr[s:e + 1], tgt_items,
                                 set(tc_names), tables=tables, user_ids=users_dev[s:e],
                                 precision=1, workspace=ws, reuse_item_prep=(s > 0),
-                                into=(whole, s))['_workspace']
+                                into=(whole, s), tc_status=status)['_workspace']
         for j, name in enumerate(names):
             sums[j] = _per_user(name, whole, nnz, n_items).sum()
-        all_scores = (sums / n_test).tolist()
+        if status is not None:
+            # one read-back for the whole evaluation: the metric sums and the tensor-core status
+            host = torch.cat([sums, status.double()]).tolist()
+            if host[-1] != 0:
+                # more users than one call can hand to the exact path had candidates the error
+                # bound could not separate (heavily tied scores): the exact path takes it all
+                return evaluate_in_batches(metric_list, test_interactions, model, k=k,
+                                           batch_size=batch_size, logger=logger, verbose=verbose,
+                                           precision=0)
+            all_scores = [v / n_test for v in host[:len(names)]]
+        else:
+            all_scores = (sums / n_test).tolist()
     else:
         if n_test < batch_size:
             batch_size = n_test

@@ -328,9 +328,11 @@ CMF_API int cmf_item_exchange_update(const cmf_peers_t *peers, float *M, float *
  *   ap [n] double (AP@k per user, fp64 like the reference's weights), n_before_best [n] int32: #items ranked before the user's best-ranked
  *   target in this shard, best_score/best_id [n]: that target's score/id (-inf/-1 when none),
  *   auc_pairs [n] double: sum over targets of (#non-targets with lower sigmoid + .5 ties).
- * precision: 0 = fp32 SIMT scoring (exact fp32; all outputs), 1 = tcgen05 tensor cores over
- *   bf16-split operands (hi.hi + hi.lo + lo.hi, fp32 accumulation): embedding_dim <= 128, k <= 16,
- *   every output except auc_pairs (want_auc must be 0).
+ * precision: 0 = fp32 SIMT scoring (exact fp32; all outputs), 1 = tcgen05 tensor cores select
+ *   (bf16 operands, fp32 accumulation, a stated error bound) and fp32 decides (every candidate of
+ *   the top-k and every item whose order against the best target is in doubt is re-scored in
+ *   the exact path's summation order): embedding_dim <= 128, k <= 16, every output except
+ *   auc_pairs (want_auc must be 0); ids, scores, ap and n_before_best equal precision 0 bit for bit.
  */
 typedef struct {
   const float *U, *I, *bu, *bi;
@@ -360,15 +362,25 @@ typedef struct {
    * scoring (the metric callables' `preds` argument, collie/metrics.py:144-147); U/I/bu/bi and
    * user_ids are then ignored */
   const float *scores_in;
-  /* precision = 1 only: non-zero = the item table has not changed since the previous call with
-   * this workspace, so its bf16 split copy in the workspace is reused */
+  /* precision = 1 only: non-zero = the item table, the shard and want_mrr are those of the
+   * previous call with this workspace, so the bf16 copy of the items in the workspace is reused */
   int32_t reuse_item_prep;
   int32_t reserved_;
+  /* precision = 1 only, optional: int32[2] on the device, ADDED to by every call: [0] users whose
+   * candidates the error bound could not separate and that were therefore ranked by the exact
+   * path inside the call (results are exact either way), [1] such users beyond what the
+   * workspace can take over in one call -- their outputs are NOT written: the caller repeats the
+   * tile with precision = 0 when it finds [1] != 0 */
+  int32_t *tc_status;
 } cmf_eval_t;
 
 CMF_API size_t cmf_eval_workspace_bytes(int64_t n_users_tile, int64_t num_items_shard, int32_t D, int32_t k,
                                 int32_t precision);
 CMF_API int cmf_eval_tile(const cmf_eval_t *args, void *stream);
+/* Facts about the precision = 1 path for measurement: out[0] / out[1] = K extent the GEMM issues
+ * per output with one bf16 term (top-k / MAP@k only) / three terms (with the MRR counter);
+ * out[2] / out[3] = the error-bound coefficients c1 / c3. */
+CMF_API int cmf_eval_tc_info(int32_t D, double *out);
 
 /*
  * cmf_eval_tile without a caller-provided workspace. (No counterpart in the reference: Collie's
@@ -418,7 +430,8 @@ CMF_API int cmf_gather_probe(const void *table, const int32_t *idx, int64_t n_id
  * widest lane group per row in the generic fused kernel (8, 16 or 32); key 2: kernel choice
  * (0 automatic, 1 generic fused kernel, 2 split k_fwd_loss + k_bwd_update); key 3: experiments on
  * the tensor-core evaluation kernel (0 = off; 1 = skip the ranking, 2 = skip the inserts: timing
- * only, results are then meaningless); key 6: programmatic dependent launch of k_bwd_update and
+ * only, results are then meaningless); key 4: bf16 terms of the tensor-core evaluation (0 =
+ * automatic: 1 without the MRR counter, 3 with it; 1 or 3 = forced, results stay exact); key 6: programmatic dependent launch of k_bwd_update and
  * k_update_rows (0 = plain stream order, the default; 1 = on: 1 % faster steps when nothing else
  * shares the GPU, slower pipelines when other streams need SMs between the step's kernels). Results do not depend on keys 0-2 and 6 beyond fp32 summation
  * order; tests use them to cross-check the in-place and the accumulate paths. Returns the previous
