@@ -920,7 +920,10 @@ def eval_block(job, peaks, with_cpu):
             variants[label] = {'error': repr(e)[:300]}
             continue
         useful = flops / (dev_ms * 1e-3) / 1e12
+        from collie_b200 import metrics as M_
+        tc_status = dict(M_.LAST_TC_STATUS) if precision == 1 else None
         variants[label] = {
+            'tc_status_rank0': tc_status,
             'value': n_eval / (dev_ms * 1e-3), 'unit': 'users/s', 'ms': dev_ms,
             'e2e': {'value': n_eval / wall, 'unit': 'users/s',
                     'what': 'wall clock of the public call (evaluate_in_batches / '

@@ -11,11 +11,11 @@
 // mapk :144-198, mrr :201-240.
 //
 // Operands: x = hi + lo with hi = bf16(x), lo = bf16(x - hi).
-//   terms = 1 (top-k / MAP@k only):  A' = [Uh | bu_hi, bu_lo, 1, 1],  B' = [Ih | 1, 1, bi_hi, bi_lo]
-//     K' = D + 4: one bf16 product per element. |S~ - S| <= c1 |u| |i| + 2^-15 (|bu| + |bi|),
+//   terms = 1 (top-k / MAP@k only):  A' = [Uh | bu as 3 bf16 pieces, 1, 1, 1],  B' = [Ih | 1, 1, 1, bi as 3 pieces]
+//     K' = D + 6: one bf16 product per element. |S~ - S| <= c1 |u| |i| + 2^-20 (|bu| + |bi|),
 //     c1 = 4.1e-3 (2^-8 for the two roundings, Cauchy-Schwarz over d, plus both accumulations).
 //   terms = 3 (with the MRR counter): A' = [Uh | Uh | Ul | ...], B' = [Ih | Il | Ih | ...],
-//     K' = 3 D + 4, S~ = Uh.Ih + Uh.Il + Ul.Ih: c3 = 8e-5 (3 * 2^-18 for the dropped terms, the
+//     K' = 3 D + 6, S~ = Uh.Ih + Uh.Il + Ul.Ih: c3 = 8e-5 (3 * 2^-18 for the dropped terms, the
 //     rest for fp32 accumulation of 3 D + 4 products), a band of a few items per user.
 //   Per user the margin uses the largest item norm of the shard: E_u = c |u| max|i| + ...
 //
@@ -49,6 +49,7 @@ constexpr int TC_BN = 256;        // items per MMA tile (one instruction: M = 12
 constexpr int TC_BK = 64;         // bf16 per K block = one 128-byte swizzle row
 constexpr int TC_STAGES = 3;
 constexpr int TC_MAXK = 16;       // largest k
+constexpr int TC_BIAS_SLOTS = 6;   // K slots that carry the two biases (three bf16 pieces each)
 constexpr int TC_BCAP = 16;       // band entries kept per (user, slot) for the MRR counter
 constexpr int TC_A_BYTES = TC_BM * TC_BK * 2;   // 16 KB: one K-block of the user tile
 constexpr int TC_B_BYTES = TC_BN * TC_BK * 2;   // 32 KB: one K-block of an item tile
@@ -202,12 +203,12 @@ __device__ __forceinline__ void split_bf16(float x, __nv_bfloat16& hi, __nv_bflo
 // sends a few more items to the exact re-scoring, one that is too small breaks parity.
 constexpr float kTcC1 = 4.1e-3f;
 constexpr float kTcC3 = 8.0e-5f;
-constexpr float kTcCBias = 3.0517578125e-5f;   // 2^-15
+constexpr float kTcCBias = 9.5367431640625e-7f;   // 2^-20: the biases are exact, their sums are not
 
 // rows of `src` (optionally gathered through `ids`) -> bf16 rows of length Kp, T = 1 or 3 terms:
-//   T = 3  items: [hi | lo | hi | 1, 1, bi_hi, bi_lo | 0...]   users: [hi | hi | lo | bu_hi, bu_lo, 1, 1 | 0...]
-//   T = 1  items: [hi | 1, 1, bi_hi, bi_lo | 0...]             users: [hi | bu_hi, bu_lo, 1, 1 | 0...]
-// so the GEMM yields  <u, i> + bu + bi  directly (the biases are split like the rows). Rows
+//   T = 3  items: [hi | lo | hi | 1, 1, 1, bi x3 | 0...]   users: [hi | hi | lo | bu x3, 1, 1, 1 | 0...]
+//   T = 1  items: [hi | 1, 1, 1, bi x3 | 0...]             users: [hi | bu x3, 1, 1, 1 | 0...]
+// so the GEMM yields  <u, i> + bu + bi  directly (each bias as three bf16 pieces: exact). Rows
 // >= n_rows are zero. Also the row's L2 norm and |bias| (users: per row; items: the maximum over
 // the shard, by atomicMax on the bit pattern of a non-negative float).
 // One warp per row; a lane produces two adjacent bf16 at a time (one 4-byte store, 128 bytes per
@@ -221,12 +222,18 @@ __device__ __forceinline__ __nv_bfloat16 tc_split_elem(const float* __restrict__
     const bool want_lo = T == 3 && (users ? (seg == 2) : (seg == 1));
     return want_lo ? lo : hi;
   }
-  if (c < T * D + 4) {
+  if (c < T * D + TC_BIAS_SLOTS) {
+    // the bias as THREE bf16 pieces (24 mantissa bits: the whole fp32 value) against 1.0, so the
+    // biases enter the accumulator exactly; users own the first three slots, items the last three
     const int q = c - T * D;
-    __nv_bfloat16 hi, lo;
-    split_bf16(b, hi, lo);
-    const bool own = users ? (q < 2) : (q >= 2);     // own bias in two slots, 1.0 in the others
-    return own ? ((q & 1) ? lo : hi) : __float2bfloat16_rn(1.f);
+    const bool own = users ? (q < 3) : (q >= 3);
+    if (!own) return __float2bfloat16_rn(1.f);
+    const __nv_bfloat16 p0 = __float2bfloat16_rn(b);
+    const float r1 = b - __bfloat162float(p0);
+    const __nv_bfloat16 p1 = __float2bfloat16_rn(r1);
+    const __nv_bfloat16 p2 = __float2bfloat16_rn(r1 - __bfloat162float(p1));
+    const int piece = q % 3;
+    return piece == 0 ? p0 : (piece == 1 ? p1 : p2);
   }
   return __float2bfloat16_rn(0.f);
 }
@@ -901,8 +908,8 @@ struct TcLayout {
 // (the layout is sized for three terms, so one workspace serves both forms)
 static TcLayout tc_layout(int64_t n_users, int64_t n_items, int D, int k, int terms) {
   TcLayout L;
-  const int Kp_max = (int)align_up((size_t)3 * D + 4, TC_BK);
-  L.Kp = (int)align_up((size_t)terms * D + 4, TC_BK);   // + the bias slots
+  const int Kp_max = (int)align_up((size_t)3 * D + TC_BIAS_SLOTS, TC_BK);
+  L.Kp = (int)align_up((size_t)terms * D + TC_BIAS_SLOTS, TC_BK);
   L.KB = L.Kp / TC_BK;
   L.KL = tc_list_len(k);
   L.m_tiles = (int)((n_users + TC_BM - 1) / TC_BM);
@@ -1023,7 +1030,7 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
 
   TcParams p{};
   p.n_users = (int)a->n_users_tile; p.k = a->k; p.KB = L.KB; p.n_tiles = L.n_tiles;
-  p.last_steps = (terms * a->D + 4 - (L.KB - 1) * TC_BK + 15) / 16;
+  p.last_steps = (terms * a->D + TC_BIAS_SLOTS - (L.KB - 1) * TC_BK + 15) / 16;
   p.m_tiles = L.m_tiles; p.n_slots = L.n_slots; p.chunk = L.chunk; p.total_work = L.total_work;
   p.want_mrr = mrr ? 1 : 0;
   p.n_items = a->num_items_shard; p.item_offset = a->item_offset; p.debug = g_tc_debug;
@@ -1092,8 +1099,8 @@ using namespace cmf;
 
 extern "C" int cmf_eval_tc_info(int32_t D, double* out /* [4] */) {
   CMF_REQUIRE(out && D >= 1, "cmf_eval_tc_info: bad arguments");
-  out[0] = (double)(((D + 4) + 15) / 16 * 16);        // K extent issued per output, 1 term
-  out[1] = (double)(((3 * D + 4) + 15) / 16 * 16);    // ... 3 terms
+  out[0] = (double)(((D + TC_BIAS_SLOTS) + 15) / 16 * 16);        // K extent issued per output, 1 term
+  out[1] = (double)(((3 * D + TC_BIAS_SLOTS) + 15) / 16 * 16);    // ... 3 terms
   out[2] = (double)kTcC1;
   out[3] = (double)kTcC3;
   return CMF_OK;

@@ -20,6 +20,8 @@ from .interactions import Interactions
 _TILE_USERS = 512
 _MAX_TILE_BYTES = 1 << 30
 _TC_TILE_USERS = 32768   # users per tensor-core call (128-user CTA tiles inside)
+# what the last tensor-core evaluation reported (see cmf_eval_t.tc_status): informative
+LAST_TC_STATUS = {}
 
 
 def _targets_device(targets: csr_matrix, user_ids, device):
@@ -270,6 +272,8 @@ def evaluate_in_batches(metric_list, test_interactions, model, k=10, batch_size=
         if status is not None:
             # one read-back for the whole evaluation: the metric sums and the tensor-core status
             host = torch.cat([sums, status.double()]).tolist()
+            LAST_TC_STATUS.update(users=n_test, handed_to_exact_path=int(host[-2]),
+                                  not_taken_over=int(host[-1]))
             if host[-1] != 0:
                 # more users than one call can hand to the exact path had candidates the error
                 # bound could not separate (heavily tied scores): the exact path takes it all

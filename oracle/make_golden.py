@@ -237,6 +237,38 @@ def split_case(seed, n_users=40, n_items=70, n=900):
     return out
 
 
+def checkpoint_case(seed, n_users=37, n_items=53, dim=16):
+    """A checkpoint WRITTEN BY THE REFERENCE (``save_model``, base_pipeline.py:880-900) after one
+    training epoch, its tables, and its own predictions for a few pairs: what ``load_model_path=``
+    of the B200 model must read back (tests/golden/reference_checkpoint.pth)."""
+    from collie.model import CollieMinimalTrainer
+    rng = np.random.default_rng(seed)
+    torch.manual_seed(seed)
+    users, items = synthetic_pairs(rng, n_users, n_items, 500)
+    train = Interactions(users=users, items=items, ratings=np.ones(len(users)),
+                         num_negative_samples=4, num_users=n_users, num_items=n_items,
+                         allow_missing_ids=True, remove_duplicate_user_item_pairs=False,
+                         check_num_negative_samples_is_valid=False)
+    model = MatrixFactorizationModel(train=train, embedding_dim=dim, sparse=False, lr=1e-2,
+                                     bias_lr=5e-2, optimizer='adam', bias_optimizer='sgd',
+                                     loss='adaptive_hinge', lr_scheduler_func=None)
+    trainer = CollieMinimalTrainer(model, max_epochs=1, gpus=0, logger=None, verbosity=0,
+                                   enable_model_summary=False)
+    trainer.fit(model)
+    model.eval()
+    model.save_model(os.path.join(OUT, 'reference_checkpoint.pth'))
+    pu = rng.integers(0, n_users, 64)
+    pi = rng.integers(0, n_items, 64)
+    with torch.no_grad():
+        preds = model(torch.from_numpy(pu), torch.from_numpy(pi)).numpy()
+    out = {'pred_users': pu, 'pred_items': pi, 'preds': preds,
+           'hparams_keys': np.array(sorted(model.hparams.keys())),
+           'num_epochs_completed': int(model.hparams.num_epochs_completed)}
+    for k, v in state(model).items():
+        out[k] = v
+    return out
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     cases = {
@@ -261,8 +293,14 @@ def main():
         'metrics_exact_grid': metrics_case(42, exact_grid=True),
         'metrics_d128': metrics_case(43, n_users=64, n_items=333, dim=128, n_test=700),
     }
-    if len(sys.argv) > 1 and sys.argv[1] == 'similarity':     # only the cases added later
+    if len(sys.argv) > 1 and sys.argv[1] in ('similarity', 'checkpoint'):   # the cases added later
         cases = {}
+    if len(sys.argv) > 1 and sys.argv[1] == 'checkpoint':
+        cases = {'reference_checkpoint': checkpoint_case(71)}
+        for name, arrays in cases.items():
+            np.savez_compressed(os.path.join(OUT, name + '.npz'), **arrays)
+            print(name, 'ok')
+        return
     cases['splits'] = split_case(61)
     cases['similarity_random'] = similarity_case(51)
     cases['similarity_d128'] = similarity_case(52, n_users=40, n_items=90, dim=128)

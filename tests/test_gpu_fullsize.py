@@ -186,13 +186,16 @@ def test_evaluation_paths_agree_at_full_item_count(world):
             e = min(s + tile, n_u)
             res = M._eval_tile('cuda', e - s, N_ITEMS, 10, indptr[s:e + 1], items,
                                {'topk', 'mapk', 'mrr'}, tables=tabs, user_ids=users[s:e],
-                               precision=precision)
+                               precision=precision, tc_status=status if precision else None)
             for name in tot:
                 tot[name] += M._per_user(name, res, nnz[s:e], N_ITEMS).sum().item()
             keep.append((res['topk_ids'].clone(), res['topk_scores'].clone()))
         return tot, keep
+    status = torch.zeros(2, dtype=torch.int32, device='cuda')
     exact, k0 = run(0, 256)
     tc, k1 = run(1, n_u)
+    # (users handed to the exact path inside the call: a few at most; none left over)
+    assert int(status[1]) == 0 and int(status[0]) <= n_u // 100, status.tolist()
     for name in exact:
         np.testing.assert_allclose(tc[name], exact[name], rtol=1e-12)
     scores = k1[0][1]

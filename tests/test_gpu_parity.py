@@ -571,6 +571,9 @@ def test_tensor_core_eval_matches_exact_path(shape):
         tc = M._eval_tile('cuda', n_users, n_items, k, indptr, items, want, tables=tabs,
                           user_ids=users, precision=1, tc_status=status)
         assert int(status[1]) == 0
+        # ... and by the tensor-core route itself: the exact path may take over the odd user whose
+        # scores are too close to call, not the fixture
+        assert int(status[0]) <= max(2, n_users // 20), status.tolist()
         assert torch.equal(tc['topk_ids'], ex['topk_ids'])
         assert torch.equal(tc['topk_scores'], ex['topk_scores'])
         assert torch.equal(tc['ap'], ex['ap'])
