@@ -19,11 +19,16 @@ constexpr int TM = 64, TN = 64, TK = 16;
 __global__ void __launch_bounds__(256)
 k_score_tile(const float* __restrict__ U, const float* __restrict__ I, const float* __restrict__ bu,
              const float* __restrict__ bi, int D, const int32_t* __restrict__ user_ids, int64_t n_users,
-             int64_t item_offset, int64_t n_items, float* __restrict__ out, int64_t ld_out) {
+             int64_t item_offset, int64_t n_items, float* __restrict__ out, int64_t ld_out,
+             const int32_t* __restrict__ n_users_dev) {
   __shared__ float As[TK][TM + 4];
   __shared__ float Bs[TK][TN + 4];
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;  // 16 x 16 threads, 4x4 outputs each
   const int64_t row0 = (int64_t)blockIdx.y * TM, col0 = (int64_t)blockIdx.x * TN;
+  if (n_users_dev) {   // the row count lives on the device (the tensor-core path's hand-over)
+    if ((int64_t)*n_users_dev < n_users) n_users = *n_users_dev;
+    if (row0 >= n_users) return;
+  }
   float acc[4][4] = {};
   // loader mapping: 256 threads fetch 64 rows x 16 k-values; thread -> (row = t / 4, 4 k's)
   const int lr = threadIdx.x >> 2, lk = (threadIdx.x & 3) * 4;
@@ -73,12 +78,17 @@ __global__ void __launch_bounds__(256)
 k_score_tile_128(const float* __restrict__ U, const float* __restrict__ I,
                  const float* __restrict__ bu, const float* __restrict__ bi, int D,
                  const int32_t* __restrict__ user_ids, int64_t n_users, int64_t item_offset,
-                 int64_t n_items, float* __restrict__ out, int64_t ld_out) {
+                 int64_t n_items, float* __restrict__ out, int64_t ld_out,
+                 const int32_t* __restrict__ n_users_dev) {
   __shared__ __align__(16) float As[2][BK][BM];
   __shared__ __align__(16) float Bs[2][BK][BN];
   const int tid = threadIdx.x;
   const int tx = tid & 15, ty = tid >> 4;
   const int64_t row0 = (int64_t)blockIdx.y * BM, col0 = (int64_t)blockIdx.x * BN;
+  if (n_users_dev) {
+    if ((int64_t)*n_users_dev < n_users) n_users = *n_users_dev;
+    if (row0 >= n_users) return;
+  }
   // loader: thread -> (row = tid / 2, four consecutive k's)
   const int lr = tid >> 1, lk = (tid & 1) * 4;
   const int64_t arow = row0 + lr, brow = col0 + lr;
@@ -399,16 +409,27 @@ static size_t eval_ws_scores(int64_t n, int64_t items) { return align_up(sizeof(
 // 128 x 128 tiles when the user tile fills them, else the 64 x 64 kernel (identical results)
 static void launch_score_tile(const float* U, const float* I, const float* bu, const float* bi,
                               int D, const int32_t* user_ids, int64_t n_users, int64_t item_offset,
-                              int64_t n_items, float* out, int64_t ld_out, cudaStream_t s) {
+                              int64_t n_items, float* out, int64_t ld_out, cudaStream_t s,
+                              const int32_t* n_users_dev = nullptr) {
   if (n_users >= 96 && n_items >= 96) {
     dim3 grid((unsigned)((n_items + BN - 1) / BN), (unsigned)((n_users + BM - 1) / BM));
     k_score_tile_128<<<grid, 256, 0, s>>>(U, I, bu, bi, D, user_ids, n_users, item_offset, n_items,
-                                          out, ld_out);
+                                          out, ld_out, n_users_dev);
   } else {
     dim3 grid((unsigned)((n_items + TN - 1) / TN), (unsigned)((n_users + TM - 1) / TM));
     k_score_tile<<<grid, 256, 0, s>>>(U, I, bu, bi, D, user_ids, n_users, item_offset, n_items, out,
-                                      ld_out);
+                                      ld_out, n_users_dev);
   }
+}
+
+// exact scores of up to `cap` users whose number is only known on the device (both score kernels
+// give the same bits, so the tile shape does not matter)
+int launch_score_rows_counted(const cmf_eval_t* a, const int32_t* user_ids, int cap,
+                              const int32_t* count, float* out, cudaStream_t s) {
+  launch_score_tile(a->U, a->I, a->bu, a->bi, a->D, user_ids, cap, a->item_offset,
+                    a->num_items_shard, out, a->num_items_shard, s, count);
+  CMF_LAUNCH_CHECK();
+  return CMF_OK;
 }
 
 static RankDev rank_args(const cmf_eval_t* a, const float* S, float* sig) {

@@ -179,6 +179,15 @@ __device__ __forceinline__ uint64_t smem_desc_from_lo(uint32_t lo) {
 constexpr uint32_t kIdescBf16 =
     (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
 
+// a - b as one FFMA (b * -1 + a: the same bits as the subtraction). On sm_100 FADD issues on the
+// alu pipe, where the funnel shifts of the mask pass already are; FFMA with an immediate
+// multiplier issues on the fma pipe at twice the rate, so the pass is no longer alu-bound.
+__device__ __forceinline__ float sub_on_fma_pipe(float a, float b) {
+  float d;
+  asm("fma.rn.f32 %0, %1, 0fBF800000, %2;" : "=f"(d) : "f"(b), "f"(a));
+  return d;
+}
+
 // v[j] for a run-time j without spilling v to local memory (whose traffic would compete with the
 // MMA's operand reads for the shared-memory pipe): a 5-level select tree, 31 selects
 __device__ __forceinline__ float pick32(const float (&v)[32], int j) {
@@ -362,6 +371,17 @@ k_tc_target_best(const float* __restrict__ U, const float* __restrict__ I,
   if (lane == 0) { best_s[r] = bs; best_id[r] = bid; }
 }
 
+// order-preserving 32-bit pattern of a float (larger float -> larger uint; -inf -> smallest used)
+__device__ __forceinline__ uint32_t tc_score_key_u32(float s) {
+  const uint32_t u = __float_as_uint(s + 0.0f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float tc_key_score_u32(uint32_t u) {
+  if (u == 0) return -INFINITY;      // (the array starts zeroed)
+  u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+  return __uint_as_float(u);
+}
+
 // ---------------------------------------------------------------------------------- GEMM + top-k
 struct TcParams {
   int n_users, k, KB, n_tiles, m_tiles, n_slots, want_mrr, debug;
@@ -371,11 +391,13 @@ struct TcParams {
   const float* best_s;   // exact score of the user's best target (MRR), may be NULL
   const int32_t* best_id;
   const float* margin;   // E_u per user row
+  uint32_t* thr_g;       // [n_users_pad] the row's filter threshold shared by all its segments
   float* cand_s;         // [n_users_pad][n_slots][KL]
   int32_t* cand_i;
   int32_t* cnt;          // [n_users_pad][n_slots] items surely ranked before the best target
   int32_t* bcnt;         // [n_users_pad][n_slots] items in the band around it (may exceed TC_BCAP)
   int32_t* band_i;       // [n_users_pad][n_slots][TC_BCAP] their ids
+  unsigned long long* dbg;   // experiments (debug == 4): [0] list insertions, [1] insert-loop rounds
 };
 
 // The (user tile, item tile) pairs are numbered m * n_tiles + n and cut into equal contiguous
@@ -385,11 +407,12 @@ __device__ __forceinline__ int tc_slot(int64_t lin_start, int m, int n_tiles, in
   return (int)(lin_start / chunk - ((int64_t)m * n_tiles) / chunk);
 }
 
-constexpr int TC_EPI_WARPS = 8;   // two per scheduler; each pair splits a tile's columns in halves
-constexpr int TC_THREADS = 128 + 32 * TC_EPI_WARPS;
-
-template <int KL>   // per-row list length kept in registers, > k
-__global__ void __launch_bounds__(TC_THREADS, 1)
+// EW epilogue warps (8 or 16): EW / 4 per scheduler, each takes 1 / (EW / 4) of a tile's columns.
+// The epilogue is bound by issue latency, not by instruction count (two instructions per score on
+// two different pipes): four warps per scheduler keep both pipes fed where two leave them idle
+// more than half of the time. Sixteen warps leave 96 registers per thread: lists up to KL = 16.
+template <int KL, int EW>   // KL = per-row list length kept in registers, > k
+__global__ void __launch_bounds__(128 + 32 * EW, 1)
 k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const TcParams p) {
   extern __shared__ unsigned char smem_raw[];
@@ -417,7 +440,7 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     for (int i = 0; i < TC_STAGES; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); }
     mbar_init(bar_a, 1);
     mbar_init(bar_afree, 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(bar_tfull + 8 * i, 1); mbar_init(bar_tempty + 8 * i, TC_EPI_WARPS); }
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_tfull + 8 * i, 1); mbar_init(bar_tempty + 8 * i, EW); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -516,13 +539,15 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp >= 4) {
     // ===================================================================== epilogue
     const int q = warp & 3;               // TMEM lane quarter this warp may read
-    const int half = (warp - 4) >> 2;     // which half of every tile's columns
+    constexpr int NSUB = EW / 4;          // column parts of a tile, one per warp of a quarter
+    constexpr int SUBW = TC_BN / NSUB;    // columns per part (128 or 64)
+    const int sub = (warp - 4) >> 2;      // which part of every tile's columns
     const int row = q * 32 + lane;        // user row inside the tile
     int t = 0;
     for (int64_t w = w_lo; w < w_hi;) {
       const int m = (int)(w / p.n_tiles);
       const int64_t seg_hi = min(w_hi, (int64_t)(m + 1) * p.n_tiles);
-      const int slot = tc_slot(w, m, p.n_tiles, p.chunk) * 2 + half;
+      const int slot = tc_slot(w, m, p.n_tiles, p.chunk) * NSUB + sub;
       const int urow = m * TC_BM + row;
       const bool valid = urow < p.n_users;
       // the row's best KL so far, sorted (score desc, id asc), in registers; thr = the last one
@@ -530,7 +555,15 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int li[KL];
 #pragma unroll
       for (int e = 0; e < KL; ++e) { ls[e] = -INFINITY; li[e] = -1; }
-      float thr = -INFINITY;
+      // The filter threshold of the row is shared by everybody who works on it (the other column
+      // parts, other CTAs' segments) through one word per row: whoever raises its own KL-th best
+      // publishes it (atomicMax on the order-preserving bit pattern), everybody picks the
+      // largest up once per item tile. An item below ANY list's KL-th best cannot be among the
+      // best KL of the row, so skipping it is safe, and the lists fill more slowly than with
+      // private thresholds. k_tc_finish takes the final value of the word as the bound on
+      // everything outside the lists.
+      float thr = -INFINITY, thr_pub = -INFINITY;
+      uint32_t* thr_word = p.thr_g + urow;
       // MRR: x > t_hi is surely ranked before the best target, x < t_lo surely after it; what
       // lies between cannot be told from it with these scores and is re-scored by k_tc_finish
       const bool mrr = p.want_mrr && valid && p.best_id[urow] >= 0;
@@ -542,6 +575,7 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       int before = 0, nband = 0;
       int32_t* band = p.band_i + ((int64_t)urow * p.n_slots + slot) * TC_BCAP;
+      unsigned dbg_ins = 0, dbg_rounds = 0;
 
       for (; w < seg_hi; ++w, ++t) {
         const int acc = t & 1;
@@ -549,37 +583,38 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_wait(bar_tfull + 8 * acc, (t >> 1) & 1);
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) +
-                               (uint32_t)(acc * TC_BN + half * (TC_BN / 2));
+                               (uint32_t)(acc * TC_BN + sub * SUBW);
         const int ncols = (int)min((int64_t)TC_BN, p.n_items - n0);   // < TC_BN only in the last tile
         const int gid0 = (int)(p.item_offset + n0);
-        // 64 columns at a time go to registers; the accumulator is handed back as soon as the
+        {
+          uint32_t w_;
+          asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(w_) : "l"(thr_word) : "memory");
+          thr = fmaxf(thr, tc_key_score_u32(w_));
+        }
+        // 32 columns at a time go to registers; the accumulator is handed back as soon as the
         // last of them has been read, before they are ranked
 #pragma unroll 1
-        for (int pp = 0; pp < TC_BN / 128; ++pp) {
-        float v[2][32];
-        tmem_ld32_nowait(taddr + pp * 64, v[0]);
-        tmem_ld32_nowait(taddr + pp * 64 + 32, v[1]);
-        tmem_wait_ld(v[0]);
-        tmem_ld_dep(v[1]);
-        if (pp == TC_BN / 128 - 1) {
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
-        }
-        if (p.debug == 1) continue;
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const int c0 = half * (TC_BN / 2) + pp * 64 + h * 32;
+        for (int g = 0; g < SUBW / 32; ++g) {
+          float v[32];
+          tmem_ld32_nowait(taddr + g * 32, v);
+          tmem_wait_ld(v);
+          if (g == SUBW / 32 - 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+          }
+          if (p.debug == 1) continue;
+          const int c0 = sub * SUBW + g * 32;
           // branch-free pass: bit j of each mask = predicate of column c0 + j. x > y <=> the sign
           // bit of (y - x) (no flush-to-zero here, so a nonzero difference keeps its sign; equal
           // values give +0), and one funnel shift moves that bit into the mask: two instructions
-          // per column and mask, in four independent chains
+          // per column and mask (one on the fma pipe, one on the alu pipe), four independent chains
           uint32_t mi[4] = {0, 0, 0, 0};
 #pragma unroll
           for (int j = 7; j >= 0; --j) {
 #pragma unroll
             for (int c = 0; c < 4; ++c)
-              mi[c] = __funnelshift_l(__float_as_uint(thr - v[h][8 * c + j]), mi[c], 1);
+              mi[c] = __funnelshift_l(__float_as_uint(sub_on_fma_pipe(thr, v[8 * c + j])), mi[c], 1);
           }
           uint32_t m_ins = mi[0] | (mi[1] << 8) | (mi[2] << 16) | (mi[3] << 24);
           const int left = ncols - c0;
@@ -591,9 +626,9 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             for (int j = 7; j >= 0; --j) {
 #pragma unroll
               for (int c = 0; c < 4; ++c) {
-                const float x = v[h][8 * c + j];
-                mg[c] = __funnelshift_l(__float_as_uint(t_hi - x), mg[c], 1);   // x > t_hi
-                ml[c] = __funnelshift_l(__float_as_uint(x - t_lo), ml[c], 1);   // x < t_lo
+                const float x = v[8 * c + j];
+                mg[c] = __funnelshift_l(__float_as_uint(sub_on_fma_pipe(t_hi, x)), mg[c], 1);   // x > t_hi
+                ml[c] = __funnelshift_l(__float_as_uint(sub_on_fma_pipe(x, t_lo)), ml[c], 1);   // x < t_lo
               }
             }
             const uint32_t m_gt = mg[0] | (mg[1] << 8) | (mg[2] << 16) | (mg[3] << 24);
@@ -611,13 +646,13 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (p.debug == 2) m_ins &= 1u;   // experiments: (almost) no inserts
           // lanes insert side by side, each its own next candidate (column j differs per lane)
           while (__any_sync(0xffffffffu, m_ins != 0)) {
+            ++dbg_rounds;
             if (m_ins) {
               const int j = __ffs(m_ins) - 1;
               m_ins &= m_ins - 1;
-              const float sc = pick32(v[h], j);
+              const float sc = pick32(v, j);
               if (sc > thr) {     // thr may have risen within the chunk
-                // sorted insert; an equal score stays behind the entries already there (ids
-                // only grow along a segment), which is the canonical order
+                // sorted insert; an equal score stays behind the entries already there
                 float cs = sc;
                 int ci = gid0 + c0 + j;
                 bool up = false;   // sticky: below the insertion point everything shifts down
@@ -631,12 +666,20 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                   cs = up ? os : cs;
                   ci = up ? oi : ci;
                 }
-                thr = ls[KL - 1];
+                thr = fmaxf(thr, ls[KL - 1]);
+                ++dbg_ins;
               }
             }
           }
         }
+        if (thr > thr_pub) {      // publish a raised threshold once per item tile
+          atomicMax(thr_word, tc_score_key_u32(thr));
+          thr_pub = thr;
         }
+      }
+      if (p.debug == 4) {
+        atomicAdd(p.dbg + 0, (unsigned long long)dbg_ins);
+        if (lane == 0) atomicAdd(p.dbg + 1, (unsigned long long)dbg_rounds);
       }
       if (valid) {
         float* cs = p.cand_s + ((int64_t)urow * p.n_slots + slot) * KL;
@@ -689,6 +732,7 @@ struct TcFinish {
   int n_slots, KL, k, D, want_mrr;
   int64_t n_users;
   const float* margin;
+  const uint32_t* thr_g;
   const float *U, *I, *bu, *bi;
   const int32_t* user_ids;
   const int64_t* tgt_indptr;
@@ -699,7 +743,8 @@ struct TcFinish {
   float* topk_scores;
   double* ap;
   int32_t* n_before_best;
-  int32_t* fb_list;     // users handed to the exact path
+  int32_t* fb_list;     // users handed to the exact path (rows of the tile) ...
+  int32_t* fb_uid;      // ... and their user ids
   int32_t* status;      // [0] their number, [1] how many did not fit into fb_list
   int fb_cap;
 };
@@ -744,11 +789,8 @@ k_tc_finish(const TcFinish p) {
     prev = best;
     ++found;
   }
-  float T = -INFINITY;
-  for (int sl = lane; sl < p.n_slots; sl += 32)
-    if (ci[sl * p.KL + p.KL - 1] >= 0) T = fmaxf(T, cs[sl * p.KL + p.KL - 1]);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) T = fmaxf(T, __shfl_xor_sync(0xffffffffu, T, o));
+  // everything outside the lists was filtered out or pushed out at or below this value
+  const float T = tc_key_score_u32(p.thr_g[r]);
   const float thresh = found == p.k ? tc_key_score(prev) - 2.f * E : -INFINITY;
   if (!(T < thresh) && T != -INFINITY) fallback = true;
   // ---- MRR ingredients (before anything is written: a band that overflowed also falls back)
@@ -786,7 +828,7 @@ k_tc_finish(const TcFinish p) {
   if (fallback) {
     if (lane == 0) {
       const int at = atomicAdd(p.status + 0, 1);
-      if (at < p.fb_cap) p.fb_list[at] = (int32_t)r;
+      if (at < p.fb_cap) { p.fb_list[at] = (int32_t)r; p.fb_uid[at] = (int32_t)p.user_ids[r]; }
       else atomicAdd(p.status + 1, 1);
     }
     return;
@@ -841,24 +883,11 @@ k_tc_finish(const TcFinish p) {
   }
 }
 
-// exact scores of the users handed to the exact path: one CTA per such user, fb_scores[b][c]
-__global__ void __launch_bounds__(256)
-k_tc_fb_scores(const float* __restrict__ U, const float* __restrict__ I,
-               const float* __restrict__ bu, const float* __restrict__ bi, int D,
-               const int32_t* __restrict__ user_ids, int64_t item_offset, int64_t n_items,
-               const int32_t* __restrict__ fb_list, const int32_t* __restrict__ status, int fb_cap,
-               float* __restrict__ fb_scores) {
-  const int n_fb = min(status[0], fb_cap);
-  if ((int)blockIdx.x >= n_fb) return;
-  const int64_t u = user_ids[fb_list[blockIdx.x]];
-  const float ub = bu[u];
-  float* out = fb_scores + (int64_t)blockIdx.x * n_items;
-  for (int64_t c = threadIdx.x; c < n_items; c += blockDim.x)
-    out[c] = tc_exact_score(U + u * D, I + (item_offset + c) * D, D, ub, bi[item_offset + c]);
-}
-
-__global__ void k_tc_status_add(const int32_t* __restrict__ status, int32_t* __restrict__ out) {
+__global__ void k_tc_status_add(const int32_t* __restrict__ status, int32_t* __restrict__ out,
+                                int with_dbg) {
   if (threadIdx.x < 2 && status[threadIdx.x]) atomicAdd(out + threadIdx.x, status[threadIdx.x]);
+  // experiments: the caller's array is int32[8] then; [4..7] = two 64-bit counters of the last call
+  if (with_dbg && threadIdx.x >= 4 && threadIdx.x < 8) out[threadIdx.x] = status[threadIdx.x];
 }
 
 // ---------------------------------------------------------------------------------- host side
@@ -896,13 +925,19 @@ static int make_map(CUtensorMap* map, void* base, int64_t rows, int Kp, int box_
 
 int g_tc_terms = 0;   // cmf_set_tuning key 4: 0 = automatic (1 without the MRR counter, else 3)
 
-static int tc_list_len(int k) { return k <= 4 ? 8 : (k <= 10 ? 16 : 24); }
+int g_tc_epi_warps = 0;  // cmf_set_tuning key 7: 0 = automatic, 8 or 16 epilogue warps
+int g_tc_list_len = 0;   // cmf_set_tuning key 5: 0 = automatic, else 8 / 16 / 24 (must exceed k)
+
+static int tc_list_len(int k) {
+  if (g_tc_list_len > k) return g_tc_list_len;
+  return k <= 4 ? 8 : (k <= 10 ? 16 : 24);
+}
 
 struct TcLayout {
-  int Kp, KB, KL, m_tiles, n_tiles, n_ctas, n_slots, fb_cap;
+  int Kp, KB, KL, epi_warps, m_tiles, n_tiles, n_ctas, n_slots, fb_cap;
   int64_t m_pad, chunk, total_work;
-  size_t Bp, Ap, unorm, uabsb, margin, stats, best_s, best_id, cand_s, cand_i, cnt, bcnt, band_i,
-      fb_list, status, fb_scores, fb_sig, total;
+  size_t Bp, Ap, unorm, uabsb, margin, thr_g, stats, best_s, best_id, cand_s, cand_i, cnt, bcnt, band_i,
+      fb_list, fb_uid, status, fb_scores, fb_sig, total;
 };
 
 // (the layout is sized for three terms, so one workspace serves both forms)
@@ -921,8 +956,10 @@ static TcLayout tc_layout(int64_t n_users, int64_t n_items, int D, int k, int te
   if (ctas > L.total_work) ctas = L.total_work;
   L.chunk = (L.total_work + ctas - 1) / ctas;
   L.n_ctas = (int)((L.total_work + L.chunk - 1) / L.chunk);
-  // segments a user tile can be cut into (x 2: the epilogue keeps one list per column half)
-  L.n_slots = 2 * (int)((L.n_tiles + L.chunk - 1) / L.chunk + 1);
+  // segments a user tile can be cut into (x the column parts the epilogue keeps a list for)
+  // (measured: sixteen epilogue warps of 32-column groups are ~15 % slower than eight)
+  L.epi_warps = (g_tc_epi_warps == 16 && L.KL <= 16) ? 16 : 8;
+  L.n_slots = (L.epi_warps / 4) * (int)((L.n_tiles + L.chunk - 1) / L.chunk + 1);
   // users the exact path can take over per call: up to 64 MB of score rows
   int64_t cap = ((int64_t)64 << 20) / (int64_t)(sizeof(float) * (size_t)n_items);
   L.fb_cap = (int)(cap < 1 ? 1 : (cap > 256 ? 256 : cap));
@@ -934,6 +971,7 @@ static TcLayout tc_layout(int64_t n_users, int64_t n_items, int D, int k, int te
   L.unorm = take(sizeof(float) * L.m_pad);
   L.uabsb = take(sizeof(float) * L.m_pad);
   L.margin = take(sizeof(float) * L.m_pad);
+  L.thr_g = take(sizeof(uint32_t) * L.m_pad);
   L.stats = take(sizeof(uint32_t) * 8);     // [0..1] of the items split with 1 term, [2..3] with 3, [4] which one Bp holds
   L.best_s = take(sizeof(float) * L.m_pad);
   L.best_id = take(sizeof(int32_t) * L.m_pad);
@@ -943,6 +981,7 @@ static TcLayout tc_layout(int64_t n_users, int64_t n_items, int D, int k, int te
   L.bcnt = take(sizeof(int32_t) * L.m_pad * L.n_slots);
   L.band_i = take(sizeof(int32_t) * L.m_pad * L.n_slots * TC_BCAP);
   L.fb_list = take(sizeof(int32_t) * L.fb_cap);
+  L.fb_uid = take(sizeof(int32_t) * L.fb_cap);
   L.status = take(sizeof(int32_t) * 8);
   L.fb_scores = take(sizeof(float) * (size_t)L.fb_cap * n_items);
   L.fb_sig = take(2 * sizeof(float) * (size_t)L.fb_cap * n_items);
@@ -961,6 +1000,9 @@ size_t eval_tc_workspace_bytes(int64_t n_users, int64_t n_items, int D, int k) {
 int launch_rank_rows_mapped(const cmf_eval_t* a, const float* scores, float* sig_scratch,
                             const int32_t* row_map, const int32_t* row_count, int row_cap,
                             cudaStream_t s);
+// eval.cu: the exact path's score kernel over `cap` user ids of which only *count exist
+int launch_score_rows_counted(const cmf_eval_t* a, const int32_t* user_ids, int cap,
+                              const int32_t* count, float* out, cudaStream_t s);
 
 int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   CMF_REQUIRE(!a->want_auc, "cmf_eval_tile: AUC is computed by the exact path (precision = 0)");
@@ -1035,6 +1077,9 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   p.want_mrr = mrr ? 1 : 0;
   p.n_items = a->num_items_shard; p.item_offset = a->item_offset; p.debug = g_tc_debug;
   p.best_s = best_s; p.best_id = best_id; p.margin = margin;
+  p.thr_g = (uint32_t*)(base + L.thr_g);
+  p.dbg = (unsigned long long*)(status + 4);     // (status[4..7]; cleared with it)
+  CMF_CUDA(cudaMemsetAsync(p.thr_g, 0, sizeof(uint32_t) * L.m_pad, s));
   p.cand_s = (float*)(base + L.cand_s); p.cand_i = (int32_t*)(base + L.cand_i);
   p.cnt = (int32_t*)(base + L.cnt); p.bcnt = (int32_t*)(base + L.bcnt);
   p.band_i = (int32_t*)(base + L.band_i);
@@ -1049,45 +1094,46 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   }
   CMF_CUDA(cudaMemsetAsync(status, 0, sizeof(int32_t) * 8, s));
   // list length: the smallest instantiation that leaves a margin above k
-#define CMF_TC_LAUNCH(KL)                                                                        \
+#define CMF_TC_LAUNCH(KL, EW)                                                                    \
   do {                                                                                           \
-    CMF_CUDA(cudaFuncSetAttribute(k_tc_gemm_topk<KL>,                                            \
+    CMF_CUDA(cudaFuncSetAttribute(k_tc_gemm_topk<KL, EW>,                                        \
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));      \
-    k_tc_gemm_topk<KL><<<(unsigned)L.n_ctas, TC_THREADS, smem, s>>>(tmA, tmB, p);                \
+    k_tc_gemm_topk<KL, EW><<<(unsigned)L.n_ctas, 128 + 32 * EW, smem, s>>>(tmA, tmB, p);         \
   } while (0)
-  if (L.KL == 8) CMF_TC_LAUNCH(8);
-  else if (L.KL == 16) CMF_TC_LAUNCH(16);
-  else CMF_TC_LAUNCH(24);
+  if (L.KL == 8 && L.epi_warps == 16) CMF_TC_LAUNCH(8, 16);
+  else if (L.KL == 8) CMF_TC_LAUNCH(8, 8);
+  else if (L.KL == 16 && L.epi_warps == 16) CMF_TC_LAUNCH(16, 16);
+  else if (L.KL == 16) CMF_TC_LAUNCH(16, 8);
+  else CMF_TC_LAUNCH(24, 8);
 #undef CMF_TC_LAUNCH
   CMF_LAUNCH_CHECK();
 
   TcFinish f{};
   f.cand_s = p.cand_s; f.cand_i = p.cand_i; f.cnt = p.cnt; f.bcnt = p.bcnt; f.band_i = p.band_i;
   f.n_slots = L.n_slots; f.KL = L.KL; f.k = a->k; f.D = a->D; f.want_mrr = mrr ? 1 : 0;
-  f.n_users = a->n_users_tile; f.margin = margin;
+  f.n_users = a->n_users_tile; f.margin = margin; f.thr_g = p.thr_g;
   f.U = a->U; f.I = a->I; f.bu = a->bu; f.bi = a->bi; f.user_ids = a->user_ids;
   f.tgt_indptr = a->tgt_indptr; f.tgt_items = a->tgt_items;
   f.best_s = best_s; f.best_id = best_id;
   f.topk_ids = a->topk_ids; f.topk_scores = a->topk_scores; f.ap = a->ap;
   f.n_before_best = a->n_before_best;
-  f.fb_list = (int32_t*)(base + L.fb_list); f.status = status; f.fb_cap = L.fb_cap;
+  f.fb_list = (int32_t*)(base + L.fb_list); f.fb_uid = (int32_t*)(base + L.fb_uid);
+  f.status = status; f.fb_cap = L.fb_cap;
   k_tc_finish<<<(unsigned)((a->n_users_tile * 32 + 255) / 256), 256, 0, s>>>(f);
   CMF_LAUNCH_CHECK();
 
   // the users the bound could not settle: exact scores of their rows, ranked by the exact path's
   // own kernel (both grids are sized for fb_cap users and return at once when there are none)
   float* fb_scores = (float*)(base + L.fb_scores);
-  k_tc_fb_scores<<<(unsigned)L.fb_cap, 256, 0, s>>>(a->U, a->I, a->bu, a->bi, a->D, a->user_ids,
-                                                    a->item_offset, a->num_items_shard, f.fb_list,
-                                                    status, L.fb_cap, fb_scores);
-  CMF_LAUNCH_CHECK();
+  rc = launch_score_rows_counted(a, f.fb_uid, L.fb_cap, status, fb_scores, s);
+  if (rc) return rc;
   cmf_eval_t b = *a;
   if (mrr) { b.ext_best_score = best_s; b.ext_best_id = best_id; b.best_score = nullptr; b.best_id = nullptr; }
   rc = launch_rank_rows_mapped(&b, fb_scores, (float*)(base + L.fb_sig), f.fb_list, status,
                                L.fb_cap, s);
   if (rc) return rc;
   if (a->tc_status) {
-    k_tc_status_add<<<1, 32, 0, s>>>(status, a->tc_status);
+    k_tc_status_add<<<1, 32, 0, s>>>(status, a->tc_status, g_tc_debug == 4);
     CMF_LAUNCH_CHECK();
   }
   return CMF_OK;

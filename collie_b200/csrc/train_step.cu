@@ -28,6 +28,8 @@ namespace cmf {
 
 extern int g_tc_debug;
 extern int g_tc_terms;
+extern int g_tc_list_len;
+extern int g_tc_epi_warps;
 extern int g_pdl;
 
 struct WsLayout {
@@ -524,6 +526,19 @@ extern "C" int cmf_set_tuning(int32_t key, int32_t value) {
     CMF_REQUIRE(value == 0 || value == 1 || value == 3, "cmf_set_tuning: terms %d", value);
     const int prev = g_tc_terms;
     g_tc_terms = value;
+    return prev;
+  }
+  if (key == 5) {
+    CMF_REQUIRE(value == 0 || value == 8 || value == 16 || value == 24,
+                "cmf_set_tuning: list length %d", value);
+    const int prev = g_tc_list_len;
+    g_tc_list_len = value;
+    return prev;
+  }
+  if (key == 7) {
+    CMF_REQUIRE(value == 0 || value == 8 || value == 16, "cmf_set_tuning: epilogue warps %d", value);
+    const int prev = g_tc_epi_warps;
+    g_tc_epi_warps = value;
     return prev;
   }
   if (key == 6) {

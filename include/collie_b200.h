@@ -431,7 +431,8 @@ CMF_API int cmf_gather_probe(const void *table, const int32_t *idx, int64_t n_id
  * (0 automatic, 1 generic fused kernel, 2 split k_fwd_loss + k_bwd_update); key 3: experiments on
  * the tensor-core evaluation kernel (0 = off; 1 = skip the ranking, 2 = skip the inserts: timing
  * only, results are then meaningless); key 4: bf16 terms of the tensor-core evaluation (0 =
- * automatic: 1 without the MRR counter, 3 with it; 1 or 3 = forced, results stay exact); key 6: programmatic dependent launch of k_bwd_update and
+ * automatic: 1 without the MRR counter, 3 with it; 1 or 3 = forced, results stay exact); key 5: candidate-list length of the tensor-core
+ * evaluation (0 = automatic, 8 / 16 / 24; must exceed k); key 7: its epilogue warps (0 = automatic, 8 or 16); key 6: programmatic dependent launch of k_bwd_update and
  * k_update_rows (0 = plain stream order, the default; 1 = on: 1 % faster steps when nothing else
  * shares the GPU, slower pipelines when other streams need SMs between the step's kernels). Results do not depend on keys 0-2 and 6 beyond fp32 summation
  * order; tests use them to cross-check the in-place and the accumulate paths. Returns the previous
