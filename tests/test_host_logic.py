@@ -37,7 +37,7 @@ def test_argument_errors_without_gpu():
     assert lib.cmf_train_workspace_bytes(0, 5, 10, 10, 8) == 0
     assert lib.cmf_train_workspace_bytes(1024, 5, 100, 50, 16) > 0
     assert lib.cmf_eval_workspace_bytes(8, 50, 16, 10, 0) > 0
-    assert lib.cmf_set_tuning(7, 1) < 0
+    assert lib.cmf_set_tuning(99, 1) < 0
     assert b'unknown key' in lib.cmf_last_error()
     rc = lib.cmf_forward_scores(None, None, None, None, 8, None, None, 4, 0, None, None, None)
     assert rc == -1 and b'null' in lib.cmf_last_error()
