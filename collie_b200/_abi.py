@@ -206,3 +206,13 @@ def make_opt(rule, lr, step, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0):
     o.weight_decay = float(weight_decay)
     o.step = int(step)
     return o
+
+
+def on_device(device):
+    """Context that makes ``device`` the current CUDA device. The library keeps per-device state
+    (side streams, SM counts, the scratch of ``cmf_eval_tile_noalloc``) keyed by the CURRENT
+    device, so every call is made with the device that owns its tensors current."""
+    import contextlib
+    import torch
+    device = torch.device(device)
+    return torch.cuda.device(device) if device.type == 'cuda' else contextlib.nullcontext()

@@ -78,13 +78,18 @@ class BaseInteractions(torch.utils.data.Dataset):
                 _check_all_ids_present(mat.col, num_items, 'mat.shape[1]')
 
         if remove_duplicate_user_item_pairs:
-            # keep the LAST value of a duplicated (user, item) pair, as the reference's
-            # dict-update de-duplication does (datasets.py:137-146)
+            # a duplicated (user, item) pair stays at the position of its FIRST occurrence and
+            # takes the value of its LAST one: the reference pushes the entries through a dict
+            # (``dok_matrix._update`` + ``tocoo``, datasets.py:137-146), which keeps insertion
+            # order and overwrites values
             key = mat.row.astype(np.int64) * int(mat.shape[1]) + mat.col.astype(np.int64)
-            _, last_rev = np.unique(key[::-1], return_index=True)
-            keep = np.sort(len(key) - 1 - last_rev)
-            if len(keep) != len(key):
-                mat = coo_matrix((mat.data[keep], (mat.row[keep], mat.col[keep])), shape=mat.shape)
+            _, first = np.unique(key, return_index=True)
+            if len(first) != len(key):
+                _, last_rev = np.unique(key[::-1], return_index=True)
+                last = len(key) - 1 - last_rev               # (same key order as ``first``)
+                order = np.argsort(first, kind='stable')
+                pos, val = first[order], last[order]
+                mat = coo_matrix((mat.data[val], (mat.row[pos], mat.col[pos])), shape=mat.shape)
 
         self.mat = mat
         self.allow_missing_ids = allow_missing_ids

@@ -112,7 +112,8 @@ def _eval_tile(device, n_users, n_items, k, indptr, tgt_items, want, tables=None
     if workspace is None or workspace.numel() < need:
         workspace = torch.empty(int(need), dtype=torch.uint8, device=device)
     a.workspace, a.workspace_bytes = workspace.data_ptr(), workspace.numel()
-    rc = _abi.lib().cmf_eval_tile(_abi.C.byref(a), _abi.stream_ptr(device))
+    with _abi.on_device(device):
+        rc = _abi.lib().cmf_eval_tile(_abi.C.byref(a), _abi.stream_ptr(device))
     _abi.check(rc, 'cmf_eval_tile')
     out['_workspace'] = workspace
     return out
@@ -186,9 +187,10 @@ def get_preds(model, user_ids, n_items, device=None):
     U, I, bu, bi = _model_tables(model)
     users = torch.as_tensor(np.asarray(user_ids)).to(U.device, torch.int32).contiguous()
     out = torch.empty((users.shape[0], int(n_items)), dtype=torch.float32, device=U.device)
-    rc = _abi.lib().cmf_score_tile(_abi.ptr(U), _abi.ptr(I), _abi.ptr(bu), _abi.ptr(bi),
-                                   U.shape[1], _abi.ptr(users), users.shape[0], int(n_items),
-                                   _abi.ptr(out), _abi.stream_ptr(U.device))
+    with _abi.on_device(U.device):
+        rc = _abi.lib().cmf_score_tile(_abi.ptr(U), _abi.ptr(I), _abi.ptr(bu), _abi.ptr(bi),
+                                       U.shape[1], _abi.ptr(users), users.shape[0], int(n_items),
+                                       _abi.ptr(out), _abi.stream_ptr(U.device))
     _abi.check(rc, 'cmf_score_tile')
     return out
 

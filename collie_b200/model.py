@@ -107,9 +107,11 @@ class RowOptimizer(torch.optim.Optimizer):
                 opt, st = self.abi_opt(p)
                 rows, dim = (p.shape[0], p.shape[1]) if p.dim() == 2 else (p.numel(), 1)
                 grad = p.grad.contiguous()
-                rc = _abi.lib().cmf_optimizer_rows(
-                    _abi.ptr(p.data), _abi.ptr(st.get('exp_avg')), _abi.ptr(st.get('exp_avg_sq')),
-                    _abi.ptr(grad), rows, dim, None, 0, opt, 0, _abi.stream_ptr(p.device))
+                with _abi.on_device(p.device):
+                    rc = _abi.lib().cmf_optimizer_rows(
+                        _abi.ptr(p.data), _abi.ptr(st.get('exp_avg')),
+                        _abi.ptr(st.get('exp_avg_sq')), _abi.ptr(grad), rows, dim, None, 0, opt, 0,
+                        _abi.stream_ptr(p.device))
                 _abi.check(rc, 'cmf_optimizer_rows')
         return loss
 
@@ -121,10 +123,11 @@ class _ScoresFunction(torch.autograd.Function):
     def forward(ctx, U, I, bu, bi, users, items, y_range):
         out = torch.empty(users.shape[0], dtype=torch.float32, device=U.device)
         yr = (_abi.C.c_float * 2)(*y_range) if y_range is not None else None
-        rc = _abi.lib().cmf_forward_scores(
-            _abi.ptr(U), _abi.ptr(I), _abi.ptr(bu), _abi.ptr(bi), U.shape[1], _abi.ptr(users),
-            _abi.ptr(items), users.element_size(), users.shape[0], yr, _abi.ptr(out),
-            _abi.stream_ptr(U.device))
+        with _abi.on_device(U.device):
+            rc = _abi.lib().cmf_forward_scores(
+                _abi.ptr(U), _abi.ptr(I), _abi.ptr(bu), _abi.ptr(bi), U.shape[1], _abi.ptr(users),
+                _abi.ptr(items), users.element_size(), users.shape[0], yr, _abi.ptr(out),
+                _abi.stream_ptr(U.device))
         _abi.check(rc, 'cmf_forward_scores')
         ctx.save_for_backward(U, I, users, items, out)
         ctx.y_range = y_range
@@ -139,10 +142,11 @@ class _ScoresFunction(torch.autograd.Function):
         gbi = torch.zeros(ctx.shapes[1], dtype=torch.float32, device=U.device)
         yr = (_abi.C.c_float * 2)(*ctx.y_range) if ctx.y_range is not None else None
         g = grad_out.contiguous().float()
-        rc = _abi.lib().cmf_backward_scores(
-            _abi.ptr(U), _abi.ptr(I), U.shape[1], _abi.ptr(users), _abi.ptr(items),
-            users.element_size(), users.shape[0], _abi.ptr(g), _abi.ptr(out), yr, _abi.ptr(gU),
-            _abi.ptr(gI), _abi.ptr(gbu), _abi.ptr(gbi), _abi.stream_ptr(U.device))
+        with _abi.on_device(U.device):
+            rc = _abi.lib().cmf_backward_scores(
+                _abi.ptr(U), _abi.ptr(I), U.shape[1], _abi.ptr(users), _abi.ptr(items),
+                users.element_size(), users.shape[0], _abi.ptr(g), _abi.ptr(out), yr, _abi.ptr(gU),
+                _abi.ptr(gI), _abi.ptr(gbu), _abi.ptr(gbi), _abi.stream_ptr(U.device))
         _abi.check(rc, 'cmf_backward_scores')
         return gU, gI, gbu, gbi, None, None, None
 
@@ -266,7 +270,7 @@ class MatrixFactorizationModel(torch.nn.Module):
 
     # ------------------------------------------------------------------ set-up
     def _load_model_init_helper(self, load_model_path, map_location):
-        loaded = torch.load(str(load_model_path), map_location=map_location, weights_only=False)
+        loaded = _load_checkpoint(load_model_path, map_location)
         for key, value in loaded['hparams'].items():
             self.hparams[key] = value
         self.hparams['load_model_path'] = load_model_path
@@ -585,13 +589,14 @@ class MatrixFactorizationModel(torch.nn.Module):
         a.num_items_logical = int(num_items_logical)
         if item_grads_event is not None:
             a.item_grads_ready_event = int(item_grads_event.cuda_event)
-        if epoch_batch_size is not None:
-            rc = _abi.lib().cmf_train_epoch(_abi.C.byref(a), n_total, loss_out.data_ptr(),
-                                            _abi.stream_ptr(self.device))
-            _abi.check(rc, 'cmf_train_epoch')
-            return loss_out[:n_steps]
-        rc = _abi.lib().cmf_train_step(_abi.C.byref(a), _abi.stream_ptr(self.device))
-        _abi.check(rc, 'cmf_train_step')
+        with _abi.on_device(self.device):
+            if epoch_batch_size is not None:
+                rc = _abi.lib().cmf_train_epoch(_abi.C.byref(a), n_total, loss_out.data_ptr(),
+                                                _abi.stream_ptr(self.device))
+                _abi.check(rc, 'cmf_train_epoch')
+                return loss_out[:n_steps]
+            rc = _abi.lib().cmf_train_step(_abi.C.byref(a), _abi.stream_ptr(self.device))
+            _abi.check(rc, 'cmf_train_step')
         return loss_out[0]
 
     def calculate_loss(self, batch):
@@ -678,6 +683,32 @@ class MatrixFactorizationModel(torch.nn.Module):
         """``{'state_dict', 'hparams'}`` exactly as the reference writes it
         (base_pipeline.py:880-900); optimizer state and datasets are not saved."""
         torch.save({'state_dict': self.state_dict(), 'hparams': dict(self.hparams)}, str(filename))
+
+
+def _load_checkpoint(path, map_location=None):
+    """``{'state_dict', 'hparams'}`` as ``save_model`` of either library wrote it
+    (collie/model/base/base_pipeline.py:880-900). The reference pickles ``hparams`` as PyTorch
+    Lightning's ``AttributeDict``; Lightning is not a dependency here, so classes of its packages
+    that cannot be imported are read as plain attribute dictionaries."""
+    import pickle
+    import types
+
+    class _Unpickler(pickle.Unpickler):
+        def find_class(self, module, name):
+            try:
+                return super().find_class(module, name)
+            except (ImportError, AttributeError):
+                if module.split('.')[0] in ('pytorch_lightning', 'lightning', 'lightning_fabric',
+                                            'lightning_utilities'):
+                    return HParams
+                raise
+
+    shim = types.ModuleType('collie_b200_checkpoint_pickle')
+    shim.Unpickler = _Unpickler
+    shim.load = lambda f, **kw: _Unpickler(f, **kw).load()
+    shim.__dict__.update({k: getattr(pickle, k) for k in ('UnpicklingError', 'PickleError')})
+    return torch.load(str(path), map_location=map_location, weights_only=False,
+                      pickle_module=shim)
 
 
 def _has_negs(loader):

@@ -143,3 +143,19 @@ def test_no_cpu_fallback_anywhere():
                 text = open(os.path.join(root, f)).read()
                 assert not re.search(r'^\s*(from|import)\s+oracle|#include.*oracle|'
                                      r'import_module\(.oracle', text, flags=re.M), f
+
+
+def test_duplicate_pairs_keep_first_position_and_last_value():
+    """collie/interactions/datasets.py:137-146: the reference pushes the entries through a dict, so
+    a duplicated (user, item) pair stays where it FIRST appeared and takes its LAST value (checked
+    against the reference itself when this was written: rows [0 1 2 0], cols [5 3 1 2], data
+    [3 5 4 6] for the input below)."""
+    import collie_b200 as cb
+    users = np.array([0, 1, 0, 2, 1, 0])
+    items = np.array([5, 3, 5, 1, 3, 2])
+    ratings = np.array([1., 2., 3., 4., 5., 6.])
+    d = cb.ExplicitInteractions(users=users, items=items, ratings=ratings, num_users=3, num_items=6,
+                                allow_missing_ids=True)
+    assert d.mat.row.tolist() == [0, 1, 2, 0]
+    assert d.mat.col.tolist() == [5, 3, 1, 2]
+    assert d.mat.data.tolist() == [3., 5., 4., 6.]
