@@ -50,7 +50,7 @@ constexpr int TC_BK = 64;         // bf16 per K block = one 128-byte swizzle row
 constexpr int TC_STAGES = 3;
 constexpr int TC_MAXK = 16;       // largest k
 constexpr int TC_BIAS_SLOTS = 6;   // K slots that carry the two biases (three bf16 pieces each)
-constexpr int TC_BCAP = 16;       // band entries kept per (user, slot) for the MRR counter
+constexpr int TC_BCAP = 64;       // band entries kept per (user, slot) for the MRR counter
 constexpr int TC_A_BYTES = TC_BM * TC_BK * 2;   // 16 KB: one K-block of the user tile
 constexpr int TC_B_BYTES = TC_BN * TC_BK * 2;   // 32 KB: one K-block of an item tile
 
@@ -371,17 +371,6 @@ k_tc_target_best(const float* __restrict__ U, const float* __restrict__ I,
   if (lane == 0) { best_s[r] = bs; best_id[r] = bid; }
 }
 
-// order-preserving 32-bit pattern of a float (larger float -> larger uint; -inf -> smallest used)
-__device__ __forceinline__ uint32_t tc_score_key_u32(float s) {
-  const uint32_t u = __float_as_uint(s + 0.0f);
-  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
-}
-__device__ __forceinline__ float tc_key_score_u32(uint32_t u) {
-  if (u == 0) return -INFINITY;      // (the array starts zeroed)
-  u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
-  return __uint_as_float(u);
-}
-
 // ---------------------------------------------------------------------------------- GEMM + top-k
 struct TcParams {
   int n_users, k, KB, n_tiles, m_tiles, n_slots, want_mrr, debug;
@@ -391,7 +380,6 @@ struct TcParams {
   const float* best_s;   // exact score of the user's best target (MRR), may be NULL
   const int32_t* best_id;
   const float* margin;   // E_u per user row
-  uint32_t* thr_g;       // [n_users_pad] the row's filter threshold shared by all its segments
   float* cand_s;         // [n_users_pad][n_slots][KL]
   int32_t* cand_i;
   int32_t* cnt;          // [n_users_pad][n_slots] items surely ranked before the best target
@@ -555,15 +543,7 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int li[KL];
 #pragma unroll
       for (int e = 0; e < KL; ++e) { ls[e] = -INFINITY; li[e] = -1; }
-      // The filter threshold of the row is shared by everybody who works on it (the other column
-      // parts, other CTAs' segments) through one word per row: whoever raises its own KL-th best
-      // publishes it (atomicMax on the order-preserving bit pattern), everybody picks the
-      // largest up once per item tile. An item below ANY list's KL-th best cannot be among the
-      // best KL of the row, so skipping it is safe, and the lists fill more slowly than with
-      // private thresholds. k_tc_finish takes the final value of the word as the bound on
-      // everything outside the lists.
-      float thr = -INFINITY, thr_pub = -INFINITY;
-      uint32_t* thr_word = p.thr_g + urow;
+      float thr = -INFINITY;
       // MRR: x > t_hi is surely ranked before the best target, x < t_lo surely after it; what
       // lies between cannot be told from it with these scores and is re-scored by k_tc_finish
       const bool mrr = p.want_mrr && valid && p.best_id[urow] >= 0;
@@ -586,11 +566,6 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                                (uint32_t)(acc * TC_BN + sub * SUBW);
         const int ncols = (int)min((int64_t)TC_BN, p.n_items - n0);   // < TC_BN only in the last tile
         const int gid0 = (int)(p.item_offset + n0);
-        {
-          uint32_t w_;
-          asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(w_) : "l"(thr_word) : "memory");
-          thr = fmaxf(thr, tc_key_score_u32(w_));
-        }
         // 32 columns at a time go to registers; the accumulator is handed back as soon as the
         // last of them has been read, before they are ranked
 #pragma unroll 1
@@ -666,15 +641,11 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                   cs = up ? os : cs;
                   ci = up ? oi : ci;
                 }
-                thr = fmaxf(thr, ls[KL - 1]);
+                thr = ls[KL - 1];
                 ++dbg_ins;
               }
             }
           }
-        }
-        if (thr > thr_pub) {      // publish a raised threshold once per item tile
-          atomicMax(thr_word, tc_score_key_u32(thr));
-          thr_pub = thr;
         }
       }
       if (p.debug == 4) {
@@ -732,7 +703,6 @@ struct TcFinish {
   int n_slots, KL, k, D, want_mrr;
   int64_t n_users;
   const float* margin;
-  const uint32_t* thr_g;
   const float *U, *I, *bu, *bi;
   const int32_t* user_ids;
   const int64_t* tgt_indptr;
@@ -789,8 +759,13 @@ k_tc_finish(const TcFinish p) {
     prev = best;
     ++found;
   }
-  // everything outside the lists was filtered out or pushed out at or below this value
-  const float T = tc_key_score_u32(p.thr_g[r]);
+  // everything outside the lists was pushed out of a full list: it lies at or below that list's
+  // last entry (lists that never filled have lost nothing)
+  float T = -INFINITY;
+  for (int sl = lane; sl < p.n_slots; sl += 32)
+    if (ci[sl * p.KL + p.KL - 1] >= 0) T = fmaxf(T, cs[sl * p.KL + p.KL - 1]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) T = fmaxf(T, __shfl_xor_sync(0xffffffffu, T, o));
   const float thresh = found == p.k ? tc_key_score(prev) - 2.f * E : -INFINITY;
   if (!(T < thresh) && T != -INFINITY) fallback = true;
   // ---- MRR ingredients (before anything is written: a band that overflowed also falls back)
@@ -936,7 +911,7 @@ static int tc_list_len(int k) {
 struct TcLayout {
   int Kp, KB, KL, epi_warps, m_tiles, n_tiles, n_ctas, n_slots, fb_cap;
   int64_t m_pad, chunk, total_work;
-  size_t Bp, Ap, unorm, uabsb, margin, thr_g, stats, best_s, best_id, cand_s, cand_i, cnt, bcnt, band_i,
+  size_t Bp, Ap, unorm, uabsb, margin, stats, best_s, best_id, cand_s, cand_i, cnt, bcnt, band_i,
       fb_list, fb_uid, status, fb_scores, fb_sig, total;
 };
 
@@ -971,7 +946,6 @@ static TcLayout tc_layout(int64_t n_users, int64_t n_items, int D, int k, int te
   L.unorm = take(sizeof(float) * L.m_pad);
   L.uabsb = take(sizeof(float) * L.m_pad);
   L.margin = take(sizeof(float) * L.m_pad);
-  L.thr_g = take(sizeof(uint32_t) * L.m_pad);
   L.stats = take(sizeof(uint32_t) * 8);     // [0..1] of the items split with 1 term, [2..3] with 3, [4] which one Bp holds
   L.best_s = take(sizeof(float) * L.m_pad);
   L.best_id = take(sizeof(int32_t) * L.m_pad);
@@ -1077,9 +1051,7 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   p.want_mrr = mrr ? 1 : 0;
   p.n_items = a->num_items_shard; p.item_offset = a->item_offset; p.debug = g_tc_debug;
   p.best_s = best_s; p.best_id = best_id; p.margin = margin;
-  p.thr_g = (uint32_t*)(base + L.thr_g);
   p.dbg = (unsigned long long*)(status + 4);     // (status[4..7]; cleared with it)
-  CMF_CUDA(cudaMemsetAsync(p.thr_g, 0, sizeof(uint32_t) * L.m_pad, s));
   p.cand_s = (float*)(base + L.cand_s); p.cand_i = (int32_t*)(base + L.cand_i);
   p.cnt = (int32_t*)(base + L.cnt); p.bcnt = (int32_t*)(base + L.bcnt);
   p.band_i = (int32_t*)(base + L.band_i);
@@ -1111,7 +1083,7 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   TcFinish f{};
   f.cand_s = p.cand_s; f.cand_i = p.cand_i; f.cnt = p.cnt; f.bcnt = p.bcnt; f.band_i = p.band_i;
   f.n_slots = L.n_slots; f.KL = L.KL; f.k = a->k; f.D = a->D; f.want_mrr = mrr ? 1 : 0;
-  f.n_users = a->n_users_tile; f.margin = margin; f.thr_g = p.thr_g;
+  f.n_users = a->n_users_tile; f.margin = margin;
   f.U = a->U; f.I = a->I; f.bu = a->bu; f.bi = a->bi; f.user_ids = a->user_ids;
   f.tgt_indptr = a->tgt_indptr; f.tgt_items = a->tgt_items;
   f.best_s = best_s; f.best_id = best_id;

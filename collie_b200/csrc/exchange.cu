@@ -338,7 +338,7 @@ extern "C" int cmf_item_exchange_update(const cmf_peers_t* peers, float* M, floa
     if (fenced) {                                                                                \
       CMF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, KERNEL, kThreads, 0));        \
       CMF_REQUIRE(occ >= 1, "cmf_item_exchange_update: the kernel does not fit on an SM");       \
-      if (occ > 4) occ = 4;                                                                      \
+      if (occ > 2) occ = 2; /* (its CTAs spin at the barriers: leave the SMs to the step) */     \
     } else {                                                                                     \
       occ = 8;                                                                                   \
     }                                                                                            \

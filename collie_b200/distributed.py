@@ -192,7 +192,9 @@ class ShardedMatrixFactorization(object):
             self._p2p.update(pad=pad, pad_ptrs=[int(p) for p in hp.buffer_ptrs])
             self._p2p['handles'].append(hp)
             dev = self.I_full.device
-            self._xstream = torch.cuda.Stream(dev, priority=-1)
+            # (default priority: the step's own kernels, launched first, are placed first; the
+            # exchange kernel's CTAs mostly wait at its barriers)
+            self._xstream = torch.cuda.Stream(dev)
             self._ev_grads, self._ev_done = torch.cuda.Event(), torch.cuda.Event()
             self._ev_grads.record(torch.cuda.current_stream(dev))
             self._ev_done.record(torch.cuda.current_stream(dev))

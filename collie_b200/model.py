@@ -286,6 +286,7 @@ class MatrixFactorizationModel(torch.nn.Module):
         self.loss_function = None
         self._loss_name = None
         if callable(self.loss):
+            # (the reference leaves ``_is_implicit`` unset for callables, base_pipeline.py:281)
             self.loss_function = self.loss
             return
         self.hparams._is_implicit = False
@@ -365,8 +366,12 @@ class MatrixFactorizationModel(torch.nn.Module):
         else:
             params, lr = [p for _, p in named], self.hparams.lr
         if callable(optimizer):
-            raise ValueError('collie_b200 runs the optimizer inside the fused training step; pass '
-                             "one of 'sgd', 'adagrad', 'adam', 'sparse_adam' instead of a callable")
+            # a user-supplied optimizer class / factory (base_pipeline.py:409-416): the trainers
+            # then run the reference's unfused loop (differentiable forward, optimizer.step())
+            try:
+                return optimizer(params, lr=lr, weight_decay=self.hparams.weight_decay)
+            except TypeError:
+                return optimizer(params, lr=lr)
         if optimizer not in _abi.OPT_IDS:
             raise ValueError('{} is not a valid optimizer!'.format(optimizer))
         wd = 0.0 if optimizer == 'sparse_adam' else self.hparams.weight_decay
@@ -599,12 +604,55 @@ class MatrixFactorizationModel(torch.nn.Module):
             _abi.check(rc, 'cmf_train_step')
         return loss_out[0]
 
-    def calculate_loss(self, batch):
-        """Loss of one batch in the reference's formats (base_pipeline.py:582-654), no update.
+    def calculate_loss(self, batch, differentiable=None):
+        """Loss of one batch in the reference's formats (base_pipeline.py:582-654).
 
-        Training goes through the trainers (``fused_step``), which compute the same loss and apply
-        its gradient in the same kernels."""
-        return self.fused_step(batch, train=False)
+        Named losses: the fused kernel's value, no autograd graph -- training goes through the
+        trainers (``fused_step``), which compute the same loss and apply its gradient in the same
+        kernels. ``differentiable=True`` (the default for a callable ``loss``, and what the
+        trainers' unfused loop asks for) builds the reference's own graph instead: ``forward`` for
+        the positives, ``forward`` for ``users.repeat(N)`` and the flattened negatives
+        (base_pipeline.py:616-623), the loss callable with the reference's keyword arguments
+        (:626-634); ``backward()`` then runs ``cmf_backward_scores``."""
+        if differentiable is None:
+            differentiable = self._loss_name is None or getattr(self, '_unfused', False)
+        if not differentiable:
+            return self.fused_step(batch, train=False)
+        h = self.hparams
+        users, items, negs, gidx, ratings = self._normalise_batch(batch)
+        if negs is None and ratings is None:      # a DeviceBatch of implicit data: draw them
+            data = self.train_loader.interactions
+            negs = data.sample_negatives(users, gidx)
+        if ratings is not None:
+            if h.get('_is_implicit') is True:
+                raise ValueError('Implicit loss with explicit data is invalid!')
+            preds = self(users, items)
+            fn = self.loss_function
+            if fn == 'mse':
+                return torch.nn.functional.mse_loss(preds, ratings.float())
+            if fn == 'mae':
+                return torch.nn.functional.l1_loss(preds, ratings.float())
+            return fn(preds, ratings.float())
+        if h.get('_is_implicit') is False:
+            raise ValueError('Explicit loss with implicit data is invalid!')
+        n_neg = int(negs.shape[1])
+        neg_t = negs.t().contiguous()                       # [N, B], like the reference
+        pos_preds = self(users.long(), items.long())
+        neg_preds = self(users.long().repeat(n_neg), neg_t.reshape(-1)).view(n_neg, len(users))
+        fn = self.loss_function
+        if isinstance(fn, str):
+            from . import loss as L
+            fn = L.NAMED[fn]
+            if self._loss_name in ('bpr', 'hinge'):
+                neg_preds, neg_t = neg_preds[0], neg_t[0]
+        elif n_neg == 1:
+            neg_preds, neg_t = neg_preds.view(-1), neg_t.view(-1)
+        meta = h.get('metadata_for_loss')
+        if meta:
+            meta = {k: torch.as_tensor(v).to(self.device) for k, v in meta.items()}
+        return fn(pos_preds, neg_preds, num_items=h.num_items, positive_items=items.long(),
+                  negative_items=neg_t, metadata=meta,
+                  metadata_weights=h.get('metadata_for_loss_weights'))
 
     # ------------------------------------------------------------------ predictions / checkpoints
     def get_item_predictions(self, user_id=0, unseen_items_only=False, sort_values=True):

@@ -183,6 +183,71 @@ def _rank_main(rank, world, port):
         os._exit(1)
 
 
+def _trainer_main(rank, world, port):
+    """``CollieTrainer(model, gpus=world)`` under torch.distributed.run: trains over the ranks and
+    leaves every rank's model with the same, trained, full tables."""
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device('cuda', rank)
+    dist.init_process_group('nccl', rank=rank, world_size=world, device_id=dev)
+    try:
+        import collie_b200 as cb
+        rng = np.random.default_rng(11)
+        n_users, n_items = 301, 187
+        flat = rng.choice(n_users * n_items, size=12000, replace=False)
+        kw = dict(num_users=n_users, num_items=n_items, num_negative_samples=5,
+                  allow_missing_ids=True, check_num_negative_samples_is_valid=False,
+                  max_number_of_samples_to_consider=0, seed=9)
+        train = cb.Interactions(users=flat[:10000] // n_items, items=flat[:10000] % n_items, **kw)
+        val = cb.Interactions(users=flat[10000:] // n_items, items=flat[10000:] % n_items, **kw)
+        torch.manual_seed(4)
+        model = cb.MatrixFactorizationModel(
+            train=cb.InteractionsDataLoader(train, batch_size=1024, shuffle=True),
+            val=cb.InteractionsDataLoader(val, batch_size=1024, shuffle=False),
+            embedding_dim=32, sparse=True, lr=3e-2, bias_lr=3e-2, optimizer='sparse_adam',
+            loss='bpr', lr_scheduler_func=None)
+        start = {k: v.clone() for k, v in model.state_dict().items()}
+        before = cb.evaluate_in_batches([cb.mapk], val, model.cuda(), k=10, verbose=False)
+        trainer = cb.CollieTrainer(model, max_epochs=4, gpus=world, verbosity=0,
+                                   enable_model_summary=False, logger=None)
+        trainer.fit(model)
+        assert model.hparams.num_epochs_completed == 4
+        sd = model.state_dict()
+        for k in sd:
+            assert sd[k].shape == start[k].shape and not torch.equal(sd[k].cpu(), start[k].cpu()), k
+            # every rank holds the same tables
+            ref = sd[k].clone()
+            dist.broadcast(ref, src=0)
+            assert torch.equal(ref, sd[k]), k
+        after = cb.evaluate_in_batches([cb.mapk], val, model, k=10, verbose=False)
+        train_map = cb.evaluate_in_batches([cb.mapk], train, model, k=10, verbose=False)
+        assert train_map > 5 * max(before, 1e-3), (before, after, train_map)   # it learned
+        dist.barrier()
+        dist.destroy_process_group()
+        return f'ok (train MAP@10 {train_map:.4f}, val {before:.4f} -> {after:.4f})'
+    except BaseException:  # pragma: no cover
+        import traceback
+        print(f'rank {rank} of {world}: FAILED:\n' + traceback.format_exc(), flush=True)
+        os._exit(1)
+
+
+@pytest.mark.parametrize('world', [2])
+def test_trainer_gpus_n_trains_over_the_ranks(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f'needs {world} GPUs')
+    import subprocess
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node',
+           str(world), '--master-addr', '127.0.0.1', '--master-port', str(_free_port()),
+           os.path.abspath(__file__), 'trainer']
+    out = subprocess.run(cmd, cwd=ROOT, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                         timeout=300).stdout
+    for r in range(world):
+        assert f'rank {r} of {world}: ok' in out, out[-6000:]
+    print(out[-1500:])
+
+
 @pytest.mark.parametrize('world', [2, 4, 8])
 def test_sharded_step_matches_single_gpu(world):
     """Launches ``world`` ranks the way the driver does (torch.distributed.run, one per GPU)."""
@@ -202,6 +267,7 @@ def test_sharded_step_matches_single_gpu(world):
 if __name__ == '__main__':   # one rank of the test above
     import faulthandler
     faulthandler.dump_traceback_later(240, exit=True)
-    res = _rank_main(int(os.environ['RANK']), int(os.environ['WORLD_SIZE']),
-                     int(os.environ['MASTER_PORT']))
+    main_fn = _trainer_main if 'trainer' in sys.argv[1:] else _rank_main
+    res = main_fn(int(os.environ['RANK']), int(os.environ['WORLD_SIZE']),
+                  int(os.environ['MASTER_PORT']))
     print(f"rank {os.environ['RANK']} of {os.environ['WORLD_SIZE']}: {res}", flush=True)
