@@ -13,14 +13,17 @@ from .interactions import (ApproximateNegativeSamplingInteractionsDataLoader,
                            ExplicitInteractions, Interactions, InteractionsDataLoader)
 from .metrics import (MeanAbsoluteError, MeanSquaredError, auc, evaluate_in_batches,
                       explicit_evaluate_in_batches, get_preds, mapk, mrr)
+from .hybrid import HybridPretrainedModel
+from . import loss  # noqa: F401  (bpr_loss, hinge_loss, adaptive_*, warp_loss)
 from .model import (MatrixFactorizationModel, RowOptimizer, ScaledEmbedding, ZeroEmbedding)
 from .trainer import CollieMinimalTrainer, CollieTrainer
 
-__version__ = '0.1.0'
+__version__ = '0.2.0'
 
 __all__ = [
     'ApproximateNegativeSamplingInteractionsDataLoader', 'CollieMinimalTrainer', 'CollieTrainer',
-    'ExplicitInteractions', 'Interactions', 'InteractionsDataLoader', 'MatrixFactorizationModel',
+    'ExplicitInteractions', 'HybridPretrainedModel', 'Interactions', 'InteractionsDataLoader',
+    'MatrixFactorizationModel',
     'MeanAbsoluteError', 'MeanSquaredError', 'explicit_evaluate_in_batches',
     'RowOptimizer', 'ScaledEmbedding', 'ZeroEmbedding', 'auc', 'evaluate_in_batches', 'get_preds',
     'mapk', 'mrr',

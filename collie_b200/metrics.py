@@ -184,6 +184,15 @@ def _model_tables(model):
 def get_preds(model, user_ids, n_items, device=None):
     """Scores of every item for ``user_ids``: tensor ``n_users x n_items``
     (collie/metrics.py:77-107), one tiled kernel instead of ``n_users * n_items`` gathers."""
+    if not getattr(model, '_fusable', True):
+        # a model whose score is not <u, i> + biases (dense layers on top): every (user, item)
+        # pair through its forward, like the reference (collie/metrics.py:60-72, :104-107)
+        dev = model.device
+        users = torch.as_tensor(np.asarray(user_ids)).to(dev).long()
+        items = torch.arange(int(n_items), device=dev)
+        with torch.no_grad():
+            return model(users.repeat_interleave(int(n_items)),
+                         items.repeat(users.shape[0])).view(-1, int(n_items)).float()
     U, I, bu, bi = _model_tables(model)
     users = torch.as_tensor(np.asarray(user_ids)).to(U.device, torch.int32).contiguous()
     out = torch.empty((users.shape[0], int(n_items)), dtype=torch.float32, device=U.device)
@@ -229,7 +238,7 @@ def evaluate_in_batches(metric_list, test_interactions, model, k=10, batch_size=
     n_test = len(test_users)
     names = [_FUSED.get(m) for m in metric_list]
 
-    if all(n is not None for n in names):
+    if all(n is not None for n in names) and getattr(model, '_fusable', True):
         if 'mapk' in names:
             _check_k(k, n_items)
         tables = _model_tables(model)

@@ -435,8 +435,8 @@ class CollieMinimalTrainer(object):
         else:
             raise ValueError('Unexpected output from ``model.configure_optimizers()``!')
         self.optimizer = MultiOptimizer(list(optimizers))
-        fused = model._loss_name is not None and all(isinstance(o, RowOptimizer)
-                                                     for o in optimizers)
+        fused = (getattr(model, '_fusable', True) and model._loss_name is not None
+                 and all(isinstance(o, RowOptimizer) for o in optimizers))
         return _FusedEngine(self, model) if fused else _AutogradEngine(self, model)
 
     def _report(self, epoch, report):

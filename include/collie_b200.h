@@ -406,6 +406,21 @@ CMF_API int cmf_eval_tc_info(int32_t D, double *out);
  */
 CMF_API int cmf_eval_tile_noalloc(const cmf_eval_t *args, void *stream);
 
+/*
+ * Row gather into a column block of a wider matrix, and its transpose (vector RED): the input of
+ * the first dense layer of HybridPretrainedModel, X[r] = [user_meta[u] | U[u] | I[i] | item_meta[i]],
+ * is written by one call per source table (out + col0 with row pitch ld floats), instead of the
+ * reference's four gathers + torch.cat (collie/model/hybrid_pretrained_matrix_factorization.py
+ * :401-464); cmf_scatter_add_rows is the embedding backward of the same (grad_table[ids[r]] +=
+ * grad_out[r, col0 : col0 + D]). ids: int32 or int64 (idx_bytes 4 / 8).
+ */
+CMF_API int cmf_gather_rows(const float *table, int64_t num_rows, int32_t D, const void *ids,
+                    int32_t idx_bytes, int64_t n, float *out, int64_t ld, int32_t col0,
+                    void *stream);
+CMF_API int cmf_scatter_add_rows(float *grad_table, int64_t num_rows, int32_t D, const void *ids,
+                         int32_t idx_bytes, int64_t n, const float *grad_out, int64_t ld,
+                         int32_t col0, void *stream);
+
 /* Materialised score tile out[n, num_items] (for user-supplied metric callables and get_preds,
  * collie/metrics.py:77-107). */
 CMF_API int cmf_score_tile(const float *U, const float *I, const float *bu, const float *bi, int32_t D,

@@ -491,3 +491,37 @@ def train_step(model: OracleMF, optimizers, loss_closure) -> float:
     for opt in optimizers:
         opt.step()
     return float(loss.detach())
+
+
+# ------------------------------------------------------------------------------------------------
+# HybridPretrainedModel
+# ------------------------------------------------------------------------------------------------
+
+
+def hybrid_forward(state: Dict[str, torch.Tensor], item_metadata: torch.Tensor,
+                   users: torch.Tensor, items: torch.Tensor,
+                   user_metadata: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Scores of ``HybridPretrainedModel`` in eval mode from its ``state_dict`` (reference names):
+    ``[user_meta_out | U[u] | I[i] | item_meta_out]`` -> ``combined_layer_*`` with ``leaky_relu``
+    between them -> + both biases (collie/model/hybrid_pretrained_matrix_factorization.py
+    :327-361 metadata layers, :363-399 prediction, :401-464 forward). Pinned by
+    tests/golden/hybrid_*.npz, which the unmodified reference produced."""
+    users, items = users.long(), items.long()
+
+    def stack(prefix, x, last_linear):
+        i = 0
+        while f'{prefix}_{i}.weight' in state:
+            x = torch.nn.functional.linear(x, state[f'{prefix}_{i}.weight'],
+                                           state[f'{prefix}_{i}.bias'])
+            if not (last_linear and f'{prefix}_{i + 1}.weight' not in state):
+                x = torch.nn.functional.leaky_relu(x)
+            i += 1
+        return x
+    parts = []
+    if user_metadata is not None:
+        parts.append(stack('user_metadata_layer', user_metadata[users], False))
+    parts += [state['embeddings.0.weight'][users], state['embeddings.1.weight'][items]]
+    if item_metadata is not None:
+        parts.append(stack('item_metadata_layer', item_metadata[items], False))
+    out = stack('combined_layer', torch.cat(parts, dim=1), True)
+    return (out + state['biases.0.weight'][users] + state['biases.1.weight'][items]).squeeze()
