@@ -144,7 +144,7 @@ class _AutogradEngine(_FusedEngine):
         model._unfused = True           # calculate_loss builds the autograd graph
         total = torch.zeros((), dtype=torch.float32, device=model.device)
         n = 0
-        for batch_idx, batch in enumerate(loader):
+        for batch_idx, batch in enumerate(self._reference_batches(loader, epoch)):
             if train:
                 t.optimizer.zero_grad()
                 loss = model.calculate_loss(batch)
@@ -162,6 +162,20 @@ class _AutogradEngine(_FusedEngine):
         if train and t.detect_anomaly and not bool(torch.isfinite(total)):
             raise RuntimeError('non-finite training loss detected')
         return (total / max(n, 1)).item()
+
+    def _reference_batches(self, loader, epoch):
+        """Batches in the reference's formats, drawn exactly like the fused route draws them (the
+        same epoch plan, negatives keyed by the trainer's epoch), so that the two routes see the
+        same data."""
+        if not hasattr(loader, 'device_batches'):
+            yield from loader
+            return
+        data = loader.interactions
+        for db in loader.device_batches(self.model.device, epoch=epoch):
+            if db.ratings is not None:
+                yield db.users, db.items, db.ratings
+            else:
+                yield (db.users, db.items), data.sample_negatives(db.users, db.gidx, epoch=epoch)
 
     def finish(self):
         self.model._unfused = False
