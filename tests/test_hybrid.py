@@ -79,6 +79,14 @@ def test_hybrid_predictions_losses_and_steps_match_the_reference(name):
         exp = g['final_' + k]
         if frozen and k.startswith('embeddings'):
             assert np.array_equal(v.cpu().numpy(), g['init_' + k]), k      # never touched
+        if k == 'biases.0.weight':
+            # The true gradient of a user bias is exactly zero: every interaction sends it +g (the
+            # positive) and -g (the chosen negative). What reaches Adam is the rounding residue
+            # of that sum (~1e-9, its sign a matter of summation order), which Adam's g / |g|
+            # turns into a step of up to +-lr: noise in the reference and here alike. Bounded, not
+            # compared.
+            assert np.abs(v.cpu().numpy() - g['init_' + k]).max() <= s * float(g['lr']) * 1.001
+            continue
         np.testing.assert_allclose(v.cpu().numpy(), exp, rtol=1e-4, atol=1e-5, err_msg=k)
         tight = np.abs(v.cpu().numpy() - exp) <= 1e-6 + 1e-5 * np.abs(exp)
         assert tight.mean() >= 0.98, (k, float(tight.mean()))
