@@ -75,16 +75,17 @@ def test_hybrid_predictions_losses_and_steps_match_the_reference(name):
         s += 1
     assert s == 3
     frozen = bool(int(g['freeze']))
+    last = len(model.combined_layers) - 1
     for k, v in model.state_dict().items():
         exp = g['final_' + k]
         if frozen and k.startswith('embeddings'):
             assert np.array_equal(v.cpu().numpy(), g['init_' + k]), k      # never touched
-        if k == 'biases.0.weight':
-            # The true gradient of a user bias is exactly zero: every interaction sends it +g (the
-            # positive) and -g (the chosen negative). What reaches Adam is the rounding residue
-            # of that sum (~1e-9, its sign a matter of summation order), which Adam's g / |g|
-            # turns into a step of up to +-lr: noise in the reference and here alike. Bounded, not
-            # compared.
+        if k in ('biases.0.weight', f'combined_layer_{last}.bias'):
+            # The true gradient of a user bias -- and of the last layer's bias, which enters every
+            # score alike -- is exactly zero: every interaction sends it +g (the positive) and -g
+            # (the chosen negative). What reaches Adam is the rounding residue of that sum
+            # (~1e-9, its sign a matter of summation order), which Adam's g / |g| turns into a
+            # step of up to +-lr: noise in the reference and here alike. Bounded, not compared.
             assert np.abs(v.cpu().numpy() - g['init_' + k]).max() <= s * float(g['lr']) * 1.001
             continue
         np.testing.assert_allclose(v.cpu().numpy(), exp, rtol=1e-4, atol=1e-5, err_msg=k)
