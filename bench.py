@@ -57,6 +57,11 @@ WORKLOADS = {
         'lr': 1e-3, 'bias_lr': 1e-2, 'seed': 3, 'eval_users': 4096,
     },
 }
+for _k in ('num_users', 'num_items', 'n_neg'):       # experiments: CMF_C5_NUM_USERS=... etc.
+    if os.environ.get('CMF_C5_' + _k.upper()):
+        WORKLOADS['c5'][_k] = int(os.environ['CMF_C5_' + _k.upper()])
+if os.environ.get('CMF_C5_LOSS'):
+    WORKLOADS['c5']['loss'] = WORKLOADS['c5']['loss_resolved'] = os.environ['CMF_C5_LOSS']
 METRIC = 'MF train interactions/s (fwd+bwd+sparse Adam)'
 NVLINK_GBS_PER_DIR = 900.0
 STRONG_GLOBAL_BATCH = 2097152
@@ -800,8 +805,12 @@ def parity_block(job, n_steps=3):
             ref_opts[1].state_for(p)['step'] = ustep
     del U, bu, Um, Uv, Im, Iv
     loss_pairs = []
-    for _ in range(n_steps):
-        db, ep = job.next_batch()
+    for k_ in range(n_steps):
+        db, _ = job.next_batch()
+        # one epoch number for the whole global batch (it only keys the negative-sampling stream):
+        # the ranks' loaders hold slightly different numbers of batches, so their own epoch
+        # counters drift apart on short datasets, and the replay below has one epoch per step
+        ep = 100000 + k_
         gu = [torch.empty_like(db.users) for _ in range(world)]
         gi = [torch.empty_like(db.items) for _ in range(world)]
         gg = [torch.empty_like(db.gidx) for _ in range(world)]

@@ -167,7 +167,56 @@ struct StepDev {
   float* neg_out;
   float* g_arr;     // [B] d loss / d positive score (split path: k_fwd_loss -> k_bwd_update)
   int32_t* sel_arr; // [B] item id of the selected negative, -1 when none
+  // dropout on both embeddings of every scored pair (matrix_factorization.py:118, :147): keep an
+  // element when its Philox word >= drop_thr, scaled by drop_scale = 1 / (1 - p); 0 = off
+  uint32_t drop_thr;
+  float drop_scale;
+  uint32_t drop_key_hi;   // optimizer step: a batch that is repeated draws fresh masks
 };
+
+// The dropout mask of one row of one scored pair: interaction at dataset position gidx, slot 0 =
+// the positive / 1 + n = negative n, side 0 = user row / 1 = item row. Element d takes word d % 4
+// of the Philox block (gidx, epoch, slot, side, d / 4); see oracle.dropout_mask.
+__device__ __forceinline__ float drop_factor(const StepDev& p, int64_t gidx, int slot, int side,
+                                             int d) {
+  const uint4 w = philox4x32_10(
+      make_uint4((uint32_t)gidx, (uint32_t)((uint64_t)gidx >> 32), p.epoch,
+                 ((uint32_t)slot << 16) | ((uint32_t)side << 15) | (uint32_t)(d >> 2)),
+      make_uint2((uint32_t)p.seed ^ 0x85EBCA6Bu, (uint32_t)(p.seed >> 32) ^ p.drop_key_hi));
+  const uint32_t word = (d & 3) == 0 ? w.x : (d & 3) == 1 ? w.y : (d & 3) == 2 ? w.z : w.w;
+  return word >= p.drop_thr ? p.drop_scale : 0.f;
+}
+template <int V, int G, int R>
+__device__ __forceinline__ void drop_row(const StepDev& p, int64_t gidx, int slot, int side, int D,
+                                         int l, Row<V, G, R>& x) {
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int d0 = (r * G + l) * V;
+    if (d0 >= D) continue;
+    if (V == 4) {
+      const uint4 w = philox4x32_10(
+          make_uint4((uint32_t)gidx, (uint32_t)((uint64_t)gidx >> 32), p.epoch,
+                     ((uint32_t)slot << 16) | ((uint32_t)side << 15) | (uint32_t)(d0 >> 2)),
+          make_uint2((uint32_t)p.seed ^ 0x85EBCA6Bu, (uint32_t)(p.seed >> 32) ^ p.drop_key_hi));
+      x.f[r * V + 0] *= w.x >= p.drop_thr ? p.drop_scale : 0.f;
+      x.f[r * V + 1] *= w.y >= p.drop_thr ? p.drop_scale : 0.f;
+      x.f[r * V + 2] *= w.z >= p.drop_thr ? p.drop_scale : 0.f;
+      x.f[r * V + 3] *= w.w >= p.drop_thr ? p.drop_scale : 0.f;
+    } else {
+#pragma unroll
+      for (int j = 0; j < V; ++j) x.f[r * V + j] *= drop_factor(p, gidx, slot, side, d0 + j);
+    }
+  }
+}
+// the same two masks applied to a gradient direction: out = mask_user * mask_item * x
+template <int V, int G, int R>
+__device__ __forceinline__ Row<V, G, R> drop_both(const StepDev& p, int64_t gidx, int slot, int D,
+                                                  int l, const Row<V, G, R>& x) {
+  Row<V, G, R> y = x;
+  drop_row<V, G, R>(p, gidx, slot, 0, D, l, y);
+  drop_row<V, G, R>(p, gidx, slot, 1, D, l, y);
+  return y;
+}
 
 __device__ __forceinline__ void mark_row(int* flag, int* list, int* count, int id, int use_list) {
   if (*(volatile int*)(flag + id) == 0) {

@@ -144,9 +144,16 @@ k_fused_step(const StepDev p) {
       Row<V, G, R> irow;
       irow.load(p.I + (int64_t)pos * D, D, l);
 
+      const bool drop = p.drop_thr != 0;
+      const int64_t gi_b = p.gidx ? p.gidx[b] : p.gidx_base + b;
       if (!implicit) {
         // ---------------- explicit: mse / mae (base_pipeline.py:635-650)
-        const float s = group_sum<G>(urow.dot(irow), mask) + ubias + p.bi[pos];
+        Row<V, G, R> um = urow, im = irow;
+        if (drop) {
+          drop_row<V, G, R>(p, gi_b, 0, 0, D, l, um);
+          drop_row<V, G, R>(p, gi_b, 0, 1, D, l, im);
+        }
+        const float s = group_sum<G>(um.dot(im), mask) + ubias + p.bi[pos];
         float sg = 0.f, pred = s;
         if (p.has_range) { sg = sigmoidf_(s); pred = sg * (p.y_hi - p.y_lo) + p.y_lo; }
         const float diff = pred - p.ratings[b];
@@ -156,11 +163,12 @@ k_fused_step(const StepDev p) {
         const float ds = p.has_range ? dp * (sg * (1.f - sg) * (p.y_hi - p.y_lo)) : dp;
         if (p.pos_out && l == 0) p.pos_out[b] = pred;
         if (p.train) {
-          gu.axpy(ds, irow);
+          // (with dropout the score is <mu * u, mi * i>: both masks reach both gradients)
+          gu.axpy(ds, drop ? drop_both<V, G, R>(p, gi_b, 0, D, l, irow) : irow);
           gbu_acc += ds;
           Row<V, G, R> t;
           t.zero();
-          t.axpy(ds, urow);
+          t.axpy(ds, drop ? drop_both<V, G, R>(p, gi_b, 0, D, l, urow) : urow);
           t.red_add(p.GI + (int64_t)pos * D, D, l);
           if (l == 0) {
             atomicAdd(p.gbi + pos, ds);
@@ -171,7 +179,15 @@ k_fused_step(const StepDev p) {
       }
 
       // ---------------- implicit
-      const float sp = group_sum<G>(urow.dot(irow), mask) + ubias + p.bi[pos];
+      float sp;
+      if (drop) {
+        Row<V, G, R> um = urow, im = irow;
+        drop_row<V, G, R>(p, gi_b, 0, 0, D, l, um);
+        drop_row<V, G, R>(p, gi_b, 0, 1, D, l, im);
+        sp = group_sum<G>(um.dot(im), mask) + ubias + p.bi[pos];
+      } else {
+        sp = group_sum<G>(urow.dot(irow), mask) + ubias + p.bi[pos];
+      }
       if (p.pos_out && l == 0) p.pos_out[b] = sp;
 
       // negatives of this interaction -> shared memory
@@ -228,7 +244,15 @@ k_fused_step(const StepDev p) {
         for (int j = 0; j < NC; ++j) {
           if (ids[j] < 0) continue;
           const int n = n0 + j;
-          const float s = group_sum<G>(urow.dot(rows[j]), mask) + ubias + p.bi[ids[j]];
+          float s;
+          if (drop) {
+            Row<V, G, R> um = urow, im = rows[j];
+            drop_row<V, G, R>(p, gi_b, 1 + n, 0, D, l, um);
+            drop_row<V, G, R>(p, gi_b, 1 + n, 1, D, l, im);
+            s = group_sum<G>(um.dot(im), mask) + ubias + p.bi[ids[j]];
+          } else {
+            s = group_sum<G>(urow.dot(rows[j]), mask) + ubias + p.bi[ids[j]];
+          }
           if (p.neg_out && l == 0) p.neg_out[b * N + n] = s;
           if (p.loss == CMF_LOSS_WARP) {
             // h = ideal - pos + neg, first strict violation wins (warp.py:95-105,136-154)
@@ -270,7 +294,25 @@ k_fused_step(const StepDev p) {
       }
 
       if (p.train) {
-        if (g != 0.f) {
+        if (g != 0.f && drop) {
+          // <mu * u, mi * i>: the pair's two masks reach both gradients; the positive and the
+          // selected negative were scored under different masks
+          gu.axpy(g, drop_both<V, G, R>(p, gi_b, 0, D, l, irow));
+          gu.axpy(-g, drop_both<V, G, R>(p, gi_b, 1 + sel, D, l, sel_row));
+          gbu_acc += g;
+          gbu_acc += -g;
+          Row<V, G, R> t;
+          t.zero();
+          t.axpy(g, drop_both<V, G, R>(p, gi_b, 0, D, l, urow));
+          t.red_add(p.GI + (int64_t)pos * D, D, l);
+          t.zero();
+          t.axpy(-g, drop_both<V, G, R>(p, gi_b, 1 + sel, D, l, urow));
+          t.red_add(p.GI + (int64_t)sel_id * D, D, l);
+          if (l == 0) {
+            atomicAdd(p.gbi + pos, g);
+            atomicAdd(p.gbi + sel_id, -g);
+          }
+        } else if (g != 0.f) {
           gu.axpy(g, irow);
           gu.axpy(-g, sel_row);
           gbu_acc += g;
@@ -705,8 +747,17 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
   p.g_arr = (float*)(base + w.g_arr);
   p.sel_arr = (int32_t*)(base + w.sel_arr);
 
+  CMF_REQUIRE(a->dropout_p >= 0.f && a->dropout_p < 1.f, "cmf_train_step: dropout_p %g not in [0, 1)",
+              (double)a->dropout_p);
+  if (a->dropout_p > 0.f) {
+    p.drop_thr = (uint32_t)((double)a->dropout_p * 4294967296.0);
+    if (p.drop_thr == 0) p.drop_thr = 1;
+    p.drop_scale = 1.0f / (1.0f - a->dropout_p);
+    p.drop_key_hi = (uint32_t)a->emb_opt.step;
+  }
   const int version = g_kernel_version.load();
-  const bool split = version != 1 && v3_supported(a->D, a->N);
+  // (dropout lives in the generic kernel only: it keeps the scored rows and their masks together)
+  const bool split = version != 1 && v3_supported(a->D, a->N) && a->dropout_p == 0.f;
   CMF_REQUIRE(split || version != 2,
               "cmf_train_step: the split kernels do not support this shape (D=%d, N=%d)", a->D, a->N);
   const int forced_len = g_forced_chunk_len.load() > 0 ? g_forced_chunk_len.load() : 0;

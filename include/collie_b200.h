@@ -146,6 +146,14 @@ typedef struct {
    * skip_item_update a caller can start the exchange on another stream while the remaining
    * user-row updates run */
   void *item_grads_ready_event;
+  /* dropout on both embeddings of every scored pair, training mode only
+   * (collie/model/matrix_factorization.py:118, :147): each element of the user row and of the
+   * item row of every (interaction, positive-or-negative) pair is zeroed with probability
+   * dropout_p and scaled by 1 / (1 - dropout_p) otherwise, independently. The masks come from
+   * the counter-based stream of the negatives (other key), keyed by (seed, emb_opt.step, epoch,
+   * dataset position, pair, side, element), so a step can be replayed. 0 = off. */
+  float dropout_p;
+  int32_t reserved3;
 } cmf_step_t;
 
 /* scratch for cmf_train_step; depends only on the table shapes and the largest batch */

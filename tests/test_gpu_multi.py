@@ -30,6 +30,10 @@ CASES = {
     # the generic 64-bit-vector kernels and the exchange kernel's V = 2 form
     'warp_n10_d30': dict(n_users=257, n_items=203, dim=30, n_neg=10, loss='warp',
                          optimizer='sparse_adam', sparse=True, lr=1e-2),
+    # a catalogue far larger than a batch: most item rows are NOT gathered in a given step, some
+    # only by one rank (the other cases touch every row every step)
+    'sparse_touch_d32': dict(n_users=3001, n_items=5003, dim=32, n_neg=4, loss='bpr',
+                             optimizer='sparse_adam', sparse=True, lr=1e-2),
     # the reference's DEFAULT optimizer: dense Adam moves every row every step, on every owner
     'hinge_n3_adam_d16': dict(n_users=120, n_items=75, dim=16, n_neg=3, loss='hinge',
                               optimizer='adam', sparse=False, lr=1e-2),
