@@ -29,52 +29,7 @@ from torch.optim.lr_scheduler import ReduceLROnPlateau
 
 from . import _abi
 from .model import (HParams, MatrixFactorizationModel, RowOptimizer, ScaledEmbedding,
-                    ZeroEmbedding, _as_ids, _load_checkpoint)
-
-
-class _GatherConcat(torch.autograd.Function):
-    """``X[r] = [table_0[ids_0[r]] | table_1[ids_1[r]] | ...]`` through ``cmf_gather_rows``;
-    backward adds the column blocks of ``dX`` into dense gradient tables of the sources that
-    require one (``cmf_scatter_add_rows``)."""
-
-    @staticmethod
-    def forward(ctx, ids_list, *tables):
-        n = int(ids_list[0].shape[0])
-        widths = [int(t.shape[1]) for t in tables]
-        out = torch.empty((n, sum(widths)), dtype=torch.float32, device=tables[0].device)
-        lib = _abi.lib()
-        col = 0
-        with _abi.on_device(out.device):
-            for ids, table, w in zip(ids_list, tables, widths):
-                _abi.require_cuda(table, 'table')
-                _abi.check(lib.cmf_gather_rows(
-                    _abi.ptr(table), table.shape[0], w, _abi.ptr(ids), ids.element_size(), n,
-                    _abi.ptr(out), out.shape[1], col, _abi.stream_ptr(out.device)),
-                    'cmf_gather_rows')
-                col += w
-        ctx.ids_list, ctx.widths = ids_list, widths
-        ctx.shapes = [tuple(t.shape) for t in tables]
-        ctx.needs = [t.requires_grad for t in tables]
-        return out
-
-    @staticmethod
-    def backward(ctx, grad_out):
-        grad_out = grad_out.contiguous()
-        lib = _abi.lib()
-        grads, col = [], 0
-        n = int(grad_out.shape[0])
-        with _abi.on_device(grad_out.device):
-            for ids, shape, w, need in zip(ctx.ids_list, ctx.shapes, ctx.widths, ctx.needs):
-                g = None
-                if need:
-                    g = torch.zeros(shape, dtype=torch.float32, device=grad_out.device)
-                    _abi.check(lib.cmf_scatter_add_rows(
-                        _abi.ptr(g), shape[0], w, _abi.ptr(ids), ids.element_size(), n,
-                        _abi.ptr(grad_out), grad_out.shape[1], col,
-                        _abi.stream_ptr(grad_out.device)), 'cmf_scatter_add_rows')
-                grads.append(g)
-                col += w
-        return (None,) + tuple(grads)
+                    ZeroEmbedding, _GatherConcat, _as_ids, _load_checkpoint)
 
 
 def _as_float_table(x):

@@ -151,6 +151,52 @@ class _ScoresFunction(torch.autograd.Function):
         return gU, gI, gbu, gbi, None, None, None
 
 
+class _GatherConcat(torch.autograd.Function):
+    """``X[r] = [table_0[ids_0[r]] | table_1[ids_1[r]] | ...]`` through ``cmf_gather_rows`` (one
+    pass per source table straight into its column block); backward adds the column blocks of
+    ``dX`` into dense gradient tables of the sources that require one
+    (``cmf_scatter_add_rows``)."""
+
+    @staticmethod
+    def forward(ctx, ids_list, *tables):
+        n = int(ids_list[0].shape[0])
+        widths = [int(t.shape[1]) for t in tables]
+        out = torch.empty((n, sum(widths)), dtype=torch.float32, device=tables[0].device)
+        lib = _abi.lib()
+        col = 0
+        with _abi.on_device(out.device):
+            for ids, table, w in zip(ids_list, tables, widths):
+                _abi.require_cuda(table, 'table')
+                _abi.check(lib.cmf_gather_rows(
+                    _abi.ptr(table), table.shape[0], w, _abi.ptr(ids), ids.element_size(), n,
+                    _abi.ptr(out), out.shape[1], col, _abi.stream_ptr(out.device)),
+                    'cmf_gather_rows')
+                col += w
+        ctx.ids_list, ctx.widths = ids_list, widths
+        ctx.shapes = [tuple(t.shape) for t in tables]
+        ctx.needs = [t.requires_grad for t in tables]
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        grad_out = grad_out.contiguous()
+        lib = _abi.lib()
+        grads, col = [], 0
+        n = int(grad_out.shape[0])
+        with _abi.on_device(grad_out.device):
+            for ids, shape, w, need in zip(ctx.ids_list, ctx.shapes, ctx.widths, ctx.needs):
+                g = None
+                if need:
+                    g = torch.zeros(shape, dtype=torch.float32, device=grad_out.device)
+                    _abi.check(lib.cmf_scatter_add_rows(
+                        _abi.ptr(g), shape[0], w, _abi.ptr(ids), ids.element_size(), n,
+                        _abi.ptr(grad_out), grad_out.shape[1], col,
+                        _abi.stream_ptr(grad_out.device)), 'cmf_scatter_add_rows')
+                grads.append(g)
+                col += w
+        return (None,) + tuple(grads)
+
+
 def _as_ids(t, device):
     if not torch.is_tensor(t):
         t = torch.as_tensor(np.asarray(t))
@@ -162,8 +208,7 @@ def _as_ids(t, device):
 class MatrixFactorizationModel(torch.nn.Module):
     """Matrix factorization with user/item biases, trained by the fused B200 step.
 
-    Same constructor as the reference (matrix_factorization.py:73-94). ``dropout_p`` must be 0 for
-    training through the fused step.
+    Same constructor as the reference (matrix_factorization.py:73-94).
     """
 
     def __init__(self, train=None, val=None, embedding_dim=30, dropout_p=0.0, sparse=False,
@@ -382,8 +427,6 @@ class MatrixFactorizationModel(torch.nn.Module):
         """``preds = <U[u], I[i]> + bu[u] + bi[i]`` (+ ``y_range`` sigmoid), one fused kernel
         (matrix_factorization.py:120-159)."""
         U = _abi.require_cuda(self.user_embeddings.weight, 'user_embeddings.weight')
-        if self.training and self.hparams.dropout_p > 0:
-            raise _abi.CmfError('dropout_p > 0 is not supported by the fused B200 kernels')
         users = _as_ids(users, U.device)
         items = _as_ids(items, U.device)
         if users.dtype != items.dtype:
@@ -392,6 +435,19 @@ class MatrixFactorizationModel(torch.nn.Module):
             raise ValueError('``users`` and ``items`` must be 1-d tensors of equal length')
         yr = tuple(float(v) for v in self.hparams.y_range) if self.hparams.y_range is not None \
             else None
+        if self.training and self.hparams.dropout_p > 0:
+            # the stand-alone forward of a model in training mode (matrix_factorization.py:143-157:
+            # dropout on each embedding, then the product): rows through the gather kernel, the
+            # masks from torch's generator. The fused training step draws its own masks in-kernel.
+            D = U.shape[1]
+            rows = _GatherConcat.apply([users, items], U, self.item_embeddings.weight)
+            bias = _GatherConcat.apply([users, items], self.user_biases.weight,
+                                       self.item_biases.weight)
+            preds = (self.dropout(rows[:, :D]) * self.dropout(rows[:, D:])).sum(dim=1) \
+                + bias[:, 0] + bias[:, 1]
+            if yr is not None:
+                preds = torch.sigmoid(preds) * (yr[1] - yr[0]) + yr[0]
+            return preds
         return _ScoresFunction.apply(U, self.item_embeddings.weight, self.user_biases.weight,
                                      self.item_biases.weight, users, items, yr)
 
@@ -478,8 +534,6 @@ class MatrixFactorizationModel(torch.nn.Module):
             raise _abi.CmfError('a custom loss callable cannot run inside the fused step; use one '
                                 "of 'bpr', 'hinge', 'adaptive', 'adaptive_bpr', 'warp', 'mse', "
                                 "'mae'")
-        if train and self.hparams.dropout_p > 0:
-            raise _abi.CmfError('dropout_p > 0 is not supported by the fused B200 kernels')
         h = self.hparams
         users, items, negs, gidx, ratings = self._normalise_batch(batch)
         U = _abi.require_cuda(self.user_embeddings.weight.data, 'user_embeddings.weight')
@@ -592,6 +646,14 @@ class MatrixFactorizationModel(torch.nn.Module):
         a.B_global = int(global_batch)
         a.skip_item_update = 1 if skip_item_update else 0
         a.num_items_logical = int(num_items_logical)
+        if self.training and h.dropout_p > 0:
+            # nn.Dropout semantics: active whenever the module is in training mode
+            a.dropout_p = float(h.dropout_p)
+            data = interactions if interactions is not None else self.train_loader.interactions
+            a.seed = int(getattr(data, 'seed', 0) or 0)
+            a.epoch = int(epoch)
+            if not train:       # (no optimizer step to key the masks with)
+                a.emb_opt.step = 1
         if item_grads_event is not None:
             a.item_grads_ready_event = int(item_grads_event.cuda_event)
         with _abi.on_device(self.device):

@@ -525,3 +525,42 @@ def hybrid_forward(state: Dict[str, torch.Tensor], item_metadata: torch.Tensor,
         parts.append(stack('item_metadata_layer', item_metadata[items], False))
     out = stack('combined_layer', torch.cat(parts, dim=1), True)
     return (out + state['biases.0.weight'][users] + state['biases.1.weight'][items]).squeeze()
+
+
+# ------------------------------------------------------------------------------------------------
+# dropout (collie/model/matrix_factorization.py:118, :147)
+# ------------------------------------------------------------------------------------------------
+
+
+def dropout_mask(seed: int, step: int, epoch: int, gidx: int, slot: int, side: int, dim: int,
+                 p: float) -> np.ndarray:
+    """The mask ``nn.Dropout(p)`` would apply to one embedding row of one scored pair, drawn from
+    this project's counter-based stream (the reference draws from torch's global generator, which
+    no test pins): interaction at dataset position ``gidx``, ``slot`` 0 = the positive / 1 + n =
+    negative n, ``side`` 0 = user row / 1 = item row. Element d takes word d % 4 of the Philox
+    block with counter (gidx_lo, gidx_hi, epoch, slot << 16 | side << 15 | d // 4) and key
+    (seed_lo ^ 0x85EBCA6B, seed_hi ^ step); it is kept, scaled by 1 / (1 - p), when the word is
+    >= floor(p * 2^32)."""
+    thr = max(1, int(p * 4294967296.0))
+    scale = np.float32(1.0) / (np.float32(1.0) - np.float32(p))
+    out = np.zeros(dim, dtype=np.float32)
+    key = ((seed & 0xFFFFFFFF) ^ 0x85EBCA6B, ((seed >> 32) & 0xFFFFFFFF) ^ (step & 0xFFFFFFFF))
+    for blk in range((dim + 3) // 4):
+        words = philox4x32_10((gidx & 0xFFFFFFFF, gidx >> 32, epoch,
+                               (slot << 16) | (side << 15) | blk), key)
+        for j in range(4):
+            d = blk * 4 + j
+            if d < dim and words[j] >= thr:
+                out[d] = scale
+    return out
+
+
+def mf_forward_dropout(U, I, bu, bi, users, items, mask_u, mask_i, y_range=None):
+    """``forward`` in training mode: masks on both gathered embeddings, then the product
+    (matrix_factorization.py:143-157)."""
+    users, items = users.long(), items.long()
+    s = ((U[users] * mask_u) * (I[items] * mask_i)).sum(dim=1) + bu[users].squeeze(1) \
+        + bi[items].squeeze(1)
+    if y_range is not None:
+        s = torch.sigmoid(s) * (y_range[1] - y_range[0]) + y_range[0]
+    return s
