@@ -530,14 +530,23 @@ extern "C" int cmf_eval_tile_noalloc(const cmf_eval_t* a, void* stream) {
   CMF_REQUIRE(a, "cmf_eval_tile_noalloc: null args");
   // In host code `g_noalloc_scratch` is only a handle for the symbol; the device address has to be
   // asked for, once per device, with that device current.
-  static void* dev_ptr[64] = {nullptr};
+  static std::atomic<void*> dev_ptr[64];   // (zero-initialised; threads may race to fill a slot
+                                           // with the same address)
   int dev = -1;
   CMF_CUDA(cudaGetDevice(&dev));
   CMF_REQUIRE(dev >= 0 && dev < 64, "cmf_eval_tile_noalloc: device ordinal %d not supported", dev);
-  if (dev_ptr[dev] == nullptr) {
+  // the scratch belongs to the CURRENT device: the tables must live there too
+  if (a->I) {
+    cudaPointerAttributes attr{};
+    CMF_CUDA(cudaPointerGetAttributes(&attr, a->I));
+    CMF_REQUIRE(attr.type != cudaMemoryTypeDevice || attr.device == dev,
+                "cmf_eval_tile_noalloc: the tables live on device %d but device %d is current; "
+                "make the owning device current before the call", attr.device, dev);
+  }
+  if (dev_ptr[dev].load(std::memory_order_acquire) == nullptr) {
     void* ptr = nullptr;
     CMF_CUDA(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
-    dev_ptr[dev] = ptr;
+    dev_ptr[dev].store(ptr, std::memory_order_release);
   }
   const size_t need = cmf_eval_workspace_bytes(a->n_users_tile, a->num_items_shard, a->D, a->k,
                                                a->precision);
@@ -548,7 +557,7 @@ extern "C" int cmf_eval_tile_noalloc(const cmf_eval_t* a, void* stream) {
                 (long long)a->n_users_tile, (long long)a->num_items_shard, need,
                 (size_t)kNoAllocScratchBytes);
   cmf_eval_t b = *a;
-  b.workspace = dev_ptr[dev];
+  b.workspace = dev_ptr[dev].load(std::memory_order_acquire);
   b.workspace_bytes = kNoAllocScratchBytes;
   return cmf_eval_tile(&b, stream);
 }

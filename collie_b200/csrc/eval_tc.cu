@@ -905,6 +905,8 @@ int g_tc_list_len = 0;   // cmf_set_tuning key 5: 0 = automatic, else 8 / 16 / 2
 
 static int tc_list_len(int k) {
   if (g_tc_list_len > k) return g_tc_list_len;
+  // (a list only has to hold what ITS segment contributes to the top-k plus a margin for the
+  // error bound: the union of a row's eight and more lists is what k_tc_finish works on)
   return k <= 4 ? 8 : (k <= 10 ? 16 : 24);
 }
 
@@ -1074,6 +1076,7 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   } while (0)
   if (L.KL == 8 && L.epi_warps == 16) CMF_TC_LAUNCH(8, 16);
   else if (L.KL == 8) CMF_TC_LAUNCH(8, 8);
+  else if (L.KL == 12) CMF_TC_LAUNCH(12, 8);
   else if (L.KL == 16 && L.epi_warps == 16) CMF_TC_LAUNCH(16, 16);
   else if (L.KL == 16) CMF_TC_LAUNCH(16, 8);
   else CMF_TC_LAUNCH(24, 8);

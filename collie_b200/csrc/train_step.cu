@@ -571,7 +571,7 @@ extern "C" int cmf_set_tuning(int32_t key, int32_t value) {
     return prev;
   }
   if (key == 5) {
-    CMF_REQUIRE(value == 0 || value == 8 || value == 16 || value == 24,
+    CMF_REQUIRE(value == 0 || value == 8 || value == 12 || value == 16 || value == 24,
                 "cmf_set_tuning: list length %d", value);
     const int prev = g_tc_list_len;
     g_tc_list_len = value;

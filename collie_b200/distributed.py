@@ -520,7 +520,7 @@ def evaluate_sharded(metric_list, local_test, model, k=10, group=None, **kwargs)
 
 
 def evaluate_item_sharded(metric_list, test_interactions, model, k=10, group=None, precision=0,
-                          tile_users=512):
+                          tile_users=None):
     """``evaluate_in_batches`` for ``mapk`` / ``mrr`` with the ITEM axis sharded (for
     catalogues too large to score on one GPU): every rank holds the same test users and scores
     them against its own contiguous block of item rows.
@@ -549,6 +549,11 @@ def evaluate_item_sharded(metric_list, test_interactions, model, k=10, group=Non
     lo = min(rank * per_rank, n_items)
     hi = min(lo + per_rank, n_items)
     n_loc = hi - lo
+    if tile_users is None:
+        # users per call: the tensor-core path keeps no score tile, so a call takes as many users
+        # as the collectives of the merge are worth; the exact path scores into a workspace of
+        # 12 bytes per user x item
+        tile_users = 32768 if precision == 1 else max(1, min(4096, (1 << 30) // max(1, 12 * n_loc)))
     test_users = np.unique(test_interactions.mat.row)
     indptr, tgt_items, nnz = M._targets_all_users_device(test_interactions.mat.tocsr(), test_users,
                                                          dev)

@@ -278,6 +278,15 @@ def evaluate_in_batches(metric_list, test_interactions, model, k=10, batch_size=
                                 set(tc_names), tables=tables, user_ids=users_dev[s:e],
                                 precision=1, workspace=ws, reuse_item_prep=(s > 0),
                                 into=(whole, s), tc_status=status)['_workspace']
+                if s == 0 and e < n_test and int(status[1].item()) > (e - s) // 8:
+                    # the first tile already left many users to the exact path (scores too
+                    # close together for the error bound, e.g. an untrained model): do not spend
+                    # the remaining tiles on the tensor cores
+                    LAST_TC_STATUS.update(users=n_test, handed_to_exact_path=int(status[0]),
+                                          not_taken_over=int(status[1]), gave_up_after=e)
+                    return evaluate_in_batches(metric_list, test_interactions, model, k=k,
+                                               batch_size=batch_size, logger=logger,
+                                               verbose=verbose, precision=0)
         for j, name in enumerate(names):
             sums[j] = _per_user(name, whole, nnz, n_items).sum()
         if status is not None:
