@@ -875,14 +875,22 @@ def eval_block(job, peaks, with_cpu):
     tu, ti = eval_test_set(w, n_eval)
     ikw = dict(allow_missing_ids=True, check_num_negative_samples_is_valid=False,
                remove_duplicate_user_item_pairs=False, max_number_of_samples_to_consider=0)
-    model = job.model
     ni = w['num_items']
+    # two states of the same architecture: freshly initialised weights (ScaledEmbedding /
+    # ZeroEmbedding: the contract's "random-init weights"; headline) and the bench model after the
+    # training steps above (sparse Adam has moved every gathered row by ~lr per step: scores of
+    # thousands of items within 1e-7 of each other, the hard case for any selection by bound)
+    trained = job.model
+    torch.manual_seed(4242)             # the same tables on every rank
+    fresh = cb.MatrixFactorizationModel(train=job.data, embedding_dim=w['dim'], sparse=True,
+                                        lr_scheduler_func=None, loss=w['loss']).to(dev)
+    model = fresh
     if world == 1:
         local = cb.Interactions(users=tu, items=ti, num_users=w['num_users'], num_items=ni, **ikw)
         n_local = n_eval
 
-        def run(metrics, precision):
-            return cb.evaluate_in_batches(metrics, local, model, k=10, verbose=False,
+        def run(metrics, precision, m=None):
+            return cb.evaluate_in_batches(metrics, local, m or model, k=10, verbose=False,
                                           precision=precision)
     else:
         ltu, lti, _ = D.partition_interactions(tu, ti, rank, world)
@@ -891,8 +899,8 @@ def eval_block(job, peaks, with_cpu):
                                 num_items=ni, **ikw)
         n_local = len(np.unique(ltu))
 
-        def run(metrics, precision):
-            return D.evaluate_sharded(metrics, local, model, k=10, precision=precision)
+        def run(metrics, precision, m=None):
+            return D.evaluate_sharded(metrics, local, m or model, k=10, precision=precision)
 
     def timed(fn, reps):
         fn()                                       # first call: derives the device-side test set
@@ -941,6 +949,25 @@ def eval_block(job, peaks, with_cpu):
             'metrics': res if isinstance(res, list) else [res],
             'useful_tflops': useful, 'useful_frac_of_bf16_peak': useful / tpeak}
     out['variants'] = variants
+    out['weights'] = 'freshly initialised (ScaledEmbedding / ZeroEmbedding); see ' \
+                     'variants_after_training_steps for the bench model after its steps'
+    after = {}
+    for label, metrics, precision in (('mapk_tensor_core', [cb.mapk], 1),
+                                      ('mapk_mrr_tensor_core', [cb.mapk, cb.mrr], 1),
+                                      ('mapk_mrr_auc_exact_fp32', [cb.mapk, cb.mrr, cb.auc], 0)):
+        try:
+            dev_ms, wall, res = timed(lambda: run(metrics, precision, trained), 2)
+        except Exception as e:
+            _log(f'eval variant {label} (trained model) failed: {e!r}')
+            if world > 1:
+                raise
+            after[label] = {'error': repr(e)[:300]}
+            continue
+        from collie_b200 import metrics as M_
+        after[label] = {'value': n_eval / (dev_ms * 1e-3), 'unit': 'users/s', 'ms': dev_ms,
+                        'metrics': res if isinstance(res, list) else [res],
+                        'tc_status_rank0': dict(M_.LAST_TC_STATUS) if precision == 1 else None}
+    out['variants_after_training_steps'] = after
     head = variants.get('mapk_tensor_core', {})
     if 'value' in head:
         out.update(value=head['value'], ms=head['ms'], e2e=head['e2e'],

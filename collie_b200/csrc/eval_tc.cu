@@ -717,6 +717,12 @@ struct TcFinish {
   int32_t* fb_uid;      // ... and their user ids
   int32_t* status;      // [0] their number, [1] how many did not fit into fb_list
   int fb_cap;
+  // optional: the rows that did not fit, for the caller to re-rank (row_base + row of the tile,
+  // appended at the cursor caller_status[2])
+  int32_t* overflow_rows;
+  int32_t* caller_status;
+  int64_t row_base;
+  int overflow_cap;
 };
 
 constexpr int TC_LANE_CAND = 6;   // exact re-scorings one lane can hold; more -> the exact path
@@ -803,8 +809,16 @@ k_tc_finish(const TcFinish p) {
   if (fallback) {
     if (lane == 0) {
       const int at = atomicAdd(p.status + 0, 1);
-      if (at < p.fb_cap) { p.fb_list[at] = (int32_t)r; p.fb_uid[at] = (int32_t)p.user_ids[r]; }
-      else atomicAdd(p.status + 1, 1);
+      if (at < p.fb_cap) {
+        p.fb_list[at] = (int32_t)r;
+        p.fb_uid[at] = (int32_t)p.user_ids[r];
+      } else {
+        atomicAdd(p.status + 1, 1);
+        if (p.overflow_rows) {
+          const int idx = atomicAdd(p.caller_status + 2, 1);
+          if (idx < p.overflow_cap) p.overflow_rows[idx] = (int32_t)(p.row_base + r);
+        }
+      }
     }
     return;
   }
@@ -1094,6 +1108,10 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   f.n_before_best = a->n_before_best;
   f.fb_list = (int32_t*)(base + L.fb_list); f.fb_uid = (int32_t*)(base + L.fb_uid);
   f.status = status; f.fb_cap = L.fb_cap;
+  if (a->tc_status && a->tc_overflow_rows && a->tc_overflow_cap > 0) {
+    f.overflow_rows = a->tc_overflow_rows; f.caller_status = a->tc_status;
+    f.row_base = a->tc_row_base; f.overflow_cap = a->tc_overflow_cap;
+  }
   k_tc_finish<<<(unsigned)((a->n_users_tile * 32 + 255) / 256), 256, 0, s>>>(f);
   CMF_LAUNCH_CHECK();
 

@@ -58,7 +58,7 @@ def _targets_all_users_device(targets: csr_matrix, test_users, device):
 
 def _eval_tile(device, n_users, n_items, k, indptr, tgt_items, want, tables=None, user_ids=None,
                scores=None, precision=0, workspace=None, reuse_item_prep=False, item_offset=0,
-               ext_best=None, into=None, tc_status=None):
+               ext_best=None, into=None, tc_status=None, tc_overflow=None):
     """One ``cmf_eval_tile`` call; returns dict of per-user device tensors. ``item_offset`` /
     ``n_items`` select an item shard of the table (global ids come back); ``ext_best`` = (score,
     id) of every user's best target over ALL shards, against which the MRR counter counts;
@@ -87,6 +87,11 @@ def _eval_tile(device, n_users, n_items, k, indptr, tgt_items, want, tables=None
     if tc_status is not None:
         a.tc_status = tc_status.data_ptr()
         keep.append(tc_status)
+        if tc_overflow is not None:          # (rows tensor, row number of the tile's first user)
+            a.tc_overflow_rows = tc_overflow[0].data_ptr()
+            a.tc_overflow_cap = int(tc_overflow[0].numel())
+            a.tc_row_base = int(tc_overflow[1])
+            keep.append(tc_overflow[0])
     out = {}
 
     def vec(name, dtype):
@@ -271,17 +276,20 @@ def evaluate_in_batches(metric_list, test_interactions, model, k=10, batch_size=
         if tc_names:
             tile = _TC_TILE_USERS
             ws = None
-            status = torch.zeros(2, dtype=torch.int32, device=device)
+            status = torch.zeros(4, dtype=torch.int32, device=device)
+            overflow = torch.empty(n_test, dtype=torch.int32, device=device)
             for s in range(0, n_test, tile):
                 e = min(s + tile, n_test)
                 ws = _eval_tile(device, e - s, n_items, k, indptr[s:e + 1], tgt_items,
                                 set(tc_names), tables=tables, user_ids=users_dev[s:e],
                                 precision=1, workspace=ws, reuse_item_prep=(s > 0),
-                                into=(whole, s), tc_status=status)['_workspace']
-                if s == 0 and e < n_test and int(status[1].item()) > (e - s) // 8:
-                    # the first tile already left many users to the exact path (scores too
-                    # close together for the error bound, e.g. an untrained model): do not spend
-                    # the remaining tiles on the tensor cores
+                                into=(whole, s), tc_status=status,
+                                tc_overflow=(overflow, s))['_workspace']
+                if s == 0 and e < n_test and int(status[1].item()) > (e - s) // 4:
+                    # the first tile already left a quarter of its users to the exact path
+                    # (scores too close together for the error bound, e.g. an untrained model):
+                    # do not spend the remaining tiles on the tensor cores
+                    LAST_TC_STATUS.clear()
                     LAST_TC_STATUS.update(users=n_test, handed_to_exact_path=int(status[0]),
                                           not_taken_over=int(status[1]), gave_up_after=e)
                     return evaluate_in_batches(metric_list, test_interactions, model, k=k,
@@ -291,15 +299,35 @@ def evaluate_in_batches(metric_list, test_interactions, model, k=10, batch_size=
             sums[j] = _per_user(name, whole, nnz, n_items).sum()
         if status is not None:
             # one read-back for the whole evaluation: the metric sums and the tensor-core status
+            n_over = int(status[2].item()) if tc_names else 0
+            if n_over:
+                # users beyond what the calls could hand to the exact path themselves: ONLY they
+                # go through it now (their rows of the per-user arrays are overwritten)
+                rows = torch.sort(overflow[:n_over].long())[0]
+                sub_nnz = nnz[rows]
+                sub_indptr = torch.zeros(n_over + 1, dtype=torch.int64, device=device)
+                torch.cumsum(sub_nnz, 0, out=sub_indptr[1:])
+                take = torch.repeat_interleave(indptr[rows] - sub_indptr[:-1], sub_nnz) \
+                    + torch.arange(int(sub_indptr[-1]), device=device)
+                sub_items = tgt_items[take]
+                sub_users = users_dev[rows].contiguous()
+                tile_x = max(1, min(_TILE_USERS, _MAX_TILE_BYTES // max(1, 12 * n_items)))
+                ws_x = None
+                for s in range(0, n_over, tile_x):
+                    e = min(s + tile_x, n_over)
+                    res = _eval_tile(device, e - s, n_items, k, sub_indptr[s:e + 1], sub_items,
+                                     set(tc_names), tables=tables, user_ids=sub_users[s:e],
+                                     precision=0, workspace=ws_x)
+                    ws_x = res['_workspace']
+                    for n_ in tc_names:
+                        key_ = _ING[n_][0]
+                        whole[key_][rows[s:e]] = res[key_]
+                for j, name in enumerate(names):
+                    sums[j] = _per_user(name, whole, nnz, n_items).sum()
             host = torch.cat([sums, status.double()]).tolist()
-            LAST_TC_STATUS.update(users=n_test, handed_to_exact_path=int(host[-2]),
-                                  not_taken_over=int(host[-1]))
-            if host[-1] != 0:
-                # more users than one call can hand to the exact path had candidates the error
-                # bound could not separate (heavily tied scores): the exact path takes it all
-                return evaluate_in_batches(metric_list, test_interactions, model, k=k,
-                                           batch_size=batch_size, logger=logger, verbose=verbose,
-                                           precision=0)
+            LAST_TC_STATUS.clear()
+            LAST_TC_STATUS.update(users=n_test, handed_to_exact_path=int(host[-4]),
+                                  not_taken_over=int(host[-3]), re_ranked_afterwards=n_over)
             all_scores = [v / n_test for v in host[:len(names)]]
         else:
             all_scores = (sums / n_test).tolist()

@@ -380,6 +380,13 @@ typedef struct {
    * workspace can take over in one call -- their outputs are NOT written: the caller repeats the
    * tile with precision = 0 when it finds [1] != 0 */
   int32_t *tc_status;
+  /* optional, with tc_status (then int32[4]): the users of [1] are listed for the caller instead
+   * of being lost -- tc_overflow_rows[tc_status[2]++] = tc_row_base + (row of the tile) -- so that
+   * only they are repeated with precision = 0 (tc_overflow_cap entries at most) */
+  int32_t *tc_overflow_rows;
+  int64_t tc_row_base;
+  int32_t tc_overflow_cap;
+  int32_t reserved4_;
 } cmf_eval_t;
 
 CMF_API size_t cmf_eval_workspace_bytes(int64_t n_users_tile, int64_t num_items_shard, int32_t D, int32_t k,
