@@ -123,8 +123,8 @@ class ShardedMatrixFactorization(object):
             raise ValueError("CMF_FENCE must be 'kernel', 'symm' or 'nccl'")
         if multicast not in ('auto', True, False):
             raise ValueError("multicast must be 'auto', True or False")
-        if multicast == 'auto' and os.environ.get('CMF_MULTICAST', '1') == '0':
-            multicast = False
+        if multicast == 'auto' and os.environ.get('CMF_MULTICAST') in ('0', '1'):
+            multicast = os.environ['CMF_MULTICAST'] == '1'      # experiments / A-B runs
         self._multicast = multicast
         self.rank = dist.get_rank(group)
         self.world = dist.get_world_size(group)
