@@ -324,7 +324,9 @@ CMF_API int cmf_item_exchange_update(const cmf_peers_t *peers, float *M, float *
 
 /*
  * Evaluation of one tile of users against the whole item table (or an item shard):
- * scores S = U[user_ids] . I^T + bu + bi are never written to HBM; per user the kernel keeps the
+ * scores S = U[user_ids] . I^T + bu + bi are not returned (precision 1 never writes them to
+ * memory; precision 0 keeps the tile's scores in the caller's workspace between its scoring and its
+ * ranking kernel); per user the call keeps the
  * top-k (score descending, item id ascending), and -- given the users' target items in CSR form --
  * the MAP@k / MRR / AUC ingredients. Replaces get_preds + mapk + mrr + auc,
  * collie/metrics.py:77-107, 144-198, 201-240, 243-282, for one iteration of the loop at :379-384.
