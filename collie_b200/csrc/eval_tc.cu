@@ -11,13 +11,27 @@
 // mapk :144-198, mrr :201-240.
 //
 // Operands: x = hi + lo with hi = bf16(x), lo = bf16(x - hi).
-//   terms = 1 (top-k / MAP@k only):  A' = [Uh | bu as 3 bf16 pieces, 1, 1, 1],  B' = [Ih | 1, 1, 1, bi as 3 pieces]
-//     K' = D + 6: one bf16 product per element. |S~ - S| <= c1 |u| |i| + 2^-20 (|bu| + |bi|),
+//   terms = 1 (top-k / MAP@k only):  A' = [Uh | bu as 3 bf16 pieces, 1, 1, 1 | a_u, a2_u]
+//                                    B' = [Ih | 1, 1, 1, bi as 3 pieces     | b_i, 1   ]
+//     K' = D + 8: one bf16 product per element. |S~ - S| <= c1 |u| |i| + 2^-20 (|bu| + |bi|),
 //     c1 = 4.1e-3 (2^-8 for the two roundings, Cauchy-Schwarz over d, plus both accumulations).
 //   terms = 3 (with the MRR counter): A' = [Uh | Uh | Ul | ...], B' = [Ih | Il | Ih | ...],
-//     K' = 3 D + 6, S~ = Uh.Ih + Uh.Il + Ul.Ih: c3 = 8e-5 (3 * 2^-18 for the dropped terms, the
-//     rest for fp32 accumulation of 3 D + 4 products), a band of a few items per user.
-//   Per user the margin uses the largest item norm of the shard: E_u = c |u| max|i| + ...
+//     K' = 3 D + 8, S~ = Uh.Ih + Uh.Il + Ul.Ih: c3 = 8e-5 (3 * 2^-18 for the dropped terms, the
+//     rest for fp32 accumulation of 3 D + 4 products).
+//   The last two slots carry the bound ITSELF into the accumulator: a_u = c |u|, b_i = |i| (both
+//   rounded UP to bf16), a2_u = 2^-20 (|bu| + max |bi|), so the GEMM yields
+//       B = S~ + a_u b_i + a2_u >= S,
+//   an upper bound of the exact score with the margin e = a_u b_i + a2_u of that very pair (no
+//   shard-wide largest norm: a few large item rows do not widen everybody's margin), and
+//   B - 2 e (1 + 2^-10) <= S is the matching lower bound, recomputed by k_tc_finish for the few
+//   entries it looks at. Lists are kept by B. Sufficiency: if the largest B any list dropped lies
+//   below the k-th largest LOWER bound of the entries, no dropped item can be in the exact top-k;
+//   candidates = entries whose B reaches that k-th lower bound.
+//   MRR: B < best target's exact score: surely not before it; B > that score + 2 e_tile (e_tile =
+//   the largest margin among the tile's 256 columns): surely before it; between: re-scored. For
+//   this form the split copy holds the item rows ORDERED BY NORM (radix sort of the squared norms,
+//   once per evaluation), which makes e_tile tight; lists and band then hold positions in that
+//   copy and k_tc_finish maps them back to ids.
 //
 // The (128-user tile, 256-item tile) pairs are cut into equal contiguous chunks, one per CTA, one
 // CTA per SM: a CTA walks its chunk as segments that each lie inside one user tile and leaves every
@@ -29,7 +43,7 @@
 //   warp 2      TMEM allocation
 //   warps 4..11 epilogue, two warps per scheduler (each takes half of a tile's columns):
 //               tcgen05.ld 32x32b (thread = user row); the biases are folded into the GEMM (four
-//               extra K slots), so the accumulator IS the score: a branch-free pass builds 32-bit
+//               extra K slots), so the accumulator IS the (upper bound of the) score: a branch-free pass builds 32-bit
 //               predicate masks per 32 columns (beats the row's KL-th best / surely beats the best
 //               target / cannot be told from it), then lane-parallel inserts into a sorted list
 //               held in registers
@@ -37,6 +51,7 @@
 // nothing outside the lists can reach the top-k, exact re-scoring, exact top-k, AP@k, MRR counter.
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cub/device/device_radix_sort.cuh>
 
 #include "common.cuh"
 
@@ -49,7 +64,7 @@ constexpr int TC_BN = 256;        // items per MMA tile (one instruction: M = 12
 constexpr int TC_BK = 64;         // bf16 per K block = one 128-byte swizzle row
 constexpr int TC_STAGES = 3;
 constexpr int TC_MAXK = 16;       // largest k
-constexpr int TC_BIAS_SLOTS = 6;   // K slots that carry the two biases (three bf16 pieces each)
+constexpr int TC_BIAS_SLOTS = 8;   // extra K slots: the two biases (three bf16 pieces each) + two error-bound slots
 constexpr int TC_BCAP = 64;       // band entries kept per (user, slot) for the MRR counter
 constexpr int TC_A_BYTES = TC_BM * TC_BK * 2;   // 16 KB: one K-block of the user tile
 constexpr int TC_B_BYTES = TC_BN * TC_BK * 2;   // 32 KB: one K-block of an item tile
@@ -222,8 +237,17 @@ constexpr float kTcCBias = 9.5367431640625e-7f;   // 2^-20: the biases are exact
 // the shard, by atomicMax on the bit pattern of a non-negative float).
 // One warp per row; a lane produces two adjacent bf16 at a time (one 4-byte store, 128 bytes per
 // warp), the row id is read once per row.
+// smallest bf16 >= x (x >= 0)
+__device__ __forceinline__ __nv_bfloat16 bf16_up(float x) {
+  __nv_bfloat16 h = __float2bfloat16_rn(x);
+  if (__bfloat162float(h) < x) h = __ushort_as_bfloat16((unsigned short)(__bfloat16_as_ushort(h) + 1));
+  return h;
+}
+
+// ea / eb: this row's two error-bound slots (users: a_u, a2_u; items: b_i, 1), see the file header
 __device__ __forceinline__ __nv_bfloat16 tc_split_elem(const float* __restrict__ srow, float b,
-                                                       int c, int D, int users, int T) {
+                                                       int c, int D, int users, int T,
+                                                       __nv_bfloat16 ea, __nv_bfloat16 eb) {
   if (c < T * D) {
     const int seg = c / D, d = c - seg * D;
     __nv_bfloat16 hi, lo;
@@ -231,7 +255,7 @@ __device__ __forceinline__ __nv_bfloat16 tc_split_elem(const float* __restrict__
     const bool want_lo = T == 3 && (users ? (seg == 2) : (seg == 1));
     return want_lo ? lo : hi;
   }
-  if (c < T * D + TC_BIAS_SLOTS) {
+  if (c < T * D + 6) {
     // the bias as THREE bf16 pieces (24 mantissa bits: the whole fp32 value) against 1.0, so the
     // biases enter the accumulator exactly; users own the first three slots, items the last three
     const int q = c - T * D;
@@ -244,29 +268,42 @@ __device__ __forceinline__ __nv_bfloat16 tc_split_elem(const float* __restrict__
     const int piece = q % 3;
     return piece == 0 ? p0 : (piece == 1 ? p1 : p2);
   }
+  if (c == T * D + 6) return ea;
+  if (c == T * D + 7) return eb;
   return __float2bfloat16_rn(0.f);
 }
 
+// Error-bound slots. Users carry a_u = bf16_up(c |u|) and a2_u = bf16_up(2^-20 (|bu| + max|bi|)),
+// items b_i = bf16_up(|i|) and 1: the accumulator becomes B = S~ + a_u b_i + a2_u >= S, an UPPER
+// bound of the exact score with the margin of that very pair (no shard-wide largest norm). The
+// values as stored (as floats) go to row_a / row_a2 so that k_tc_finish can take the margin off
+// again: users row_a = a_u, row_a2 = a2_u; items row_a = b_i. stats[1] = max |bi| of the shard
+// (items are split first).
 __global__ void __launch_bounds__(256)
 k_tc_split(const float* __restrict__ src, const float* __restrict__ bias,
            const int32_t* __restrict__ ids, int64_t row_offset, int64_t n_rows, int64_t n_rows_pad,
-           int D, int Kp, int users, int T, __nv_bfloat16* __restrict__ out,
-           float* __restrict__ row_norm, float* __restrict__ row_absb, uint32_t* __restrict__ stats) {
+           int D, int Kp, int users, int T, float c, __nv_bfloat16* __restrict__ out,
+           float* __restrict__ row_a, float* __restrict__ row_a2, uint32_t* __restrict__ stats) {
   const int lane = threadIdx.x & 31;
   const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const float bmax = users ? __uint_as_float(stats[1]) : 0.f;
   for (int64_t r = warp0; r < n_rows_pad; r += n_warps) {
     __nv_bfloat162* orow = reinterpret_cast<__nv_bfloat162*>(out + r * Kp);   // Kp is even
     if (r >= n_rows) {
       for (int c2 = lane; c2 < Kp / 2; c2 += 32) orow[c2] = __floats2bfloat162_rn(0.f, 0.f);
-      if (lane == 0 && row_norm) { row_norm[r] = 0.f; row_absb[r] = 0.f; }
+      if (lane == 0) {
+        if (row_a) row_a[r] = 0.f;
+        if (row_a2) row_a2[r] = 0.f;
+      }
       continue;
     }
-    const int64_t row = ids ? (int64_t)ids[r] : row_offset + r;
+    const int64_t row = row_offset + (ids ? (int64_t)ids[r] : r);
     const float* srow = src + row * D;
     const float b = bias[row];
     float ss = 0.f;
-    if ((D & 1) == 0 && (reinterpret_cast<uintptr_t>(src) & 7) == 0) {
+    const bool fast = (D & 1) == 0 && (reinterpret_cast<uintptr_t>(src) & 7) == 0;
+    if (fast) {
       // each value is split once and stored to its segments
       for (int d2 = lane; d2 < D / 2; d2 += 32) {
         const float2 x = *reinterpret_cast<const float2*>(srow + 2 * d2);
@@ -281,42 +318,65 @@ k_tc_split(const float* __restrict__ src, const float* __restrict__ bias,
           orow[D + d2] = users ? lo : hi;
         }
       }
-      for (int c2 = T * D / 2 + lane; c2 < Kp / 2; c2 += 32) {   // bias slots + zero tail
-        __nv_bfloat162 v;
-        v.x = tc_split_elem(srow, b, 2 * c2, D, users, T);
-        v.y = tc_split_elem(srow, b, 2 * c2 + 1, D, users, T);
-        orow[c2] = v;
-      }
     } else {
       for (int d = lane; d < D; d += 32) ss = fmaf(srow[d], srow[d], ss);
-      for (int c2 = lane; c2 < Kp / 2; c2 += 32) {
-        __nv_bfloat162 v;
-        v.x = tc_split_elem(srow, b, 2 * c2, D, users, T);
-        v.y = tc_split_elem(srow, b, 2 * c2 + 1, D, users, T);
-        orow[c2] = v;
-      }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    const float nrm = sqrtf(ss) * 1.00002f;     // (fp32 sum of squares: D * 2^-24 relative)
+    const __nv_bfloat16 ea = bf16_up(users ? c * nrm : nrm);
+    const __nv_bfloat16 eb = users ? bf16_up(kTcCBias * (fabsf(b) + bmax) + 1e-37f)
+                                   : __float2bfloat16_rn(1.f);
+    for (int c2 = (fast ? T * D / 2 : 0) + lane; c2 < Kp / 2; c2 += 32) {   // (bias, bound slots, zero tail)
+      __nv_bfloat162 v;
+      v.x = tc_split_elem(srow, b, 2 * c2, D, users, T, ea, eb);
+      v.y = tc_split_elem(srow, b, 2 * c2 + 1, D, users, T, ea, eb);
+      orow[c2] = v;
+    }
     if (lane == 0) {
-      const float nrm = sqrtf(ss) * 1.00002f;     // (fp32 sum of squares: D * 2^-24 relative)
-      if (row_norm) { row_norm[r] = nrm; row_absb[r] = fabsf(b); }
-      if (stats) {
-        atomicMax(stats + 0, __float_as_uint(nrm));
-        atomicMax(stats + 1, __float_as_uint(fabsf(b)));
+      if (row_a) row_a[r] = __bfloat162float(ea);
+      if (row_a2) row_a2[r] = __bfloat162float(eb);
+      if (!users && stats) {   // (read first: all rows hammering one word was most of the kernel's time)
+        if (__float_as_uint(fabsf(b)) > *(volatile uint32_t*)(stats + 1))
+          atomicMax(stats + 1, __float_as_uint(fabsf(b)));
       }
     }
   }
 }
 
-// per-user margin E_u = c |u| max|i| + 2^-15 (|bu| + max|bi|)
-__global__ void k_tc_margin(const float* __restrict__ unorm, const float* __restrict__ uabsb,
-                            const uint32_t* __restrict__ stats, float c, int64_t n,
-                            float* __restrict__ E) {
-  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (r >= n) return;
-  const float imax = __uint_as_float(stats[0]), bmax = __uint_as_float(stats[1]);
-  E[r] = c * unorm[r] * imax + kTcCBias * (uabsb[r] + bmax) + 1e-37f;
+// sort keys for the item order of the MRR form: squared norm of every row (non-negative floats
+// order like their bit patterns) and the row's number
+__global__ void __launch_bounds__(256)
+k_tc_norm_keys(const float* __restrict__ src, int64_t row_offset, int64_t n_rows, int D,
+               uint32_t* __restrict__ keys, int32_t* __restrict__ vals) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp0; r < n_rows; r += n_warps) {
+    const float* srow = src + (row_offset + r) * D;
+    float ss = 0.f;
+    for (int d = lane; d < D; d += 32) ss = fmaf(srow[d], srow[d], ss);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    if (lane == 0) { keys[r] = __float_as_uint(ss); vals[r] = (int32_t)r; }
+  }
+}
+
+// largest b_i of every item tile (TC_BN rows): what the epilogue can know about a column's margin
+__global__ void __launch_bounds__(TC_BN)
+k_tc_tile_max(const float* __restrict__ item_b, int64_t n_items, float* __restrict__ tile_bmax) {
+  const int64_t i = (int64_t)blockIdx.x * TC_BN + threadIdx.x;
+  float v = i < n_items ? item_b[i] : 0.f;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  __shared__ float sm[TC_BN / 32];
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float m = 0.f;
+    for (int w = 0; w < TC_BN / 32; ++w) m = fmaxf(m, sm[w]);
+    tile_bmax[blockIdx.x] = m;
+  }
 }
 
 // the exact path's score of one (user, item) pair: fmaf over d ascending from 0, then + bu, + bi
@@ -379,7 +439,9 @@ struct TcParams {
   int64_t n_items, item_offset;
   const float* best_s;   // exact score of the user's best target (MRR), may be NULL
   const int32_t* best_id;
-  const float* margin;   // E_u per user row
+  const float* ua;       // a_u, a2_u per user row and the largest b_i per item tile: the margin
+  const float* ub2;      // of a pair is a_u b_i + a2_u (k_tc_split)
+  const float* tile_bmax;
   float* cand_s;         // [n_users_pad][n_slots][KL]
   int32_t* cand_i;
   int32_t* cnt;          // [n_users_pad][n_slots] items surely ranked before the best target
@@ -399,7 +461,9 @@ __device__ __forceinline__ int tc_slot(int64_t lin_start, int m, int n_tiles, in
 // The epilogue is bound by issue latency, not by instruction count (two instructions per score on
 // two different pipes): four warps per scheduler keep both pipes fed where two leave them idle
 // more than half of the time. Sixteen warps leave 96 registers per thread: lists up to KL = 16.
-template <int KL, int EW>   // KL = per-row list length kept in registers, > k
+// DBG: the experiment switches of cmf_set_tuning key 3 and the insert counters (kept out of the
+// shipped instantiations: the counter updates alone were 5 % of the kernel's instructions).
+template <int KL, int EW, bool DBG>   // KL = per-row list length kept in registers, > k
 __global__ void __launch_bounds__(128 + 32 * EW, 1)
 k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const TcParams p) {
@@ -547,11 +611,15 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       // MRR: x > t_hi is surely ranked before the best target, x < t_lo surely after it; what
       // lies between cannot be told from it with these scores and is re-scored by k_tc_finish
       const bool mrr = p.want_mrr && valid && p.best_id[urow] >= 0;
+      // The accumulator is an upper bound B >= S. B < bs: surely not before the target. B beyond
+      // bs + twice the largest margin of the tile's columns: surely before it.
       float t_hi = INFINITY, t_lo = INFINITY;   // (no target: nothing before, nothing in the band)
+      float m_ua = 0.f, m_ub2 = 0.f, m_bs = 0.f;
       if (mrr) {
-        const float bs = p.best_s[urow], E = p.margin[urow];
-        t_hi = bs + E;
-        t_lo = bs - E;
+        m_bs = p.best_s[urow];
+        m_ua = p.ua[urow];
+        m_ub2 = p.ub2[urow];
+        t_lo = m_bs;
       }
       int before = 0, nband = 0;
       int32_t* band = p.band_i + ((int64_t)urow * p.n_slots + slot) * TC_BCAP;
@@ -565,20 +633,13 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) +
                                (uint32_t)(acc * TC_BN + sub * SUBW);
         const int ncols = (int)min((int64_t)TC_BN, p.n_items - n0);   // < TC_BN only in the last tile
-        const int gid0 = (int)(p.item_offset + n0);
-        // 32 columns at a time go to registers; the accumulator is handed back as soon as the
-        // last of them has been read, before they are ranked
-#pragma unroll 1
-        for (int g = 0; g < SUBW / 32; ++g) {
-          float v[32];
-          tmem_ld32_nowait(taddr + g * 32, v);
-          tmem_wait_ld(v);
-          if (g == SUBW / 32 - 1) {
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
-          }
-          if (p.debug == 1) continue;
+        const int gid0 = (int)n0;   // lists and band hold POSITIONS in the split copy; k_tc_finish maps them to ids
+        if (mrr) t_hi = m_bs + 2.002f * fmaf(m_ua, p.tile_bmax[n0 / TC_BN], m_ub2);
+        // 32 columns at a time go to registers, the next 32 already on their way from TMEM while
+        // these are ranked; the accumulator is handed back as soon as the last of them has been
+        // read, before they are ranked
+        auto rank32 = [&](const float (&v)[32], int g) {
+          if (DBG && p.debug == 1) return;
           const int c0 = sub * SUBW + g * 32;
           // branch-free pass: bit j of each mask = predicate of column c0 + j. x > y <=> the sign
           // bit of (y - x) (no flush-to-zero here, so a nonzero difference keeps its sign; equal
@@ -618,37 +679,58 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
           }
           m_ins &= m_rng;
-          if (p.debug == 2) m_ins &= 1u;   // experiments: (almost) no inserts
+          if (DBG && p.debug == 2) m_ins &= 1u;   // experiments: (almost) no inserts
           // lanes insert side by side, each its own next candidate (column j differs per lane)
           while (__any_sync(0xffffffffu, m_ins != 0)) {
-            ++dbg_rounds;
+            if (DBG) ++dbg_rounds;
             if (m_ins) {
               const int j = __ffs(m_ins) - 1;
               m_ins &= m_ins - 1;
               const float sc = pick32(v, j);
               if (sc > thr) {     // thr may have risen within the chunk
-                // sorted insert; an equal score stays behind the entries already there
-                float cs = sc;
-                int ci = gid0 + c0 + j;
-                bool up = false;   // sticky: below the insertion point everything shifts down
+                // sorted insert; an equal score stays behind the entries already there. The list
+                // is non-increasing, so "sc beats entry e" is monotone in e and the new entry e is
+                // old e - 1 where sc beats e - 1, sc where it beats e only, old e otherwise: every
+                // entry on its own, no chain through the list (a carried insert runs at the
+                // latency of 3 * KL dependent instructions with two warps per scheduler)
+                const int ci = gid0 + c0 + j;
+                bool beats[KL];
 #pragma unroll
-                for (int e = 0; e < KL; ++e) {
-                  up = up || cs > ls[e];
-                  const float os = ls[e];
-                  const int oi = li[e];
-                  ls[e] = up ? cs : os;
-                  li[e] = up ? ci : oi;
-                  cs = up ? os : cs;
-                  ci = up ? oi : ci;
+                for (int e = 0; e < KL; ++e) beats[e] = sc > ls[e];
+#pragma unroll
+                for (int e = KL - 1; e >= 1; --e) {
+                  ls[e] = beats[e - 1] ? ls[e - 1] : (beats[e] ? sc : ls[e]);
+                  li[e] = beats[e - 1] ? li[e - 1] : (beats[e] ? ci : li[e]);
                 }
+                ls[0] = beats[0] ? sc : ls[0];
+                li[0] = beats[0] ? ci : li[0];
                 thr = ls[KL - 1];
-                ++dbg_ins;
+                if (DBG) ++dbg_ins;
               }
             }
           }
+        };
+        constexpr int NG = SUBW / 32;
+        static_assert(NG % 2 == 0, "chunks are processed in pairs");
+        auto release_acc = [&]() {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+        };
+        float va[32], vb[32];
+        tmem_ld32_nowait(taddr, va);
+#pragma unroll 1
+        for (int g = 0; g < NG; g += 2) {
+          tmem_wait_ld(va);
+          tmem_ld32_nowait(taddr + (g + 1) * 32, vb);
+          rank32(va, g);
+          tmem_wait_ld(vb);
+          if (g + 2 < NG) tmem_ld32_nowait(taddr + (g + 2) * 32, va);
+          else release_acc();
+          rank32(vb, g + 1);
         }
       }
-      if (p.debug == 4) {
+      if (DBG && p.debug == 4) {
         atomicAdd(p.dbg + 0, (unsigned long long)dbg_ins);
         if (lane == 0) atomicAdd(p.dbg + 1, (unsigned long long)dbg_rounds);
       }
@@ -702,7 +784,10 @@ struct TcFinish {
   const int32_t *cnt, *bcnt, *band_i;
   int n_slots, KL, k, D, want_mrr;
   int64_t n_users;
-  const float* margin;
+  const float *ua, *ub2;     // a_u, a2_u per user row; b_i per item of the shard (k_tc_split)
+  const float* item_b;       // ... by position in the split copy
+  const int32_t* perm;       // position -> row of the shard (NULL: identity)
+  int64_t item_offset;
   const float *U, *I, *bu, *bi;
   const int32_t* user_ids;
   const int64_t* tgt_indptr;
@@ -726,6 +811,7 @@ struct TcFinish {
 };
 
 constexpr int TC_LANE_CAND = 6;   // exact re-scorings one lane can hold; more -> the exact path
+constexpr int TC_EPL = 6;         // list entries per lane kept in registers (192 per user)
 
 // One warp per user. (1) A_k = the k-th best key of the union of the slots' lists; T = the best
 // score any item OUTSIDE the lists can have (the largest last entry of a full list). (2) If
@@ -740,39 +826,66 @@ k_tc_finish(const TcFinish p) {
   const int n_ent = p.n_slots * p.KL;
   const float* cs = p.cand_s + r * n_ent;
   const int32_t* ci = p.cand_i + r * n_ent;
-  const float E = p.margin[r];
+  const float ua = p.ua[r], ub2 = p.ub2[r];
   // entry e of the walk = rank j of slot s with e = j * n_slots + s: the heads of the lists,
-  // where the candidates are, spread over the lanes
-  auto entry = [&](int e, float& s, int& id) {
+  // where the candidates are, spread over the lanes. s = the pair's UPPER bound B (what the
+  // accumulator held); lo = B minus twice the pair's own margin, a LOWER bound of the exact score.
+  auto entry = [&](int e, float& s, float& lo, int& id) {
     const int j = e / p.n_slots, sl = e - j * p.n_slots;
     s = cs[sl * p.KL + j];
-    id = ci[sl * p.KL + j];
+    const int pos = ci[sl * p.KL + j];
+    id = pos >= 0 ? (int)(p.item_offset + (p.perm ? p.perm[pos] : pos)) : -1;
+    lo = pos >= 0 ? s - 2.002f * fmaf(ua, p.item_b[pos], ub2) : -INFINITY;
   };
   bool fallback = false;
-  // ---- (1)
+  // the lists are read ONCE: up to TC_EPL entries per lane stay in registers (the k selection
+  // rounds below re-read them from memory before: ten round trips per user)
+  const bool in_regs = n_ent <= 32 * TC_EPL;
+  uint64_t lk[TC_EPL];    // ranking keys by lower bound
+  float ub_s[TC_EPL];     // upper bounds
+#pragma unroll
+  for (int c = 0; c < TC_EPL; ++c) {
+    lk[c] = 0;
+    ub_s[c] = -INFINITY;
+    const int e = lane + 32 * c;
+    if (in_regs && e < n_ent) {
+      float s, lo; int id;
+      entry(e, s, lo, id);
+      lk[c] = tc_key(lo, id);
+      ub_s[c] = s;
+    }
+  }
+  // ---- (1) the k-th largest lower bound: at least k items have an exact score >= it
   uint64_t prev = ~0ull;
   int found = 0;
   for (int round = 0; round < p.k; ++round) {
     uint64_t best = 0;
-    for (int e = lane; e < n_ent; e += 32) {
-      float s; int id;
-      entry(e, s, id);
-      const uint64_t key = tc_key(s, id);
-      if (key < prev && key > best) best = key;
+    if (in_regs) {
+#pragma unroll
+      for (int c = 0; c < TC_EPL; ++c)
+        if (lk[c] < prev && lk[c] > best) best = lk[c];
+    } else {
+      for (int e = lane; e < n_ent; e += 32) {
+        float s, lo; int id;
+        entry(e, s, lo, id);
+        const uint64_t key = tc_key(lo, id);
+        if (key < prev && key > best) best = key;
+      }
     }
     best = warp_max_u64(best);
     if (best == 0) break;
     prev = best;
     ++found;
   }
-  // everything outside the lists was pushed out of a full list: it lies at or below that list's
-  // last entry (lists that never filled have lost nothing)
+  // everything outside the lists was pushed out of a full list: its upper bound lies at or below
+  // that list's last entry (lists that never filled have lost nothing)
   float T = -INFINITY;
   for (int sl = lane; sl < p.n_slots; sl += 32)
     if (ci[sl * p.KL + p.KL - 1] >= 0) T = fmaxf(T, cs[sl * p.KL + p.KL - 1]);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) T = fmaxf(T, __shfl_xor_sync(0xffffffffu, T, o));
-  const float thresh = found == p.k ? tc_key_score(prev) - 2.f * E : -INFINITY;
+  // an item can be in the exact top-k only if its upper bound reaches the k-th lower bound
+  const float thresh = found == p.k ? tc_key_score(prev) : -INFINITY;
   if (!(T < thresh) && T != -INFINITY) fallback = true;
   // ---- MRR ingredients (before anything is written: a band that overflowed also falls back)
   const bool mrr = p.want_mrr != 0;
@@ -793,17 +906,26 @@ k_tc_finish(const TcFinish p) {
   int n_mine = 0;
 #pragma unroll
   for (int c = 0; c < TC_LANE_CAND; ++c) ek[c] = 0;
-  for (int e = lane; e < n_ent; e += 32) {
-    float s; int id;
-    entry(e, s, id);
-    if (id < 0 || !(s >= thresh)) continue;
-    if (n_mine == TC_LANE_CAND) { fallback = true; break; }
+  auto rescore = [&](float s, int id) {
+    if (id < 0 || !(s >= thresh) || fallback) return;
+    if (n_mine == TC_LANE_CAND) { fallback = true; return; }
     const float ex = tc_exact_score(urow, p.I + (int64_t)id * p.D, p.D, ub, p.bi[id]);
     const uint64_t key = tc_key(ex, id);
 #pragma unroll
     for (int c = 0; c < TC_LANE_CAND; ++c)
       if (c == n_mine) ek[c] = key;
     ++n_mine;
+  };
+  if (in_regs) {
+#pragma unroll
+    for (int c = 0; c < TC_EPL; ++c)
+      if (lk[c]) rescore(ub_s[c], tc_key_id(lk[c]));
+  } else {
+    for (int e = lane; e < n_ent; e += 32) {
+      float s, lo; int id;
+      entry(e, s, lo, id);
+      rescore(s, id);
+    }
   }
   fallback = __any_sync(0xffffffffu, fallback);
   if (fallback) {
@@ -859,7 +981,8 @@ k_tc_finish(const TcFinish p) {
       for (int e = lane; e < p.n_slots * TC_BCAP; e += 32) {
         const int sl = e / TC_BCAP, n = e - sl * TC_BCAP;
         if (n >= p.bcnt[r * p.n_slots + sl]) continue;
-        const int id = p.band_i[(r * p.n_slots + sl) * TC_BCAP + n];
+        const int pos = p.band_i[(r * p.n_slots + sl) * TC_BCAP + n];
+        const int id = (int)(p.item_offset + (p.perm ? p.perm[pos] : pos));
         if (id == bid) continue;     // the target never precedes itself
         const float ex = tc_exact_score(urow, p.I + (int64_t)id * p.D, p.D, ub, p.bi[id]);
         more += (ex > bs || (ex == bs && id < bid)) ? 1 : 0;
@@ -927,7 +1050,7 @@ static int tc_list_len(int k) {
 struct TcLayout {
   int Kp, KB, KL, epi_warps, m_tiles, n_tiles, n_ctas, n_slots, fb_cap;
   int64_t m_pad, chunk, total_work;
-  size_t Bp, Ap, unorm, uabsb, margin, stats, best_s, best_id, cand_s, cand_i, cnt, bcnt, band_i,
+  size_t Bp, Ap, ua, ub2, item_b, tile_bmax, perm, sort_keys, sort_keys2, sort_vals, sort_temp, sort_temp_bytes, stats, best_s, best_id, cand_s, cand_i, cnt, bcnt, band_i,
       fb_list, fb_uid, status, fb_scores, fb_sig, total;
 };
 
@@ -959,9 +1082,20 @@ static TcLayout tc_layout(int64_t n_users, int64_t n_items, int D, int k, int te
   auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes, 1024); return at; };
   L.Bp = take((size_t)n_items * Kp_max * 2);
   L.Ap = take((size_t)L.m_pad * Kp_max * 2);
-  L.unorm = take(sizeof(float) * L.m_pad);
-  L.uabsb = take(sizeof(float) * L.m_pad);
-  L.margin = take(sizeof(float) * L.m_pad);
+  L.ua = take(sizeof(float) * L.m_pad);
+  L.ub2 = take(sizeof(float) * L.m_pad);
+  L.item_b = take(sizeof(float) * (size_t)n_items);
+  L.tile_bmax = take(sizeof(float) * (size_t)L.n_tiles);
+  // item order by norm (MRR form): permutation + radix-sort scratch
+  L.perm = take(sizeof(int32_t) * (size_t)n_items);
+  L.sort_keys = take(sizeof(uint32_t) * (size_t)n_items);
+  L.sort_keys2 = take(sizeof(uint32_t) * (size_t)n_items);
+  L.sort_vals = take(sizeof(int32_t) * (size_t)n_items);
+  L.sort_temp_bytes = 0;
+  cub::DeviceRadixSort::SortPairs((void*)nullptr, L.sort_temp_bytes, (const uint32_t*)nullptr,
+                                  (uint32_t*)nullptr, (const int32_t*)nullptr, (int32_t*)nullptr,
+                                  (int)n_items);
+  L.sort_temp = take(L.sort_temp_bytes);
   L.stats = take(sizeof(uint32_t) * 8);     // [0..1] of the items split with 1 term, [2..3] with 3, [4] which one Bp holds
   L.best_s = take(sizeof(float) * L.m_pad);
   L.best_id = take(sizeof(int32_t) * L.m_pad);
@@ -1010,29 +1144,45 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   char* base = (char*)a->workspace;
   __nv_bfloat16* Bp = (__nv_bfloat16*)(base + L.Bp);
   __nv_bfloat16* Ap = (__nv_bfloat16*)(base + L.Ap);
-  float* unorm = (float*)(base + L.unorm);
-  float* uabsb = (float*)(base + L.uabsb);
-  float* margin = (float*)(base + L.margin);
+  float* ua = (float*)(base + L.ua);
+  float* ub2 = (float*)(base + L.ub2);
+  float* item_b = (float*)(base + L.item_b);
+  float* tile_bmax = (float*)(base + L.tile_bmax);
   uint32_t* stats = (uint32_t*)(base + L.stats);
   float* best_s = (float*)(base + L.best_s);
   int32_t* best_id = (int32_t*)(base + L.best_id);
   int32_t* status = (int32_t*)(base + L.status);
   const int grid = num_sms() * 8;
+  const float c = terms == 1 ? kTcC1 : kTcC3;
+  int32_t* perm = (int32_t*)(base + L.perm);
+  const bool sorted = mrr;   // (a caller that reuses the item side keeps asking for the same outputs)
 
-  // the item side of the workspace (split copy + largest norm) is reused across calls on request
+  // the item side of the workspace (split copy, per-item and per-tile bounds, largest |bias|) is
+  // reused across calls on request
   const bool reuse = a->reuse_item_prep != 0;
   if (!reuse) {
     CMF_CUDA(cudaMemsetAsync(stats, 0, sizeof(uint32_t) * 8, s));
-    k_tc_split<<<grid, 256, 0, s>>>(a->I, a->bi, nullptr, a->item_offset, a->num_items_shard,
-                                    a->num_items_shard, a->D, L.Kp, 0, terms, Bp, nullptr, nullptr,
-                                    stats);
+    if (sorted) {
+      // MRR form: the split copy holds the item rows in order of their norm, so that the largest
+      // margin of a tile (all the epilogue knows about a column) is close to every column's own
+      uint32_t* k1 = (uint32_t*)(base + L.sort_keys);
+      uint32_t* k2 = (uint32_t*)(base + L.sort_keys2);
+      int32_t* v1 = (int32_t*)(base + L.sort_vals);
+      k_tc_norm_keys<<<grid, 256, 0, s>>>(a->I, a->item_offset, a->num_items_shard, a->D, k1, v1);
+      CMF_LAUNCH_CHECK();
+      size_t temp = L.sort_temp_bytes;
+      CMF_CUDA(cub::DeviceRadixSort::SortPairs(base + L.sort_temp, temp, k1, k2, v1, perm,
+                                               (int)a->num_items_shard, 0, 32, s));
+    }
+    k_tc_split<<<grid, 256, 0, s>>>(a->I, a->bi, sorted ? perm : nullptr, a->item_offset,
+                                    a->num_items_shard, a->num_items_shard, a->D, L.Kp, 0, terms,
+                                    c, Bp, item_b, nullptr, stats);
+    CMF_LAUNCH_CHECK();
+    k_tc_tile_max<<<(unsigned)L.n_tiles, TC_BN, 0, s>>>(item_b, a->num_items_shard, tile_bmax);
     CMF_LAUNCH_CHECK();
   }
   k_tc_split<<<grid, 256, 0, s>>>(a->U, a->bu, a->user_ids, 0, a->n_users_tile, L.m_pad, a->D,
-                                  L.Kp, 1, terms, Ap, unorm, uabsb, nullptr);
-  CMF_LAUNCH_CHECK();
-  k_tc_margin<<<(unsigned)((L.m_pad + 255) / 256), 256, 0, s>>>(
-      unorm, uabsb, stats, terms == 1 ? kTcC1 : kTcC3, L.m_pad, margin);
+                                  L.Kp, 1, terms, c, Ap, ua, ub2, stats);
   CMF_LAUNCH_CHECK();
   if (mrr) {
     if (a->ext_best_id) {
@@ -1066,7 +1216,7 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   p.m_tiles = L.m_tiles; p.n_slots = L.n_slots; p.chunk = L.chunk; p.total_work = L.total_work;
   p.want_mrr = mrr ? 1 : 0;
   p.n_items = a->num_items_shard; p.item_offset = a->item_offset; p.debug = g_tc_debug;
-  p.best_s = best_s; p.best_id = best_id; p.margin = margin;
+  p.best_s = best_s; p.best_id = best_id; p.ua = ua; p.ub2 = ub2; p.tile_bmax = tile_bmax;
   p.dbg = (unsigned long long*)(status + 4);     // (status[4..7]; cleared with it)
   p.cand_s = (float*)(base + L.cand_s); p.cand_i = (int32_t*)(base + L.cand_i);
   p.cnt = (int32_t*)(base + L.cnt); p.bcnt = (int32_t*)(base + L.bcnt);
@@ -1084,11 +1234,17 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   // list length: the smallest instantiation that leaves a margin above k
 #define CMF_TC_LAUNCH(KL, EW)                                                                    \
   do {                                                                                           \
-    CMF_CUDA(cudaFuncSetAttribute(k_tc_gemm_topk<KL, EW>,                                        \
+    CMF_CUDA(cudaFuncSetAttribute(k_tc_gemm_topk<KL, EW, false>,                                 \
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));      \
-    k_tc_gemm_topk<KL, EW><<<(unsigned)L.n_ctas, 128 + 32 * EW, smem, s>>>(tmA, tmB, p);         \
+    k_tc_gemm_topk<KL, EW, false><<<(unsigned)L.n_ctas, 128 + 32 * EW, smem, s>>>(tmA, tmB, p);  \
   } while (0)
-  if (L.KL == 8 && L.epi_warps == 16) CMF_TC_LAUNCH(8, 16);
+  if (g_tc_debug != 0) {   // experiments: one instantiation carries the switches and counters
+    CMF_REQUIRE(L.KL == 16 && L.epi_warps == 8,
+                "cmf_set_tuning(3, ...): the debug kernel exists for list length 16, 8 epilogue warps");
+    CMF_CUDA(cudaFuncSetAttribute(k_tc_gemm_topk<16, 8, true>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_tc_gemm_topk<16, 8, true><<<(unsigned)L.n_ctas, 128 + 32 * 8, smem, s>>>(tmA, tmB, p);
+  } else if (L.KL == 8 && L.epi_warps == 16) CMF_TC_LAUNCH(8, 16);
   else if (L.KL == 8) CMF_TC_LAUNCH(8, 8);
   else if (L.KL == 12) CMF_TC_LAUNCH(12, 8);
   else if (L.KL == 16 && L.epi_warps == 16) CMF_TC_LAUNCH(16, 16);
@@ -1100,7 +1256,8 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   TcFinish f{};
   f.cand_s = p.cand_s; f.cand_i = p.cand_i; f.cnt = p.cnt; f.bcnt = p.bcnt; f.band_i = p.band_i;
   f.n_slots = L.n_slots; f.KL = L.KL; f.k = a->k; f.D = a->D; f.want_mrr = mrr ? 1 : 0;
-  f.n_users = a->n_users_tile; f.margin = margin;
+  f.n_users = a->n_users_tile; f.ua = ua; f.ub2 = ub2; f.item_b = item_b;
+  f.item_offset = a->item_offset; f.perm = sorted ? perm : nullptr;
   f.U = a->U; f.I = a->I; f.bu = a->bu; f.bi = a->bi; f.user_ids = a->user_ids;
   f.tgt_indptr = a->tgt_indptr; f.tgt_items = a->tgt_items;
   f.best_s = best_s; f.best_id = best_id;

@@ -222,8 +222,7 @@ k_item_exchange_update(const PeersDev P, float* __restrict__ M, float* __restric
       p.load(P.I[P.rank] + row * D, D, l);
       if (rule_has_m(o.rule)) m.load(M + lr * D, D, l); else m.zero();
       if (rule_has_v(o.rule)) v.load(Vv + lr * D, D, l); else v.zero();
-#pragma unroll
-      for (int i = 0; i < R * V; ++i) apply_rule(o, p.f[i], m.f[i], v.f[i], g.f[i]);
+      apply_rule_n<R * V>(o, p.f, m.f, v.f, g.f);
       if (rule_has_m(o.rule)) m.store(M + lr * D, D, l);
       if (rule_has_v(o.rule)) v.store(Vv + lr * D, D, l);
       if (MC) {

@@ -60,39 +60,76 @@ inline int validate_opt(const cmf_opt_t& o, const char* which, const float* m, c
 
 // sqrt / division of the update term with the SFU approximations (<= 2 ulp each): the term is
 // multiplied by lr before it touches the parameter, so the parameter moves by < 1e-9 relative.
-__device__ __forceinline__ float fast_sqrt(float x) { return x > 0.f ? x * rsqrtf(x) : 0.f; }
+// The bare MUFU forms (no denormal rescaling around them): arguments are second moments or sums
+// of squares; below 1e-30 their root (< 1e-15) vanishes next to eps and is taken as zero, and the
+// divisors are >= eps. For normal arguments these are the bits rsqrtf / __fdividef return.
+__device__ __forceinline__ float rsqrt_ftz(float x) {
+  float y;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_ftz(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float fast_sqrt(float x) { return x > 1e-30f ? x * rsqrt_ftz(x) : 0.f; }
+__device__ __forceinline__ float fast_div(float a, float b) { return a * rcp_ftz(b); }
 
-// One parameter element. m/v are the rule's state (Adagrad keeps its sum in m).
-__device__ __forceinline__ void apply_rule(const OptDev& o, float& p, float& m, float& v, float g) {
+// N parameter elements. m/v are the rule's state (Adagrad keeps its sum in m). The rule is chosen
+// ONCE per call, outside the element loop (per element, the four-way branch and the library
+// forms of rsqrt / division made the optimizer arithmetic 70 % of k_bwd_update's instructions).
+template <int N>
+__device__ __forceinline__ void apply_rule_n(const OptDev& o, float* p, float* m, float* v,
+                                             const float* g_in) {
   switch (o.rule) {
     case CMF_OPT_SPARSE_ADAM: {  // torch/optim/sparse_adam.py (functional sparse_adam)
-      const float mn = m + (g - m) * o.omb1;
-      const float vn = v + (g * g - v) * o.omb2;
-      m = mn;
-      v = vn;
-      p = p - o.step_size * __fdividef(mn, fast_sqrt(vn) + o.eps);
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        const float g = g_in[i];
+        const float mn = m[i] + (g - m[i]) * o.omb1;
+        const float vn = v[i] + (g * g - v[i]) * o.omb2;
+        m[i] = mn;
+        v[i] = vn;
+        p[i] = p[i] - o.step_size * fast_div(mn, fast_sqrt(vn) + o.eps);
+      }
       break;
     }
     case CMF_OPT_ADAM: {  // torch/optim/adam.py _single_tensor_adam
-      if (o.wd != 0.f) g = g + o.wd * p;
-      m = m + o.omb1 * (g - m);
-      v = v * o.b2 + (o.omb2 * g) * g;
-      const float denom = __fdividef(fast_sqrt(v), o.bc2_sqrt) + o.eps;
-      p = p - o.step_size * __fdividef(m, denom);
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        float g = g_in[i];
+        if (o.wd != 0.f) g = g + o.wd * p[i];
+        m[i] = m[i] + o.omb1 * (g - m[i]);
+        v[i] = v[i] * o.b2 + (o.omb2 * g) * g;
+        const float denom = fast_div(fast_sqrt(v[i]), o.bc2_sqrt) + o.eps;
+        p[i] = p[i] - o.step_size * fast_div(m[i], denom);
+      }
       break;
     }
     case CMF_OPT_ADAGRAD: {  // torch/optim/adagrad.py _single_tensor_adagrad
-      if (o.wd != 0.f) g = g + o.wd * p;
-      m = m + g * g;
-      p = p - o.lr * __fdividef(g, fast_sqrt(m) + o.eps);
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        float g = g_in[i];
+        if (o.wd != 0.f) g = g + o.wd * p[i];
+        m[i] = m[i] + g * g;
+        p[i] = p[i] - o.lr * fast_div(g, fast_sqrt(m[i]) + o.eps);
+      }
       break;
     }
     default: {  // SGD
-      if (o.wd != 0.f) g = g + o.wd * p;
-      p = p - o.lr * g;
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        float g = g_in[i];
+        if (o.wd != 0.f) g = g + o.wd * p[i];
+        p[i] = p[i] - o.lr * g;
+      }
       break;
     }
   }
+}
+__device__ __forceinline__ void apply_rule(const OptDev& o, float& p, float& m, float& v, float g) {
+  apply_rule_n<1>(o, &p, &m, &v, &g);
 }
 
 __device__ __forceinline__ bool rule_has_m(int rule) { return rule != CMF_OPT_SGD; }
@@ -108,8 +145,7 @@ __device__ __forceinline__ void update_row(const OptDev& o, float* __restrict__ 
   p.load(P + row * D, D, l);
   if (rule_has_m(o.rule)) m.load(M + row * D, D, l); else m.zero();
   if (rule_has_v(o.rule)) v.load(Vv + row * D, D, l); else v.zero();
-#pragma unroll
-  for (int i = 0; i < R * V; ++i) apply_rule(o, p.f[i], m.f[i], v.f[i], g.f[i]);
+  apply_rule_n<R * V>(o, p.f, m.f, v.f, g.f);
   p.store(P + row * D, D, l);
   if (rule_has_m(o.rule)) m.store(M + row * D, D, l);
   if (rule_has_v(o.rule)) v.store(Vv + row * D, D, l);
@@ -172,6 +208,7 @@ struct StepDev {
   uint32_t drop_thr;
   float drop_scale;
   uint32_t drop_key_hi;   // optimizer step: a batch that is repeated draws fresh masks
+  int red_in_fwd;         // the forward kernel sends the item-row gradient contributions itself
 };
 
 // The dropout mask of one row of one scored pair: interaction at dataset position gidx, slot 0 =

@@ -31,6 +31,7 @@ extern int g_tc_terms;
 extern int g_tc_list_len;
 extern int g_tc_epi_warps;
 extern int g_pdl;
+extern int g_red_in_fwd;
 
 struct WsLayout {
   // persistent (zero between steps; the kernels restore the invariant)
@@ -414,8 +415,7 @@ struct RowJob {
         z.zero();
         z.store(q.G[t] + off, q.D, l);
       }
-#pragma unroll
-      for (int i = 0; i < R * V; ++i) apply_rule(q.emb, p.f[i], m.f[i], v.f[i], g.f[i]);
+      apply_rule_n<R * V>(q.emb, p.f, m.f, v.f, g.f);
       p.store(q.P[t] + off, q.D, l);
       if (rule_has_m(q.emb.rule)) m.store(q.M[t] + off, q.D, l);
       if (rule_has_v(q.emb.rule)) v.store(q.Vv[t] + off, q.D, l);
@@ -575,6 +575,11 @@ extern "C" int cmf_set_tuning(int32_t key, int32_t value) {
                 "cmf_set_tuning: list length %d", value);
     const int prev = g_tc_list_len;
     g_tc_list_len = value;
+    return prev;
+  }
+  if (key == 8) {
+    const int prev = g_red_in_fwd;
+    g_red_in_fwd = value ? 1 : 0;
     return prev;
   }
   if (key == 7) {
@@ -809,6 +814,7 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
 
   if (split) {
     // e0 -> e1: k_fwd_loss;  e1 -> e2: what is left of the sort;  e2 -> e3: k_bwd_update
+    p.red_in_fwd = (g_red_in_fwd && p.train && a->D / 4 <= 32) ? 1 : 0;
     int rc = launch_fwd_loss_v3(p, side != nullptr, s);
     if (rc != CMF_OK) return rc;
     if (g_prof_on) CMF_CUDA(cudaEventRecord(prof.e[1], s));

@@ -570,6 +570,30 @@ k_fwd_loss_g8(const StepDev p, const int NP) {
           p.sel_arr[b] = sel_id;
         }
       }
+      if (p.red_in_fwd && g != 0.f) {
+        // item side of the backward pass, here, where the user row is in registers anyway:
+        // d loss / d item row = +-g * user row (products rounded before they are added, as in
+        // k_bwd_update), sent with vector RED; the backward kernel keeps the user side
+        const int tgt = implicit ? sel_id : pos;
+        float* gp = p.GI + (int64_t)pos * D + l * 4;
+        float* gs = p.GI + (int64_t)tgt * D + l * 4;
+#pragma unroll
+        for (int k = 0; k < KQ; ++k) {
+          if (FULL || k * 8 + l < D4) {
+            float tt[4] = {__fmul_rn(g, ur[k].x), __fmul_rn(g, ur[k].y), __fmul_rn(g, ur[k].z),
+                           __fmul_rn(g, ur[k].w)};
+            red_vec<4>(gp + k * 32, tt);
+            if (implicit) {
+              tt[0] = -tt[0]; tt[1] = -tt[1]; tt[2] = -tt[2]; tt[3] = -tt[3];
+              red_vec<4>(gs + k * 32, tt);
+            }
+          }
+        }
+        if (l == 0) {
+          atomicAdd(p.gbi + pos, g);
+          if (implicit) atomicAdd(p.gbi + sel_id, -g);
+        }
+      }
     }
     __syncwarp();   // the id table is rewritten by the next chunk
   }
@@ -652,10 +676,7 @@ k_bwd_update(const StepDev p) {
         for (int r = 0; r < R; ++r) {
           const int i = r * 32 + lane;
           if (FULL || i < D4) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-              apply_rule(p.emb, pr.f[r * 4 + k], m_pre.f[r * 4 + k], v_pre.f[r * 4 + k],
-                         gu.f[r * 4 + k]);
+            apply_rule_n<4>(p.emb, pr.f + r * 4, m_pre.f + r * 4, v_pre.f + r * 4, gu.f + r * 4);
             st_vec<4>(p.U + off + i * 4, pr.f + r * 4);
             if (emb_m) st_vec<4>(p.U_m + off + i * 4, m_pre.f + r * 4);
             if (emb_v) st_vec<4>(p.U_v + off + i * 4, v_pre.f + r * 4);
@@ -733,27 +754,27 @@ k_bwd_update(const StepDev p) {
             f[3] = __fadd_rn(f[3], __fmul_rn(g, xp[r].w));
             float tt[4] = {__fmul_rn(g, pu[0]), __fmul_rn(g, pu[1]), __fmul_rn(g, pu[2]),
                            __fmul_rn(g, pu[3])};
-            red_vec<4>(gi_pos + r * 128, tt);
+            if (!p.red_in_fwd) red_vec<4>(gi_pos + r * 128, tt);
             if (implicit) {
               f[0] = __fadd_rn(f[0], __fmul_rn(-g, xs[r].x));
               f[1] = __fadd_rn(f[1], __fmul_rn(-g, xs[r].y));
               f[2] = __fadd_rn(f[2], __fmul_rn(-g, xs[r].z));
               f[3] = __fadd_rn(f[3], __fmul_rn(-g, xs[r].w));
               tt[0] = -tt[0]; tt[1] = -tt[1]; tt[2] = -tt[2]; tt[3] = -tt[3];
-              red_vec<4>(gi_sel + r * 128, tt);
+              if (!p.red_in_fwd) red_vec<4>(gi_sel + r * 128, tt);
             }
           }
         }
         if (implicit) {
           gbu_acc += g;
           gbu_acc += -g;
-          if (lane == 0) {
+          if (lane == 0 && !p.red_in_fwd) {
             atomicAdd(p.gbi + pos, g);
             atomicAdd(p.gbi + sel_id, -g);
           }
         } else {
           gbu_acc += g;
-          if (lane == 0) atomicAdd(p.gbi + pos, g);
+          if (lane == 0 && !p.red_in_fwd) atomicAdd(p.gbi + pos, g);
         }
       }
     }
@@ -835,6 +856,12 @@ static int pdl_default() {
 // moment the previous grid drains, so kernels of OTHER streams (a host-fed pipeline's batch sort on
 // its copy stream) find no way in until the step ends: end-to-end throughput fell by 12 %.
 int g_pdl = pdl_default();
+// cmf_set_tuning key 8 (or CMF_RED_IN_FWD=1): item-row gradient REDs issued by k_fwd_loss_g8
+static int red_in_fwd_default() {
+  const char* e = getenv("CMF_RED_IN_FWD");
+  return e ? atoi(e) : 0;
+}
+int g_red_in_fwd = red_in_fwd_default();
 
 int launch_bwd_update_v3(const StepDev& p_in, int max_chunk_len, cudaStream_t s) {
   StepDev p = p_in;

@@ -466,7 +466,7 @@ CMF_API int cmf_gather_probe(const void *table, const int32_t *idx, int64_t n_id
  * automatic: 1 without the MRR counter, 3 with it; 1 or 3 = forced, results stay exact); key 5: candidate-list length of the tensor-core
  * evaluation (0 = automatic, 8 / 16 / 24; must exceed k); key 7: its epilogue warps (0 = automatic, 8 or 16); key 6: programmatic dependent launch of k_bwd_update and
  * k_update_rows (0 = plain stream order, the default; 1 = on: 1 % faster steps when nothing else
- * shares the GPU, slower pipelines when other streams need SMs between the step's kernels). Results do not depend on keys 0-2 and 6 beyond fp32 summation
+ * shares the GPU, slower pipelines when other streams need SMs between the step's kernels). key 8: the item-row gradient contributions are sent by k_fwd_loss_g8 (which holds the user row) instead of k_bwd_update (0 / 1; also CMF_RED_IN_FWD). Results do not depend on keys 0-2, 6 and 8 beyond fp32 summation
  * order; tests use them to cross-check the in-place and the accumulate paths. Returns the previous
  * value, or a negative cmf_status for an unknown key. */
 CMF_API int cmf_set_tuning(int32_t key, int32_t value);

@@ -593,6 +593,46 @@ def test_tensor_core_eval_matches_exact_path(shape):
     np.testing.assert_allclose(got, exp, rtol=1e-12)
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize('shape', [(1024, 26744, 128), (300, 3000, 64)])
+def test_tensor_core_eval_with_uneven_item_norms(shape):
+    """Item rows whose norms spread over two orders of magnitude (what a trained model has:
+    popular items grow), biases of mixed size: the error bound of a pair follows THAT pair's
+    norms, so the tensor-core route still settles (nearly) every user itself, and what it returns
+    is the exact path's result bit for bit."""
+    from collie_b200 import metrics as M
+    n_users, n_items, dim = shape
+    rng = np.random.default_rng(7 * n_items)
+    iscale = np.exp(rng.normal(0.0, 1.0, (n_items, 1))).astype(np.float32)     # lognormal norms
+    uscale = np.exp(rng.normal(0.0, 0.5, (n_users, 1))).astype(np.float32)
+    tabs = (rng.normal(0, 0.3 / np.sqrt(dim), (n_users, dim)).astype(np.float32) * uscale,
+            rng.normal(0, 0.3 / np.sqrt(dim), (n_items, dim)).astype(np.float32) * iscale,
+            rng.normal(0, 0.05, (n_users, 1)).astype(np.float32),
+            (rng.normal(0, 0.05, (n_items, 1)) * iscale).astype(np.float32))
+    tabs = tuple(torch.from_numpy(np.ascontiguousarray(t)).cuda() for t in tabs)
+    tu = rng.integers(0, n_users, 6 * n_users)
+    ti = rng.integers(0, n_items, 6 * n_users)
+    coo = sp.coo_matrix((np.ones(len(tu)), (tu, ti)), shape=(n_users, n_items))
+    coo.sum_duplicates()
+    tile = np.arange(n_users)
+    indptr, items, nnz = M._targets_device(coo.tocsr(), tile, 'cuda')
+    users = torch.from_numpy(tile.astype(np.int32)).cuda()
+    k = 10
+    ex = M._eval_tile('cuda', n_users, n_items, k, indptr, items, {'topk', 'mapk', 'mrr'},
+                      tables=tabs, user_ids=users, precision=0)
+    for want in ({'topk', 'mapk', 'mrr'}, {'topk', 'mapk'}):
+        status = torch.zeros(2, dtype=torch.int32, device='cuda')
+        tc = M._eval_tile('cuda', n_users, n_items, k, indptr, items, want, tables=tabs,
+                          user_ids=users, precision=1, tc_status=status)
+        assert int(status[1]) == 0, status.tolist()
+        assert int(status[0]) <= n_users // 20, status.tolist()
+        assert torch.equal(tc['topk_ids'], ex['topk_ids'])
+        assert torch.equal(tc['topk_scores'], ex['topk_scores'])
+        assert torch.equal(tc['ap'], ex['ap'])
+        if 'mrr' in want:
+            assert torch.equal(tc['n_before_best'], ex['n_before_best'])
+
+
 # ------------------------------------------------------------------------------------ epoch plan
 @pytest.mark.gpu
 @pytest.mark.parametrize('n,batch,n_users,with_gpos', [(10_000, 256, 300, False),
