@@ -769,13 +769,37 @@ __device__ __forceinline__ float tc_key_score(uint64_t key) {
   return __uint_as_float(u);
 }
 __device__ __forceinline__ int tc_key_id(uint64_t key) { return 0x7fffffff - (int)(uint32_t)key; }
+// warp-wide maximum of 64-bit keys: two REDUX instructions (the high words, then the low words of
+// the lanes that hold that high word) instead of five shuffle levels of 64-bit compares
 __device__ __forceinline__ uint64_t warp_max_u64(uint64_t v) {
+  const uint32_t hi = (uint32_t)(v >> 32);
+  const uint32_t mh = __reduce_max_sync(0xffffffffu, hi);
+  const uint32_t ml = __reduce_max_sync(0xffffffffu, hi == mh ? (uint32_t)v : 0u);
+  return ((uint64_t)mh << 32) | ml;
+}
+// six keys in descending order (12 compare-exchanges, the optimal network for six inputs)
+__device__ __forceinline__ void sort6_desc(uint64_t (&a)[6]) {
+#define CMF_CE(i, j)                                   \
+  do {                                                 \
+    const uint64_t x = a[i], y = a[j];                 \
+    const bool sw = x < y;                             \
+    a[i] = sw ? y : x;                                 \
+    a[j] = sw ? x : y;                                 \
+  } while (0)
+  CMF_CE(0, 5); CMF_CE(1, 3); CMF_CE(2, 4);
+  CMF_CE(1, 2); CMF_CE(3, 4);
+  CMF_CE(0, 3); CMF_CE(2, 5);
+  CMF_CE(0, 1); CMF_CE(2, 3); CMF_CE(4, 5);
+  CMF_CE(1, 2); CMF_CE(3, 4);
+#undef CMF_CE
+}
+// the lane whose head is `best` drops it (distinct keys: item ids differ)
+__device__ __forceinline__ void pop6_if(uint64_t (&a)[6], uint64_t best) {
+  if (a[0] == best) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    const uint64_t w = __shfl_xor_sync(0xffffffffu, v, o);
-    v = w > v ? w : v;
+    for (int c = 0; c < 5; ++c) a[c] = a[c + 1];
+    a[5] = 0;
   }
-  return v;
 }
 
 struct TcFinish {
@@ -811,6 +835,7 @@ struct TcFinish {
 };
 
 constexpr int TC_LANE_CAND = 6;   // exact re-scorings one lane can hold; more -> the exact path
+static_assert(TC_LANE_CAND == 6, "sort6_desc");
 constexpr int TC_EPL = 6;         // list entries per lane kept in registers (192 per user)
 
 // One warp per user. (1) A_k = the k-th best key of the union of the slots' lists; T = the best
@@ -858,12 +883,14 @@ k_tc_finish(const TcFinish p) {
   // ---- (1) the k-th largest lower bound: at least k items have an exact score >= it
   uint64_t prev = ~0ull;
   int found = 0;
+  uint64_t sk[TC_EPL];    // this lane's keys in descending order; the head is its candidate
+#pragma unroll
+  for (int c = 0; c < TC_EPL; ++c) sk[c] = lk[c];
+  if (in_regs) sort6_desc(sk);
   for (int round = 0; round < p.k; ++round) {
     uint64_t best = 0;
     if (in_regs) {
-#pragma unroll
-      for (int c = 0; c < TC_EPL; ++c)
-        if (lk[c] < prev && lk[c] > best) best = lk[c];
+      best = sk[0];
     } else {
       for (int e = lane; e < n_ent; e += 32) {
         float s, lo; int id;
@@ -874,6 +901,7 @@ k_tc_finish(const TcFinish p) {
     }
     best = warp_max_u64(best);
     if (best == 0) break;
+    if (in_regs) pop6_if(sk, best);
     prev = best;
     ++found;
   }
@@ -948,16 +976,12 @@ k_tc_finish(const TcFinish p) {
   const int64_t t0 = p.tgt_indptr[r];
   const int n_tgt = (int)(p.tgt_indptr[r + 1] - t0);
   uint64_t my_pick = 0;
-  prev = ~0ull;
+  sort6_desc(ek);
   for (int round = 0; round < p.k; ++round) {
-    uint64_t best = 0;
-#pragma unroll
-    for (int c = 0; c < TC_LANE_CAND; ++c)
-      if (ek[c] < prev && ek[c] > best) best = ek[c];
-    best = warp_max_u64(best);
+    const uint64_t best = warp_max_u64(ek[0]);
     if (round == lane) my_pick = best;
     if (best == 0) break;
-    prev = best;
+    pop6_if(ek, best);
   }
   bool hit = false;
   if (lane < p.k) {

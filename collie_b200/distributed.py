@@ -590,7 +590,6 @@ def _item_sharded_tiles(M, names, k, group, world, precision, tile_users, tables
     want = {'topk'} | ({'mrr'} if 'mrr' in names else set())
     sums = {n_: torch.zeros((), dtype=torch.float64, device=dev) for n_ in names}
     status = torch.zeros(2, dtype=torch.int32, device=dev) if precision == 1 else None
-    tgt_keys = row_of.long() * n_items + tgt_items.long()      # sorted: CSR order
     ws = None
     for s0 in range(0, n_test, tile_users):
         e0 = min(s0 + tile_users, n_test)
@@ -610,13 +609,18 @@ def _item_sharded_tiles(M, names, k, group, world, precision, tile_users, tables
             if 'mrr' in names:
                 before = res['n_before_best'].clamp(min=0).long()
         if 'mapk' in names:
-            all_ids = [torch.empty_like(loc_ids) for _ in range(world)]
-            all_s = [torch.empty_like(loc_s) for _ in range(world)]
-            dist.all_gather(all_ids, loc_ids, group=group)
-            dist.all_gather(all_s, loc_s, group=group)
-            _, top = merge_topk(torch.cat(all_s, dim=1), torch.cat(all_ids, dim=1), k)
-            ap = ap_from_topk_ids(top, torch.arange(s0, e0, device=dev), tgt_keys, counts[s0:e0],
-                                  n_items)
+            # [shard][user][k] lists of all ranks, merged and scored by one kernel
+            all_ids = torch.empty((world, nt, k), dtype=torch.int32, device=dev)
+            all_s = torch.empty((world, nt, k), dtype=torch.float32, device=dev)
+            dist.all_gather_into_tensor(all_ids, loc_ids, group=group)
+            dist.all_gather_into_tensor(all_s, loc_s, group=group)
+            ap = torch.empty(nt, dtype=torch.float64, device=dev)
+            tile_indptr = indptr[s0:e0 + 1]
+            with _abi.on_device(dev):
+                _abi.check(_abi.lib().cmf_merge_topk(
+                    all_ids.data_ptr(), all_s.data_ptr(), world, nt, k, tile_indptr.data_ptr(),
+                    tgt_items.data_ptr(), None, None, ap.data_ptr(),
+                    torch.cuda.current_stream(dev).cuda_stream))
             sums['mapk'] += ap.sum()
         if 'mrr' in names:
             dist.all_reduce(before, group=group)
@@ -634,7 +638,8 @@ def _item_sharded_tiles(M, names, k, group, world, precision, tile_users, tables
 
 
 def ap_from_topk_ids(top_ids, rows, tgt_keys, n_targets, n_items):
-    """AP@k per user from ranked ids ``[n, k]`` (-1 = padding): ``tgt_keys`` = sorted
+    """(torch statement of what ``cmf_merge_topk`` computes; the tests check the kernel against it)
+    AP@k per user from ranked ids ``[n, k]`` (-1 = padding): ``tgt_keys`` = sorted
     ``row * n_items + item`` of every (user row, target) pair, ``rows`` = the user row of each line
     of ``top_ids``, ``n_targets`` = targets per user. Same formula as ``mapk``
     (collie/metrics.py:176-196): sum_j hit_j * precision@j / min(k, n_targets); 0 without targets."""
@@ -654,7 +659,8 @@ def ap_from_topk_ids(top_ids, rows, tgt_keys, n_targets, n_items):
 
 
 def merge_topk(scores, ids, k):
-    """Merge per-shard top-k candidates ``[n, shards * k]`` into the global top-k in canonical order
+    """(torch statement of what ``cmf_merge_topk`` computes; the tests check the kernel against it)
+    Merge per-shard top-k candidates ``[n, shards * k]`` into the global top-k in canonical order
     (score descending, item id ascending); ids < 0 are padding. Returns ``(scores, ids)``."""
     key = ids.long() + (ids < 0).long() * (1 << 40)          # padding last
     by_id = torch.argsort(key, dim=1, stable=True)

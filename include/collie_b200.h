@@ -424,6 +424,19 @@ CMF_API int cmf_eval_tc_info(int32_t D, double *out);
 CMF_API int cmf_eval_tile_noalloc(const cmf_eval_t *args, void *stream);
 
 /*
+ * Item-sharded evaluation, merge step (distributed.py evaluate_item_sharded): ids / scores are the
+ * all-gathered per-shard top-k lists [n_shards][n_users][k] (ids < 0 = padding; the shards score
+ * disjoint item blocks), merged per user into the global top-k in the canonical order (score
+ * descending, item id ascending); AP@k (collie/metrics.py:176-196) against the users' sorted
+ * target ids (tgt_indptr [n_users + 1] absolute offsets into tgt_items). Outputs may be NULL.
+ * The reference scores the whole row on one device (metrics.py:144-198); the merge has no
+ * counterpart there. k <= 32.
+ */
+CMF_API int cmf_merge_topk(const int32_t *ids, const float *scores, int32_t n_shards, int64_t n_users,
+                   int32_t k, const int64_t *tgt_indptr, const int32_t *tgt_items,
+                   int32_t *out_ids, float *out_scores, double *ap, void *stream);
+
+/*
  * Row gather into a column block of a wider matrix, and its transpose (vector RED): the input of
  * the first dense layer of HybridPretrainedModel, X[r] = [user_meta[u] | U[u] | I[i] | item_meta[i]],
  * is written by one call per source table (out + col0 with row pitch ld floats), instead of the

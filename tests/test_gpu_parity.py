@@ -633,6 +633,51 @@ def test_tensor_core_eval_with_uneven_item_norms(shape):
             assert torch.equal(tc['n_before_best'], ex['n_before_best'])
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize('n_shards,n_users,k', [(2, 300, 10), (8, 1000, 10), (5, 77, 1), (8, 64, 16),
+                                                (12, 50, 12)])
+def test_merge_of_sharded_topk_lists(n_shards, n_users, k):
+    """cmf_merge_topk (item-sharded evaluation): global top-k in canonical order and AP@k from the
+    shards' lists, against the torch statement of the same merge; scores drawn from a few values
+    so that ties across shards decide by item id, short lists padded with -1."""
+    from collie_b200 import _abi
+    from collie_b200.distributed import ap_from_topk_ids, merge_topk
+    rng = np.random.default_rng(n_shards * 1000 + k)
+    block = 40
+    n_items = n_shards * block
+    ids = np.full((n_shards, n_users, k), -1, dtype=np.int32)
+    sc = np.full((n_shards, n_users, k), -np.inf, dtype=np.float32)
+    for s_ in range(n_shards):
+        for u in range(n_users):
+            m = int(rng.integers(0, k + 1)) if u % 7 == 0 else k
+            pick = rng.choice(block, size=m, replace=False) + s_ * block
+            val = rng.integers(-3, 4, size=m).astype(np.float32) * 0.5
+            order = np.lexsort((pick, -val))
+            ids[s_, u, :m], sc[s_, u, :m] = pick[order], val[order]
+    counts = rng.integers(0, 6, n_users)
+    tgt = [np.sort(rng.choice(n_items, size=c, replace=False)).astype(np.int32) for c in counts]
+    indptr = torch.from_numpy(np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)).cuda()
+    tgt_items = torch.from_numpy(np.concatenate(tgt + [np.zeros(0, np.int32)])).cuda()
+    d_ids, d_sc = torch.from_numpy(ids).cuda(), torch.from_numpy(sc).cuda()
+    out_ids = torch.empty((n_users, k), dtype=torch.int32, device='cuda')
+    out_sc = torch.empty((n_users, k), dtype=torch.float32, device='cuda')
+    ap = torch.empty(n_users, dtype=torch.float64, device='cuda')
+    _abi.check(_abi.lib().cmf_merge_topk(d_ids.data_ptr(), d_sc.data_ptr(), n_shards, n_users, k,
+                                         indptr.data_ptr(), tgt_items.data_ptr(),
+                                         out_ids.data_ptr(), out_sc.data_ptr(), ap.data_ptr(),
+                                         torch.cuda.current_stream().cuda_stream))
+    exp_s, exp_i = merge_topk(d_sc.permute(1, 0, 2).reshape(n_users, -1),
+                              d_ids.permute(1, 0, 2).reshape(n_users, -1), k)
+    assert torch.equal(out_ids, exp_i)
+    assert torch.equal(out_sc, torch.where(exp_i < 0, torch.full_like(exp_s, -float('inf')), exp_s))
+    row_of = torch.repeat_interleave(torch.arange(n_users, device='cuda'),
+                                     torch.from_numpy(counts).cuda())
+    keys = row_of.long() * n_items + tgt_items.long()
+    exp_ap = ap_from_topk_ids(exp_i, torch.arange(n_users, device='cuda'), keys,
+                              torch.from_numpy(counts).cuda(), n_items)
+    np.testing.assert_allclose(ap.cpu().numpy(), exp_ap.cpu().numpy(), rtol=1e-12, atol=0)
+
+
 # ------------------------------------------------------------------------------------ epoch plan
 @pytest.mark.gpu
 @pytest.mark.parametrize('n,batch,n_users,with_gpos', [(10_000, 256, 300, False),
