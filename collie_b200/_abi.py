@@ -79,7 +79,7 @@ class cmf_eval_t(C.Structure):
         ('topk_ids', C.c_void_p), ('topk_scores', C.c_void_p), ('ap', C.c_void_p),
         ('n_before_best', C.c_void_p), ('best_score', C.c_void_p), ('best_id', C.c_void_p),
         ('auc_pairs', C.c_void_p), ('workspace', C.c_void_p), ('workspace_bytes', C.c_size_t),
-        ('scores_in', C.c_void_p), ('reuse_item_prep', C.c_int32), ('reserved_', C.c_int32),
+        ('scores_in', C.c_void_p), ('reuse_item_prep', C.c_int32), ('tc_terms', C.c_int32),
         ('tc_status', C.c_void_p), ('tc_overflow_rows', C.c_void_p), ('tc_row_base', C.c_int64),
         ('tc_overflow_cap', C.c_int32), ('reserved4_', C.c_int32),
     ]

@@ -311,9 +311,9 @@ k_rank_rows(const RankDev p) {
   double total = 0.0;
   const bool one_pass = lists || (p.want_mrr && best.id >= 0) || auc;
   if (one_pass) {
-    for (int64_t c = tid; c < p.n_items; c += blockDim.x) {
+    auto visit = [&](float score, int64_t c) {
       Key cur;
-      cur.s = row[c];
+      cur.s = score;
       cur.id = (int)(p.item_offset + c);
       if (lists && (have < K || cur.s > worst)) {
         // ids grow along a thread's walk: an equal score never displaces an entry; sorted insert
@@ -340,7 +340,26 @@ k_rank_rows(const RankDev p) {
         while (lo < hi) { const int mid = (lo + hi) >> 1; if (sig[mid] <= v) lo = mid + 1; else hi = mid; }
         total += (double)(n_tgt - lo) + 0.5 * (double)(lo - lb);
       }
+    };
+    // 16-byte loads, four scores per thread and iteration (a CTA alone on its SM, as in the
+    // tensor-core path's hand-over, runs at the latency of its loads); the elements before the
+    // first aligned one and after the last whole vector go one by one. A thread's ids still grow
+    // along its walk.
+    const int64_t mis = (int64_t)((reinterpret_cast<uintptr_t>(row) >> 2) & 3);
+    int64_t lead = (4 - mis) & 3;
+    if (lead > p.n_items) lead = p.n_items;
+    const int64_t n_vec = (p.n_items - lead) >> 2;
+    if (tid < lead) visit(row[tid], tid);
+    const float4* vrow = reinterpret_cast<const float4*>(row + lead);
+    for (int64_t v4 = tid; v4 < n_vec; v4 += blockDim.x) {
+      const float4 x = vrow[v4];
+      const int64_t c = lead + 4 * v4;
+      visit(x.x, c);
+      visit(x.y, c + 1);
+      visit(x.z, c + 2);
+      visit(x.w, c + 3);
     }
+    for (int64_t c = lead + 4 * n_vec + tid; c < p.n_items; c += blockDim.x) visit(row[c], c);
   }
 
   // ---- top-k: k block-wide selections, over the list heads (or over the row when k is large)

@@ -65,7 +65,7 @@ constexpr int TC_BK = 64;         // bf16 per K block = one 128-byte swizzle row
 constexpr int TC_STAGES = 3;
 constexpr int TC_MAXK = 16;       // largest k
 constexpr int TC_BIAS_SLOTS = 8;   // extra K slots: the two biases (three bf16 pieces each) + two error-bound slots
-constexpr int TC_BCAP = 64;       // band entries kept per (user, slot) for the MRR counter
+constexpr int TC_BCAP = 512;      // band entries kept per USER for the MRR counter (all its slots share them)
 constexpr int TC_A_BYTES = TC_BM * TC_BK * 2;   // 16 KB: one K-block of the user tile
 constexpr int TC_B_BYTES = TC_BN * TC_BK * 2;   // 32 KB: one K-block of an item tile
 
@@ -445,8 +445,8 @@ struct TcParams {
   float* cand_s;         // [n_users_pad][n_slots][KL]
   int32_t* cand_i;
   int32_t* cnt;          // [n_users_pad][n_slots] items surely ranked before the best target
-  int32_t* bcnt;         // [n_users_pad][n_slots] items in the band around it (may exceed TC_BCAP)
-  int32_t* band_i;       // [n_users_pad][n_slots][TC_BCAP] their ids
+  int32_t* bcnt;         // [n_users_pad] items in the band around it (may exceed TC_BCAP)
+  int32_t* band_i;       // [n_users_pad][TC_BCAP] their positions, appended through bcnt
   unsigned long long* dbg;   // experiments (debug == 4): [0] list insertions, [1] insert-loop rounds
 };
 
@@ -621,8 +621,8 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         m_ub2 = p.ub2[urow];
         t_lo = m_bs;
       }
-      int before = 0, nband = 0;
-      int32_t* band = p.band_i + ((int64_t)urow * p.n_slots + slot) * TC_BCAP;
+      int before = 0;
+      int32_t* band = p.band_i + (int64_t)urow * TC_BCAP;
       unsigned dbg_ins = 0, dbg_rounds = 0;
 
       for (; w < seg_hi; ++w, ++t) {
@@ -674,8 +674,8 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             while (m_band) {          // rare: a handful of items per user
               const int j = __ffs(m_band) - 1;
               m_band &= m_band - 1;
-              if (nband < TC_BCAP) band[nband] = gid0 + c0 + j;
-              ++nband;
+              const int at = atomicAdd(p.bcnt + urow, 1);   // (the user's segments share the buffer)
+              if (at < TC_BCAP) band[at] = gid0 + c0 + j;
             }
           }
           m_ins &= m_rng;
@@ -741,7 +741,6 @@ k_tc_gemm_topk(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int j = 0; j < KL; ++j) { cs[j] = ls[j]; ci[j] = li[j]; }
         if (p.want_mrr) {
           p.cnt[(int64_t)urow * p.n_slots + slot] = before;
-          p.bcnt[(int64_t)urow * p.n_slots + slot] = nband;
         }
       }
     }
@@ -921,10 +920,8 @@ k_tc_finish(const TcFinish p) {
   const float bs = mrr && bid >= 0 ? p.best_s[r] : 0.f;
   int sure = 0;
   if (mrr && bid >= 0) {
-    for (int sl = lane; sl < p.n_slots; sl += 32) {
-      sure += p.cnt[r * p.n_slots + sl];
-      if (p.bcnt[r * p.n_slots + sl] > TC_BCAP) fallback = true;
-    }
+    for (int sl = lane; sl < p.n_slots; sl += 32) sure += p.cnt[r * p.n_slots + sl];
+    if (p.bcnt[r] > TC_BCAP) fallback = true;
   }
   // ---- (2) this lane's candidates
   const int64_t u = p.user_ids[r];
@@ -1002,10 +999,9 @@ k_tc_finish(const TcFinish p) {
   if (mrr && p.n_before_best) {
     int more = 0;
     if (bid >= 0) {
-      for (int e = lane; e < p.n_slots * TC_BCAP; e += 32) {
-        const int sl = e / TC_BCAP, n = e - sl * TC_BCAP;
-        if (n >= p.bcnt[r * p.n_slots + sl]) continue;
-        const int pos = p.band_i[(r * p.n_slots + sl) * TC_BCAP + n];
+      const int n_band = p.bcnt[r];
+      for (int e = lane; e < n_band; e += 32) {
+        const int pos = p.band_i[r * TC_BCAP + e];
         const int id = (int)(p.item_offset + (p.perm ? p.perm[pos] : pos));
         if (id == bid) continue;     // the target never precedes itself
         const float ex = tc_exact_score(urow, p.I + (int64_t)id * p.D, p.D, ub, p.bi[id]);
@@ -1075,7 +1071,7 @@ struct TcLayout {
   int Kp, KB, KL, epi_warps, m_tiles, n_tiles, n_ctas, n_slots, fb_cap;
   int64_t m_pad, chunk, total_work;
   size_t Bp, Ap, ua, ub2, item_b, tile_bmax, perm, sort_keys, sort_keys2, sort_vals, sort_temp, sort_temp_bytes, stats, best_s, best_id, cand_s, cand_i, cnt, bcnt, band_i,
-      fb_list, fb_uid, status, fb_scores, fb_sig, total;
+      fb_list, fb_uid, status, fb_scores, total;
 };
 
 // (the layout is sized for three terms, so one workspace serves both forms)
@@ -1098,9 +1094,9 @@ static TcLayout tc_layout(int64_t n_users, int64_t n_items, int D, int k, int te
   // (measured: sixteen epilogue warps of 32-column groups are ~15 % slower than eight)
   L.epi_warps = (g_tc_epi_warps == 16 && L.KL <= 16) ? 16 : 8;
   L.n_slots = (L.epi_warps / 4) * (int)((L.n_tiles + L.chunk - 1) / L.chunk + 1);
-  // users the exact path can take over per call: up to 64 MB of score rows
-  int64_t cap = ((int64_t)64 << 20) / (int64_t)(sizeof(float) * (size_t)n_items);
-  L.fb_cap = (int)(cap < 1 ? 1 : (cap > 256 ? 256 : cap));
+  // users the exact path can take over per call: up to 128 MB of score rows
+  int64_t cap = ((int64_t)128 << 20) / (int64_t)(sizeof(float) * (size_t)n_items);
+  L.fb_cap = (int)(cap < 1 ? 1 : (cap > 1024 ? 1024 : cap));
   if (L.fb_cap > n_users) L.fb_cap = (int)n_users;
   size_t o = 0;
   auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes, 1024); return at; };
@@ -1126,13 +1122,12 @@ static TcLayout tc_layout(int64_t n_users, int64_t n_items, int D, int k, int te
   L.cand_s = take(sizeof(float) * L.m_pad * L.n_slots * L.KL);
   L.cand_i = take(sizeof(int32_t) * L.m_pad * L.n_slots * L.KL);
   L.cnt = take(sizeof(int32_t) * L.m_pad * L.n_slots);
-  L.bcnt = take(sizeof(int32_t) * L.m_pad * L.n_slots);
-  L.band_i = take(sizeof(int32_t) * L.m_pad * L.n_slots * TC_BCAP);
+  L.bcnt = take(sizeof(int32_t) * L.m_pad);
+  L.band_i = take(sizeof(int32_t) * L.m_pad * TC_BCAP);
   L.fb_list = take(sizeof(int32_t) * L.fb_cap);
   L.fb_uid = take(sizeof(int32_t) * L.fb_cap);
   L.status = take(sizeof(int32_t) * 8);
   L.fb_scores = take(sizeof(float) * (size_t)L.fb_cap * n_items);
-  L.fb_sig = take(2 * sizeof(float) * (size_t)L.fb_cap * n_items);
   L.total = o;
   return L;
 }
@@ -1159,7 +1154,10 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
                 "cmf_eval_tile: the tensor-core path takes embedding_dim <= 128 and k <= %d "
                 "(got D = %d, k = %d); use precision = 0", TC_MAXK, a->D, a->k);
   const bool mrr = a->want_mrr != 0;
-  const int terms = g_tc_terms == 1 || g_tc_terms == 3 ? g_tc_terms : (mrr ? 3 : 1);
+  CMF_REQUIRE(a->tc_terms == 0 || a->tc_terms == 1 || a->tc_terms == 3,
+              "cmf_eval_tile: tc_terms must be 0, 1 or 3 (got %d)", a->tc_terms);
+  const int terms = a->tc_terms ? a->tc_terms
+                                : (g_tc_terms == 1 || g_tc_terms == 3 ? g_tc_terms : (mrr ? 3 : 1));
   const TcLayout L = tc_layout(a->n_users_tile, a->num_items_shard, a->D, a->k, terms);
   const size_t need = eval_tc_workspace_bytes(a->n_users_tile, a->num_items_shard, a->D, a->k);
   if (!a->workspace || a->workspace_bytes < need)
@@ -1252,7 +1250,7 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   CMF_CUDA(cudaMemsetAsync(p.cand_i, 0xFF, sizeof(int32_t) * L.m_pad * L.n_slots * L.KL, s));
   if (mrr) {
     CMF_CUDA(cudaMemsetAsync(p.cnt, 0, sizeof(int32_t) * L.m_pad * L.n_slots, s));
-    CMF_CUDA(cudaMemsetAsync(p.bcnt, 0, sizeof(int32_t) * L.m_pad * L.n_slots, s));
+    CMF_CUDA(cudaMemsetAsync(p.bcnt, 0, sizeof(int32_t) * L.m_pad, s));
   }
   CMF_CUDA(cudaMemsetAsync(status, 0, sizeof(int32_t) * 8, s));
   // list length: the smallest instantiation that leaves a margin above k
@@ -1303,7 +1301,7 @@ int eval_tile_tc(const cmf_eval_t* a, cudaStream_t s) {
   if (rc) return rc;
   cmf_eval_t b = *a;
   if (mrr) { b.ext_best_score = best_s; b.ext_best_id = best_id; b.best_score = nullptr; b.best_id = nullptr; }
-  rc = launch_rank_rows_mapped(&b, fb_scores, (float*)(base + L.fb_sig), f.fb_list, status,
+  rc = launch_rank_rows_mapped(&b, fb_scores, nullptr /* (AUC scratch: not on this path) */, f.fb_list, status,
                                L.fb_cap, s);
   if (rc) return rc;
   if (a->tc_status) {

@@ -58,7 +58,7 @@ def _targets_all_users_device(targets: csr_matrix, test_users, device):
 
 def _eval_tile(device, n_users, n_items, k, indptr, tgt_items, want, tables=None, user_ids=None,
                scores=None, precision=0, workspace=None, reuse_item_prep=False, item_offset=0,
-               ext_best=None, into=None, tc_status=None, tc_overflow=None):
+               ext_best=None, into=None, tc_status=None, tc_overflow=None, tc_terms=0):
     """One ``cmf_eval_tile`` call; returns dict of per-user device tensors. ``item_offset`` /
     ``n_items`` select an item shard of the table (global ids come back); ``ext_best`` = (score,
     id) of every user's best target over ALL shards, against which the MRR counter counts;
@@ -84,6 +84,7 @@ def _eval_tile(device, n_users, n_items, k, indptr, tgt_items, want, tables=None
     a.tgt_indptr, a.tgt_items = indptr.data_ptr(), tgt_items.data_ptr()
     a.precision = precision
     a.reuse_item_prep = 1 if reuse_item_prep else 0
+    a.tc_terms = tc_terms
     if tc_status is not None:
         a.tc_status = tc_status.data_ptr()
         keep.append(tc_status)
@@ -278,23 +279,37 @@ def evaluate_in_batches(metric_list, test_interactions, model, k=10, batch_size=
             ws = None
             status = torch.zeros(4, dtype=torch.int32, device=device)
             overflow = torch.empty(n_test, dtype=torch.int32, device=device)
-            for s in range(0, n_test, tile):
+            terms, fresh_prep, s = 0, True, 0
+            while s < n_test:
                 e = min(s + tile, n_test)
                 ws = _eval_tile(device, e - s, n_items, k, indptr[s:e + 1], tgt_items,
                                 set(tc_names), tables=tables, user_ids=users_dev[s:e],
-                                precision=1, workspace=ws, reuse_item_prep=(s > 0),
+                                precision=1, workspace=ws, reuse_item_prep=not fresh_prep,
                                 into=(whole, s), tc_status=status,
-                                tc_overflow=(overflow, s))['_workspace']
-                if s == 0 and e < n_test and int(status[1].item()) > (e - s) // 4:
-                    # the first tile already left a quarter of its users to the exact path
-                    # (scores too close together for the error bound, e.g. an untrained model):
-                    # do not spend the remaining tiles on the tensor cores
-                    LAST_TC_STATUS.clear()
-                    LAST_TC_STATUS.update(users=n_test, handed_to_exact_path=int(status[0]),
-                                          not_taken_over=int(status[1]), gave_up_after=e)
-                    return evaluate_in_batches(metric_list, test_interactions, model, k=k,
-                                               batch_size=batch_size, logger=logger,
-                                               verbose=verbose, precision=0)
+                                tc_overflow=(overflow, s), tc_terms=terms)['_workspace']
+                fresh_prep = False
+                if s == 0 and e < n_test:
+                    # the first tile of several tells how the rest will go (one read-back)
+                    handed, lost = (int(x) for x in status[:2].tolist())
+                    if terms == 0 and 'mrr' not in tc_names and handed > (e - s) // 50:
+                        # one bf16 term left more than 2 % of the tile to the exact path (top
+                        # scores closer together than its bound can tell): three terms cost less
+                        # than that many exact re-rankings; a tile that lost a quarter is redone
+                        terms, fresh_prep = 3, True
+                        if lost > (e - s) // 4:
+                            status.zero_()
+                            continue
+                    elif lost > (e - s) // 4:
+                        # a quarter of the users left to the exact path even so (e.g. an
+                        # untrained model: all scores within the bound of each other): do not
+                        # spend the remaining tiles on the tensor cores
+                        LAST_TC_STATUS.clear()
+                        LAST_TC_STATUS.update(users=n_test, handed_to_exact_path=handed,
+                                              not_taken_over=lost, gave_up_after=e)
+                        return evaluate_in_batches(metric_list, test_interactions, model, k=k,
+                                                   batch_size=batch_size, logger=logger,
+                                                   verbose=verbose, precision=0)
+                s = e
         for j, name in enumerate(names):
             sums[j] = _per_user(name, whole, nnz, n_items).sum()
         if status is not None:

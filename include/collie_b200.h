@@ -375,7 +375,11 @@ typedef struct {
   /* precision = 1 only: non-zero = the item table, the shard and want_mrr are those of the
    * previous call with this workspace, so the bf16 copy of the items in the workspace is reused */
   int32_t reuse_item_prep;
-  int32_t reserved_;
+  /* precision = 1 only: bf16 terms of the operands, 0 = automatic (1 without the MRR counter, 3
+   * with it), 1 or 3 = as said (3 costs three times the MMA work and settles users whose top
+   * scores lie closer together than the one-term bound can tell; results are exact either way;
+   * part of what reuse_item_prep assumes unchanged) */
+  int32_t tc_terms;
   /* precision = 1 only, optional: int32[2] on the device, ADDED to by every call: [0] users whose
    * candidates the error bound could not separate and that were therefore ranked by the exact
    * path inside the call (results are exact either way), [1] such users beyond what the

@@ -566,10 +566,10 @@ def test_tensor_core_eval_matches_exact_path(shape):
                       tables=tabs, user_ids=users, precision=0)
     # the tensor cores select, fp32 decides: ids, scores, AP and the MRR counter are the exact
     # path's, bit for bit -- with the MRR counter (three bf16 terms) and without (one term)
-    for want in ({'topk', 'mapk', 'mrr'}, {'topk', 'mapk'}):
+    for want, terms in (({'topk', 'mapk', 'mrr'}, 0), ({'topk', 'mapk'}, 0), ({'topk', 'mapk'}, 3)):
         status = torch.zeros(2, dtype=torch.int32, device='cuda')
         tc = M._eval_tile('cuda', n_users, n_items, k, indptr, items, want, tables=tabs,
-                          user_ids=users, precision=1, tc_status=status)
+                          user_ids=users, precision=1, tc_status=status, tc_terms=terms)
         assert int(status[1]) == 0
         # ... and by the tensor-core route itself: the exact path may take over the odd user whose
         # scores are too close to call, not the fixture
