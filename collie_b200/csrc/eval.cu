@@ -228,12 +228,15 @@ struct RankDev {
   int row_cap;
 };
 
-constexpr int kListK = 12;   // k up to which the one-pass ranking keeps per-thread lists
+constexpr int kListL = 4;    // entries of a thread's list in the one-pass ranking
 
 // One CTA per user row. Everything that needs the whole row is gathered in ONE pass over it:
 // per-thread top-k lists (shared memory, sorted), the count of items ranked before the best
 // target (MRR), the Mann-Whitney pair count against the sorted target sigmoids (AUC); the lists
-// are then merged by k block-wide selections. k > kListK falls back to k selection passes.
+// are then merged by k block-wide selections. A thread keeps only its best kListL items and the
+// best score it let go: if that could belong to the top-k after all (more than kListL of the top-k
+// in one thread's 1/256 of the row, or ties at the k-th score), the row is ranked again by k
+// selection passes over the scores.
 __global__ void __launch_bounds__(256)
 k_rank_rows(const RankDev p) {
   __shared__ Key s_key[8];
@@ -241,8 +244,8 @@ k_rank_rows(const RankDev p) {
   __shared__ double s_dbl[8];
   __shared__ float s_sig[kSigSmem];
   __shared__ float s_raw[kSigSmem];
-  __shared__ float s_ls[kListK][256];   // [rank in the thread's list][thread]: conflict-free
-  __shared__ int s_li[kListK][256];
+  __shared__ float s_ls[kListL][256];   // [rank in the thread's list][thread]: conflict-free
+  __shared__ int s_li[kListL][256];
   const int tid = threadIdx.x;
   int r = blockIdx.x;
   const float* row = p.S + (int64_t)blockIdx.x * p.ld;
@@ -257,7 +260,9 @@ k_rank_rows(const RankDev p) {
   const int lo_id = (int)p.item_offset, hi_id = (int)(p.item_offset + p.n_items);
   const int K = p.k;
   const bool want_topk = p.topk_ids || p.topk_scores || p.ap;
-  const bool lists = want_topk && K <= kListK;
+  const bool lists = want_topk;
+  const int L = K < kListL ? K : kListL;   // list length
+  float dropped = -INFINITY;               // best score this thread did not keep
 
   // ---- MRR: the best-ranked target (its row entry is read directly)
   Key best;
@@ -286,6 +291,7 @@ k_rank_rows(const RankDev p) {
   // ---- AUC: the targets' sigmoids, rank-sorted ascending by counting
   const bool auc = p.want_auc && n_tgt > 0;
   float* sig = s_sig;
+  int sig_pow2 = 0;   // > 0: sig is padded to this power of two (shared-memory case)
   if (auc) {
     const bool in_smem = n_tgt <= kSigSmem;
     sig = in_smem ? s_sig : p.sig_scratch + 2 * (t0 - p.tgt_indptr[0]);
@@ -301,6 +307,11 @@ k_rank_rows(const RankDev p) {
       }
       sig[rank] = v;
     }
+    if (in_smem) {
+      sig_pow2 = 1;
+      while (sig_pow2 < n_tgt) sig_pow2 <<= 1;
+      for (int t = n_tgt + tid; t < sig_pow2; t += blockDim.x) sig[t] = INFINITY;
+    }
     __syncthreads();
   }
 
@@ -315,29 +326,48 @@ k_rank_rows(const RankDev p) {
       Key cur;
       cur.s = score;
       cur.id = (int)(p.item_offset + c);
-      if (lists && (have < K || cur.s > worst)) {
-        // ids grow along a thread's walk: an equal score never displaces an entry; sorted insert
-        int pos = have < K ? have : K - 1;
-        while (pos > 0 && s_ls[pos - 1][tid] < cur.s) {
-          s_ls[pos][tid] = s_ls[pos - 1][tid];
-          s_li[pos][tid] = s_li[pos - 1][tid];
-          --pos;
+      if (lists) {
+        if (have < L || cur.s > worst) {
+          // ids grow along a thread's walk: an equal score never displaces an entry; sorted insert
+          if (have == L) dropped = fmaxf(dropped, worst);
+          int pos = have < L ? have : L - 1;
+          while (pos > 0 && s_ls[pos - 1][tid] < cur.s) {
+            s_ls[pos][tid] = s_ls[pos - 1][tid];
+            s_li[pos][tid] = s_li[pos - 1][tid];
+            --pos;
+          }
+          s_ls[pos][tid] = cur.s;
+          s_li[pos][tid] = cur.id;
+          if (have < L) ++have;
+          if (have == L) worst = s_ls[L - 1][tid];
+        } else {
+          dropped = fmaxf(dropped, cur.s);
         }
-        s_ls[pos][tid] = cur.s;
-        s_li[pos][tid] = cur.id;
-        if (have < K) ++have;
-        if (have == K) worst = s_ls[K - 1][tid];
       }
       // (the target never precedes itself, whatever arithmetic produced an external threshold)
       if (p.want_mrr && best.id >= 0) cnt += (cur.id != best.id && before(cur, best)) ? 1 : 0;
       if (auc) {
         // every item adds (#targets above it) + (#targets equal to it) / 2
         const float v = sigmoidf_(cur.s);
-        int lo = 0, hi = n_tgt;  // lower_bound
-        while (lo < hi) { const int mid = (lo + hi) >> 1; if (sig[mid] < v) lo = mid + 1; else hi = mid; }
-        const int lb = lo;
-        hi = n_tgt;              // upper_bound
-        while (lo < hi) { const int mid = (lo + hi) >> 1; if (sig[mid] <= v) lo = mid + 1; else hi = mid; }
+        int lb, lo;
+        if (sig_pow2 > 0) {
+          // the sorted sigmoids padded with +inf to a power of two: a lower bound in log2 steps
+          // of select arithmetic, the same for all lanes (the two branching searches were 30 %
+          // of this kernel's instructions); equal targets are then counted forward (rare)
+          int pos = 0;
+          for (int step = sig_pow2 >> 1; step > 0; step >>= 1) pos += (sig[pos + step - 1] < v) ? step : 0;
+          pos += (sig[pos] < v) ? 1 : 0;
+          lb = pos;
+          while (pos < n_tgt && sig[pos] == v) ++pos;
+          lo = pos;
+        } else {
+          int hi = n_tgt;  // lower_bound
+          lo = 0;
+          while (lo < hi) { const int mid = (lo + hi) >> 1; if (sig[mid] < v) lo = mid + 1; else hi = mid; }
+          lb = lo;
+          hi = n_tgt;              // upper_bound
+          while (lo < hi) { const int mid = (lo + hi) >> 1; if (sig[mid] <= v) lo = mid + 1; else hi = mid; }
+        }
         total += (double)(n_tgt - lo) + 0.5 * (double)(lo - lb);
       }
     };
@@ -363,17 +393,19 @@ k_rank_rows(const RankDev p) {
   }
 
   // ---- top-k: k block-wide selections, over the list heads (or over the row when k is large)
-  if (want_topk) {
-    int hits = 0, head = 0;
+  for (int attempt = 0; want_topk && attempt < 2; ++attempt) {
+    const bool use_lists = lists && attempt == 0;
+    int hits = 0, head = 0, picks = 0;
     double ap_acc = 0.0;
-    Key prev;
+    Key prev, pick;
     prev.s = INFINITY;
     prev.id = -1;
+    pick = prev;
     for (int j = 0; j < K; ++j) {
       Key mine;
       mine.s = -INFINITY;
       mine.id = -1;
-      if (lists) {
+      if (use_lists) {
         if (head < have) { mine.s = s_ls[head][tid]; mine.id = s_li[head][tid]; }
       } else {
         for (int64_t c = tid; c < p.n_items; c += blockDim.x) {
@@ -384,8 +416,8 @@ k_rank_rows(const RankDev p) {
           if (after_prev && (mine.id < 0 || before(cur, mine))) mine = cur;
         }
       }
-      const Key pick = block_best(mine, s_key);
-      if (lists && pick.id >= 0 && pick.id == mine.id) ++head;
+      pick = block_best(mine, s_key);
+      if (use_lists && pick.id >= 0 && pick.id == mine.id) ++head;
       if (tid == 0) {
         if (p.topk_ids) p.topk_ids[(int64_t)r * K + j] = pick.id;
         if (p.topk_scores) p.topk_scores[(int64_t)r * K + j] = pick.id >= 0 ? pick.s : -INFINITY;
@@ -403,12 +435,17 @@ k_rank_rows(const RankDev p) {
           }
         break;
       }
+      ++picks;
     }
     if (tid == 0 && p.ap) {
       // AP@k = sum_j acc_j * cumsum_j / j / min(k, nnz_u); 0 when the user has no targets
       const int denom = K < n_tgt ? K : n_tgt;
       p.ap[r] = denom > 0 ? ap_acc / (double)denom : 0.0;
     }
+    if (!use_lists) break;
+    // could something a thread let go belong to the top-k? (then rank again without the lists)
+    const bool doubt = dropped > -INFINITY && (picks < K || dropped >= pick.s);
+    if (!__syncthreads_or(doubt ? 1 : 0)) break;
   }
 
   if (p.want_mrr) {
