@@ -64,7 +64,7 @@ class cmf_step_t(C.Structure):
         ('workspace', C.c_void_p), ('workspace_bytes', C.c_size_t),
         ('B_global', C.c_int64), ('skip_item_update', C.c_int32), ('num_items_logical', C.c_int32),
         ('item_grads_ready_event', C.c_void_p), ('dropout_p', C.c_float),
-        ('reserved3', C.c_int32),
+        ('deterministic', C.c_int32),
     ]
 
 

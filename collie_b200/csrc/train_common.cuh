@@ -209,6 +209,10 @@ struct StepDev {
   float drop_scale;
   uint32_t drop_key_hi;   // optimizer step: a batch that is repeated draws fresh masks
   int red_in_fwd;         // the forward kernel sends the item-row gradient contributions itself
+  int bwd_skip_item;      // k_bwd_update leaves the item side alone (red_in_fwd, or the deterministic reduce)
+  // deterministic step: chunk c of k_bwd_update = [chunk_starts[c], chunk_starts[c + 1]), cut at
+  // user boundaries, so every user is summed by one warp in batch order (NULL: chunks of L)
+  const int32_t* chunk_starts;
 };
 
 // The dropout mask of one row of one scored pair: interaction at dataset position gidx, slot 0 =
@@ -273,6 +277,7 @@ __device__ __forceinline__ float ideal_of(const StepDev& p, int pos, int neg) {
 // train_step_v3.cu: the split fast path (k_fwd_loss + k_bwd_update)
 bool v3_supported(int D, int N);
 int launch_fwd_loss_v3(const StepDev& p, bool sort_runs_alongside, cudaStream_t s);
-int launch_bwd_update_v3(const StepDev& p, int max_chunk_len, cudaStream_t s);
+int launch_bwd_update_v3(const StepDev& p, int max_chunk_len, cudaStream_t s,
+                         int32_t* aligned_chunk_starts = nullptr);
 
 }  // namespace cmf

@@ -32,6 +32,11 @@ extern int g_tc_list_len;
 extern int g_tc_epi_warps;
 extern int g_pdl;
 extern int g_red_in_fwd;
+size_t det_sort_bytes(int64_t n_pairs);
+int launch_aligned_chunks(const StepDev& p, int32_t* starts, cudaStream_t s);
+int launch_det_item_side(const StepDev& p, int64_t num_item_rows, uint32_t* keys, uint32_t* keys2,
+                         uint32_t* vals, uint32_t* vals2, int32_t* starts, void* temp,
+                         size_t temp_bytes, cudaStream_t s);
 
 struct WsLayout {
   // persistent (zero between steps; the kernels restore the invariant)
@@ -41,6 +46,9 @@ struct WsLayout {
   size_t cub_temp_bytes, total;
   // large item tables: the touched-row list sorted by row, so the update streams through memory
   size_t item_list_sorted, cub_items_temp, cub_items_temp_bytes;
+  // deterministic step (train_det.cu): sorted (item, contribution) pairs, item segment starts,
+  // user-aligned chunk starts
+  size_t det_keys, det_keys2, det_vals, det_vals2, det_starts, det_chunks, det_temp, det_temp_bytes;
 };
 
 static size_t cub_sort_bytes(int64_t B) {
@@ -80,6 +88,14 @@ static WsLayout ws_layout(int64_t B, int64_t num_users, int64_t num_items, int D
   cub::DeviceRadixSort::SortKeys((void*)nullptr, w.cub_items_temp_bytes, (const uint32_t*)nullptr,
                                  (uint32_t*)nullptr, (int)num_items, 0, 32, (cudaStream_t)0);
   w.cub_items_temp = take(w.cub_items_temp_bytes);
+  w.det_keys = take(sizeof(uint32_t) * 2 * B);
+  w.det_keys2 = take(sizeof(uint32_t) * 2 * B);
+  w.det_vals = take(sizeof(uint32_t) * 2 * B);
+  w.det_vals2 = take(sizeof(uint32_t) * 2 * B);
+  w.det_starts = take(sizeof(int32_t) * (num_items + 1));
+  w.det_chunks = take(sizeof(int32_t) * (B + 2));
+  w.det_temp_bytes = det_sort_bytes(2 * B);
+  w.det_temp = take(w.det_temp_bytes);
   w.total = o;
   return w;
 }
@@ -763,6 +779,10 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
   const int version = g_kernel_version.load();
   // (dropout lives in the generic kernel only: it keeps the scored rows and their masks together)
   const bool split = version != 1 && v3_supported(a->D, a->N) && a->dropout_p == 0.f;
+  CMF_REQUIRE(split || !(a->train && a->deterministic),
+              "cmf_train_step: the deterministic step needs embedding_dim %% 4 == 0, at most %d "
+              "negatives and no dropout (got D = %d, N = %d, dropout_p = %g)", kMaxNeg, a->D, a->N,
+              (double)a->dropout_p);
   CMF_REQUIRE(split || version != 2,
               "cmf_train_step: the split kernels do not support this shape (D=%d, N=%d)", a->D, a->N);
   const int forced_len = g_forced_chunk_len.load() > 0 ? g_forced_chunk_len.load() : 0;
@@ -814,14 +834,24 @@ extern "C" int cmf_train_step(const cmf_step_t* a, void* stream) {
 
   if (split) {
     // e0 -> e1: k_fwd_loss;  e1 -> e2: what is left of the sort;  e2 -> e3: k_bwd_update
-    p.red_in_fwd = (g_red_in_fwd && p.train && a->D / 4 <= 32) ? 1 : 0;
+    const bool det = p.train && a->deterministic != 0;
+    p.red_in_fwd = (!det && g_red_in_fwd && p.train && a->D / 4 <= 32) ? 1 : 0;
+    p.bwd_skip_item = (p.red_in_fwd || det) ? 1 : 0;
     int rc = launch_fwd_loss_v3(p, side != nullptr, s);
     if (rc != CMF_OK) return rc;
     if (g_prof_on) CMF_CUDA(cudaEventRecord(prof.e[1], s));
     if (side) CMF_CUDA(cudaStreamWaitEvent(s, side->join, 0));
     if (g_prof_on) CMF_CUDA(cudaEventRecord(prof.e[2], s));
+    if (det) {
+      // item side first: it reads the user rows the backward kernel is about to update in place
+      rc = launch_det_item_side(p, a->num_items, (uint32_t*)(base + w.det_keys),
+                                (uint32_t*)(base + w.det_keys2), (uint32_t*)(base + w.det_vals),
+                                (uint32_t*)(base + w.det_vals2), (int32_t*)(base + w.det_starts),
+                                base + w.det_temp, w.det_temp_bytes, s);
+      if (rc != CMF_OK) return rc;
+    }
     if (p.train) {
-      rc = launch_bwd_update_v3(p, forced_len, s);
+      rc = launch_bwd_update_v3(p, forced_len, s, det ? (int32_t*)(base + w.det_chunks) : nullptr);
       if (rc != CMF_OK) return rc;
     }
   } else {

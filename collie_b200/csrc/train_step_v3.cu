@@ -646,21 +646,32 @@ k_bwd_update(const StepDev p) {
   const int64_t gwarp = (int64_t)blockIdx.x * 8 + warp;
   const int64_t n_warps = (int64_t)gridDim.x * 8;
 
+  const bool aligned = p.chunk_starts != nullptr;   // chunks cut at user boundaries: no straddlers
   for (int64_t ch = gwarp; ch < p.num_chunks; ch += n_warps) {
-    const int64_t e0 = ch * p.L;
-    const int n_e = (int)((e0 + p.L < p.B ? e0 + p.L : p.B) - e0);
-    if (lane < n_e) {
-      const int64_t e = e0 + lane;
-      const int64_t b = p.perm ? (int64_t)p.perm[e] : e;
-      const uint32_t t = a_tab + lane * 16;
-      sts_i32(t, p.su[e]);
-      sts_i32(t + 4, p.items[b]);
-      sts_i32(t + 8, p.sel_arr[b]);
-      sts_f32(t + 12, p.g_arr[b]);
-    }
+    const int64_t c0 = aligned ? (int64_t)p.chunk_starts[ch] : ch * p.L;
+    const int64_t c1 = aligned ? (int64_t)p.chunk_starts[ch + 1]
+                               : (c0 + p.L < p.B ? c0 + p.L : p.B);
+    if (c0 >= c1) continue;
+    // (an aligned chunk can be longer than the table: it is walked in table-sized pieces)
+    int64_t e0 = c0;
+    int n_e = (int)(c1 - c0 < kMaxChunkB ? c1 - c0 : kMaxChunkB);
+    auto load_table = [&]() {
+      if (lane < n_e) {
+        const int64_t e = e0 + lane;
+        const int64_t b = p.perm ? (int64_t)p.perm[e] : e;
+        const uint32_t t = a_tab + lane * 16;
+        sts_i32(t, p.su[e]);
+        sts_i32(t + 4, p.items[b]);
+        sts_i32(t + 8, p.sel_arr[b]);
+        sts_f32(t + 12, p.g_arr[b]);
+      }
+    };
+    load_table();
     // the users just outside the chunk decide whether a boundary segment is whole
-    if (lane == 30) sts_i32(a_meta, (e0 > 0) ? p.su[e0 - 1] : -1);
-    if (lane == 31) sts_i32(a_meta + 4, (e0 + n_e < p.B) ? p.su[e0 + n_e] : -1);
+    if (!aligned) {
+      if (lane == 30) sts_i32(a_meta, (e0 > 0) ? p.su[e0 - 1] : -1);
+      if (lane == 31) sts_i32(a_meta + 4, (e0 + n_e < p.B) ? p.su[e0 + n_e] : -1);
+    }
     __syncwarp();
 
     int cur_user = -1;
@@ -698,6 +709,7 @@ k_bwd_update(const StepDev p) {
       }
     };
 
+    for (;;) {
     for (int le = 0; le < n_e; ++le) {
       const uint32_t t = a_tab + le * 16;
       const int u = lds_i32(t);
@@ -720,7 +732,7 @@ k_bwd_update(const StepDev p) {
       if (u != cur_user) {
         finish_user(true);   // another user follows inside the chunk
         cur_user = u;
-        left_whole = (le > 0) || (lds_i32(a_meta) != u);
+        left_whole = aligned || (le > 0) || (lds_i32(a_meta) != u);
         gu.zero();
         gbu_acc = 0.f;
         m_pre.zero();
@@ -754,31 +766,38 @@ k_bwd_update(const StepDev p) {
             f[3] = __fadd_rn(f[3], __fmul_rn(g, xp[r].w));
             float tt[4] = {__fmul_rn(g, pu[0]), __fmul_rn(g, pu[1]), __fmul_rn(g, pu[2]),
                            __fmul_rn(g, pu[3])};
-            if (!p.red_in_fwd) red_vec<4>(gi_pos + r * 128, tt);
+            if (!p.bwd_skip_item) red_vec<4>(gi_pos + r * 128, tt);
             if (implicit) {
               f[0] = __fadd_rn(f[0], __fmul_rn(-g, xs[r].x));
               f[1] = __fadd_rn(f[1], __fmul_rn(-g, xs[r].y));
               f[2] = __fadd_rn(f[2], __fmul_rn(-g, xs[r].z));
               f[3] = __fadd_rn(f[3], __fmul_rn(-g, xs[r].w));
               tt[0] = -tt[0]; tt[1] = -tt[1]; tt[2] = -tt[2]; tt[3] = -tt[3];
-              if (!p.red_in_fwd) red_vec<4>(gi_sel + r * 128, tt);
+              if (!p.bwd_skip_item) red_vec<4>(gi_sel + r * 128, tt);
             }
           }
         }
         if (implicit) {
           gbu_acc += g;
           gbu_acc += -g;
-          if (lane == 0 && !p.red_in_fwd) {
+          if (lane == 0 && !p.bwd_skip_item) {
             atomicAdd(p.gbi + pos, g);
             atomicAdd(p.gbi + sel_id, -g);
           }
         } else {
           gbu_acc += g;
-          if (lane == 0 && !p.red_in_fwd) atomicAdd(p.gbi + pos, g);
+          if (lane == 0 && !p.bwd_skip_item) atomicAdd(p.gbi + pos, g);
         }
       }
     }
-    finish_user(lds_i32(a_meta + 4) != cur_user);
+      e0 += n_e;
+      if (e0 >= c1) break;
+      __syncwarp();   // next piece of a long aligned chunk: the user in progress carries over
+      n_e = (int)(c1 - e0 < kMaxChunkB ? c1 - e0 : kMaxChunkB);
+      load_table();
+      __syncwarp();
+    }
+    finish_user(aligned || lds_i32(a_meta + 4) != cur_user);
     __syncwarp();   // the table is rewritten by the next chunk
   }
 }
@@ -863,7 +882,10 @@ static int red_in_fwd_default() {
 }
 int g_red_in_fwd = red_in_fwd_default();
 
-int launch_bwd_update_v3(const StepDev& p_in, int max_chunk_len, cudaStream_t s) {
+int launch_aligned_chunks(const StepDev& p, int32_t* starts, cudaStream_t s);
+
+int launch_bwd_update_v3(const StepDev& p_in, int max_chunk_len, cudaStream_t s,
+                         int32_t* aligned_chunk_starts /* = nullptr */) {
   StepDev p = p_in;
   const int R = (p.D / 4 + 31) / 32;
   const bool full = (p.D == 128 * R);
@@ -874,6 +896,12 @@ int launch_bwd_update_v3(const StepDev& p_in, int max_chunk_len, cudaStream_t s)
   if (max_chunk_len > 0) L = max_chunk_len < kMaxChunkB ? max_chunk_len : kMaxChunkB;
   p.L = L;
   p.num_chunks = (p.B + L - 1) / L;
+  if (aligned_chunk_starts) {
+    // deterministic step: chunks cut at user boundaries
+    const int rc = launch_aligned_chunks(p, aligned_chunk_starts, s);
+    if (rc != CMF_OK) return rc;
+    p.chunk_starts = aligned_chunk_starts;
+  }
   const int grid = blocks_for(p.num_chunks, 8);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)grid);

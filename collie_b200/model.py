@@ -646,6 +646,12 @@ class MatrixFactorizationModel(torch.nn.Module):
         a.B_global = int(global_batch)
         a.skip_item_update = 1 if skip_item_update else 0
         a.num_items_logical = int(num_items_logical)
+        # torch.use_deterministic_algorithms(True) (or model.deterministic = True) asks for the
+        # bit-repeatable form of the step (cmf_step_t.deterministic)
+        det = getattr(self, 'deterministic', None)
+        if det is None:
+            det = torch.are_deterministic_algorithms_enabled()
+        a.deterministic = 1 if (det and train) else 0
         if self.training and h.dropout_p > 0:
             # nn.Dropout semantics: active whenever the module is in training mode
             a.dropout_p = float(h.dropout_p)

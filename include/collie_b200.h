@@ -153,7 +153,15 @@ typedef struct {
    * the counter-based stream of the negatives (other key), keyed by (seed, emb_opt.step, epoch,
    * dataset position, pair, side, element), so a step can be replayed. 0 = off. */
   float dropout_p;
-  int32_t reserved3;
+  /* non-zero: bit-repeatable step. The item-row gradients are summed in batch order from a
+   * radix-sorted (item, contribution) list instead of vector RED in arrival order, and every user
+   * is summed by one warp (chunks cut at user boundaries), so two runs of the same steps give the
+   * same bits whatever the schedule, chunk length or GPU. Slower (one sort of 2 B pairs and a
+   * serial sum per item row per step). Needs embedding_dim % 4 == 0 and dropout_p == 0. With
+   * skip_item_update the rank's accumulators are repeatable; the sum over the ranks is so only
+   * with the plain (non-multicast) exchange. The reference's CPU path is deterministic, torch's
+   * CUDA index_add is not (no counterpart of this switch in collie). */
+  int32_t deterministic;
 } cmf_step_t;
 
 /* scratch for cmf_train_step; depends only on the table shapes and the largest batch */
