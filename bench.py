@@ -1093,6 +1093,21 @@ def run_ours(args, rank, world, local_rank, w):
         eval_info = eval_block(job, peaks, with_cpu=(world == 1 and not args.no_cpu_baseline))
         _log('evaluation done')
 
+    # the bit-repeatable form of the step (cmf_step_t.deterministic), same batches, N = 1 only
+    det = None
+    if world == 1 and not args.no_strong:
+        job.model.deterministic = True
+        try:
+            d_steps = max(4, min(steps, 12))
+            msd, _, _, _, _, _ = time_device_steps(job, d_steps, 3)
+            det = {'ms_per_step': msd / d_steps, 'steps': d_steps,
+                   'value': d_steps * job.B / (msd * 1e-3), 'unit': 'interactions/s',
+                   'what': 'item gradients summed in batch order from a sorted contribution list, '
+                           'users summed by one warp: two runs give the same bits'}
+        finally:
+            job.model.deterministic = False
+        _log(f'deterministic step: {det}')
+
     # one constant-GLOBAL-work point (strong scaling): 2,097,152 interactions per global step,
     # i.e. 2,097,152 / N per GPU, so the weak-scaling curve above (whose per-rank user set shrinks
     # with N) has a fixed-work companion
@@ -1152,6 +1167,7 @@ def run_ours(args, rank, world, local_rank, w):
                               'slowest_step': int(np.argmax(step_ms))},
             'clocks': clk, 'final_loss': float(loss), 'parity': parity, 'eval': eval_info,
             'fixed_global_work': strong,
+            'deterministic_step': det,
         }
         print(json.dumps(line), file=OUT, flush=True)
     if world > 1:
