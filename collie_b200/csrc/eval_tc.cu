@@ -1100,10 +1100,9 @@ static TcLayout tc_layout(int64_t n_users, int64_t n_items, int D, int k, int te
   if (L.fb_cap > n_users) L.fb_cap = (int)n_users;
   size_t o = 0;
   auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes, 1024); return at; };
+  // item side first: what a call with reuse_item_prep finds again must not move with the number
+  // of users of the tile (the last tile of an evaluation is usually smaller)
   L.Bp = take((size_t)n_items * Kp_max * 2);
-  L.Ap = take((size_t)L.m_pad * Kp_max * 2);
-  L.ua = take(sizeof(float) * L.m_pad);
-  L.ub2 = take(sizeof(float) * L.m_pad);
   L.item_b = take(sizeof(float) * (size_t)n_items);
   L.tile_bmax = take(sizeof(float) * (size_t)L.n_tiles);
   // item order by norm (MRR form): permutation + radix-sort scratch
@@ -1116,7 +1115,10 @@ static TcLayout tc_layout(int64_t n_users, int64_t n_items, int D, int k, int te
                                   (uint32_t*)nullptr, (const int32_t*)nullptr, (int32_t*)nullptr,
                                   (int)n_items);
   L.sort_temp = take(L.sort_temp_bytes);
-  L.stats = take(sizeof(uint32_t) * 8);     // [0..1] of the items split with 1 term, [2..3] with 3, [4] which one Bp holds
+  L.stats = take(sizeof(uint32_t) * 8);     // [1] largest |item bias| of the shard
+  L.Ap = take((size_t)L.m_pad * Kp_max * 2);
+  L.ua = take(sizeof(float) * L.m_pad);
+  L.ub2 = take(sizeof(float) * L.m_pad);
   L.best_s = take(sizeof(float) * L.m_pad);
   L.best_id = take(sizeof(int32_t) * L.m_pad);
   L.cand_s = take(sizeof(float) * L.m_pad * L.n_slots * L.KL);

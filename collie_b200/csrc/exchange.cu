@@ -5,8 +5,8 @@
 // kernel: an entry barrier (every rank's step kernels have finished: its accumulators are
 // complete) and an exit barrier (every owner's stores have landed in every copy) over a small
 // signal pad in symmetric memory, so one step costs one launch instead of fence + kernel + fence.
-// After the exit barrier every rank clears its OWN accumulators (nobody reads them any more),
-// which keeps the zeroing off the links.
+// After the kernel (i.e. after the exit barrier) every rank clears its OWN accumulators with a
+// local memset (nobody reads them any more), which keeps the zeroing off the links.
 //
 // Reference: PyTorch Lightning DDP all-reduces dense gradients of the replicated model between
 // backward and optimizer.step (collie/model/base/trainer.py:463-470 is the single-process form);
@@ -262,15 +262,10 @@ k_item_exchange_update(const PeersDev P, float* __restrict__ M, float* __restric
       st_release_gpu(my + kPadGoExit, P.epoch);
     }
   }
-  if (P.clear_vec > 0) {
-    // nobody reads this rank's accumulators any more: clear them for the next step, locally
-    if (threadIdx.x == 0) spin_until<false>(my + kPadGoExit, P.epoch);
-    __syncthreads();
-    const uint4 z = make_uint4(0, 0, 0, 0);
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < P.clear_vec;
-         i += (int64_t)gridDim.x * blockDim.x)
-      P.clear_ptr[i] = z;
-  }
+  // (nobody reads this rank's accumulators once the kernel has completed: the host clears them
+  // with a memset behind it. Doing it here needed every CTA to wait for the last one, i.e. the
+  // whole grid resident at once next to whatever else runs on the GPU: with a host-fed pipeline's
+  // high-priority copy stream alongside, that hung.)
 }
 
 }  // namespace cmf
@@ -329,8 +324,8 @@ extern "C" int cmf_item_exchange_update(const cmf_peers_t* peers, float* M, floa
   if (blocks < 1) blocks = 1;
   cudaStream_t s = (cudaStream_t)stream;
   const int D = peers->D;
-  // the in-kernel barriers need every CTA resident at once: the grid is capped by what the
-  // instantiation's registers allow per SM
+  // CTAs spin at the entry barrier (and one at the exit barrier): the grid is capped so that they
+  // leave room on every SM for the step's own kernels
 #define LAUNCH(KERNEL)                                                                           \
   do {                                                                                           \
     int occ = 1;                                                                                 \
@@ -353,5 +348,9 @@ extern "C" int cmf_item_exchange_update(const cmf_peers_t* peers, float* M, floa
 #undef CALL
 #undef LAUNCH
   CMF_LAUNCH_CHECK();
+  // the kernel completes after the exit barrier: every rank has finished reading this rank's
+  // accumulators, which are cleared locally for the next step
+  if (fenced && peers->clear_ptr && peers->clear_bytes > 0)
+    CMF_CUDA(cudaMemsetAsync(peers->clear_ptr, 0, peers->clear_bytes, s));
   return CMF_OK;
 }

@@ -678,6 +678,103 @@ def test_merge_of_sharded_topk_lists(n_shards, n_users, k):
     np.testing.assert_allclose(ap.cpu().numpy(), exp_ap.cpu().numpy(), rtol=1e-12, atol=0)
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize('n_shards,precision', [(2, 1), (3, 1), (2, 0)])
+def test_item_shards_merge_to_the_unsharded_result(n_shards, precision):
+    """What evaluate_item_sharded does, on one GPU: every shard of item rows is scored by its own
+    cmf_eval_tile call (item_offset, the users' best target over ALL shards given from outside),
+    the shards' top-k lists are merged by cmf_merge_topk and the MRR counters summed: ids, AP@k and
+    the counter equal the unsharded exact evaluation bit for bit."""
+    from collie_b200 import _abi
+    from collie_b200 import metrics as M
+    n_users, n_items, dim, k = 700, 5003, 128, 10
+    rng = np.random.default_rng(n_shards)
+    tabs = tuple(torch.from_numpy(rng.normal(0, 0.3 / np.sqrt(dim), s).astype(np.float32)).cuda()
+                 for s in ((n_users, dim), (n_items, dim), (n_users, 1), (n_items, 1)))
+    tu = rng.integers(0, n_users, 6 * n_users)
+    ti = rng.integers(0, n_items, 6 * n_users)
+    coo = sp.coo_matrix((np.ones(len(tu)), (tu, ti)), shape=(n_users, n_items))
+    coo.sum_duplicates()
+    tile = np.arange(n_users)
+    indptr, items, nnz = M._targets_device(coo.tocsr(), tile, 'cuda')
+    users = torch.from_numpy(tile.astype(np.int32)).cuda()
+    ex = M._eval_tile('cuda', n_users, n_items, k, indptr, items, {'topk', 'mapk', 'mrr'},
+                      tables=tabs, user_ids=users, precision=0)
+    # the best target of every user over all shards: exact scores of the targets
+    U, I, bu, bi = tabs
+    row_of = torch.repeat_interleave(torch.arange(n_users, device='cuda'), nnz.long())
+    S = torch.full((n_users, n_items), -float('inf'), device='cuda')
+    full = M._eval_tile('cuda', n_users, n_items, n_items if n_items <= 16 else 16, indptr, items,
+                        {'topk'}, tables=tabs, user_ids=users, precision=0)
+    del S, full
+    from collie_b200 import _abi as A
+    sc_all = torch.empty((n_users, n_items), dtype=torch.float32, device='cuda')
+    A.check(A.lib().cmf_score_tile(U.data_ptr(), I.data_ptr(), bu.data_ptr(), bi.data_ptr(), dim,
+                                   users.data_ptr(), n_users, n_items, sc_all.data_ptr(),
+                                   torch.cuda.current_stream().cuda_stream))
+    tsc = sc_all[row_of, items.long()]
+    best_s = torch.full((n_users,), -float('inf'), device='cuda')
+    best_s.scatter_reduce_(0, row_of, tsc, reduce='amax', include_self=True)
+    big = torch.iinfo(torch.int32).max
+    best_id = torch.full((n_users,), big, dtype=torch.int32, device='cuda')
+    at = tsc == best_s[row_of]
+    best_id.scatter_reduce_(0, row_of[at], items[at].int(), reduce='amin', include_self=True)
+    best_id = torch.where(best_id == big, torch.full_like(best_id, -1), best_id)
+    per = (n_items + n_shards - 1) // n_shards
+    all_ids = torch.full((n_shards, n_users, k), -1, dtype=torch.int32, device='cuda')
+    all_s = torch.full((n_shards, n_users, k), -float('inf'), dtype=torch.float32, device='cuda')
+    before = torch.zeros(n_users, dtype=torch.int64, device='cuda')
+    status = torch.zeros(2, dtype=torch.int32, device='cuda')
+    for sh in range(n_shards):
+        lo, hi = sh * per, min((sh + 1) * per, n_items)
+        res = M._eval_tile('cuda', n_users, hi - lo, k, indptr, items, {'topk', 'mrr'},
+                           tables=tabs, user_ids=users, precision=precision, item_offset=lo,
+                           ext_best=(best_s, best_id),
+                           tc_status=status if precision == 1 else None)
+        all_ids[sh], all_s[sh] = res['topk_ids'], res['topk_scores']
+        before += res['n_before_best'].clamp(min=0).long()
+    torch.cuda.synchronize()
+    assert int(status[1]) == 0
+    out_ids = torch.empty((n_users, k), dtype=torch.int32, device='cuda')
+    out_sc = torch.empty((n_users, k), dtype=torch.float32, device='cuda')
+    ap = torch.empty(n_users, dtype=torch.float64, device='cuda')
+    _abi.check(_abi.lib().cmf_merge_topk(all_ids.data_ptr(), all_s.data_ptr(), n_shards, n_users,
+                                         k, indptr.data_ptr(), items.data_ptr(),
+                                         out_ids.data_ptr(), out_sc.data_ptr(), ap.data_ptr(),
+                                         torch.cuda.current_stream().cuda_stream))
+    assert torch.equal(out_ids, ex['topk_ids'])
+    assert torch.equal(out_sc, ex['topk_scores'])
+    assert torch.equal(ap, ex['ap'])
+    has = ex['n_before_best'] >= 0
+    assert torch.equal(before[has], ex['n_before_best'][has].long())
+
+
+@pytest.mark.gpu
+def test_tensor_core_eval_over_tiles_of_unequal_size():
+    """An evaluation of 40,000 users runs as a 32,768-user tile and a smaller one that reuses the
+    item side of the workspace (bf16 copy, per-item bounds, norm order): what the second call
+    finds again must not depend on how many users the tile has."""
+    import collie_b200 as cb
+    n_users, n_items, dim = 40_000, 2_003, 32
+    rng = np.random.default_rng(5)
+    tu = np.repeat(np.arange(n_users), 2)
+    ti = rng.integers(0, n_items, len(tu))
+    test = cb.Interactions(users=tu, items=ti, num_users=n_users, num_items=n_items,
+                           allow_missing_ids=True, check_num_negative_samples_is_valid=False,
+                           max_number_of_samples_to_consider=0)
+    model = cb.MatrixFactorizationModel(train=test, embedding_dim=dim, lr_scheduler_func=None).cuda()
+    with torch.no_grad():
+        for t in _tables(model).values():
+            t.copy_(torch.from_numpy(rng.normal(0, 0.3 / np.sqrt(dim), tuple(t.shape))
+                                     .astype(np.float32)))
+    for metrics in ([cb.mapk], [cb.mapk, cb.mrr]):
+        got = cb.evaluate_in_batches(metrics, test, model, k=10, verbose=False, precision=1)
+        exp = cb.evaluate_in_batches(metrics, test, model, k=10, verbose=False)
+        np.testing.assert_allclose(np.atleast_1d(got), np.atleast_1d(exp), rtol=1e-12)
+        from collie_b200 import metrics as M
+        assert M.LAST_TC_STATUS.get('not_taken_over', 0) == 0, M.LAST_TC_STATUS
+
+
 # ------------------------------------------------------------------------------------ epoch plan
 @pytest.mark.gpu
 @pytest.mark.parametrize('n,batch,n_users,with_gpos', [(10_000, 256, 300, False),
