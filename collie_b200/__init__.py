@@ -14,6 +14,7 @@ from .interactions import (ApproximateNegativeSamplingInteractionsDataLoader,
 from .metrics import (MeanAbsoluteError, MeanSquaredError, auc, evaluate_in_batches,
                       explicit_evaluate_in_batches, get_preds, mapk, mrr)
 from .hybrid import HybridPretrainedModel
+from .cml import CollaborativeMetricLearningModel
 from . import loss  # noqa: F401  (bpr_loss, hinge_loss, adaptive_*, warp_loss)
 from .model import (MatrixFactorizationModel, RowOptimizer, ScaledEmbedding, ZeroEmbedding)
 from .trainer import CollieMinimalTrainer, CollieTrainer
@@ -21,7 +22,8 @@ from .trainer import CollieMinimalTrainer, CollieTrainer
 __version__ = '0.2.0'
 
 __all__ = [
-    'ApproximateNegativeSamplingInteractionsDataLoader', 'CollieMinimalTrainer', 'CollieTrainer',
+    'ApproximateNegativeSamplingInteractionsDataLoader', 'CollaborativeMetricLearningModel',
+    'CollieMinimalTrainer', 'CollieTrainer',
     'ExplicitInteractions', 'HybridPretrainedModel', 'Interactions', 'InteractionsDataLoader',
     'MatrixFactorizationModel',
     'MeanAbsoluteError', 'MeanSquaredError', 'explicit_evaluate_in_batches',

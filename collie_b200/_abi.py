@@ -133,6 +133,11 @@ SIGNATURES = {
     'cmf_eval_tile_noalloc': (C.c_int, [C.POINTER(cmf_eval_t), C.c_void_p]),
     'cmf_score_tile': (C.c_int, [C.c_void_p] * 4 + [C.c_int32, C.c_void_p, C.c_int64, C.c_int64,
                                                    C.c_void_p, C.c_void_p]),
+    'cmf_pairwise_distance': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
+                                        C.c_int32, C.c_int64, C.c_void_p, C.c_void_p]),
+    'cmf_pairwise_distance_backward': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
+                                                 C.c_void_p, C.c_int32, C.c_int64, C.c_void_p,
+                                                 C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'cmf_merge_topk': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_int32,
                                  C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                  C.c_void_p]),

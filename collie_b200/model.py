@@ -107,11 +107,21 @@ class RowOptimizer(torch.optim.Optimizer):
                 opt, st = self.abi_opt(p)
                 rows, dim = (p.shape[0], p.shape[1]) if p.dim() == 2 else (p.numel(), 1)
                 grad = p.grad.contiguous()
+                # SparseAdam moves the rows of the (coalesced) sparse gradient only: the autograd
+                # functions of this package note the rows they gathered on the parameter
+                touched, n_touched = None, 0
+                noted = getattr(p, '_cmf_rows', None)
+                if noted:
+                    if self.rule == 'sparse_adam':
+                        touched = torch.unique(torch.cat([r.reshape(-1).long() for r in noted])) \
+                            .int().contiguous()
+                        n_touched = int(touched.numel())
+                    p._cmf_rows = []
                 with _abi.on_device(p.device):
                     rc = _abi.lib().cmf_optimizer_rows(
                         _abi.ptr(p.data), _abi.ptr(st.get('exp_avg')),
-                        _abi.ptr(st.get('exp_avg_sq')), _abi.ptr(grad), rows, dim, None, 0, opt, 0,
-                        _abi.stream_ptr(p.device))
+                        _abi.ptr(st.get('exp_avg_sq')), _abi.ptr(grad), rows, dim,
+                        _abi.ptr(touched), n_touched, opt, 0, _abi.stream_ptr(p.device))
                 _abi.check(rc, 'cmf_optimizer_rows')
         return loss
 
@@ -132,6 +142,7 @@ class _ScoresFunction(torch.autograd.Function):
         ctx.save_for_backward(U, I, users, items, out)
         ctx.y_range = y_range
         ctx.shapes = (bu.shape, bi.shape)
+        ctx.params = (U, I, bu, bi)
         return out
 
     @staticmethod
@@ -148,6 +159,16 @@ class _ScoresFunction(torch.autograd.Function):
                 users.element_size(), users.shape[0], _abi.ptr(g), _abi.ptr(out), yr, _abi.ptr(gU),
                 _abi.ptr(gI), _abi.ptr(gbu), _abi.ptr(gbi), _abi.stream_ptr(U.device))
         _abi.check(rc, 'cmf_backward_scores')
+        # the rows this call gathered (what torch's sparse embedding gradient would contain):
+        # RowOptimizer('sparse_adam').step() moves those rows only
+        for p, ids in zip(ctx.params, (users, items, users, items)):
+            rows = getattr(p, '_cmf_rows', None)
+            if rows is None:
+                try:
+                    rows = p._cmf_rows = []
+                except AttributeError:
+                    continue
+            rows.append(ids)
         return gU, gI, gbu, gbi, None, None, None
 
 

@@ -436,6 +436,21 @@ CMF_API int cmf_eval_tc_info(int32_t D, double *out);
 CMF_API int cmf_eval_tile_noalloc(const cmf_eval_t *args, void *stream);
 
 /*
+ * Forward / backward of the metric-learning model's score (collie/model/
+ * collaborative_metric_learning.py:100-124): out[r] = || U[users[r]] - I[items[r]] + 1e-6 ||_2
+ * (torch.nn.functional.pairwise_distance: both gathers and the reduction in one kernel), and
+ * gU[users[r]] += grad_out[r] * (U[u] - I[i] + 1e-6) / dist[r], gI[items[r]] -= the same (dense
+ * gradient tables, zero where dist is 0; either may be NULL). ids: int32 or int64.
+ */
+CMF_API int cmf_pairwise_distance(const float *U, const float *I, int32_t D, const void *users,
+                          const void *items, int32_t idx_bytes, int64_t n, float *out,
+                          void *stream);
+CMF_API int cmf_pairwise_distance_backward(const float *U, const float *I, int32_t D, const void *users,
+                                   const void *items, int32_t idx_bytes, int64_t n,
+                                   const float *grad_out, const float *dist, float *gU, float *gI,
+                                   void *stream);
+
+/*
  * Item-sharded evaluation, merge step (distributed.py evaluate_item_sharded): ids / scores are the
  * all-gathered per-shard top-k lists [n_shards][n_users][k] (ids < 0 = padding; the shards score
  * disjoint item blocks), merged per user into the global top-k in the canonical order (score

@@ -325,6 +325,51 @@ def hybrid_case(seed, freeze, n_users=37, n_items=53, dim=12, n_meta=6, n_neg=4,
     return out
 
 
+def cml_case(seed, optimizer='adam', sparse=False, loss='hinge', n_users=37, n_items=53, dim=12,
+             n_neg=4, batch=64, steps=3):
+    """``CollaborativeMetricLearningModel`` of the reference (collaborative_metric_learning.py:
+    86-124: two embedding tables, prediction = pairwise_distance): predictions, and losses + both
+    tables after ``steps`` iterations of the reference's own loop with injected negatives."""
+    from collie.model import CollaborativeMetricLearningModel
+    rng = np.random.default_rng(seed)
+    torch.manual_seed(seed)
+    users, items = synthetic_pairs(rng, n_users, n_items, 400)
+    train = Interactions(users=users, items=items, ratings=np.ones(len(users)),
+                         num_negative_samples=n_neg, num_users=n_users, num_items=n_items,
+                         allow_missing_ids=True, remove_duplicate_user_item_pairs=False,
+                         check_num_negative_samples_is_valid=False)
+    model = CollaborativeMetricLearningModel(train=train, embedding_dim=dim, sparse=sparse, lr=1e-2,
+                                             optimizer=optimizer, loss=loss, lr_scheduler_func=None)
+    with torch.no_grad():
+        for p in model.parameters():
+            p.copy_(torch.from_numpy(rng.normal(0, 0.5, size=tuple(p.shape)).astype(np.float32)))
+    out = {'n_users': n_users, 'n_items': n_items, 'dim': dim, 'n_neg': n_neg, 'lr': 1e-2}
+    for k, v in model.state_dict().items():
+        out['init_' + k] = v.detach().numpy().copy()
+    model.eval()
+    pu, pi = rng.integers(0, n_users, 80), rng.integers(0, n_items, 80)
+    with torch.no_grad():
+        out['pred_users'], out['pred_items'] = pu, pi
+        out['preds'] = model(torch.from_numpy(pu), torch.from_numpy(pi)).numpy()
+    model.train()
+    opt = model.configure_optimizers()
+    assert isinstance(opt, torch.optim.Optimizer)
+    for s in range(steps):
+        bu = rng.integers(0, n_users, batch)
+        bp = rng.integers(0, n_items, batch)
+        bn = rng.integers(0, n_items, (batch, n_neg))
+        b = ((torch.from_numpy(bu), torch.from_numpy(bp)), torch.from_numpy(bn))
+        opt.zero_grad()
+        loss = model.calculate_loss(b)
+        loss.backward()
+        opt.step()
+        out[f'step{s}_users'], out[f'step{s}_pos'], out[f'step{s}_negs'] = bu, bp, bn
+        out[f'step{s}_loss'] = float(loss.detach())
+    for k, v in model.state_dict().items():
+        out['final_' + k] = v.detach().numpy().copy()
+    return out
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     cases = {
@@ -349,8 +394,17 @@ def main():
         'metrics_exact_grid': metrics_case(42, exact_grid=True),
         'metrics_d128': metrics_case(43, n_users=64, n_items=333, dim=128, n_test=700),
     }
-    if len(sys.argv) > 1 and sys.argv[1] in ('similarity', 'checkpoint', 'hybrid'):   # the cases added later
+    if len(sys.argv) > 1 and sys.argv[1] in ('similarity', 'checkpoint', 'hybrid', 'cml'):   # the cases added later
         cases = {}
+    if len(sys.argv) > 1 and sys.argv[1] == 'cml':
+        cases = {'cml_hinge_adam': cml_case(91),
+                 'cml_adaptive_sparse_adam': cml_case(92, optimizer='sparse_adam', sparse=True,
+                                                      loss='adaptive_hinge', dim=32),
+                 'cml_bpr_sgd': cml_case(93, optimizer='sgd', loss='bpr', dim=7)}
+        for name, arrays in cases.items():
+            np.savez_compressed(os.path.join(OUT, name + '.npz'), **arrays)
+            print(name, 'ok')
+        return
     if len(sys.argv) > 1 and sys.argv[1] == 'hybrid':
         cases = {'hybrid_frozen': hybrid_case(81, True),
                  'hybrid_unfrozen': hybrid_case(82, False),
