@@ -49,10 +49,8 @@ class _PairwiseDistance(torch.autograd.Function):
         _abi.check(rc, 'cmf_pairwise_distance_backward')
         # the rows this step gathered: what torch's sparse embedding gradient would contain
         for p, ids, need in ((ctx.params[0], users, need_u), (ctx.params[1], items, need_i)):
-            if need:
-                rows = getattr(p, '_cmf_rows', None)
-                if rows is None:
-                    rows = p._cmf_rows = []
+            rows = getattr(p, '_cmf_rows', None)     # (set by RowOptimizer('sparse_adam'))
+            if need and rows is not None:
                 rows.append(ids)
         return gU, gI, None, None
 

@@ -66,6 +66,13 @@ class RowOptimizer(torch.optim.Optimizer):
         defaults = dict(lr=lr, weight_decay=weight_decay, betas=betas, eps=eps)
         super().__init__(params, defaults)
         self.rule = rule
+        if rule == 'sparse_adam':
+            # step() moves only the rows a step gathered: the autograd functions of this package
+            # note them on parameters that carry this list
+            for group in self.param_groups:
+                for p in group['params']:
+                    if not hasattr(p, '_cmf_rows'):
+                        p._cmf_rows = []
 
     def state_for(self, p):
         st = self.state[p]
@@ -163,12 +170,8 @@ class _ScoresFunction(torch.autograd.Function):
         # RowOptimizer('sparse_adam').step() moves those rows only
         for p, ids in zip(ctx.params, (users, items, users, items)):
             rows = getattr(p, '_cmf_rows', None)
-            if rows is None:
-                try:
-                    rows = p._cmf_rows = []
-                except AttributeError:
-                    continue
-            rows.append(ids)
+            if rows is not None:
+                rows.append(ids)
         return gU, gI, gbu, gbi, None, None, None
 
 
