@@ -41,6 +41,21 @@ def test_argument_errors_without_gpu():
     assert b'unknown key' in lib.cmf_last_error()
     rc = lib.cmf_forward_scores(None, None, None, None, 8, None, None, 4, 0, None, None, None)
     assert rc == -1 and b'null' in lib.cmf_last_error()
+    # the entry points added in round 2 refuse bad arguments before they touch a device
+    rc = lib.cmf_merge_topk(None, None, 2, 10, 5, None, None, None, None, None, None)
+    assert rc != 0 and b'null' in lib.cmf_last_error()
+    one = (_abi.C.c_int32 * 1)()
+    onef = (_abi.C.c_float * 1)()
+    rc = lib.cmf_merge_topk(one, onef, 2, 10, 64, None, None, None, None, None, None)
+    assert rc != 0 and b'k <= 32' in lib.cmf_last_error()
+    rc = lib.cmf_pairwise_distance(None, None, 8, None, None, 4, 0, None, None)
+    assert rc != 0 and b'null' in lib.cmf_last_error()
+    rc = lib.cmf_pairwise_distance(onef, onef, 8, one, one, 2, 1, onef, None)
+    assert rc != 0 and b'int32 or int64' in lib.cmf_last_error()
+    assert lib.cmf_exchange_pad_bytes() == 128
+    info = (_abi.C.c_double * 4)()
+    assert lib.cmf_eval_tc_info(128, info) == 0
+    assert info[0] == 144 and info[1] == 400 and 0 < info[3] < info[2] < 1e-2
 
 
 def _pairs(n_users=20, n_items=30, n=200, seed=0):
