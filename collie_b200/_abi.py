@@ -133,6 +133,10 @@ SIGNATURES = {
     'cmf_eval_tile_noalloc': (C.c_int, [C.POINTER(cmf_eval_t), C.c_void_p]),
     'cmf_score_tile': (C.c_int, [C.c_void_p] * 4 + [C.c_int32, C.c_void_p, C.c_int64, C.c_int64,
                                                    C.c_void_p, C.c_void_p]),
+    'cmf_ingest_workspace_bytes': (C.c_size_t, [C.c_int64]),
+    'cmf_ingest_pairs': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64,
+                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                   C.c_void_p, C.c_size_t, C.c_void_p]),
     'cmf_pairwise_distance': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
                                         C.c_int32, C.c_int64, C.c_void_p, C.c_void_p]),
     'cmf_pairwise_distance_backward': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,

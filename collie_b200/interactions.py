@@ -36,6 +36,33 @@ def _check_all_ids_present(array, max_value, name):
             '``allow_missing_ids=True`` to skip this check.')
 
 
+# inputs of at least this many entries are de-duplicated on the device (when there is one)
+_DEVICE_INGEST_MIN = 1 << 18
+
+
+def _ingest_on_device(row, col, num_users, num_items, device=None):
+    """``cmf_ingest_pairs``: positions kept (first occurrence of every pair, dataset order), the
+    positions their values come from (last occurrence), and ``(device, indptr, csr_items)``."""
+    dev = torch.device('cuda', torch.cuda.current_device()) if device is None else device
+    n = int(len(row))
+    u = torch.from_numpy(np.ascontiguousarray(row, dtype=np.int32)).to(dev)
+    i = torch.from_numpy(np.ascontiguousarray(col, dtype=np.int32)).to(dev)
+    keep_pos = torch.empty(n, dtype=torch.int32, device=dev)
+    keep_val = torch.empty(n, dtype=torch.int32, device=dev)
+    n_out = torch.zeros(1, dtype=torch.int64, device=dev)
+    indptr = torch.empty(int(num_users) + 1, dtype=torch.int64, device=dev)
+    csr_items = torch.empty(n, dtype=torch.int32, device=dev)
+    ws = torch.empty(int(_abi.lib().cmf_ingest_workspace_bytes(n)), dtype=torch.uint8, device=dev)
+    with _abi.on_device(dev):
+        _abi.check(_abi.lib().cmf_ingest_pairs(
+            _abi.ptr(u), _abi.ptr(i), n, int(num_users), int(num_items), _abi.ptr(keep_pos),
+            _abi.ptr(keep_val), _abi.ptr(n_out), _abi.ptr(indptr), _abi.ptr(csr_items),
+            _abi.ptr(ws), ws.numel(), _abi.stream_ptr(dev)), 'cmf_ingest_pairs')
+    m = int(n_out.item())
+    return (keep_pos[:m].cpu().numpy().astype(np.int64), keep_val[:m].cpu().numpy().astype(np.int64),
+            (dev, indptr, csr_items[:m].clone()))
+
+
 def _infer_num(num, array):
     if num == 'infer':
         return int(np.max(array)) + 1
@@ -77,7 +104,16 @@ class BaseInteractions(torch.utils.data.Dataset):
                 _check_all_ids_present(mat.row, num_users, 'mat.shape[0]')
                 _check_all_ids_present(mat.col, num_items, 'mat.shape[1]')
 
-        if remove_duplicate_user_item_pairs:
+        self._ingest_csr = None
+        if remove_duplicate_user_item_pairs and mat.nnz >= _DEVICE_INGEST_MIN \
+                and torch.cuda.is_available():
+            # large inputs: the same rule (below) applied by ``cmf_ingest_pairs`` on the device,
+            # which also leaves the positives CSR there
+            pos, val, csr = _ingest_on_device(mat.row, mat.col, mat.shape[0], mat.shape[1])
+            if len(pos) != mat.nnz:
+                mat = coo_matrix((mat.data[val], (mat.row[pos], mat.col[pos])), shape=mat.shape)
+            self._ingest_csr = csr
+        elif remove_duplicate_user_item_pairs:
             # a duplicated (user, item) pair stays at the position of its FIRST occurrence and
             # takes the value of its LAST one: the reference pushes the entries through a dict
             # (``dok_matrix._update`` + ``tocoo``, datasets.py:137-146), which keeps insertion
@@ -218,6 +254,9 @@ class Interactions(BaseInteractions):
 
     def _extra_device_state(self, st, device):
         # positives CSR (sorted item ids per user) replaces the reference's set((row, col))
+        if self._ingest_csr is not None and self._ingest_csr[0] == device:
+            st['indptr'], st['csr_items'] = self._ingest_csr[1], self._ingest_csr[2]
+            return
         csr = self.mat.tocsr()
         csr.sort_indices()
         st['indptr'] = torch.from_numpy(csr.indptr.astype(np.int64)).to(device)

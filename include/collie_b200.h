@@ -436,6 +436,21 @@ CMF_API int cmf_eval_tc_info(int32_t D, double *out);
 CMF_API int cmf_eval_tile_noalloc(const cmf_eval_t *args, void *stream);
 
 /*
+ * Dataset ingest on the device (collie/interactions/datasets.py:81-155, 359-366): of every
+ * duplicated (user, item) pair the FIRST position and the LAST value are kept, as the reference's
+ * dict-backed construction does -- keep_pos[j] / keep_val[j] (j < *n_out, dataset order; both
+ * arrays have room for n) are the position whose (user, item) and the position whose rating
+ * entry j of the de-duplicated dataset takes -- and the positives CSR falls out of the same sort:
+ * indptr [num_users + 1], csr_items [n] (the first *n_out are valid: distinct items per user,
+ * ascending). n_out, indptr, csr_items are device memory; indptr / csr_items may both be NULL.
+ */
+CMF_API size_t cmf_ingest_workspace_bytes(int64_t n);
+CMF_API int cmf_ingest_pairs(const int32_t *users, const int32_t *items, int64_t n, int64_t num_users,
+                     int64_t num_items, int32_t *keep_pos, int32_t *keep_val, int64_t *n_out,
+                     int64_t *indptr, int32_t *csr_items, void *workspace, size_t workspace_bytes,
+                     void *stream);
+
+/*
  * Forward / backward of the metric-learning model's score (collie/model/
  * collaborative_metric_learning.py:100-124): out[r] = || U[users[r]] - I[items[r]] + 1e-6 ||_2
  * (torch.nn.functional.pairwise_distance: both gathers and the reduction in one kernel), and

@@ -775,6 +775,44 @@ def test_tensor_core_eval_over_tiles_of_unequal_size():
         assert M.LAST_TC_STATUS.get('not_taken_over', 0) == 0, M.LAST_TC_STATUS
 
 
+@pytest.mark.gpu
+def test_device_ingest_equals_the_host_rule(monkeypatch):
+    """cmf_ingest_pairs (large inputs): a duplicated (user, item) pair keeps its FIRST position and
+    its LAST value, like the reference's dict-backed construction (datasets.py:137-146), and the
+    positives CSR left on the device equals scipy's."""
+    import collie_b200 as cb
+    from collie_b200 import interactions as X
+    rng = np.random.default_rng(8)
+    n_users, n_items, n = 3000, 700, 400_000                   # ~17 % duplicates
+    users, items = rng.integers(0, n_users, n), rng.integers(0, n_items, n)
+    ratings = rng.integers(1, 6, n).astype(np.float64)
+    dev = cb.ExplicitInteractions(users=users, items=items, ratings=ratings, num_users=n_users,
+                                  num_items=n_items, allow_missing_ids=True)
+    assert dev._ingest_csr is not None
+    monkeypatch.setattr(X, '_DEVICE_INGEST_MIN', 1 << 60)      # the host rule
+    host = cb.ExplicitInteractions(users=users, items=items, ratings=ratings, num_users=n_users,
+                                   num_items=n_items, allow_missing_ids=True)
+    assert host._ingest_csr is None and host.num_interactions < n
+    np.testing.assert_array_equal(dev.mat.row, host.mat.row)
+    np.testing.assert_array_equal(dev.mat.col, host.mat.col)
+    np.testing.assert_array_equal(dev.mat.data, host.mat.data)
+    monkeypatch.undo()
+    imp = cb.Interactions(users=users, items=items, num_users=n_users, num_items=n_items,
+                          allow_missing_ids=True, check_num_negative_samples_is_valid=False)
+    st = imp.device_state(torch.device('cuda', torch.cuda.current_device()))
+    csr = imp.mat.tocsr()
+    csr.sort_indices()
+    np.testing.assert_array_equal(st['indptr'].cpu().numpy(), csr.indptr)
+    np.testing.assert_array_equal(st['csr_items'].cpu().numpy(), csr.indices)
+    # no duplicates at all: everything is kept, in order
+    flat = rng.choice(n_users * n_items, size=300_000, replace=False)
+    uniq = cb.Interactions(users=flat // n_items, items=flat % n_items, num_users=n_users,
+                           num_items=n_items, allow_missing_ids=True,
+                           check_num_negative_samples_is_valid=False)
+    np.testing.assert_array_equal(uniq.mat.row, flat // n_items)
+    np.testing.assert_array_equal(uniq.mat.col, flat % n_items)
+
+
 # ------------------------------------------------------------------------------------ epoch plan
 @pytest.mark.gpu
 @pytest.mark.parametrize('n,batch,n_users,with_gpos', [(10_000, 256, 300, False),
